@@ -1,0 +1,116 @@
+"""Synthetic structured-AMR inputs in the reference's "exajet cells" format.
+
+cells   : int32[N,4] = {x, y, z, level}, level 0 = finest, cell width 1<<level
+          (reference: builder/builder.cpp:120-134, README.md:76-82)
+scalars : float32[N], same order (tools/artificial/artificial.cpp:177-178)
+
+`grids_to_cells` restates tools/artificial/artificial.cpp:58-88,131-165 (exaArtificial) so
+the reference's ex0..ex4.grids fixtures can be expanded anywhere; `nested_boxes` makes the
+nested-refinement shapes SURVEY.md §8(d) names for configs C1/C2.
+"""
+import numpy as np
+
+_M64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def splitmix64(x):
+    """vectorised splitmix64 finaliser over uint64 counters"""
+    with np.errstate(over="ignore"):
+        z = (x + np.uint64(0x9E3779B97F4A7C15)) & _M64
+        z = ((z ^ (z >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)) & _M64
+        z = ((z ^ (z >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)) & _M64
+        return z ^ (z >> np.uint64(31))
+
+
+def uniform01(n, seed):
+    """n floats in [0,1) from splitmix64(seed + i)"""
+    with np.errstate(over="ignore"):
+        ctr = np.arange(n, dtype=np.uint64) + np.uint64(seed)
+    return (splitmix64(ctr) >> np.uint64(40)).astype(np.float32) * np.float32(1.0 / (1 << 24))
+
+
+def random_points(n, lo, hi, seed=1):
+    u = uniform01(3 * n, seed).reshape(n, 3)
+    lo = np.asarray(lo, np.float32)
+    hi = np.asarray(hi, np.float32)
+    return (lo + u * (hi - lo)).astype(np.float32)
+
+
+def grids_to_cells(text):
+    """exaArtificial: one box per line 'minx miny minz nx ny nz level v0 [v1..v7]'"""
+    cells, scalars = [], []
+    for line in text.splitlines():
+        tok = line.split()
+        if len(tok) not in (8, 15):
+            continue
+        mc = [int(t, 0) for t in tok[:3]]
+        nx, ny, nz, level = (int(t, 0) for t in tok[3:7])
+        v = [np.float32(t) for t in tok[7:]]
+        if len(v) == 1:
+            v = v * 8
+        cs = 1 << level
+        maxc = [mc[0] + (nx - 1) * cs, mc[1] + (ny - 1) * cs, mc[2] + (nz - 1) * cs]
+        f32 = np.float32
+        lerp = lambda a, b, x: (f32(1) - x) * a + x * b
+        for cz in range(mc[2], maxc[2] + 1, cs):
+            for cy in range(mc[1], maxc[1] + 1, cs):
+                for cx in range(mc[0], maxc[0] + 1, cs):
+                    x = f32(cx - mc[0]) / (f32(maxc[0]) - f32(mc[0]) + f32(1))
+                    y = f32(cy - mc[1]) / (f32(maxc[1]) - f32(mc[1]) + f32(1))
+                    z = f32(cz - mc[2]) / (f32(maxc[2]) - f32(mc[2]) + f32(1))
+                    cells.append((cx, cy, cz, level))
+                    scalars.append(lerp(lerp(lerp(v[0], v[1], x), lerp(v[2], v[3], x), y),
+                                        lerp(lerp(v[4], v[5], x), lerp(v[6], v[7], x), y), z))
+    return np.array(cells, np.int32).reshape(-1, 4), np.array(scalars, np.float32)
+
+
+def _box_cells(lo, hi, level, hole=None):
+    """all level-`level` cells tiling [lo,hi)^3 (3-vectors) except those inside `hole`"""
+    cw = 1 << level
+    ax = [np.arange(lo[d], hi[d], cw, dtype=np.int32) for d in range(3)]
+    z, y, x = np.meshgrid(ax[2], ax[1], ax[0], indexing="ij")
+    x, y, z = x.ravel(), y.ravel(), z.ravel()
+    if hole is not None:
+        hl, hh = hole
+        inside = ((x >= hl[0]) & (x < hh[0]) & (y >= hl[1]) & (y < hh[1]) & (z >= hl[2]) & (z < hh[2]))
+        x, y, z = x[~inside], y[~inside], z[~inside]
+    out = np.empty((len(x), 4), np.int32)
+    out[:, 0], out[:, 1], out[:, 2], out[:, 3] = x, y, z, level
+    return out
+
+
+def nested_boxes(domain, boxes):
+    """Nested refinement: boxes[k] = (lo, hi) (ints or 3-vectors) is the region refined to
+    level <= k; level len(boxes) fills the rest of [0,domain)^3.  E.g. SURVEY C1:
+    nested_boxes(256, [(72,184), (32,224)]) -> L0 in [72,184)^3, L1 shell to [32,224)^3,
+    L2 elsewhere (2 265 600 cells)."""
+    def v3(a):
+        return np.array([a, a, a] if np.isscalar(a) else a, np.int64)
+    dom_lo, dom_hi = v3(0), v3(domain)
+    parts, hole = [], None
+    for k, (lo, hi) in enumerate(boxes):
+        lo, hi = v3(lo), v3(hi)
+        parts.append(_box_cells(lo, hi, k, hole))
+        hole = (lo, hi)
+    parts.append(_box_cells(dom_lo, dom_hi, len(boxes), hole))
+    return np.concatenate(parts)
+
+
+def analytic_field(cells, domain, channel=0, noise=0.05):
+    """s = 0.5 + 0.5 sin(2pi x/Lx) cos(2pi y/Ly) sin(2pi z/Lz + phi_c) + noise*U(-1,1)
+    evaluated at cell centres; noise from splitmix64 seeded 0xE8AB51C4 + channel."""
+    cells = np.asarray(cells)
+    L = np.array([domain] * 3 if np.isscalar(domain) else domain, np.float64)
+    cw = (1 << cells[:, 3]).astype(np.float64)
+    c = cells[:, :3].astype(np.float64) + 0.5 * cw[:, None]
+    phi = 0.7 * channel
+    s = 0.5 + 0.5 * np.sin(2 * np.pi * c[:, 0] / L[0]) * np.cos(2 * np.pi * c[:, 1] / L[1]) * np.sin(2 * np.pi * c[:, 2] / L[2] + phi)
+    u = uniform01(len(cells), 0xE8AB51C4 + channel).astype(np.float64)
+    return (s + noise * (2.0 * u - 1.0)).astype(np.float32)
+
+
+def linear_field(cells, coef=(0.01, 0.02, 0.03), offset=0.1):
+    cells = np.asarray(cells)
+    cw = (1 << cells[:, 3]).astype(np.float64)
+    c = cells[:, :3].astype(np.float64) + 0.5 * cw[:, None]
+    return (offset + c @ np.asarray(coef, np.float64)).astype(np.float32)

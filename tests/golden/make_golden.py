@@ -1,0 +1,66 @@
+"""Generate tests/golden/*.npz from the reference's OWN code (oracle/_ref, built by
+`make -C oracle ref` from /root/reference in place).  Run in the build container only:
+
+    python tests/golden/make_golden.py
+
+Each fixture holds the input (cells, scalar fields) and the reference's outputs:
+the bytes of the .bricks file written by exaBuilder (builder/builder.cpp:895-902) and the
+regions/leafList produced by ExaBrickRegions::buildFrom (exa/Regions.cpp:242-320) dumped
+by oracle/ref_abr_main.cpp.  Large cases are pinned by SHA-256 only (golden_hashes.json).
+"""
+import hashlib, json, os, sys, tempfile
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import orc                     # noqa: E402
+from owlexabrick_b200 import synth         # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_GRIDS = "/root/reference/tools/artificial"
+
+
+def cases():
+    for i in range(5):
+        c, s = synth.grids_to_cells(open("%s/ex%d.grids" % (REF_GRIDS, i)).read())
+        yield "ex%d" % i, c, [s], 127, True
+    c = synth.nested_boxes(64, [(18, 46), (8, 56)])
+    yield "nb64", c, [synth.analytic_field(c, 64, 0), synth.analytic_field(c, 64, 1)], 127, True
+    yield "nb64_mlw8", c, [synth.analytic_field(c, 64, 0)], 8, True
+    # duplicates + a shuffled order exercise the dedup path (builder.cpp:301-350)
+    rng = np.random.RandomState(7)
+    c2 = np.concatenate([c, c[rng.randint(0, len(c), 500)]])
+    perm = rng.permutation(len(c2))
+    c2 = c2[perm]
+    yield "nb64_dups", c2, [synth.analytic_field(c2, 64, 0)], 127, True
+    c = synth.nested_boxes(256, [(72, 184), (32, 224)])          # SURVEY config C1
+    yield "C1", c, [synth.analytic_field(c, 256, 0)], 127, False
+
+
+def main():
+    assert orc.have_ref(), "run `make -C oracle ref` first (needs /root/reference)"
+    hashes = {}
+    for name, cells, fields, mlw, store in cases():
+        with tempfile.TemporaryDirectory() as d:
+            # exaArtificial is also exercised for the ex* cases: its .cells must equal ours
+            if name.startswith("ex"):
+                import subprocess
+                subprocess.check_call([os.path.join(orc.REF_DIR, "exaArtificial"), "%s/%s.grids" % (REF_GRIDS, name),
+                                       "-o", os.path.join(d, "a")], stdout=subprocess.DEVNULL)
+                assert np.array_equal(np.fromfile(os.path.join(d, "a.cells"), np.int32).reshape(-1, 4), cells)
+                assert np.array_equal(np.fromfile(os.path.join(d, "a.scalars"), np.float32), fields[0])
+            bricks = orc.ref_build_bricks(cells, d, None if mlw == 127 else mlw)
+            abr = orc.ref_build_abr(bricks, fields, d)
+        hashes[name] = {"cells": len(cells), "max_leaf_width": mlw,
+                        "bricks_sha256": hashlib.sha256(bricks).hexdigest(),
+                        "abr_sha256": hashlib.sha256(abr).hexdigest()}
+        if store:
+            np.savez_compressed(os.path.join(HERE, name + ".npz"), cells=cells, fields=np.stack(fields),
+                                bricks=np.frombuffer(bricks, np.uint8), abr=np.frombuffer(abr, np.uint8),
+                                max_leaf_width=mlw)
+        print(name, hashes[name])
+    json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
