@@ -1,0 +1,294 @@
+/* exabrick_b200.h — C ABI of libexabrick_b200.so
+ *
+ * Drop-in boundary for the ExaBricks rendering hot path of owl-project/owlExaBrick
+ * (reference paths below are relative to the reference repo root).  The reference has no
+ * FFI; its boundary is the C++ class exa::OptixRenderer (exa/OptixRenderer.h:32-188) plus
+ * POD structs (programs/*.h) and file formats.  Every entry point here names the
+ * reference interface it replaces.  The C++ mirror of the reference classes on top of
+ * this ABI is include/exa/exa.hpp; INTEGRATION.md shows the reference-side binding.
+ *
+ * Conventions: every function returns EXA_OK (0) or an error code; the message of the last
+ * error on the calling thread is exa_last_error().  No function falls back to the CPU:
+ * device entry points fail with EXA_ERR_CUDA when no sm_100 device/driver is usable.
+ * Handles are not thread-safe (same as the reference: one GLUT thread drives everything).
+ */
+#ifndef EXABRICK_B200_H
+#define EXABRICK_B200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+  EXA_OK = 0,
+  EXA_ERR_INVALID = 1,   /* bad argument / malformed input (reference: std::runtime_error) */
+  EXA_ERR_IO = 2,        /* file could not be opened / read */
+  EXA_ERR_CUDA = 3,      /* CUDA runtime error or no usable device */
+  EXA_ERR_LIMIT = 4      /* a size limit was exceeded */
+};
+
+#define EXA_NUM_XF_VALUES      128   /* exa/common.h:40 */
+#define EXA_MAX_CHANNELS       10    /* exa/common.h:42 */
+#define EXA_MAX_ISO_SURFACES   2     /* exa/common.h:43 */
+#define EXA_MAX_CONTOUR_PLANES 3     /* exa/common.h:44 */
+
+/* ---------------------------------------------------------------------------------------
+ * POD contract (layouts probed from the reference with g++ 13 / x86-64)
+ * ------------------------------------------------------------------------------------- */
+
+/* programs/Brick.h:31-71 — 32 bytes */
+typedef struct ExaBrick {
+  int32_t  lower[3];
+  int32_t  size[3];
+  int32_t  level;
+  uint32_t begin;      /* offset of the brick's first cell in the flattened scalar arrays */
+} ExaBrick;
+
+/* exa/Regions.h:31-41 (ExaBrickRegions::BrickRegion == SameBricksRegion) — 44 bytes */
+typedef struct ExaBrickRegion {
+  float   domain_lower[3], domain_upper[3];
+  float   valueRange_lower, valueRange_upper;
+  int32_t leafListBegin, leafListSize;
+  float   finestLevelCellWidth;
+} ExaBrickRegion;
+
+/* exa/KdTree.h:25-135 — 12 bytes, as written by `exaBuilder -kd` */
+typedef struct ExaKdTreeNode {
+  uint32_t split_or_first_prim;
+  uint32_t axis_bits;          /* axis<<30 | (first_child or num_prims) */
+  int32_t  max_level;
+} ExaKdTreeNode;
+
+/* programs/FrameState.h:29-71 — 408 bytes */
+typedef struct ExaFrameState {
+  struct { float pos[3], dir00[3], dirDu[3], dirDv[3]; } camera;                 /*   0 */
+  struct { uint8_t enabled; uint8_t _p[3]; float value; int32_t channel; }
+      isoSurface[EXA_MAX_ISO_SURFACES];                                          /*  48 */
+  struct { uint8_t enabled; uint8_t _p[3]; float normal[3]; int32_t channel; float offset; }
+      contourPlane[EXA_MAX_CONTOUR_PLANES];                                      /*  72 */
+  struct { float lower[3], upper[3]; uint8_t enabled; uint8_t _p[3]; } clipBox;  /* 144 */
+  struct { float length; uint8_t enabled; uint8_t _p[3]; } ao;                   /* 172 */
+  float    clockScale;                                                           /* 180 */
+  struct { float vx[3], vy[3], vz[3], p[3]; } voxelSpaceTransform;               /* 184 */
+  int32_t  frameID;                                                              /* 232 */
+  float    xfDomain[EXA_MAX_CHANNELS][2];                                        /* 236 */
+  uint32_t _pad0;                                                                /* 316 */
+  uint64_t xfTexture[EXA_MAX_CHANNELS];  /* cudaTextureObject_t in the reference; here:
+                                            device pointers to float4[128] tables   320 */
+  float    xfOpacityScale;                                                       /* 400 */
+  uint32_t _pad1;
+} ExaFrameState;
+
+/* programs/LaunchParams.h:26-80 — 240 bytes.  The four OptixTraversableHandle slots
+ * become opaque 64-bit device pointers (kd-tree node arrays / activity masks). */
+typedef struct ExaLaunchParams {
+  int32_t  deviceIndex, deviceCount;                                             /*   0 */
+  uint64_t volumeBVH, surfaceModel, isoSurfaceBVH, streamlineBVH;                /*   8 */
+  uint32_t fbSize[2];                                                            /*  40 */
+  float    worldSpaceBounds_lo[3], worldSpaceBounds_hi[3];                       /*  48 */
+  float    voxelSpaceBounds_lo[3], voxelSpaceBounds_hi[3];                       /*  72 */
+  uint64_t colorBufferPtr;                                                       /*  96 */
+  uint64_t accumBufferPtr;                                                       /* 104 */
+  uint64_t frameStateBuffer;                                                     /* 112 */
+  float    dt; uint32_t _pad0;                                                   /* 120 */
+  uint64_t sameBrickRegionsBuffer;                                               /* 128 */
+  uint64_t sameBrickRegionsLeafList;                                             /* 136 */
+  uint64_t brickBuffer;                                                          /* 144 */
+  uint64_t scalarBuffers;                                                        /* 152 */
+  uint64_t scalarBufferOffsets;                                                  /* 160 */
+  uint64_t primaryChannels;                                                      /* 168 */
+  int32_t  colormapChannel, numPrimaryChannels;                                  /* 176 */
+  int32_t  gradientShadingDVR, gradientShadingISO;                               /* 184 */
+  int32_t  tracerEnabled; uint32_t _pad1;                                        /* 192 */
+  uint64_t traces;                                                               /* 200 */
+  int32_t  tracerChannels[3];                                                    /* 208 */
+  int32_t  numTraces, numTimesteps;                                              /* 220 */
+  float    steplen;                                                              /* 228 */
+  uint64_t currentTimestep;                                                      /* 232 */
+} ExaLaunchParams;
+
+/* counters behind the algorithmic-bytes model of SURVEY.md §8(d) / BASELINE.md §2 */
+typedef struct ExaStats {
+  uint64_t samples;       /* sample x channel reconstructions */
+  uint64_t brickVisits;   /* sum over samples of bricks looped (4+32 B each) */
+  uint64_t cornerLoads;   /* sum n_k: scalar loads issued (4 B each) */
+  uint64_t segments;      /* region segments integrated (44 B each) */
+} ExaStats;
+
+const char *exa_last_error(void);
+/* 1 if a CUDA device of compute capability 10.x is usable, else 0 (message set) */
+int exa_cuda_available(void);
+void exa_free(void *p);
+
+/* ---------------------------------------------------------------------------------------
+ * ExaBricks container — replaces exa::ExaBricks (exa/ExaBricks.h:23-45) and the builder
+ * executable exaBuilder (builder/builder.cpp:836-915)
+ * ------------------------------------------------------------------------------------- */
+typedef struct exa_bricks exa_bricks_t;
+
+enum { EXA_BUILDER_SPATIAL_MEDIAN = 0, EXA_BUILDER_SAH_ALIKE = 1 };   /* builder.cpp:31-33 */
+
+/* exaBuilder in.cells -o out.bricks: cells = numCells x {x,y,z,level}
+ * (loadExaJet builder.cpp:813-834; Bricker builder.cpp:406-811).  Output brick order and
+ * cell IDs are bit-exact with the reference's serial builder.  maxLeafWidth: 127 default
+ * (builder.cpp:50). */
+int exa_bricks_build(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth,
+                     exa_bricks_t **out);
+/* ExaBricks::load (exa/ExaBricks.cpp:21-55) */
+int exa_bricks_load(const char *fileName, exa_bricks_t **out);
+int exa_bricks_from_memory(const void *bytes, size_t numBytes, exa_bricks_t **out);
+/* writer of builder.cpp:895-902 (+ optional kd file, :904-907; NULL to skip) */
+int exa_bricks_save(const exa_bricks_t *b, const char *bricksFileName, const char *kdFileName);
+void exa_bricks_destroy(exa_bricks_t *b);
+size_t exa_bricks_count(const exa_bricks_t *b);
+size_t exa_bricks_num_cells(const exa_bricks_t *b);          /* ExaBricks::totalNumCells */
+/* flattened view = what OptixRenderer's ctor builds (exa/OptixRenderer.cpp:71-93) */
+const ExaBrick *exa_bricks_headers(const exa_bricks_t *b);
+const int32_t *exa_bricks_cell_ids(const exa_bricks_t *b);   /* indexVector */
+/* ExaBricks::getBounds (exa/ExaBricks.cpp:57-63) */
+int exa_bricks_get_bounds(const exa_bricks_t *b, float lower[3], float upper[3]);
+size_t exa_bricks_kd_count(const exa_bricks_t *b);           /* 0 unless built here */
+const ExaKdTreeNode *exa_bricks_kd_nodes(const exa_bricks_t *b);
+
+/* ---------------------------------------------------------------------------------------
+ * Loaders — replace exa::ScalarField (exa/ScalarField.cpp:22-96), exa::ColorMapper
+ * (exa/ColorMapper.h:64-80) and exa::Config (exa/Config.cpp:23-180)
+ * ------------------------------------------------------------------------------------- */
+/* ScalarField::load. compat!=0 copies the reference quirk of sizing the vector by file
+ * BYTES (ScalarField.cpp:27-34): *count = 4x the float count, zero tail, and valueRange
+ * therefore includes 0.  values is malloc'd (exa_free). */
+int exa_scalar_field_load(const char *fileName, int compat, float **values, size_t *count,
+                          float valueRange[2]);
+/* ScalarField::loadAndComputeMagnitude on three arrays already in memory */
+int exa_scalar_field_magnitude(const float *x, const float *y, const float *z, size_t count,
+                               float *out, float valueRange[2]);
+/* ColorMapper::operator()(t) over control points {t,r,g,b} sorted by t */
+int exa_colormap_eval(const float *controlPoints4, int numPoints, float t, float rgb[3]);
+
+typedef struct exa_config exa_config_t;
+/* Config::parseConfigFile + finalize (tokens remap_from remap_to scalar vector value_range
+ * bricks; 'triangles' is accepted and ignored, 'scalar .. expr' is not supported) */
+int exa_config_parse(const char *fileName, int scalarCompat, exa_config_t **out);
+void exa_config_destroy(exa_config_t *c);
+const exa_bricks_t *exa_config_bricks(const exa_config_t *c);
+int exa_config_num_fields(const exa_config_t *c);
+const float *exa_config_field(const exa_config_t *c, int i, size_t *count, float valueRange[2],
+                              const char **name);
+/* bricks.voxelSpaceTransform as 12 floats: vx, vy, vz, p (Config.cpp:23-44) */
+int exa_config_voxel_space_transform(const exa_config_t *c, float xfm12[12]);
+/* Config::getBounds — world-space bounds (Config.cpp:48-55) */
+int exa_config_get_bounds(const exa_config_t *c, float lower[3], float upper[3]);
+
+/* ---------------------------------------------------------------------------------------
+ * Renderer — replaces exa::OptixRenderer (exa/OptixRenderer.h:32-188)
+ * ------------------------------------------------------------------------------------- */
+typedef struct exa_renderer exa_renderer_t;
+
+/* OptixRenderer::OptixRenderer(bricks, surfaces, scalarFields) (OptixRenderer.cpp:38-317):
+ * flatten + scalar gather through cell IDs (:71-141, on the GPU), ABR build
+ * (exa/Regions.cpp:242-320, on the GPU, bit-exact), kd-tree for traversal.
+ * fields[i] has fieldCounts[i] floats indexed by cell ID.  multiFieldDvr semantics
+ * (OptixRenderer.h:110): all fields are primary channels. */
+int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields,
+                        const size_t *fieldCounts, int numFields, int cudaDevice,
+                        exa_renderer_t **out);
+void exa_renderer_destroy(exa_renderer_t *r);
+/* use an externally owned cudaStream_t for all launches (NULL = default stream) */
+int exa_renderer_set_stream(exa_renderer_t *r, void *cudaStream);
+
+/* ABR access (ExaBrickRegions::brickRegions / leafList, exa/Regions.h:62-64).
+ * Pass NULL buffers to query the counts. */
+int exa_renderer_get_abr(exa_renderer_t *r, ExaBrickRegion *regions, size_t *numRegions,
+                         int32_t *leafList, size_t *leafListLen);
+/* traversal kd-tree statistics: nodes, depth */
+int exa_renderer_get_kd_info(exa_renderer_t *r, size_t *numNodes, int *depth);
+/* host copies of the reference's launch contract (programs/LaunchParams.h, FrameState.h) */
+int exa_renderer_get_launch_params(exa_renderer_t *r, ExaLaunchParams *lp, ExaFrameState *fs);
+
+int exa_renderer_set_voxel_space_transform(exa_renderer_t *r, const float xfm12[12]); /* :322-339 */
+/* resizeFrameBuffer(fbPointer, size) (:341-355). fbPointer: caller-owned RGBA8 buffer that
+ * device code can write (device or managed memory), or NULL to let the renderer own one. */
+int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int width, int height);
+int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3],
+                               const float dirDu[3], const float dirDv[3]);          /* :357-368 */
+/* updateXF(chan, opacities[128], colorMap[128] rgb, domain, opacityScale) (:370-404) */
+int exa_renderer_update_xf(exa_renderer_t *r, int channel, const float *opacities128,
+                           const float *rgb128x3, float domainLower, float domainUpper,
+                           float opacityScale);
+int exa_renderer_update_iso_values(exa_renderer_t *r, const float *isoValues,
+                                   const int *channels, const int *enabled);         /* :489-502 */
+int exa_renderer_update_frame_id(exa_renderer_t *r, int frameID);                    /* :406-411 */
+int exa_renderer_update_dt(exa_renderer_t *r, float dt);                             /* :413-416 */
+int exa_renderer_set_space_skipping(exa_renderer_t *r, int enable);                  /* :418-432 */
+int exa_renderer_set_gradient_shading_dvr(exa_renderer_t *r, int enable);            /* :434-437 */
+int exa_renderer_set_gradient_shading_iso(exa_renderer_t *r, int enable);            /* :439-442 */
+int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], const float hi[3]);
+/* early-ray-termination threshold (reference constant 0.98, exabrick.cu:49); >1 disables */
+int exa_renderer_set_ert_threshold(exa_renderer_t *r, float threshold);
+/* tracer (OptixRenderer.h:155-165, .cpp:444-487) */
+int exa_renderer_set_tracer_enabled(exa_renderer_t *r, int enable);
+int exa_renderer_set_tracer_params(exa_renderer_t *r, int numTraces, int numTimesteps,
+                                   float steplen, const int channels[3],
+                                   const float seedLo[3], const float seedHi[3]);
+int exa_renderer_reset_tracer(exa_renderer_t *r);
+/* replace the seeds generated by reset_tracer (libstdc++'s default_random_engine is what
+ * the reference uses; this keeps tests independent of it) */
+int exa_renderer_set_tracer_seeds(exa_renderer_t *r, const float *xyz, int numTraces);
+int exa_renderer_advance_tracer(exa_renderer_t *r, int *rebuilt);
+/* advance all remaining timesteps in one launch (the per-frame stepping is a viewer
+ * animation artefact) */
+int exa_renderer_trace_all(exa_renderer_t *r);
+int exa_renderer_read_traces(exa_renderer_t *r, float *xyz /* numTraces*numTimesteps*3 */);
+
+/* render() (:531-552): refresh activity masks if dirty, launch the fused frame kernel,
+ * synchronise */
+int exa_renderer_render(exa_renderer_t *r);
+int exa_renderer_render_async(exa_renderer_t *r);      /* no synchronise */
+int exa_renderer_sync(exa_renderer_t *r);
+/* headless read-back (replaces the GL blit of glutViewer/OWLViewer.cpp:140-197) */
+int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut);
+int exa_renderer_read_accum(exa_renderer_t *r, float *hostOutRGBA);
+/* device pointers of the current frame buffers (float4 accum, uint32 rgba8) */
+int exa_renderer_device_buffers(exa_renderer_t *r, void **accum, void **rgba8);
+
+/* tent-basis reconstruction at arbitrary points (samplePoint / samplePointWithDerivative,
+ * programs/exabrick.cu:781-816, 883-942).  xyz in voxel space.  grad may be NULL.
+ * _host copies in/out; _device takes device pointers and only enqueues on the stream. */
+int exa_sample_points_host(exa_renderer_t *r, const float *xyz, size_t n, int channel,
+                           float *values, uint8_t *valid, float *grad);
+int exa_sample_points_device(exa_renderer_t *r, const float *d_xyz, size_t n, int channel,
+                             float *d_values, uint8_t *d_valid, float *d_grad);
+
+/* instrumented (untimed) variants: same kernels with counters on */
+int exa_renderer_render_stats(exa_renderer_t *r, ExaStats *stats);
+int exa_sample_points_stats(exa_renderer_t *r, const float *d_xyz, size_t n, int channel,
+                            ExaStats *stats);
+/* number of kernels this library has launched on this handle so far */
+uint64_t exa_renderer_launch_count(const exa_renderer_t *r);
+
+/* ---------------------------------------------------------------------------------------
+ * Multi-GPU (new; the reference only replicates)
+ * ------------------------------------------------------------------------------------- */
+enum { EXA_PARTITION_NONE = 0, EXA_PARTITION_SORT_LAST = 1, EXA_PARTITION_IMAGE_TILES = 2 };
+/* restrict this renderer to part `rank` of `numRanks` (power of two for sort-last) */
+int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRanks);
+/* sort-last: render this rank's sub-volume to a premultiplied float4 partial image
+ * (device memory, W*H*4 floats) */
+int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA);
+/* for round `round` of binary swap: 1 if this rank's sub-volume is in FRONT of its
+ * partner's (rank ^ (1<<round)) as seen from the current camera */
+int exa_renderer_swap_order(exa_renderer_t *r, int round, int *iAmFront);
+/* d_mine = over(front, back) on `count` float4 pixels; mineIsFront selects the order */
+int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, size_t count,
+                       int mineIsFront);
+/* final shading of composited pixels [first, first+count): background, accumulation,
+ * sRGB, RGBA8 pack (exabrick.cu:1701-1719) */
+int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_compositedRGBA, size_t first,
+                               size_t count, uint32_t *d_rgba8Out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,56 @@
+"""Build libexabrick_b200.so in-tree with nvcc for sm_100a (cross-compiles without a GPU).
+
+    python -m owlexabrick_b200.build
+"""
+import os
+import subprocess
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(HERE, "libexabrick_b200.so")
+OBJ = os.path.join(HERE, "build")
+
+NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp", "-DEXA_BUILD"]
+SOURCES = ["host.cpp", "builder.cpp", "abr.cu", "render.cu", "capi.cu"]
+HEADERS = ["exa_internal.h", "render.cuh", "capi_render.inl", os.path.join("..", "..", "include", "exabrick_b200.h")]
+
+
+def _stale(out, deps):
+    if not os.path.exists(out):
+        return True
+    t = os.path.getmtime(out)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build_lib(force=False, verbose=False):
+    os.makedirs(OBJ, exist_ok=True)
+    hdrs = [os.path.join(CSRC, h) for h in HEADERS]
+
+    def compile_one(src):
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ, src + ".o")
+        if force or _stale(o, [s] + hdrs):
+            cmd = [NVCC] + ARCH + COMMON + ["-c", s, "-o", o]
+            if src.endswith(".cpp"):
+                cmd = [NVCC] + COMMON + ["-x", "cu", "-c", s, "-o", o] + ARCH
+            if verbose:
+                print(" ".join(cmd))
+            subprocess.check_call(cmd)
+        return o
+
+    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+        objs = list(ex.map(compile_one, SOURCES))
+    if force or _stale(LIB, objs):
+        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-Xcompiler", "-fopenmp", "-lgomp"]
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.check_call(cmd)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build_lib(force="--force" in sys.argv, verbose=True))

@@ -1,0 +1,277 @@
+// builder.cpp — cells -> bricks kd builder, bit-exact with the reference's serial exaBuilder
+// (builder/builder.cpp:301-350 dedup, 447-530 tryMakeLeaf, 538-811 buildRec, 895-907 writer).
+//
+// Same decisions, different machinery: cells travel with the recursion as compact
+// {x,y,z,level,id} records (streaming passes instead of id -> cell gathers), duplicates are
+// removed with a lock-free hash set instead of a 20-byte-pair std::sort (the reference's ID
+// order inside a node never influences the output, only WHICH of two identical cells
+// survives: the one with the smallest id, builder.cpp:338-342), per-axis slice statistics
+// come from one pass, and the left/right union boxes of all candidate planes come from
+// prefix/suffix unions instead of an O(planes x slices) rescan.  Passes over large nodes
+// are OpenMP-parallel; the recursion itself stays serial (left, then right) because that is
+// what defines the brick order.
+#include "exa_internal.h"
+#include <algorithm>
+#include <atomic>
+#include <climits>
+#include <cstring>
+#include <limits>
+#include <stdexcept>
+#include <omp.h>
+
+namespace exa {
+
+struct BricksImpl;
+BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, std::vector<int32_t> &&ids, std::vector<ExaKdTreeNode> &&kd);
+
+namespace {
+
+struct Rec { int x, y, z, level, id; };
+
+struct Box4 {
+  int lo[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
+  int hi[4] = {INT_MIN, INT_MIN, INT_MIN, INT_MIN};
+  inline void extendCell(const Rec &c)
+  {
+    const int cw = 1 << c.level;                      // SingleCell::getBounds, builder.cpp:121-130
+    lo[0] = std::min(lo[0], c.x); lo[1] = std::min(lo[1], c.y); lo[2] = std::min(lo[2], c.z); lo[3] = std::min(lo[3], c.level);
+    hi[0] = std::max(hi[0], c.x + cw); hi[1] = std::max(hi[1], c.y + cw); hi[2] = std::max(hi[2], c.z + cw); hi[3] = std::max(hi[3], c.level + 1);
+  }
+  inline void extend(const Box4 &o) { for (int i = 0; i < 4; i++) { lo[i] = std::min(lo[i], o.lo[i]); hi[i] = std::max(hi[i], o.hi[i]); } }
+  inline int size(int i) const { return hi[i] - lo[i]; }
+  inline bool empty() const { return lo[0] > hi[0]; }
+};
+inline size_t unitCellVolume(const Box4 &b) { return (size_t)b.size(0) * (size_t)b.size(1) * (size_t)b.size(2); }   // :164-168
+inline size_t areaOf(const Box4 &b)                                                                                    // :170-177
+{ return (size_t)b.size(0) * (size_t)b.size(1) + (size_t)b.size(1) * (size_t)b.size(2) + (size_t)b.size(2) * (size_t)b.size(0); }
+inline int divDown(int a, int b) { return a >= 0 ? a / b : (a - (b - 1)) / b; }   // :53-59
+inline int divUp(int a, int b) { return a >= 0 ? (a + b - 1) / b : a / b; }       // :61-67
+
+static const size_t PAR_THRESHOLD = 1u << 16;
+
+struct Builder {
+  int builderType, maxLeafWidth;
+  std::vector<ExaBrick> hdr; std::vector<int32_t> ids; std::vector<ExaKdTreeNode> tree;
+
+  // ---- duplicate removal (builder.cpp:301-350) ----
+  static inline uint64_t hashCell(const int32_t *c)
+  {
+    uint64_t h = (uint64_t)(uint32_t)c[0] * 0x9E3779B97F4A7C15ull;
+    h ^= (uint64_t)(uint32_t)c[1] * 0xC2B2AE3D27D4EB4Full + (h << 6) + (h >> 2);
+    h ^= (uint64_t)(uint32_t)c[2] * 0x165667B19E3779F9ull + (h << 6) + (h >> 2);
+    h ^= (uint64_t)(uint32_t)c[3] * 0x27D4EB2F165667C5ull + (h << 6) + (h >> 2);
+    h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
+    return h;
+  }
+  std::vector<Rec> dedup(const int32_t *cells, size_t n)
+  {
+    size_t cap = 1; while (cap < 2 * n + 16) cap <<= 1;
+    std::vector<std::atomic<int32_t>> table(cap);
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < cap; i++) table[i].store(-1, std::memory_order_relaxed);
+    auto same = [&](int32_t a, const int32_t *c) { return memcmp(cells + 4 * (size_t)a, c, 16) == 0; };
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; i++) {
+      const int32_t *c = cells + 4 * i;
+      size_t h = hashCell(c) & (cap - 1);
+      for (;;) {
+        int32_t cur = table[h].load(std::memory_order_acquire);
+        if (cur == -1) {
+          if (table[h].compare_exchange_strong(cur, (int32_t)i, std::memory_order_acq_rel)) break;
+        }
+        if (same(cur, c)) {           // slot owned by this cell: keep the smallest id
+          while (cur > (int32_t)i && !table[h].compare_exchange_weak(cur, (int32_t)i, std::memory_order_acq_rel)) {}
+          break;
+        }
+        h = (h + 1) & (cap - 1);
+      }
+    }
+    std::vector<uint8_t> keep(n);
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < n; i++) {
+      const int32_t *c = cells + 4 * i;
+      size_t h = hashCell(c) & (cap - 1);
+      for (;;) {
+        const int32_t cur = table[h].load(std::memory_order_relaxed);
+        if (same(cur, c)) { keep[i] = cur == (int32_t)i; break; }
+        h = (h + 1) & (cap - 1);
+      }
+    }
+    std::vector<Rec> out; out.reserve(n);
+    for (size_t i = 0; i < n; i++)
+      if (keep[i]) out.push_back(Rec{cells[4 * i], cells[4 * i + 1], cells[4 * i + 2], cells[4 * i + 3], (int)i});
+    return out;
+  }
+
+  Box4 boundsOf(const std::vector<Rec> &v)
+  {
+    Box4 b;
+    if (v.size() < PAR_THRESHOLD) { for (auto &c : v) b.extendCell(c); return b; }
+#pragma omp parallel
+    {
+      Box4 lb;
+#pragma omp for schedule(static) nowait
+      for (size_t i = 0; i < v.size(); i++) lb.extendCell(v[i]);
+#pragma omp critical
+      b.extend(lb);
+    }
+    return b;
+  }
+
+  // tryMakeLeaf, builder.cpp:447-530
+  bool tryMakeLeaf(const Box4 &b, const std::vector<Rec> &v, unsigned nodeID)
+  {
+    if (v.empty()) throw std::runtime_error("empty ID vector in tryMakeLeaf!?");
+    if (b.size(3) > 1) return false;
+    const size_t cw = 1ULL << (b.hi[3] - 1);
+    for (int d = 0; d < 3; d++) if ((size_t)b.size(d) / cw > (size_t)maxLeafWidth) return false;
+    const long long vol = (long long)b.size(0) * b.size(1) * b.size(2) * b.size(3);
+    if ((size_t)vol != v.size() * (cw * cw * cw)) return false;
+    ExaBrick h;
+    for (int d = 0; d < 3; d++) { h.lower[d] = b.lo[d]; h.size[d] = b.size(d) / (int)cw; }
+    h.level = b.lo[3];
+    if (ids.size() + v.size() > 0xffffffffull) throw std::runtime_error("overflow in 32-bit brick offset");
+    h.begin = (uint32_t)ids.size();
+    const size_t base = ids.size();
+    ids.resize(base + v.size(), -1);
+    int32_t *dst = ids.data() + base;
+    const size_t sx = h.size[0], sxy = (size_t)h.size[0] * h.size[1];
+#pragma omp parallel for schedule(static) if (v.size() >= PAR_THRESHOLD)
+    for (size_t i = 0; i < v.size(); i++) {
+      const Rec &c = v[i];
+      dst[(c.x - b.lo[0]) / (int)cw + sx * ((c.y - b.lo[1]) / (int)cw) + sxy * ((c.z - b.lo[2]) / (int)cw)] = c.id;
+    }
+    // KdTreeNode::set_leaf(first_prim = brick index, count 1), exa/KdTree.h:102-107
+    tree[nodeID].split_or_first_prim = (uint32_t)hdr.size();
+    tree[nodeID].axis_bits = (3u << 30) | 1u;
+    hdr.push_back(h);
+    return true;
+  }
+
+  struct Slices { std::vector<size_t> vol; std::vector<Box4> box; };
+
+  // Bricker::buildRec, builder.cpp:538-811
+  void buildRec(std::vector<Rec> &v, unsigned nodeID)
+  {
+    Box4 cb = boundsOf(v);                               // computeCoarsestLevelBounds :201-225
+    const int ccw = 1 << (cb.hi[3] - 1);
+    for (int d = 0; d < 3; d++) { cb.lo[d] = ccw * divDown(cb.lo[d], ccw); cb.hi[d] = ccw * divUp(cb.hi[d], ccw); }
+    if (tryMakeLeaf(cb, v, nodeID)) return;
+    const int dims[3] = {cb.size(0) / ccw, cb.size(1) / ccw, cb.size(2) / ccw};
+    if (dims[0] == 1 && dims[1] == 1 && dims[2] == 1) throw std::runtime_error("coarse size 1 that's not a leaf!?");
+    const int maxLevel = cb.hi[3] - 1;                   // == max over slice level lists, :592-598
+
+    int bestDim = -1, bestPos = -1;
+    if (builderType == EXA_BUILDER_SAH_ALIKE) {
+      // ---- per-axis slice statistics, one pass (:557-590) ----
+      Slices sl[3];
+      for (int d = 0; d < 3; d++) { sl[d].vol.assign(dims[d], 0); sl[d].box.assign(dims[d], Box4()); }
+      auto splat = [&](Slices *s, const Rec &c) {
+        const int cw = 1 << c.level; const size_t cv = (size_t)cw * cw * cw;
+        const int bin[3] = {(c.x - cb.lo[0]) / ccw, (c.y - cb.lo[1]) / ccw, (c.z - cb.lo[2]) / ccw};
+        for (int d = 0; d < 3; d++) { s[d].vol[bin[d]] += cv; s[d].box[bin[d]].extendCell(c); }
+      };
+      if (v.size() < PAR_THRESHOLD) { for (auto &c : v) splat(sl, c); }
+      else {
+#pragma omp parallel
+        {
+          Slices loc[3];
+          for (int d = 0; d < 3; d++) { loc[d].vol.assign(dims[d], 0); loc[d].box.assign(dims[d], Box4()); }
+#pragma omp for schedule(static) nowait
+          for (size_t i = 0; i < v.size(); i++) splat(loc, v[i]);
+#pragma omp critical
+          for (int d = 0; d < 3; d++) for (int i = 0; i < dims[d]; i++) { sl[d].vol[i] += loc[d].vol[i]; sl[d].box[i].extend(loc[d].box[i]); }
+        }
+      }
+      // ---- boundary planes and SAH-alike cost (:603-722) ----
+      double bestCost = std::numeric_limits<float>::infinity();
+      for (int d = 0; d < 3; d++) {
+        if (dims[d] == 0) continue;
+        const size_t expected = unitCellVolume(cb) / dims[d];
+        std::vector<Box4> suffix(dims[d] + 1);           // suffix[i] = union of slices [i, dims)
+        for (int i = dims[d] - 1; i >= 0; i--) { suffix[i] = suffix[i + 1]; suffix[i].extend(sl[d].box[i]); }
+        Box4 prefix;                                     // union of slices [0, plane)
+        for (int plane = 1; plane < dims[d]; plane++) {
+          prefix.extend(sl[d].box[plane - 1]);
+          const int L = plane - 1, R = plane;
+          const bool lFull = sl[d].vol[L] == expected, rFull = sl[d].vol[R] == expected;
+          // :636-643 — an empty slice is never full, so its w-extent never decides anything
+          bool isBoundary = true;
+          if (lFull && rFull)
+            isBoundary = !(sl[d].box[L].lo[3] == sl[d].box[R].lo[3] && sl[d].box[L].size(3) == sl[d].box[R].size(3));
+          if (!isBoundary) continue;
+          const Box4 &lb = prefix, &rb = suffix[plane];
+          const double cost = areaOf(lb) * (double)unitCellVolume(lb) * lb.size(3)
+                            + areaOf(rb) * (double)unitCellVolume(rb) * rb.size(3);
+          if (cost < bestCost) { bestCost = cost; bestDim = d; bestPos = cb.lo[d] + plane * ccw; }
+        }
+      }
+    }
+    if (bestDim == -1) {                                 // spatial median fallback, :728-734
+      bestDim = 0;
+      for (int i = 1; i < 3; i++) if (dims[i] > dims[bestDim]) bestDim = i;
+      bestPos = cb.lo[bestDim] + (dims[bestDim] / 2) * ccw;
+    }
+
+    // ---- partition (:753-770) ----
+    std::vector<Rec> l, r;
+    auto coord = [&](const Rec &c) { return bestDim == 0 ? c.x : bestDim == 1 ? c.y : c.z; };
+    if (v.size() < PAR_THRESHOLD) {
+      for (auto &c : v) {
+        const int lo = coord(c);
+        if (lo >= bestPos) r.push_back(c);
+        else if (lo + (1 << c.level) <= bestPos) l.push_back(c);
+        else throw std::runtime_error("cell straddles split plane!?");
+      }
+    } else {
+      const int T = omp_get_max_threads();
+      std::vector<size_t> cl(T + 1, 0), cr(T + 1, 0);
+      bool straddle = false;
+#pragma omp parallel num_threads(T)
+      {
+        const int t = omp_get_thread_num();
+        const size_t b = v.size() * t / T, e = v.size() * (t + 1) / T;
+        size_t nl = 0, nr = 0;
+        for (size_t i = b; i < e; i++) {
+          const int lo = coord(v[i]);
+          if (lo >= bestPos) nr++; else if (lo + (1 << v[i].level) <= bestPos) nl++; else straddle = true;
+        }
+        cl[t + 1] = nl; cr[t + 1] = nr;
+#pragma omp barrier
+#pragma omp single
+        {
+          for (int k = 0; k < T; k++) { cl[k + 1] += cl[k]; cr[k + 1] += cr[k]; }
+          l.resize(cl[T]); r.resize(cr[T]);
+        }
+        size_t pl = cl[t], pr = cr[t];
+        if (!straddle)
+          for (size_t i = b; i < e; i++) { if (coord(v[i]) >= bestPos) r[pr++] = v[i]; else l[pl++] = v[i]; }
+      }
+      if (straddle) throw std::runtime_error("cell straddles split plane!?");
+    }
+    if (l.empty() || r.empty()) throw std::runtime_error("invalid split...");
+    const unsigned firstChild = (unsigned)tree.size();   // :794-800
+    tree.emplace_back(ExaKdTreeNode{0, 0, 0}); tree.emplace_back(ExaKdTreeNode{0, 0, 0});
+    tree[nodeID].axis_bits = ((unsigned)bestDim << 30) | firstChild;
+    tree[nodeID].split_or_first_prim = (uint32_t)bestPos;
+    tree[nodeID].max_level = maxLevel;
+    std::vector<Rec>().swap(v);
+    buildRec(l, firstChild);                             // :808-810 left, then right
+    buildRec(r, firstChild + 1);
+  }
+};
+
+} // namespace
+
+BricksImpl *buildBricks(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth)
+{
+  if (numCells > 0x7fffffffull) throw std::runtime_error("more than 2^31 cells: ids are 32-bit (builder.cpp:45)");
+  Builder B; B.builderType = builderType; B.maxLeafWidth = maxLeafWidth;
+  B.tree.emplace_back(ExaKdTreeNode{0, 0, 0});
+  for (size_t i = 0; i < numCells; i++) if (cells[4 * i + 3] < 0 || cells[4 * i + 3] > 30) throw std::runtime_error("cell level out of range");
+  std::vector<Rec> v = B.dedup(cells, numCells);
+  if (!v.empty()) B.buildRec(v, 0);
+  return bricksFromParts(std::move(B.hdr), std::move(B.ids), std::move(B.tree));
+}
+
+} // namespace exa

@@ -1,0 +1,339 @@
+// capi.cu — exa_renderer_* : the C ABI over the CUDA path (replaces exa::OptixRenderer,
+// exa/OptixRenderer.{h,cpp}).  No CPU fallback anywhere: every entry point that needs the
+// device fails with EXA_ERR_CUDA when CUDA is unusable.
+#include "render.cuh"
+#include <cmath>
+#include <cstring>
+#include <random>
+#include <string>
+
+using namespace exa;
+
+#define CKR(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    setError(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call); return EXA_ERR_CUDA; } } while (0)
+
+struct exa_renderer {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  uint64_t launches = 0;
+  // scene
+  ExaBrick *d_bricks = nullptr; int numBricks = 0;
+  float *d_scalars = nullptr; uint64_t numCells = 0; int numFields = 0;
+  unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
+  AbrResult abr;
+  std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
+  float voxelLo[3], voxelHi[3], worldLo[3], worldHi[3];
+  // frame state
+  ExaFrameState fs; ExaLaunchParams lp;
+  float4 *d_xf = nullptr;                // [numFields][128]
+  float dt = 0.5f; float ert = 0.98f;
+  int spaceSkipping = 1, gradDVR = 1, gradISO = 1;
+  bool masksDirty = true;
+  uint8_t *d_regionVol = nullptr, *d_regionIso = nullptr, *d_volActive = nullptr, *d_isoActive = nullptr, *d_inPart = nullptr;
+  // framebuffer
+  int width = 0, height = 0;
+  float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
+  // partition
+  int partMode = EXA_PARTITION_NONE, rank = 0, numRanks = 1; int partRoot = 0;
+  std::vector<int> partPath;             // kd node visited at each partition level
+  // tracer
+  int tracerEnabled = 0, numTraces = 1000, numTimesteps = 100, timestep = 0;
+  float steplen = 1e-6f; int tracerChannels[3] = {0, 1, 2};
+  float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
+  float *d_traces = nullptr; size_t tracesCap = 0;
+  unsigned long long *d_stats = nullptr;
+};
+
+static int cudaUsable()
+{
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0) { setError(std::string("no usable CUDA device: ") + (e != cudaSuccess ? cudaGetErrorString(e) : "device count 0")); cudaGetLastError(); return 0; }
+  return n;
+}
+
+static void identityXfm(float m[12]) { memset(m, 0, 48); m[0] = m[4] = m[8] = 1.f; }
+
+static void fillParams(exa_renderer *r, RenderParams &P)
+{
+  memset(&P, 0, sizeof(P));
+  DeviceScene &S = P.scene;
+  S.bricks = r->d_bricks; S.numBricks = r->numBricks; S.scalars = r->d_scalars; S.numCells = r->numCells; S.numFields = r->numFields;
+  S.regions = r->abr.regions; S.numRegions = r->abr.numRegions; S.leafList = r->abr.leafList; S.leafListLen = r->abr.leafListLen;
+  S.kd = r->abr.kd; S.numKdNodes = r->abr.numKdNodes; S.kdDepth = r->abr.depth; S.blobs = r->abr.blobs;
+  for (int d = 0; d < 3; d++) { S.boundsLo[d] = r->abr.boundsLo[d]; S.boundsHi[d] = r->abr.boundsHi[d]; }
+  memcpy(P.camPos, r->fs.camera.pos, 12); memcpy(P.dir00, r->fs.camera.dir00, 12);
+  memcpy(P.dirDu, r->fs.camera.dirDu, 12); memcpy(P.dirDv, r->fs.camera.dirDv, 12);
+  memcpy(P.xfm, &r->fs.voxelSpaceTransform, 48);
+  P.width = r->width; P.height = r->height; P.frameID = r->fs.frameID; P.dt = r->dt;
+  P.numChannels = r->numFields; P.colormapChannel = 0;     // multiFieldDvr (OptixRenderer.h:110, .cpp:276-283)
+  P.gradDVR = r->gradDVR; P.gradISO = r->gradISO;
+  P.xfOpacityScale = r->fs.xfOpacityScale;
+  memcpy(P.xfDomain, r->fs.xfDomain, sizeof(P.xfDomain));
+  P.xf = r->d_xf;
+  for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
+    P.isoEnabled[i] = r->fs.isoSurface[i].enabled; P.isoValue[i] = r->fs.isoSurface[i].value; P.isoChannel[i] = r->fs.isoSurface[i].channel;
+    P.anyIso |= P.isoEnabled[i];
+  }
+  P.clipEnabled = r->fs.clipBox.enabled; memcpy(P.clipLo, r->fs.clipBox.lower, 12); memcpy(P.clipHi, r->fs.clipBox.upper, 12);
+  P.ertThreshold = r->ert;
+  P.volActive = r->d_volActive; P.isoActive = r->d_isoActive;
+  P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
+  P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
+  P.traces = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
+  P.stats = nullptr;
+  P.kdStack = r->abr.depth + 2;
+}
+
+static void syncLaunchParams(exa_renderer *r)
+{
+  ExaLaunchParams &lp = r->lp;
+  lp.deviceIndex = r->rank; lp.deviceCount = r->numRanks;
+  lp.volumeBVH = (uint64_t)r->abr.kd; lp.surfaceModel = 0; lp.isoSurfaceBVH = (uint64_t)r->abr.kd; lp.streamlineBVH = 0;
+  lp.fbSize[0] = r->width; lp.fbSize[1] = r->height;
+  memcpy(lp.worldSpaceBounds_lo, r->worldLo, 12); memcpy(lp.worldSpaceBounds_hi, r->worldHi, 12);
+  memcpy(lp.voxelSpaceBounds_lo, r->voxelLo, 12); memcpy(lp.voxelSpaceBounds_hi, r->voxelHi, 12);
+  lp.colorBufferPtr = (uint64_t)r->d_rgba8; lp.accumBufferPtr = (uint64_t)r->d_accum; lp.frameStateBuffer = 0;
+  lp.dt = r->dt;
+  lp.sameBrickRegionsBuffer = (uint64_t)r->abr.regions; lp.sameBrickRegionsLeafList = (uint64_t)r->abr.leafList;
+  lp.brickBuffer = (uint64_t)r->d_bricks; lp.scalarBuffers = (uint64_t)r->d_scalars; lp.scalarBufferOffsets = (uint64_t)r->d_scalarOffsets;
+  lp.primaryChannels = (uint64_t)r->d_primaryChannels; lp.colormapChannel = 0; lp.numPrimaryChannels = r->numFields;
+  lp.gradientShadingDVR = r->gradDVR; lp.gradientShadingISO = r->gradISO;
+  lp.tracerEnabled = r->tracerEnabled; lp.traces = (uint64_t)r->d_traces;
+  memcpy(lp.tracerChannels, r->tracerChannels, 12);
+  lp.numTraces = r->numTraces; lp.numTimesteps = r->numTimesteps; lp.steplen = r->steplen; lp.currentTimestep = 0;
+  for (int c = 0; c < EXA_MAX_CHANNELS; c++) r->fs.xfTexture[c] = c < r->numFields ? (uint64_t)(r->d_xf + 128 * c) : 0;
+}
+
+static void computeWorldBounds(exa_renderer *r)
+{
+  // OptixRenderer::setVoxelSpaceTransform (:330-332): world = rcp(xfm) * voxel bounds corners
+  const float *m = (const float *)&r->fs.voxelSpaceTransform;
+  const float *vx = m, *vy = m + 3, *vz = m + 6, *p = m + 9;
+  const float cx[3] = {vy[1] * vz[2] - vy[2] * vz[1], vy[2] * vz[0] - vy[0] * vz[2], vy[0] * vz[1] - vy[1] * vz[0]};
+  const float cy[3] = {vz[1] * vx[2] - vz[2] * vx[1], vz[2] * vx[0] - vz[0] * vx[2], vz[0] * vx[1] - vz[1] * vx[0]};
+  const float cz[3] = {vx[1] * vy[2] - vx[2] * vy[1], vx[2] * vy[0] - vx[0] * vy[2], vx[0] * vy[1] - vx[1] * vy[0]};
+  const float det = vx[0] * cx[0] + vx[1] * cx[1] + vx[2] * cx[2];
+  float il[9] = {cx[0] / det, cy[0] / det, cz[0] / det, cx[1] / det, cy[1] / det, cz[1] / det, cx[2] / det, cy[2] / det, cz[2] / det};
+  float ip[3];
+  for (int k = 0; k < 3; k++) ip[k] = -(il[k] * p[0] + il[3 + k] * p[1] + il[6 + k] * p[2]);
+  for (int k = 0; k < 3; k++) {
+    r->worldLo[k] = il[k] * r->voxelLo[0] + il[3 + k] * r->voxelLo[1] + il[6 + k] * r->voxelLo[2] + ip[k];
+    r->worldHi[k] = il[k] * r->voxelHi[0] + il[3 + k] * r->voxelHi[1] + il[6 + k] * r->voxelHi[2] + ip[k];
+  }
+}
+
+extern "C" {
+
+int exa_cuda_available(void)
+{
+  if (!cudaUsable()) return 0;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, 0) != cudaSuccess) { setError("cudaGetDeviceProperties failed"); return 0; }
+  if (prop.major != 10) { setError("device 0 is not compute capability 10.x (this library ships sm_100a code only)"); return 0; }
+  return 1;
+}
+
+int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
+                        int numFields, int cudaDevice, exa_renderer_t **out)
+{
+  if (!bricks || !out || !fields || !fieldCounts) { setError("exa_renderer_create: null argument"); return EXA_ERR_INVALID; }
+  if (numFields < 1 || numFields > EXA_MAX_CHANNELS) { setError("exa_renderer_create: numFields must be 1.." + std::to_string(EXA_MAX_CHANNELS)); return EXA_ERR_INVALID; }
+  const size_t nb = exa_bricks_count(bricks), nc = exa_bricks_num_cells(bricks);
+  if (nb == 0 || nc == 0) { setError("exa_renderer_create: empty brick set"); return EXA_ERR_INVALID; }
+  if (nb > 0x3fffffffull) { setError("too many bricks"); return EXA_ERR_LIMIT; }
+  const int ndev = cudaUsable(); if (!ndev) return EXA_ERR_CUDA;
+  if (cudaDevice < 0 || cudaDevice >= ndev) { setError("exa_renderer_create: bad device index"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(cudaDevice));
+  exa_renderer *r = new exa_renderer;
+  r->device = cudaDevice;
+  memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
+  identityXfm((float *)&r->fs.voxelSpaceTransform);
+  r->fs.xfOpacityScale = 1.f; r->fs.ao.length = 1e20f; r->fs.ao.enabled = 0;
+  for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) { r->fs.contourPlane[i].normal[0] = 1.f; r->fs.contourPlane[i].offset = .5f; }
+  for (int c = 0; c < EXA_MAX_CHANNELS; c++) { r->fs.xfDomain[c][0] = 0.f; r->fs.xfDomain[c][1] = 1.f; }
+  r->numBricks = (int)nb; r->numCells = nc; r->numFields = numFields;
+  exa_bricks_get_bounds(bricks, r->voxelLo, r->voxelHi);
+  memcpy(r->worldLo, r->voxelLo, 12); memcpy(r->worldHi, r->voxelHi, 12);
+  cudaStream_t s = r->stream;
+  int rc = EXA_OK;
+#define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
+    setError(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call); exa_renderer_destroy(r); return EXA_ERR_CUDA; } } while (0)
+  // ---- flatten: Brick[] + scalar gather through the cell IDs (OptixRenderer.cpp:71-141) ----
+  CKC(cudaMalloc(&r->d_bricks, nb * sizeof(ExaBrick)));
+  CKC(cudaMemcpyAsync(r->d_bricks, exa_bricks_headers(bricks), nb * sizeof(ExaBrick), cudaMemcpyHostToDevice, s));
+  CKC(cudaMalloc(&r->d_scalars, sizeof(float) * nc * (size_t)numFields));
+  {
+    int32_t *d_ids = nullptr; float *d_field = nullptr; int *d_err = nullptr; size_t fieldCap = 0;
+    CKC(cudaMalloc(&d_ids, nc * 4)); CKC(cudaMalloc(&d_err, 4)); CKC(cudaMemsetAsync(d_err, 0, 4, s));
+    CKC(cudaMemcpyAsync(d_ids, exa_bricks_cell_ids(bricks), nc * 4, cudaMemcpyHostToDevice, s));
+    for (int f = 0; f < numFields; f++) {
+      if (!fields[f] || fieldCounts[f] == 0) { setError("exa_renderer_create: empty scalar field"); rc = EXA_ERR_INVALID; break; }
+      if (fieldCounts[f] > fieldCap) { if (d_field) { cudaStreamSynchronize(s); cudaFree(d_field); } CKC(cudaMalloc(&d_field, fieldCounts[f] * 4)); fieldCap = fieldCounts[f]; }
+      CKC(cudaMemcpyAsync(d_field, fields[f], fieldCounts[f] * 4, cudaMemcpyHostToDevice, s));
+      if (launchGather(d_field, fieldCounts[f], d_ids, nc, r->d_scalars + (size_t)f * nc, d_err, s) < 0) { setError("gather launch failed"); rc = EXA_ERR_CUDA; break; }
+      r->launches++;
+      CKC(cudaStreamSynchronize(s));
+    }
+    int herr = 0;
+    if (!rc) { CKC(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost)); }
+    cudaFree(d_ids); cudaFree(d_field); cudaFree(d_err);
+    if (!rc && herr) { setError(herr == 1 ? "negative cell ID" : "invalid cell ID"); rc = EXA_ERR_INVALID; }   // OptixRenderer.cpp:122-127
+    if (rc) { exa_renderer_destroy(r); return rc; }
+  }
+  {
+    std::vector<unsigned> offs(numFields); std::vector<int> prim(numFields);
+    for (int f = 0; f < numFields; f++) { offs[f] = (unsigned)((size_t)f * nc); prim[f] = f; }   // 32-bit view valid while C*Nc < 2^32
+    CKC(cudaMalloc(&r->d_scalarOffsets, 4 * numFields)); CKC(cudaMalloc(&r->d_primaryChannels, 4 * numFields));
+    CKC(cudaMemcpy(r->d_scalarOffsets, offs.data(), 4 * numFields, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(r->d_primaryChannels, prim.data(), 4 * numFields, cudaMemcpyHostToDevice));
+  }
+  // ---- ABR build on the GPU (exa/Regions.cpp:242-320) ----
+  rc = abrBuild(r->d_bricks, r->numBricks, r->d_scalars, r->numCells, numFields, s, r->abr);
+  if (rc) { exa_renderer_destroy(r); return rc; }
+  r->launches += r->abr.launches;
+  if (r->abr.depth + 2 > 1024) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
+  r->h_kd.resize(r->abr.numKdNodes);
+  CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
+  const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);
+  CKC(cudaMalloc(&r->d_regionVol, nr)); CKC(cudaMalloc(&r->d_regionIso, nr));
+  CKC(cudaMalloc(&r->d_volActive, nn)); CKC(cudaMalloc(&r->d_isoActive, nn)); CKC(cudaMalloc(&r->d_inPart, nn));
+  CKC(cudaMemset(r->d_inPart, 1, nn));
+  CKC(cudaMalloc(&r->d_xf, sizeof(float4) * 128 * numFields));
+  {
+    // default XF: alpha ramp i/127 (viewer.cpp:558-566), grey colour ramp; callers normally updateXF
+    std::vector<float4> lut(128 * numFields);
+    for (int c = 0; c < numFields; c++) for (int i = 0; i < 128; i++) { float t = i / 127.f; lut[c * 128 + i] = make_float4(t, t, t, t); }
+    CKC(cudaMemcpy(r->d_xf, lut.data(), sizeof(float4) * lut.size(), cudaMemcpyHostToDevice));
+  }
+  CKC(cudaMalloc(&r->d_stats, 4 * sizeof(unsigned long long)));
+#undef CKC
+  syncLaunchParams(r);
+  *out = r;
+  return EXA_OK;
+}
+
+void exa_renderer_destroy(exa_renderer_t *r)
+{
+  if (!r) return;
+  cudaSetDevice(r->device);
+  cudaFree(r->d_bricks); cudaFree(r->d_scalars); cudaFree(r->d_scalarOffsets); cudaFree(r->d_primaryChannels);
+  abrFree(r->abr);
+  cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
+  cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
+  cudaFree(r->d_traces); cudaFree(r->d_stats);
+  delete r;
+}
+
+int exa_renderer_set_stream(exa_renderer_t *r, void *cudaStream)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  r->stream = (cudaStream_t)cudaStream; return EXA_OK;
+}
+
+int exa_renderer_get_abr(exa_renderer_t *r, ExaBrickRegion *regions, size_t *numRegions, int32_t *leafList, size_t *leafListLen)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (numRegions) *numRegions = r->abr.numRegions;
+  if (leafListLen) *leafListLen = r->abr.leafListLen;
+  if (regions && r->abr.numRegions) CKR(cudaMemcpy(regions, r->abr.regions, sizeof(ExaBrickRegion) * r->abr.numRegions, cudaMemcpyDeviceToHost));
+  if (leafList && r->abr.leafListLen) CKR(cudaMemcpy(leafList, r->abr.leafList, 4 * (size_t)r->abr.leafListLen, cudaMemcpyDeviceToHost));
+  return EXA_OK;
+}
+
+int exa_renderer_get_kd_info(exa_renderer_t *r, size_t *numNodes, int *depth)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (numNodes) *numNodes = r->abr.numKdNodes;
+  if (depth) *depth = r->abr.depth;
+  return EXA_OK;
+}
+
+int exa_renderer_get_launch_params(exa_renderer_t *r, ExaLaunchParams *lp, ExaFrameState *fs)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  syncLaunchParams(r);
+  if (lp) *lp = r->lp;
+  if (fs) *fs = r->fs;
+  return EXA_OK;
+}
+
+int exa_renderer_set_voxel_space_transform(exa_renderer_t *r, const float xfm12[12])
+{
+  if (!r || !xfm12) { setError("null argument"); return EXA_ERR_INVALID; }
+  memcpy(&r->fs.voxelSpaceTransform, xfm12, 48);
+  computeWorldBounds(r);
+  return EXA_OK;
+}
+
+int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int width, int height)
+{
+  if (!r || width <= 0 || height <= 0) { setError("resize_framebuffer: bad argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaStreamSynchronize(r->stream));
+  cudaFree(r->d_accum); r->d_accum = nullptr;
+  if (r->ownRgba8) cudaFree(r->d_rgba8);
+  r->d_rgba8 = nullptr; r->ownRgba8 = false;
+  const size_t n = (size_t)width * height;
+  CKR(cudaMalloc(&r->d_accum, n * sizeof(float4)));
+  CKR(cudaMemset(r->d_accum, 0, n * sizeof(float4)));
+  if (fbPointer) r->d_rgba8 = (uint32_t *)fbPointer;
+  else { CKR(cudaMalloc(&r->d_rgba8, n * 4)); CKR(cudaMemset(r->d_rgba8, 0, n * 4)); r->ownRgba8 = true; }
+  r->width = width; r->height = height;
+  return EXA_OK;
+}
+
+int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3], const float dirDu[3], const float dirDv[3])
+{
+  if (!r || !pos || !dir00 || !dirDu || !dirDv) { setError("null argument"); return EXA_ERR_INVALID; }
+  memcpy(r->fs.camera.pos, pos, 12); memcpy(r->fs.camera.dir00, dir00, 12);
+  memcpy(r->fs.camera.dirDu, dirDu, 12); memcpy(r->fs.camera.dirDv, dirDv, 12);
+  return EXA_OK;
+}
+
+int exa_renderer_update_xf(exa_renderer_t *r, int channel, const float *opacities128, const float *rgb128x3,
+                           float domainLower, float domainUpper, float opacityScale)
+{
+  if (!r || !opacities128 || !rgb128x3) { setError("null argument"); return EXA_ERR_INVALID; }
+  if (channel < 0 || channel >= r->numFields) { setError("updateXF: channel out of range"); return EXA_ERR_INVALID; }
+  r->fs.xfDomain[channel][0] = domainLower; r->fs.xfDomain[channel][1] = domainUpper;
+  r->fs.xfOpacityScale = opacityScale;
+  float4 lut[128];
+  for (int i = 0; i < 128; i++) lut[i] = make_float4(rgb128x3[3 * i], rgb128x3[3 * i + 1], rgb128x3[3 * i + 2], opacities128[i]);
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(r->d_xf + 128 * channel, lut, sizeof(lut), cudaMemcpyHostToDevice, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  r->masksDirty = true;                                     // needVolumeBVHRebuild (:403)
+  return EXA_OK;
+}
+
+int exa_renderer_update_iso_values(exa_renderer_t *r, const float *isoValues, const int *channels, const int *enabled)
+{
+  if (!r || !isoValues || !channels || !enabled) { setError("null argument"); return EXA_ERR_INVALID; }
+  for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
+    if (enabled[i] && (channels[i] < 0 || channels[i] >= r->numFields)) { setError("updateIsoValues: channel out of range"); return EXA_ERR_INVALID; }
+    r->fs.isoSurface[i].value = isoValues[i]; r->fs.isoSurface[i].channel = channels[i]; r->fs.isoSurface[i].enabled = enabled[i] ? 1 : 0;
+  }
+  r->masksDirty = true;                                     // needIsoBVHRebuild (:501)
+  return EXA_OK;
+}
+
+int exa_renderer_update_frame_id(exa_renderer_t *r, int frameID) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->fs.frameID = frameID; return EXA_OK; }
+int exa_renderer_update_dt(exa_renderer_t *r, float dt) { if (!r || !(dt > 0.f)) { setError("updateDt: dt must be > 0"); return EXA_ERR_INVALID; } r->dt = dt; return EXA_OK; }
+int exa_renderer_set_space_skipping(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->spaceSkipping = enable != 0; r->masksDirty = true; return EXA_OK; }
+int exa_renderer_set_gradient_shading_dvr(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->gradDVR = enable != 0; return EXA_OK; }
+int exa_renderer_set_gradient_shading_iso(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->gradISO = enable != 0; return EXA_OK; }
+int exa_renderer_set_ert_threshold(exa_renderer_t *r, float t) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->ert = t; return EXA_OK; }
+int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], const float hi[3])
+{
+  if (!r || (enable && (!lo || !hi))) { setError("null argument"); return EXA_ERR_INVALID; }
+  r->fs.clipBox.enabled = enable ? 1 : 0;
+  if (lo) memcpy(r->fs.clipBox.lower, lo, 12);
+  if (hi) memcpy(r->fs.clipBox.upper, hi, 12);
+  return EXA_OK;
+}
+uint64_t exa_renderer_launch_count(const exa_renderer_t *r) { return r ? r->launches : 0; }
+
+} // extern "C"
+
+#include "capi_render.inl"

@@ -1,0 +1,309 @@
+// capi_render.inl — second half of capi.cu: render(), sampling, tracer, sort-last helpers.
+
+static int refreshMasks(exa_renderer *r, RenderParams &P)
+{
+  if (!r->masksDirty) return EXA_OK;
+  // space skipping is forced off while a contour plane is enabled (OptixRenderer.cpp:418-432)
+  bool contour = false;
+  for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) contour |= r->fs.contourPlane[i].enabled != 0;
+  const uint8_t *inPart = r->partMode == EXA_PARTITION_SORT_LAST ? r->d_inPart : nullptr;
+  int n = launchRegionActivity(P, r->abr.levelOffset, !contour && r->spaceSkipping, inPart,
+                               r->d_regionVol, r->d_regionIso, r->d_volActive, r->d_isoActive, r->stream);
+  if (n < 0) { setError(std::string("activity kernels failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += n;
+  r->masksDirty = false;
+  return EXA_OK;
+}
+
+static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool sync)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (!r->d_accum || r->width <= 0) { setError("render: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  RenderParams P; fillParams(r, P);
+  int rc = refreshMasks(r, P); if (rc) return rc;
+  P.partialOut = partialOut;
+  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 32, r->stream)); P.stats = r->d_stats; }
+  if (launchRenderFrame(P, r->stream) < 0) { setError(std::string("frame kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches++;
+  if (stats) {
+    unsigned long long h[4];
+    CKR(cudaMemcpyAsync(h, r->d_stats, 32, cudaMemcpyDeviceToHost, r->stream));
+    CKR(cudaStreamSynchronize(r->stream));
+    stats->samples = h[0]; stats->brickVisits = h[1]; stats->cornerLoads = h[2]; stats->segments = h[3];
+  } else if (sync) CKR(cudaStreamSynchronize(r->stream));
+  return EXA_OK;
+}
+
+extern "C" {
+
+int exa_renderer_render(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, true); }
+int exa_renderer_render_async(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, false); }
+int exa_renderer_render_stats(exa_renderer_t *r, ExaStats *stats)
+{
+  if (!stats) { setError("null stats"); return EXA_ERR_INVALID; }
+  return doRender(r, nullptr, stats, true);
+}
+int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA)
+{
+  if (!d_partialRGBA) { setError("null partial buffer"); return EXA_ERR_INVALID; }
+  return doRender(r, (float4 *)d_partialRGBA, nullptr, false);
+}
+int exa_renderer_sync(exa_renderer_t *r)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device)); CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+}
+
+int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut)
+{
+  if (!r || !hostOut || !r->d_rgba8) { setError("read_rgba8: no framebuffer"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(hostOut, r->d_rgba8, (size_t)r->width * r->height * 4, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+}
+int exa_renderer_read_accum(exa_renderer_t *r, float *hostOut)
+{
+  if (!r || !hostOut || !r->d_accum) { setError("read_accum: no framebuffer"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(hostOut, r->d_accum, (size_t)r->width * r->height * 16, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+}
+int exa_renderer_device_buffers(exa_renderer_t *r, void **accum, void **rgba8)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (accum) *accum = r->d_accum;
+  if (rgba8) *rgba8 = r->d_rgba8;
+  return EXA_OK;
+}
+
+// ---- point sampling ------------------------------------------------------------------
+static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int channel, float *d_values, uint8_t *d_valid, float *d_grad, ExaStats *stats)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (channel < 0 || channel >= r->numFields) { setError("sample_points: channel out of range"); return EXA_ERR_INVALID; }
+  if (n && !d_xyz) { setError("sample_points: null points"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  RenderParams RP; fillParams(r, RP);
+  SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
+  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 32, r->stream)); P.stats = r->d_stats; }
+  const int k = launchSamplePoints(P, r->stream);
+  if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  if (stats) {
+    unsigned long long h[4];
+    CKR(cudaMemcpyAsync(h, r->d_stats, 32, cudaMemcpyDeviceToHost, r->stream));
+    CKR(cudaStreamSynchronize(r->stream));
+    stats->samples = h[0]; stats->brickVisits = h[1]; stats->cornerLoads = h[2]; stats->segments = h[3];
+  }
+  return EXA_OK;
+}
+
+int exa_sample_points_device(exa_renderer_t *r, const float *d_xyz, size_t n, int channel, float *d_values, uint8_t *d_valid, float *d_grad)
+{ return samplePointsDev(r, d_xyz, n, channel, d_values, d_valid, d_grad, nullptr); }
+
+int exa_sample_points_stats(exa_renderer_t *r, const float *d_xyz, size_t n, int channel, ExaStats *stats)
+{
+  if (!stats) { setError("null stats"); return EXA_ERR_INVALID; }
+  return samplePointsDev(r, d_xyz, n, channel, nullptr, nullptr, nullptr, stats);
+}
+
+int exa_sample_points_host(exa_renderer_t *r, const float *xyz, size_t n, int channel, float *values, uint8_t *valid, float *grad)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (n == 0) return EXA_OK;
+  if (!xyz || !values || !valid) { setError("sample_points: null argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  float *d_xyz = nullptr, *d_val = nullptr, *d_grad = nullptr; uint8_t *d_ok = nullptr;
+  int rc = EXA_OK;
+  cudaError_t e;
+  if ((e = cudaMalloc(&d_xyz, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_val, n * 4)) != cudaSuccess || (e = cudaMalloc(&d_ok, n)) != cudaSuccess ||
+      (grad && (e = cudaMalloc(&d_grad, n * 12)) != cudaSuccess)) { setError(std::string("CUDA error: ") + cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
+  if (!rc && (e = cudaMemcpyAsync(d_xyz, xyz, n * 12, cudaMemcpyHostToDevice, r->stream)) != cudaSuccess) { setError(cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
+  if (!rc) rc = samplePointsDev(r, d_xyz, n, channel, d_val, d_ok, d_grad, nullptr);
+  if (!rc) {
+    cudaMemcpyAsync(values, d_val, n * 4, cudaMemcpyDeviceToHost, r->stream);
+    cudaMemcpyAsync(valid, d_ok, n, cudaMemcpyDeviceToHost, r->stream);
+    if (grad) cudaMemcpyAsync(grad, d_grad, n * 12, cudaMemcpyDeviceToHost, r->stream);
+    if ((e = cudaStreamSynchronize(r->stream)) != cudaSuccess) { setError(std::string("CUDA error: ") + cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
+  }
+  cudaFree(d_xyz); cudaFree(d_val); cudaFree(d_ok); cudaFree(d_grad);
+  return rc;
+}
+
+// ---- tracer (OptixRenderer.cpp:444-487) ----------------------------------------------
+int exa_renderer_set_tracer_enabled(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->tracerEnabled = enable != 0; return EXA_OK; }
+
+int exa_renderer_set_tracer_params(exa_renderer_t *r, int numTraces, int numTimesteps, float steplen, const int channels[3],
+                                   const float seedLo[3], const float seedHi[3])
+{
+  if (!r || numTraces < 0 || numTimesteps < 1) { setError("set_tracer_params: bad argument"); return EXA_ERR_INVALID; }
+  if (channels) for (int i = 0; i < 3; i++) if (channels[i] < 0 || channels[i] >= r->numFields) { setError("tracer channel out of range"); return EXA_ERR_INVALID; }
+  r->numTraces = numTraces; r->numTimesteps = numTimesteps; r->steplen = steplen;
+  if (channels) memcpy(r->tracerChannels, channels, 12);
+  if (seedLo) memcpy(r->seedLo, seedLo, 12);
+  if (seedHi) memcpy(r->seedHi, seedHi, 12);
+  return EXA_OK;
+}
+
+static int uploadSeeds(exa_renderer *r, const std::vector<float> &host)
+{
+  CKR(cudaSetDevice(r->device));
+  const size_t n = host.size();
+  if (n > r->tracesCap) { CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_traces); r->d_traces = nullptr; CKR(cudaMalloc(&r->d_traces, std::max(n, (size_t)3) * 4)); r->tracesCap = n; }
+  if (n) CKR(cudaMemcpyAsync(r->d_traces, host.data(), n * 4, cudaMemcpyHostToDevice, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  r->timestep = 0;
+  return EXA_OK;
+}
+
+int exa_renderer_reset_tracer(exa_renderer_t *r)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  for (int i = 0; i < 3; i++) if (r->tracerChannels[i] >= r->numFields) { setError("tracer needs 3 scalar channels (vx,vy,vz)"); return EXA_ERR_INVALID; }
+  // OptixRenderer::resetTracer (:450-460): seeds from std::default_random_engine(0), x,y,z in
+  // that order, uniform in seedRegion * voxel-bounds EXTENT (not offset by bounds.lower)
+  std::vector<float> host((size_t)r->numTraces * r->numTimesteps * 3, 0.f);
+  const float size[3] = {r->voxelHi[0] - r->voxelLo[0], r->voxelHi[1] - r->voxelLo[1], r->voxelHi[2] - r->voxelLo[2]};
+  std::default_random_engine engine(0);
+  std::uniform_real_distribution<float> x(r->seedLo[0] * size[0], r->seedHi[0] * size[0]);
+  std::uniform_real_distribution<float> y(r->seedLo[1] * size[1], r->seedHi[1] * size[1]);
+  std::uniform_real_distribution<float> z(r->seedLo[2] * size[2], r->seedHi[2] * size[2]);
+  for (int i = 0; i < r->numTraces; i++) {
+    float *p = host.data() + (size_t)i * r->numTimesteps * 3;
+    p[0] = x(engine); p[1] = y(engine); p[2] = z(engine);
+  }
+  return uploadSeeds(r, host);
+}
+
+int exa_renderer_set_tracer_seeds(exa_renderer_t *r, const float *xyz, int numTraces)
+{
+  if (!r || !xyz || numTraces < 0) { setError("set_tracer_seeds: bad argument"); return EXA_ERR_INVALID; }
+  for (int i = 0; i < 3; i++) if (r->tracerChannels[i] >= r->numFields) { setError("tracer needs 3 scalar channels (vx,vy,vz)"); return EXA_ERR_INVALID; }
+  r->numTraces = numTraces;
+  std::vector<float> host((size_t)numTraces * r->numTimesteps * 3, 0.f);
+  for (int i = 0; i < numTraces; i++) memcpy(host.data() + (size_t)i * r->numTimesteps * 3, xyz + 3 * i, 12);
+  return uploadSeeds(r, host);
+}
+
+static int traceSteps(exa_renderer *r, int first, int last)
+{
+  if (!r->d_traces) { setError("tracer: resetTracer was never called"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  RenderParams RP; fillParams(r, RP);
+  TraceParams P; P.scene = RP.scene; P.traces = r->d_traces; P.numTraces = r->numTraces; P.numTimesteps = r->numTimesteps;
+  P.firstStep = first; P.lastStep = last; memcpy(P.channels, r->tracerChannels, 12); P.steplen = r->steplen;
+  memcpy(P.worldLo, r->worldLo, 12); memcpy(P.worldHi, r->worldHi, 12);
+  const int k = launchTrace(P, r->stream);
+  if (k < 0) { setError(std::string("trace kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  return EXA_OK;
+}
+
+int exa_renderer_advance_tracer(exa_renderer_t *r, int *rebuilt)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (rebuilt) *rebuilt = 0;
+  if (!r->tracerEnabled) return EXA_OK;                      // advanceTracer (:476-487)
+  r->timestep++;
+  if (r->timestep <= r->numTimesteps) {
+    if (rebuilt) *rebuilt = 1;
+    if (r->timestep < r->numTimesteps) return traceSteps(r, r->timestep, r->timestep);   // device: t < numTimesteps (exabrick.cu:1539)
+  }
+  return EXA_OK;
+}
+
+int exa_renderer_trace_all(exa_renderer_t *r)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  const int first = r->timestep + 1;
+  if (first >= r->numTimesteps) return EXA_OK;
+  int rc = traceSteps(r, first, r->numTimesteps - 1);
+  if (!rc) r->timestep = r->numTimesteps;
+  return rc;
+}
+
+int exa_renderer_read_traces(exa_renderer_t *r, float *xyz)
+{
+  if (!r || !xyz || !r->d_traces) { setError("read_traces: no traces"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(xyz, r->d_traces, (size_t)r->numTraces * r->numTimesteps * 12, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  return EXA_OK;
+}
+
+// ---- multi-GPU ------------------------------------------------------------------------
+int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRanks)
+{
+  if (!r || numRanks < 1 || rank < 0 || rank >= numRanks) { setError("set_partition: bad rank"); return EXA_ERR_INVALID; }
+  if (mode != EXA_PARTITION_NONE && mode != EXA_PARTITION_SORT_LAST && mode != EXA_PARTITION_IMAGE_TILES) { setError("set_partition: bad mode"); return EXA_ERR_INVALID; }
+  r->partMode = mode; r->rank = rank; r->numRanks = numRanks; r->masksDirty = true;
+  r->partPath.clear(); r->partRoot = 0;
+  if (mode != EXA_PARTITION_SORT_LAST) return EXA_OK;
+  int levels = 0; while ((1 << levels) < numRanks) levels++;
+  if ((1 << levels) != numRanks) { setError("sort-last needs a power-of-two rank count"); return EXA_ERR_INVALID; }
+  // Walk the top `levels` levels of the ABR kd-tree, most significant rank bit first:
+  // bit 0 -> left (below the plane), 1 -> right.  If a leaf is reached early, the rank whose
+  // remaining bits are all 0 keeps it and the others own nothing.
+  int node = 0;
+  for (int l = 0; l < levels; l++) {
+    const int bit = (rank >> (levels - 1 - l)) & 1;
+    const KdNode nd = r->h_kd[node];
+    r->partPath.push_back(node);
+    if ((nd.info >> 30) == 3) {
+      const int rest = rank & ((1 << (levels - l)) - 1);
+      if (rest != 0) node = -1;
+      for (int k = l + 1; k < levels; k++) r->partPath.push_back(-1);
+      break;
+    }
+    node = (int)(nd.info & 0x3fffffffu) + bit;
+  }
+  r->partRoot = node;
+  CKR(cudaSetDevice(r->device));
+  const int k = launchPartitionMask(r->abr.kd, r->abr.levelOffset, node, r->d_inPart, r->stream);
+  if (k < 0) { setError("partition mask kernels failed"); return EXA_ERR_CUDA; }
+  r->launches += k;
+  return EXA_OK;
+}
+
+int exa_renderer_swap_order(exa_renderer_t *r, int round, int *iAmFront)
+{
+  if (!r || !iAmFront || r->partMode != EXA_PARTITION_SORT_LAST) { setError("swap_order: renderer is not in sort-last mode"); return EXA_ERR_INVALID; }
+  int levels = 0; while ((1 << levels) < r->numRanks) levels++;
+  if (round < 0 || round >= levels) { setError("swap_order: bad round"); return EXA_ERR_INVALID; }
+  // partner = rank ^ (1<<round): both share the path down to tree level (levels-1-round)
+  const int lvl = levels - 1 - round;
+  const int node = lvl < (int)r->partPath.size() ? r->partPath[lvl] : -1;
+  const int myBit = (r->rank >> round) & 1;
+  if (node < 0 || (r->h_kd[node].info >> 30) == 3) { *iAmFront = myBit == 0; return EXA_OK; }   // one side is empty: order is irrelevant
+  const KdNode nd = r->h_kd[node];
+  const int axis = (int)(nd.info >> 30);
+  // camera position in voxel space decides which half-space is in front for every pixel
+  const float *m = (const float *)&r->fs.voxelSpaceTransform; const float *p = r->fs.camera.pos;
+  const float camV = p[0] * m[axis] + p[1] * m[3 + axis] + p[2] * m[6 + axis] + m[9 + axis];
+  const bool camBelow = camV < nd.split;
+  *iAmFront = (myBit == 0) == camBelow;
+  return EXA_OK;
+}
+
+int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, size_t count, int mineIsFront)
+{
+  if (!r || !d_mine || !d_other) { setError("composite_over: null argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  const int k = launchCompositeOver((float4 *)d_mine, (const float4 *)d_other, count, mineIsFront, r->ert, r->stream);
+  if (k < 0) { setError("composite kernel launch failed"); return EXA_ERR_CUDA; }
+  r->launches += k; return EXA_OK;
+}
+
+int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_comp, size_t first, size_t count, uint32_t *d_rgba8Out)
+{
+  if (!r || !d_comp || !d_rgba8Out || !r->d_accum) { setError("finish_pixels: bad argument"); return EXA_ERR_INVALID; }
+  if (first + count > (size_t)r->width * r->height) { setError("finish_pixels: range outside the frame"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  RenderParams P; fillParams(r, P);
+  const int k = launchFinishPixels(P, (const float4 *)d_comp, first, count, d_rgba8Out, r->stream);
+  if (k < 0) { setError("finish kernel launch failed"); return EXA_ERR_CUDA; }
+  r->launches += k; return EXA_OK;
+}
+
+} // extern "C"

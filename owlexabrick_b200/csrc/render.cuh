@@ -1,0 +1,61 @@
+// render.cuh — parameters of the fused frame kernels (render.cu)
+#pragma once
+#include "exa_internal.h"
+#include <cuda_runtime.h>
+
+namespace exa {
+
+struct RenderParams {
+  DeviceScene scene;
+  // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
+  float camPos[3], dir00[3], dirDu[3], dirDv[3];
+  float xfm[12];                       // voxelSpaceTransform: vx, vy, vz, p
+  int width, height, frameID;
+  float dt;
+  int numChannels, colormapChannel;
+  int gradDVR, gradISO;
+  float xfOpacityScale;
+  float xfDomain[EXA_MAX_CHANNELS][2];
+  const float4 *xf;                    // [numFields][128] rgba tables
+  int isoEnabled[2]; float isoValue[2]; int isoChannel[2]; int anyIso;
+  int clipEnabled; float clipLo[3], clipHi[3];
+  float ertThreshold;
+  const uint8_t *volActive;            // per kd node: subtree has an active region (space skipping x partition)
+  const uint8_t *isoActive;            // per kd node: subtree has a region whose range holds an iso value
+  float4 *accum; uint32_t *rgba8;
+  float4 *partialOut;                  // != null: write premultiplied partial, skip bg/accum/pack
+  int tileMode, rank, numRanks;        // image-tile partition
+  const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones
+  unsigned long long *stats;           // 4 counters (ExaStats) or null
+  int kdStack;                         // stack entries per warp
+};
+
+struct SampleParams {
+  DeviceScene scene;
+  const float *xyz; size_t n; int channel;
+  float *values; uint8_t *valid; float *grad;
+  unsigned long long *stats;
+};
+
+struct TraceParams {
+  DeviceScene scene;
+  float *traces; int numTraces, numTimesteps;
+  int firstStep, lastStep;             // advance steps [firstStep, lastStep]
+  int channels[3]; float steplen;
+  float worldLo[3], worldHi[3];
+};
+
+// launchers (render.cu); each returns the number of kernels launched or <0 on error
+int launchRenderFrame(const RenderParams &P, cudaStream_t s);
+int launchSamplePoints(const SampleParams &P, cudaStream_t s);
+int launchTrace(const TraceParams &P, cudaStream_t s);
+int launchRegionActivity(const RenderParams &P, const std::vector<int> &levelOffset, int spaceSkipping,
+                         const uint8_t *nodeInPartition, uint8_t *regionVol, uint8_t *regionIso,
+                         uint8_t *volActive, uint8_t *isoActive, cudaStream_t s);
+int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
+int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellIDs, size_t numCells, float *d_out,
+                 int *d_errFlag, cudaStream_t s);
+int launchCompositeOver(float4 *mine, const float4 *other, size_t count, int mineIsFront, float ertThreshold, cudaStream_t s);
+int launchFinishPixels(const RenderParams &P, const float4 *composited, size_t first, size_t count, uint32_t *rgba8Out, cudaStream_t s);
+
+} // namespace exa
