@@ -1,0 +1,110 @@
+"""Shared test helpers: the same scene / frame description fed to the CPU oracle (oracle/)
+and to the CUDA path (through the C ABI)."""
+import ctypes as C
+import numpy as np
+
+from owlexabrick_b200 import synth
+
+
+def xf_ramp(alpha_scale=1.0, colors=None):
+    """default viewer XF: alpha ramp i/127 (viewer.cpp:558-566) + a simple colour map"""
+    t = np.arange(128, dtype=np.float32) / np.float32(127)
+    alpha = (t * np.float32(alpha_scale)).astype(np.float32)
+    if colors is None:
+        rgb = np.stack([t, 1 - np.abs(2 * t - 1), 1 - t], axis=1).astype(np.float32)
+    else:
+        rgb = np.asarray(colors, np.float32)
+    return alpha, rgb
+
+
+class FrameDesc:
+    """everything that defines one frame; applied to both implementations"""
+
+    def __init__(self, width, height, cam, num_channels=1):
+        self.width, self.height = width, height
+        self.cam = cam                                  # pos, dir00, du, dv
+        self.xfm = np.array([1, 0, 0, 0, 1, 0, 0, 0, 1, 0, 0, 0], np.float32)
+        self.frame_id = 0
+        self.dt = 0.5
+        self.num_channels = num_channels
+        self.grad_dvr = True
+        self.grad_iso = True
+        self.space_skipping = True
+        self.opacity_scale = 1.0
+        self.xf = [xf_ramp() for _ in range(num_channels)]
+        self.xf_domain = [(0.0, 1.0)] * num_channels
+        self.iso = [(0, 0.0, 0), (0, 0.0, 0)]           # (enabled, value, channel)
+        self.clip = None
+        self.ert = 0.98
+
+    def to_orc(self, orc):
+        f = orc.OrcFrame()
+        for name, v in zip(("cam_pos", "cam_dir00", "cam_du", "cam_dv"), self.cam):
+            getattr(f, name)[:] = [float(x) for x in v]
+        f.xf_vx[:] = [float(x) for x in self.xfm[0:3]]
+        f.xf_vy[:] = [float(x) for x in self.xfm[3:6]]
+        f.xf_vz[:] = [float(x) for x in self.xfm[6:9]]
+        f.xf_p[:] = [float(x) for x in self.xfm[9:12]]
+        f.width, f.height, f.frameID, f.dt = self.width, self.height, self.frame_id, self.dt
+        f.numPrimaryChannels, f.colormapChannel = self.num_channels, 0
+        f.gradientShadingDVR, f.gradientShadingISO = int(self.grad_dvr), int(self.grad_iso)
+        f.spaceSkipping = int(self.space_skipping)
+        f.xfOpacityScale = self.opacity_scale
+        for c in range(self.num_channels):
+            f.xfDomain[c][0], f.xfDomain[c][1] = self.xf_domain[c]
+            alpha, rgb = self.xf[c]
+            tab = np.concatenate([rgb, alpha[:, None]], axis=1).astype(np.float32)
+            C.memmove(C.addressof(f.xf[c]), tab.ctypes.data, 128 * 16)
+        for i, (en, val, ch) in enumerate(self.iso):
+            f.isoEnabled[i], f.isoValue[i], f.isoChannel[i] = int(en), float(val), int(ch)
+        if self.clip is not None:
+            f.clipEnabled = 1
+            f.clipLo[:] = [float(x) for x in self.clip[0]]
+            f.clipHi[:] = [float(x) for x in self.clip[1]]
+        f.ertThreshold = self.ert
+        f.texFilter8bit = 0
+        f.partial = 0
+        f.traces = None
+        return f
+
+    def apply(self, r):
+        r.setVoxelSpaceTransform(self.xfm)
+        if r.fb_size != (self.width, self.height):
+            r.resizeFrameBuffer(None, (self.width, self.height))
+        r.updateCamera(*self.cam)
+        for c in range(self.num_channels):
+            alpha, rgb = self.xf[c]
+            r.updateXF(c, alpha, rgb, self.xf_domain[c], self.opacity_scale)
+        r.updateIsoValues([i[1] for i in self.iso], [i[2] for i in self.iso], [i[0] for i in self.iso])
+        r.updateFrameID(self.frame_id)
+        r.updateDt(self.dt)
+        r.setSpaceSkipping(self.space_skipping)
+        r.setGradientShadingDVR(self.grad_dvr)
+        r.setGradientShadingISO(self.grad_iso)
+        if self.clip is not None:
+            r.setClipBox(True, self.clip[0], self.clip[1])
+        else:
+            r.setClipBox(False)
+        r.setErtThreshold(self.ert)
+
+
+def unpack_rgba8(img):
+    img = np.asarray(img, np.uint32)
+    return np.stack([(img >> s) & 0xff for s in (0, 8, 16, 24)], axis=-1).astype(np.int32)
+
+
+def small_scene(kind="nb32", channels=1):
+    """cells + fields for small parity scenes"""
+    if kind == "nb32":
+        cells = synth.nested_boxes(32, [(10, 22), (4, 28)])
+        dom = 32
+    elif kind == "nb64":
+        cells = synth.nested_boxes(64, [(18, 46), (8, 56)])
+        dom = 64
+    elif kind == "nb64_off":              # off-centre refinement, 4 levels
+        cells = synth.nested_boxes(64, [((8, 16, 24), (24, 32, 40)), ((4, 8, 16), (36, 40, 48)), ((0, 0, 8), (48, 48, 56))])
+        dom = 64
+    else:
+        raise ValueError(kind)
+    fields = [synth.analytic_field(cells, dom, c) for c in range(channels)]
+    return cells, fields, dom

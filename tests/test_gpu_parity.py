@@ -1,0 +1,303 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI,
+against the CPU oracle on the same seeded inputs and against the golden fixtures made from
+the reference's own code.
+
+Bars (BASELINE.json north_star): ABR/brick/cell-ID construction bit-exact; reconstructed
+scalars within 1e-5 relative; rendered RGBA within 1e-3 max absolute per channel at an
+identical step size, jitter and transfer function.
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, load_golden
+from owlexabrick_b200 import synth
+import scenes
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-5          # reconstruction: |gpu-oracle| <= REL_TOL * max(|oracle|, 1e-3 * max|field|)
+RGBA_TOL = 1e-3         # frame: max abs per channel of the linear float colour
+
+
+@pytest.fixture(scope="module")
+def R(built_lib):
+    assert built_lib.lib.exa_cuda_available() == 1, built_lib.last_error()
+    from owlexabrick_b200 import renderer
+    return renderer
+
+
+def make_pair(R, orc, cells, fields, mlw=127):
+    """(product renderer, oracle scene) over the same input"""
+    b = R.ExaBricks.build(cells, max_leaf_width=mlw)
+    r = R.Renderer(b, fields)
+    bricks, ids = b.headers, b.cell_ids
+    sc = orc.flatten_scalars(ids, fields)
+    regions, leaf = orc.build_abr(bricks.view(orc.BRICK_DT), sc)
+    return r, orc.Scene(bricks.view(orc.BRICK_DT), sc, regions, leaf), b
+
+
+# ------------------------------------------------------------------------------------------
+# ABR build (exa/Regions.cpp) — bit-exact
+# ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["ex0", "ex1", "ex2", "ex3", "ex4", "nb64", "nb64_mlw8", "nb64_dups"])
+def test_abr_bit_exact_vs_reference_golden(R, orc, name):
+    g = load_golden(name)
+    b = R.ExaBricks.from_bytes(g["bricks"].tobytes())
+    r = R.Renderer(b, list(g["fields"]))
+    regions, leaf = r.get_abr()
+    rr, rl = orc.parse_abr(g["abr"].tobytes())
+    assert len(regions) == len(rr) and len(leaf) == len(rl)
+    assert leaf.tobytes() == rl.tobytes()
+    assert regions.tobytes() == rr.tobytes()
+
+
+@pytest.mark.parametrize("kind,mlw,channels", [("nb32", 127, 1), ("nb64_off", 127, 3), ("nb64_off", 6, 2), ("nb64", 4, 1)])
+def test_abr_bit_exact_vs_oracle(R, orc, kind, mlw, channels):
+    cells, fields, _ = scenes.small_scene(kind, channels)
+    r, sc, _ = make_pair(R, orc, cells, fields, mlw)
+    regions, leaf = r.get_abr()
+    assert leaf.tobytes() == sc.leaf.tobytes()
+    assert regions.tobytes() == sc.regions.tobytes()
+    nodes, depth = r.kd_info()
+    assert nodes >= 2 * len(regions) - 1 and depth >= 1
+
+
+def test_abr_c1_hash_vs_reference(R, orc):
+    """config C1 (2.27 M cells): GPU ABR output == reference buildFrom output (SHA-256)"""
+    hashes = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))
+    cells = synth.nested_boxes(256, [(72, 184), (32, 224)])
+    b = R.ExaBricks.build(cells)
+    r = R.Renderer(b, [synth.analytic_field(cells, 256, 0)])
+    regions, leaf = r.get_abr()
+    raw = np.array([len(regions), len(leaf)], "<i4").tobytes() + regions.tobytes() + leaf.tobytes()
+    assert hashlib.sha256(raw).hexdigest() == hashes["C1"]["abr_sha256"]
+
+
+# ------------------------------------------------------------------------------------------
+# tent-basis reconstruction (exabrick.cu:620-816, 883-942) — 1e-5 relative
+# ------------------------------------------------------------------------------------------
+def _check_samples(gv, gok, ov, ook, fmax):
+    assert (gok == ook).all(), "validity differs at %d points" % int((gok != ook).sum())
+    m = ook == 1
+    err = np.abs(gv[m].astype(np.float64) - ov[m])
+    bound = REL_TOL * np.maximum(np.abs(ov[m]), 1e-3 * fmax)
+    assert (err <= bound).all(), "max rel err %.3g" % float((err / np.maximum(np.abs(ov[m]), 1e-3 * fmax)).max())
+
+
+@pytest.mark.parametrize("kind,mlw,channels", [("nb32", 127, 1), ("nb64_off", 127, 3), ("nb64_off", 6, 2), ("nb64", 4, 1)])
+def test_reconstruction_vs_oracle(R, orc, kind, mlw, channels):
+    cells, fields, dom = scenes.small_scene(kind, channels)
+    r, sc, _ = make_pair(R, orc, cells, fields, mlw)
+    pts = synth.random_points(200000, [-1.0] * 3, [dom + 1.0] * 3, seed=1)
+    for c in range(channels):
+        gv, gok = r.sample_points(pts, c)
+        ov, ook, _ = sc.sample(pts, c)
+        _check_samples(gv, gok, ov, ook, float(np.abs(fields[c]).max()))
+    gv, gok, gg = r.sample_points(pts, 0, grad=True)
+    ov, ook, og, _ = sc.sample(pts, 0, grad=True)
+    _check_samples(gv, gok, ov, ook, float(np.abs(fields[0]).max()))
+    m = ook == 1
+    gscale = np.abs(og[m]).max()
+    assert np.abs(gg[m] - og[m]).max() <= 1e-4 * gscale
+
+
+def test_reconstruction_1m_points_c1(R, orc):
+    """north_star gate: 1 M random points on config C1 within 1e-5 relative"""
+    cells = synth.nested_boxes(256, [(72, 184), (32, 224)])
+    f = synth.analytic_field(cells, 256, 0)
+    r, sc, _ = make_pair(R, orc, cells, [f])
+    pts = synth.random_points(1000000, [0.0] * 3, [256.0] * 3, seed=1)
+    gv, gok = r.sample_points(pts, 0)
+    ov, ook, st = sc.sample(pts, 0)
+    _check_samples(gv, gok, ov, ook, float(np.abs(f).max()))
+    assert gok.sum() > 990000
+    # instrumented run: the counters behind the algorithmic-bytes model equal the oracle's
+    import torch
+    d = torch.from_numpy(pts).cuda()
+    gs = r.sample_points_stats(d.data_ptr(), len(pts), 0)
+    assert gs["brickVisits"] == st["brickVisits"] and gs["cornerLoads"] == st["cornerLoads"]
+
+
+def test_reconstruction_edge_cases(R, orc):
+    cells, fields, dom = scenes.small_scene("nb32")
+    r, sc, _ = make_pair(R, orc, cells, fields)
+    gv, gok = r.sample_points(np.zeros((0, 3), np.float32))
+    assert len(gv) == 0
+    # points on region faces, on the outer boundary, far outside, NaN
+    faces = np.unique(np.concatenate([sc.regions["lo"].ravel(), sc.regions["hi"].ravel()]))
+    rng = np.random.RandomState(2)
+    pts = rng.uniform(0, dom, size=(3000, 3)).astype(np.float32)
+    pts[:1000, 0] = rng.choice(faces, 1000)
+    pts[1000:2000, 1] = rng.choice(faces, 1000)
+    pts[2000:, 2] = rng.choice(faces, 1000)
+    extra = np.array([[-0.5, -0.5, -0.5], [dom + 0.5] * 3, [1e9, 0, 0], [np.nan, 1, 1], [-1e9, -1e9, -1e9]], np.float32)
+    pts = np.concatenate([pts, extra])
+    gv, gok = r.sample_points(pts)
+    ov, ook, _ = sc.sample(pts)
+    _check_samples(gv, gok, ov, ook, 1.0)
+    with pytest.raises(Exception):
+        r.sample_points(pts, channel=5)
+
+
+# ------------------------------------------------------------------------------------------
+# frames: DVR, gradient shading, clip box, accumulation, iso-surfaces — 1e-3 abs
+# ------------------------------------------------------------------------------------------
+def _frame_pair(R, orc, kind="nb32", channels=1, size=(96, 64), mlw=127):
+    cells, fields, dom = scenes.small_scene(kind, channels)
+    r, sc, _ = make_pair(R, orc, cells, fields, mlw)
+    cam = R.default_camera([0] * 3, [dom] * 3, size[0], size[1])
+    return r, sc, scenes.FrameDesc(size[0], size[1], cam, channels), dom
+
+
+def _render_both(r, sc, fd, orc, accum=None):
+    fd.apply(r)
+    r.render()
+    g_acc, g_rgba = r.read_accum(), r.read_rgba8()
+    o_acc, o_rgba, o_st = sc.render(fd.to_orc(orc), accum=accum)
+    return g_acc, g_rgba, o_acc, o_rgba, o_st
+
+
+def _assert_frame(g_acc, g_rgba, o_acc, o_rgba):
+    err = np.abs(g_acc[..., :3] - o_acc[..., :3]).max()
+    assert err <= RGBA_TOL, "max abs colour error %.3g" % err
+    d8 = np.abs(scenes.unpack_rgba8(g_rgba) - scenes.unpack_rgba8(o_rgba)).max()
+    assert d8 <= 1, "RGBA8 differs by %d levels" % d8
+    assert o_acc[..., :3].max() > 0.05, "test frame is empty"
+
+
+@pytest.mark.parametrize("grad", [True, False])
+@pytest.mark.parametrize("kind,channels,mlw", [("nb32", 1, 127), ("nb64_off", 2, 127), ("nb64", 1, 6)])
+def test_dvr_frame_vs_oracle(R, orc, kind, channels, mlw, grad):
+    r, sc, fd, dom = _frame_pair(R, orc, kind, channels, mlw=mlw)
+    fd.grad_dvr = grad
+    fd.opacity_scale = 0.3
+    _assert_frame(*_render_both(r, sc, fd, orc)[:4])
+
+
+def test_dvr_stats_match_oracle(R, orc):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 1)
+    fd.opacity_scale = 0.2
+    fd.apply(r)
+    gs = r.render_stats()
+    _, _, os_ = sc.render(fd.to_orc(orc))
+    for k in ("samples", "brickVisits", "cornerLoads", "segments"):
+        assert abs(gs[k] - os_[k]) <= 2e-3 * os_[k] + 32 * fd.width * fd.height * (k != "segments"), (k, gs[k], os_[k])
+
+
+def test_dvr_no_ert_no_skipping_dt(R, orc):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 1)
+    fd.ert = 2.0
+    fd.space_skipping = False
+    fd.dt = 0.8
+    fd.opacity_scale = 0.05
+    _assert_frame(*_render_both(r, sc, fd, orc)[:4])
+
+
+def test_dvr_space_skipping_partial_xf(R, orc):
+    """XF that is transparent below 0.6: most regions must be skipped, result unchanged"""
+    r, sc, fd, dom = _frame_pair(R, orc, "nb64", 1, mlw=8)
+    alpha, rgb = fd.xf[0]
+    alpha = np.where(np.arange(128) / 127.0 < 0.6, 0.0, alpha).astype(np.float32)
+    fd.xf[0] = (alpha, rgb)
+    g_acc, g_rgba, o_acc, o_rgba, _ = _render_both(r, sc, fd, orc)
+    _assert_frame(g_acc, g_rgba, o_acc, o_rgba)
+    fd.space_skipping = False
+    g2, _, _, _, _ = _render_both(r, sc, fd, orc)
+    assert np.abs(g2 - g_acc).max() <= 1e-5
+
+
+def test_dvr_clip_box_and_transform(R, orc):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 1)
+    # world = voxel/16 - 1  <=>  voxel = 16*(world+1)
+    fd.xfm = np.array([16, 0, 0, 0, 16, 0, 0, 0, 16, 16, 16, 16], np.float32)
+    fd.cam = R.default_camera([-1] * 3, [1] * 3, fd.width, fd.height)
+    fd.clip = ([-0.5, -1, -1], [0.7, 1, 0.4])
+    fd.opacity_scale = 0.3
+    _assert_frame(*_render_both(r, sc, fd, orc)[:4])
+
+
+def test_progressive_accumulation(R, orc):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 1, size=(48, 32))
+    fd.opacity_scale = 0.3
+    o_acc = None
+    for frame in range(3):
+        fd.frame_id = frame
+        g_acc, g_rgba, o_acc, o_rgba, _ = _render_both(r, sc, fd, orc, accum=o_acc)
+        assert np.abs(g_acc[..., :3] - o_acc[..., :3]).max() <= RGBA_TOL * (frame + 1)
+        assert np.abs(scenes.unpack_rgba8(g_rgba) - scenes.unpack_rgba8(o_rgba)).max() <= 1
+
+
+@pytest.mark.parametrize("grad_iso", [True, False])
+def test_iso_surface_plus_dvr(R, orc, grad_iso):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb64_off", 1)
+    fd.iso = [(1, 0.5, 0), (0, 0.0, 0)]
+    fd.grad_iso = grad_iso
+    fd.opacity_scale = 0.02
+    g_acc, g_rgba, o_acc, o_rgba, _ = _render_both(r, sc, fd, orc)
+    # an iso hit decided by samples that bracket the value to within rounding may flip
+    # between implementations: allow a handful of pixels, bound everything else
+    err = np.abs(g_acc[..., :3] - o_acc[..., :3]).max(axis=-1)
+    assert (err > RGBA_TOL).sum() <= 0.002 * err.size, "%d pixels differ" % int((err > RGBA_TOL).sum())
+    assert o_acc[..., :3].max() > 0.2
+
+
+def test_two_iso_surfaces(R, orc):
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 2)
+    fd.iso = [(1, 0.35, 0), (1, 0.65, 1)]
+    fd.xf[0] = (np.zeros(128, np.float32), fd.xf[0][1])      # no DVR contribution from channel 0
+    fd.xf[1] = (np.zeros(128, np.float32), fd.xf[1][1])
+    g_acc, g_rgba, o_acc, o_rgba, _ = _render_both(r, sc, fd, orc)
+    err = np.abs(g_acc[..., :3] - o_acc[..., :3]).max(axis=-1)
+    assert (err > RGBA_TOL).sum() <= 0.005 * err.size, "%d pixels differ" % int((err > RGBA_TOL).sum())
+
+
+def test_render_errors(R, orc):
+    g = load_golden("ex4")
+    b = R.ExaBricks.from_bytes(g["bricks"].tobytes())
+    r = R.Renderer(b, [g["fields"][0]])
+    with pytest.raises(Exception, match="resizeFrameBuffer"):
+        r.render()
+    with pytest.raises(RuntimeError, match="mismatching xf size"):
+        r.updateXF(0, np.zeros(100, np.float32), np.zeros((100, 3), np.float32), (0, 1), 1.0)
+    with pytest.raises(Exception):
+        R.Renderer(b, [g["fields"][0][:50]])                 # "invalid cell ID" (OptixRenderer.cpp:125)
+    lp, fs = r.launch_params()
+    assert len(lp) == 240 and len(fs) == 408
+    assert r.launch_count() > 0
+
+
+# ------------------------------------------------------------------------------------------
+# streamlines (exabrick.cu:1531-1574)
+# ------------------------------------------------------------------------------------------
+def test_streamlines_vs_oracle(R, orc):
+    cells, _, dom = scenes.small_scene("nb64_off")
+    c = cells[:, :3] + 0.5 * (1 << cells[:, 3:4])
+    ctr = np.array([32, 32, 32.0])
+    # swirling flow around the z axis plus drift
+    vx = (-(c[:, 1] - ctr[1]) * 0.05 + 0.2).astype(np.float32)
+    vy = ((c[:, 0] - ctr[0]) * 0.05).astype(np.float32)
+    vz = (0.3 + 0.002 * c[:, 2]).astype(np.float32)
+    r, sc, _ = make_pair(R, orc, cells, [vx, vy, vz])
+    seeds = synth.random_points(200, [10, 10, 4], [54, 54, 20], seed=11)
+    T = 60
+    r.setTracerParams(len(seeds), T, 0.7, (0, 1, 2))
+    r.setTracerSeeds(seeds)
+    r.setTracerEnabled(True)
+    r.traceAll()
+    g = r.readTraces()
+    o = sc.trace(seeds, T, (0, 1, 2), 0.7, [0, 0, 0], [dom] * 3)
+    dead_g, dead_o = g[..., 0] >= 2e10, o[..., 0] >= 2e10
+    # a trace may die one step earlier/later when it grazes the boundary
+    assert (dead_g != dead_o).sum() <= 3
+    m = ~dead_g & ~dead_o
+    assert m.sum() > 0.5 * m.size
+    assert np.abs(g[m] - o[m]).max() <= 1e-5 * dom * 4       # <= 1e-5 relative to the domain, accumulated over 60 RK4 steps
+    # per-frame stepping (advanceTracer) gives the same vertices as traceAll
+    r.setTracerSeeds(seeds)
+    for _ in range(T + 2):
+        r.advanceTracer()
+    assert np.array_equal(r.readTraces(), g)

@@ -1,0 +1,171 @@
+"""CPU tests of the product's host side: the bit-exact builder, loaders/file formats, the
+C-ABI surface (every symbol of include/exabrick_b200.h is exported) and loud failure
+without a GPU.  No compute call needs a device here."""
+import ctypes as C
+import hashlib
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, ROOT, load_golden
+from owlexabrick_b200 import synth
+
+CASES = ["ex0", "ex1", "ex2", "ex3", "ex4", "nb64", "nb64_mlw8", "nb64_dups"]
+
+
+@pytest.fixture(scope="module")
+def R(built_lib):
+    from owlexabrick_b200 import renderer
+    return renderer
+
+
+def test_header_symbols_exported(built_lib):
+    hdr = open(os.path.join(ROOT, "include", "exabrick_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(exa_[a-z0-9_]+)\s*\(", hdr))
+    assert len(declared) > 50
+    for name in sorted(declared):
+        assert hasattr(built_lib.lib, name), "library does not export " + name
+    assert declared == set(built_lib.EXPORTS), declared ^ set(built_lib.EXPORTS)
+
+
+def test_pod_sizes(built_lib, R):
+    assert R.BRICK_DT.itemsize == 32 and R.REGION_DT.itemsize == 44 and R.KD_DT.itemsize == 12
+    assert C.sizeof(built_lib.ExaFrameState) == 408 and C.sizeof(built_lib.ExaLaunchParams) == 240
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_builder_bit_exact_with_reference(R, name):
+    g = load_golden(name)
+    b = R.ExaBricks.build(g["cells"], max_leaf_width=int(g["max_leaf_width"]))
+    assert b.to_bytes() == g["bricks"].tobytes()
+
+
+def test_builder_c1_hash(R):
+    hashes = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))
+    cells = synth.nested_boxes(256, [(72, 184), (32, 224)])
+    b = R.ExaBricks.build(cells)
+    assert hashlib.sha256(b.to_bytes()).hexdigest() == hashes["C1"]["bricks_sha256"]
+    assert b.total_num_cells == len(cells)
+
+
+def test_builder_matches_oracle_on_ragged_input(R, orc):
+    """shuffled order, duplicates, negative coordinates, 4 levels, odd leaf widths"""
+    cells, _, _ = __import__("scenes").small_scene("nb64_off")
+    cells = cells.copy()
+    cells[:, :3] -= np.array([40, 8, 24], np.int32)          # negative coordinates (multiples of 8)
+    rng = np.random.RandomState(3)
+    cells = np.concatenate([cells, cells[rng.randint(0, len(cells), 300)]])[rng.permutation(len(cells) + 300)]
+    for mlw in (127, 5):
+        b = R.ExaBricks.build(cells, max_leaf_width=mlw)
+        assert b.to_bytes() == orc.build_bricks(cells, mlw)
+
+
+def test_builder_spatial_median_and_kd(R, built_lib):
+    cells = synth.nested_boxes(32, [(10, 22), (4, 28)])
+    b = R.ExaBricks.build(cells, builder=built_lib.BUILDER_SPATIAL_MEDIAN)
+    assert b.total_num_cells == len(cells)
+    assert sorted(b.cell_ids.tolist()) == list(range(len(cells)))
+    kd = b.kd_nodes
+    leaves = kd[(kd["axis_bits"] >> 30) == 3]
+    assert len(leaves) == b.num_bricks and len(kd) == 2 * b.num_bricks - 1
+    assert sorted(leaves["split_or_first_prim"].tolist()) == list(range(b.num_bricks))
+
+
+def test_builder_errors(R, built_lib):
+    empty = R.ExaBricks.build(np.zeros((0, 4), np.int32))
+    assert empty.num_bricks == 0
+    with pytest.raises(built_lib.ExaError):
+        R.ExaBricks.build(np.array([[0, 0, 0, 99]], np.int32))
+
+
+def test_bricks_file_round_trip(R, tmp_path):
+    g = load_golden("nb64")
+    p = str(tmp_path / "a.bricks")
+    open(p, "wb").write(g["bricks"].tobytes())
+    b = R.ExaBricks.load(p)
+    assert b.to_bytes() == g["bricks"].tobytes()
+    q = str(tmp_path / "b.bricks")
+    b.save(q)
+    assert open(q, "rb").read() == g["bricks"].tobytes()
+    lo, hi = b.get_bounds()
+    assert lo.tolist() == [0, 0, 0] and hi.tolist() == [64, 64, 64]
+    h = b.headers
+    n = h["size"].astype(np.int64).prod(axis=1)
+    assert (h["begin"] == np.concatenate([[0], np.cumsum(n)[:-1]])).all()
+    with pytest.raises(Exception):
+        R.ExaBricks.load(str(tmp_path / "missing.bricks"))
+
+
+def test_scalar_field_loader_quirk(R, tmp_path):
+    v = np.linspace(0.25, 2.0, 200).astype(np.float32)
+    p = str(tmp_path / "f.scalars")
+    v.tofile(p)
+    vals, rng = R.load_scalar_field(p, compat=True)          # ScalarField.cpp:27-34: sized by BYTES
+    assert len(vals) == 800 and (vals[:200] == v).all() and (vals[200:] == 0).all()
+    assert rng[0] == 0.0 and rng[1] == 2.0
+    vals, rng = R.load_scalar_field(p, compat=False)
+    assert len(vals) == 200 and rng[0] == np.float32(0.25)
+
+
+def test_colormapper(R):
+    cm = R.ColorMapper(colors=[[0, 0, 0], [1, 0, 0], [1, 1, 1]])
+    assert np.allclose(cm(0.25), [0.5, 0, 0]) and np.allclose(cm(0.75), [1, .5, .5])
+    assert np.allclose(cm(1.0), [1, 1, 1]) and np.allclose(cm(2.0), [1, 1, 1])
+    assert cm.table().shape == (128, 3)
+    cm2 = R.ColorMapper(control_points=[[1.0, 1, 1, 1], [0.0, 0, 0, 0], [0.1, 1, 0, 0]])   # unsorted -> sorted
+    assert np.allclose(cm2(0.05), [0.5, 0, 0])
+
+
+def test_config_parser(R, tmp_path, built_lib):
+    g = load_golden("ex4")
+    open(tmp_path / "ex4.bricks", "wb").write(g["bricks"].tobytes())
+    g["fields"][0].astype(np.float32).tofile(tmp_path / "ex4.scalars")
+    cfg_text = """# comment line
+remap_from 0 0 0 8 8 4
+remap_to   -1 -1 -1  1 1 0   # trailing comment
+scalar density ex4.scalars
+value_range 0.1 0.9
+vector vel ex4.scalars ex4.scalars ex4.scalars
+bricks ex4.bricks
+"""
+    p = str(tmp_path / "ex4.exa")
+    open(p, "w").write(cfg_text)
+    cfg = R.Config(p)
+    assert [f["name"] for f in cfg.fields] == ["density", "vel"]
+    assert np.allclose(cfg.fields[0]["valueRange"], [0.1, 0.9])
+    assert np.allclose(cfg.fields[1]["values"][:200], np.sqrt(3.0) * g["fields"][0], rtol=1e-6)
+    # voxel = T(from.lo) S(from.span) (T(to.lo) S(to.span))^-1 world: world (-1,-1,-1) -> voxel (0,0,0); (1,1,0) -> (8,8,4)
+    m = cfg.voxelSpaceTransform
+    xfm = lambda w: m[0:3] * w[0] + m[3:6] * w[1] + m[6:9] * w[2] + m[9:12]
+    assert np.allclose(xfm([-1, -1, -1]), [0, 0, 0], atol=1e-6) and np.allclose(xfm([1, 1, 0]), [8, 8, 4], atol=1e-5)
+    lo, hi = cfg.get_bounds()
+    assert np.allclose(lo, [-1, -1, -1], atol=1e-6) and np.allclose(hi, [1, 1, 0], atol=1e-6)
+    open(p, "w").write("bogus_token 1 2 3\n")
+    with pytest.raises(built_lib.ExaError, match="unknown token"):
+        R.Config(p)
+    with pytest.raises(built_lib.ExaError):
+        R.Config(str(tmp_path / "nope.exa"))
+
+
+def test_no_cpu_fallback(R, built_lib):
+    """without a usable CUDA device the renderer must refuse, not compute on the host"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    assert built_lib.lib.exa_cuda_available() == 0
+    g = load_golden("ex4")
+    b = R.ExaBricks.from_bytes(g["bricks"].tobytes())
+    with pytest.raises(built_lib.ExaError) as e:
+        R.Renderer(b, [g["fields"][0]])
+    assert e.value.code == built_lib.EXA_ERR_CUDA
+
+
+def test_camera_matches_reference_math(R):
+    pos, d00, du, dv = R.simple_camera([0, 0, 5], [0, 0, 0], [0, 1, 0], 90.0, 200, 100)
+    # fovy 90, focal 5 -> screen height 10, width 20; lower-left = (-10,-5,-5)
+    assert np.allclose(d00, [-10, -5, -5], atol=1e-5)
+    assert np.allclose(du * 200, [20, 0, 0], atol=1e-5) and np.allclose(dv * 100, [0, 10, 0], atol=1e-5)
