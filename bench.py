@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""bench.py — the hot path's headline benchmark (BASELINE.json: reconstructed samples/s and
+DVR frames/s; % of HBM roofline).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload c2|c1|small]
+
+A "step" is one DVR frame of the workload through the fused frame kernel.  At N=1 the
+workload is BASELINE.json configs[1] (synthetic 3-level AMR, ~95 M cells, one scalar, DVR
+1024^2).  N>1 renders the SAME frame sort-last (kd spatial partition, NCCL binary swap), so
+scaling is "strong".  Prints ONE JSON line (see the task contract for the keys).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (domain, nested boxes, image)           SURVEY.md §8(d)
+    "c2": (1024, [(320, 704), (192, 832)], (1024, 1024)),
+    "c1": (256, [(72, 184), (32, 224)], (1024, 1024)),
+    "small": (64, [(18, 46), (8, 56)], (256, 256)),
+}
+OPACITY_SCALE = 1.0      # viewer default xfOpacityScale (viewer.cpp:113)
+DT = 0.5                 # viewer default (viewer.cpp:115)
+
+
+def log(*a):
+    print("[bench]", *a, file=sys.stderr, flush=True)
+
+
+def make_workload(name):
+    from owlexabrick_b200 import synth
+    domain, boxes, image = WORKLOADS[name]
+    t = time.time()
+    cells = synth.nested_boxes(domain, boxes)
+    field = synth.analytic_field(cells, domain, 0)
+    log("workload %s: %d cells generated in %.1fs" % (name, len(cells), time.time() - t))
+    return cells, field, domain, image
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region"""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.rows, self.stop_flag, self.proc = index, [], False, None
+
+    def run(self):
+        q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            for line in self.proc.stdout:
+                self.rows.append([x.strip() for x in line.split(",")])
+                if self.stop_flag:
+                    break
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+
+
+def frame_desc(R, domain, image, field_range):
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    W, H = image
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [domain] * 3, W, H))
+    fd.opacity_scale = OPACITY_SCALE
+    fd.dt = DT
+    fd.xf_domain = [(float(field_range[0]), float(field_range[1]))]
+    return fd
+
+
+def algorithmic_bytes(st, W, H):
+    """B_frame of BASELINE.md §2 / SURVEY.md §8(d)"""
+    return 36 * st["brickVisits"] + 4 * st["cornerLoads"] + 44 * st["segments"] + 20 * W * H
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU implementation of the path (oracle port; the reference's
+# device code needs OptiX and cannot be compiled here)
+# ---------------------------------------------------------------------------------------------
+def cpu_scene(orc, cells, field):
+    raw = orc.build_bricks(cells)
+    bricks, ids = orc.parse_bricks(raw)
+    sc = orc.flatten_scalars(ids, [field])
+    regions, leaf = orc.build_abr(bricks, sc)
+    return orc.Scene(bricks, sc, regions, leaf)
+
+
+def cpu_frame_sample(orc, scene, fd, window):
+    t = time.time()
+    _, _, st = scene.render(fd.to_orc(orc), window=window)
+    return st, time.time() - t
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import orc
+    from owlexabrick_b200 import renderer as R      # host-side camera helper only
+    orc.build()
+    name = args.workload
+    cells, field, domain, image = make_workload(name)
+    log("reference arm: building the CPU scene (oracle builder, serial)")
+    t = time.time()
+    scene = cpu_scene(orc, cells, field)
+    log("cpu scene built in %.1fs" % (time.time() - t))
+    W, H = image
+    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
+    win = 64 if name != "small" else 32
+    window = (W // 2 - win // 2, H // 2 - win // 2, W // 2 + win // 2, H // 2 + win // 2)
+    for _ in range(args.warmup):
+        cpu_frame_sample(orc, scene, fd, (window[0], window[1], window[0] + 8, window[1] + 8))
+    tot_s, tot_t = 0, 0.0
+    for _ in range(args.steps):
+        st, dt = cpu_frame_sample(orc, scene, fd, window)
+        tot_s += st["samples"]
+        tot_t += dt
+    value = tot_s / tot_t
+    sample = "%dx%d pixel window at the image centre of the %s frame per step, %d steps" % (win, win, name, args.steps)
+    line = {"impl": "reference", "metric": "dvr_reconstructed_samples_per_s", "value": value, "unit": "samples/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(name), "image": list(image), "dt": DT},
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": orc.num_threads(), "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(name):
+    domain, boxes, image = WORKLOADS[name]
+    return "%s: synthetic 3-level nested-box AMR, domain %d^3, single scalar, DVR %dx%d, default camera/XF" % (name, domain, image[0], image[1])
+
+
+# ---------------------------------------------------------------------------------------------
+# product arm
+# ---------------------------------------------------------------------------------------------
+def binary_swap(r, dist, torch, partial, npix, rank, world, rgba8_full):
+    """sort-last compositing: log2(N) rounds of half-image exchange (NCCL P2P) + fused "over",
+    then finish (accumulate, sRGB, pack) on the owned strip and all_gather of RGBA8 strips"""
+    lo, hi = 0, npix
+    rounds = world.bit_length() - 1
+    launches = 0
+    for rnd in range(rounds):
+        partner = rank ^ (1 << rnd)
+        mid = (lo + hi) // 2
+        keep_low = ((rank >> rnd) & 1) == 0
+        keep = (lo, mid) if keep_low else (mid, hi)
+        send = (mid, hi) if keep_low else (lo, mid)
+        recv_buf = torch.empty((keep[1] - keep[0], 4), dtype=torch.float32, device=partial.device)
+        ops = [dist.P2POp(dist.isend, partial[send[0]:send[1]], partner), dist.P2POp(dist.irecv, recv_buf, partner)]
+        for req in dist.batch_isend_irecv(ops):
+            req.wait()
+        r.composite_over(partial[keep[0]:keep[1]].data_ptr(), recv_buf.data_ptr(), keep[1] - keep[0], r.swap_order(rnd))
+        launches += 1
+        lo, hi = keep
+    strip = torch.empty(hi - lo, dtype=torch.int32, device=partial.device)
+    r.finish_pixels(partial[lo:hi].data_ptr(), lo, hi - lo, strip.data_ptr())
+    launches += 1
+    strips = [torch.empty_like(strip) for _ in range(world)]
+    dist.all_gather(strips, strip)
+    return strips, (lo, hi), launches
+
+
+def run_product(args):
+    import torch
+    import torch.distributed as dist
+    from owlexabrick_b200 import build
+    build.build_lib()
+    from owlexabrick_b200 import capi, renderer as R, synth
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        log("WORLD_SIZE %d != --gpus %d; using WORLD_SIZE" % (world, args.gpus))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    assert capi.lib.exa_cuda_available() == 1, capi.last_error()
+
+    name = args.workload
+    domain, boxes, image = WORKLOADS[name]
+    W, H = image
+    # ---- setup (untimed): rank 0 generates + builds, the others load from /dev/shm ----
+    shm = "/dev/shm/exa_bench_%s" % os.environ.get("MASTER_PORT", "single")
+    t0 = time.time()
+    if rank == 0:
+        cells, field, _, _ = make_workload(name)
+        t = time.time()
+        bricks = R.ExaBricks.build(cells)
+        log("exa_bricks_build: %d cells -> %d bricks in %.1fs" % (len(cells), bricks.num_bricks, time.time() - t))
+        ncells = len(cells)
+        del cells
+        if world > 1:
+            os.makedirs(shm, exist_ok=True)
+            bricks.save(os.path.join(shm, "w.bricks"))
+            field.tofile(os.path.join(shm, "w.scalars"))
+    if world > 1:
+        dist.barrier()
+        if rank != 0:
+            bricks = R.ExaBricks.load(os.path.join(shm, "w.bricks"))
+            field = np.fromfile(os.path.join(shm, "w.scalars"), np.float32)
+            ncells = bricks.total_num_cells
+    t = time.time()
+    r = R.Renderer(bricks, [field], device=local)
+    torch.cuda.synchronize()
+    regions, leaf = r.get_abr()
+    log("rank %d: renderer created in %.1fs (%d regions, L=%d, kd %s)" % (rank, time.time() - t, len(regions), len(leaf), r.kd_info()))
+    stream = torch.cuda.current_stream()
+    r.set_stream(stream.cuda_stream)
+    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
+    fd.apply(r)
+    npix = W * H
+    if world > 1:
+        r.set_partition(capi.PARTITION_SORT_LAST, rank, world)
+        partial = torch.zeros((npix, 4), dtype=torch.float32, device="cuda")
+        rgba8_full = None
+
+    def step():
+        if world == 1:
+            r.render(sync=False)
+            return 1
+        r.render_partial(partial.data_ptr())
+        _, _, k = binary_swap(r, dist, torch, partial, npix, rank, world, None)
+        return 1 + k
+
+    # instrumented, untimed: counters of the algorithmic-bytes model
+    st = r.render_stats()
+    stats_t = torch.tensor([st["samples"], st["brickVisits"], st["cornerLoads"], st["segments"]], dtype=torch.int64, device="cuda")
+    if world > 1:
+        dist.all_reduce(stats_t)
+    tot = dict(zip(["samples", "brickVisits", "cornerLoads", "segments"], [int(x) for x in stats_t.tolist()]))
+    if world > 1:
+        r.set_partition(capi.PARTITION_SORT_LAST, rank, world)   # masks were refreshed by render_stats; keep state explicit
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = r.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    launches = 0
+    for _ in range(args.steps):
+        launches += step()
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = ev0.elapsed_time(ev1)
+    tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms = float(tms.item())
+    lib_launches = r.launch_count() - l0
+    clocks = sampler.finish() if rank == 0 else None
+    ms_step = ms / args.steps
+    value = tot["samples"] / (ms_step * 1e-3)
+
+    # ---- end to end through the C ABI with host buffers (N=1 path; at N>1 rank 0's read-back) ----
+    host_img = torch.empty((H, W), dtype=torch.int32).pin_memory()
+    alpha, rgb = fd.xf[0]
+    def e2e_step():
+        r.updateCamera(*fd.cam)
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)       # host -> device: 128 float4
+        if world == 1:
+            r.render(sync=False)
+            capi.check(capi.lib.exa_renderer_read_rgba8(r.h, host_img.data_ptr()))   # device -> host: W*H*4
+        else:
+            r.render_partial(partial.data_ptr())
+            strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
+            if rank == 0:
+                torch.cat(strips).cpu()
+    for _ in range(2):
+        e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_s = float(te.item())
+    e2e_value = tot["samples"] / (e2e_s / args.steps)
+
+    # ---- reconstruction sampling (K4): 1 M random points, device resident, + host-buffer call ----
+    recon = None
+    if rank == 0:
+        npts = 1 << 20
+        pts = synth.random_points(npts, [0] * 3, [domain] * 3, seed=1)
+        d_pts = torch.from_numpy(pts).cuda()
+        d_val = torch.empty(npts, dtype=torch.float32, device="cuda")
+        d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
+        times = []
+        for i in range(args.warmup + max(args.steps, 5)):
+            flush.fill_(i & 0xff)                                            # L2 flush between iterations
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            r.sample_points_device(d_pts.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr())
+            b.record(stream)
+            torch.cuda.synchronize()
+            if i >= args.warmup:
+                times.append(a.elapsed_time(b))
+        pms = float(np.mean(times))
+        pbytes = 16 * npts + 44 * pst["segments"] + 36 * pst["brickVisits"] + 4 * pst["cornerLoads"]
+        t = time.perf_counter()
+        for _ in range(3):
+            r.sample_points(pts, 0)
+        h_s = (time.perf_counter() - t) / 3
+        peak, _ = peaks()
+        recon = {"points": npts, "ms": pms, "samples_per_s": npts / (pms * 1e-3), "algorithmic_bytes": pbytes,
+                 "achieved_gbs": pbytes / (pms * 1e-3) / 1e9, "frac": pbytes / (pms * 1e-3) / 1e9 / peak,
+                 "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB fill between iterations"}
+
+    # ---- CPU baseline beside it (rank 0, N=1 only): the oracle on a bounded sample ----
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import orc
+        orc.build()
+        t = time.time()
+        hdr = bricks.headers.view(orc.BRICK_DT)
+        sc = orc.flatten_scalars(bricks.cell_ids, [field])
+        oscene = orc.Scene(hdr, sc, regions.view(orc.REGION_DT), leaf)      # same bricks/ABRs (bit-exact with the oracle's, tests/)
+        log("cpu baseline scene in %.1fs" % (time.time() - t))
+        win = 96 if name != "small" else 32
+        window = (W // 2 - win // 2, H // 2 - win // 2, W // 2 + win // 2, H // 2 + win // 2)
+        cst, cdt = cpu_frame_sample(orc, oscene, fd, window)
+        cpu = {"value": cst["samples"] / cdt, "unit": "samples/s", "cores": orc.num_threads(), "kind": "port",
+               "sample": "%dx%d pixel window at the centre of the same frame, %.1fs" % (win, win, cdt)}
+
+    if rank == 0:
+        peak, peak_src = peaks()
+        bframe = algorithmic_bytes(tot, W, H)
+        achieved = bframe / (ms_step * 1e-3) / 1e9 / world                  # per GPU
+        line = {"metric": "dvr_reconstructed_samples_per_s", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_step, "frames_per_s": 1e3 / ms_step, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": workload_name(name), "cells": int(ncells), "bricks": bricks.num_bricks, "regions": int(len(regions)),
+                           "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
+                           "parallelism": "1 GPU" if world == 1 else "sort-last kd partition x%d, NCCL binary swap" % world,
+                           "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
+                           "samples_per_frame": tot["samples"]},
+                "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
+                        "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4},
+                "gpu_launches": int(lib_launches), "clocks": clocks,
+                "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
+                             "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; most are served by L1/L2"},
+                "recon": recon, "cpu_baseline": cpu}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="product", choices=["product", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_product(args)
+
+
+if __name__ == "__main__":
+    main()

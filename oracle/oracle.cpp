@@ -636,6 +636,7 @@ static inline float firstLatticeT(float t0, float dt, float offs)
 }
 
 // integrateBrick<GRADIENT_SHADING>, exabrick.cu:1116-1185
+static thread_local bool g_dbg = false;
 static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res, float offs, const Ray &ray,
                            int leafID, float t0, float t1, int numChannels, bool gradShading, OrcStats *st)
 {
@@ -643,6 +644,7 @@ static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res,
   const float dt = f.dt * r.finestLevelCellWidth; const int fcw = (int)r.finestLevelCellWidth;
   float t_i = firstLatticeT(t0, dt, offs); float t_last = t0;
   if (st) st->segments++;
+  if (g_dbg) printf("O seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", leafID, r.leafListSize, t0, t1, dt, t_i);
   for (;; t_i += dt) {
     const float t_next = fminf(t_i, t1);
     const float t_sample = 0.5f * (fminf(t1, t_next) + t_last);
@@ -650,6 +652,7 @@ static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res,
     const V3 pos = ray.o + t_sample * ray.d;
     float cv = 0.f; V3 g = v3(0, 0, 0);
     for (int c = 0; c < numChannels; c++) {
+      if (g_dbg) { float v2; V3 g2; if (samplePointD(s, v2, g2, leafID, pos, c, nullptr)) printf("O   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g)\n", t_sample, actual_dt, v2, g2.x, g2.y, g2.z); }
       if (gradShading) { if (samplePointD(s, cv, g, leafID, pos, c, st)) integrateVolume(f, ray, res, actual_dt, cv, g, fcw, c); }
       else             { if (samplePoint(s, cv, leafID, pos, c, st))     integrateVolume(f, ray, res, actual_dt, cv, g, fcw, c); }
     }
@@ -801,6 +804,7 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
     for (int py = y0; py < y1; py++)
       for (int px = x0; px < x1; px++) {
         const int pixelIdx = px + W * py;
+        { const char *e = getenv("ORC_DEBUG_PIXEL"); int dx = -1, dy = -1; g_dbg = e && sscanf(e, "%d,%d", &dx, &dy) == 2 && dx == px && dy == py; }
         LCG16 rnd((uint32_t)(f.frameID * W * H) + (uint32_t)px, (uint32_t)py);
         const float jx = rnd(), jy = rnd();                // oracle fixes x first
         const float sx = (float)px + jx, sy = (float)py + jy;

@@ -15,6 +15,8 @@ OBJ = os.path.join(HERE, "build")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp", "-DEXA_BUILD"]
+if os.environ.get("EXA_DEBUG"):
+    COMMON = COMMON + ["-DEXA_DEBUG"]
 SOURCES = ["host.cpp", "builder.cpp", "abr.cu", "render.cu", "capi.cu"]
 HEADERS = ["exa_internal.h", "render.cuh", "capi_render.inl", os.path.join("..", "..", "include", "exabrick_b200.h")]
 

@@ -3,6 +3,8 @@
 // device fails with EXA_ERR_CUDA when CUDA is unusable.
 #include "render.cuh"
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <random>
 #include <string>
@@ -83,6 +85,10 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.traces = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
   P.stats = nullptr;
   P.kdStack = r->abr.depth + 2;
+  P.dbg = 0;
+#ifdef EXA_DEBUG
+  if (const char *e = getenv("EXA_DEBUG_PIXEL")) { int x = 0, y = 0; if (sscanf(e, "%d,%d", &x, &y) == 2) P.dbg = 1 + x + r->width * y; }
+#endif
 }
 
 static void syncLaunchParams(exa_renderer *r)

@@ -40,6 +40,12 @@ __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x *
 __device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ float len3(float3 a) { return sqrtf(dot3(a, a)); }
 __device__ __forceinline__ float3 normalize3(float3 a) { return a * (1.f / sqrtf(dot3(a, a))); }   // owl: v * rsqrt(dot)
+// ray.origin + t * ray.direction with the product and the sum rounded separately (no FMA
+// contraction): single-sample segments put their sample at the midpoint of two region faces,
+// which is exactly a dual-cell boundary of the coarser bricks, where the gradient jumps;
+// evaluating the position as written in the reference keeps both sides on the same cell.
+__device__ __forceinline__ float3 rayAt(float3 o, float3 d, float t)
+{ return f3(__fadd_rn(o.x, __fmul_rn(t, d.x)), __fadd_rn(o.y, __fmul_rn(t, d.y)), __fadd_rn(o.z, __fmul_rn(t, d.z))); }
 __device__ __forceinline__ float comp(float3 a, int d) { return d == 0 ? a.x : d == 1 ? a.y : a.z; }
 
 struct Acc { float sw, swv; float3 sd, sdc; };
@@ -282,6 +288,9 @@ __device__ __forceinline__ bool integrateSegment(const RenderParams &P, const fl
   const float dt = P.dt * fcw;
   const float tFirst = firstLatticeT(t0, dt, offs);
   if (STATS) ws.segments++;
+#ifdef EXA_DEBUG
+  if (P.dbg && lane == 0) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)blob[2].x, K, t0, t1, dt, tFirst);
+#endif
   for (int base = 0;; base += 32) {
     const int j = base + lane;
     const float tj = fmaf((float)j, dt, tFirst);
@@ -293,7 +302,7 @@ __device__ __forceinline__ bool integrateSegment(const RenderParams &P, const fl
     const float actualDt = tNext - tLast;
     float4 L = make_float4(0.f, 0.f, 0.f, 0.f);
     if (act) {
-      const float3 pos = o + tSample * d;
+      const float3 pos = rayAt(o, d, tSample);
       for (int c = 0; c < P.numChannels; c++) {
         float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0;
         const bool ok = sampleRegion<GRAD, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
@@ -306,6 +315,9 @@ __device__ __forceinline__ bool integrateSegment(const RenderParams &P, const fl
             s.x *= scale; s.y *= scale; s.z *= scale;
           }
           s.w = 1.f - powf(1.f - s.w, actualDt);
+#ifdef EXA_DEBUG
+          if (P.dbg) printf("G   smp j=%d t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", j, tSample, actualDt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
+#endif
           const float k = (1.f - L.w) * s.w;
           L.x += k * s.x; L.y += k * s.y; L.z += k * s.z; L.w += k;
         }
@@ -338,17 +350,84 @@ __device__ __forceinline__ bool integrateSegment(const RenderParams &P, const fl
 // state of one IsoSurfaceIntegrationFunction (exabrick.cu:1018-1114), kept per channel
 struct IsoState { float lastT, lastV; };
 
-// isoIntegrateBrick (exabrick.cu:1187-1256) for one region segment.  On a crossing, colour and
-// gradient come from the FIRST crossing in the segment; t_hit / gradient are overwritten by
-// later ones exactly as in the reference (the functor keeps running after a hit).
+// Shade one iso crossing at ray parameter th (IsoSurfaceIntegrationFunction::operator(),
+// exabrick.cu:1053-1101); executed by all lanes in lock-step with identical arguments.
+template <bool STATS>
+__device__ __forceinline__ void shadeIsoHit(const RenderParams &P, const float4 *xfTables, uint4 *blob, uint32_t blobOfs, int K,
+                                            float3 o, float3 d, float th, int ii, int lane,
+                                            float4 &pc, float &tHit, float3 &hitGrad, WarpStats &ws)
+{
+  const float3 isopt = rayAt(o, d, th);
+  float cv = 0.f; float3 grad = f3(0, 0, 0); unsigned nc2 = 0;
+  float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
+  const int ich = P.isoChannel[ii];
+  if (P.gradISO) {
+    if (sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2)) {
+      smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
+      grad = normalize3(grad);
+      if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
+    }
+  } else {
+    if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2))
+      smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
+  }
+  if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc2; }
+  if (P.colormapChannel != 0) {
+    cv = 0.f; float3 g2; unsigned nc3 = 0;
+    if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, P.colormapChannel, lane, isopt, cv, g2, nc3))
+      smp = lookupXF(xfTables, P.xfDomain[0][0], P.xfDomain[0][1], P.xfOpacityScale, cv);
+    if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc3; }
+  }
+  smp.w = 1.f;
+  if (!isfinite(grad.x) || !isfinite(grad.y) || !isfinite(grad.z)) grad = f3(0, 0, 0);
+  if (len3(grad) > 0.f) {
+    const float3 l = f3(-d.x, -d.y, -d.z);
+    const float scale = .3f + .7f * fabsf(dot3(l, grad)) / sqrtf(dot3(grad, grad));
+    smp.x *= scale; smp.y *= scale; smp.z *= scale;
+  }
+  const float k = (1.f - pc.w) * smp.w;
+  pc.x += k * smp.x; pc.y += k * smp.y; pc.z += k * smp.z; pc.w += k;
+  tHit = th; hitGrad = grad;
+}
+
+// crossing test of one functor call (exabrick.cu:1035-1052): the iso indices are visited in
+// order, every match shades and overwrites t_hit; returns first and last matching index
+__device__ __forceinline__ bool isoCross(const RenderParams &P, int c, float lastV, float lastT, float v, float tSample,
+                                         float &tFirst, int &iFirst, float &tLast, int &iLast)
+{
+  bool crossed = false;
+  if (lastV >= -1e35f) {
+#pragma unroll
+    for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
+      const float isoV = P.isoValue[i];
+      if (P.isoEnabled[i] && P.isoChannel[i] == c && ((lastV <= isoV && v >= isoV) || (lastV >= isoV && v <= isoV))) {
+        const float d1 = fabsf(lastV - isoV), d2 = fabsf(v - isoV);
+        const float w1 = 1.f - d1 / (d1 + d2), w2 = 1.f - d2 / (d1 + d2);
+        const float tavg = lastT * w1 + tSample * w2;
+        if (!crossed) { tFirst = tavg; iFirst = i; }
+        tLast = tavg; iLast = i; crossed = true;
+      }
+    }
+  }
+  return crossed;
+}
+
+// isoIntegrateBrick (exabrick.cu:1187-1256) for one region segment; lanes take consecutive
+// samples.  Colour comes from the first crossing; t_hit / gradient are overwritten by later
+// crossings of the segment exactly as in the reference (its functor keeps running after a
+// hit).  One primary channel: crossings are found with ballots.  Several channels: the values
+// of a 32-sample batch are parked in shared memory and the reference's (sample, channel)
+// loop, including its "break once opaque" rule (:1249), is replayed in lock-step.
 template <bool STATS>
 __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *xfTables, uint4 *blob, uint32_t blobOfs, int K,
                                            float3 o, float3 d, float t0, float t1, int lane, IsoState *iso /*smem, per channel*/,
+                                           float *scr /*smem scratch, multi-channel only*/,
                                            float4 &pc, float &tHit, float3 &hitGrad, WarpStats &ws)
 {
   const float fcw = __uint_as_float(blob[1].z);
   const float dt = P.dt * fcw;
   const float tFirst = firstLatticeT(t0, dt, 0.f);
+  const int C = P.numChannels;
   if (STATS) ws.segments++;
   for (int base = 0;; base += 32) {
     const int j = base + lane;
@@ -358,90 +437,74 @@ __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *
     const float tNext = fminf(tj, t1);
     const float tLast = (j == 0) ? t0 : tjm1;
     const float tSample = 0.5f * (tNext + tLast);
-    const float3 pos = o + tSample * d;
-    for (int c = 0; c < P.numChannels; c++) {
-      // once the pixel is opaque the reference's channel loop breaks after the first valid
-      // channel (exabrick.cu:1249); with a single primary channel this never matters.
+    const float3 pos = rayAt(o, d, tSample);
+    if (C == 1) {
       float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0; bool ok = false;
       if (act) {
-        if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
-        else ok = sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
+        if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, 0, lane, pos, v, g, nc);
+        else ok = sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, 0, lane, pos, v, g, nc);
         if (STATS) { ws.samples++; ws.visits += K; ws.corners += nc; }
       }
-      // previous VALID sample of this channel: nearest lower lane that is valid, else carried state
+      // previous VALID sample: nearest lower valid lane, else the state carried in
       const unsigned okMask = __ballot_sync(FULL, ok);
       const unsigned below = okMask & ((1u << lane) - 1u);
       const int prevLane = below ? 31 - __clz(below) : -1;
       const float pv = __shfl_sync(FULL, v, prevLane < 0 ? 0 : prevLane);
       const float pt = __shfl_sync(FULL, tSample, prevLane < 0 ? 0 : prevLane);
-      const float lastV = prevLane < 0 ? iso[c].lastV : pv;
-      const float lastT = prevLane < 0 ? iso[c].lastT : pt;
-      bool crossed = false; float tavg = 0.f; int which = 0;
-      if (ok && lastV >= -1e35f) {
-        for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
-          const float isoV = P.isoValue[i];
-          if (P.isoEnabled[i] && P.isoChannel[i] == c &&
-              ((lastV <= isoV && v >= isoV) || (lastV >= isoV && v <= isoV))) {
-            const float d1 = fabsf(lastV - isoV), d2 = fabsf(v - isoV);
-            const float w1 = 1.f - d1 / (d1 + d2), w2 = 1.f - d2 / (d1 + d2);
-            tavg = lastT * w1 + tSample * w2; crossed = true; which = i;   // later iso index overwrites, as in the reference loop
-          }
-        }
-      }
+      const float lastV = prevLane < 0 ? iso[0].lastV : pv;
+      const float lastT = prevLane < 0 ? iso[0].lastT : pt;
+      float ta = 0.f, tb = 0.f; int ia = 0, ib = 0;
+      const bool crossed = ok && isoCross(P, 0, lastV, lastT, v, tSample, ta, ia, tb, ib);
       const unsigned crossMask = __ballot_sync(FULL, crossed);
       if (crossMask) {
-        // shade the first crossing if the pixel is still open (exabrick.cu:1053-1101)
         const int firstLane = __ffs(crossMask) - 1, lastLane = 31 - __clz(crossMask);
-        const float tFirstHit = __shfl_sync(FULL, tavg, firstLane);
-        const float tLastHit = __shfl_sync(FULL, tavg, lastLane);
-        const int isoIdx = __shfl_sync(FULL, which, firstLane);
-        const int isoIdxLast = __shfl_sync(FULL, which, lastLane);
-        // NOTE: when several iso values cross in one lane only the last index is shaded; the
-        // reference would shade each in turn under (1-alpha)=0 for all but the first.
-        for (int pass = 0; pass < 2; pass++) {
-          const float th = pass == 0 ? tFirstHit : tLastHit;
-          const int ii = pass == 0 ? isoIdx : isoIdxLast;
-          if (pass == 1 && firstLane == lastLane) break;
-          const float3 isopt = o + th * d;
-          float cv = 0.f; float3 grad = f3(0, 0, 0); unsigned nc2 = 0;
-          float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
-          const int ich = P.isoChannel[ii];
-          if (P.gradISO) {
-            if (sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2)) {
-              smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
-              grad = normalize3(grad);
-              if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
-            }
-          } else {
-            if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2))
-              smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
-          }
-          if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc2; }
-          if (P.colormapChannel != 0) {
-            cv = 0.f; float3 g2; unsigned nc3 = 0;
-            if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, P.colormapChannel, lane, isopt, cv, g2, nc3))
-              smp = lookupXF(xfTables, P.xfDomain[0][0], P.xfDomain[0][1], P.xfOpacityScale, cv);
-            if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc3; }
-          }
-          smp.w = 1.f;
-          if (!isfinite(grad.x) || !isfinite(grad.y) || !isfinite(grad.z)) grad = f3(0, 0, 0);
-          if (len3(grad) > 0.f) {
-            const float3 l = f3(-d.x, -d.y, -d.z);
-            const float scale = .3f + .7f * fabsf(dot3(l, grad)) / sqrtf(dot3(grad, grad));
-            smp.x *= scale; smp.y *= scale; smp.z *= scale;
-          }
-          const float k = (1.f - pc.w) * smp.w;
-          pc.x += k * smp.x; pc.y += k * smp.y; pc.z += k * smp.z; pc.w += k;
-          tHit = th; hitGrad = grad;
-        }
+        const float tA = __shfl_sync(FULL, ta, firstLane); const int iA = __shfl_sync(FULL, ia, firstLane);
+        const float tB = __shfl_sync(FULL, tb, lastLane); const int iB = __shfl_sync(FULL, ib, lastLane);
+        shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tA, iA, lane, pc, tHit, hitGrad, ws);
+        if (firstLane != lastLane || iA != iB)
+          shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tB, iB, lane, pc, tHit, hitGrad, ws);
       }
-      // carry the channel state to the next batch / region
       if (okMask) {
         const int lastOk = 31 - __clz(okMask);
         const float nv = __shfl_sync(FULL, v, lastOk), nt = __shfl_sync(FULL, tSample, lastOk);
         __syncwarp();
-        if (lane == 0) { iso[c].lastV = nv; iso[c].lastT = nt; }
+        if (lane == 0) { iso[0].lastV = nv; iso[0].lastT = nt; }
         __syncwarp();
+      }
+    } else {
+      // scr: tS[32] | v[C][32] | okMask[C]
+      unsigned *okMasks = reinterpret_cast<unsigned *>(scr + 32 + 32 * C);
+      __syncwarp();
+      scr[lane] = tSample;
+      for (int c = 0; c < C; c++) {
+        float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0; bool ok = false;
+        if (act) {
+          if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
+          else ok = sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
+          if (STATS) { ws.samples++; ws.visits += K; ws.corners += nc; }
+        }
+        scr[32 + 32 * c + lane] = v;
+        const unsigned m = __ballot_sync(FULL, ok);
+        if (lane == 0) okMasks[c] = m;
+      }
+      __syncwarp();
+      const unsigned actMask = __ballot_sync(FULL, act);
+      const int nAct = 32 - __clz(actMask);
+      for (int jj = 0; jj < nAct; jj++) {
+        const float ts = scr[jj];
+        for (int c = 0; c < C; c++) {
+          if (!((okMasks[c] >> jj) & 1u)) continue;
+          const float v = scr[32 + 32 * c + jj];
+          float ta = 0.f, tb = 0.f; int ia = 0, ib = 0;
+          if (isoCross(P, c, iso[c].lastV, iso[c].lastT, v, ts, ta, ia, tb, ib)) {
+            shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, ta, ia, lane, pc, tHit, hitGrad, ws);
+            if (ia != ib) shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tb, ib, lane, pc, tHit, hitGrad, ws);
+          }
+          __syncwarp();
+          if (lane == 0) { iso[c].lastV = v; iso[c].lastT = ts; }
+          __syncwarp();
+          if (pc.w >= P.ertThreshold) break;
+        }
       }
     }
     const float t31 = fmaf((float)(base + 31), dt, tFirst);
@@ -464,9 +527,10 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
   // layout: [xf tables: numChannels*128 float4][per warp: stack kdStack][per warp: blob BLOB_UNITS][per warp: iso state 10*8B=5 units]
   float4 *xfTables = reinterpret_cast<float4 *>(smem);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint4 *warpBase = smem + P.numChannels * 128 + warp * (P.kdStack + BLOB_UNITS + 5);
+  uint4 *warpBase = smem + P.numChannels * 128 + warp * P.warpUnits;
   uint4 *stack = warpBase, *blob = warpBase + P.kdStack;
   IsoState *iso = reinterpret_cast<IsoState *>(warpBase + P.kdStack + BLOB_UNITS);
+  float *isoScr = reinterpret_cast<float *>(warpBase + P.kdStack + BLOB_UNITS + 5);
   for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
   __syncthreads();
 
@@ -479,6 +543,9 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
   if (py < P.height) {
     for (int px = tx; px < tx + TILE && px < P.width; px++) {
       const int pixelIdx = px + P.width * py;
+#ifdef EXA_DEBUG
+      if (P.dbg && pixelIdx != P.dbg - 1) continue;
+#endif
       LCG16 rnd((uint32_t)(P.frameID * P.width * P.height) + (uint32_t)px, (uint32_t)py);
       const float jx = rnd.next(), jy = rnd.next();
       const float sx = (float)px + jx, sy = (float)py + jy;
@@ -503,7 +570,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
           uint32_t bo; int K; float t0, t1;
           if (!travNext(T, P.scene, P.isoActive, already, rtmax, blob, lane, bo, K, t0, t1)) break;
           float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
-          isoSegment<STATS>(P, xfTables, blob, bo, K, vo, vd, fmaxf(already, t0), fminf(rtmax, t1), lane, iso, ipc, th, hg, ws);
+          isoSegment<STATS>(P, xfTables, blob, bo, K, vo, vd, fmaxf(already, t0), fminf(rtmax, t1), lane, iso, isoScr, ipc, th, hg, ws);
           if (th >= 0.f) {
             surfPrim = -23; surfT = th / dtScale; surfNg = normalize3(hg); surfAmbient = 0.f; surfBase = f3(ipc.x, ipc.y, ipc.z);
             break;
@@ -559,10 +626,14 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
   }
 }
 
-int launchRenderFrame(const RenderParams &P, cudaStream_t s)
+int launchRenderFrame(const RenderParams &Pin, cudaStream_t s)
 {
+  RenderParams P = Pin;
+  // per-warp shared memory: kd stack | region blob | iso state | multi-channel iso scratch
+  const int scrFloats = (P.anyIso && P.numChannels > 1) ? 32 + 33 * P.numChannels : 0;
+  P.warpUnits = P.kdStack + BLOB_UNITS + 5 + (scrFloats + 3) / 4;
   const int tilesX = (P.width + TILE - 1) / TILE, tilesY = (P.height + TILE - 1) / TILE;
-  const size_t smemBytes = 16 * ((size_t)P.numChannels * 128 + (size_t)WARPS_PER_CTA * (P.kdStack + BLOB_UNITS + 5));
+  const size_t smemBytes = 16 * ((size_t)P.numChannels * 128 + (size_t)WARPS_PER_CTA * P.warpUnits);
   const dim3 grid(tilesX * tilesY), block(WARPS_PER_CTA * 32);
   const bool stats = P.stats != nullptr;
 #define LAUNCH(G, S_)                                                                                   \

@@ -28,6 +28,8 @@ struct RenderParams {
   const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones
   unsigned long long *stats;           // 4 counters (ExaStats) or null
   int kdStack;                         // stack entries per warp
+  int warpUnits;                       // set by launchRenderFrame: 16-B units of shared memory per warp
+  int dbg;                             // EXA_DEBUG builds only: print segments/samples
 };
 
 struct SampleParams {
