@@ -40,6 +40,13 @@ __device__ __forceinline__ float3 operator*(float s, float3 a) { return f3(a.x *
 __device__ __forceinline__ float dot3(float3 a, float3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
 __device__ __forceinline__ float len3(float3 a) { return sqrtf(dot3(a, a)); }
 __device__ __forceinline__ float3 normalize3(float3 a) { return a * (1.f / sqrtf(dot3(a, a))); }   // owl: v * rsqrt(dot)
+// Per-ray set-up (camera ray, voxel-space transform, normalisation) is evaluated "as written"
+// in the reference, products and sums rounded separately: it costs a few instructions per
+// ray and makes the region entry/exit parameters t0,t1 of boxTest reproducible.
+__device__ __forceinline__ float dot3nc(float3 a, float3 b)
+{ return __fadd_rn(__fadd_rn(__fmul_rn(a.x, b.x), __fmul_rn(a.y, b.y)), __fmul_rn(a.z, b.z)); }
+__device__ __forceinline__ float len3nc(float3 a) { return sqrtf(dot3nc(a, a)); }
+__device__ __forceinline__ float3 normalize3nc(float3 a) { const float s = 1.f / sqrtf(dot3nc(a, a)); return f3(a.x * s, a.y * s, a.z * s); }
 // ray.origin + t * ray.direction with the product and the sum rounded separately (no FMA
 // contraction): single-sample segments put their sample at the midpoint of two region faces,
 // which is exactly a dual-cell boundary of the coarser bricks, where the gradient jumps;
@@ -513,9 +520,9 @@ __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *
 }
 
 __device__ __forceinline__ float3 xfmVector(const float *m, float3 v)
-{ return f3(v.x * m[0] + v.y * m[3] + v.z * m[6], v.x * m[1] + v.y * m[4] + v.z * m[7], v.x * m[2] + v.y * m[5] + v.z * m[8]); }
+{ return f3(dot3nc(v, f3(m[0], m[3], m[6])), dot3nc(v, f3(m[1], m[4], m[7])), dot3nc(v, f3(m[2], m[5], m[8]))); }
 __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
-{ const float3 r = xfmVector(m, v); return f3(r.x + m[9], r.y + m[10], r.z + m[11]); }
+{ const float3 r = xfmVector(m, v); return f3(__fadd_rn(r.x, m[9]), __fadd_rn(r.y, m[10]), __fadd_rn(r.z, m[11])); }
 
 // -----------------------------------------------------------------------------------------
 // __raygen__renderFrame (exabrick.cu:1576-1720): one warp per pixel
@@ -551,15 +558,15 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
       const float sx = (float)px + jx, sy = (float)py + jy;
       // Camera::generateRay (programs/Camera.h:27-44)
       float3 o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
-      float3 d = normalize3(f3(P.dir00[0] + sx * P.dirDu[0] + sy * P.dirDv[0],
-                               P.dir00[1] + sx * P.dirDu[1] + sy * P.dirDv[1],
-                               P.dir00[2] + sx * P.dirDu[2] + sy * P.dirDv[2]));
+      float3 d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
+                                 __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
+                                 __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
       float tmin = 1e-6f, tmax = 1e8f;
       // ---- surfaces: implicit iso-surfaces (traceSurfaces :1514-1527, traceIsoRay :1408-1460)
       int surfPrim = -1; float surfT = tmax; float3 surfNg = f3(0, 0, 0), surfBase = f3(0, 0, 0); float surfAmbient = 0.f;
       if (P.anyIso) {
         const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
-        const float dtScale = len3(vd); vd = normalize3(vd);
+        const float dtScale = len3nc(vd); vd = normalize3nc(vd);
         float already = dtScale * tmin; float rtmax = tmax;
         __syncwarp();
         if (lane < EXA_MAX_CHANNELS) { iso[lane].lastV = -1e36f; iso[lane].lastT = 0.f; }
@@ -594,7 +601,7 @@ __global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid
       if (P.clipEnabled) { float a, b; boxTest(o, d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
       const float tHitWorld = tmax;
       o = xfmPoint(P.xfm, o); d = xfmVector(P.xfm, d);
-      const float dtScale = len3(d); d = normalize3(d);
+      const float dtScale = len3nc(d); d = normalize3nc(d);
       float already = dtScale * tmin;
       const float rayTmax = tHitWorld * dtScale;
       Trav T; travInit(T, stack, o, d, already, rayTmax, P.scene);
