@@ -198,7 +198,7 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   rc = abrBuild(r->d_bricks, r->numBricks, r->d_scalars, r->numCells, numFields, s, r->abr);
   if (rc) { exa_renderer_destroy(r); return rc; }
   r->launches += r->abr.launches;
-  if (r->abr.depth + 2 > 1024) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
+  if (r->abr.depth + 2 > 160) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
   r->h_kd.resize(r->abr.numKdNodes);
   CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);

@@ -1,17 +1,16 @@
 // render.cu — fused sm_100a kernels of the ExaBricks rendering hot path.
 //
-//   k_renderFrame   one WARP per ray.  Ordered kd-tree traversal over the ABRs (replaces
-//                   optixTrace + __intersection__VolumeBVH, programs/exabrick.cu:184-238,
-//                   without per-region restarts), then per region segment the 32 lanes take
-//                   32 CONSECUTIVE samples of the ray: tent-basis reconstruction
-//                   (exabrick.cu:620-816, 883-942) from brick headers staged in shared
-//                   memory, transfer function (:135-150) from a shared-memory table,
-//                   opacity correction + gradient shading (:988-1016), and front-to-back
-//                   compositing (:1116-1185) as a warp-wide prefix "over", with early ray
-//                   termination located exactly (first sample whose running alpha crosses
-//                   the threshold).  Implicit iso-surfaces (:1018-1114, 1187-1256,
-//                   1408-1460) run as a first pass of the same kernel; accumulation, sRGB
-//                   and RGBA8 pack (:1701-1719) as its tail.
+//   k_renderFrame   one thread per ray, 8x4 pixel tile per warp.  Ordered kd-tree traversal
+//                   over the ABRs with a per-thread stack in shared memory (replaces optixTrace
+//                   + __intersection__VolumeBVH, programs/exabrick.cu:184-238, without the
+//                   per-region restarts), then per region segment: tent-basis reconstruction
+//                   (exabrick.cu:620-816, 883-942) straight from the region blob (header +
+//                   brick headers, one contiguous 16-byte-aligned record per region),
+//                   transfer function (:135-150) from a shared-memory table, opacity
+//                   correction + gradient shading (:988-1016), front-to-back compositing with
+//                   early ray termination (:1116-1185).  Implicit iso-surfaces (:1018-1114,
+//                   1187-1256, 1408-1460) run as a first pass of the same kernel;
+//                   accumulation, sRGB and RGBA8 pack (:1701-1719) are its tail.
 //   k_samplePoints  one thread per point: kd point location + reconstruction.
 //   k_trace         RK4 streamline advection (exabrick.cu:1531-1574), one thread per seed.
 //   k_regionActive / k_nodeActiveUp   space-skipping masks (exabrick.cu:250-331, 373-402):
@@ -24,10 +23,6 @@
 namespace exa {
 
 #define FULL 0xffffffffu
-static constexpr int WARPS_PER_CTA = 8;
-static constexpr int TILE = 8;           // 8x8 pixel tile per CTA, one row per warp
-static constexpr int MAXK = 16;          // brick headers staged per chunk
-static constexpr int BLOB_UNITS = 3 + 2 * MAXK;
 
 // -----------------------------------------------------------------------------------------
 // small device helpers
@@ -65,7 +60,7 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
                                             float px, float py, float pz, unsigned &nCorners)
 {
   for (int i = 0; i < k; i++) {
-    const uint4 u0 = hdrs[2 * i], u1 = hdrs[2 * i + 1];
+    const uint4 u0 = __ldg(hdrs + 2 * i), u1 = __ldg(hdrs + 2 * i + 1);
     const float invCw = __uint_as_float(u0.w);
     const int sx = (int)u1.x, sy = (int)u1.y, sz = (int)u1.z;
     const float lx = (px - __uint_as_float(u0.x)) * invCw - 0.5f;
@@ -171,54 +166,55 @@ __device__ __forceinline__ uint32_t make_rgba8(float3 c)
 { return (uint32_t)(make_8bit(c.x) << 0) + (uint32_t)(make_8bit(c.y) << 8) + (uint32_t)(make_8bit(c.z) << 16) + (0xffu << 24); }
 
 // -----------------------------------------------------------------------------------------
-// ordered kd traversal, one warp in lock-step; stack in shared memory
+// ordered kd traversal, one thread per ray; per-thread stack in shared memory
 // -----------------------------------------------------------------------------------------
 struct Trav {
-  uint4 *stack;          // per warp: {node, tn bits, tf bits, -}
+  uint2 *stack;          // this thread's column: entry e at stack[e * blockDim.x]  {node, tf bits}
   int sp;
   int cur; float tn, tf; // node being descended (-1: pop)
   float3 o, d;
 };
 
-__device__ __forceinline__ void travInit(Trav &T, uint4 *stack, float3 o, float3 d, float tmin, float tmax, const DeviceScene &S)
+__device__ __forceinline__ void travInit(Trav &T, uint2 *stack, float3 o, float3 d, float tmin, float tmax, const DeviceScene &S)
 {
-  T.stack = stack; T.sp = 0; T.o = o; T.d = d; T.cur = -1;
+  T.stack = stack; T.sp = 0; T.o = o; T.d = d; T.cur = -1; T.tn = 0.f; T.tf = 0.f;
   float t0, t1;
   if (boxTest(o, d, tmin, tmax, S.boundsLo, S.boundsHi, t0, t1)) {
-    // widen a little: the root interval is only used for culling, leaves do the exact test
+    // widen a little: node intervals are only used for culling, leaves do the exact test
     T.cur = 0; T.tn = t0 - 1e-5f * fabsf(t0) - 1e-6f; T.tf = t1 + 1e-5f * fabsf(t1) + 1e-6f;
   }
 }
 
+struct Segment { uint32_t blobOfs; int K; float t0, t1, fcw; };
+
 // Finds the next region (front-to-back) with t0 = max(tmin, entry) < t1 = min(tmax, exit)
-// (exabrick.cu:213-238); on success the region blob (header + up to MAXK brick headers) is
-// staged in `blob` (shared memory) and true is returned.
+// (exabrick.cu:213-238).  Inner nodes use one IEEE division for the plane distance (the same
+// expression boxTest evaluates for that face); leaves run the reference's boxTest verbatim.
 __device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
-                                         float tmin, float tmax, uint4 *blob, int lane,
-                                         uint32_t &blobOfs, int &K, float &t0, float &t1)
+                                         float tmin, float tmax, Segment &seg)
 {
+  const int stride = blockDim.x;
   for (;;) {
     if (T.cur < 0) {
       if (T.sp == 0) return false;
       T.sp--;
-      const uint4 e = T.stack[T.sp];
-      T.cur = (int)e.x; T.tn = __uint_as_float(e.y); T.tf = __uint_as_float(e.z);
+      const uint2 e = T.stack[T.sp * stride];
+      T.cur = (int)e.x; T.tf = __uint_as_float(e.y);
+      T.tn = tmin;                                   // conservative: everything before tmin is done
     }
-    if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || (active && !active[T.cur])) { T.cur = -1; continue; }
+    if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || !active[T.cur]) { T.cur = -1; continue; }
     const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + T.cur);
     const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
     if (axis == 3) {
       T.cur = -1;
       if (payload == KD_EMPTY) continue;
-      K = (int)raw.x;
-      const int units = 3 + 2 * min(K, MAXK);
-      __syncwarp();
-      for (int u = lane; u < units; u += 32) blob[u] = __ldg(S.blobs + payload + u);
-      __syncwarp();
-      const uint4 h0 = blob[0], h1 = blob[1];
+      const uint4 h0 = __ldg(S.blobs + payload), h1 = __ldg(S.blobs + payload + 1);
       const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
       const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
-      if (boxTest(T.o, T.d, tmin, tmax, lo, hi, t0, t1)) { blobOfs = payload; return true; }
+      if (boxTest(T.o, T.d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
+        seg.blobOfs = payload; seg.K = (int)raw.x; seg.fcw = __uint_as_float(h1.z);
+        return true;
+      }
       continue;
     }
     const float split = __uint_as_float(raw.x);
@@ -228,15 +224,15 @@ __device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const ui
     const int first = (int)payload + (belowFirst ? 0 : 1), second = (int)payload + (belowFirst ? 1 : 0);
     const float eps = 1e-5f * fabsf(tp) + 1e-6f;
     if (tp != tp) {                                  // ray inside the plane: visit both halves
-      if (lane == 0) T.stack[T.sp] = make_uint4((uint32_t)second, __float_as_uint(T.tn), __float_as_uint(T.tf), 0);
-      T.sp++; __syncwarp(); T.cur = first;
+      T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
+      T.sp++; T.cur = first;
     } else if (tp > T.tf + eps || tp <= 0.f) {
       T.cur = first;
     } else if (tp < T.tn - eps) {
       T.cur = second;
     } else {
-      if (lane == 0) T.stack[T.sp] = make_uint4((uint32_t)second, __float_as_uint(tp - eps), __float_as_uint(T.tf), 0);
-      T.sp++; __syncwarp();
+      T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
+      T.sp++;
       T.cur = first; T.tf = tp + eps;
     }
   }
@@ -245,8 +241,8 @@ __device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const ui
 // common sample-lattice set-up of integrateBrick / isoIntegrateBrick (exabrick.cu:1141-1144)
 __device__ __forceinline__ float firstLatticeT(float t0, float dt, float offs)
 {
-  const int i0 = (int)ceilf((t0 - dt * offs) / dt);
-  float t_i = (offs + (float)i0) * dt;
+  const int i0 = (int)ceilf(__fsub_rn(t0, __fmul_rn(dt, offs)) / dt);
+  float t_i = __fmul_rn(offs + (float)i0, dt);
   while ((t_i - dt) >= t0) t_i = t_i - dt;
   while (t_i < t0) t_i += dt;
   return t_i;
@@ -259,263 +255,140 @@ __device__ __forceinline__ float4 over(float4 a, float4 b)
   return make_float4(a.x + k * b.x, a.y + k * b.y, a.z + k * b.z, a.w + k * b.w);
 }
 
-// Reconstruct at `pos` for one channel, all lanes in lock-step over the same region.
+struct RayStats { unsigned samples, visits, corners, segments; };
+
+// samplePoint / samplePointWithDerivative (exabrick.cu:781-816, 883-942) inside a known region
 template <bool GRAD, bool STATS>
-__device__ __forceinline__ bool sampleRegion(const DeviceScene &S, uint4 *blob, uint32_t blobOfs, int K, int channel, int lane,
-                                             float3 pos, float &value, float3 &g, unsigned &nCorners)
+__device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment &seg, int channel, float3 pos,
+                                             float &value, float3 &g, RayStats &rs)
 {
   Acc a; accZero(a);
-  const float *chan = S.scalars + (size_t)channel * S.numCells;
-  accumBricks<GRAD, STATS>(a, blob + 3, min(K, MAXK), chan, pos.x, pos.y, pos.z, nCorners);
-  if (K > MAXK) {               // rare: more bricks than staged; stream the rest through the buffer
-    for (int k0 = MAXK; k0 < K; k0 += MAXK) {
-      const int kc = min(MAXK, K - k0);
-      __syncwarp();
-      for (int u = lane; u < 2 * kc; u += 32) blob[3 + u] = __ldg(S.blobs + blobOfs + 3 + 2 * k0 + u);
-      __syncwarp();
-      accumBricks<GRAD, STATS>(a, blob + 3, kc, chan, pos.x, pos.y, pos.z, nCorners);
-    }
-    __syncwarp();
-    for (int u = lane; u < 2 * MAXK; u += 32) blob[3 + u] = __ldg(S.blobs + blobOfs + 3 + u);
-    __syncwarp();
-  }
+  unsigned nc = 0;
+  accumBricks<GRAD, STATS>(a, S.blobs + seg.blobOfs + 3, seg.K, S.scalars + (size_t)channel * S.numCells, pos.x, pos.y, pos.z, nc);
+  if (STATS) { rs.samples++; rs.visits += seg.K; rs.corners += nc; }
   return accFinish<GRAD>(a, value, g);
 }
 
-struct WarpStats { unsigned samples, visits, corners, segments; };
-
-// integrateBrick<GRADIENT_SHADING> (exabrick.cu:1116-1185) for one region segment; lanes take
-// consecutive samples.  Returns true if the ray terminated (alpha >= threshold).
+// integrateBrick<GRADIENT_SHADING> + integrateVolume (exabrick.cu:1116-1185, 988-1016), as written.
+// Returns true if the ray terminated (alpha >= threshold).
 template <bool GRAD, bool STATS>
-__device__ __forceinline__ bool integrateSegment(const RenderParams &P, const float4 *xfTables, uint4 *blob, uint32_t blobOfs, int K,
-                                                 float3 o, float3 d, float t0, float t1, float offs, int lane,
-                                                 float4 &pc, WarpStats &ws)
+__device__ __forceinline__ bool integrateSegment(const RenderParams &P, const float4 *xfTables, const Segment &seg,
+                                                 float3 o, float3 d, float offs, float4 &pc, RayStats &rs)
 {
-  const float fcw = __uint_as_float(blob[1].z);
-  const float dt = P.dt * fcw;
-  const float tFirst = firstLatticeT(t0, dt, offs);
-  if (STATS) ws.segments++;
+  const float dt = P.dt * seg.fcw;
+  const float t0 = seg.t0, t1 = seg.t1;
+  float t_i = firstLatticeT(t0, dt, offs);
+  float t_last = t0;
+  if (STATS) rs.segments++;
 #ifdef EXA_DEBUG
-  if (P.dbg && lane == 0) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)blob[2].x, K, t0, t1, dt, tFirst);
+  if (P.dbg) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)P.scene.blobs[seg.blobOfs + 2].x, seg.K, t0, t1, dt, t_i);
 #endif
-  for (int base = 0;; base += 32) {
-    const int j = base + lane;
-    const float tj = fmaf((float)j, dt, tFirst);
-    const float tjm1 = fmaf((float)(j - 1), dt, tFirst);
-    const bool act = (j == 0) || (tjm1 < t1);
-    const float tNext = fminf(tj, t1);
-    const float tLast = (j == 0) ? t0 : tjm1;
-    const float tSample = 0.5f * (tNext + tLast);
-    const float actualDt = tNext - tLast;
-    float4 L = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (act) {
-      const float3 pos = rayAt(o, d, tSample);
-      for (int c = 0; c < P.numChannels; c++) {
-        float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0;
-        const bool ok = sampleRegion<GRAD, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
-        if (STATS) { ws.samples++; ws.visits += K; ws.corners += nc; }
-        if (ok && actualDt != 0.f) {                       // integrateVolume, exabrick.cu:988-1016
-          float4 s = lookupXF(xfTables + c * 128, P.xfDomain[c][0], P.xfDomain[c][1], P.xfOpacityScale, v);
-          if (GRAD && len3(g) > (float)(int)fcw * 1e-6f) {
-            const float3 l = f3(-d.x, -d.y, -d.z);
-            const float scale = fabsf(dot3(l, g)) / sqrtf(dot3(g, g) * dot3(l, l));
-            s.x *= scale; s.y *= scale; s.z *= scale;
-          }
-          s.w = 1.f - powf(1.f - s.w, actualDt);
-#ifdef EXA_DEBUG
-          if (P.dbg) printf("G   smp j=%d t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", j, tSample, actualDt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
-#endif
-          const float k = (1.f - L.w) * s.w;
-          L.x += k * s.x; L.y += k * s.y; L.z += k * s.z; L.w += k;
+  for (;; t_i += dt) {
+    const float t_next = fminf(t_i, t1);
+    const float t_sample = 0.5f * (t_next + t_last);
+    const float actual_dt = t_next - t_last;
+    t_last = t_next;
+    const float3 pos = rayAt(o, d, t_sample);
+    for (int c = 0; c < P.numChannels; c++) {
+      float v = 0.f; float3 g = f3(0, 0, 0);
+      if (sampleRegion<GRAD, STATS>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
+        float4 s = lookupXF(xfTables + c * 128, P.xfDomain[c][0], P.xfDomain[c][1], P.xfOpacityScale, v);
+        if (GRAD && len3(g) > (float)(int)seg.fcw * 1e-6f) {
+          const float3 l = f3(-d.x, -d.y, -d.z);
+          const float scale = fabsf(dot3(l, g)) / sqrtf(dot3(g, g) * dot3(l, l));
+          s.x *= scale; s.y *= scale; s.z *= scale;
         }
+        s.w = 1.f - powf(1.f - s.w, actual_dt);
+#ifdef EXA_DEBUG
+        if (P.dbg) printf("G   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", t_sample, actual_dt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
+#endif
+        const float k = (1.f - pc.w) * s.w;
+        pc.x += k * s.x; pc.y += k * s.y; pc.z += k * s.z; pc.w += k;
       }
     }
-    // inclusive prefix "over" across lanes (samples are ordered by lane)
-#pragma unroll
-    for (int ofs = 1; ofs < 32; ofs <<= 1) {
-      float4 prev;
-      prev.x = __shfl_up_sync(FULL, L.x, ofs); prev.y = __shfl_up_sync(FULL, L.y, ofs);
-      prev.z = __shfl_up_sync(FULL, L.z, ofs); prev.w = __shfl_up_sync(FULL, L.w, ofs);
-      if (lane >= ofs) L = over(prev, L);
-    }
-    const float4 after = over(pc, L);                      // pixel colour after this lane's sample
-    const unsigned term = __ballot_sync(FULL, act && after.w >= P.ertThreshold);
-    const unsigned actMask = __ballot_sync(FULL, act);
-    int src;
-    bool done = false;
-    if (term) { src = __ffs(term) - 1; done = true; }
-    else src = 31 - __clz(actMask);                        // last active lane
-    pc.x = __shfl_sync(FULL, after.x, src); pc.y = __shfl_sync(FULL, after.y, src);
-    pc.z = __shfl_sync(FULL, after.z, src); pc.w = __shfl_sync(FULL, after.w, src);
-    if (done) return true;
-    // the reference loop ends after the first sample whose t_next reached t1
-    const float t31 = fmaf((float)(base + 31), dt, tFirst);
-    if (t31 >= t1) return false;
+    if (pc.w >= P.ertThreshold) return true;
+    if (t_next >= t1) return false;
   }
 }
 
-// state of one IsoSurfaceIntegrationFunction (exabrick.cu:1018-1114), kept per channel
-struct IsoState { float lastT, lastV; };
-
-// Shade one iso crossing at ray parameter th (IsoSurfaceIntegrationFunction::operator(),
-// exabrick.cu:1053-1101); executed by all lanes in lock-step with identical arguments.
+// IsoSurfaceIntegrationFunction::operator() (exabrick.cu:1024-1109) for channel `c`
 template <bool STATS>
-__device__ __forceinline__ void shadeIsoHit(const RenderParams &P, const float4 *xfTables, uint4 *blob, uint32_t blobOfs, int K,
-                                            float3 o, float3 d, float th, int ii, int lane,
-                                            float4 &pc, float &tHit, float3 &hitGrad, WarpStats &ws)
+__device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
+                                           int c, float t_sample, float cellValue, float &lastT, float &lastV,
+                                           float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
 {
-  const float3 isopt = rayAt(o, d, th);
-  float cv = 0.f; float3 grad = f3(0, 0, 0); unsigned nc2 = 0;
-  float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
-  const int ich = P.isoChannel[ii];
-  if (P.gradISO) {
-    if (sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2)) {
-      smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
-      grad = normalize3(grad);
-      if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
-    }
-  } else {
-    if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, ich, lane, isopt, cv, grad, nc2))
-      smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
-  }
-  if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc2; }
-  if (P.colormapChannel != 0) {
-    cv = 0.f; float3 g2; unsigned nc3 = 0;
-    if (sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, P.colormapChannel, lane, isopt, cv, g2, nc3))
-      smp = lookupXF(xfTables, P.xfDomain[0][0], P.xfDomain[0][1], P.xfOpacityScale, cv);
-    if (STATS && lane == 0) { ws.samples++; ws.visits += K; ws.corners += nc3; }
-  }
-  smp.w = 1.f;
-  if (!isfinite(grad.x) || !isfinite(grad.y) || !isfinite(grad.z)) grad = f3(0, 0, 0);
-  if (len3(grad) > 0.f) {
-    const float3 l = f3(-d.x, -d.y, -d.z);
-    const float scale = .3f + .7f * fabsf(dot3(l, grad)) / sqrtf(dot3(grad, grad));
-    smp.x *= scale; smp.y *= scale; smp.z *= scale;
-  }
-  const float k = (1.f - pc.w) * smp.w;
-  pc.x += k * smp.x; pc.y += k * smp.y; pc.z += k * smp.z; pc.w += k;
-  tHit = th; hitGrad = grad;
-}
-
-// crossing test of one functor call (exabrick.cu:1035-1052): the iso indices are visited in
-// order, every match shades and overwrites t_hit; returns first and last matching index
-__device__ __forceinline__ bool isoCross(const RenderParams &P, int c, float lastV, float lastT, float v, float tSample,
-                                         float &tFirst, int &iFirst, float &tLast, int &iLast)
-{
-  bool crossed = false;
   if (lastV >= -1e35f) {
-#pragma unroll
     for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
       const float isoV = P.isoValue[i];
-      if (P.isoEnabled[i] && P.isoChannel[i] == c && ((lastV <= isoV && v >= isoV) || (lastV >= isoV && v <= isoV))) {
-        const float d1 = fabsf(lastV - isoV), d2 = fabsf(v - isoV);
+      if (P.isoEnabled[i] && P.isoChannel[i] == c &&
+          ((lastV <= isoV && cellValue >= isoV) || (lastV >= isoV && cellValue <= isoV))) {
+        const float d1 = fabsf(lastV - isoV), d2 = fabsf(cellValue - isoV);
         const float w1 = 1.f - d1 / (d1 + d2), w2 = 1.f - d2 / (d1 + d2);
-        const float tavg = lastT * w1 + tSample * w2;
-        if (!crossed) { tFirst = tavg; iFirst = i; }
-        tLast = tavg; iLast = i; crossed = true;
+        const float tavg = __fadd_rn(__fmul_rn(lastT, w1), __fmul_rn(t_sample, w2));
+        const float3 isopt = rayAt(o, d, tavg);
+        float cv = 0.f; float3 grad = f3(0, 0, 0);
+        float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
+        const int ich = P.isoChannel[i];
+        if (P.gradISO) {
+          if (sampleRegion<true, STATS>(P.scene, seg, ich, isopt, cv, grad, rs)) {
+            smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
+            grad = normalize3(grad);
+            if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
+          }
+        } else {
+          if (sampleRegion<false, STATS>(P.scene, seg, ich, isopt, cv, grad, rs))
+            smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
+        }
+        if (P.colormapChannel != 0) {
+          cv = 0.f; float3 g2;
+          if (sampleRegion<false, STATS>(P.scene, seg, P.colormapChannel, isopt, cv, g2, rs))
+            smp = lookupXF(xfTables, P.xfDomain[0][0], P.xfDomain[0][1], P.xfOpacityScale, cv);
+        }
+        smp.w = 1.f;
+        if (!isfinite(grad.x) || !isfinite(grad.y) || !isfinite(grad.z)) grad = f3(0, 0, 0);
+        if (len3(grad) > 0.f) {
+          const float3 l = f3(-d.x, -d.y, -d.z);
+          const float scale = .3f + .7f * fabsf(dot3(l, grad)) / sqrtf(dot3(grad, grad));
+          smp.x *= scale; smp.y *= scale; smp.z *= scale;
+        }
+        const float k = (1.f - pc.w) * smp.w;
+        pc.x += k * smp.x; pc.y += k * smp.y; pc.z += k * smp.z; pc.w += k;
+        tHit = tavg; hitGrad = grad;
       }
     }
   }
-  return crossed;
+  lastT = t_sample; lastV = cellValue;
 }
 
-// isoIntegrateBrick (exabrick.cu:1187-1256) for one region segment; lanes take consecutive
-// samples.  Colour comes from the first crossing; t_hit / gradient are overwritten by later
-// crossings of the segment exactly as in the reference (its functor keeps running after a
-// hit).  One primary channel: crossings are found with ballots.  Several channels: the values
-// of a 32-sample batch are parked in shared memory and the reference's (sample, channel)
-// loop, including its "break once opaque" rule (:1249), is replayed in lock-step.
+// isoIntegrateBrick (exabrick.cu:1187-1256), as written; per-channel functor state lives in
+// this thread's column of shared memory (isoT / isoV, entry c at [c * blockDim.x])
 template <bool STATS>
-__device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *xfTables, uint4 *blob, uint32_t blobOfs, int K,
-                                           float3 o, float3 d, float t0, float t1, int lane, IsoState *iso /*smem, per channel*/,
-                                           float *scr /*smem scratch, multi-channel only*/,
-                                           float4 &pc, float &tHit, float3 &hitGrad, WarpStats &ws)
+__device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
+                                           float t0, float t1, float *isoT, float *isoV,
+                                           float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
 {
-  const float fcw = __uint_as_float(blob[1].z);
-  const float dt = P.dt * fcw;
-  const float tFirst = firstLatticeT(t0, dt, 0.f);
-  const int C = P.numChannels;
-  if (STATS) ws.segments++;
-  for (int base = 0;; base += 32) {
-    const int j = base + lane;
-    const float tj = fmaf((float)j, dt, tFirst);
-    const float tjm1 = fmaf((float)(j - 1), dt, tFirst);
-    const bool act = (j == 0) || (tjm1 < t1);
-    const float tNext = fminf(tj, t1);
-    const float tLast = (j == 0) ? t0 : tjm1;
-    const float tSample = 0.5f * (tNext + tLast);
-    const float3 pos = rayAt(o, d, tSample);
-    if (C == 1) {
-      float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0; bool ok = false;
-      if (act) {
-        if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, 0, lane, pos, v, g, nc);
-        else ok = sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, 0, lane, pos, v, g, nc);
-        if (STATS) { ws.samples++; ws.visits += K; ws.corners += nc; }
-      }
-      // previous VALID sample: nearest lower valid lane, else the state carried in
-      const unsigned okMask = __ballot_sync(FULL, ok);
-      const unsigned below = okMask & ((1u << lane) - 1u);
-      const int prevLane = below ? 31 - __clz(below) : -1;
-      const float pv = __shfl_sync(FULL, v, prevLane < 0 ? 0 : prevLane);
-      const float pt = __shfl_sync(FULL, tSample, prevLane < 0 ? 0 : prevLane);
-      const float lastV = prevLane < 0 ? iso[0].lastV : pv;
-      const float lastT = prevLane < 0 ? iso[0].lastT : pt;
-      float ta = 0.f, tb = 0.f; int ia = 0, ib = 0;
-      const bool crossed = ok && isoCross(P, 0, lastV, lastT, v, tSample, ta, ia, tb, ib);
-      const unsigned crossMask = __ballot_sync(FULL, crossed);
-      if (crossMask) {
-        const int firstLane = __ffs(crossMask) - 1, lastLane = 31 - __clz(crossMask);
-        const float tA = __shfl_sync(FULL, ta, firstLane); const int iA = __shfl_sync(FULL, ia, firstLane);
-        const float tB = __shfl_sync(FULL, tb, lastLane); const int iB = __shfl_sync(FULL, ib, lastLane);
-        shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tA, iA, lane, pc, tHit, hitGrad, ws);
-        if (firstLane != lastLane || iA != iB)
-          shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tB, iB, lane, pc, tHit, hitGrad, ws);
-      }
-      if (okMask) {
-        const int lastOk = 31 - __clz(okMask);
-        const float nv = __shfl_sync(FULL, v, lastOk), nt = __shfl_sync(FULL, tSample, lastOk);
-        __syncwarp();
-        if (lane == 0) { iso[0].lastV = nv; iso[0].lastT = nt; }
-        __syncwarp();
-      }
-    } else {
-      // scr: tS[32] | v[C][32] | okMask[C]
-      unsigned *okMasks = reinterpret_cast<unsigned *>(scr + 32 + 32 * C);
-      __syncwarp();
-      scr[lane] = tSample;
-      for (int c = 0; c < C; c++) {
-        float v = 0.f; float3 g = f3(0, 0, 0); unsigned nc = 0; bool ok = false;
-        if (act) {
-          if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
-          else ok = sampleRegion<false, STATS>(P.scene, blob, blobOfs, K, c, lane, pos, v, g, nc);
-          if (STATS) { ws.samples++; ws.visits += K; ws.corners += nc; }
-        }
-        scr[32 + 32 * c + lane] = v;
-        const unsigned m = __ballot_sync(FULL, ok);
-        if (lane == 0) okMasks[c] = m;
-      }
-      __syncwarp();
-      const unsigned actMask = __ballot_sync(FULL, act);
-      const int nAct = 32 - __clz(actMask);
-      for (int jj = 0; jj < nAct; jj++) {
-        const float ts = scr[jj];
-        for (int c = 0; c < C; c++) {
-          if (!((okMasks[c] >> jj) & 1u)) continue;
-          const float v = scr[32 + 32 * c + jj];
-          float ta = 0.f, tb = 0.f; int ia = 0, ib = 0;
-          if (isoCross(P, c, iso[c].lastV, iso[c].lastT, v, ts, ta, ia, tb, ib)) {
-            shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, ta, ia, lane, pc, tHit, hitGrad, ws);
-            if (ia != ib) shadeIsoHit<STATS>(P, xfTables, blob, blobOfs, K, o, d, tb, ib, lane, pc, tHit, hitGrad, ws);
-          }
-          __syncwarp();
-          if (lane == 0) { iso[c].lastV = v; iso[c].lastT = ts; }
-          __syncwarp();
-          if (pc.w >= P.ertThreshold) break;
-        }
+  const int stride = blockDim.x;
+  const float dt = P.dt * seg.fcw;
+  float t_i = firstLatticeT(t0, dt, 0.f);
+  float t_last = t0;
+  if (STATS) rs.segments++;
+  for (;; t_i += dt) {
+    const float t_next = fminf(t_i, t1);
+    const float t_sample = 0.5f * (t_next + t_last);
+    t_last = t_next;
+    const float3 pos = rayAt(o, d, t_sample);
+    for (int c = 0; c < P.numChannels; c++) {
+      float v = 0.f; float3 g = f3(0, 0, 0); bool ok;
+      if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, seg, c, pos, v, g, rs);
+      else ok = sampleRegion<false, STATS>(P.scene, seg, c, pos, v, g, rs);
+      if (ok) {
+        float lt = isoT[c * stride], lv = isoV[c * stride];
+        isoFunctor<STATS>(P, xfTables, seg, o, d, c, t_sample, v, lt, lv, pc, tHit, hitGrad, rs);
+        isoT[c * stride] = lt; isoV[c * stride] = lv;
+        if (pc.w >= P.ertThreshold) break;
       }
     }
-    const float t31 = fmaf((float)(base + 31), dt, tFirst);
-    if (t31 >= t1) return;
+    if (t_next >= t1) return;
   }
 }
 
@@ -525,123 +398,120 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 { const float3 r = xfmVector(m, v); return f3(__fadd_rn(r.x, m[9]), __fadd_rn(r.y, m[10]), __fadd_rn(r.z, m[11])); }
 
 // -----------------------------------------------------------------------------------------
-// __raygen__renderFrame (exabrick.cu:1576-1720): one warp per pixel
+// __raygen__renderFrame (exabrick.cu:1576-1720): one thread per pixel, 8x4 pixel tile per warp
 // -----------------------------------------------------------------------------------------
+static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
+static constexpr int TILE_W = 16, TILE_H = 8;
+
 template <bool GRAD, bool STATS>
-__global__ void __launch_bounds__(WARPS_PER_CTA * 32) k_renderFrame(const __grid_constant__ RenderParams P)
+__global__ void __launch_bounds__(FRAME_THREADS, 5) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
-  // layout: [xf tables: numChannels*128 float4][per warp: stack kdStack][per warp: blob BLOB_UNITS][per warp: iso state 10*8B=5 units]
+  // layout: [xf tables: numChannels*128 float4][kd stacks: kdStack x 128 uint2][iso state: 2 x numChannels x 128 float]
   float4 *xfTables = reinterpret_cast<float4 *>(smem);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  uint4 *warpBase = smem + P.numChannels * 128 + warp * P.warpUnits;
-  uint4 *stack = warpBase, *blob = warpBase + P.kdStack;
-  IsoState *iso = reinterpret_cast<IsoState *>(warpBase + P.kdStack + BLOB_UNITS);
-  float *isoScr = reinterpret_cast<float *>(warpBase + P.kdStack + BLOB_UNITS + 5);
+  uint2 *stackBase = reinterpret_cast<uint2 *>(smem + P.numChannels * 128);
+  float *isoBase = reinterpret_cast<float *>(stackBase + (size_t)P.kdStack * FRAME_THREADS);
   for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
   __syncthreads();
 
-  const int tilesX = (P.width + TILE - 1) / TILE;
+  const int tilesX = (P.width + TILE_W - 1) / TILE_W;
   const int tileId = blockIdx.x;
   if (P.tileMode && (tileId % P.numRanks) != P.rank) return;
-  const int tx = (tileId % tilesX) * TILE, ty = (tileId / tilesX) * TILE;
-  const int py = ty + warp;
-  WarpStats ws = {0, 0, 0, 0};
-  if (py < P.height) {
-    for (int px = tx; px < tx + TILE && px < P.width; px++) {
-      const int pixelIdx = px + P.width * py;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  // warp w covers the 8x4 sub-tile (w&1, w>>1) of the 16x8 CTA tile
+  const int px = (tileId % tilesX) * TILE_W + (warp & 1) * 8 + (lane & 7);
+  const int py = (tileId / tilesX) * TILE_H + (warp >> 1) * 4 + (lane >> 3);
+  RayStats rs = {0, 0, 0, 0};
+  bool inside = px < P.width && py < P.height;
 #ifdef EXA_DEBUG
-      if (P.dbg && pixelIdx != P.dbg - 1) continue;
+  if (P.dbg && (px + P.width * py) != P.dbg - 1) inside = false;
 #endif
-      LCG16 rnd((uint32_t)(P.frameID * P.width * P.height) + (uint32_t)px, (uint32_t)py);
-      const float jx = rnd.next(), jy = rnd.next();
-      const float sx = (float)px + jx, sy = (float)py + jy;
-      // Camera::generateRay (programs/Camera.h:27-44)
-      float3 o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
-      float3 d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
-                                 __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
-                                 __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
-      float tmin = 1e-6f, tmax = 1e8f;
-      // ---- surfaces: implicit iso-surfaces (traceSurfaces :1514-1527, traceIsoRay :1408-1460)
-      int surfPrim = -1; float surfT = tmax; float3 surfNg = f3(0, 0, 0), surfBase = f3(0, 0, 0); float surfAmbient = 0.f;
-      if (P.anyIso) {
-        const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
-        const float dtScale = len3nc(vd); vd = normalize3nc(vd);
-        float already = dtScale * tmin; float rtmax = tmax;
-        __syncwarp();
-        if (lane < EXA_MAX_CHANNELS) { iso[lane].lastV = -1e36f; iso[lane].lastT = 0.f; }
-        __syncwarp();
-        Trav T; rtmax = rtmax * dtScale;
-        travInit(T, stack, vo, vd, already, rtmax, P.scene);
-        for (;;) {
-          uint32_t bo; int K; float t0, t1;
-          if (!travNext(T, P.scene, P.isoActive, already, rtmax, blob, lane, bo, K, t0, t1)) break;
-          float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
-          isoSegment<STATS>(P, xfTables, blob, bo, K, vo, vd, fmaxf(already, t0), fminf(rtmax, t1), lane, iso, isoScr, ipc, th, hg, ws);
-          if (th >= 0.f) {
-            surfPrim = -23; surfT = th / dtScale; surfNg = normalize3(hg); surfAmbient = 0.f; surfBase = f3(ipc.x, ipc.y, ipc.z);
-            break;
-          }
-          already = t1 * 1.0000001f;
-          rtmax = rtmax * dtScale;                          // (sic) exabrick.cu:1434
-        }
-      }
-      float3 bg = f3(0, 0, 0);
-      if (surfPrim == -23) {                                // :1604-1652 with AO disabled
-        const bool shade = P.gradISO != 0;
-        if (shade && len3(surfNg) > 0.f) {
-          const float k = fabsf(dot3(d, surfNg));
-          bg = f3(surfAmbient + surfBase.x * k, surfAmbient + surfBase.y * k, surfAmbient + surfBase.z * k);
-        } else bg = surfBase;
-      }
-      // ---- DVR (:1654-1699)
-      float4 pc = make_float4(0, 0, 0, 0);
-      const float offs = rnd.next();
-      tmax = surfT;
-      if (P.clipEnabled) { float a, b; boxTest(o, d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
-      const float tHitWorld = tmax;
-      o = xfmPoint(P.xfm, o); d = xfmVector(P.xfm, d);
-      const float dtScale = len3nc(d); d = normalize3nc(d);
-      float already = dtScale * tmin;
-      const float rayTmax = tHitWorld * dtScale;
-      Trav T; travInit(T, stack, o, d, already, rayTmax, P.scene);
+  if (inside) {
+    uint2 *stack = stackBase + threadIdx.x;
+    float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
+    const int pixelIdx = px + P.width * py;
+    LCG16 rnd((uint32_t)(P.frameID * P.width * P.height) + (uint32_t)px, (uint32_t)py);
+    const float jx = rnd.next(), jy = rnd.next();
+    const float sx = (float)px + jx, sy = (float)py + jy;
+    // Camera::generateRay (programs/Camera.h:27-44)
+    float3 o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
+    float3 d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
+                               __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
+                               __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
+    float tmin = 1e-6f, tmax = 1e8f;
+    // ---- surfaces: implicit iso-surfaces (traceSurfaces :1514-1527, traceIsoRay :1408-1460)
+    int surfPrim = -1; float surfT = tmax; float3 surfNg = f3(0, 0, 0), surfBase = f3(0, 0, 0); float surfAmbient = 0.f;
+    if (P.anyIso) {
+      const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
+      const float dtScale = len3nc(vd); vd = normalize3nc(vd);
+      float already = dtScale * tmin; float rtmax = tmax;
+      for (int c = 0; c < P.numChannels; c++) { isoV[c * FRAME_THREADS] = -1e36f; isoT[c * FRAME_THREADS] = 0.f; }
+      rtmax = rtmax * dtScale;
+      Trav T; travInit(T, stack, vo, vd, already, rtmax, P.scene);
       for (;;) {
-        uint32_t bo; int K; float t0, t1;
-        if (!travNext(T, P.scene, P.volActive, already, rayTmax, blob, lane, bo, K, t0, t1)) break;
-        const bool term = integrateSegment<GRAD, STATS>(P, xfTables, blob, bo, K, o, d, t0, t1, offs, lane, pc, ws);
-        if (term || pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); break; }
-        already = t1 * 1.0000001f;
-      }
-      if (lane == 0) {
-        if (P.partialOut) P.partialOut[pixelIdx] = pc;
-        else {
-          float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
-          if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
-          P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
-          const float inv = (float)P.frameID + 1.f;
-          color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
-          P.rgba8[pixelIdx] = make_rgba8(color);
+        Segment seg;
+        if (!travNext(T, P.scene, P.isoActive, already, rtmax, seg)) break;
+        float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
+        isoSegment<STATS>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
+        if (th >= 0.f) {
+          surfPrim = -23; surfT = th / dtScale; surfNg = normalize3(hg); surfAmbient = 0.f; surfBase = f3(ipc.x, ipc.y, ipc.z);
+          break;
         }
+        already = seg.t1 * 1.0000001f;
+        rtmax = rtmax * dtScale;                          // (sic) exabrick.cu:1434
       }
+    }
+    float3 bg = f3(0, 0, 0);
+    if (surfPrim == -23) {                                // :1604-1652 with AO disabled
+      const bool shade = P.gradISO != 0;
+      if (shade && len3(surfNg) > 0.f) {
+        const float k = fabsf(dot3(d, surfNg));
+        bg = f3(surfAmbient + surfBase.x * k, surfAmbient + surfBase.y * k, surfAmbient + surfBase.z * k);
+      } else bg = surfBase;
+    }
+    // ---- DVR (:1654-1699)
+    float4 pc = make_float4(0, 0, 0, 0);
+    const float offs = rnd.next();
+    tmax = surfT;
+    if (P.clipEnabled) { float a, b; boxTest(o, d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
+    const float tHitWorld = tmax;
+    o = xfmPoint(P.xfm, o); d = xfmVector(P.xfm, d);
+    const float dtScale = len3nc(d); d = normalize3nc(d);
+    float already = dtScale * tmin;
+    const float rayTmax = tHitWorld * dtScale;
+    Trav T; travInit(T, stack, o, d, already, rayTmax, P.scene);
+    for (;;) {
+      Segment seg;
+      if (!travNext(T, P.scene, P.volActive, already, rayTmax, seg)) break;
+      integrateSegment<GRAD, STATS>(P, xfTables, seg, o, d, offs, pc, rs);
+      if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); break; }
+      already = seg.t1 * 1.0000001f;
+    }
+    if (P.partialOut) P.partialOut[pixelIdx] = pc;
+    else {
+      float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
+      if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
+      P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
+      const float inv = (float)P.frameID + 1.f;
+      color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
+      P.rgba8[pixelIdx] = make_rgba8(color);
     }
   }
   if (STATS) {
-    // per-lane counters: samples/visits/corners are per lane, segments per warp (lane 0)
-    unsigned long long a = ws.samples, b = ws.visits, c = ws.corners;
-    for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); }
-    if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], (unsigned long long)ws.segments); }
+    unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
+    for (int o2 = 16; o2 > 0; o2 >>= 1) {
+      a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); e += __shfl_xor_sync(FULL, e, o2);
+    }
+    if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], e); }
   }
 }
 
-int launchRenderFrame(const RenderParams &Pin, cudaStream_t s)
+int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 {
-  RenderParams P = Pin;
-  // per-warp shared memory: kd stack | region blob | iso state | multi-channel iso scratch
-  const int scrFloats = (P.anyIso && P.numChannels > 1) ? 32 + 33 * P.numChannels : 0;
-  P.warpUnits = P.kdStack + BLOB_UNITS + 5 + (scrFloats + 3) / 4;
-  const int tilesX = (P.width + TILE - 1) / TILE, tilesY = (P.height + TILE - 1) / TILE;
-  const size_t smemBytes = 16 * ((size_t)P.numChannels * 128 + (size_t)WARPS_PER_CTA * P.warpUnits);
-  const dim3 grid(tilesX * tilesY), block(WARPS_PER_CTA * 32);
+  const int tilesX = (P.width + TILE_W - 1) / TILE_W, tilesY = (P.height + TILE_H - 1) / TILE_H;
+  const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
+                           (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
+  const dim3 grid(tilesX * tilesY), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
 #define LAUNCH(G, S_)                                                                                   \
   { cudaFuncSetAttribute(k_renderFrame<G, S_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \
