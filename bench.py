@@ -325,6 +325,27 @@ def run_product(args):
     if world > 1:
         dist.barrier()
 
+    # ---- secondary measurement: the same frame with a translucent XF (opacity scale 0.02), which
+    # makes rays traverse the whole volume instead of terminating after a few samples ----
+    translucent = None
+    if world == 1:
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], 0.02)
+        tst = r.render_stats()
+        for _ in range(3):
+            r.render(sync=False)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(args.steps):
+            r.render(sync=False)
+        b.record(stream)
+        torch.cuda.synchronize()
+        tms_ = a.elapsed_time(b) / args.steps
+        tb = algorithmic_bytes(tst, W, H)
+        translucent = {"xf_opacity_scale": 0.02, "ms_per_frame": tms_, "samples_per_frame": tst["samples"], "segments_per_frame": tst["segments"],
+                       "samples_per_s": tst["samples"] / (tms_ * 1e-3), "algorithmic_gbs": tb / (tms_ * 1e-3) / 1e9,
+                       "frac": tb / (tms_ * 1e-3) / 1e9 / peaks()[0]}
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)
+
     # ---- reconstruction sampling (K4): 1 M random points, device resident, + host-buffer call ----
     recon = None
     if rank == 0:
@@ -386,14 +407,14 @@ def run_product(args):
                            "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
                            "parallelism": "1 GPU" if world == 1 else "sort-last kd partition x%d, NCCL binary swap" % world,
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
-                           "samples_per_frame": tot["samples"]},
+                           "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"]},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
                         "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; most are served by L1/L2"},
-                "recon": recon, "cpu_baseline": cpu}
+                "dvr_translucent": translucent, "recon": recon, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
