@@ -17,6 +17,11 @@ ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-fopenmp", "-DEXA_BUILD"]
 if os.environ.get("EXA_DEBUG"):
     COMMON = COMMON + ["-DEXA_DEBUG"]
+if os.environ.get("EXA_VARIANT"):
+    # kernel-variant build for A/B timing: EXA_VARIANT=name EXA_FLAGS="-DX=1 ..." -> libexabrick_b200.<name>.so
+    COMMON = COMMON + os.environ.get("EXA_FLAGS", "").split()
+    LIB = os.path.join(HERE, "libexabrick_b200.%s.so" % os.environ["EXA_VARIANT"])
+    OBJ = os.path.join(HERE, "build", os.environ["EXA_VARIANT"])
 SOURCES = ["host.cpp", "builder.cpp", "abr.cu", "render.cu", "capi.cu"]
 HEADERS = ["exa_internal.h", "render.cuh", "capi_render.inl", os.path.join("..", "..", "include", "exabrick_b200.h")]
 

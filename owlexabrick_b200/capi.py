@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libexabrick_b200.so")
+LIB_PATH = os.environ.get("EXA_LIB") or os.path.join(HERE, "libexabrick_b200.so")   # EXA_LIB: kernel-variant builds (tools/perf_quick.py)
 
 if not os.path.exists(LIB_PATH):
     raise ImportError("%s is missing - build it with `python -m owlexabrick_b200.build` "

@@ -53,8 +53,14 @@ __device__ __forceinline__ float comp(float3 a, int d) { return d == 0 ? a.x : d
 struct Acc { float sw, swv; float3 sd, sdc; };
 __device__ __forceinline__ void accZero(Acc &a) { a.sw = 0.f; a.swv = 0.f; a.sd = f3(0, 0, 0); a.sdc = f3(0, 0, 0); }
 
-// addBasisFunctions (exabrick.cu:620-777) for k staged brick headers; `chan` = base of the
-// channel's flattened scalars.  Invalid corners contribute weight 0 (== being skipped).
+// addBasisFunctions (exabrick.cu:620-777) for k brick headers; `chan` = base of the channel's
+// flattened scalars.  A corner is valid iff it is valid on each axis, so its tent weight
+// (wz*wy)*wx factorises into per-axis weights that are zeroed on the invalid side: the eight
+// corner terms of the reference collapse into three nested lerps (x, then y, then z), the
+// weight sum into a product of three per-axis sums, and the derivative terms
+//   sumDC.x = sum_valid (wz*wy)*sx      sumD.x = sum_valid (wz*wy)*sx*s      (sx = -1 low, +1 high)
+// into differences of the same partial sums.  Same real-number result as the reference's
+// corner loop, different fp32 rounding order (gate: 1e-5 relative).
 template <bool GRAD, bool STATS>
 __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hdrs, int k, const float *__restrict__ chan,
                                             float px, float py, float pz, unsigned &nCorners)
@@ -68,39 +74,39 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
     const float lz = (pz - __uint_as_float(u0.z)) * invCw - 0.5f;
     const int ix0 = max(-1, (int)floorf(lx)), iy0 = max(-1, (int)floorf(ly)), iz0 = max(-1, (int)floorf(lz));
     const float fx = lx - (float)ix0, fy = ly - (float)iy0, fz = lz - (float)iz0;
-    const float gx = 1.f - fx, gy = 1.f - fy, gz = 1.f - fz;
     const bool x0 = ix0 >= 0 && ix0 < sx, x1 = ix0 + 1 < sx;
     const bool y0 = iy0 >= 0 && iy0 < sy, y1 = iy0 + 1 < sy;
     const bool z0 = iz0 >= 0 && iz0 < sz, z1 = iz0 + 1 < sz;
-    const float *base = chan + u1.w + ix0 + iy0 * sx + iz0 * (sx * sy);
     const int dy = sx, dz = sx * sy;
-    const bool v000 = z0 && y0 && x0, v001 = z0 && y0 && x1, v010 = z0 && y1 && x0, v011 = z0 && y1 && x1;
-    const bool v100 = z1 && y0 && x0, v101 = z1 && y0 && x1, v110 = z1 && y1 && x0, v111 = z1 && y1 && x1;
-    const float s000 = v000 ? __ldg(base) : 0.f;
-    const float s001 = v001 ? __ldg(base + 1) : 0.f;
-    const float s010 = v010 ? __ldg(base + dy) : 0.f;
-    const float s011 = v011 ? __ldg(base + dy + 1) : 0.f;
-    const float s100 = v100 ? __ldg(base + dz) : 0.f;
-    const float s101 = v101 ? __ldg(base + dz + 1) : 0.f;
-    const float s110 = v110 ? __ldg(base + dz + dy) : 0.f;
-    const float s111 = v111 ? __ldg(base + dz + dy + 1) : 0.f;
-    if (STATS) nCorners += v000 + v001 + v010 + v011 + v100 + v101 + v110 + v111;
-    const float zy00 = gz * gy, zy01 = gz * fy, zy10 = fz * gy, zy11 = fz * fy;
-#define EXA_CORNER(V, S, WZY, WX, WZ, WY, SXN, SYN, SZN)                                          \
-    { const float w = (V) ? (WZY) * (WX) : 0.f; a.sw += w; a.swv += w * (S);                     \
-      if (GRAD) { const float ddx = (V) ? (WZY) * (SXN) : 0.f, ddy = (V) ? ((WZ) * (WX)) * (SYN) : 0.f, \
-                  ddz = (V) ? ((WY) * (WX)) * (SZN) : 0.f;                                       \
-        a.sdc.x += ddx; a.sdc.y += ddy; a.sdc.z += ddz;                                          \
-        a.sd.x += ddx * (S); a.sd.y += ddy * (S); a.sd.z += ddz * (S); } }
-    EXA_CORNER(v000, s000, zy00, gx, gz, gy, -1.f, -1.f, -1.f)
-    EXA_CORNER(v001, s001, zy00, fx, gz, gy, +1.f, -1.f, -1.f)
-    EXA_CORNER(v010, s010, zy01, gx, gz, fy, -1.f, +1.f, -1.f)
-    EXA_CORNER(v011, s011, zy01, fx, gz, fy, +1.f, +1.f, -1.f)
-    EXA_CORNER(v100, s100, zy10, gx, fz, gy, -1.f, -1.f, +1.f)
-    EXA_CORNER(v101, s101, zy10, fx, fz, gy, +1.f, -1.f, +1.f)
-    EXA_CORNER(v110, s110, zy11, gx, fz, fy, -1.f, +1.f, +1.f)
-    EXA_CORNER(v111, s111, zy11, fx, fz, fy, +1.f, +1.f, +1.f)
-#undef EXA_CORNER
+    const float *base = chan + u1.w + ix0 + iy0 * dy + iz0 * dz;
+    const bool r00 = z0 && y0, r01 = z0 && y1, r10 = z1 && y0, r11 = z1 && y1;    // (z,y) rows
+    const float s000 = (r00 && x0) ? __ldg(base) : 0.f;
+    const float s001 = (r00 && x1) ? __ldg(base + 1) : 0.f;
+    const float s010 = (r01 && x0) ? __ldg(base + dy) : 0.f;
+    const float s011 = (r01 && x1) ? __ldg(base + dy + 1) : 0.f;
+    const float s100 = (r10 && x0) ? __ldg(base + dz) : 0.f;
+    const float s101 = (r10 && x1) ? __ldg(base + dz + 1) : 0.f;
+    const float s110 = (r11 && x0) ? __ldg(base + dz + dy) : 0.f;
+    const float s111 = (r11 && x1) ? __ldg(base + dz + dy + 1) : 0.f;
+    if (STATS) nCorners += ((int)z0 + (int)z1) * ((int)y0 + (int)y1) * ((int)x0 + (int)x1);
+    const float wx0 = x0 ? 1.f - fx : 0.f, wx1 = x1 ? fx : 0.f;
+    const float wy0 = y0 ? 1.f - fy : 0.f, wy1 = y1 ? fy : 0.f;
+    const float wz0 = z0 ? 1.f - fz : 0.f, wz1 = z1 ? fz : 0.f;
+    const float X00 = wx0 * s000 + wx1 * s001, X01 = wx0 * s010 + wx1 * s011;
+    const float X10 = wx0 * s100 + wx1 * s101, X11 = wx0 * s110 + wx1 * s111;
+    const float Y0 = wy0 * X00 + wy1 * X01, Y1 = wy0 * X10 + wy1 * X11;
+    const float wsx = wx0 + wx1, wsy = wy0 + wy1, wsz = wz0 + wz1;
+    a.swv += wz0 * Y0 + wz1 * Y1;
+    a.sw += (wsz * wsy) * wsx;
+    if (GRAD) {
+      const float D00 = s001 - s000, D01 = s011 - s010, D10 = s101 - s100, D11 = s111 - s110;
+      a.sd.x += wz0 * (wy0 * D00 + wy1 * D01) + wz1 * (wy0 * D10 + wy1 * D11);
+      a.sd.y += wz0 * (X01 - X00) + wz1 * (X11 - X10);
+      a.sd.z += Y1 - Y0;
+      a.sdc.x += (wsz * wsy) * ((x1 ? 1.f : 0.f) - (x0 ? 1.f : 0.f));
+      a.sdc.y += (wsz * wsx) * ((y1 ? 1.f : 0.f) - (y0 ? 1.f : 0.f));
+      a.sdc.z += (wsy * wsx) * ((z1 ? 1.f : 0.f) - (z0 ? 1.f : 0.f));
+    }
   }
 }
 
@@ -129,6 +135,17 @@ __device__ __forceinline__ float4 lookupXF(const float4 *__restrict__ table, flo
   float4 r = make_float4(a.x + w * (b.x - a.x), a.y + w * (b.y - a.y), a.z + w * (b.z - a.z), a.w + w * (b.w - a.w));
   r.w *= opacityScale;
   return r;
+}
+// Same lookup for the per-sample hot loop: `k127` = 127 / ((hi - lo) + 1e-20) is hoisted per
+// channel, so the two IEEE divisions become multiplications (<= 2 ulp on the table coordinate).
+__device__ __forceinline__ float4 lookupXFfast(const float4 *__restrict__ table, float lo, float k127, float opacityScale, float in)
+{
+  const float sc = fminf(fmaxf((in - lo) * k127 + .5f, 0.f), 127.f);
+  const float x = sc * (128.f / 127.f) - 0.5f;
+  const float fl = floorf(x), w = x - fl;
+  const int i0 = max(0, (int)fl), i1 = min(127, (int)fl + 1);
+  const float4 a = table[i0], b = table[i1];
+  return make_float4(a.x + w * (b.x - a.x), a.y + w * (b.y - a.y), a.z + w * (b.z - a.z), (a.w + w * (b.w - a.w)) * opacityScale);
 }
 
 // boxTest (exabrick.cu:197-210)
@@ -272,7 +289,7 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
 // integrateBrick<GRADIENT_SHADING> + integrateVolume (exabrick.cu:1116-1185, 988-1016), as written.
 // Returns true if the ray terminated (alpha >= threshold).
 template <bool GRAD, bool STATS>
-__device__ __forceinline__ bool integrateSegment(const RenderParams &P, const float4 *xfTables, const Segment &seg,
+__device__ __forceinline__ bool integrateSegment(const RenderParams &P, const float4 *xfTables, const float *xfK, const Segment &seg,
                                                  float3 o, float3 d, float offs, float4 &pc, RayStats &rs)
 {
   const float dt = P.dt * seg.fcw;
@@ -292,13 +309,18 @@ __device__ __forceinline__ bool integrateSegment(const RenderParams &P, const fl
     for (int c = 0; c < P.numChannels; c++) {
       float v = 0.f; float3 g = f3(0, 0, 0);
       if (sampleRegion<GRAD, STATS>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
-        float4 s = lookupXF(xfTables + c * 128, P.xfDomain[c][0], P.xfDomain[c][1], P.xfOpacityScale, v);
-        if (GRAD && len3(g) > (float)(int)seg.fcw * 1e-6f) {
-          const float3 l = f3(-d.x, -d.y, -d.z);
-          const float scale = fabsf(dot3(l, g)) / sqrtf(dot3(g, g) * dot3(l, l));
-          s.x *= scale; s.y *= scale; s.z *= scale;
+        float4 s = lookupXFfast(xfTables + c * 128, P.xfDomain[c][0], xfK[c], P.xfOpacityScale, v);
+        if (GRAD) {
+          const float gg = dot3(g, g), thr = (float)(int)seg.fcw * 1e-6f;
+          if (gg > thr * thr) {                               // length(g) > fcw*1e-6 (:1004)
+            const float3 l = f3(-d.x, -d.y, -d.z);
+            const float scale = fabsf(dot3(l, g)) * rsqrtf(gg * dot3(l, l));
+            s.x *= scale; s.y *= scale; s.z *= scale;
+          }
         }
-        s.w = 1.f - powf(1.f - s.w, actual_dt);
+        // opacity correction 1 - (1-a)^dt (:1011); the reference's device build is
+        // --use_fast_math, i.e. exactly this exp2(dt*log2(1-a)) form
+        s.w = 1.f - __powf(1.f - s.w, actual_dt);
 #ifdef EXA_DEBUG
         if (P.dbg) printf("G   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", t_sample, actual_dt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
 #endif
@@ -400,18 +422,23 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 // -----------------------------------------------------------------------------------------
 // __raygen__renderFrame (exabrick.cu:1576-1720): one thread per pixel, 8x4 pixel tile per warp
 // -----------------------------------------------------------------------------------------
+#ifndef EXA_FRAME_MINBLOCKS
+#define EXA_FRAME_MINBLOCKS 5
+#endif
 static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
 template <bool GRAD, bool STATS>
-__global__ void __launch_bounds__(FRAME_THREADS, 5) k_renderFrame(const __grid_constant__ RenderParams P)
+__global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
   // layout: [xf tables: numChannels*128 float4][kd stacks: kdStack x 128 uint2][iso state: 2 x numChannels x 128 float]
   float4 *xfTables = reinterpret_cast<float4 *>(smem);
   uint2 *stackBase = reinterpret_cast<uint2 *>(smem + P.numChannels * 128);
   float *isoBase = reinterpret_cast<float *>(stackBase + (size_t)P.kdStack * FRAME_THREADS);
+  __shared__ float xfK[EXA_MAX_CHANNELS];      // 127 / ((hi - lo) + 1e-20) per channel (lookupXFfast)
   for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
+  if (threadIdx.x < P.numChannels) xfK[threadIdx.x] = 127.f / ((P.xfDomain[threadIdx.x][1] - P.xfDomain[threadIdx.x][0]) + 1e-20f);
   __syncthreads();
 
   const int tilesX = (P.width + TILE_W - 1) / TILE_W;
@@ -483,7 +510,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, 5) k_renderFrame(const __grid_c
     for (;;) {
       Segment seg;
       if (!travNext(T, P.scene, P.volActive, already, rayTmax, seg)) break;
-      integrateSegment<GRAD, STATS>(P, xfTables, seg, o, d, offs, pc, rs);
+      integrateSegment<GRAD, STATS>(P, xfTables, xfK, seg, o, d, offs, pc, rs);
       if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); break; }
       already = seg.t1 * 1.0000001f;
     }

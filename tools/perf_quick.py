@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Quick A/B timing of the hot kernels on the C2 scene (GPU box only; not the bench).
+
+    python tools/perf_quick.py [--workload c2] [--tag name]
+    EXA_LIB=owlexabrick_b200/libexabrick_b200.<variant>.so python tools/perf_quick.py --tag <variant>
+
+The scene (bricks + field) is cached under /dev/shm so that several variants can be timed in one
+gpurun call.  Prints one JSON line: opaque / translucent frame ms, 1 M point sampling us.
+"""
+import argparse, json, os, sys, time
+import numpy as np
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="c2")
+    ap.add_argument("--tag", default="base")
+    ap.add_argument("--steps", type=int, default=10)
+    a = ap.parse_args()
+    import torch
+    import bench
+    from owlexabrick_b200 import capi, renderer as R, synth
+    domain, boxes, image = bench.WORKLOADS[a.workload]
+    cache = "/dev/shm/exa_pq_%s" % a.workload
+    if os.path.exists(cache + ".bricks"):
+        bricks = R.ExaBricks.load(cache + ".bricks"); field = np.fromfile(cache + ".scalars", np.float32)
+    else:
+        cells, field, _, _ = bench.make_workload(a.workload)
+        bricks = R.ExaBricks.build(cells); del cells
+        bricks.save(cache + ".bricks"); field.tofile(cache + ".scalars")
+    r = R.Renderer(bricks, [field]); torch.cuda.synchronize()
+    stream = torch.cuda.current_stream(); r.set_stream(stream.cuda_stream)
+    W, H = image
+    fd = bench.frame_desc(R, domain, image, (float(field.min()), float(field.max()))); fd.apply(r)
+    alpha, rgb = fd.xf[0]
+    out = {"tag": a.tag, "lib": os.path.basename(capi.LIB_PATH)}
+
+    def time_frames(n):
+        for _ in range(3): r.render(sync=False)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(n): r.render(sync=False)
+        e1.record(stream); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / n
+    for name, scale in (("opaque", 1.0), ("translucent", 0.02)):
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
+        st = r.render_stats()
+        ms = time_frames(a.steps)
+        out[name] = {"ms": round(ms, 4), "Gsamples_s": round(st["samples"] / ms / 1e6, 3), "alg_GBs": round(bench.algorithmic_bytes(st, W, H) / ms / 1e6, 1)}
+    for gs in (False, True):
+        r.setGradientShadingDVR(gs)
+    r.setGradientShadingDVR(False); out["translucent_nograd_ms"] = round(time_frames(a.steps), 4); r.setGradientShadingDVR(True)
+    npts = 1 << 20
+    pts = synth.random_points(npts, [0] * 3, [domain] * 3, seed=1)
+    d_pts = torch.from_numpy(pts).cuda(); d_val = torch.empty(npts, dtype=torch.float32, device="cuda"); d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
+    ts = []
+    for i in range(8):
+        flush.fill_(i)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream); r.sample_points_device(d_pts.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr()); e1.record(stream)
+        torch.cuda.synchronize()
+        if i >= 3: ts.append(e0.elapsed_time(e1))
+    pb = 16 * npts + 44 * pst["segments"] + 36 * pst["brickVisits"] + 4 * pst["cornerLoads"]
+    out["points"] = {"us": round(1e3 * float(np.mean(ts)), 2), "alg_GBs": round(pb / np.mean(ts) / 1e6, 1), "visits_per_pt": round(pst["brickVisits"] / npts, 3), "corners_per_pt": round(pst["cornerLoads"] / npts, 3)}
+    out["checksum"] = float(d_val.double().sum().item())
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()
