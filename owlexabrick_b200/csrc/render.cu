@@ -286,50 +286,36 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
   return accFinish<GRAD>(a, value, g);
 }
 
-// integrateBrick<GRADIENT_SHADING> + integrateVolume (exabrick.cu:1116-1185, 988-1016), as written.
-// Returns true if the ray terminated (alpha >= threshold).
+// One lattice sample of integrateBrick<GRADIENT_SHADING> + integrateVolume (exabrick.cu:1116-1185,
+// 988-1016), as written: t_next = min(t_i, t1), sample at the midpoint of [t_last, t_next] with the
+// actual segment length in the opacity correction.  The caller owns the loop (k_renderFrame runs
+// it as a flat per-lane state machine so that the lanes of a warp stay converged).
 template <bool GRAD, bool STATS>
-__device__ __forceinline__ bool integrateSegment(const RenderParams &P, const float4 *xfTables, const float *xfK, const Segment &seg,
-                                                 float3 o, float3 d, float offs, float4 &pc, RayStats &rs)
+__device__ __forceinline__ void integrateSample(const RenderParams &P, const float4 *xfTables, const float *xfK, const Segment &seg,
+                                                float3 o, float3 d, float t_sample, float actual_dt, float4 &pc, RayStats &rs)
 {
-  const float dt = P.dt * seg.fcw;
-  const float t0 = seg.t0, t1 = seg.t1;
-  float t_i = firstLatticeT(t0, dt, offs);
-  float t_last = t0;
-  if (STATS) rs.segments++;
-#ifdef EXA_DEBUG
-  if (P.dbg) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)P.scene.blobs[seg.blobOfs + 2].x, seg.K, t0, t1, dt, t_i);
-#endif
-  for (;; t_i += dt) {
-    const float t_next = fminf(t_i, t1);
-    const float t_sample = 0.5f * (t_next + t_last);
-    const float actual_dt = t_next - t_last;
-    t_last = t_next;
-    const float3 pos = rayAt(o, d, t_sample);
-    for (int c = 0; c < P.numChannels; c++) {
-      float v = 0.f; float3 g = f3(0, 0, 0);
-      if (sampleRegion<GRAD, STATS>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
-        float4 s = lookupXFfast(xfTables + c * 128, P.xfDomain[c][0], xfK[c], P.xfOpacityScale, v);
-        if (GRAD) {
-          const float gg = dot3(g, g), thr = (float)(int)seg.fcw * 1e-6f;
-          if (gg > thr * thr) {                               // length(g) > fcw*1e-6 (:1004)
-            const float3 l = f3(-d.x, -d.y, -d.z);
-            const float scale = fabsf(dot3(l, g)) * rsqrtf(gg * dot3(l, l));
-            s.x *= scale; s.y *= scale; s.z *= scale;
-          }
+  const float3 pos = rayAt(o, d, t_sample);
+  for (int c = 0; c < P.numChannels; c++) {
+    float v = 0.f; float3 g = f3(0, 0, 0);
+    if (sampleRegion<GRAD, STATS>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
+      float4 s = lookupXFfast(xfTables + c * 128, P.xfDomain[c][0], xfK[c], P.xfOpacityScale, v);
+      if (GRAD) {
+        const float gg = dot3(g, g), thr = (float)(int)seg.fcw * 1e-6f;
+        if (gg > thr * thr) {                               // length(g) > fcw*1e-6 (:1004)
+          const float3 l = f3(-d.x, -d.y, -d.z);
+          const float scale = fabsf(dot3(l, g)) * rsqrtf(gg * dot3(l, l));
+          s.x *= scale; s.y *= scale; s.z *= scale;
         }
-        // opacity correction 1 - (1-a)^dt (:1011); the reference's device build is
-        // --use_fast_math, i.e. exactly this exp2(dt*log2(1-a)) form
-        s.w = 1.f - __powf(1.f - s.w, actual_dt);
-#ifdef EXA_DEBUG
-        if (P.dbg) printf("G   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", t_sample, actual_dt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
-#endif
-        const float k = (1.f - pc.w) * s.w;
-        pc.x += k * s.x; pc.y += k * s.y; pc.z += k * s.z; pc.w += k;
       }
+      // opacity correction 1 - (1-a)^dt (:1011); the reference's device build is
+      // --use_fast_math, i.e. exactly this exp2(dt*log2(1-a)) form
+      s.w = 1.f - __powf(1.f - s.w, actual_dt);
+#ifdef EXA_DEBUG
+      if (P.dbg) printf("G   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g) rgba=(%.6g %.6g %.6g %.6g)\n", t_sample, actual_dt, v, g.x, g.y, g.z, s.x, s.y, s.z, s.w);
+#endif
+      const float k = (1.f - pc.w) * s.w;
+      pc.x += k * s.x; pc.y += k * s.y; pc.z += k * s.z; pc.w += k;
     }
-    if (pc.w >= P.ertThreshold) return true;
-    if (t_next >= t1) return false;
   }
 }
 
@@ -453,16 +439,22 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #ifdef EXA_DEBUG
   if (P.dbg && (px + P.width * py) != P.dbg - 1) inside = false;
 #endif
+  // per-lane DVR state; the integration loop below is shared by all 32 lanes of the warp
+  const int pixelIdx = px + P.width * py;
+  bool live = false;                                         // lane still has volume to integrate
+  float3 o = f3(0, 0, 0), d = f3(0, 0, 1), bg = f3(0, 0, 0);
+  float4 pc = make_float4(0, 0, 0, 0);
+  float offs = 0.f, already = 0.f, rayTmax = 0.f;
+  Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.o = o; T.d = d;
   if (inside) {
     uint2 *stack = stackBase + threadIdx.x;
     float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
-    const int pixelIdx = px + P.width * py;
     LCG16 rnd((uint32_t)(P.frameID * P.width * P.height) + (uint32_t)px, (uint32_t)py);
     const float jx = rnd.next(), jy = rnd.next();
     const float sx = (float)px + jx, sy = (float)py + jy;
     // Camera::generateRay (programs/Camera.h:27-44)
-    float3 o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
-    float3 d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
+    o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
+    d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
                                __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
                                __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
     float tmin = 1e-6f, tmax = 1e8f;
@@ -488,7 +480,6 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         rtmax = rtmax * dtScale;                          // (sic) exabrick.cu:1434
       }
     }
-    float3 bg = f3(0, 0, 0);
     if (surfPrim == -23) {                                // :1604-1652 with AO disabled
       const bool shade = P.gradISO != 0;
       if (shade && len3(surfNg) > 0.f) {
@@ -496,24 +487,52 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         bg = f3(surfAmbient + surfBase.x * k, surfAmbient + surfBase.y * k, surfAmbient + surfBase.z * k);
       } else bg = surfBase;
     }
-    // ---- DVR (:1654-1699)
-    float4 pc = make_float4(0, 0, 0, 0);
-    const float offs = rnd.next();
+    // ---- DVR set-up (:1654-1674)
+    offs = rnd.next();
     tmax = surfT;
     if (P.clipEnabled) { float a, b; boxTest(o, d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
     const float tHitWorld = tmax;
     o = xfmPoint(P.xfm, o); d = xfmVector(P.xfm, d);
     const float dtScale = len3nc(d); d = normalize3nc(d);
-    float already = dtScale * tmin;
-    const float rayTmax = tHitWorld * dtScale;
-    Trav T; travInit(T, stack, o, d, already, rayTmax, P.scene);
+    already = dtScale * tmin;
+    rayTmax = tHitWorld * dtScale;
+    travInit(T, stack, o, d, already, rayTmax, P.scene);
+    live = true;
+  }
+  // ---- DVR region loop (:1675-1699) + integrateBrick's sample loop (:1141-1184), flattened into
+  // one per-lane state machine: each trip, lanes without a current region segment advance the kd
+  // traversal to their next one, then every live lane takes exactly ONE lattice sample.  With the
+  // nested loops as written, a warp pays sum-over-segments of the longest lane; flat, it pays the
+  // longest lane's total.  __all_sync at the head keeps the warp converged.  Arithmetic and
+  // per-ray order of operations are unchanged.
+  {
+    bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;
+    float dtS = 0.f, t_i = 0.f, t_last = 0.f;
     for (;;) {
-      Segment seg;
-      if (!travNext(T, P.scene, P.volActive, already, rayTmax, seg)) break;
-      integrateSegment<GRAD, STATS>(P, xfTables, xfK, seg, o, d, offs, pc, rs);
-      if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); break; }
-      already = seg.t1 * 1.0000001f;
+      if (__all_sync(FULL, !live)) break;
+      if (live && !haveSeg) {
+        if (!travNext(T, P.scene, P.volActive, already, rayTmax, seg)) live = false;
+        else {
+          dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0; haveSeg = true;
+          if (STATS) rs.segments++;
+#ifdef EXA_DEBUG
+          if (P.dbg) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)P.scene.blobs[seg.blobOfs + 2].x, seg.K, seg.t0, seg.t1, dtS, t_i);
+#endif
+        }
+      }
+      if (live) {
+        const float t_next = fminf(t_i, seg.t1);
+        const float t_sample = 0.5f * (t_next + t_last);
+        const float actual_dt = t_next - t_last;
+        t_last = t_next;
+        integrateSample<GRAD, STATS>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
+        if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
+        else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                             // :1698
+        else t_i += dtS;
+      }
     }
+  }
+  if (inside) {
     if (P.partialOut) P.partialOut[pixelIdx] = pc;
     else {
       float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
