@@ -195,6 +195,15 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields,
                         const size_t *fieldCounts, int numFields, int cudaDevice,
                         exa_renderer_t **out);
 void exa_renderer_destroy(exa_renderer_t *r);
+/* Device layout of the scalars the sampling kernels read (new; the reference has only FLAT,
+ * exa/OptixRenderer.cpp:103-132).  DUAL = one 32-byte record of the 8 corner scalars per dual
+ * cell: 8x the memory, one DRAM sector per brick visit.  AUTO (default) = DUAL when the records
+ * fit in 40% of the free device memory, else FLAT.  Applies to renderers created afterwards;
+ * the environment variable EXA_SCALAR_LAYOUT=0|1|2 overrides it.  Results are identical. */
+enum { EXA_LAYOUT_AUTO = 0, EXA_LAYOUT_FLAT = 1, EXA_LAYOUT_DUAL = 2 };
+int exa_set_scalar_layout(int mode);
+/* layout in use (EXA_LAYOUT_FLAT or EXA_LAYOUT_DUAL) and the bytes of scalar data the kernels read from */
+int exa_renderer_get_scalar_layout(const exa_renderer_t *r, int *layout, uint64_t *bytes);
 /* use an externally owned cudaStream_t for all launches (NULL = default stream) */
 int exa_renderer_set_stream(exa_renderer_t *r, void *cudaStream);
 

@@ -17,6 +17,7 @@ lib = C.CDLL(LIB_PATH)
 EXA_OK, EXA_ERR_INVALID, EXA_ERR_IO, EXA_ERR_CUDA, EXA_ERR_LIMIT = range(5)
 BUILDER_SPATIAL_MEDIAN, BUILDER_SAH_ALIKE = 0, 1
 PARTITION_NONE, PARTITION_SORT_LAST, PARTITION_IMAGE_TILES = 0, 1, 2
+LAYOUT_AUTO, LAYOUT_FLAT, LAYOUT_DUAL = 0, 1, 2
 
 
 class ExaError(RuntimeError):
@@ -45,6 +46,8 @@ _SIG = {
     "exa_last_error": (C.c_char_p, []),
     "exa_cuda_available": (i32, []),
     "exa_free": (None, [vp]),
+    "exa_set_scalar_layout": (i32, [i32]),
+    "exa_renderer_get_scalar_layout": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
     "exa_bricks_build": (i32, [vp, sz, i32, i32, C.POINTER(vp)]),
     "exa_bricks_load": (i32, [C.c_char_p, C.POINTER(vp)]),
     "exa_bricks_from_memory": (i32, [vp, sz, C.POINTER(vp)]),

@@ -240,7 +240,7 @@ __device__ __forceinline__ float decF(unsigned a) { a ^= (a >> 31) ? 0x80000000u
 // per kd node that is a leaf: write region record, leaf list, blob; renumber the node
 __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, const int *offLeaf, const int *offList,
                            const Box3 *leafDom, const int *leafPoolBegin, const int *leafCount, const int *pool,
-                           const ExaBrick *bricks, ExaBrickRegion *regions, int *leafList, int *entryRegion,
+                           const ExaBrick *bricks, const uint32_t *dualBegin, ExaBrickRegion *regions, int *leafList, int *entryRegion,
                            unsigned *rangeEnc, uint4 *blobs)
 {
   int g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -258,7 +258,7 @@ __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, cons
     const ExaBrick b = bricks[bid];
     finest = min(finest, b.level);
     BrickHdr h; h.lx = (float)b.lower[0]; h.ly = (float)b.lower[1]; h.lz = (float)b.lower[2];
-    h.invCw = 1.f / (float)(1 << b.level); h.sx = b.size[0]; h.sy = b.size[1]; h.sz = b.size[2]; h.begin = b.begin;
+    h.invCw = 1.f / (float)(1 << b.level); h.sx = b.size[0]; h.sy = b.size[1]; h.sz = b.size[2]; h.begin = dualBegin ? dualBegin[bid] : b.begin;
     const uint4 *hp = reinterpret_cast<const uint4 *>(&h);
     blobs[blobOfs + 3 + 2 * k] = hp[0]; blobs[blobOfs + 3 + 2 * k + 1] = hp[1];
   }
@@ -346,7 +346,7 @@ void abrFree(AbrResult &r)
 }
 
 int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t numCells,
-             int numFields, void *streamV, AbrResult &out)
+             int numFields, const uint32_t *d_dualBegin, void *streamV, AbrResult &out)
 {
   cudaStream_t s = (cudaStream_t)streamV;
   out = AbrResult();
@@ -457,7 +457,7 @@ int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t 
   CK(cudaMalloc(&entryRegion, 4 * (size_t)std::max(L, 1))); CK(cudaMalloc(&rangeEnc, 8 * (size_t)std::max(nr, 1)));
   CK(cudaMalloc(&blobs, 16 * std::max(blobUnits, (size_t)1)));
   k_finalize<<<blocks(numNodes), 256, 0, s>>>(numNodes, kd.p, leafOfNode.p, offLeaf, offList, leafDom.p, leafPoolBegin.p, leafCount.p, pool.p,
-                                               d_bricks, regions, leafList, entryRegion, rangeEnc, blobs); launches++;
+                                               d_bricks, d_dualBegin, regions, leafList, entryRegion, rangeEnc, blobs); launches++;
   if (L > 0) { k_valueRange<<<L, 256, 0, s>>>(L, leafList, entryRegion, d_bricks, regions, d_scalars, (unsigned long long)numCells, numFields, rangeEnc); launches++; }
   if (nr > 0) { k_rangeDecode<<<blocks(nr), 256, 0, s>>>(nr, rangeEnc, regions, blobs); launches++; }
   CK(cudaStreamSynchronize(s));

@@ -22,6 +22,8 @@ struct exa_renderer {
   ExaBrick *d_bricks = nullptr; int numBricks = 0;
   float *d_scalars = nullptr; uint64_t numCells = 0; int numFields = 0;
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
+  int32_t *d_locGrid = nullptr; int locG = 0; float locScale[3] = {0, 0, 0};              // point-location grid
+  float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
   float voxelLo[3], voxelHi[3], worldLo[3], worldHi[3];
@@ -54,6 +56,8 @@ static int cudaUsable()
   return n;
 }
 
+static int g_scalarLayout = EXA_LAYOUT_AUTO;
+
 static void identityXfm(float m[12]) { memset(m, 0, 48); m[0] = m[4] = m[8] = 1.f; }
 
 static void fillParams(exa_renderer *r, RenderParams &P)
@@ -62,6 +66,8 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   DeviceScene &S = P.scene;
   S.bricks = r->d_bricks; S.numBricks = r->numBricks; S.scalars = r->d_scalars; S.numCells = r->numCells; S.numFields = r->numFields;
   S.regions = r->abr.regions; S.numRegions = r->abr.numRegions; S.leafList = r->abr.leafList; S.leafListLen = r->abr.leafListLen;
+  S.dual = r->d_dual; S.dualRecords = r->dualRecords;
+  S.locGrid = r->d_locGrid; S.locG = r->locG; for (int d = 0; d < 3; d++) S.locScale[d] = r->locScale[d];
   S.kd = r->abr.kd; S.numKdNodes = r->abr.numKdNodes; S.kdDepth = r->abr.depth; S.blobs = r->abr.blobs;
   for (int d = 0; d < 3; d++) { S.boundsLo[d] = r->abr.boundsLo[d]; S.boundsHi[d] = r->abr.boundsHi[d]; }
   memcpy(P.camPos, r->fs.camera.pos, 12); memcpy(P.dir00, r->fs.camera.dir00, 12);
@@ -151,6 +157,7 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   const int ndev = cudaUsable(); if (!ndev) return EXA_ERR_CUDA;
   if (cudaDevice < 0 || cudaDevice >= ndev) { setError("exa_renderer_create: bad device index"); return EXA_ERR_INVALID; }
   CKR(cudaSetDevice(cudaDevice));
+  if (const char *e = getenv("EXA_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob: 32/64/128
   exa_renderer *r = new exa_renderer;
   r->device = cudaDevice;
   memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
@@ -194,11 +201,52 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
     CKC(cudaMemcpy(r->d_scalarOffsets, offs.data(), 4 * numFields, cudaMemcpyHostToDevice));
     CKC(cudaMemcpy(r->d_primaryChannels, prim.data(), 4 * numFields, cudaMemcpyHostToDevice));
   }
+  // ---- dual-cell records (8x the scalar memory, one DRAM sector per brick visit) ----
+  {
+    int mode = g_scalarLayout;
+    if (const char *e = getenv("EXA_SCALAR_LAYOUT")) mode = atoi(e);
+    const ExaBrick *hb = exa_bricks_headers(bricks);
+    std::vector<uint32_t> begin(nb); uint64_t total = 0; bool fits32 = true;
+    for (size_t i = 0; i < nb; i++) {
+      if (total > 0xffffffffull) { fits32 = false; break; }
+      begin[i] = (uint32_t)total;
+      total += (uint64_t)(hb[i].size[0] + 1) * (uint64_t)(hb[i].size[1] + 1) * (uint64_t)(hb[i].size[2] + 1);
+    }
+    size_t freeB = 0, totalB = 0; CKC(cudaMemGetInfo(&freeB, &totalB));
+    const uint64_t need = total * 32ull * (uint64_t)numFields;
+    // auto: build the records when they fit in 40% of the free HBM and 32-bit record offsets
+    const bool want = mode == EXA_LAYOUT_DUAL || (mode == EXA_LAYOUT_AUTO && need <= (uint64_t)(0.4 * (double)freeB));
+    if (want && fits32 && total <= 0xffffffffull && need + (64ull << 20) < freeB) {
+      CKC(cudaMalloc(&r->d_dualBegin, nb * 4));
+      CKC(cudaMemcpyAsync(r->d_dualBegin, begin.data(), nb * 4, cudaMemcpyHostToDevice, s));
+      CKC(cudaMalloc(&r->d_dual, need));
+      r->dualRecords = total;
+      for (int f = 0; f < numFields; f++) {
+        if (launchExpandDual(r->d_bricks, r->numBricks, r->d_dualBegin, total, r->d_scalars + (size_t)f * nc, r->d_dual + 2 * (size_t)f * total, s) < 0) {
+          setError("dual-record expansion failed"); exa_renderer_destroy(r); return EXA_ERR_CUDA; }
+        r->launches++;
+      }
+      CKC(cudaStreamSynchronize(s));
+    } else if (mode == EXA_LAYOUT_DUAL) {
+      setError("EXA_LAYOUT_DUAL requested but the dual-cell records do not fit (memory or 32-bit record offsets)");
+      exa_renderer_destroy(r); return EXA_ERR_LIMIT;
+    }
+  }
   // ---- ABR build on the GPU (exa/Regions.cpp:242-320) ----
-  rc = abrBuild(r->d_bricks, r->numBricks, r->d_scalars, r->numCells, numFields, s, r->abr);
+  rc = abrBuild(r->d_bricks, r->numBricks, r->d_scalars, r->numCells, numFields, r->d_dualBegin, s, r->abr);
   if (rc) { exa_renderer_destroy(r); return rc; }
   r->launches += r->abr.launches;
   if (r->abr.depth + 2 > 160) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
+  {
+    // point-location grid: ~8 cells per region, 16^3 .. 128^3
+    int G = 16; while (G < 128 && (double)G * G * G < 8.0 * r->abr.numRegions) G *= 2;
+    if (!getenv("EXA_NO_LOCGRID")) {
+      CKC(cudaMalloc(&r->d_locGrid, sizeof(int32_t) * (size_t)G * G * G));
+      if (launchBuildLocGrid(r->abr.kd, G, r->abr.boundsLo, r->abr.boundsHi, r->d_locGrid, r->locScale, s) < 0) {
+        setError("point-location grid kernel failed"); exa_renderer_destroy(r); return EXA_ERR_CUDA; }
+      r->locG = G; r->launches++;
+    }
+  }
   r->h_kd.resize(r->abr.numKdNodes);
   CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);
@@ -223,12 +271,26 @@ void exa_renderer_destroy(exa_renderer_t *r)
 {
   if (!r) return;
   cudaSetDevice(r->device);
+  cudaFree(r->d_dual); cudaFree(r->d_dualBegin); cudaFree(r->d_locGrid);
   cudaFree(r->d_bricks); cudaFree(r->d_scalars); cudaFree(r->d_scalarOffsets); cudaFree(r->d_primaryChannels);
   abrFree(r->abr);
   cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
   cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
   cudaFree(r->d_traces); cudaFree(r->d_stats);
   delete r;
+}
+
+int exa_set_scalar_layout(int mode)
+{
+  if (mode != EXA_LAYOUT_AUTO && mode != EXA_LAYOUT_FLAT && mode != EXA_LAYOUT_DUAL) { setError("exa_set_scalar_layout: bad mode"); return EXA_ERR_INVALID; }
+  g_scalarLayout = mode; return EXA_OK;
+}
+int exa_renderer_get_scalar_layout(const exa_renderer_t *r, int *layout, uint64_t *bytes)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (layout) *layout = r->d_dual ? EXA_LAYOUT_DUAL : EXA_LAYOUT_FLAT;
+  if (bytes) *bytes = r->d_dual ? r->dualRecords * 32ull * (uint64_t)r->numFields : r->numCells * 4ull * (uint64_t)r->numFields;
+  return EXA_OK;
 }
 
 int exa_renderer_set_stream(exa_renderer_t *r, void *cudaStream)

@@ -67,7 +67,11 @@ struct DeviceScene {
   const int32_t *leafList; int leafListLen;
   const KdNode *kd; int numKdNodes; int kdDepth;
   const uint4 *blobs;                                       // region blobs, 16-B units
+  const float4 *dual; uint64_t dualRecords;                 // dual-cell records (2 float4 each), channel c at dual + 2*c*dualRecords; null = flat layout
   float boundsLo[3], boundsHi[3];                           // root domain of the ABR tree
+  // point-location grid: per cell the deepest kd node whose box contains the whole (slightly
+  // grown) cell; a point query starts its descent there instead of at the root
+  const int32_t *locGrid; int locG; float locScale[3];
 };
 
 // result of the GPU ABR build (all device pointers owned by the caller afterwards)
@@ -83,8 +87,10 @@ struct AbrResult {
 };
 
 // abr.cu
+// d_dualBegin != null: brick headers inside the region blobs carry the brick's first dual-cell
+// record instead of its first flat cell
 int abrBuild(const ExaBrick *d_bricks, int numBricks, const float *d_scalars, uint64_t numCells,
-             int numFields, void *stream, AbrResult &out);
+             int numFields, const uint32_t *d_dualBegin, void *stream, AbrResult &out);
 void abrFree(AbrResult &r);
 
 } // namespace exa

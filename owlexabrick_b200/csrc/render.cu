@@ -51,6 +51,13 @@ __device__ __forceinline__ float3 rayAt(float3 o, float3 d, float t)
 __device__ __forceinline__ float comp(float3 a, int d) { return d == 0 ? a.x : d == 1 ? a.y : a.z; }
 
 struct Acc { float sw, swv; float3 sd, sdc; };
+// base of channel c: flat scalars (reference layout) or dual-cell records (DeviceScene::dual)
+template <bool DUAL>
+__device__ __forceinline__ const void *chanBase(const DeviceScene &S, int c)
+{
+  if (DUAL) return S.dual + 2 * (size_t)c * S.dualRecords;
+  return S.scalars + (size_t)c * S.numCells;
+}
 __device__ __forceinline__ void accZero(Acc &a) { a.sw = 0.f; a.swv = 0.f; a.sd = f3(0, 0, 0); a.sdc = f3(0, 0, 0); }
 
 // addBasisFunctions (exabrick.cu:620-777) for k brick headers; `chan` = base of the channel's
@@ -61,8 +68,8 @@ __device__ __forceinline__ void accZero(Acc &a) { a.sw = 0.f; a.swv = 0.f; a.sd 
 //   sumDC.x = sum_valid (wz*wy)*sx      sumD.x = sum_valid (wz*wy)*sx*s      (sx = -1 low, +1 high)
 // into differences of the same partial sums.  Same real-number result as the reference's
 // corner loop, different fp32 rounding order (gate: 1e-5 relative).
-template <bool GRAD, bool STATS>
-__device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hdrs, int k, const float *__restrict__ chan,
+template <bool GRAD, bool STATS, bool DUAL>
+__device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hdrs, int k, const void *__restrict__ chanV,
                                             float px, float py, float pz, unsigned &nCorners)
 {
   for (int i = 0; i < k; i++) {
@@ -77,17 +84,31 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
     const bool x0 = ix0 >= 0 && ix0 < sx, x1 = ix0 + 1 < sx;
     const bool y0 = iy0 >= 0 && iy0 < sy, y1 = iy0 + 1 < sy;
     const bool z0 = iz0 >= 0 && iz0 < sz, z1 = iz0 + 1 < sz;
-    const int dy = sx, dz = sx * sy;
-    const float *base = chan + u1.w + ix0 + iy0 * dy + iz0 * dz;
-    const bool r00 = z0 && y0, r01 = z0 && y1, r10 = z1 && y0, r11 = z1 && y1;    // (z,y) rows
-    const float s000 = (r00 && x0) ? __ldg(base) : 0.f;
-    const float s001 = (r00 && x1) ? __ldg(base + 1) : 0.f;
-    const float s010 = (r01 && x0) ? __ldg(base + dy) : 0.f;
-    const float s011 = (r01 && x1) ? __ldg(base + dy + 1) : 0.f;
-    const float s100 = (r10 && x0) ? __ldg(base + dz) : 0.f;
-    const float s101 = (r10 && x1) ? __ldg(base + dz + 1) : 0.f;
-    const float s110 = (r11 && x0) ? __ldg(base + dz + dy) : 0.f;
-    const float s111 = (r11 && x1) ? __ldg(base + dz + dy + 1) : 0.f;
+    float s000, s001, s010, s011, s100, s101, s110, s111;
+    if (DUAL) {
+      // dual-cell records: the 8 corner scalars of dual cell (ix0,iy0,iz0) lie in ONE 32-byte
+      // sector (zeros where the corner is outside the brick); u1.w = first record of the brick
+      float4 lo4 = make_float4(0, 0, 0, 0), hi4 = lo4;
+      if (ix0 < sx && iy0 < sy && iz0 < sz) {
+        const int rx = sx + 1, ry = sy + 1;
+        const float4 *rec = reinterpret_cast<const float4 *>(chanV) +
+                            2 * ((size_t)u1.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry)));
+        lo4 = __ldg(rec); hi4 = __ldg(rec + 1);
+      }
+      s000 = lo4.x; s001 = lo4.y; s010 = lo4.z; s011 = lo4.w; s100 = hi4.x; s101 = hi4.y; s110 = hi4.z; s111 = hi4.w;
+    } else {
+      const int dy = sx, dz = sx * sy;
+      const float *base = reinterpret_cast<const float *>(chanV) + u1.w + ix0 + iy0 * dy + iz0 * dz;
+      const bool r00 = z0 && y0, r01 = z0 && y1, r10 = z1 && y0, r11 = z1 && y1;    // (z,y) rows
+      s000 = (r00 && x0) ? __ldg(base) : 0.f;
+      s001 = (r00 && x1) ? __ldg(base + 1) : 0.f;
+      s010 = (r01 && x0) ? __ldg(base + dy) : 0.f;
+      s011 = (r01 && x1) ? __ldg(base + dy + 1) : 0.f;
+      s100 = (r10 && x0) ? __ldg(base + dz) : 0.f;
+      s101 = (r10 && x1) ? __ldg(base + dz + 1) : 0.f;
+      s110 = (r11 && x0) ? __ldg(base + dz + dy) : 0.f;
+      s111 = (r11 && x1) ? __ldg(base + dz + dy + 1) : 0.f;
+    }
     if (STATS) nCorners += ((int)z0 + (int)z1) * ((int)y0 + (int)y1) * ((int)x0 + (int)x1);
     const float wx0 = x0 ? 1.f - fx : 0.f, wx1 = x1 ? fx : 0.f;
     const float wy0 = y0 ? 1.f - fy : 0.f, wy1 = y1 ? fy : 0.f;
@@ -275,13 +296,13 @@ __device__ __forceinline__ float4 over(float4 a, float4 b)
 struct RayStats { unsigned samples, visits, corners, segments; };
 
 // samplePoint / samplePointWithDerivative (exabrick.cu:781-816, 883-942) inside a known region
-template <bool GRAD, bool STATS>
+template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment &seg, int channel, float3 pos,
                                              float &value, float3 &g, RayStats &rs)
 {
   Acc a; accZero(a);
   unsigned nc = 0;
-  accumBricks<GRAD, STATS>(a, S.blobs + seg.blobOfs + 3, seg.K, S.scalars + (size_t)channel * S.numCells, pos.x, pos.y, pos.z, nc);
+  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + seg.blobOfs + 3, seg.K, chanBase<DUAL>(S, channel), pos.x, pos.y, pos.z, nc);
   if (STATS) { rs.samples++; rs.visits += seg.K; rs.corners += nc; }
   return accFinish<GRAD>(a, value, g);
 }
@@ -290,14 +311,14 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
 // 988-1016), as written: t_next = min(t_i, t1), sample at the midpoint of [t_last, t_next] with the
 // actual segment length in the opacity correction.  The caller owns the loop (k_renderFrame runs
 // it as a flat per-lane state machine so that the lanes of a warp stay converged).
-template <bool GRAD, bool STATS>
+template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ void integrateSample(const RenderParams &P, const float4 *xfTables, const float *xfK, const Segment &seg,
                                                 float3 o, float3 d, float t_sample, float actual_dt, float4 &pc, RayStats &rs)
 {
   const float3 pos = rayAt(o, d, t_sample);
   for (int c = 0; c < P.numChannels; c++) {
     float v = 0.f; float3 g = f3(0, 0, 0);
-    if (sampleRegion<GRAD, STATS>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
+    if (sampleRegion<GRAD, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
       float4 s = lookupXFfast(xfTables + c * 128, P.xfDomain[c][0], xfK[c], P.xfOpacityScale, v);
       if (GRAD) {
         const float gg = dot3(g, g), thr = (float)(int)seg.fcw * 1e-6f;
@@ -320,7 +341,7 @@ __device__ __forceinline__ void integrateSample(const RenderParams &P, const flo
 }
 
 // IsoSurfaceIntegrationFunction::operator() (exabrick.cu:1024-1109) for channel `c`
-template <bool STATS>
+template <bool STATS, bool DUAL>
 __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
                                            int c, float t_sample, float cellValue, float &lastT, float &lastV,
                                            float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
@@ -338,18 +359,18 @@ __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *
         float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
         const int ich = P.isoChannel[i];
         if (P.gradISO) {
-          if (sampleRegion<true, STATS>(P.scene, seg, ich, isopt, cv, grad, rs)) {
+          if (sampleRegion<true, STATS, DUAL>(P.scene, seg, ich, isopt, cv, grad, rs)) {
             smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
             grad = normalize3(grad);
             if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
           }
         } else {
-          if (sampleRegion<false, STATS>(P.scene, seg, ich, isopt, cv, grad, rs))
+          if (sampleRegion<false, STATS, DUAL>(P.scene, seg, ich, isopt, cv, grad, rs))
             smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
         }
         if (P.colormapChannel != 0) {
           cv = 0.f; float3 g2;
-          if (sampleRegion<false, STATS>(P.scene, seg, P.colormapChannel, isopt, cv, g2, rs))
+          if (sampleRegion<false, STATS, DUAL>(P.scene, seg, P.colormapChannel, isopt, cv, g2, rs))
             smp = lookupXF(xfTables, P.xfDomain[0][0], P.xfDomain[0][1], P.xfOpacityScale, cv);
         }
         smp.w = 1.f;
@@ -370,7 +391,7 @@ __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *
 
 // isoIntegrateBrick (exabrick.cu:1187-1256), as written; per-channel functor state lives in
 // this thread's column of shared memory (isoT / isoV, entry c at [c * blockDim.x])
-template <bool STATS>
+template <bool STATS, bool DUAL>
 __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
                                            float t0, float t1, float *isoT, float *isoV,
                                            float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
@@ -387,11 +408,11 @@ __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *
     const float3 pos = rayAt(o, d, t_sample);
     for (int c = 0; c < P.numChannels; c++) {
       float v = 0.f; float3 g = f3(0, 0, 0); bool ok;
-      if (P.gradISO) ok = sampleRegion<true, STATS>(P.scene, seg, c, pos, v, g, rs);
-      else ok = sampleRegion<false, STATS>(P.scene, seg, c, pos, v, g, rs);
+      if (P.gradISO) ok = sampleRegion<true, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs);
+      else ok = sampleRegion<false, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs);
       if (ok) {
         float lt = isoT[c * stride], lv = isoV[c * stride];
-        isoFunctor<STATS>(P, xfTables, seg, o, d, c, t_sample, v, lt, lv, pc, tHit, hitGrad, rs);
+        isoFunctor<STATS, DUAL>(P, xfTables, seg, o, d, c, t_sample, v, lt, lv, pc, tHit, hitGrad, rs);
         isoT[c * stride] = lt; isoV[c * stride] = lv;
         if (pc.w >= P.ertThreshold) break;
       }
@@ -414,7 +435,7 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
-template <bool GRAD, bool STATS>
+template <bool GRAD, bool STATS, bool DUAL>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
@@ -471,7 +492,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         Segment seg;
         if (!travNext(T, P.scene, P.isoActive, already, rtmax, seg)) break;
         float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
-        isoSegment<STATS>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
+        isoSegment<STATS, DUAL>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
         if (th >= 0.f) {
           surfPrim = -23; surfT = th / dtScale; surfNg = normalize3(hg); surfAmbient = 0.f; surfBase = f3(ipc.x, ipc.y, ipc.z);
           break;
@@ -525,7 +546,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         const float t_sample = 0.5f * (t_next + t_last);
         const float actual_dt = t_next - t_last;
         t_last = t_next;
-        integrateSample<GRAD, STATS>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
+        integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
         if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
         else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                             // :1698
         else t_i += dtS;
@@ -559,11 +580,13 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
   const dim3 grid(tilesX * tilesY), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
-#define LAUNCH(G, S_)                                                                                   \
-  { cudaFuncSetAttribute(k_renderFrame<G, S_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \
-    k_renderFrame<G, S_><<<grid, block, smemBytes, s>>>(P); }
-  if (P.gradDVR) { if (stats) LAUNCH(true, true) else LAUNCH(true, false) }
-  else { if (stats) LAUNCH(false, true) else LAUNCH(false, false) }
+#define LAUNCH(G, S_, D_)                                                                                   \
+  { cudaFuncSetAttribute(k_renderFrame<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \
+    k_renderFrame<G, S_, D_><<<grid, block, smemBytes, s>>>(P); }
+#define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }
+  if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
+  else { if (stats) LAUNCH_D(false, true) else LAUNCH_D(false, false) }
+#undef LAUNCH_D
 #undef LAUNCH
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
@@ -576,6 +599,13 @@ __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py,
   if (!(px >= S.boundsLo[0] && px <= S.boundsHi[0] && py >= S.boundsLo[1] && py <= S.boundsHi[1] && pz >= S.boundsLo[2] && pz <= S.boundsHi[2]))
     return false;
   int node = 0;
+  if (S.locGrid) {
+    const int G = S.locG;
+    const int cx = min(G - 1, (int)((px - S.boundsLo[0]) * S.locScale[0]));
+    const int cy = min(G - 1, (int)((py - S.boundsLo[1]) * S.locScale[1]));
+    const int cz = min(G - 1, (int)((pz - S.boundsLo[2]) * S.locScale[2]));
+    node = __ldg(S.locGrid + cx + G * (cy + G * cz));
+  }
   for (;;) {
     const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + node);
     const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
@@ -591,19 +621,19 @@ __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py,
   }
 }
 
-template <bool GRAD, bool STATS>
+template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
                                                   float &value, float3 &g, unsigned &visits, unsigned &corners)
 {
   uint32_t bo; int K;
   if (!locate(S, px, py, pz, bo, K)) return false;
   Acc a; accZero(a);
-  accumBricks<GRAD, STATS>(a, S.blobs + bo + 3, K, S.scalars + (size_t)channel * S.numCells, px, py, pz, corners);
+  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + bo + 3, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
   return accFinish<GRAD>(a, value, g);
 }
 
-template <bool GRAD, bool STATS>
+template <bool GRAD, bool STATS, bool DUAL>
 __global__ void __launch_bounds__(256) k_samplePoints(const __grid_constant__ SampleParams P)
 {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -611,7 +641,7 @@ __global__ void __launch_bounds__(256) k_samplePoints(const __grid_constant__ Sa
   if (i < P.n) {
     const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
     float v = 0.f; float3 g = f3(0, 0, 0);
-    const bool ok = samplePointGlobal<GRAD, STATS>(P.scene, px, py, pz, P.channel, v, g, visits, corners);
+    const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners);
     counted = visits > 0;
     if (P.values) P.values[i] = ok ? v : 0.f;
     if (P.valid) P.valid[i] = ok ? 1 : 0;
@@ -629,23 +659,27 @@ int launchSamplePoints(const SampleParams &P, cudaStream_t s)
   if (P.n == 0) return 0;
   const unsigned grid = (unsigned)((P.n + 255) / 256);
   const bool stats = P.stats != nullptr;
-  if (P.grad) { if (stats) k_samplePoints<true, true><<<grid, 256, 0, s>>>(P); else k_samplePoints<true, false><<<grid, 256, 0, s>>>(P); }
-  else { if (stats) k_samplePoints<false, true><<<grid, 256, 0, s>>>(P); else k_samplePoints<false, false><<<grid, 256, 0, s>>>(P); }
+#define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, 256, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, 256, 0, s>>>(P); }
+  if (P.grad) { if (stats) LAUNCH_P(true, true) else LAUNCH_P(true, false) }
+  else { if (stats) LAUNCH_P(false, true) else LAUNCH_P(false, false) }
+#undef LAUNCH_P
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
 // -----------------------------------------------------------------------------------------
 // streamlines: computeTraces / sampleDirection (exabrick.cu:945-963, 1531-1574)
 // -----------------------------------------------------------------------------------------
+template <bool DUAL>
 __device__ __forceinline__ bool sampleDirection(const DeviceScene &S, float3 p, const int ch[3], float3 &out)
 {
   // a point query that misses every region is an invalid sample (the reference indexes
   // region -1 there: undefined behaviour that is not copied)
   float v[3]; float3 g; unsigned a = 0, b = 0;
-  for (int i = 0; i < 3; i++) if (!samplePointGlobal<false, false>(S, p.x, p.y, p.z, ch[i], v[i], g, a, b)) return false;
+  for (int i = 0; i < 3; i++) if (!samplePointGlobal<false, false, DUAL>(S, p.x, p.y, p.z, ch[i], v[i], g, a, b)) return false;
   out = f3(v[0], v[1], v[2]); return true;
 }
 
+template <bool DUAL>
 __global__ void k_trace(const __grid_constant__ TraceParams P)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -655,10 +689,10 @@ __global__ void k_trace(const __grid_constant__ TraceParams P)
     float3 p = f3(src[0], src[1], src[2]); const float3 pp = p;
     if (p.x < 2e10f) {
       bool valid = true; float3 k1 = f3(0, 0, 0), k2 = k1, k3 = k1, k4 = k1;
-      valid &= sampleDirection(P.scene, p, P.channels, k1); k1 = k1 * P.steplen; const float3 p1 = p + k1 * .5f;
-      valid &= sampleDirection(P.scene, p1, P.channels, k2); k2 = k2 * P.steplen; const float3 p2 = p + k2 * .5f;
-      valid &= sampleDirection(P.scene, p2, P.channels, k3); k3 = k3 * P.steplen; const float3 p3 = p + k3;
-      valid &= sampleDirection(P.scene, p3, P.channels, k4); k4 = k4 * P.steplen;
+      valid &= sampleDirection<DUAL>(P.scene, p, P.channels, k1); k1 = k1 * P.steplen; const float3 p1 = p + k1 * .5f;
+      valid &= sampleDirection<DUAL>(P.scene, p1, P.channels, k2); k2 = k2 * P.steplen; const float3 p2 = p + k2 * .5f;
+      valid &= sampleDirection<DUAL>(P.scene, p2, P.channels, k3); k3 = k3 * P.steplen; const float3 p3 = p + k3;
+      valid &= sampleDirection<DUAL>(P.scene, p3, P.channels, k4); k4 = k4 * P.steplen;
       p = p + (1 / 6.f) * (k1 + 2.f * k2 + 2.f * k3 + k4);
       const bool inside = p.x >= P.worldLo[0] && p.x <= P.worldHi[0] && p.y >= P.worldLo[1] && p.y <= P.worldHi[1] && p.z >= P.worldLo[2] && p.z <= P.worldHi[2];
       if (!valid || !inside || len3(p - pp) < 1e-10f) p = f3(2e10f, 2e10f, 2e10f);
@@ -670,7 +704,7 @@ __global__ void k_trace(const __grid_constant__ TraceParams P)
 int launchTrace(const TraceParams &P, cudaStream_t s)
 {
   if (P.numTraces <= 0) return 0;
-  k_trace<<<(P.numTraces + 63) / 64, 64, 0, s>>>(P);
+  if (P.scene.dual) k_trace<true><<<(P.numTraces + 63) / 64, 64, 0, s>>>(P); else k_trace<false><<<(P.numTraces + 63) / 64, 64, 0, s>>>(P);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
@@ -778,6 +812,79 @@ int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellI
 {
   if (numCells == 0) return 0;
   k_gather<<<(unsigned)((numCells + 255) / 256), 256, 0, s>>>(d_field, fieldCount, d_cellIDs, numCells, d_out, d_err);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// -----------------------------------------------------------------------------------------
+// point-location grid (see DeviceScene::locGrid).  The cell box is grown by 1% of a cell on
+// every side before it is tested against a split plane, which is orders of magnitude more
+// than the rounding of the cell-index computation in locate(): every point that maps to a
+// cell lies inside the grown box, so starting at the stored node gives exactly the leaf the
+// root descent would reach.
+// -----------------------------------------------------------------------------------------
+__global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, float loz, float wx, float wy, float wz, int32_t *grid)
+{
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= G * G * G) return;
+  const int cx = c % G, cy = (c / G) % G, cz = c / (G * G);
+  const float lo[3] = {lox + ((float)cx - 0.01f) * wx, loy + ((float)cy - 0.01f) * wy, loz + ((float)cz - 0.01f) * wz};
+  const float hi[3] = {lox + ((float)cx + 1.01f) * wx, loy + ((float)cy + 1.01f) * wy, loz + ((float)cz + 1.01f) * wz};
+  int node = 0;
+  for (;;) {
+    const KdNode nd = kd[node];
+    const uint32_t axis = nd.info >> 30;
+    if (axis == 3) break;
+    const int child = (int)(nd.info & 0x3fffffffu);
+    if (hi[axis] < nd.split) node = child;                  // p < split for every p in the cell
+    else if (lo[axis] >= nd.split) node = child + 1;        // p >= split for every p in the cell
+    else break;
+  }
+  grid[c] = node;
+}
+
+int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], int32_t *d_grid, float scaleOut[3], cudaStream_t s)
+{
+  float w[3];
+  for (int d = 0; d < 3; d++) { w[d] = (hi[d] - lo[d]) / (float)G; scaleOut[d] = (float)G / (hi[d] - lo[d]); }
+  k_buildLocGrid<<<(G * G * G + 255) / 256, 256, 0, s>>>(kd, G, lo[0], lo[1], lo[2], w[0], w[1], w[2], d_grid);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// -----------------------------------------------------------------------------------------
+// dual-cell records: for every brick and every dual cell (i,j,k) in [-1,sx-1]x[-1,sy-1]x[-1,sz-1]
+// the 8 corner scalars {s000,s001,s010,s011,s100,s101,s110,s111} (x fastest, 0 outside the
+// brick) as one 32-byte record, so that one tent-basis brick visit reads ONE DRAM sector
+// instead of >= 4.  8x the scalar memory: a capacity-for-bandwidth trade that 180 GB of HBM3e
+// affords; the flat reference layout stays (ABI, value-range pass, fallback).
+// -----------------------------------------------------------------------------------------
+__global__ void k_expandDual(const ExaBrick *bricks, int numBricks, const uint32_t *dualBegin, uint64_t numRecords,
+                             const float *scalars, float4 *dual)
+{
+  const uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= numRecords) return;
+  int lo = 0, hi = numBricks - 1;                            // last brick with dualBegin <= r
+  while (lo < hi) { const int mid = (lo + hi + 1) >> 1; if ((uint64_t)__ldg(dualBegin + mid) <= r) lo = mid; else hi = mid - 1; }
+  const ExaBrick b = bricks[lo];
+  const int sx = b.size[0], sy = b.size[1], sz = b.size[2], rx = sx + 1, ry = sy + 1;
+  uint32_t q = (uint32_t)(r - dualBegin[lo]);
+  const int i = (int)(q % rx) - 1; q /= rx;
+  const int j = (int)(q % ry) - 1, k = (int)(q / ry) - 1;
+  const float *base = scalars + b.begin;
+  float v[8];
+#pragma unroll
+  for (int c = 0; c < 8; c++) {
+    const int x = i + (c & 1), y = j + ((c >> 1) & 1), z = k + (c >> 2);
+    v[c] = (x >= 0 && x < sx && y >= 0 && y < sy && z >= 0 && z < sz) ? __ldg(base + x + (size_t)sx * y + (size_t)sx * sy * z) : 0.f;
+  }
+  dual[2 * r] = make_float4(v[0], v[1], v[2], v[3]);
+  dual[2 * r + 1] = make_float4(v[4], v[5], v[6], v[7]);
+}
+
+int launchExpandDual(const ExaBrick *d_bricks, int numBricks, const uint32_t *d_dualBegin, uint64_t numRecords,
+                     const float *d_scalars, float4 *d_dual, cudaStream_t s)
+{
+  if (numRecords == 0) return 0;
+  k_expandDual<<<(unsigned)((numRecords + 255) / 256), 256, 0, s>>>(d_bricks, numBricks, d_dualBegin, numRecords, d_scalars, d_dual);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -200,14 +200,18 @@ def default_camera(world_lo, world_hi, width, height, fovy=70.0):
 class Renderer:
     """exa::OptixRenderer, headless.  fields: list of float32 arrays indexed by cell ID."""
 
-    def __init__(self, bricks, fields, device=0):
+    def __init__(self, bricks, fields, device=0, layout=None):
         self.bricks = bricks
+        if layout is not None:
+            check(lib.exa_set_scalar_layout(int(layout)))
         fields = [np.ascontiguousarray(f, dtype=np.float32) for f in fields]
         ptrs = (C.c_void_p * len(fields))(*[f.ctypes.data for f in fields])
         counts = (C.c_size_t * len(fields))(*[len(f) for f in fields])
         handle = bricks.h if isinstance(bricks, ExaBricks) else C.c_void_p(bricks)
         out = C.c_void_p()
         check(lib.exa_renderer_create(handle, ptrs, counts, len(fields), device, C.byref(out)))
+        if layout is not None:
+            lib.exa_set_scalar_layout(capi.LAYOUT_AUTO)
         self.h = out
         self.num_fields = len(fields)
         self.fb_size = (0, 0)
@@ -219,6 +223,12 @@ class Renderer:
         if getattr(self, "h", None):
             lib.exa_renderer_destroy(self.h)
             self.h = None
+
+    def scalar_layout(self):
+        """(layout, bytes): capi.LAYOUT_FLAT or capi.LAYOUT_DUAL and the size of the scalar data the kernels read"""
+        lay, nbytes = C.c_int(), C.c_uint64()
+        check(lib.exa_renderer_get_scalar_layout(self.h, C.byref(lay), C.byref(nbytes)))
+        return lay.value, int(nbytes.value)
 
     def set_stream(self, cuda_stream):
         check(lib.exa_renderer_set_stream(self.h, C.c_void_p(cuda_stream)))

@@ -30,6 +30,16 @@ def R(built_lib):
     return renderer
 
 
+@pytest.fixture(params=["flat", "dual"], autouse=True)
+def scalar_layout(request, built_lib):
+    """every GPU parity test runs against both device layouts of the scalars (flat reference
+    layout, dual-cell records); results must be identical"""
+    mode = built_lib.LAYOUT_FLAT if request.param == "flat" else built_lib.LAYOUT_DUAL
+    built_lib.check(built_lib.lib.exa_set_scalar_layout(mode))
+    yield request.param
+    built_lib.lib.exa_set_scalar_layout(built_lib.LAYOUT_AUTO)
+
+
 def make_pair(R, orc, cells, fields, mlw=127):
     """(product renderer, oracle scene) over the same input"""
     b = R.ExaBricks.build(cells, max_leaf_width=mlw)

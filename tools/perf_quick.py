@@ -35,7 +35,7 @@ def main():
     W, H = image
     fd = bench.frame_desc(R, domain, image, (float(field.min()), float(field.max()))); fd.apply(r)
     alpha, rgb = fd.xf[0]
-    out = {"tag": a.tag, "lib": os.path.basename(capi.LIB_PATH)}
+    out = {"tag": a.tag, "lib": os.path.basename(capi.LIB_PATH), "layout": r.scalar_layout()}
 
     def time_frames(n):
         for _ in range(3): r.render(sync=False)
@@ -58,8 +58,10 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
     ts = []
+    flush2 = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     for i in range(8):
         flush.fill_(i)
+        if os.environ.get("PQ_CLEAN_FLUSH"): flush2.sum()      # leave L2 full of CLEAN lines (no write-back during the kernel)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream); r.sample_points_device(d_pts.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr()); e1.record(stream)
         torch.cuda.synchronize()
