@@ -249,8 +249,8 @@ __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, cons
   if (lf < 0) return;
   const int rid = offLeaf[g], lb = offList[g], cnt = leafCount[lf], pb = leafPoolBegin[lf];
   const Box3 dom = leafDom[lf];
-  // blob offset (16-B units): 3 units header per region + 2 per list entry
-  const uint32_t blobOfs = (uint32_t)(3 * rid + 2 * lb);
+  // blob offset (16-B units): BLOB_HDR_UNITS header units per region + 2 per list entry
+  const uint32_t blobOfs = (uint32_t)(BLOB_HDR_UNITS * rid + 2 * lb);
   int finest = 1 << 30;
   for (int k = 0; k < cnt; k++) {
     const int bid = pool[pb + k];
@@ -260,7 +260,7 @@ __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, cons
     BrickHdr h; h.lx = (float)b.lower[0]; h.ly = (float)b.lower[1]; h.lz = (float)b.lower[2];
     h.invCw = 1.f / (float)(1 << b.level); h.sx = b.size[0]; h.sy = b.size[1]; h.sz = b.size[2]; h.begin = dualBegin ? dualBegin[bid] : b.begin;
     const uint4 *hp = reinterpret_cast<const uint4 *>(&h);
-    blobs[blobOfs + 3 + 2 * k] = hp[0]; blobs[blobOfs + 3 + 2 * k + 1] = hp[1];
+    blobs[blobOfs + BLOB_HDR_UNITS + 2 * k] = hp[0]; blobs[blobOfs + BLOB_HDR_UNITS + 2 * k + 1] = hp[1];
   }
   ExaBrickRegion r;
   for (int d = 0; d < 3; d++) { r.domain_lower[d] = dom.lo[d]; r.domain_upper[d] = dom.hi[d]; }
@@ -319,8 +319,8 @@ __global__ void k_rangeDecode(int nr, const unsigned *rangeEnc, ExaBrickRegion *
   for (int d = 0; d < 3; d++) { h.lo[d] = r.domain_lower[d]; h.hi[d] = r.domain_upper[d]; }
   h.fcw = r.finestLevelCellWidth; h.k = r.leafListSize; h.regionID = i; h.vlo = r.valueRange_lower; h.vhi = r.valueRange_upper; h.pad = 0;
   const uint4 *hp = reinterpret_cast<const uint4 *>(&h);
-  const size_t ofs = (size_t)3 * i + (size_t)2 * r.leafListBegin;
-  blobs[ofs] = hp[0]; blobs[ofs + 1] = hp[1]; blobs[ofs + 2] = hp[2];
+  const size_t ofs = (size_t)BLOB_HDR_UNITS * i + (size_t)2 * r.leafListBegin;
+  blobs[ofs] = hp[0]; blobs[ofs + 1] = hp[1]; blobs[ofs + 2] = hp[2]; blobs[ofs + 3] = make_uint4(0, 0, 0, 0);
 }
 
 struct Scanner {
@@ -451,7 +451,7 @@ int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t 
   }
   const int nr = numLeaves, L = poolUsed;
   ExaBrickRegion *regions; int *leafList, *entryRegion; unsigned *rangeEnc; uint4 *blobs;
-  const size_t blobUnits = (size_t)3 * nr + (size_t)2 * L;
+  const size_t blobUnits = (size_t)BLOB_HDR_UNITS * nr + (size_t)2 * L;
   if (blobUnits >= KD_EMPTY) { setError("abrBuild: region blob exceeds 30-bit offset"); return EXA_ERR_LIMIT; }
   CK(cudaMalloc(&regions, sizeof(ExaBrickRegion) * (size_t)std::max(nr, 1))); CK(cudaMalloc(&leafList, 4 * (size_t)std::max(L, 1)));
   CK(cudaMalloc(&entryRegion, 4 * (size_t)std::max(L, 1))); CK(cudaMalloc(&rangeEnc, 8 * (size_t)std::max(nr, 1)));

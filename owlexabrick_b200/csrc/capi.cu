@@ -22,7 +22,7 @@ struct exa_renderer {
   ExaBrick *d_bricks = nullptr; int numBricks = 0;
   float *d_scalars = nullptr; uint64_t numCells = 0; int numFields = 0;
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
-  int32_t *d_locGrid = nullptr; int locG = 0; float locScale[3] = {0, 0, 0};              // point-location grid
+  uint2 *d_locGrid = nullptr; int locG = 0; float locScale[3] = {0, 0, 0};              // point-location grid
   float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
@@ -238,10 +238,10 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   r->launches += r->abr.launches;
   if (r->abr.depth + 2 > 160) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
   {
-    // point-location grid: ~8 cells per region, 16^3 .. 128^3
-    int G = 16; while (G < 128 && (double)G * G * G < 8.0 * r->abr.numRegions) G *= 2;
+    // point-location grid: ~32+ cells per region, 16^3 .. 128^3 (8 B per cell)
+    int G = 16; while (G < 128 && (double)G * G * G < 32.0 * r->abr.numRegions) G *= 2;
     if (!getenv("EXA_NO_LOCGRID")) {
-      CKC(cudaMalloc(&r->d_locGrid, sizeof(int32_t) * (size_t)G * G * G));
+      CKC(cudaMalloc(&r->d_locGrid, sizeof(uint2) * (size_t)G * G * G));
       if (launchBuildLocGrid(r->abr.kd, G, r->abr.boundsLo, r->abr.boundsHi, r->d_locGrid, r->locScale, s) < 0) {
         setError("point-location grid kernel failed"); exa_renderer_destroy(r); return EXA_ERR_CUDA; }
       r->locG = G; r->launches++;

@@ -43,8 +43,11 @@ struct KdNode {
 };
 static const uint32_t KD_EMPTY = 0x3fffffffu;
 
-// Region blob, one per region, 16-byte aligned, laid out so ONE bulk copy stages everything a
-// warp needs for a segment: header (48 B) followed by K brick headers (32 B each).
+// Region blob, one per region, 32-byte aligned: a 64-B header (48 B used) followed by K brick
+// headers of 32 B each, so that every brick header is ONE aligned 256-bit load
+// (ld.global.nc.v8, LDG.E.ENL2.256 on sm_100a) and the region -> leafList -> Brick dependent
+// chain of the reference is one contiguous read.
+static const int BLOB_HDR_UNITS = 4;    // 16-B units
 struct RegionBlobHdr {
   float lo[3], hi[3];
   float fcw;                            // finestLevelCellWidth
@@ -71,7 +74,7 @@ struct DeviceScene {
   float boundsLo[3], boundsHi[3];                           // root domain of the ABR tree
   // point-location grid: per cell the deepest kd node whose box contains the whole (slightly
   // grown) cell; a point query starts its descent there instead of at the root
-  const int32_t *locGrid; int locG; float locScale[3];
+  const uint2 *locGrid; int locG; float locScale[3];
 };
 
 // result of the GPU ABR build (all device pointers owned by the caller afterwards)

@@ -50,6 +50,17 @@ __device__ __forceinline__ float3 rayAt(float3 o, float3 d, float t)
 { return f3(__fadd_rn(o.x, __fmul_rn(t, d.x)), __fadd_rn(o.y, __fmul_rn(t, d.y)), __fadd_rn(o.z, __fmul_rn(t, d.z))); }
 __device__ __forceinline__ float comp(float3 a, int d) { return d == 0 ? a.x : d == 1 ? a.y : a.z; }
 
+// One aligned 256-bit read-only load (PTX ld.global.nc.v8.f32 -> SASS LDG.E.ENL2.256, new on
+// sm_100): a 32-byte brick header or dual-cell record costs ONE L1 tag look-up per thread.
+struct __align__(32) U8 { uint4 lo, hi; };
+__device__ __forceinline__ U8 ldg256(const void *p)
+{
+  U8 r;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
+  return r;
+}
+
 struct Acc { float sw, swv; float3 sd, sdc; };
 // base of channel c: flat scalars (reference layout) or dual-cell records (DeviceScene::dual)
 template <bool DUAL>
@@ -73,7 +84,8 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
                                             float px, float py, float pz, unsigned &nCorners)
 {
   for (int i = 0; i < k; i++) {
-    const uint4 u0 = __ldg(hdrs + 2 * i), u1 = __ldg(hdrs + 2 * i + 1);
+    const U8 hdr = ldg256(hdrs + 2 * i);
+    const uint4 u0 = hdr.lo, u1 = hdr.hi;
     const float invCw = __uint_as_float(u0.w);
     const int sx = (int)u1.x, sy = (int)u1.y, sz = (int)u1.z;
     const float lx = (px - __uint_as_float(u0.x)) * invCw - 0.5f;
@@ -93,7 +105,9 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
         const int rx = sx + 1, ry = sy + 1;
         const float4 *rec = reinterpret_cast<const float4 *>(chanV) +
                             2 * ((size_t)u1.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry)));
-        lo4 = __ldg(rec); hi4 = __ldg(rec + 1);
+        const U8 q = ldg256(rec);
+        lo4 = make_float4(__uint_as_float(q.lo.x), __uint_as_float(q.lo.y), __uint_as_float(q.lo.z), __uint_as_float(q.lo.w));
+        hi4 = make_float4(__uint_as_float(q.hi.x), __uint_as_float(q.hi.y), __uint_as_float(q.hi.z), __uint_as_float(q.hi.w));
       }
       s000 = lo4.x; s001 = lo4.y; s010 = lo4.z; s011 = lo4.w; s100 = hi4.x; s101 = hi4.y; s110 = hi4.z; s111 = hi4.w;
     } else {
@@ -246,7 +260,8 @@ __device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const ui
     if (axis == 3) {
       T.cur = -1;
       if (payload == KD_EMPTY) continue;
-      const uint4 h0 = __ldg(S.blobs + payload), h1 = __ldg(S.blobs + payload + 1);
+      const U8 hb = ldg256(S.blobs + payload);
+      const uint4 h0 = hb.lo, h1 = hb.hi;
       const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
       const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
       if (boxTest(T.o, T.d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
@@ -302,7 +317,7 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
 {
   Acc a; accZero(a);
   unsigned nc = 0;
-  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + seg.blobOfs + 3, seg.K, chanBase<DUAL>(S, channel), pos.x, pos.y, pos.z, nc);
+  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + seg.blobOfs + BLOB_HDR_UNITS, seg.K, chanBase<DUAL>(S, channel), pos.x, pos.y, pos.z, nc);
   if (STATS) { rs.samples++; rs.visits += seg.K; rs.corners += nc; }
   return accFinish<GRAD>(a, value, g);
 }
@@ -596,28 +611,30 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 // -----------------------------------------------------------------------------------------
 __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K)
 {
-  if (!(px >= S.boundsLo[0] && px <= S.boundsHi[0] && py >= S.boundsLo[1] && py <= S.boundsHi[1] && pz >= S.boundsLo[2] && pz <= S.boundsHi[2]))
+  // Regions are the half-open leaf boxes [lo,hi) of the kd-tree and tile its root box, so
+  // "lo <= p < hi of the root" + a descent with (p < split -> left) finds the region with
+  // lo <= p < hi; empty leaves are holes.  (NaN fails the first test.)
+  if (!(px >= S.boundsLo[0] && px < S.boundsHi[0] && py >= S.boundsLo[1] && py < S.boundsHi[1] && pz >= S.boundsLo[2] && pz < S.boundsHi[2]))
     return false;
-  int node = 0;
+  uint2 raw;
   if (S.locGrid) {
+    // the grid cell holds a COPY of the deepest kd node that contains the whole cell: for most
+    // cells that is already the leaf, and the query is one 8-byte load
     const int G = S.locG;
     const int cx = min(G - 1, (int)((px - S.boundsLo[0]) * S.locScale[0]));
     const int cy = min(G - 1, (int)((py - S.boundsLo[1]) * S.locScale[1]));
     const int cz = min(G - 1, (int)((pz - S.boundsLo[2]) * S.locScale[2]));
-    node = __ldg(S.locGrid + cx + G * (cy + G * cz));
-  }
+    raw = __ldg(S.locGrid + cx + G * (cy + G * cz));
+  } else raw = __ldg(reinterpret_cast<const uint2 *>(S.kd));
   for (;;) {
-    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + node);
     const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
     if (axis == 3) {
       if (payload == KD_EMPTY) return false;
       blobOfs = payload; K = (int)raw.x;
-      // regions are half-open [lo,hi): only the outer upper faces need the explicit check
-      const uint4 h0 = __ldg(S.blobs + payload), h1 = __ldg(S.blobs + payload + 1);
-      return px < __uint_as_float(h0.w) && py < __uint_as_float(h1.x) && pz < __uint_as_float(h1.y);
+      return true;
     }
     const float p = axis == 0 ? px : axis == 1 ? py : pz;
-    node = (int)payload + (p < __uint_as_float(raw.x) ? 0 : 1);
+    raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + payload + (p < __uint_as_float(raw.x) ? 0 : 1));
   }
 }
 
@@ -628,7 +645,7 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
   uint32_t bo; int K;
   if (!locate(S, px, py, pz, bo, K)) return false;
   Acc a; accZero(a);
-  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + bo + 3, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
+  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
   return accFinish<GRAD>(a, value, g);
 }
@@ -822,7 +839,7 @@ int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellI
 // cell lies inside the grown box, so starting at the stored node gives exactly the leaf the
 // root descent would reach.
 // -----------------------------------------------------------------------------------------
-__global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, float loz, float wx, float wy, float wz, int32_t *grid)
+__global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, float loz, float wx, float wy, float wz, uint2 *grid)
 {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= G * G * G) return;
@@ -839,10 +856,10 @@ __global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, fl
     else if (lo[axis] >= nd.split) node = child + 1;        // p >= split for every p in the cell
     else break;
   }
-  grid[c] = node;
+  grid[c] = reinterpret_cast<const uint2 *>(kd)[node];
 }
 
-int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], int32_t *d_grid, float scaleOut[3], cudaStream_t s)
+int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s)
 {
   float w[3];
   for (int d = 0; d < 3; d++) { w[d] = (hi[d] - lo[d]) / (float)G; scaleOut[d] = (float)G / (hi[d] - lo[d]); }

@@ -57,7 +57,7 @@ int launchRegionActivity(const RenderParams &P, const std::vector<int> &levelOff
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
 int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellIDs, size_t numCells, float *d_out,
                  int *d_errFlag, cudaStream_t s);
-int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], int32_t *d_grid, float scaleOut[3], cudaStream_t s);
+int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s);
 int launchExpandDual(const ExaBrick *d_bricks, int numBricks, const uint32_t *d_dualBegin, uint64_t numRecords,
                      const float *d_scalars, float4 *d_dual, cudaStream_t s);
 int launchCompositeOver(float4 *mine, const float4 *other, size_t count, int mineIsFront, float ertThreshold, cudaStream_t s);
