@@ -46,6 +46,8 @@ struct exa_renderer {
   float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
   float *d_traces = nullptr; size_t tracesCap = 0;
   unsigned long long *d_stats = nullptr;
+  // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
+  TileOrder *d_tileOrder[2] = {nullptr, nullptr}; int tileOrderCap = 0, tileOrderCur = 0; bool tileOrderValid = false;
 };
 
 static int cudaUsable()
@@ -90,6 +92,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   P.traces = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
   P.stats = nullptr;
+  P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
   P.kdStack = r->abr.depth + 2;
   P.dbg = 0;
 #ifdef EXA_DEBUG
@@ -276,7 +279,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   abrFree(r->abr);
   cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
   cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
-  cudaFree(r->d_traces); cudaFree(r->d_stats);
+  cudaFree(r->d_traces); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]);
   delete r;
 }
 
@@ -348,6 +351,10 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   if (fbPointer) r->d_rgba8 = (uint32_t *)fbPointer;
   else { CKR(cudaMalloc(&r->d_rgba8, n * 4)); CKR(cudaMemset(r->d_rgba8, 0, n * 4)); r->ownRgba8 = true; }
   r->width = width; r->height = height;
+  for (int i = 0; i < 2; i++) { cudaFree(r->d_tileOrder[i]); r->d_tileOrder[i] = nullptr; }
+  r->tileOrderCap = ((width + 15) / 16) * ((height + 7) / 8); r->tileOrderValid = false;
+  if (!getenv("EXA_NO_TILE_ORDER"))
+    for (int i = 0; i < 2; i++) CKR(cudaMalloc(&r->d_tileOrder[i], sizeof(TileOrder) + sizeof(uint32_t) * (size_t)TILE_BUCKETS * r->tileOrderCap));
   return EXA_OK;
 }
 

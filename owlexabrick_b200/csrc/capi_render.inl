@@ -24,6 +24,11 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
   int rc = refreshMasks(r, P); if (rc) return rc;
   P.partialOut = partialOut;
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 32, r->stream)); P.stats = r->d_stats; }
+  if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)
+    if (r->tileOrderValid) P.tileOrderIn = r->d_tileOrder[r->tileOrderCur];
+    P.tileOrderOut = r->d_tileOrder[r->tileOrderCur ^ 1];
+    r->tileOrderCur ^= 1; r->tileOrderValid = true;
+  }
   if (launchRenderFrame(P, r->stream) < 0) { setError(std::string("frame kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
   r->launches++;
   if (stats) {
@@ -238,6 +243,7 @@ int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRan
   if (!r || numRanks < 1 || rank < 0 || rank >= numRanks) { setError("set_partition: bad rank"); return EXA_ERR_INVALID; }
   if (mode != EXA_PARTITION_NONE && mode != EXA_PARTITION_SORT_LAST && mode != EXA_PARTITION_IMAGE_TILES) { setError("set_partition: bad mode"); return EXA_ERR_INVALID; }
   r->partMode = mode; r->rank = rank; r->numRanks = numRanks; r->masksDirty = true;
+  r->tileOrderValid = false;                                 // the set of owned tiles may have changed
   r->partPath.clear(); r->partRoot = 0;
   if (mode != EXA_PARTITION_SORT_LAST) return EXA_OK;
   int levels = 0; while ((1 << levels) < numRanks) levels++;

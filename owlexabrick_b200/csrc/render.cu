@@ -464,8 +464,18 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   __syncthreads();
 
   const int tilesX = (P.width + TILE_W - 1) / TILE_W;
-  const int tileId = blockIdx.x;
-  if (P.tileMode && (tileId % P.numRanks) != P.rank) return;
+  // Tile schedule: CTA q renders the q-th tile of the PREVIOUS frame's cost order (most expensive
+  // first: longest-processing-time-first keeps the SMs busy to the end of the frame; without it
+  // a few tiles of long rays finish alone).  Costs are CTA cycle counts, bucketed by log2; each
+  // frame writes the lists the next one reads.  Image-tile mode (multi-GPU, data replicated):
+  // rank r owns tiles r, r + numRanks, ...; the grid holds only the owned tiles.
+  const long long t_start = clock64();
+  int tileId;
+  if (P.tileOrderIn) {
+    int q = (int)blockIdx.x, b = TILE_BUCKETS - 1;
+    for (; b > 0; b--) { const int n = P.tileOrderIn->count[b]; if (q < n) break; q -= n; }
+    tileId = (int)P.tileOrderIn->list[(size_t)b * P.tileOrderCap + q];
+  } else tileId = P.tileMode ? P.rank + (int)blockIdx.x * P.numRanks : (int)blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // warp w covers the 8x4 sub-tile (w&1, w>>1) of the 16x8 CTA tile
   const int px = (tileId % tilesX) * TILE_W + (warp & 1) * 8 + (lane & 7);
@@ -586,6 +596,15 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     }
     if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], e); }
   }
+  if (P.tileOrderOut) {                                      // record this tile's cost for the next frame's schedule
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned long long cyc = (unsigned long long)(clock64() - t_start);
+      const int b = min(TILE_BUCKETS - 1, max(0, 63 - __clzll(cyc | 1ull) - 10));      // log2(cycles / 1024)
+      const int idx = atomicAdd(&P.tileOrderOut->count[b], 1);
+      P.tileOrderOut->list[(size_t)b * P.tileOrderCap + idx] = (uint32_t)tileId;
+    }
+  }
 }
 
 int launchRenderFrame(const RenderParams &P, cudaStream_t s)
@@ -593,7 +612,11 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   const int tilesX = (P.width + TILE_W - 1) / TILE_W, tilesY = (P.height + TILE_H - 1) / TILE_H;
   const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
-  const dim3 grid(tilesX * tilesY), block(FRAME_THREADS);
+  const int numTiles = tilesX * tilesY;
+  const int numMine = P.tileMode ? (numTiles - P.rank + P.numRanks - 1) / P.numRanks : numTiles;
+  if (numMine <= 0) return 0;
+  if (P.tileOrderOut) cudaMemsetAsync(P.tileOrderOut->count, 0, sizeof(int) * TILE_BUCKETS, s);
+  const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
 #define LAUNCH(G, S_, D_)                                                                                   \
   { cudaFuncSetAttribute(k_renderFrame<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \

@@ -5,6 +5,11 @@
 
 namespace exa {
 
+// tile cost order of one frame: per log2(cycles) bucket a count and a list of tile ids
+// (list[b * cap + i]); written by frame N, read by frame N+1 (render.cu:k_renderFrame)
+static const int TILE_BUCKETS = 16;
+struct TileOrder { int count[TILE_BUCKETS]; uint32_t list[1]; };   // list: TILE_BUCKETS * cap entries
+
 struct RenderParams {
   DeviceScene scene;
   // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
@@ -27,6 +32,8 @@ struct RenderParams {
   int tileMode, rank, numRanks;        // image-tile partition
   const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones
   unsigned long long *stats;           // 4 counters (ExaStats) or null
+  const TileOrder *tileOrderIn;        // previous frame's tile cost order (null: scan order)
+  TileOrder *tileOrderOut; int tileOrderCap;   // where this frame records its own (null: off)
   int kdStack;                         // stack entries per warp
   int warpUnits;                       // set by launchRenderFrame: 16-B units of shared memory per warp
   int dbg;                             // EXA_DEBUG builds only: print segments/samples

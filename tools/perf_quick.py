@@ -69,6 +69,28 @@ def main():
     pb = 16 * npts + 44 * pst["segments"] + 36 * pst["brickVisits"] + 4 * pst["cornerLoads"]
     out["points"] = {"us": round(1e3 * float(np.mean(ts)), 2), "alg_GBs": round(pb / np.mean(ts) / 1e6, 1), "visits_per_pt": round(pst["brickVisits"] / npts, 3), "corners_per_pt": round(pst["cornerLoads"] / npts, 3)}
     out["checksum"] = float(d_val.double().sum().item())
+    if os.environ.get("PQ_DIAG"):
+        # diagnostics: (a) points confined to a 128^3 box (data L2-resident), (b) the same random points sorted along x-major cells
+        def run(p_np):
+            dp = torch.from_numpy(np.ascontiguousarray(p_np)).cuda(); tt = []
+            for i in range(8):
+                flush.fill_(i); flush2.sum()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(stream); r.sample_points_device(dp.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr()); e1.record(stream)
+                torch.cuda.synchronize()
+                if i >= 3: tt.append(e0.elapsed_time(e1))
+            return round(1e3 * float(np.mean(tt)), 2)
+        c = domain / 2
+        out["points_local128_us"] = run(synth.random_points(npts, [c - 64] * 3, [c + 64] * 3, seed=2))
+        key = (pts[:, 2] // 16).astype(np.int64) * 4096 * 4096 + (pts[:, 1] // 16).astype(np.int64) * 4096 + (pts[:, 0] // 16).astype(np.int64)
+        out["points_sorted_us"] = run(pts[np.argsort(key, kind="stable")])
+        # no flush at all (everything that can be L2-resident is)
+        tt = []
+        for i in range(8):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream); r.sample_points_device(d_pts.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr()); e1.record(stream)
+            torch.cuda.synchronize(); tt.append(e0.elapsed_time(e1))
+        out["points_noflush_us"] = round(1e3 * float(np.mean(tt[3:])), 2)
     print(json.dumps(out), flush=True)
 
 
