@@ -161,30 +161,17 @@ def workload_name(name):
 # product arm
 # ---------------------------------------------------------------------------------------------
 def binary_swap(r, dist, torch, partial, npix, rank, world, rgba8_full):
-    """sort-last compositing: log2(N) rounds of half-image exchange (NCCL P2P) + fused "over",
-    then finish (accumulate, sRGB, pack) on the owned strip and all_gather of RGBA8 strips"""
-    lo, hi = 0, npix
-    rounds = world.bit_length() - 1
-    launches = 0
-    for rnd in range(rounds):
-        partner = rank ^ (1 << rnd)
-        mid = (lo + hi) // 2
-        keep_low = ((rank >> rnd) & 1) == 0
-        keep = (lo, mid) if keep_low else (mid, hi)
-        send = (mid, hi) if keep_low else (lo, mid)
-        recv_buf = torch.empty((keep[1] - keep[0], 4), dtype=torch.float32, device=partial.device)
-        ops = [dist.P2POp(dist.isend, partial[send[0]:send[1]], partner), dist.P2POp(dist.irecv, recv_buf, partner)]
-        for req in dist.batch_isend_irecv(ops):
-            req.wait()
-        r.composite_over(partial[keep[0]:keep[1]].data_ptr(), recv_buf.data_ptr(), keep[1] - keep[0], r.swap_order(rnd))
-        launches += 1
-        lo, hi = keep
-    strip = torch.empty(hi - lo, dtype=torch.int32, device=partial.device)
-    r.finish_pixels(partial[lo:hi].data_ptr(), lo, hi - lo, strip.data_ptr())
-    launches += 1
-    strips = [torch.empty_like(strip) for _ in range(world)]
-    dist.all_gather(strips, strip)
-    return strips, (lo, hi), launches
+    """sort-last compositing (owlexabrick_b200/multigpu.py) with the CUDA kernels of the library"""
+    from owlexabrick_b200 import multigpu
+
+    def composite(mine, other, front):
+        r.composite_over(mine.data_ptr(), other.data_ptr(), mine.shape[0], front)
+
+    def finish(pixels, first):
+        strip = torch.empty(pixels.shape[0], dtype=torch.int32, device=pixels.device)
+        r.finish_pixels(pixels.data_ptr(), first, pixels.shape[0], strip.data_ptr())
+        return strip
+    return multigpu.binary_swap(dist, torch, partial, rank, world, composite, r.swap_order, finish)
 
 
 def run_product(args):
@@ -236,14 +223,52 @@ def run_product(args):
     fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
     fd.apply(r)
     npix = W * H
-    if world > 1:
+    mode = "none" if world == 1 else args.partition
+    peer_fb = None
+    if mode == "sortlast":
         r.set_partition(capi.PARTITION_SORT_LAST, rank, world)
         partial = torch.zeros((npix, 4), dtype=torch.float32, device="cuda")
-        rgba8_full = None
+    elif mode == "tiles":
+        # data replicated, rank r renders tiles r, r+N, ...; every rank's frame kernel stores its
+        # RGBA8 tiles straight into rank 0's frame buffer over NVLink (CUDA IPC peer pointer), so
+        # the only per-frame exchange is a 4-byte all-reduce that orders the frame's completion
+        r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
+        import ctypes as C
+        hbuf = torch.zeros(64, dtype=torch.uint8)
+        if rank == 0:
+            _, fb0 = r.device_buffers()
+            capi.check(capi.lib.exa_ipc_export(C.c_void_p(fb0), C.c_void_p(hbuf.data_ptr())))
+        hdev = hbuf.cuda()
+        dist.broadcast(hdev, 0)
+        hbuf = hdev.cpu()
+        if rank != 0:
+            pp = C.c_void_p()
+            try:
+                capi.check(capi.lib.exa_ipc_import(C.c_void_p(hbuf.data_ptr()), local, C.byref(pp)))
+                peer_fb = pp.value
+                r.resizeFrameBuffer(peer_fb, (W, H))
+            except Exception as e:                                    # no peer mapping: fall back to an NCCL reduce of the frame
+                log("rank %d: CUDA IPC import failed (%s); using NCCL reduce" % (rank, e))
+        ok = torch.tensor([1 if (rank == 0 or peer_fb) else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        use_peer = bool(ok.item())
+        fb_t = None
+        if not use_peer:                                              # caller-owned torch frame buffers, summed onto rank 0
+            fb_t = torch.zeros(npix, dtype=torch.int32, device="cuda")
+            r.resizeFrameBuffer(fb_t.data_ptr(), (W, H)); peer_fb = None
+        done_flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        log("rank %d: image-tile mode, %s" % (rank, "peer frame buffer over NVLink" if use_peer else "NCCL reduce"))
 
     def step():
-        if world == 1:
+        if mode == "none":
             r.render(sync=False)
+            return 1
+        if mode == "tiles":
+            r.render(sync=False)
+            if use_peer:
+                dist.all_reduce(done_flag)                            # frame complete on every rank
+            else:
+                dist.reduce(fb_t, 0)                                  # tiles are disjoint and the rest is 0: sum = union (rank 0's copy is final)
             return 1
         r.render_partial(partial.data_ptr())
         _, _, k = binary_swap(r, dist, torch, partial, npix, rank, world, None)
@@ -255,8 +280,8 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(stats_t)
     tot = dict(zip(["samples", "brickVisits", "cornerLoads", "segments"], [int(x) for x in stats_t.tolist()]))
-    if world > 1:
-        r.set_partition(capi.PARTITION_SORT_LAST, rank, world)   # masks were refreshed by render_stats; keep state explicit
+    if mode == "tiles" and not use_peer:
+        fb_t.zero_()
 
     sampler = ClockSampler(local)          # samples clocks from the warm-up to the end of the e2e loop
     if rank == 0:
@@ -295,6 +320,13 @@ def run_product(args):
         if world == 1:
             r.render(sync=False)
             capi.check(capi.lib.exa_renderer_read_rgba8(r.h, host_img.data_ptr()))   # device -> host: W*H*4
+        elif mode == "tiles":
+            step()
+            if rank == 0:
+                if use_peer:
+                    capi.check(capi.lib.exa_renderer_read_rgba8(r.h, host_img.data_ptr()))
+                else:
+                    host_img.view(-1).copy_(fb_t, non_blocking=False)
         else:
             r.render_partial(partial.data_ptr())
             strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
@@ -327,6 +359,36 @@ def run_product(args):
 
     # ---- secondary measurement: the same frame with a translucent XF (opacity scale 0.02), which
     # makes rays traverse the whole volume instead of terminating after a few samples ----
+    # ---- multi-GPU check (untimed): the N-GPU frame against the same frame rendered by rank 0 alone ----
+    mg_check = None
+    if world > 1:
+        from owlexabrick_b200 import multigpu
+        if mode == "tiles":
+            step(); torch.cuda.synchronize(); dist.barrier()
+            if rank == 0:
+                img_n = r.read_rgba8().reshape(-1) if use_peer else fb_t.cpu().numpy().view(np.uint32)
+        else:
+            r.render_partial(partial.data_ptr())
+            strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
+            if rank == 0:
+                img_n = np.zeros(npix, np.uint32)
+                for k in range(world):
+                    lo, hi = multigpu.final_span(k, world, npix)
+                    img_n[lo:hi] = strips[k].cpu().numpy().view(np.uint32)
+        dist.barrier()
+        if rank == 0:
+            r.set_partition(capi.PARTITION_NONE, 0, 1)
+            r.resizeFrameBuffer(None, (W, H))
+            r.render()
+            img_1 = r.read_rgba8().reshape(-1)
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import scenes
+            dif = np.abs(scenes.unpack_rgba8(img_n) - scenes.unpack_rgba8(img_1))
+            mg_check = {"max_abs_rgba8_diff_vs_1gpu": int(dif.max()), "pixels_differing": int((dif.max(axis=-1) > 0).sum()),
+                        "note": "image tiles: bit-identical expected; sort-last: per-rank early termination (H1) bounds the deviation"}
+            log("multi-GPU check:", mg_check)
+        dist.barrier()
+
     translucent = None
     if world == 1:
         r.updateXF(0, alpha, rgb, fd.xf_domain[0], 0.02)
@@ -355,10 +417,12 @@ def run_product(args):
         d_val = torch.empty(npts, dtype=torch.float32, device="cuda")
         d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
         flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+        flush2 = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
         pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
         times = []
         for i in range(args.warmup + max(args.steps, 5)):
-            flush.fill_(i & 0xff)                                            # L2 flush between iterations
+            flush.fill_(i & 0xff)                                            # L2 flush between iterations: write 256 MiB,
+            flush2.sum()                                                     # then read 256 MiB so that L2 holds clean lines (no write-back inside the timed kernel)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record(stream)
             r.sample_points_device(d_pts.data_ptr(), npts, 0, d_val.data_ptr(), d_ok.data_ptr())
@@ -375,7 +439,7 @@ def run_product(args):
         peak, _ = peaks()
         recon = {"points": npts, "ms": pms, "samples_per_s": npts / (pms * 1e-3), "algorithmic_bytes": pbytes,
                  "achieved_gbs": pbytes / (pms * 1e-3) / 1e9, "frac": pbytes / (pms * 1e-3) / 1e9 / peak,
-                 "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB fill between iterations"}
+                 "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB write + 256 MiB read between iterations"}
 
     # ---- CPU baseline beside it (rank 0, N=1 only): the oracle on a bounded sample ----
     cpu = None
@@ -405,7 +469,9 @@ def run_product(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload_name(name), "cells": int(ncells), "bricks": bricks.num_bricks, "regions": int(len(regions)),
                            "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
-                           "parallelism": "1 GPU" if world == 1 else "sort-last kd partition x%d, NCCL binary swap" % world,
+                           "parallelism": "1 GPU" if world == 1 else ("sort-last kd partition x%d, NCCL binary swap" % world if mode == "sortlast" else
+                                           "image tiles x%d (data replicated), %s" % (world, "RGBA8 stored into rank 0's frame buffer over NVLink peer memory + 4-B all-reduce" if use_peer else "NCCL reduce of the RGBA8 frame")),
+                           "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
                            "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"]},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
@@ -414,7 +480,7 @@ def run_product(args):
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; most are served by L1/L2"},
-                "dvr_translucent": translucent, "recon": recon, "cpu_baseline": cpu}
+                "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
@@ -429,6 +495,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
     if args.impl == "reference":

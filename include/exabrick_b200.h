@@ -297,6 +297,14 @@ int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, s
 int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_compositedRGBA, size_t first,
                                size_t count, uint32_t *d_rgba8Out);
 
+/* Peer framebuffer (one process per GPU, one node): rank 0 exports its RGBA8 buffer, the other
+ * ranks import it and pass the pointer to exa_renderer_resize_framebuffer, so that in
+ * image-tile mode every rank's frame kernel stores its tiles straight into rank 0's frame
+ * buffer over NVLink (no gather).  handle = the 64 bytes of a cudaIpcMemHandle_t. */
+int exa_ipc_export(const void *d_ptr, uint8_t handle[64]);
+int exa_ipc_import(const uint8_t handle[64], int cudaDevice, void **d_ptr);
+int exa_ipc_close(void *d_ptr);
+
 #ifdef __cplusplus
 }
 #endif

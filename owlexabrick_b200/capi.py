@@ -46,6 +46,9 @@ _SIG = {
     "exa_last_error": (C.c_char_p, []),
     "exa_cuda_available": (i32, []),
     "exa_free": (None, [vp]),
+    "exa_ipc_export": (i32, [vp, vp]),
+    "exa_ipc_import": (i32, [vp, i32, C.POINTER(vp)]),
+    "exa_ipc_close": (i32, [vp]),
     "exa_set_scalar_layout": (i32, [i32]),
     "exa_renderer_get_scalar_layout": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
     "exa_bricks_build": (i32, [vp, sz, i32, i32, C.POINTER(vp)]),

@@ -283,6 +283,28 @@ void exa_renderer_destroy(exa_renderer_t *r)
   delete r;
 }
 
+int exa_ipc_export(const void *d_ptr, uint8_t handle[64])
+{
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t");
+  if (!d_ptr || !handle) { setError("exa_ipc_export: null argument"); return EXA_ERR_INVALID; }
+  cudaIpcMemHandle_t h;
+  CKR(cudaIpcGetMemHandle(&h, const_cast<void *>(d_ptr)));
+  memcpy(handle, &h, 64); return EXA_OK;
+}
+int exa_ipc_import(const uint8_t handle[64], int cudaDevice, void **d_ptr)
+{
+  if (!handle || !d_ptr) { setError("exa_ipc_import: null argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(cudaDevice));
+  cudaIpcMemHandle_t h; memcpy(&h, handle, 64);
+  CKR(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return EXA_OK;
+}
+int exa_ipc_close(void *d_ptr)
+{
+  if (!d_ptr) return EXA_OK;
+  CKR(cudaIpcCloseMemHandle(d_ptr)); return EXA_OK;
+}
+
 int exa_set_scalar_layout(int mode)
 {
   if (mode != EXA_LAYOUT_AUTO && mode != EXA_LAYOUT_FLAT && mode != EXA_LAYOUT_DUAL) { setError("exa_set_scalar_layout: bad mode"); return EXA_ERR_INVALID; }
