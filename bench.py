@@ -291,6 +291,33 @@ def run_product(args):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
+    # N>1, image tiles: the step (frame kernel + completion all-reduce) is a few tens of
+    # microseconds of GPU work, so it is captured once into a CUDA graph and replayed
+    graph, graph_launches = None, 0
+    if mode == "tiles" and args.graph:
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                r.set_stream(torch.cuda.current_stream().cuda_stream)
+                graph_launches = step()
+            graph = g
+        except Exception as e:
+            log("rank %d: CUDA graph capture failed (%s); eager steps" % (rank, e))
+        r.set_stream(stream.cuda_stream)
+        okg = torch.tensor([1 if graph is not None else 0], device="cuda")
+        dist.all_reduce(okg, op=dist.ReduceOp.MIN)
+        if not bool(okg.item()):
+            graph = None
+        if graph is not None:
+            eager_step = step
+
+            def step():                                              # noqa: F811
+                graph.replay()
+                return graph_launches
+            for _ in range(3):
+                step()
+            torch.cuda.synchronize()
+            dist.barrier()
     l0 = r.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
@@ -307,7 +334,7 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms = float(tms.item())
-    lib_launches = r.launch_count() - l0
+    lib_launches = (r.launch_count() - l0) if graph is None else launches   # graph replays do not pass through the library's counter
     ms_step = ms / args.steps
     value = tot["samples"] / (ms_step * 1e-3)
 
@@ -347,10 +374,15 @@ def run_product(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
     e2e_value = tot["samples"] / (e2e_s / args.steps)
-    if rank == 0:
-        # keep the GPU under the same load until nvidia-smi has produced a few samples
-        t = time.time()
-        while world == 1 and len(sampler.rows) < 5 and time.time() - t < 3.0:
+    # keep the GPU(s) under the same load until nvidia-smi has produced a few samples
+    t = time.time()
+    while True:
+        need = 1 if (rank == 0 and len(sampler.rows) < 5 and time.time() - t < 3.0) else 0
+        if world > 1:
+            nt = torch.tensor([need], device="cuda"); dist.broadcast(nt, 0); need = int(nt.item())
+        if not need:
+            break
+        for _ in range(50):
             step()
         torch.cuda.synchronize()
     clocks = sampler.finish() if rank == 0 else None
@@ -473,7 +505,8 @@ def run_product(args):
                                            "image tiles x%d (data replicated), %s" % (world, "RGBA8 stored into rank 0's frame buffer over NVLink peer memory + 4-B all-reduce" if use_peer else "NCCL reduce of the RGBA8 frame")),
                            "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
-                           "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"]},
+                           "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"],
+                           "step": "CUDA graph replay" if graph is not None else "eager launches"},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
                         "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
@@ -483,6 +516,10 @@ def run_product(args):
                 "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
+        if graph is not None:                                        # a live graph that captured NCCL work blocks the teardown
+            step = None
+            del graph, g
+            torch.cuda.synchronize()
         dist.barrier()
         dist.destroy_process_group()
 
@@ -495,6 +532,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="N>1 image tiles: capture the step into a CUDA graph (measured: no gain, the step is GPU-bound)")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup
