@@ -391,6 +391,27 @@ def run_product(args):
 
     # ---- secondary measurement: the same frame with a translucent XF (opacity scale 0.02), which
     # makes rays traverse the whole volume instead of terminating after a few samples ----
+    # ---- N>1 diagnostic: this rank's frame kernel alone (no completion exchange), max over ranks ----
+    render_only_ms = None
+    if world > 1 and mode == "tiles":
+        for _ in range(3):
+            r.render(sync=False)
+        torch.cuda.synchronize(); dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for _ in range(args.steps):
+            r.render(sync=False)
+        b.record(stream); torch.cuda.synchronize()
+        ro = torch.tensor([a.elapsed_time(b) / args.steps], dtype=torch.float64, device="cuda")
+        dist.all_reduce(ro, op=dist.ReduceOp.MAX)
+        render_only_ms = float(ro.item())
+        a.record(stream)
+        for _ in range(args.steps):
+            dist.all_reduce(done_flag)
+        b.record(stream); torch.cuda.synchronize()
+        log("rank %d: frame kernel alone %.4f ms/step, 4-byte all-reduce alone %.4f ms" % (rank, render_only_ms, a.elapsed_time(b) / args.steps))
+        dist.barrier()
+
     # ---- multi-GPU check (untimed): the N-GPU frame against the same frame rendered by rank 0 alone ----
     mg_check = None
     if world > 1:
@@ -513,7 +534,7 @@ def run_product(args):
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; most are served by L1/L2"},
-                "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "cpu_baseline": cpu}
+                "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
         if graph is not None:                                        # a live graph that captured NCCL work blocks the teardown

@@ -47,6 +47,7 @@ struct exa_renderer {
   float *d_traces = nullptr; size_t tracesCap = 0;
   unsigned long long *d_stats = nullptr;
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
+  LongRay *d_longQueue = nullptr; int *d_longCount = nullptr; int sampleBudget = 0;       // long-ray hand-over to k_renderLong; 0 = single pass (default: measured faster on C2)
   TileOrder *d_tileOrder[2] = {nullptr, nullptr}; int tileOrderCap = 0, tileOrderCur = 0; bool tileOrderValid = false;
 };
 
@@ -92,6 +93,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   P.traces = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
   P.stats = nullptr;
+  P.longQueue = r->d_longQueue; P.longCount = r->d_longCount; P.sampleBudget = r->sampleBudget;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
   P.kdStack = r->abr.depth + 2;
   P.dbg = 0;
@@ -279,7 +281,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   abrFree(r->abr);
   cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
   cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
-  cudaFree(r->d_traces); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]);
+  cudaFree(r->d_traces); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
   delete r;
 }
 
@@ -373,6 +375,12 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   if (fbPointer) r->d_rgba8 = (uint32_t *)fbPointer;
   else { CKR(cudaMalloc(&r->d_rgba8, n * 4)); CKR(cudaMemset(r->d_rgba8, 0, n * 4)); r->ownRgba8 = true; }
   r->width = width; r->height = height;
+  cudaFree(r->d_longQueue); r->d_longQueue = nullptr;
+  if (const char *e = getenv("EXA_SAMPLE_BUDGET")) r->sampleBudget = atoi(e);         // 0: single pass
+  if (r->sampleBudget > 0) {
+    CKR(cudaMalloc(&r->d_longQueue, sizeof(LongRay) * n));
+    if (!r->d_longCount) CKR(cudaMalloc(&r->d_longCount, 2 * sizeof(int)));
+  }
   for (int i = 0; i < 2; i++) { cudaFree(r->d_tileOrder[i]); r->d_tileOrder[i] = nullptr; }
   r->tileOrderCap = ((width + 15) / 16) * ((height + 7) / 8); r->tileOrderValid = false;
   if (!getenv("EXA_NO_TILE_ORDER"))

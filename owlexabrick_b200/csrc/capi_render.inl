@@ -29,8 +29,9 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
     P.tileOrderOut = r->d_tileOrder[r->tileOrderCur ^ 1];
     r->tileOrderCur ^= 1; r->tileOrderValid = true;
   }
-  if (launchRenderFrame(P, r->stream) < 0) { setError(std::string("frame kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
-  r->launches++;
+  const int nLaunched = launchRenderFrame(P, r->stream);
+  if (nLaunched < 0) { setError(std::string("frame kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += nLaunched;
   if (stats) {
     unsigned long long h[4];
     CKR(cudaMemcpyAsync(h, r->d_stats, 32, cudaMemcpyDeviceToHost, r->stream));

@@ -444,6 +444,20 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 // -----------------------------------------------------------------------------------------
 // __raygen__renderFrame (exabrick.cu:1576-1720): one thread per pixel, 8x4 pixel tile per warp
 // -----------------------------------------------------------------------------------------
+// final colour of a pixel (exabrick.cu:1701-1719): background blend (sic: premultiplied colour
+// times alpha again), progressive accumulation, sRGB, RGBA8 pack; or the raw premultiplied
+// partial in sort-last mode
+__device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, float4 pc, float3 bg)
+{
+  if (P.partialOut) { P.partialOut[pixelIdx] = pc; return; }
+  float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
+  if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
+  P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
+  const float inv = (float)P.frameID + 1.f;
+  color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
+  P.rgba8[pixelIdx] = make_rgba8(color);
+}
+
 #ifndef EXA_FRAME_MINBLOCKS
 #define EXA_FRAME_MINBLOCKS 5
 #endif
@@ -487,7 +501,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #endif
   // per-lane DVR state; the integration loop below is shared by all 32 lanes of the warp
   const int pixelIdx = px + P.width * py;
-  bool live = false;                                         // lane still has volume to integrate
+  bool live = false, parked = false;                         // lane still has volume to integrate / ray handed to k_renderLong
   float3 o = f3(0, 0, 0), d = f3(0, 0, 1), bg = f3(0, 0, 0);
   float4 pc = make_float4(0, 0, 0, 0);
   float offs = 0.f, already = 0.f, rayTmax = 0.f;
@@ -554,6 +568,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   {
     bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;
     float dtS = 0.f, t_i = 0.f, t_last = 0.f;
+    int budget = P.sampleBudget;
     for (;;) {
       if (__all_sync(FULL, !live)) break;
       if (live && !haveSeg) {
@@ -575,20 +590,22 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
         else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                             // :1698
         else t_i += dtS;
+        // A ray that is still alive after `sampleBudget` samples is a LONG ray: one lane stepping
+        // it sample by sample would be the critical path of the whole frame.  It is handed,
+        // with its state, to k_renderLong, where a full warp finishes it 32 samples at a time.
+        if (live && --budget <= 0 && P.longQueue) {
+          LongRay q;
+          q.ox = o.x; q.oy = o.y; q.oz = o.z; q.dx = d.x; q.dy = d.y; q.dz = d.z;
+          q.pcx = pc.x; q.pcy = pc.y; q.pcz = pc.z; q.pcw = pc.w;
+          q.offs = offs; q.already = already; q.rayTmax = rayTmax; q.t_i = t_i; q.t_last = t_last; q.haveSeg = haveSeg ? 1 : 0;
+          q.bgx = bg.x; q.bgy = bg.y; q.bgz = bg.z; q.pixelIdx = pixelIdx;
+          P.longQueue[atomicAdd(P.longCount, 1)] = q;              // capacity = width * height: cannot overflow
+          live = false; parked = true;
+        }
       }
     }
   }
-  if (inside) {
-    if (P.partialOut) P.partialOut[pixelIdx] = pc;
-    else {
-      float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
-      if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
-      P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
-      const float inv = (float)P.frameID + 1.f;
-      color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
-      P.rgba8[pixelIdx] = make_rgba8(color);
-    }
-  }
+  if (inside && !parked) writePixel(P, pixelIdx, pc, bg);
   if (STATS) {
     unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
     for (int o2 = 16; o2 > 0; o2 >>= 1) {
@@ -607,6 +624,88 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   }
 }
 
+// -----------------------------------------------------------------------------------------
+// k_renderLong: warp-cooperative continuation of the long rays parked by k_renderFrame.
+// One warp per ray (persistent warps pull rays from the queue).  The traversal state is
+// uniform across the warp (every lane walks the same kd stack); the 32 lanes take 32
+// consecutive lattice samples of the current region segment (t_i by repeated addition:
+// exactly the values of the sequential loop), each forms its sample's premultiplied
+// contribution, and an inclusive shuffle scan of the associative "over" operator yields
+// every prefix, hence the first sample at which alpha >= threshold (early termination,
+// exabrick.cu:1180) or the segment ends (:1184).  Same result as the sequential loop up to
+// fp32 re-association of the compositing sum.
+// -----------------------------------------------------------------------------------------
+template <bool GRAD, bool STATS, bool DUAL>
+__global__ void __launch_bounds__(FRAME_THREADS) k_renderLong(const __grid_constant__ RenderParams P)
+{
+  extern __shared__ uint4 smem[];
+  float4 *xfTables = reinterpret_cast<float4 *>(smem);
+  uint2 *stackBase = reinterpret_cast<uint2 *>(smem + P.numChannels * 128);
+  __shared__ float xfK[EXA_MAX_CHANNELS];
+  const int count = *P.longCount;                           // written by k_renderFrame, earlier on this stream
+  if (count == 0) return;
+  for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
+  if (threadIdx.x < P.numChannels) xfK[threadIdx.x] = 127.f / ((P.xfDomain[threadIdx.x][1] - P.xfDomain[threadIdx.x][0]) + 1e-20f);
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  RayStats rs = {0, 0, 0, 0};
+  for (;;) {
+    int qi = 0;
+    if (lane == 0) qi = atomicAdd(P.longCount + 1, 1);
+    qi = __shfl_sync(FULL, qi, 0);
+    if (qi >= count) break;
+    const LongRay q = P.longQueue[qi];                       // same address in every lane: broadcast
+    const float3 ro = f3(q.ox, q.oy, q.oz), rd = f3(q.dx, q.dy, q.dz);
+    float4 rp = make_float4(q.pcx, q.pcy, q.pcz, q.pcw);
+    // restart the ordered traversal at the ray's current tmin: it returns the segment the ray
+    // was parked in (same boxTest, same tmin), so no kd stack has to travel with the ray
+    Trav RT; travInit(RT, stackBase + warp, ro, rd, q.already, q.rayTmax, P.scene);
+    Segment rseg; rseg.blobOfs = 0; rseg.K = 0; rseg.t0 = rseg.t1 = 0.f; rseg.fcw = 1.f;
+    float rdt = 0.f, rti = q.t_i, rtl = q.t_last, ralready = q.already;
+    bool rHave = false, alive = true;
+    if (q.haveSeg) {
+      if (travNext(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg)) { rdt = P.dt * rseg.fcw; rHave = true; }
+      else alive = false;
+    }
+    while (alive) {
+      if (!rHave) {
+        if (!travNext(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg)) break;
+        rdt = P.dt * rseg.fcw; rti = firstLatticeT(rseg.t0, rdt, q.offs); rtl = rseg.t0; rHave = true;
+        if (STATS && lane == 0) rs.segments++;
+      }
+      float ti = rti; for (int j = 0; j < lane; j++) ti += rdt;   // t_i of lattice sample `lane`
+      const float tnext = fminf(ti, rseg.t1);
+      float tprev = __shfl_up_sync(FULL, tnext, 1); if (lane == 0) tprev = rtl;
+      const bool exists = lane == 0 || tprev < rseg.t1;
+      float4 c = make_float4(0, 0, 0, 0); RayStats bs = {0, 0, 0, 0};
+      if (exists) integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, rseg, ro, rd, 0.5f * (tnext + tprev), tnext - tprev, c, bs);
+#pragma unroll
+      for (int s2 = 1; s2 < 32; s2 <<= 1) {
+        const float4 f = make_float4(__shfl_up_sync(FULL, c.x, s2), __shfl_up_sync(FULL, c.y, s2), __shfl_up_sync(FULL, c.z, s2), __shfl_up_sync(FULL, c.w, s2));
+        if (lane >= s2) c = over(f, c);
+      }
+      const float4 tot = over(rp, c);
+      const bool ert = exists && tot.w >= P.ertThreshold, last = exists && tnext >= rseg.t1;
+      const unsigned stopMask = __ballot_sync(FULL, ert || last);
+      const int stop = stopMask ? __ffs(stopMask) - 1 : 31;
+      if (STATS && lane <= stop) { rs.samples += bs.samples; rs.visits += bs.visits; rs.corners += bs.corners; }
+      rp = make_float4(__shfl_sync(FULL, tot.x, stop), __shfl_sync(FULL, tot.y, stop), __shfl_sync(FULL, tot.z, stop), __shfl_sync(FULL, tot.w, stop));
+      if (stopMask) {
+        if (__shfl_sync(FULL, ert ? 1 : 0, stop)) { rp = make_float4(rp.x * rp.w, rp.y * rp.w, rp.z * rp.w, 1.f); break; }   // :1180, :1694-1697
+        rHave = false; ralready = rseg.t1 * 1.0000001f;                                                          // :1698
+      } else { rti = __shfl_sync(FULL, ti + rdt, 31); rtl = __shfl_sync(FULL, tnext, 31); }
+    }
+    if (lane == 0) writePixel(P, q.pixelIdx, rp, f3(q.bgx, q.bgy, q.bgz));
+  }
+  if (STATS) {
+    unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
+    for (int o2 = 16; o2 > 0; o2 >>= 1) {
+      a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); e += __shfl_xor_sync(FULL, e, o2);
+    }
+    if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], e); }
+  }
+}
+
 int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 {
   const int tilesX = (P.width + TILE_W - 1) / TILE_W, tilesY = (P.height + TILE_H - 1) / TILE_H;
@@ -618,15 +717,23 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   if (P.tileOrderOut) cudaMemsetAsync(P.tileOrderOut->count, 0, sizeof(int) * TILE_BUCKETS, s);
   const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
+  static int numSMs = 0;
+  if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); if (numSMs <= 0) numSMs = 148; }
+  const bool twoPass = P.longQueue != nullptr;
+  if (twoPass) cudaMemsetAsync(P.longCount, 0, 2 * sizeof(int), s);
+  const size_t smemLong = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS;
+  const dim3 gridLong(numSMs * 8);
 #define LAUNCH(G, S_, D_)                                                                                   \
   { cudaFuncSetAttribute(k_renderFrame<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \
-    k_renderFrame<G, S_, D_><<<grid, block, smemBytes, s>>>(P); }
+    k_renderFrame<G, S_, D_><<<grid, block, smemBytes, s>>>(P);                                           \
+    if (twoPass) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); \
+                   k_renderLong<G, S_, D_><<<gridLong, block, smemLong, s>>>(P); } }
 #define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }
   if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
   else { if (stats) LAUNCH_D(false, true) else LAUNCH_D(false, false) }
 #undef LAUNCH_D
 #undef LAUNCH
-  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+  return cudaGetLastError() == cudaSuccess ? (twoPass ? 2 : 1) : -1;
 }
 
 // -----------------------------------------------------------------------------------------

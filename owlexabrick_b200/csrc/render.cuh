@@ -10,6 +10,13 @@ namespace exa {
 static const int TILE_BUCKETS = 16;
 struct TileOrder { int count[TILE_BUCKETS]; uint32_t list[1]; };   // list: TILE_BUCKETS * cap entries
 
+// a long ray handed from k_renderFrame to k_renderLong (voxel-space ray + integration state)
+struct LongRay {
+  float ox, oy, oz, dx, dy, dz, pcx, pcy, pcz, pcw, offs, already, rayTmax, t_i, t_last;
+  int haveSeg; float bgx, bgy, bgz; int pixelIdx;
+};
+static_assert(sizeof(LongRay) == 80, "LongRay");
+
 struct RenderParams {
   DeviceScene scene;
   // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
@@ -32,6 +39,8 @@ struct RenderParams {
   int tileMode, rank, numRanks;        // image-tile partition
   const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones
   unsigned long long *stats;           // 4 counters (ExaStats) or null
+  LongRay *longQueue; int *longCount;  // long-ray queue (capacity width*height) and {count, head}; null: off
+  int sampleBudget;                    // samples a ray may take in k_renderFrame before it is handed over
   const TileOrder *tileOrderIn;        // previous frame's tile cost order (null: scan order)
   TileOrder *tileOrderOut; int tileOrderCap;   // where this frame records its own (null: off)
   int kdStack;                         // stack entries per warp
