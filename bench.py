@@ -244,6 +244,8 @@ def run_product(args):
         if rank != 0:
             pp = C.c_void_p()
             try:
+                if args.no_peer_fb:
+                    raise RuntimeError("--no-peer-fb")
                 capi.check(capi.lib.exa_ipc_import(C.c_void_p(hbuf.data_ptr()), local, C.byref(pp)))
                 peer_fb = pp.value
                 r.resizeFrameBuffer(peer_fb, (W, H))
@@ -402,6 +404,7 @@ def run_product(args):
         for _ in range(args.steps):
             r.render(sync=False)
         b.record(stream); torch.cuda.synchronize()
+        log("rank %d: own frame kernel %.4f ms/step" % (rank, a.elapsed_time(b) / args.steps))
         ro = torch.tensor([a.elapsed_time(b) / args.steps], dtype=torch.float64, device="cuda")
         dist.all_reduce(ro, op=dist.ReduceOp.MAX)
         render_only_ms = float(ro.item())
@@ -553,6 +556,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-peer-fb", action="store_true", help="N>1 image tiles: NCCL reduce of the frame instead of peer-memory stores")
     ap.add_argument("--graph", action="store_true", help="N>1 image tiles: capture the step into a CUDA graph (measured: no gain, the step is GPU-bound)")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()

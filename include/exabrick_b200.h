@@ -256,6 +256,10 @@ int exa_renderer_read_traces(exa_renderer_t *r, float *xyz /* numTraces*numTimes
 int exa_renderer_render(exa_renderer_t *r);
 int exa_renderer_render_async(exa_renderer_t *r);      /* no synchronise */
 int exa_renderer_sync(exa_renderer_t *r);
+/* histogram of the last frame's per-tile (16x8 pixels) cost: counts[b] = tiles whose CTA ran for
+ * [2^(b+10), 2^(b+11)) SM cycles (b = 15: or more).  The frame kernel schedules the next frame's
+ * tiles in descending order of these buckets. */
+int exa_renderer_get_tile_cost_histogram(exa_renderer_t *r, int counts[16]);
 /* headless read-back (replaces the GL blit of glutViewer/OWLViewer.cpp:140-197) */
 int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut);
 int exa_renderer_read_accum(exa_renderer_t *r, float *hostOutRGBA);

@@ -55,6 +55,16 @@ int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA)
   if (!d_partialRGBA) { setError("null partial buffer"); return EXA_ERR_INVALID; }
   return doRender(r, (float4 *)d_partialRGBA, nullptr, false);
 }
+int exa_renderer_get_tile_cost_histogram(exa_renderer_t *r, int counts[16])
+{
+  if (!r || !counts) { setError("null argument"); return EXA_ERR_INVALID; }
+  memset(counts, 0, 16 * sizeof(int));
+  if (!r->d_tileOrder[0] || !r->tileOrderValid) return EXA_OK;
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaStreamSynchronize(r->stream));
+  CKR(cudaMemcpy(counts, r->d_tileOrder[r->tileOrderCur]->count, 16 * sizeof(int), cudaMemcpyDeviceToHost));
+  return EXA_OK;
+}
 int exa_renderer_sync(exa_renderer_t *r)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }

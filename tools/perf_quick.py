@@ -48,6 +48,9 @@ def main():
         r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
         st = r.render_stats()
         ms = time_frames(a.steps)
+        import ctypes as C
+        hist = (C.c_int * 16)(); capi.check(capi.lib.exa_renderer_get_tile_cost_histogram(r.h, hist))
+        out[name + "_tile_cost_hist"] = list(hist)
         out[name] = {"ms": round(ms, 4), "Gsamples_s": round(st["samples"] / ms / 1e6, 3), "alg_GBs": round(bench.algorithmic_bytes(st, W, H) / ms / 1e6, 1)}
     for gs in (False, True):
         r.setGradientShadingDVR(gs)
