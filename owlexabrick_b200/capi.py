@@ -47,6 +47,7 @@ _SIG = {
     "exa_cuda_available": (i32, []),
     "exa_free": (None, [vp]),
     "exa_renderer_get_tile_cost_histogram": (i32, [vp, vp]),
+    "exa_renderer_debug_counters": (i32, [vp, vp]),
     "exa_ipc_export": (i32, [vp, vp]),
     "exa_ipc_import": (i32, [vp, i32, C.POINTER(vp)]),
     "exa_ipc_close": (i32, [vp]),

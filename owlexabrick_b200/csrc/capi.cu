@@ -265,7 +265,7 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
     for (int c = 0; c < numFields; c++) for (int i = 0; i < 128; i++) { float t = i / 127.f; lut[c * 128 + i] = make_float4(t, t, t, t); }
     CKC(cudaMemcpy(r->d_xf, lut.data(), sizeof(float4) * lut.size(), cudaMemcpyHostToDevice));
   }
-  CKC(cudaMalloc(&r->d_stats, 4 * sizeof(unsigned long long)));
+  CKC(cudaMalloc(&r->d_stats, 8 * sizeof(unsigned long long)));
 #undef CKC
   syncLaunchParams(r);
   *out = r;

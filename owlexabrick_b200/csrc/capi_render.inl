@@ -23,7 +23,7 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
   RenderParams P; fillParams(r, P);
   int rc = refreshMasks(r, P); if (rc) return rc;
   P.partialOut = partialOut;
-  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 32, r->stream)); P.stats = r->d_stats; }
+  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)
     if (r->tileOrderValid) P.tileOrderIn = r->d_tileOrder[r->tileOrderCur];
     P.tileOrderOut = r->d_tileOrder[r->tileOrderCur ^ 1];
@@ -65,6 +65,14 @@ int exa_renderer_get_tile_cost_histogram(exa_renderer_t *r, int counts[16])
   CKR(cudaMemcpy(counts, r->d_tileOrder[r->tileOrderCur]->count, 16 * sizeof(int), cudaMemcpyDeviceToHost));
   return EXA_OK;
 }
+int exa_renderer_debug_counters(exa_renderer_t *r, uint64_t out[4])
+{
+  if (!r || !out) { setError("null argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaStreamSynchronize(r->stream));
+  CKR(cudaMemcpy(out, r->d_stats + 4, 32, cudaMemcpyDeviceToHost));
+  return EXA_OK;
+}
 int exa_renderer_sync(exa_renderer_t *r)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
@@ -102,7 +110,7 @@ static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int ch
   CKR(cudaSetDevice(r->device));
   RenderParams RP; fillParams(r, RP);
   SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
-  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 32, r->stream)); P.stats = r->d_stats; }
+  if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   const int k = launchSamplePoints(P, r->stream);
   if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
   r->launches += k;

@@ -80,11 +80,13 @@ __device__ __forceinline__ void accZero(Acc &a) { a.sw = 0.f; a.swv = 0.f; a.sd 
 // into differences of the same partial sums.  Same real-number result as the reference's
 // corner loop, different fp32 rounding order (gate: 1e-5 relative).
 template <bool GRAD, bool STATS, bool DUAL>
-__device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hdrs, int k, const void *__restrict__ chanV,
+__device__ __forceinline__ void accumBricks(Acc &a, const U8 &hdr0, const uint4 *__restrict__ hdrs, int k, const void *__restrict__ chanV,
                                             float px, float py, float pz, unsigned &nCorners)
 {
   for (int i = 0; i < k; i++) {
-    const U8 hdr = ldg256(hdrs + 2 * i);
+    // the first brick's header travels with the region segment (registers): for the common
+    // one-brick region a sample has ONE dependent load (the record), not header -> record
+    const U8 hdr = i == 0 ? hdr0 : ldg256(hdrs + 2 * i);
     const uint4 u0 = hdr.lo, u1 = hdr.hi;
     const float invCw = __uint_as_float(u0.w);
     const int sx = (int)u1.x, sy = (int)u1.y, sz = (int)u1.z;
@@ -142,6 +144,25 @@ __device__ __forceinline__ void accumBricks(Acc &a, const uint4 *__restrict__ hd
       a.sdc.y += (wsz * wsx) * ((y1 ? 1.f : 0.f) - (y0 ? 1.f : 0.f));
       a.sdc.z += (wsy * wsx) * ((z1 ? 1.f : 0.f) - (z0 ? 1.f : 0.f));
     }
+  }
+}
+
+// L1 prefetch of the dual-cell record the NEXT lattice sample of this segment will read from the
+// segment's first brick (its address depends only on the ray parameter): takes the L2/DRAM
+// latency of the one dependent load off the per-sample critical path.
+template <bool DUAL>
+__device__ __forceinline__ void prefetchRecord(const U8 &hdr, const void *chanV, float px, float py, float pz)
+{
+  if (!DUAL) return;
+  const float invCw = __uint_as_float(hdr.lo.w);
+  const int sx = (int)hdr.hi.x, sy = (int)hdr.hi.y, sz = (int)hdr.hi.z;
+  const int ix0 = max(-1, (int)floorf((px - __uint_as_float(hdr.lo.x)) * invCw - 0.5f));
+  const int iy0 = max(-1, (int)floorf((py - __uint_as_float(hdr.lo.y)) * invCw - 0.5f));
+  const int iz0 = max(-1, (int)floorf((pz - __uint_as_float(hdr.lo.z)) * invCw - 0.5f));
+  if (ix0 < sx && iy0 < sy && iz0 < sz) {
+    const int rx = sx + 1, ry = sy + 1;
+    const float4 *rec = reinterpret_cast<const float4 *>(chanV) + 2 * ((size_t)hdr.hi.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry)));
+    asm volatile("prefetch.global.L1 [%0];" :: "l"(rec));
   }
 }
 
@@ -224,12 +245,15 @@ struct Trav {
   uint2 *stack;          // this thread's column: entry e at stack[e * blockDim.x]  {node, tf bits}
   int sp;
   int cur; float tn, tf; // node being descended (-1: pop)
+  unsigned visits;       // kd nodes touched so far (instrumentation)
   float3 o, d;
+  float3 invd;           // 1/d (IEEE): plane distances at inner nodes are (split - o) * invd; they only order and cull
 };
 
 __device__ __forceinline__ void travInit(Trav &T, uint2 *stack, float3 o, float3 d, float tmin, float tmax, const DeviceScene &S)
 {
-  T.stack = stack; T.sp = 0; T.o = o; T.d = d; T.cur = -1; T.tn = 0.f; T.tf = 0.f;
+  T.stack = stack; T.sp = 0; T.o = o; T.d = d; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.visits = 0;
+  T.invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
   float t0, t1;
   if (boxTest(o, d, tmin, tmax, S.boundsLo, S.boundsHi, t0, t1)) {
     // widen a little: node intervals are only used for culling, leaves do the exact test
@@ -237,58 +261,82 @@ __device__ __forceinline__ void travInit(Trav &T, uint2 *stack, float3 o, float3
   }
 }
 
-struct Segment { uint32_t blobOfs; int K; float t0, t1, fcw; };
+struct Segment { uint32_t blobOfs; int K; float t0, t1, fcw; U8 hdr0; };   // hdr0: header of the region's first brick
 
-// Finds the next region (front-to-back) with t0 = max(tmin, entry) < t1 = min(tmax, exit)
-// (exabrick.cu:213-238).  Inner nodes use one IEEE division for the plane distance (the same
-// expression boxTest evaluates for that face); leaves run the reference's boxTest verbatim.
+// One step of the ordered kd traversal: pop if needed, then visit one node.  Returns 0 = keep
+// going, 1 = `seg` holds the next region (front-to-back) with t0 = max(tmin, entry) < t1 =
+// min(tmax, exit) (exabrick.cu:213-238), 2 = traversal exhausted.  Inner nodes only order and
+// cull (plane distance by reciprocal, intervals widened by eps); leaves run the reference's
+// boxTest verbatim, which alone decides t0/t1.
+__device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
+                                        float tmin, float tmax, Segment &seg)
+{
+  const int stride = blockDim.x;
+  if (T.cur < 0) {
+    if (T.sp == 0) return 2;
+    T.sp--;
+    const uint2 e = T.stack[T.sp * stride];
+    T.cur = (int)e.x; T.tf = __uint_as_float(e.y);
+    T.tn = tmin;                                     // conservative: everything before tmin is done
+  }
+  T.visits++;
+  if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || !active[T.cur]) { T.cur = -1; return 0; }
+  const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + T.cur);
+  const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
+  if (axis == 3) {
+    T.cur = -1;
+    if (payload == KD_EMPTY) return 0;
+    const U8 hb = ldg256(S.blobs + payload);
+    const uint4 h0 = hb.lo, h1 = hb.hi;
+    const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
+    const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
+    if (boxTest(T.o, T.d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
+      seg.blobOfs = payload; seg.K = (int)raw.x; seg.fcw = __uint_as_float(h1.z);
+      seg.hdr0 = ldg256(S.blobs + payload + BLOB_HDR_UNITS);
+      return 1;
+    }
+    return 0;
+  }
+  const float split = __uint_as_float(raw.x);
+  const float oa = comp(T.o, (int)axis), da = comp(T.d, (int)axis);
+  const float tp = (split - oa) * comp(T.invd, (int)axis);
+  const bool belowFirst = (oa < split) || (oa == split && da <= 0.f);
+  const int first = (int)payload + (belowFirst ? 0 : 1), second = (int)payload + (belowFirst ? 1 : 0);
+  const float eps = 1e-5f * fabsf(tp) + 1e-6f;
+  if (tp != tp) {                                    // ray inside the plane: visit both halves
+    T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
+    T.sp++; T.cur = first;
+  } else if (tp > T.tf + eps || tp <= 0.f) {
+    T.cur = first;
+  } else if (tp < T.tn - eps) {
+    T.cur = second;
+  } else {
+    T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
+    T.sp++;
+    T.cur = first; T.tf = tp + eps;
+  }
+  return 0;
+}
+
+// next region of ONE ray; callable from divergent code (iso pass)
 __device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
                                          float tmin, float tmax, Segment &seg)
 {
-  const int stride = blockDim.x;
-  for (;;) {
-    if (T.cur < 0) {
-      if (T.sp == 0) return false;
-      T.sp--;
-      const uint2 e = T.stack[T.sp * stride];
-      T.cur = (int)e.x; T.tf = __uint_as_float(e.y);
-      T.tn = tmin;                                   // conservative: everything before tmin is done
-    }
-    if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || !active[T.cur]) { T.cur = -1; continue; }
-    const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + T.cur);
-    const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
-    if (axis == 3) {
-      T.cur = -1;
-      if (payload == KD_EMPTY) continue;
-      const U8 hb = ldg256(S.blobs + payload);
-      const uint4 h0 = hb.lo, h1 = hb.hi;
-      const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
-      const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
-      if (boxTest(T.o, T.d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
-        seg.blobOfs = payload; seg.K = (int)raw.x; seg.fcw = __uint_as_float(h1.z);
-        return true;
-      }
-      continue;
-    }
-    const float split = __uint_as_float(raw.x);
-    const float oa = comp(T.o, (int)axis), da = comp(T.d, (int)axis);
-    const float tp = (split - oa) / da;
-    const bool belowFirst = (oa < split) || (oa == split && da <= 0.f);
-    const int first = (int)payload + (belowFirst ? 0 : 1), second = (int)payload + (belowFirst ? 1 : 0);
-    const float eps = 1e-5f * fabsf(tp) + 1e-6f;
-    if (tp != tp) {                                  // ray inside the plane: visit both halves
-      T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
-      T.sp++; T.cur = first;
-    } else if (tp > T.tf + eps || tp <= 0.f) {
-      T.cur = first;
-    } else if (tp < T.tn - eps) {
-      T.cur = second;
-    } else {
-      T.stack[T.sp * stride] = make_uint2((uint32_t)second, __float_as_uint(T.tf));
-      T.sp++;
-      T.cur = first; T.tf = tp + eps;
-    }
+  for (;;) { const int r = travStep(T, S, active, tmin, tmax, seg); if (r) return r == 1; }
+}
+
+// next region for every lane with `need` set; must be called by ALL 32 lanes of the warp.  The
+// lanes advance in lock step, one node visit per trip, until the last one has its answer: the
+// cost is the LONGEST lane's node count.  (With per-lane loops and early returns the lanes of a
+// warp ran their traversals one after the other: measured ~5000 cycles per call on C1/C2.)
+__device__ __forceinline__ bool travNextWarp(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
+                                             float tmin, float tmax, Segment &seg, bool need)
+{
+  bool found = false;
+  while (__any_sync(FULL, need)) {
+    if (need) { const int r = travStep(T, S, active, tmin, tmax, seg); if (r) { need = false; found = r == 1; } }
   }
+  return found;
 }
 
 // common sample-lattice set-up of integrateBrick / isoIntegrateBrick (exabrick.cu:1141-1144)
@@ -317,7 +365,7 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
 {
   Acc a; accZero(a);
   unsigned nc = 0;
-  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + seg.blobOfs + BLOB_HDR_UNITS, seg.K, chanBase<DUAL>(S, channel), pos.x, pos.y, pos.z, nc);
+  accumBricks<GRAD, STATS, DUAL>(a, seg.hdr0, S.blobs + seg.blobOfs + BLOB_HDR_UNITS, seg.K, chanBase<DUAL>(S, channel), pos.x, pos.y, pos.z, nc);
   if (STATS) { rs.samples++; rs.visits += seg.K; rs.corners += nc; }
   return accFinish<GRAD>(a, value, g);
 }
@@ -458,13 +506,19 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
   P.rgba8[pixelIdx] = make_rgba8(color);
 }
 
+#ifndef EXA_PREFETCH
+#define EXA_PREFETCH 0      // next-record L1 prefetch: measured slower on C2 (extra address math on an issue-bound kernel)
+#endif
 #ifndef EXA_FRAME_MINBLOCKS
 #define EXA_FRAME_MINBLOCKS 5
 #endif
 static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
-template <bool GRAD, bool STATS, bool DUAL>
+// ISO: the implicit iso-surface pass is compiled in only when an iso-surface is enabled; the plain
+// DVR instantiation is less than half the code, which matters because every CTA runs through
+// the kernel once, front to back (instruction fetch, not data, is what a lone CTA waits for).
+template <bool GRAD, bool STATS, bool DUAL, bool ISO>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
@@ -484,6 +538,9 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // frame writes the lists the next one reads.  Image-tile mode (multi-GPU, data replicated):
   // rank r owns tiles r, r + numRanks, ...; the grid holds only the owned tiles.
   const long long t_start = clock64();
+#ifdef EXA_PHASE_TIMING
+  long long ph_setup = 0, ph_trav = 0, ph_sample = 0, ph_iters = 0, ph_t;
+#endif
   int tileId;
   if (P.tileOrderIn) {
     int q = (int)blockIdx.x, b = TILE_BUCKETS - 1;
@@ -505,7 +562,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   float3 o = f3(0, 0, 0), d = f3(0, 0, 1), bg = f3(0, 0, 0);
   float4 pc = make_float4(0, 0, 0, 0);
   float offs = 0.f, already = 0.f, rayTmax = 0.f;
-  Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.o = o; T.d = d;
+  Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.o = o; T.d = d; T.visits = 0; T.invd = f3(0, 0, 0);
   if (inside) {
     uint2 *stack = stackBase + threadIdx.x;
     float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
@@ -520,7 +577,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     float tmin = 1e-6f, tmax = 1e8f;
     // ---- surfaces: implicit iso-surfaces (traceSurfaces :1514-1527, traceIsoRay :1408-1460)
     int surfPrim = -1; float surfT = tmax; float3 surfNg = f3(0, 0, 0), surfBase = f3(0, 0, 0); float surfAmbient = 0.f;
-    if (P.anyIso) {
+    if (ISO && P.anyIso) {
       const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
       const float dtScale = len3nc(vd); vd = normalize3nc(vd);
       float already = dtScale * tmin; float rtmax = tmax;
@@ -559,6 +616,9 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     travInit(T, stack, o, d, already, rayTmax, P.scene);
     live = true;
   }
+#ifdef EXA_PHASE_TIMING
+  ph_setup = clock64() - t_start;
+#endif
   // ---- DVR region loop (:1675-1699) + integrateBrick's sample loop (:1141-1184), flattened into
   // one per-lane state machine: each trip, lanes without a current region segment advance the kd
   // traversal to their next one, then every live lane takes exactly ONE lattice sample.  With the
@@ -571,8 +631,13 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     int budget = P.sampleBudget;
     for (;;) {
       if (__all_sync(FULL, !live)) break;
-      if (live && !haveSeg) {
-        if (!travNext(T, P.scene, P.volActive, already, rayTmax, seg)) live = false;
+#ifdef EXA_PHASE_TIMING
+      ph_t = clock64(); ph_iters++;
+#endif
+      const bool need = live && !haveSeg;
+      const bool got = travNextWarp(T, P.scene, P.volActive, already, rayTmax, seg, need);
+      if (need) {
+        if (!got) live = false;
         else {
           dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0; haveSeg = true;
           if (STATS) rs.segments++;
@@ -581,6 +646,9 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #endif
         }
       }
+#ifdef EXA_PHASE_TIMING
+      __syncwarp(); ph_trav += clock64() - ph_t; ph_t = clock64();
+#endif
       if (live) {
         const float t_next = fminf(t_i, seg.t1);
         const float t_sample = 0.5f * (t_next + t_last);
@@ -589,7 +657,14 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
         integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
         if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
         else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                             // :1698
-        else t_i += dtS;
+        else {
+          t_i += dtS;
+#if EXA_PREFETCH
+          const float tn2 = fminf(t_i, seg.t1);
+          const float3 pn = rayAt(o, d, 0.5f * (tn2 + t_last));
+          prefetchRecord<DUAL>(seg.hdr0, chanBase<DUAL>(P.scene, 0), pn.x, pn.y, pn.z);
+#endif
+        }
         // A ray that is still alive after `sampleBudget` samples is a LONG ray: one lane stepping
         // it sample by sample would be the critical path of the whole frame.  It is handed,
         // with its state, to k_renderLong, where a full warp finishes it 32 samples at a time.
@@ -605,7 +680,20 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       }
     }
   }
+#ifdef EXA_PHASE_TIMING
+  ph_sample = clock64() - t_start - ph_setup - ph_trav;
+  const long long ph_before_write = clock64() - t_start;
+#endif
   if (inside && !parked) writePixel(P, pixelIdx, pc, bg);
+#ifdef EXA_PHASE_TIMING
+  if (lane == 0 && (blockIdx.x % 997) == 0 && P.frameID == 77)
+    printf("CTA %d warp %d tile %d: setup %lld, loop trips %lld, traversal %lld, sampling+rest %lld, total-before-write %lld, total %lld cycles\n",
+           (int)blockIdx.x, warp, tileId, ph_setup, ph_iters, ph_trav, ph_sample, ph_before_write, (long long)(clock64() - t_start));
+#endif
+  if (STATS && P.stats && inside) {                          // instrumentation: per-ray maxima
+    atomicMax(&P.stats[4], (unsigned long long)T.visits); atomicAdd(&P.stats[6], (unsigned long long)T.visits);
+    atomicMax(&P.stats[5], (unsigned long long)(P.sampleBudget > 0 ? 0 : rs.samples));
+  }
   if (STATS) {
     unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
     for (int o2 = 16; o2 > 0; o2 >>= 1) {
@@ -664,12 +752,12 @@ __global__ void __launch_bounds__(FRAME_THREADS) k_renderLong(const __grid_const
     float rdt = 0.f, rti = q.t_i, rtl = q.t_last, ralready = q.already;
     bool rHave = false, alive = true;
     if (q.haveSeg) {
-      if (travNext(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg)) { rdt = P.dt * rseg.fcw; rHave = true; }
+      if (travNextWarp(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg, true)) { rdt = P.dt * rseg.fcw; rHave = true; }
       else alive = false;
     }
     while (alive) {
       if (!rHave) {
-        if (!travNext(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg)) break;
+        if (!travNextWarp(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg, true)) break;
         rdt = P.dt * rseg.fcw; rti = firstLatticeT(rseg.t0, rdt, q.offs); rtl = rseg.t0; rHave = true;
         if (STATS && lane == 0) rs.segments++;
       }
@@ -723,10 +811,15 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   if (twoPass) cudaMemsetAsync(P.longCount, 0, 2 * sizeof(int), s);
   const size_t smemLong = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS;
   const dim3 gridLong(numSMs * 8);
+  // cudaFuncSetAttribute is a slow driver call: raise each instantiation's dynamic shared memory
+  // limit only when it has to grow
 #define LAUNCH(G, S_, D_)                                                                                   \
-  { cudaFuncSetAttribute(k_renderFrame<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); \
-    k_renderFrame<G, S_, D_><<<grid, block, smemBytes, s>>>(P);                                           \
-    if (twoPass) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); \
+  { static size_t capF = 0, capL = 0;                                                                       \
+    if (smemBytes > capF) { cudaFuncSetAttribute(k_renderFrame<G, S_, D_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
+                            cudaFuncSetAttribute(k_renderFrame<G, S_, D_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capF = smemBytes; } \
+    if (P.anyIso) k_renderFrame<G, S_, D_, true><<<grid, block, smemBytes, s>>>(P);                       \
+    else k_renderFrame<G, S_, D_, false><<<grid, block, smemBytes, s>>>(P);                               \
+    if (twoPass) { if (smemLong > capL) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); capL = smemLong; } \
                    k_renderLong<G, S_, D_><<<gridLong, block, smemLong, s>>>(P); } }
 #define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }
   if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
@@ -775,7 +868,7 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
   uint32_t bo; int K;
   if (!locate(S, px, py, pz, bo, K)) return false;
   Acc a; accZero(a);
-  accumBricks<GRAD, STATS, DUAL>(a, S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
+  accumBricks<GRAD, STATS, DUAL>(a, ldg256(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
   return accFinish<GRAD>(a, value, g);
 }

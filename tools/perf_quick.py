@@ -47,6 +47,9 @@ def main():
     for name, scale in (("opaque", 1.0), ("translucent", 0.02)):
         r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
         st = r.render_stats()
+        import ctypes as C
+        dbg = (C.c_uint64 * 4)(); capi.check(capi.lib.exa_renderer_debug_counters(r.h, dbg))
+        out[name + "_dbg"] = {"max_kd_nodes_per_ray": int(dbg[0]), "max_samples_per_ray": int(dbg[1]), "kd_nodes_total": int(dbg[2]), "segments": st["segments"]}
         ms = time_frames(a.steps)
         import ctypes as C
         hist = (C.c_int * 16)(); capi.check(capi.lib.exa_renderer_get_tile_cost_histogram(r.h, hist))
