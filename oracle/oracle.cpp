@@ -337,7 +337,33 @@ struct OrcScene {
   // uniform grid for point location (oracle-private accelerator; regions are disjoint
   // half-open boxes, so the result equals a brute-force search)
   float glo[3], ghi[3]; int G; std::vector<int> cellStart, cellItems;
+  // bounding-volume hierarchy over the region boxes for the closest-region ray query
+  // (oracle-private accelerator standing in for the OptiX BVH; returns exactly what the
+  // brute-force loop returns, see closestRegion); ORC_BRUTE_FORCE=1 disables it
+  struct BvhNode { float lo[3], hi[3]; int left, right, first, count; };
+  std::vector<BvhNode> bvh; std::vector<int> bvhItems; bool useBvh;
 };
+
+static int buildBvh(OrcScene &s, int first, int count)
+{
+  OrcScene::BvhNode n; n.left = n.right = -1; n.first = first; n.count = count;
+  for (int d = 0; d < 3; d++) { n.lo[d] = INFINITY; n.hi[d] = -INFINITY; }
+  for (int i = first; i < first + count; i++) {
+    const OrcRegion &r = s.regions[s.bvhItems[i]];
+    for (int d = 0; d < 3; d++) { n.lo[d] = std::min(n.lo[d], r.lo[d]); n.hi[d] = std::max(n.hi[d], r.hi[d]); }
+  }
+  const int id = (int)s.bvh.size(); s.bvh.push_back(n);
+  if (count > 4) {
+    int axis = 0;
+    for (int d = 1; d < 3; d++) if (n.hi[d] - n.lo[d] > n.hi[axis] - n.lo[axis]) axis = d;
+    auto key = [&](int ri) { return s.regions[ri].lo[axis] + s.regions[ri].hi[axis]; };
+    std::nth_element(s.bvhItems.begin() + first, s.bvhItems.begin() + first + count / 2, s.bvhItems.begin() + first + count,
+                     [&](int a, int b) { return key(a) < key(b); });
+    const int l = buildBvh(s, first, count / 2), r = buildBvh(s, first + count / 2, count - count / 2);
+    s.bvh[id].left = l; s.bvh[id].right = r; s.bvh[id].count = 0;
+  }
+  return id;
+}
 
 extern "C" OrcScene *orc_scene_create(const OrcBrick *bricks, int64_t nb, const float *scalars,
                                       int64_t numCells, int numFields,
@@ -366,6 +392,9 @@ extern "C" OrcScene *orc_scene_create(const OrcBrick *bricks, int64_t nb, const 
   }
   s->cellStart.resize(lists.size() + 1); s->cellStart[0] = 0;
   for (size_t i = 0; i < lists.size(); i++) s->cellStart[i + 1] = s->cellStart[i] + (int)lists[i].size();
+  s->bvhItems.resize(nr); for (int64_t i = 0; i < nr; i++) s->bvhItems[i] = (int)i;
+  s->useBvh = nr > 0 && !(getenv("ORC_BRUTE_FORCE") && atoi(getenv("ORC_BRUTE_FORCE")));
+  if (s->useBvh) buildBvh(*s, 0, (int)nr);
   s->cellItems.resize(s->cellStart.back());
   for (size_t i = 0; i < lists.size(); i++) std::copy(lists[i].begin(), lists[i].end(), s->cellItems.begin() + s->cellStart[i]);
   return s;
@@ -551,6 +580,28 @@ static inline bool boxTest(const Ray &r, const float lo[3], const float hi[3], f
 static int closestRegion(const OrcScene &s, const std::vector<uint8_t> &active, const Ray &r, float &t0, float &t1)
 {
   int best = -1; float bt0 = 0, bt1 = 0;
+  if (s.useBvh) {
+    // Same answer as the loop below: a region's [a,b) lies inside its ancestors' (fp subtraction
+    // and division are monotonic), so a node whose own box test fails, or whose entry is
+    // strictly behind the best entry found so far, cannot hold the winner; ties keep the
+    // lowest region ID.
+    int stack[64], sp = 0; stack[sp++] = 0;
+    while (sp) {
+      const OrcScene::BvhNode &n = s.bvh[stack[--sp]];
+      float a, b;
+      if (!boxTest(r, n.lo, n.hi, a, b)) continue;
+      if (best >= 0 && a > bt0) continue;
+      if (n.left < 0) {
+        for (int i = n.first; i < n.first + n.count; i++) {
+          const int ri = s.bvhItems[i];
+          if (!active[ri]) continue;
+          if (!boxTest(r, s.regions[ri].lo, s.regions[ri].hi, a, b)) continue;
+          if (best < 0 || a < bt0 || (a == bt0 && ri < best)) { best = ri; bt0 = a; bt1 = b; }
+        }
+      } else { stack[sp++] = n.left; stack[sp++] = n.right; }
+    }
+    t0 = bt0; t1 = bt1; return best;
+  }
   for (size_t i = 0; i < s.regions.size(); i++) {
     if (!active[i]) continue;
     float a, b;

@@ -159,3 +159,26 @@ def test_streamlines_uniform_flow(orc):
     assert np.allclose(tr[0, 5], [7, 4.5, 8], atol=1e-4)
     assert np.allclose(tr[1, 3], [13, 4.5, 4], atol=1e-4)
     assert (tr[1, 8:] >= 2e10).all()     # left the brick's basis domain -> dead
+
+
+def test_bvh_region_query_equals_brute_force(orc, monkeypatch):
+    """the oracle's private BVH for the closest-region ray query (stand-in for the OptiX BVH of
+    exabrick.cu:184-238) must return exactly what the brute-force loop over all regions returns"""
+    import scenes
+    from owlexabrick_b200 import renderer as R
+    cells, fields, dom = scenes.small_scene("nb64_off", 2)
+    raw = orc.build_bricks(cells)
+    bricks, ids = orc.parse_bricks(raw)
+    sc = orc.flatten_scalars(ids, fields)
+    regions, leaf = orc.build_abr(bricks, sc)
+    fd = scenes.FrameDesc(80, 60, R.default_camera([0] * 3, [dom] * 3, 80, 60), 2)
+    fd.opacity_scale = 0.1
+    fd.iso = [(1, 0.5, 0), (0, 0.0, 0)]
+    out = []
+    for brute in ("0", "1"):
+        monkeypatch.setenv("ORC_BRUTE_FORCE", brute)
+        scene = orc.Scene(bricks, sc, regions, leaf)
+        acc, rgba, st = scene.render(fd.to_orc(orc))
+        out.append((acc.copy(), rgba.copy(), dict(st)))
+    assert out[0][0].tobytes() == out[1][0].tobytes() and out[0][1].tobytes() == out[1][1].tobytes()
+    assert out[0][2] == out[1][2]
