@@ -353,13 +353,18 @@ def run_product(args):
 
     # ---- end to end through the C ABI with host buffers (N=1 path; at N>1 rank 0's read-back) ----
     host_img = torch.empty((H, W), dtype=torch.int32).pin_memory()
+    host_ring = [host_img, torch.empty((H, W), dtype=torch.int32).pin_memory()]
     alpha, rgb = fd.xf[0]
+    e2e_count = [0]
     def e2e_step():
         r.updateCamera(*fd.cam)
-        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)       # host -> device: 128 float4
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)       # host -> device: 128 float4 (stream-ordered, pinned ring)
         if world == 1:
+            # every frame is rendered from this step's inputs and read back to (pinned) host memory;
+            # the copy of frame i runs on the copy stream while frame i+1 renders into the second buffer
             r.render(sync=False)
-            capi.check(capi.lib.exa_renderer_read_rgba8(r.h, host_img.data_ptr()))   # device -> host: W*H*4
+            capi.check(capi.lib.exa_renderer_read_rgba8_async(r.h, host_ring[e2e_count[0] & 1].data_ptr()))   # device -> host: W*H*4
+            e2e_count[0] += 1
         elif mode == "tiles":
             step()
             if rank == 0:
@@ -380,6 +385,7 @@ def run_product(args):
     t = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
+    r.sync()                                                         # render stream + copy stream: the last frame is in host memory
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")

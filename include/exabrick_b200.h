@@ -220,6 +220,10 @@ int exa_renderer_set_voxel_space_transform(exa_renderer_t *r, const float xfm12[
 /* resizeFrameBuffer(fbPointer, size) (:341-355). fbPointer: caller-owned RGBA8 buffer that
  * device code can write (device or managed memory), or NULL to let the renderer own one. */
 int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int width, int height);
+/* swap the RGBA8 target without touching the accumulation buffer (double-buffered read-back:
+ * frame i+1 renders into one caller-owned buffer while frame i's is copied to the host).
+ * NULL: back to a renderer-owned buffer. */
+int exa_renderer_set_color_buffer(exa_renderer_t *r, void *fbPointer);
 int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3],
                                const float dirDu[3], const float dirDv[3]);          /* :357-368 */
 /* updateXF(chan, opacities[128], colorMap[128] rgb, domain, opacityScale) (:370-404) */
@@ -265,6 +269,10 @@ int exa_renderer_debug_counters(exa_renderer_t *r, uint64_t out[4]);
 int exa_renderer_get_tile_cost_histogram(exa_renderer_t *r, int counts[16]);
 /* headless read-back (replaces the GL blit of glutViewer/OWLViewer.cpp:140-197) */
 int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut);
+/* pipelined read-back: enqueue the copy of the frame just rendered to PINNED host memory on the
+ * renderer's copy stream and flip to a second frame buffer, so that the next render overlaps
+ * the copy; exa_renderer_sync() waits for both.  Renderer-owned frame buffers only. */
+int exa_renderer_read_rgba8_async(exa_renderer_t *r, uint32_t *pinnedHostOut);
 int exa_renderer_read_accum(exa_renderer_t *r, float *hostOutRGBA);
 /* device pointers of the current frame buffers (float4 accum, uint32 rgba8) */
 int exa_renderer_device_buffers(exa_renderer_t *r, void **accum, void **rgba8);

@@ -48,6 +48,8 @@ _SIG = {
     "exa_free": (None, [vp]),
     "exa_renderer_get_tile_cost_histogram": (i32, [vp, vp]),
     "exa_renderer_debug_counters": (i32, [vp, vp]),
+    "exa_renderer_set_color_buffer": (i32, [vp, vp]),
+    "exa_renderer_read_rgba8_async": (i32, [vp, vp]),
     "exa_ipc_export": (i32, [vp, vp]),
     "exa_ipc_import": (i32, [vp, i32, C.POINTER(vp)]),
     "exa_ipc_close": (i32, [vp]),

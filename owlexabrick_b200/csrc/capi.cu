@@ -37,6 +37,10 @@ struct exa_renderer {
   // framebuffer
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
+  // pipelined read-back (exa_renderer_read_rgba8_async): second renderer-owned RGBA8 buffer, copy stream
+  uint32_t *d_rgba8Alt = nullptr; cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr, evCopied[2] = {nullptr, nullptr}; int rbCur = 0;
+  // pinned staging ring for updateXF (no stream synchronise per update)
+  float4 *h_xfRing = nullptr; cudaEvent_t evXf[8] = {}; unsigned xfRingPos = 0;
   // partition
   int partMode = EXA_PARTITION_NONE, rank = 0, numRanks = 1; int partRoot = 0;
   std::vector<int> partPath;             // kd node visited at each partition level
@@ -281,6 +285,11 @@ void exa_renderer_destroy(exa_renderer_t *r)
   abrFree(r->abr);
   cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
   cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
+  cudaFree(r->d_rgba8Alt); if (r->copyStream) cudaStreamDestroy(r->copyStream);
+  if (r->evRendered) cudaEventDestroy(r->evRendered);
+  for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
+  for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
+  if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
   cudaFree(r->d_traces); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
   delete r;
 }
@@ -367,8 +376,10 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   CKR(cudaSetDevice(r->device));
   CKR(cudaStreamSynchronize(r->stream));
   cudaFree(r->d_accum); r->d_accum = nullptr;
+  if (r->copyStream) CKR(cudaStreamSynchronize(r->copyStream));
   if (r->ownRgba8) cudaFree(r->d_rgba8);
   r->d_rgba8 = nullptr; r->ownRgba8 = false;
+  cudaFree(r->d_rgba8Alt); r->d_rgba8Alt = nullptr;
   const size_t n = (size_t)width * height;
   CKR(cudaMalloc(&r->d_accum, n * sizeof(float4)));
   CKR(cudaMemset(r->d_accum, 0, n * sizeof(float4)));
@@ -388,6 +399,17 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   return EXA_OK;
 }
 
+int exa_renderer_set_color_buffer(exa_renderer_t *r, void *fbPointer)
+{
+  if (!r || !r->d_accum) { setError("set_color_buffer: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
+  if (fbPointer) { if (r->ownRgba8) { cudaFree(r->d_rgba8); r->ownRgba8 = false; } r->d_rgba8 = (uint32_t *)fbPointer; return EXA_OK; }
+  if (!r->ownRgba8) {
+    CKR(cudaSetDevice(r->device));
+    CKR(cudaMalloc(&r->d_rgba8, (size_t)r->width * r->height * 4)); r->ownRgba8 = true;
+  }
+  return EXA_OK;
+}
+
 int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3], const float dirDu[3], const float dirDv[3])
 {
   if (!r || !pos || !dir00 || !dirDu || !dirDv) { setError("null argument"); return EXA_ERR_INVALID; }
@@ -403,11 +425,19 @@ int exa_renderer_update_xf(exa_renderer_t *r, int channel, const float *opacitie
   if (channel < 0 || channel >= r->numFields) { setError("updateXF: channel out of range"); return EXA_ERR_INVALID; }
   r->fs.xfDomain[channel][0] = domainLower; r->fs.xfDomain[channel][1] = domainUpper;
   r->fs.xfOpacityScale = opacityScale;
-  float4 lut[128];
-  for (int i = 0; i < 128; i++) lut[i] = make_float4(rgb128x3[3 * i], rgb128x3[3 * i + 1], rgb128x3[3 * i + 2], opacities128[i]);
   CKR(cudaSetDevice(r->device));
-  CKR(cudaMemcpyAsync(r->d_xf + 128 * channel, lut, sizeof(lut), cudaMemcpyHostToDevice, r->stream));
-  CKR(cudaStreamSynchronize(r->stream));
+  if (!r->h_xfRing) {
+    CKR(cudaMallocHost(&r->h_xfRing, sizeof(float4) * 128 * 8));
+    for (int i = 0; i < 8; i++) CKR(cudaEventCreateWithFlags(&r->evXf[i], cudaEventDisableTiming));
+  }
+  // stream-ordered upload from a pinned ring slot: frames already enqueued keep the table they
+  // were launched with, and the call does not wait for them
+  const unsigned slot = r->xfRingPos++ % 8;
+  CKR(cudaEventSynchronize(r->evXf[slot]));                  // only blocks when the GPU is 8 updates behind
+  float4 *lut = r->h_xfRing + 128 * slot;
+  for (int i = 0; i < 128; i++) lut[i] = make_float4(rgb128x3[3 * i], rgb128x3[3 * i + 1], rgb128x3[3 * i + 2], opacities128[i]);
+  CKR(cudaMemcpyAsync(r->d_xf + 128 * channel, lut, sizeof(float4) * 128, cudaMemcpyHostToDevice, r->stream));
+  CKR(cudaEventRecord(r->evXf[slot], r->stream));
   r->masksDirty = true;                                     // needVolumeBVHRebuild (:403)
   return EXA_OK;
 }

@@ -76,7 +76,9 @@ int exa_renderer_debug_counters(exa_renderer_t *r, uint64_t out[4])
 int exa_renderer_sync(exa_renderer_t *r)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
-  CKR(cudaSetDevice(r->device)); CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+  CKR(cudaSetDevice(r->device)); CKR(cudaStreamSynchronize(r->stream));
+  if (r->copyStream) CKR(cudaStreamSynchronize(r->copyStream));
+  return EXA_OK;
 }
 
 int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut)
@@ -85,6 +87,28 @@ int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut)
   CKR(cudaSetDevice(r->device));
   CKR(cudaMemcpyAsync(hostOut, r->d_rgba8, (size_t)r->width * r->height * 4, cudaMemcpyDeviceToHost, r->stream));
   CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+}
+int exa_renderer_read_rgba8_async(exa_renderer_t *r, uint32_t *pinnedHostOut)
+{
+  if (!r || !pinnedHostOut || !r->d_rgba8) { setError("read_rgba8_async: no framebuffer"); return EXA_ERR_INVALID; }
+  if (!r->ownRgba8) { setError("read_rgba8_async needs a renderer-owned frame buffer (resizeFrameBuffer(NULL, ..))"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  const size_t bytes = (size_t)r->width * r->height * 4;
+  if (!r->copyStream) {
+    CKR(cudaStreamCreateWithFlags(&r->copyStream, cudaStreamNonBlocking));
+    CKR(cudaEventCreateWithFlags(&r->evRendered, cudaEventDisableTiming));
+    for (int i = 0; i < 2; i++) CKR(cudaEventCreateWithFlags(&r->evCopied[i], cudaEventDisableTiming));
+  }
+  if (!r->d_rgba8Alt) CKR(cudaMalloc(&r->d_rgba8Alt, bytes));
+  // copy THIS frame on the copy stream, flip to the other buffer for the next frame, and make
+  // the render stream wait until that buffer's previous copy has left
+  CKR(cudaEventRecord(r->evRendered, r->stream));
+  CKR(cudaStreamWaitEvent(r->copyStream, r->evRendered, 0));
+  CKR(cudaMemcpyAsync(pinnedHostOut, r->d_rgba8, bytes, cudaMemcpyDeviceToHost, r->copyStream));
+  CKR(cudaEventRecord(r->evCopied[r->rbCur], r->copyStream));
+  std::swap(r->d_rgba8, r->d_rgba8Alt); r->rbCur ^= 1;
+  CKR(cudaStreamWaitEvent(r->stream, r->evCopied[r->rbCur], 0));
+  return EXA_OK;
 }
 int exa_renderer_read_accum(exa_renderer_t *r, float *hostOut)
 {

@@ -506,6 +506,9 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
   P.rgba8[pixelIdx] = make_rgba8(color);
 }
 
+#ifndef EXA_LOOKAHEAD
+#define EXA_LOOKAHEAD 0     // kd traversal one node per trip ahead of the sampling: parity-green; C2 opaque 0.135 -> 0.152 ms, translucent 2.33 -> 2.30 ms: off
+#endif
 #ifndef EXA_PREFETCH
 #define EXA_PREFETCH 0      // next-record L1 prefetch: measured slower on C2 (extra address math on an issue-bound kernel)
 #endif
@@ -629,13 +632,31 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;
     float dtS = 0.f, t_i = 0.f, t_last = 0.f;
     int budget = P.sampleBudget;
+#if EXA_LOOKAHEAD
+    bool haveNext = false, exhausted = false; Segment nseg = seg; float nextTmin = already;
+#endif
     for (;;) {
       if (__all_sync(FULL, !live)) break;
 #ifdef EXA_PHASE_TIMING
       ph_t = clock64(); ph_iters++;
 #endif
+#if EXA_LOOKAHEAD
+      // (1) one kd-traversal step towards the NEXT region segment.  Its query depends only on the
+      // current segment (tmin = t1 * 1.0000001, :1698), so it runs ahead while the current segment
+      // is being sampled: one node visit per trip, interleaved with the samples, instead of a
+      // whole descent that every lane of the warp waits for.
+      if (live && !haveNext && !exhausted) {
+        const int tr = travStep(T, P.scene, P.volActive, nextTmin, rayTmax, nseg);
+        if (tr == 1) haveNext = true; else if (tr == 2) exhausted = true;
+      }
+      // (2) a lane without a current segment takes the prefetched one (or waits for it)
+      const bool need = live && !haveSeg && (haveNext || exhausted);
+      const bool got = haveNext;
+      if (need && got) { seg = nseg; haveNext = false; already = nextTmin; nextTmin = seg.t1 * 1.0000001f; }
+#else
       const bool need = live && !haveSeg;
       const bool got = travNextWarp(T, P.scene, P.volActive, already, rayTmax, seg, need);
+#endif
       if (need) {
         if (!got) live = false;
         else {
@@ -649,14 +670,19 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #ifdef EXA_PHASE_TIMING
       __syncwarp(); ph_trav += clock64() - ph_t; ph_t = clock64();
 #endif
-      if (live) {
+      if (live && haveSeg) {
         const float t_next = fminf(t_i, seg.t1);
         const float t_sample = 0.5f * (t_next + t_last);
         const float actual_dt = t_next - t_last;
         t_last = t_next;
         integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
         if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
-        else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                             // :1698
+        else if (t_next >= seg.t1) {                                                                               // :1698
+          haveSeg = false;
+#if !EXA_LOOKAHEAD
+          already = seg.t1 * 1.0000001f;
+#endif
+        }
         else {
           t_i += dtS;
 #if EXA_PREFETCH
@@ -672,7 +698,13 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
           LongRay q;
           q.ox = o.x; q.oy = o.y; q.oz = o.z; q.dx = d.x; q.dy = d.y; q.dz = d.z;
           q.pcx = pc.x; q.pcy = pc.y; q.pcz = pc.z; q.pcw = pc.w;
-          q.offs = offs; q.already = already; q.rayTmax = rayTmax; q.t_i = t_i; q.t_last = t_last; q.haveSeg = haveSeg ? 1 : 0;
+          q.offs = offs; q.rayTmax = rayTmax;
+#if EXA_LOOKAHEAD
+          q.already = haveSeg ? already : nextTmin;                // tmin of the query that finds the ray's current / next segment
+#else
+          q.already = already;
+#endif
+          q.t_i = t_i; q.t_last = t_last; q.haveSeg = haveSeg ? 1 : 0;
           q.bgx = bg.x; q.bgy = bg.y; q.bgz = bg.z; q.pixelIdx = pixelIdx;
           P.longQueue[atomicAdd(P.longCount, 1)] = q;              // capacity = width * height: cannot overflow
           live = false; parked = true;

@@ -321,6 +321,11 @@ class Renderer:
         check(lib.exa_renderer_read_rgba8(self.h, _p(out)))
         return out
 
+    def read_rgba8_async(self, pinned_ptr):
+        """enqueue the copy of the frame just rendered into PINNED host memory (raw pointer);
+        the next render overlaps it; sync() waits for both"""
+        check(lib.exa_renderer_read_rgba8_async(self.h, C.c_void_p(pinned_ptr)))
+
     def read_accum(self):
         out = np.zeros((self.fb_size[1], self.fb_size[0], 4), np.float32)
         check(lib.exa_renderer_read_accum(self.h, _p(out)))

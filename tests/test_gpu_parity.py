@@ -265,6 +265,41 @@ def test_two_iso_surfaces(R, orc):
     assert (err > RGBA_TOL).sum() <= 0.005 * err.size, "%d pixels differ" % int((err > RGBA_TOL).sum())
 
 
+def test_pipelined_readback_equals_blocking(R, orc):
+    """update -> render_async -> read_rgba8_async over 5 frames with a different camera and
+    transfer function each == the same frames rendered and read one by one"""
+    import torch
+    r, sc, fd, _ = _frame_pair(R, orc, "nb64_off", 1, size=(160, 96))
+    W, H = fd.width, fd.height
+    fd.apply(r)
+    alpha, rgb = fd.xf[0]
+    def inputs(i):
+        pos = np.asarray(fd.cam[0], np.float32) + np.float32(0.7 * i)
+        a = np.clip(np.asarray(alpha, np.float32) * (1.0 - 0.15 * i), 0, 1)
+        return (pos,) + tuple(fd.cam[1:]), a
+    ref = []
+    for i in range(5):
+        cam, a = inputs(i)
+        r.updateCamera(*cam); r.updateXF(0, a, rgb, fd.xf_domain[0], fd.opacity_scale)
+        r.render()
+        ref.append(r.read_rgba8().copy())
+    assert any((ref[i] != ref[0]).any() for i in range(1, 5))
+    host = [torch.empty((H, W), dtype=torch.int32).pin_memory() for _ in range(5)]
+    for i in range(5):
+        cam, a = inputs(i)
+        r.updateCamera(*cam); r.updateXF(0, a, rgb, fd.xf_domain[0], fd.opacity_scale)
+        r.render(sync=False)
+        r.read_rgba8_async(host[i].data_ptr())
+    r.sync()
+    for i in range(5):
+        assert (host[i].numpy().view(np.uint32) == ref[i]).all(), i
+    # a caller-owned frame buffer cannot be double-buffered: loud error
+    fb = torch.empty((H, W), dtype=torch.int32, device="cuda")
+    r.resizeFrameBuffer(fb.data_ptr(), (W, H))
+    with pytest.raises(RuntimeError):
+        r.read_rgba8_async(host[0].data_ptr())
+
+
 def test_render_errors(R, orc):
     g = load_golden("ex4")
     b = R.ExaBricks.from_bytes(g["bricks"].tobytes())
