@@ -23,34 +23,87 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (domain, nested boxes, image)           SURVEY.md §8(d)
+    # name: (domain, shape, image)           SURVEY.md §8(d)
+    # shape = list of nested boxes (synth.nested_boxes) or ("exajet", scale) (synth.exajet_shaped)
+    "c3": ((4096, 1024, 2048), ("exajet", 1), (3840, 2160)),
+    "c3s2": ((2048, 512, 1024), ("exajet", 2), (1920, 1080)),
+    "c3s4": ((1024, 256, 512), ("exajet", 4), (960, 540)),
     "c2": (1024, [(320, 704), (192, 832)], (1024, 1024)),
     "c1": (256, [(72, 184), (32, 224)], (1024, 1024)),
     "small": (64, [(18, 46), (8, 56)], (256, 256)),
 }
 OPACITY_SCALE = 1.0      # viewer default xfOpacityScale (viewer.cpp:113)
 DT = 0.5                 # viewer default (viewer.cpp:115)
+SCENE_CACHE_VERSION = 1  # bump when a generator changes
 
 
 def log(*a):
     print("[bench]", *a, file=sys.stderr, flush=True)
 
 
+def dom3(domain):
+    return [float(domain)] * 3 if np.isscalar(domain) else [float(x) for x in domain]
+
+
+def field_threaded(cells, domain, channel=0, chunk=1 << 20):
+    """synth.analytic_field over chunks on a thread pool (numpy releases the GIL inside the
+    ufuncs); same values as the single call — the noise counter is the global cell index"""
+    from concurrent.futures import ThreadPoolExecutor
+    from owlexabrick_b200 import synth
+    out = np.empty(len(cells), np.float32)
+
+    def work(b):
+        out[b:b + chunk] = synth.analytic_field_chunked(cells[b:b + chunk], domain, channel, chunk=chunk, first=b)
+    with ThreadPoolExecutor(max_workers=min(32, os.cpu_count() or 1)) as ex:
+        list(ex.map(work, range(0, len(cells), chunk)))
+    return out
+
+
 def make_workload(name):
     from owlexabrick_b200 import synth
-    domain, boxes, image = WORKLOADS[name]
+    domain, shape, image = WORKLOADS[name]
     t = time.time()
-    cells = synth.nested_boxes(domain, boxes)
-    field = synth.analytic_field(cells, domain, 0)
+    if isinstance(shape, tuple) and shape[0] == "exajet":
+        cells, _ = synth.exajet_shaped(shape[1])
+    else:
+        cells = synth.nested_boxes(domain, shape)
+    field = field_threaded(cells, domain, 0)
     log("workload %s: %d cells generated in %.1fs" % (name, len(cells), time.time() - t))
     return cells, field, domain, image
 
 
-def ncu_traffic(kernel):
-    """DRAM bytes per launch of `kernel` from the committed ncu capture (profiles/traffic_r01.json), or None"""
+def load_or_build_scene(name, R, cache_dir=None):
+    """-> (ExaBricks, field).  Cells -> bricks with the library's host builder (exa_bricks_build,
+    bit-exact with the reference's exaBuilder: tests/test_host.py, tests/test_oracle.py); the
+    result is cached in /dev/shm so that the two bench arms and the ranks of one box build once."""
+    cache_dir = cache_dir or os.environ.get("EXA_SCENE_CACHE", "/dev/shm")
+    base = os.path.join(cache_dir, "exa_scene_%s_v%d" % (name, SCENE_CACHE_VERSION))
+    if os.path.exists(base + ".ok"):
+        t = time.time()
+        bricks = R.ExaBricks.load(base + ".bricks")
+        field = np.fromfile(base + ".scalars", np.float32)
+        log("scene %s loaded from %s in %.1fs" % (name, base, time.time() - t))
+        return bricks, field
+    cells, field, _, _ = make_workload(name)
+    t = time.time()
+    bricks = R.ExaBricks.build(cells)
+    log("exa_bricks_build: %d cells -> %d bricks in %.1fs" % (len(cells), bricks.num_bricks, time.time() - t))
+    del cells
+    try:
+        bricks.save(base + ".bricks")
+        field.tofile(base + ".scalars")
+        open(base + ".ok", "w").write("ok")
+    except OSError as e:
+        log("scene cache not written (%s)" % e)
+    return bricks, field
+
+
+def ncu_traffic(kernel, workload="c2"):
+    """DRAM bytes per launch of `kernel` on `workload` from the committed ncu capture (profiles/traffic_r01.json), or None"""
     p = os.path.join(ROOT, "profiles", "traffic_r01.json")
     try:
-        t = json.load(open(p))[kernel]
+        t = json.load(open(p))
+        t = t[workload][kernel] if workload in t else (t[kernel] if workload == "c2" else None)
         return int(t["dram_bytes_read"]) + int(t["dram_bytes_write"])
     except Exception:
         return None
@@ -97,7 +150,7 @@ def frame_desc(R, domain, image, field_range):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import scenes
     W, H = image
-    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [domain] * 3, W, H))
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, dom3(domain), W, H))
     fd.opacity_scale = OPACITY_SCALE
     fd.dt = DT
     fd.xf_domain = [(float(field_range[0]), float(field_range[1]))]
@@ -135,10 +188,22 @@ def run_reference(args):
     from owlexabrick_b200 import renderer as R      # host-side camera helper only
     orc.build()
     name = args.workload
-    cells, field, domain, image = make_workload(name)
-    log("reference arm: building the CPU scene (oracle builder, serial)")
+    domain, _, image = WORKLOADS[name]
     t = time.time()
-    scene = cpu_scene(orc, cells, field)
+    if name.startswith("c3"):
+        # 650 M cells: the serial restatement of exaBuilder needs > 10 min, so the (untimed) scene
+        # set-up takes the bricks from the OpenMP host builder, whose output is bit-exact with
+        # it (tests/test_host.py); flatten, ABR build and the timed frames are the oracle's
+        bricks, field = load_or_build_scene(name, R)
+        hdr = bricks.headers.view(orc.BRICK_DT)
+        sc = orc.flatten_scalars(bricks.cell_ids, [field])
+        regions, leaf = orc.build_abr(hdr, sc)
+        scene = orc.Scene(hdr, sc, regions, leaf)
+    else:
+        cells, field, _, _ = make_workload(name)
+        log("reference arm: building the CPU scene (oracle builder, serial)")
+        scene = cpu_scene(orc, cells, field)
+        del cells
     log("cpu scene built in %.1fs" % (time.time() - t))
     W, H = image
     fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
@@ -164,13 +229,13 @@ def run_reference(args):
 
 
 def workload_name(name):
-    domain, boxes, image = WORKLOADS[name]
+    domain, shape, image = WORKLOADS[name]
+    if isinstance(shape, tuple):
+        return "%s: synthetic exajet-shaped 4-level AMR (fuselage/wing/tail/wake boxes), domain %dx%dx%d, single scalar, DVR %dx%d, default camera/XF" % (
+            (name,) + tuple(int(x) for x in domain) + (image[0], image[1]))
     return "%s: synthetic 3-level nested-box AMR, domain %d^3, single scalar, DVR %dx%d, default camera/XF" % (name, domain, image[0], image[1])
 
 
-# ---------------------------------------------------------------------------------------------
-# product arm
-# ---------------------------------------------------------------------------------------------
 def binary_swap(r, dist, torch, partial, npix, rank, world, rgba8_full):
     """sort-last compositing (owlexabrick_b200/multigpu.py) with the CUDA kernels of the library"""
     from owlexabrick_b200 import multigpu
@@ -205,25 +270,14 @@ def run_product(args):
     domain, boxes, image = WORKLOADS[name]
     W, H = image
     # ---- setup (untimed): rank 0 generates + builds, the others load from /dev/shm ----
-    shm = "/dev/shm/exa_bench_%s" % os.environ.get("MASTER_PORT", "single")
     t0 = time.time()
     if rank == 0:
-        cells, field, _, _ = make_workload(name)
-        t = time.time()
-        bricks = R.ExaBricks.build(cells)
-        log("exa_bricks_build: %d cells -> %d bricks in %.1fs" % (len(cells), bricks.num_bricks, time.time() - t))
-        ncells = len(cells)
-        del cells
-        if world > 1:
-            os.makedirs(shm, exist_ok=True)
-            bricks.save(os.path.join(shm, "w.bricks"))
-            field.tofile(os.path.join(shm, "w.scalars"))
+        bricks, field = load_or_build_scene(name, R)
     if world > 1:
         dist.barrier()
         if rank != 0:
-            bricks = R.ExaBricks.load(os.path.join(shm, "w.bricks"))
-            field = np.fromfile(os.path.join(shm, "w.scalars"), np.float32)
-            ncells = bricks.total_num_cells
+            bricks, field = load_or_build_scene(name, R)              # from rank 0's /dev/shm cache
+    ncells = bricks.total_num_cells
     t = time.time()
     r = R.Renderer(bricks, [field], device=local)
     torch.cuda.synchronize()
@@ -393,6 +447,18 @@ def run_product(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_s = float(te.item())
     e2e_value = tot["samples"] / (e2e_s / args.steps)
+    # what bounds e2e: the frame's device->host copy alone (pinned, device-timed)
+    d2h_ms = None
+    if rank == 0:
+        dev_img = torch.zeros((H, W), dtype=torch.int32, device="cuda")
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        host_img.copy_(dev_img, non_blocking=True); torch.cuda.synchronize()
+        c0.record(stream)
+        for _ in range(10):
+            host_img.copy_(dev_img, non_blocking=True)
+        c1.record(stream); torch.cuda.synchronize()
+        d2h_ms = c0.elapsed_time(c1) / 10
+        del dev_img
     # keep the GPU(s) under the same load until nvidia-smi has produced a few samples
     t = time.time()
     while True:
@@ -485,7 +551,7 @@ def run_product(args):
     recon = None
     if rank == 0:
         npts = 1 << 20
-        pts = synth.random_points(npts, [0] * 3, [domain] * 3, seed=1)
+        pts = synth.random_points(npts, [0] * 3, dom3(domain), seed=1)
         d_pts = torch.from_numpy(pts).cuda()
         d_val = torch.empty(npts, dtype=torch.float32, device="cuda")
         d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
@@ -512,7 +578,7 @@ def run_product(args):
         peak, _ = peaks()
         recon = {"points": npts, "ms": pms, "samples_per_s": npts / (pms * 1e-3), "algorithmic_bytes": pbytes,
                  "achieved_gbs": pbytes / (pms * 1e-3) / 1e9, "frac": pbytes / (pms * 1e-3) / 1e9 / peak,
-                 "traffic": ncu_traffic("k_samplePoints") if name == "c2" else None, "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB write + 256 MiB read between iterations"}
+                 "traffic": ncu_traffic("k_samplePoints", name), "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB write + 256 MiB read between iterations"}
 
     # ---- CPU baseline beside it (rank 0, N=1 only): the oracle on a bounded sample ----
     cpu = None
@@ -549,10 +615,11 @@ def run_product(args):
                            "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"],
                            "step": "CUDA graph replay" if graph is not None else "eager launches"},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
-                        "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4},
+                        "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4,
+                        "d2h_copy_alone_ms": d2h_ms, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory (exa_renderer_read_rgba8_async)" if world == 1 else "blocking read-back on rank 0"},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": ncu_traffic("k_renderFrame") if (world == 1 and name == "c2") else None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
+                             "traffic": ncu_traffic("k_renderFrame", name) if world == 1 else None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; almost all are served by L1/L2 (traffic = measured DRAM bytes of one launch, ncu): the frame kernel is issue-bound, not HBM-bound"},
                 "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)

@@ -33,7 +33,7 @@ struct exa_renderer {
   float dt = 0.5f; float ert = 0.98f;
   int spaceSkipping = 1, gradDVR = 1, gradISO = 1;
   bool masksDirty = true;
-  uint8_t *d_regionVol = nullptr, *d_regionIso = nullptr, *d_volActive = nullptr, *d_isoActive = nullptr, *d_inPart = nullptr;
+  uint8_t *d_volActive = nullptr, *d_isoActive = nullptr /* = d_volActive + numKdNodes */, *d_inPart = nullptr; int *d_kdParent = nullptr;
   // framebuffer
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
@@ -259,8 +259,19 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   r->h_kd.resize(r->abr.numKdNodes);
   CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);
-  CKC(cudaMalloc(&r->d_regionVol, nr)); CKC(cudaMalloc(&r->d_regionIso, nr));
-  CKC(cudaMalloc(&r->d_volActive, nn)); CKC(cudaMalloc(&r->d_isoActive, nn)); CKC(cudaMalloc(&r->d_inPart, nn));
+  CKC(cudaMalloc(&r->d_volActive, 2 * (size_t)nn)); r->d_isoActive = r->d_volActive + r->abr.numKdNodes; CKC(cudaMalloc(&r->d_inPart, nn));
+  {
+    // parent links for the activity pass (k_leafActiveUp climbs from the leaves)
+    std::vector<int> parent(nn, -1);
+    for (int g = 0; g < r->abr.numKdNodes; g++) {
+      const KdNode nd = r->h_kd[g];
+      if ((nd.info >> 30) == 3) continue;
+      const uint32_t c = nd.info & 0x3fffffffu;
+      if (c + 1 < (uint32_t)r->abr.numKdNodes) { parent[c] = g; parent[c + 1] = g; }
+    }
+    CKC(cudaMalloc(&r->d_kdParent, sizeof(int) * nn));
+    CKC(cudaMemcpy(r->d_kdParent, parent.data(), sizeof(int) * nn, cudaMemcpyHostToDevice));
+  }
   CKC(cudaMemset(r->d_inPart, 1, nn));
   CKC(cudaMalloc(&r->d_xf, sizeof(float4) * 128 * numFields));
   {
@@ -283,7 +294,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   cudaFree(r->d_dual); cudaFree(r->d_dualBegin); cudaFree(r->d_locGrid);
   cudaFree(r->d_bricks); cudaFree(r->d_scalars); cudaFree(r->d_scalarOffsets); cudaFree(r->d_primaryChannels);
   abrFree(r->abr);
-  cudaFree(r->d_xf); cudaFree(r->d_regionVol); cudaFree(r->d_regionIso); cudaFree(r->d_volActive); cudaFree(r->d_isoActive); cudaFree(r->d_inPart);
+  cudaFree(r->d_xf); cudaFree(r->d_volActive); cudaFree(r->d_kdParent); cudaFree(r->d_inPart);
   cudaFree(r->d_accum); if (r->ownRgba8) cudaFree(r->d_rgba8);
   cudaFree(r->d_rgba8Alt); if (r->copyStream) cudaStreamDestroy(r->copyStream);
   if (r->evRendered) cudaEventDestroy(r->evRendered);

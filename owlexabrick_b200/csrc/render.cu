@@ -997,49 +997,40 @@ __device__ bool activeForVolumeSampling(const RenderParams &P, float vlo, float 
   return false;
 }
 
-__global__ void k_regionActive(const __grid_constant__ RenderParams P, int spaceSkipping, uint8_t *regionVol, uint8_t *regionIso)
+// One launch per XF / iso / partition change: every kd LEAF classifies its region (value range
+// against the XF, iso values against the range) and, if active, marks itself and its
+// ancestors.  A thread stops climbing at the first ancestor that is already marked: whoever
+// marked it had found it unmarked (or raced with another marker) and keeps climbing, so the
+// chain always reaches the root.  Both masks were cleared by one memset (they are adjacent).
+__global__ void k_leafActiveUp(const __grid_constant__ RenderParams P, int numNodes, const int *kdParent, const uint8_t *inPart,
+                               int spaceSkipping, uint8_t *volActive, uint8_t *isoActive)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= P.scene.numRegions) return;
-  const ExaBrickRegion r = P.scene.regions[i];
-  bool act = false;
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= numNodes) return;
+  const KdNode nd = P.scene.kd[g];
+  const uint32_t payload = nd.info & 0x3fffffffu;
+  if ((nd.info >> 30) != 3 || payload == KD_EMPTY) return;
+  if (inPart && !inPart[g]) return;
+  const int rid = (int)P.scene.blobs[payload + 2].x;
+  const ExaBrickRegion r = P.scene.regions[rid];
+  bool act = !spaceSkipping;
   for (int c = 0; c < P.numChannels && !act; c++) act |= activeForVolumeSampling(P, r.valueRange_lower, r.valueRange_upper, c);
-  regionVol[i] = spaceSkipping ? (act ? 1 : 0) : 1;
   bool ia = false;
   for (int k = 0; k < EXA_MAX_ISO_SURFACES; k++)
     if (P.isoEnabled[k] && P.isoValue[k] >= r.valueRange_lower && P.isoValue[k] <= r.valueRange_upper) ia = true;
-  regionIso[i] = ia ? 1 : 0;
+  volatile uint8_t *va = volActive, *ia8 = isoActive;
+  if (act) for (int n = g; n >= 0 && !va[n]; n = kdParent[n]) va[n] = 1;
+  if (ia) for (int n = g; n >= 0 && !ia8[n]; n = kdParent[n]) ia8[n] = 1;
 }
 
-__global__ void k_nodeActiveUp(int first, int n, const KdNode *kd, const uint4 *blobs, const uint8_t *inPart,
-                               const uint8_t *regionVol, const uint8_t *regionIso, uint8_t *volActive, uint8_t *isoActive)
+int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping, const uint8_t *inPart,
+                         uint8_t *volActive, uint8_t *isoActive, cudaStream_t s)
 {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const int g = first + i; const KdNode nd = kd[g];
-  const uint32_t payload = nd.info & 0x3fffffffu;
-  if ((nd.info >> 30) == 3) {
-    if (payload == KD_EMPTY) { volActive[g] = 0; isoActive[g] = 0; return; }
-    const int rid = (int)blobs[payload + 2].x;
-    const bool in = inPart ? inPart[g] != 0 : true;
-    volActive[g] = in && regionVol[rid]; isoActive[g] = in && regionIso[rid];
-  } else {
-    volActive[g] = volActive[payload] | volActive[payload + 1];
-    isoActive[g] = isoActive[payload] | isoActive[payload + 1];
-  }
-}
-
-int launchRegionActivity(const RenderParams &P, const std::vector<int> &levelOffset, int spaceSkipping, const uint8_t *inPart,
-                         uint8_t *regionVol, uint8_t *regionIso, uint8_t *volActive, uint8_t *isoActive, cudaStream_t s)
-{
-  int launches = 0;
-  if (P.scene.numRegions > 0) { k_regionActive<<<(P.scene.numRegions + 127) / 128, 128, 0, s>>>(P, spaceSkipping, regionVol, regionIso); launches++; }
-  for (int lv = (int)levelOffset.size() - 2; lv >= 0; lv--) {
-    const int first = levelOffset[lv], n = levelOffset[lv + 1] - first;
-    if (n <= 0) continue;
-    k_nodeActiveUp<<<(n + 255) / 256, 256, 0, s>>>(first, n, P.scene.kd, P.scene.blobs, inPart, regionVol, regionIso, volActive, isoActive); launches++;
-  }
-  return cudaGetLastError() == cudaSuccess ? launches : -1;
+  if (isoActive != volActive + numNodes) return -1;               // one allocation, one memset
+  cudaMemsetAsync(volActive, 0, 2 * (size_t)numNodes, s);
+  if (numNodes <= 0 || P.scene.numRegions <= 0) return 0;
+  k_leafActiveUp<<<(numNodes + 127) / 128, 128, 0, s>>>(P, numNodes, kdParent, inPart, spaceSkipping, volActive, isoActive);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
 __global__ void k_partDown(int first, int n, const KdNode *kd, uint8_t *inPart)

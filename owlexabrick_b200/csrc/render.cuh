@@ -67,9 +67,8 @@ struct TraceParams {
 int launchRenderFrame(const RenderParams &P, cudaStream_t s);
 int launchSamplePoints(const SampleParams &P, cudaStream_t s);
 int launchTrace(const TraceParams &P, cudaStream_t s);
-int launchRegionActivity(const RenderParams &P, const std::vector<int> &levelOffset, int spaceSkipping,
-                         const uint8_t *nodeInPartition, uint8_t *regionVol, uint8_t *regionIso,
-                         uint8_t *volActive, uint8_t *isoActive, cudaStream_t s);
+int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping,
+                         const uint8_t *nodeInPartition, uint8_t *volActive, uint8_t *isoActive /* = volActive + numNodes */, cudaStream_t s);
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
 int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellIDs, size_t numCells, float *d_out,
                  int *d_errFlag, cudaStream_t s);

@@ -109,6 +109,82 @@ def analytic_field(cells, domain, channel=0, noise=0.05):
     return (s + noise * (2.0 * u - 1.0)).astype(np.float32)
 
 
+def analytic_field_chunked(cells, domain, channel=0, noise=0.05, chunk=1 << 24, first=0):
+    """analytic_field for arrays too large for its float64 temporaries (same values: the noise
+    counter is the global cell index; `first` = global index of cells[0] when the caller
+    passes a slice)"""
+    out = np.empty(len(cells), np.float32)
+    L = np.array([domain] * 3 if np.isscalar(domain) else domain, np.float64)
+    phi = 0.7 * channel
+    for b in range(0, len(cells), chunk):
+        c4 = cells[b:b + chunk]
+        cw = (1 << c4[:, 3]).astype(np.float64)
+        c = c4[:, :3].astype(np.float64) + 0.5 * cw[:, None]
+        s = 0.5 + 0.5 * np.sin(2 * np.pi * c[:, 0] / L[0]) * np.cos(2 * np.pi * c[:, 1] / L[1]) * np.sin(2 * np.pi * c[:, 2] / L[2] + phi)
+        with np.errstate(over="ignore"):
+            ctr = np.arange(first + b, first + b + len(c4), dtype=np.uint64) + np.uint64(0xE8AB51C4 + channel)
+        u = ((splitmix64(ctr) >> np.uint64(40)).astype(np.float32) * np.float32(1.0 / (1 << 24))).astype(np.float64)
+        out[b:b + chunk] = (s + noise * (2.0 * u - 1.0)).astype(np.float32)
+    return out
+
+
+# SURVEY §8(d) C3: exajet-shaped, 4 levels, elongated 4:1:2 domain, one long L0/L1 "fuselage"
+# box plus off-axis refinement boxes ("wings", "tail", "wake").  Boxes are (lo, hi, level) in
+# finest units of the scale-1 domain 4096 x 1024 x 2048, aligned to the coarsest cell (8);
+# a cell's level is the finest level of any box that contains it, else 3.
+EXAJET_DOMAIN = (4096, 1024, 2048)
+EXAJET_BOXES = [
+    # level 0: fuselage, wing, tail plane, fin
+    ((768, 352, 800), (3328, 672, 1248), 0),
+    ((1664, 448, 192), (2368, 576, 1856), 0),
+    ((2944, 480, 576), (3264, 544, 1472), 0),
+    ((2880, 640, 992), (3328, 896, 1056), 0),
+    # level 1: shells around those + the wake
+    ((640, 320, 704), (3456, 704, 1344), 1),
+    ((1536, 384, 128), (2496, 640, 1920), 1),
+    ((2816, 416, 448), (3392, 960, 1600), 1),
+    ((3328, 320, 704), (4032, 704, 1344), 1),
+    # level 2: far shells
+    ((384, 192, 448), (4096, 896, 1600), 2),
+    ((1280, 256, 0), (2752, 768, 2048), 2),
+]
+
+
+def exajet_shaped(scale=1):
+    """-> (cells int32[N,4], domain 3-vector).  scale=1: 4096x1024x2048 finest units, ~650 M cells
+    (SURVEY C3); scale=k divides every box coordinate by k (all box coordinates are multiples of 32,
+    so k = 1, 2, 4 keep them on the coarse grid), cells ~ 650 M / k^3."""
+    dom = np.array(EXAJET_DOMAIN, np.int64) // scale
+    cg = dom // 8                                                    # coarse (level-3) grid
+    lvl = np.full((cg[2], cg[1], cg[0]), 3, np.int8)
+    for lo, hi, l in EXAJET_BOXES:
+        lo = np.array(lo, np.int64) // scale // 8
+        hi = np.array(hi, np.int64) // scale // 8
+        sub = lvl[lo[2]:hi[2], lo[1]:hi[1], lo[0]:hi[0]]
+        np.minimum(sub, l, out=sub)
+    counts = [int((lvl == l).sum()) for l in range(4)]
+    total = sum(counts[l] * (8 >> l) ** 3 for l in range(4))
+    out = np.empty((total, 4), np.int32)
+    pos = 0
+    for l in range(4):
+        z, y, x = np.nonzero(lvl == l)
+        m = 8 >> l                                                   # cells per coarse cell per axis
+        cw = 1 << l
+        o = np.arange(m, dtype=np.int32) * cw
+        oz, oy, ox = (a.ravel() for a in np.meshgrid(o, o, o, indexing="ij"))
+        step = max(1, (1 << 22) // (m ** 3))
+        for b in range(0, len(x), step):
+            n = len(x[b:b + step]) * m ** 3
+            blk = out[pos:pos + n].reshape(-1, m ** 3, 4)
+            blk[:, :, 0] = (x[b:b + step, None] * 8).astype(np.int32) + ox[None, :]
+            blk[:, :, 1] = (y[b:b + step, None] * 8).astype(np.int32) + oy[None, :]
+            blk[:, :, 2] = (z[b:b + step, None] * 8).astype(np.int32) + oz[None, :]
+            blk[:, :, 3] = l
+            pos += n
+    assert pos == total
+    return out, dom
+
+
 def linear_field(cells, coef=(0.01, 0.02, 0.03), offset=0.1):
     cells = np.asarray(cells)
     cw = (1 << cells[:, 3]).astype(np.float64)

@@ -23,13 +23,7 @@ def main():
     import bench
     from owlexabrick_b200 import capi, renderer as R, synth
     domain, boxes, image = bench.WORKLOADS[a.workload]
-    cache = "/dev/shm/exa_pq_%s" % a.workload
-    if os.path.exists(cache + ".bricks"):
-        bricks = R.ExaBricks.load(cache + ".bricks"); field = np.fromfile(cache + ".scalars", np.float32)
-    else:
-        cells, field, _, _ = bench.make_workload(a.workload)
-        bricks = R.ExaBricks.build(cells); del cells
-        bricks.save(cache + ".bricks"); field.tofile(cache + ".scalars")
+    bricks, field = bench.load_or_build_scene(a.workload, R)
     r = R.Renderer(bricks, [field]); torch.cuda.synchronize()
     stream = torch.cuda.current_stream(); r.set_stream(stream.cuda_stream)
     W, H = image
@@ -59,7 +53,7 @@ def main():
         r.setGradientShadingDVR(gs)
     r.setGradientShadingDVR(False); out["translucent_nograd_ms"] = round(time_frames(a.steps), 4); r.setGradientShadingDVR(True)
     npts = 1 << 20
-    pts = synth.random_points(npts, [0] * 3, [domain] * 3, seed=1)
+    pts = synth.random_points(npts, [0] * 3, bench.dom3(domain), seed=1)
     d_pts = torch.from_numpy(pts).cuda(); d_val = torch.empty(npts, dtype=torch.float32, device="cuda"); d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
@@ -86,7 +80,7 @@ def main():
                 torch.cuda.synchronize()
                 if i >= 3: tt.append(e0.elapsed_time(e1))
             return round(1e3 * float(np.mean(tt)), 2)
-        c = domain / 2
+        c = min(bench.dom3(domain)) / 2
         out["points_local128_us"] = run(synth.random_points(npts, [c - 64] * 3, [c + 64] * 3, seed=2))
         key = (pts[:, 2] // 16).astype(np.int64) * 4096 * 4096 + (pts[:, 1] // 16).astype(np.int64) * 4096 + (pts[:, 0] // 16).astype(np.int64)
         out["points_sorted_us"] = run(pts[np.argsort(key, kind="stable")])
