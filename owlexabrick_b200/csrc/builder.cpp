@@ -9,11 +9,15 @@
 // come from one pass, and the left/right union boxes of all candidate planes come from
 // prefix/suffix unions instead of an O(planes x slices) rescan.  Passes over large nodes
 // are OpenMP-parallel; the recursion itself stays serial (left, then right) because that is
-// what defines the brick order.
+// what defines the brick order.  The records live in two uninitialised arrays allocated once:
+// a node partitions its span of one array into the same span of the other (left part first)
+// and the children recurse with the roles swapped, so nothing is allocated, zero-filled or
+// page-faulted serially on the way down (that, not the passes, dominated at 650 M cells).
 #include "exa_internal.h"
 #include <algorithm>
 #include <atomic>
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 #include <stdexcept>
@@ -63,10 +67,15 @@ struct Builder {
     h ^= h >> 29; h *= 0xBF58476D1CE4E5B9ull; h ^= h >> 32;
     return h;
   }
-  std::vector<Rec> dedup(const int32_t *cells, size_t n)
+  // -> number of surviving records written to out[0..) (out has room for n)
+  size_t dedup(const int32_t *cells, size_t n, Rec *out)
   {
     size_t cap = 1; while (cap < 2 * n + 16) cap <<= 1;
-    std::vector<std::atomic<int32_t>> table(cap);
+    // uninitialised storage, first touched by the parallel fill below
+    std::atomic<int32_t> *table = reinterpret_cast<std::atomic<int32_t> *>(malloc(cap * sizeof(int32_t)));
+    std::vector<uint8_t> keepStore; uint8_t *keep = nullptr;
+    if (!table) throw std::runtime_error("out of memory in the duplicate-removal table");
+    struct Free { void *p; ~Free() { free(p); } } freeTable{table};
 #pragma omp parallel for schedule(static)
     for (size_t i = 0; i < cap; i++) table[i].store(-1, std::memory_order_relaxed);
     auto same = [&](int32_t a, const int32_t *c) { return memcmp(cells + 4 * (size_t)a, c, 16) == 0; };
@@ -86,32 +95,45 @@ struct Builder {
         h = (h + 1) & (cap - 1);
       }
     }
-    std::vector<uint8_t> keep(n);
-#pragma omp parallel for schedule(static)
-    for (size_t i = 0; i < n; i++) {
-      const int32_t *c = cells + 4 * i;
-      size_t h = hashCell(c) & (cap - 1);
-      for (;;) {
-        const int32_t cur = table[h].load(std::memory_order_relaxed);
-        if (same(cur, c)) { keep[i] = cur == (int32_t)i; break; }
-        h = (h + 1) & (cap - 1);
+    keep = (uint8_t *)malloc(n ? n : 1);
+    if (!keep) throw std::runtime_error("out of memory in duplicate removal");
+    Free freeKeep{keep};
+    const int T = omp_get_max_threads();
+    std::vector<size_t> cnt(T + 1, 0);
+#pragma omp parallel num_threads(T)
+    {
+      const int t = omp_get_thread_num();
+      const size_t b = n * (size_t)t / T, e = n * (size_t)(t + 1) / T;
+      size_t k = 0;
+      for (size_t i = b; i < e; i++) {
+        const int32_t *c = cells + 4 * i;
+        size_t h = hashCell(c) & (cap - 1);
+        for (;;) {
+          const int32_t cur = table[h].load(std::memory_order_relaxed);
+          if (same(cur, c)) { keep[i] = cur == (int32_t)i; k += keep[i]; break; }
+          h = (h + 1) & (cap - 1);
+        }
       }
+      cnt[t + 1] = k;
+#pragma omp barrier
+#pragma omp single
+      for (int q = 0; q < T; q++) cnt[q + 1] += cnt[q];
+      size_t p = cnt[t];                                 // ascending id order, as the serial scan
+      for (size_t i = b; i < e; i++)
+        if (keep[i]) out[p++] = Rec{cells[4 * i], cells[4 * i + 1], cells[4 * i + 2], cells[4 * i + 3], (int)i};
     }
-    std::vector<Rec> out; out.reserve(n);
-    for (size_t i = 0; i < n; i++)
-      if (keep[i]) out.push_back(Rec{cells[4 * i], cells[4 * i + 1], cells[4 * i + 2], cells[4 * i + 3], (int)i});
-    return out;
+    return cnt[T];
   }
 
-  Box4 boundsOf(const std::vector<Rec> &v)
+  Box4 boundsOf(const Rec *v, size_t n)
   {
     Box4 b;
-    if (v.size() < PAR_THRESHOLD) { for (auto &c : v) b.extendCell(c); return b; }
+    if (n < PAR_THRESHOLD) { for (size_t i = 0; i < n; i++) b.extendCell(v[i]); return b; }
 #pragma omp parallel
     {
       Box4 lb;
 #pragma omp for schedule(static) nowait
-      for (size_t i = 0; i < v.size(); i++) lb.extendCell(v[i]);
+      for (size_t i = 0; i < n; i++) lb.extendCell(v[i]);
 #pragma omp critical
       b.extend(lb);
     }
@@ -119,25 +141,25 @@ struct Builder {
   }
 
   // tryMakeLeaf, builder.cpp:447-530
-  bool tryMakeLeaf(const Box4 &b, const std::vector<Rec> &v, unsigned nodeID)
+  bool tryMakeLeaf(const Box4 &b, const Rec *v, size_t n, unsigned nodeID)
   {
-    if (v.empty()) throw std::runtime_error("empty ID vector in tryMakeLeaf!?");
+    if (n == 0) throw std::runtime_error("empty ID vector in tryMakeLeaf!?");
     if (b.size(3) > 1) return false;
     const size_t cw = 1ULL << (b.hi[3] - 1);
     for (int d = 0; d < 3; d++) if ((size_t)b.size(d) / cw > (size_t)maxLeafWidth) return false;
     const long long vol = (long long)b.size(0) * b.size(1) * b.size(2) * b.size(3);
-    if ((size_t)vol != v.size() * (cw * cw * cw)) return false;
+    if ((size_t)vol != n * (cw * cw * cw)) return false;
     ExaBrick h;
     for (int d = 0; d < 3; d++) { h.lower[d] = b.lo[d]; h.size[d] = b.size(d) / (int)cw; }
     h.level = b.lo[3];
-    if (ids.size() + v.size() > 0xffffffffull) throw std::runtime_error("overflow in 32-bit brick offset");
+    if (ids.size() + n > 0xffffffffull) throw std::runtime_error("overflow in 32-bit brick offset");
     h.begin = (uint32_t)ids.size();
     const size_t base = ids.size();
-    ids.resize(base + v.size(), -1);
+    ids.resize(base + n, -1);
     int32_t *dst = ids.data() + base;
     const size_t sx = h.size[0], sxy = (size_t)h.size[0] * h.size[1];
-#pragma omp parallel for schedule(static) if (v.size() >= PAR_THRESHOLD)
-    for (size_t i = 0; i < v.size(); i++) {
+#pragma omp parallel for schedule(static) if (n >= PAR_THRESHOLD)
+    for (size_t i = 0; i < n; i++) {
       const Rec &c = v[i];
       dst[(c.x - b.lo[0]) / (int)cw + sx * ((c.y - b.lo[1]) / (int)cw) + sxy * ((c.z - b.lo[2]) / (int)cw)] = c.id;
     }
@@ -151,12 +173,13 @@ struct Builder {
   struct Slices { std::vector<size_t> vol; std::vector<Box4> box; };
 
   // Bricker::buildRec, builder.cpp:538-811
-  void buildRec(std::vector<Rec> &v, unsigned nodeID)
+  // v = this node's records; o = the same span of the other array (scratch for the partition)
+  void buildRec(Rec *v, Rec *o, size_t n, unsigned nodeID)
   {
-    Box4 cb = boundsOf(v);                               // computeCoarsestLevelBounds :201-225
+    Box4 cb = boundsOf(v, n);                              // computeCoarsestLevelBounds :201-225
     const int ccw = 1 << (cb.hi[3] - 1);
     for (int d = 0; d < 3; d++) { cb.lo[d] = ccw * divDown(cb.lo[d], ccw); cb.hi[d] = ccw * divUp(cb.hi[d], ccw); }
-    if (tryMakeLeaf(cb, v, nodeID)) return;
+    if (tryMakeLeaf(cb, v, n, nodeID)) return;
     const int dims[3] = {cb.size(0) / ccw, cb.size(1) / ccw, cb.size(2) / ccw};
     if (dims[0] == 1 && dims[1] == 1 && dims[2] == 1) throw std::runtime_error("coarse size 1 that's not a leaf!?");
     const int maxLevel = cb.hi[3] - 1;                   // == max over slice level lists, :592-598
@@ -171,14 +194,14 @@ struct Builder {
         const int bin[3] = {(c.x - cb.lo[0]) / ccw, (c.y - cb.lo[1]) / ccw, (c.z - cb.lo[2]) / ccw};
         for (int d = 0; d < 3; d++) { s[d].vol[bin[d]] += cv; s[d].box[bin[d]].extendCell(c); }
       };
-      if (v.size() < PAR_THRESHOLD) { for (auto &c : v) splat(sl, c); }
+      if (n < PAR_THRESHOLD) { for (size_t i = 0; i < n; i++) splat(sl, v[i]); }
       else {
 #pragma omp parallel
         {
           Slices loc[3];
           for (int d = 0; d < 3; d++) { loc[d].vol.assign(dims[d], 0); loc[d].box.assign(dims[d], Box4()); }
 #pragma omp for schedule(static) nowait
-          for (size_t i = 0; i < v.size(); i++) splat(loc, v[i]);
+          for (size_t i = 0; i < n; i++) splat(loc, v[i]);
 #pragma omp critical
           for (int d = 0; d < 3; d++) for (int i = 0; i < dims[d]; i++) { sl[d].vol[i] += loc[d].vol[i]; sl[d].box[i].extend(loc[d].box[i]); }
         }
@@ -213,51 +236,51 @@ struct Builder {
       bestPos = cb.lo[bestDim] + (dims[bestDim] / 2) * ccw;
     }
 
-    // ---- partition (:753-770) ----
-    std::vector<Rec> l, r;
+    // ---- partition (:753-770): v -> o, left part first, order kept ----
     auto coord = [&](const Rec &c) { return bestDim == 0 ? c.x : bestDim == 1 ? c.y : c.z; };
-    if (v.size() < PAR_THRESHOLD) {
-      for (auto &c : v) {
-        const int lo = coord(c);
-        if (lo >= bestPos) r.push_back(c);
-        else if (lo + (1 << c.level) <= bestPos) l.push_back(c);
-        else throw std::runtime_error("cell straddles split plane!?");
+    size_t nl = 0;
+    if (n < PAR_THRESHOLD) {
+      for (size_t i = 0; i < n; i++) {
+        const int lo = coord(v[i]);
+        if (lo >= bestPos) continue;
+        if (lo + (1 << v[i].level) > bestPos) throw std::runtime_error("cell straddles split plane!?");
+        nl++;
       }
+      size_t pl = 0, pr = nl;
+      for (size_t i = 0; i < n; i++) { if (coord(v[i]) >= bestPos) o[pr++] = v[i]; else o[pl++] = v[i]; }
     } else {
       const int T = omp_get_max_threads();
-      std::vector<size_t> cl(T + 1, 0), cr(T + 1, 0);
+      std::vector<size_t> cl(T + 1, 0);
       bool straddle = false;
 #pragma omp parallel num_threads(T)
       {
         const int t = omp_get_thread_num();
-        const size_t b = v.size() * t / T, e = v.size() * (t + 1) / T;
-        size_t nl = 0, nr = 0;
+        const size_t b = n * (size_t)t / T, e = n * (size_t)(t + 1) / T;
+        size_t k = 0;
         for (size_t i = b; i < e; i++) {
           const int lo = coord(v[i]);
-          if (lo >= bestPos) nr++; else if (lo + (1 << v[i].level) <= bestPos) nl++; else straddle = true;
+          if (lo >= bestPos) continue;
+          if (lo + (1 << v[i].level) <= bestPos) k++; else straddle = true;
         }
-        cl[t + 1] = nl; cr[t + 1] = nr;
+        cl[t + 1] = k;
 #pragma omp barrier
 #pragma omp single
-        {
-          for (int k = 0; k < T; k++) { cl[k + 1] += cl[k]; cr[k + 1] += cr[k]; }
-          l.resize(cl[T]); r.resize(cr[T]);
-        }
-        size_t pl = cl[t], pr = cr[t];
+        for (int q = 0; q < T; q++) cl[q + 1] += cl[q];
+        size_t pl = cl[t], pr = cl[T] + (b - cl[t]);
         if (!straddle)
-          for (size_t i = b; i < e; i++) { if (coord(v[i]) >= bestPos) r[pr++] = v[i]; else l[pl++] = v[i]; }
+          for (size_t i = b; i < e; i++) { if (coord(v[i]) >= bestPos) o[pr++] = v[i]; else o[pl++] = v[i]; }
       }
       if (straddle) throw std::runtime_error("cell straddles split plane!?");
+      nl = cl[T];
     }
-    if (l.empty() || r.empty()) throw std::runtime_error("invalid split...");
+    if (nl == 0 || nl == n) throw std::runtime_error("invalid split...");
     const unsigned firstChild = (unsigned)tree.size();   // :794-800
     tree.emplace_back(ExaKdTreeNode{0, 0, 0}); tree.emplace_back(ExaKdTreeNode{0, 0, 0});
     tree[nodeID].axis_bits = ((unsigned)bestDim << 30) | firstChild;
     tree[nodeID].split_or_first_prim = (uint32_t)bestPos;
     tree[nodeID].max_level = maxLevel;
-    std::vector<Rec>().swap(v);
-    buildRec(l, firstChild);                             // :808-810 left, then right
-    buildRec(r, firstChild + 1);
+    buildRec(o, v, nl, firstChild);                      // :808-810 left, then right
+    buildRec(o + nl, v + nl, n - nl, firstChild + 1);
   }
 };
 
@@ -268,9 +291,17 @@ BricksImpl *buildBricks(const int32_t *cells, size_t numCells, int builderType, 
   if (numCells > 0x7fffffffull) throw std::runtime_error("more than 2^31 cells: ids are 32-bit (builder.cpp:45)");
   Builder B; B.builderType = builderType; B.maxLeafWidth = maxLeafWidth;
   B.tree.emplace_back(ExaKdTreeNode{0, 0, 0});
-  for (size_t i = 0; i < numCells; i++) if (cells[4 * i + 3] < 0 || cells[4 * i + 3] > 30) throw std::runtime_error("cell level out of range");
-  std::vector<Rec> v = B.dedup(cells, numCells);
-  if (!v.empty()) B.buildRec(v, 0);
+  bool badLevel = false;
+#pragma omp parallel for schedule(static) reduction(|| : badLevel)
+  for (size_t i = 0; i < numCells; i++) badLevel = badLevel || cells[4 * i + 3] < 0 || cells[4 * i + 3] > 30;
+  if (badLevel) throw std::runtime_error("cell level out of range");
+  struct Buf { Rec *p = nullptr; ~Buf() { free(p); } } a, b;
+  a.p = (Rec *)malloc(sizeof(Rec) * (numCells ? numCells : 1));
+  if (!a.p) throw std::runtime_error("out of memory in the builder");
+  const size_t n = B.dedup(cells, numCells, a.p);
+  b.p = (Rec *)malloc(sizeof(Rec) * (n ? n : 1));
+  if (!b.p) throw std::runtime_error("out of memory in the builder");
+  if (n) B.buildRec(a.p, b.p, n, 0);
   return bricksFromParts(std::move(B.hdr), std::move(B.ids), std::move(B.tree));
 }
 
