@@ -312,43 +312,80 @@ def run_product(args):
         # the only per-frame exchange is a 4-byte all-reduce that orders the frame's completion
         r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
         import ctypes as C
-        hbuf = torch.zeros(64, dtype=torch.uint8)
+        # swap chain of two RGBA8 frame buffers on rank 0, mapped into every rank (CUDA IPC): frame i
+        # goes to buffer i&1, so the completion exchange (and the consumer's read-back) of frame i
+        # overlaps the rendering of frame i+1
+        hbuf = torch.zeros(2 * 64, dtype=torch.uint8)
+        fb_ptrs = [None, None]
         if rank == 0:
-            _, fb0 = r.device_buffers()
-            capi.check(capi.lib.exa_ipc_export(C.c_void_p(fb0), C.c_void_p(hbuf.data_ptr())))
+            for k in range(2):
+                pp = C.c_void_p()
+                capi.check(capi.lib.exa_device_malloc(npix * 4, local, C.byref(pp)))
+                fb_ptrs[k] = pp.value
+                capi.check(capi.lib.exa_ipc_export(C.c_void_p(pp.value), C.c_void_p(hbuf.data_ptr() + 64 * k)))
         hdev = hbuf.cuda()
         dist.broadcast(hdev, 0)
         hbuf = hdev.cpu()
         if rank != 0:
-            pp = C.c_void_p()
             try:
                 if args.no_peer_fb:
                     raise RuntimeError("--no-peer-fb")
-                capi.check(capi.lib.exa_ipc_import(C.c_void_p(hbuf.data_ptr()), local, C.byref(pp)))
-                peer_fb = pp.value
-                r.resizeFrameBuffer(peer_fb, (W, H))
+                for k in range(2):
+                    pp = C.c_void_p()
+                    capi.check(capi.lib.exa_ipc_import(C.c_void_p(hbuf.data_ptr() + 64 * k), local, C.byref(pp)))
+                    fb_ptrs[k] = pp.value
             except Exception as e:                                    # no peer mapping: fall back to an NCCL reduce of the frame
                 log("rank %d: CUDA IPC import failed (%s); using NCCL reduce" % (rank, e))
-        ok = torch.tensor([1 if (rank == 0 or peer_fb) else 0], device="cuda")
+                fb_ptrs = [None, None]
+        ok = torch.tensor([1 if (fb_ptrs[1] and not args.no_peer_fb) else 0], device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         use_peer = bool(ok.item())
-        fb_t = None
-        if not use_peer:                                              # caller-owned torch frame buffers, summed onto rank 0
+        fb_t, fb_views = None, None
+        if use_peer:
+            r.resizeFrameBuffer(fb_ptrs[0], (W, H))
+            if rank == 0:                                             # torch views of the two raw allocations (read-back source)
+                class _Raw:
+                    def __init__(self, ptr):
+                        self.__cuda_array_interface__ = {"shape": (H, W), "typestr": "<i4", "data": (ptr, False), "version": 2}
+                fb_views = [torch.as_tensor(_Raw(p_), device="cuda") for p_ in fb_ptrs]
+        else:                                                         # caller-owned torch frame buffers, summed onto rank 0
             fb_t = torch.zeros(npix, dtype=torch.int32, device="cuda")
-            r.resizeFrameBuffer(fb_t.data_ptr(), (W, H)); peer_fb = None
+            r.resizeFrameBuffer(fb_t.data_ptr(), (W, H))
         done_flag = torch.zeros(1, dtype=torch.int32, device="cuda")
-        log("rank %d: image-tile mode, %s" % (rank, "peer frame buffer over NVLink" if use_peer else "NCCL reduce"))
+        side = torch.cuda.Stream()                                    # completion exchange + read-back of the previous frame
+        ev_render = [torch.cuda.Event(), torch.cuda.Event()]
+        ev_done = [torch.cuda.Event(), torch.cuda.Event()]
+        frame_no = [0]
+        log("rank %d: image-tile mode, %s" % (rank, "double-buffered peer frame buffer over NVLink" if use_peer else "NCCL reduce"))
 
-    def step():
+    def drain():
+        """main stream waits for the completion exchanges still in flight on the side stream"""
+        if mode == "tiles" and use_peer:
+            stream.wait_event(ev_done[0]); stream.wait_event(ev_done[1])
+
+    def step(readback=None):
         if mode == "none":
             r.render(sync=False)
             return 1
+        if mode == "tiles" and use_peer:
+            b = frame_no[0] & 1
+            frame_no[0] += 1
+            stream.wait_event(ev_done[b])                             # buffer b: frame i-2 complete everywhere (and read back)
+            capi.check(capi.lib.exa_renderer_set_color_buffer(r.h, C.c_void_p(fb_ptrs[b])))
+            r.render(sync=False)                                      # own tiles -> rank 0's buffer b over NVLink
+            ev_render[b].record(stream)
+            with torch.cuda.stream(side):
+                side.wait_event(ev_render[b])
+                dist.all_reduce(done_flag)                            # frame i complete on every rank
+                if readback is not None:
+                    if rank == 0:
+                        readback[b].copy_(fb_views[b], non_blocking=True)
+                    dist.all_reduce(done_flag)                        # buffer b released by the consumer
+                ev_done[b].record(side)
+            return 1
         if mode == "tiles":
             r.render(sync=False)
-            if use_peer:
-                dist.all_reduce(done_flag)                            # frame complete on every rank
-            else:
-                dist.reduce(fb_t, 0)                                  # tiles are disjoint and the rest is 0: sum = union (rank 0's copy is final)
+            dist.reduce(fb_t, 0)                                      # tiles are disjoint and the rest is 0: sum = union (rank 0's copy is final)
             return 1
         r.render_partial(partial.data_ptr())
         _, _, k = binary_swap(r, dist, torch, partial, npix, rank, world, None)
@@ -371,33 +408,6 @@ def run_product(args):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    # N>1, image tiles: the step (frame kernel + completion all-reduce) is a few tens of
-    # microseconds of GPU work, so it is captured once into a CUDA graph and replayed
-    graph, graph_launches = None, 0
-    if mode == "tiles" and args.graph:
-        try:
-            g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
-                r.set_stream(torch.cuda.current_stream().cuda_stream)
-                graph_launches = step()
-            graph = g
-        except Exception as e:
-            log("rank %d: CUDA graph capture failed (%s); eager steps" % (rank, e))
-        r.set_stream(stream.cuda_stream)
-        okg = torch.tensor([1 if graph is not None else 0], device="cuda")
-        dist.all_reduce(okg, op=dist.ReduceOp.MIN)
-        if not bool(okg.item()):
-            graph = None
-        if graph is not None:
-            eager_step = step
-
-            def step():                                              # noqa: F811
-                graph.replay()
-                return graph_launches
-            for _ in range(3):
-                step()
-            torch.cuda.synchronize()
-            dist.barrier()
     l0 = r.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
@@ -405,6 +415,7 @@ def run_product(args):
     launches = 0
     for _ in range(args.steps):
         launches += step()
+    drain()
     ev1.record(stream)
     torch.cuda.synchronize()
     if world > 1:
@@ -414,7 +425,7 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms = float(tms.item())
-    lib_launches = (r.launch_count() - l0) if graph is None else launches   # graph replays do not pass through the library's counter
+    lib_launches = r.launch_count() - l0
     ms_step = ms / args.steps
     value = tot["samples"] / (ms_step * 1e-3)
 
@@ -432,13 +443,12 @@ def run_product(args):
             r.render(sync=False)
             capi.check(capi.lib.exa_renderer_read_rgba8_async(r.h, host_ring[e2e_count[0] & 1].data_ptr()))   # device -> host: W*H*4
             e2e_count[0] += 1
+        elif mode == "tiles" and use_peer:
+            step(readback=host_ring)                                  # rank 0 copies frame i to pinned host memory while frame i+1 renders
         elif mode == "tiles":
             step()
             if rank == 0:
-                if use_peer:
-                    capi.check(capi.lib.exa_renderer_read_rgba8(r.h, host_img.data_ptr()))
-                else:
-                    host_img.view(-1).copy_(fb_t, non_blocking=False)
+                host_img.view(-1).copy_(fb_t, non_blocking=False)
         else:
             r.render_partial(partial.data_ptr())
             strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
@@ -452,6 +462,7 @@ def run_product(args):
     t = time.perf_counter()
     for _ in range(args.steps):
         e2e_step()
+    drain()
     r.sync()                                                         # render stream + copy stream: the last frame is in host memory
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t
@@ -516,9 +527,14 @@ def run_product(args):
     if world > 1:
         from owlexabrick_b200 import multigpu
         if mode == "tiles":
-            step(); torch.cuda.synchronize(); dist.barrier()
+            last = frame_no[0] & 1 if use_peer else 0
+            drain(); torch.cuda.synchronize()
+            if rank == 0:                                             # stale pixels must not be able to hide a missing tile
+                (fb_views[last] if use_peer else fb_t).zero_(); torch.cuda.synchronize()
+            dist.barrier()
+            step(); drain(); torch.cuda.synchronize(); dist.barrier()
             if rank == 0:
-                img_n = r.read_rgba8().reshape(-1) if use_peer else fb_t.cpu().numpy().view(np.uint32)
+                img_n = (fb_views[last] if use_peer else fb_t).cpu().numpy().view(np.uint32).reshape(-1)
         else:
             r.render_partial(partial.data_ptr())
             strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
@@ -622,14 +638,14 @@ def run_product(args):
                 "config": {"workload": workload_name(name), "cells": int(ncells), "bricks": bricks.num_bricks, "regions": int(len(regions)),
                            "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
                            "parallelism": "1 GPU" if world == 1 else ("sort-last kd partition x%d, NCCL binary swap" % world if mode == "sortlast" else
-                                           "image tiles x%d (data replicated), %s" % (world, "RGBA8 stored into rank 0's frame buffer over NVLink peer memory + 4-B all-reduce" if use_peer else "NCCL reduce of the RGBA8 frame")),
+                                           "image tiles x%d (data replicated), %s" % (world, "RGBA8 stored into rank 0's double-buffered frame buffer over NVLink peer memory + 4-B all-reduce per frame" if use_peer else "NCCL reduce of the RGBA8 frame")),
                            "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
                            "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"],
-                           "step": "CUDA graph replay" if graph is not None else "eager launches"},
+                           "step": "eager launches" + (", frames double-buffered: the completion all-reduce of frame i runs on a side stream while frame i+1 renders" if (world > 1 and mode == "tiles" and use_peer) else "")},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
                         "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4,
-                        "d2h_copy_alone_ms": d2h_ms, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory (exa_renderer_read_rgba8_async)" if world == 1 else "blocking read-back on rank 0"},
+                        "d2h_copy_alone_ms": d2h_ms, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory" + (" (exa_renderer_read_rgba8_async)" if world == 1 else " on rank 0 (swap chain of two peer-mapped buffers)") if (world == 1 or (mode == "tiles" and use_peer)) else "blocking read-back on rank 0"},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": ncu_traffic("k_renderFrame", name) if world == 1 else None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
@@ -637,11 +653,17 @@ def run_product(args):
                 "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms, "cpu_baseline": cpu}
         print(json.dumps(line), flush=True)
     if world > 1:
-        if graph is not None:                                        # a live graph that captured NCCL work blocks the teardown
-            step = None
-            del graph, g
-            torch.cuda.synchronize()
+        torch.cuda.synchronize()
         dist.barrier()
+        if mode == "tiles" and use_peer:                             # unmap / free the swap chain
+            r.resizeFrameBuffer(None, (W, H))
+            for p_ in fb_ptrs:
+                capi.check(capi.lib.exa_ipc_close(C.c_void_p(p_)) if rank != 0 else 0)
+            dist.barrier()
+            if rank == 0:
+                fb_views = None
+                for p_ in fb_ptrs:
+                    capi.check(capi.lib.exa_device_free(C.c_void_p(p_)))
         dist.destroy_process_group()
 
 
@@ -654,7 +676,6 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-peer-fb", action="store_true", help="N>1 image tiles: NCCL reduce of the frame instead of peer-memory stores")
-    ap.add_argument("--graph", action="store_true", help="N>1 image tiles: capture the step into a CUDA graph (measured: no gain, the step is GPU-bound)")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup

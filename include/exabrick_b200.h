@@ -312,6 +312,11 @@ int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, s
 int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_compositedRGBA, size_t first,
                                size_t count, uint32_t *d_rgba8Out);
 
+/* A device allocation of its own (cudaMalloc, zero-filled): unlike a sub-allocation of a caching
+ * allocator it can be exported with exa_ipc_export.  Multi-GPU image-tile callers allocate the
+ * shared frame buffers with it (double-buffered swap chain, bench.py). */
+int exa_device_malloc(size_t bytes, int cudaDevice, void **d_ptr);
+int exa_device_free(void *d_ptr);
 /* Peer framebuffer (one process per GPU, one node): rank 0 exports its RGBA8 buffer, the other
  * ranks import it and pass the pointer to exa_renderer_resize_framebuffer, so that in
  * image-tile mode every rank's frame kernel stores its tiles straight into rank 0's frame

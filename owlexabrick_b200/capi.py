@@ -50,6 +50,8 @@ _SIG = {
     "exa_renderer_debug_counters": (i32, [vp, vp]),
     "exa_renderer_set_color_buffer": (i32, [vp, vp]),
     "exa_renderer_read_rgba8_async": (i32, [vp, vp]),
+    "exa_device_malloc": (i32, [C.c_size_t, i32, C.POINTER(vp)]),
+    "exa_device_free": (i32, [vp]),
     "exa_ipc_export": (i32, [vp, vp]),
     "exa_ipc_import": (i32, [vp, i32, C.POINTER(vp)]),
     "exa_ipc_close": (i32, [vp]),

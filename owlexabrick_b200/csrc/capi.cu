@@ -305,6 +305,15 @@ void exa_renderer_destroy(exa_renderer_t *r)
   delete r;
 }
 
+int exa_device_malloc(size_t bytes, int cudaDevice, void **d_ptr)
+{
+  if (!d_ptr || bytes == 0) { setError("exa_device_malloc: bad argument"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(cudaDevice));
+  CKR(cudaMalloc(d_ptr, bytes));                            // its own allocation: exportable with exa_ipc_export
+  CKR(cudaMemset(*d_ptr, 0, bytes));
+  return EXA_OK;
+}
+int exa_device_free(void *d_ptr) { if (d_ptr) CKR(cudaFree(d_ptr)); return EXA_OK; }
 int exa_ipc_export(const void *d_ptr, uint8_t handle[64])
 {
   static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t");
