@@ -25,6 +25,8 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
   P.partialOut = partialOut;
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)
+    if (!r->tileOrderValid)                                  // (re)start: both buffers' counters to zero, once
+      for (int i = 0; i < 2; i++) CKR(cudaMemsetAsync(r->d_tileOrder[i], 0, offsetof(TileOrder, list), r->stream));
     if (r->tileOrderValid) P.tileOrderIn = r->d_tileOrder[r->tileOrderCur];
     P.tileOrderOut = r->d_tileOrder[r->tileOrderCur ^ 1];
     r->tileOrderCur ^= 1; r->tileOrderValid = true;

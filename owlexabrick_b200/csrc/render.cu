@@ -521,6 +521,16 @@ static constexpr int TILE_W = 16, TILE_H = 8;
 // ISO: the implicit iso-surface pass is compiled in only when an iso-surface is enabled; the plain
 // DVR instantiation is less than half the code, which matters because every CTA runs through
 // the kernel once, front to back (instruction fetch, not data, is what a lone CTA waits for).
+// Image-tile mode: tiles are dealt in blocks of numRanks consecutive tiles and the deal rotates by
+// one from block to block, so that a rank does not get the same tile columns in every tile row
+// (a plain t mod N does when N divides the tiles per row: 3840/16 = 240 = 30 * 8).
+__host__ __device__ inline int ownedTile(int j, int rank, int numRanks) { return j * numRanks + (rank + j) % numRanks; }
+__host__ __device__ inline int numOwnedTiles(int numTiles, int rank, int numRanks)
+{
+  const int full = numTiles / numRanks, rem = numTiles % numRanks;
+  return full + ((rank + full) % numRanks < rem ? 1 : 0);
+}
+
 template <bool GRAD, bool STATS, bool DUAL, bool ISO>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
@@ -539,7 +549,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // first: longest-processing-time-first keeps the SMs busy to the end of the frame; without it
   // a few tiles of long rays finish alone).  Costs are CTA cycle counts, bucketed by log2; each
   // frame writes the lists the next one reads.  Image-tile mode (multi-GPU, data replicated):
-  // rank r owns tiles r, r + numRanks, ...; the grid holds only the owned tiles.
+  // the grid holds only the owned tiles (ownedTile()).
   const long long t_start = clock64();
 #ifdef EXA_PHASE_TIMING
   long long ph_setup = 0, ph_trav = 0, ph_sample = 0, ph_iters = 0, ph_t;
@@ -549,7 +559,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     int q = (int)blockIdx.x, b = TILE_BUCKETS - 1;
     for (; b > 0; b--) { const int n = P.tileOrderIn->count[b]; if (q < n) break; q -= n; }
     tileId = (int)P.tileOrderIn->list[(size_t)b * P.tileOrderCap + q];
-  } else tileId = P.tileMode ? P.rank + (int)blockIdx.x * P.numRanks : (int)blockIdx.x;
+  } else tileId = P.tileMode ? ownedTile((int)blockIdx.x, P.rank, P.numRanks) : (int)blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // warp w covers the 8x4 sub-tile (w&1, w>>1) of the 16x8 CTA tile
   const int px = (tileId % tilesX) * TILE_W + (warp & 1) * 8 + (lane & 7);
@@ -740,6 +750,13 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       const int b = min(TILE_BUCKETS - 1, max(0, 63 - __clzll(cyc | 1ull) - 10));      // log2(cycles / 1024)
       const int idx = atomicAdd(&P.tileOrderOut->count[b], 1);
       P.tileOrderOut->list[(size_t)b * P.tileOrderCap + idx] = (uint32_t)tileId;
+      // last CTA of the frame: every CTA has read its slot of tileOrderIn (its tile id came from
+      // there, long before this point), which is the next frame's output -> clear it here
+      // instead of a memset in front of every launch.  No fence: nothing is published.
+      if (atomicAdd(&P.tileOrderOut->done, 1) == (int)gridDim.x - 1) {
+        P.tileOrderOut->done = 0;
+        if (P.tileOrderIn) for (int i = 0; i < TILE_BUCKETS; i++) const_cast<TileOrder *>(P.tileOrderIn)->count[i] = 0;
+      }
     }
   }
 }
@@ -832,9 +849,8 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
   const int numTiles = tilesX * tilesY;
-  const int numMine = P.tileMode ? (numTiles - P.rank + P.numRanks - 1) / P.numRanks : numTiles;
+  const int numMine = P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
   if (numMine <= 0) return 0;
-  if (P.tileOrderOut) cudaMemsetAsync(P.tileOrderOut->count, 0, sizeof(int) * TILE_BUCKETS, s);
   const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
   static int numSMs = 0;

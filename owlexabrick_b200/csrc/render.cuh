@@ -8,7 +8,9 @@ namespace exa {
 // tile cost order of one frame: per log2(cycles) bucket a count and a list of tile ids
 // (list[b * cap + i]); written by frame N, read by frame N+1 (render.cu:k_renderFrame)
 static const int TILE_BUCKETS = 16;
-struct TileOrder { int count[TILE_BUCKETS]; uint32_t list[1]; };   // list: TILE_BUCKETS * cap entries
+// count[]/done of BOTH buffers are zeroed by the host when the order is invalidated; after that the
+// last CTA of a frame clears the buffer it read (the next frame's output), so no per-frame memset
+struct TileOrder { int count[TILE_BUCKETS]; int done; int pad[3]; uint32_t list[4]; };   // list: TILE_BUCKETS * cap entries
 
 // a long ray handed from k_renderFrame to k_renderLong (voxel-space ray + integration state)
 struct LongRay {

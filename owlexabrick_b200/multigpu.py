@@ -61,5 +61,12 @@ def tile_owner(tile, world):
 
 
 def owned_tiles(rank, world, width, height, tile_w=16, tile_h=8):
+    """tiles of rank `rank` in image-tile mode (render.cu:ownedTile): blocks of `world` consecutive
+    tiles, the deal rotating by one per block"""
     n = ((width + tile_w - 1) // tile_w) * ((height + tile_h - 1) // tile_h)
-    return list(range(rank, n, world))
+    out = []
+    for j in range((n + world - 1) // world):
+        t = j * world + (rank + j) % world
+        if t < n:
+            out.append(t)
+    return out

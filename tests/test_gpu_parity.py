@@ -300,6 +300,37 @@ def test_pipelined_readback_equals_blocking(R, orc):
         r.read_rgba8_async(host[0].data_ptr())
 
 
+@pytest.mark.parametrize("world", [2, 3, 8])
+def test_image_tile_partition_union_is_the_frame(R, orc, built_lib, world):
+    """multi-GPU image-tile mode, emulated on one GPU: each 'rank' renders exactly its
+    multigpu.owned_tiles into one shared frame buffer; the union is the 1-rank frame, bit for bit"""
+    import torch
+    from owlexabrick_b200 import multigpu
+    r, sc, fd, _ = _frame_pair(R, orc, "nb64_off", 1, size=(200, 116))      # not a multiple of the 16x8 tile
+    fd.apply(r)
+    r.render()
+    ref = r.read_rgba8().copy()
+    W, H = fd.width, fd.height
+    assert (ref != 0).all()                                                 # alpha byte: a written pixel is never 0
+    fb = torch.zeros((H, W), dtype=torch.int32, device="cuda")
+    built_lib.check(built_lib.lib.exa_renderer_set_color_buffer(r.h, fb.data_ptr()))
+    tiles_x = (W + 15) // 16
+    seen = np.zeros((H, W), bool)
+    for rank in range(world):
+        r.set_partition(built_lib.PARTITION_IMAGE_TILES, rank, world)
+        r.render(); r.render()                                              # second frame: cost-ordered tile schedule
+        now = fb.cpu().numpy().view(np.uint32) != 0
+        mine = np.zeros((H, W), bool)
+        for t in multigpu.owned_tiles(rank, world, W, H):
+            ty, tx = divmod(t, tiles_x)
+            mine[ty * 8:ty * 8 + 8, tx * 16:tx * 16 + 16] = True
+        assert ((now & ~seen) == mine).all(), "rank %d wrote outside its tiles / missed some" % rank
+        seen = now
+    assert (fb.cpu().numpy().view(np.uint32) == ref).all()
+    r.set_partition(built_lib.PARTITION_NONE, 0, 1)
+    built_lib.check(built_lib.lib.exa_renderer_set_color_buffer(r.h, None))
+
+
 def test_render_errors(R, orc):
     g = load_golden("ex4")
     b = R.ExaBricks.from_bytes(g["bricks"].tobytes())

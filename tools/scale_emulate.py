@@ -17,7 +17,7 @@ sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "tests"))
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", default="c2")
-    ap.add_argument("--image", default="1024x1024,3840x2160")
+    ap.add_argument("--image", default=None, help="WxH[,WxH...]; default: the workload's image")
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--ranks", default="1,2,4,8")
     a = ap.parse_args()
@@ -37,7 +37,7 @@ def main():
         for _ in range(n): r.render(sync=False)
         e1.record(stream); torch.cuda.synchronize()
         return e0.elapsed_time(e1) / n
-    for img in a.image.split(","):
+    for img in (a.image or "%dx%d" % tuple(bench.WORKLOADS[a.workload][2])).split(","):
         W, H = (int(x) for x in img.split("x"))
         fd = bench.frame_desc(R, domain, (W, H), frange); fd.apply(r)
         alpha, rgb = fd.xf[0]
@@ -45,10 +45,12 @@ def main():
             r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
             row = {"image": img, "xf": name}
             for n in (int(x) for x in a.ranks.split(",")):
-                worst = 0.0
-                for rank in sorted({0, n - 1, n // 2}):
+                worst, per_rank = 0.0, []
+                for rank in range(n):
                     r.set_partition(capi.PARTITION_IMAGE_TILES if n > 1 else capi.PARTITION_NONE, rank, n)
-                    worst = max(worst, time_frames(a.steps))
+                    per_rank.append(round(time_frames(a.steps), 4))
+                worst = max(per_rank)
+                row["N%d_ranks" % n] = per_rank
                 hist = (C.c_int * 16)(); capi.check(capi.lib.exa_renderer_get_tile_cost_histogram(r.h, hist))
                 row["N%d_ms" % n] = round(worst, 4)
                 row["N%d_hist" % n] = list(hist)
