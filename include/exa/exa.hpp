@@ -239,6 +239,12 @@ struct OptixRenderer {
 
   // headless extras
   void readColorBuffer(uint32_t *hostRGBA8) { detail::check(exa_renderer_read_rgba8(handle, hostRGBA8)); }
+  // pipelined variant: renderAsync(); readColorBufferAsync(pinned); ... sync() — frame i+1 renders while frame i is copied
+  void renderAsync() { detail::check(exa_renderer_render_async(handle)); }
+  void readColorBufferAsync(uint32_t *pinnedHostRGBA8) { detail::check(exa_renderer_read_rgba8_async(handle, pinnedHostRGBA8)); }
+  void sync() { detail::check(exa_renderer_sync(handle)); }
+  // swap the RGBA8 target without touching the accumulation buffer (swap chains, peer-mapped buffers); nullptr = renderer-owned
+  void setColorBuffer(void *fbPointer) { detail::check(exa_renderer_set_color_buffer(handle, fbPointer)); }
   void readAccumBuffer(float *hostRGBA) { detail::check(exa_renderer_read_accum(handle, hostRGBA)); }
   void samplePoints(const float *xyz, size_t n, int channel, float *values, uint8_t *valid, float *grad = nullptr)
   { detail::check(exa_sample_points_host(handle, xyz, n, channel, values, valid, grad)); }
