@@ -41,6 +41,11 @@ WORKLOADS = {
     "c3": ((4096, 1024, 2048), ("exajet", 1), (3840, 2160)),
     "c3s2": ((2048, 512, 1024), ("exajet", 2), (1920, 1080)),
     "c3s4": ((1024, 256, 512), ("exajet", 4), (960, 540)),
+    # C4 landing-gear-shaped: 7 levels, small deeply nested off-centre level-0 core -> 262 277 632 cells; iso + DVR
+    "c4": (8192, [((2048, 1536, 2560), (2608, 2080, 3104)), ((1920, 1408, 2432), (2752, 2208, 3232)), ((1664, 1152, 2176), (3008, 2496, 3520)),
+                  ((1280, 768, 1792), (3328, 2816, 3840)), ((768, 256, 1280), (3840, 3328, 4352)), ((0, 0, 0), (5120, 4096, 5120))], (3840, 2160)),
+    "c4s4": (2048, [((512, 384, 640), (652, 520, 776)), ((480, 352, 608), (688, 552, 808)), ((416, 288, 544), (752, 624, 880)),
+                    ((320, 192, 448), (832, 704, 960)), ((192, 64, 320), (960, 832, 1088)), ((0, 0, 0), (1280, 1024, 1280))], (960, 540)),
     "c2": (1024, [(320, 704), (192, 832)], (1024, 1024)),
     "c1": (256, [(72, 184), (32, 224)], (1024, 1024)),
     "small": (64, [(18, 46), (8, 56)], (256, 256)),
@@ -159,7 +164,7 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
 
 
-def frame_desc(R, domain, image, field_range):
+def frame_desc(R, domain, image, field_range, iso=False):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import scenes
     W, H = image
@@ -167,7 +172,13 @@ def frame_desc(R, domain, image, field_range):
     fd.opacity_scale = OPACITY_SCALE
     fd.dt = DT
     fd.xf_domain = [(float(field_range[0]), float(field_range[1]))]
+    if iso:                                  # C4: one implicit iso-surface at the XF-domain midpoint, channel 0, + DVR
+        fd.iso = [(1, 0.5 * (float(field_range[0]) + float(field_range[1])), 0), (0, 0.0, 0)]
     return fd
+
+
+def has_iso(name):
+    return name.startswith("c4")
 
 
 def algorithmic_bytes(st, W, H):
@@ -203,8 +214,8 @@ def run_reference(args):
     name = args.workload
     domain, _, image = WORKLOADS[name]
     t = time.time()
-    if name.startswith("c3"):
-        # 650 M cells: the serial restatement of exaBuilder needs > 10 min, so the (untimed) scene
+    if name in ("c3", "c3s2", "c3s4", "c4"):
+        # 260-650 M cells: the serial restatement of exaBuilder needs > 10 min, so the (untimed) scene
         # set-up takes the bricks from the OpenMP host builder, whose output is bit-exact with
         # it (tests/test_host.py); flatten, ABR build and the timed frames are the oracle's
         bricks, field = load_or_build_scene(name, R)
@@ -219,7 +230,7 @@ def run_reference(args):
         del cells
     log("cpu scene built in %.1fs" % (time.time() - t))
     W, H = image
-    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
+    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())), iso=has_iso(name))
     # one step = the WHOLE frame on all host cores (the oracle's region query is BVH-accelerated,
     # oracle.cpp:closestRegion, so a C2 frame is a fraction of a second)
     window = (0, 0, W, H)
@@ -246,6 +257,9 @@ def workload_name(name):
     if isinstance(shape, tuple):
         return "%s: synthetic exajet-shaped 4-level AMR (fuselage/wing/tail/wake boxes), domain %dx%dx%d, single scalar, DVR %dx%d, default camera/XF" % (
             (name,) + tuple(int(x) for x in domain) + (image[0], image[1]))
+    if has_iso(name):
+        return "%s: synthetic landing-gear-shaped %d-level nested AMR (off-centre core), domain %d^3, single scalar, implicit iso-surface (XF-domain midpoint) + DVR %dx%d, default camera/XF" % (
+            name, len(shape) + 1, domain, image[0], image[1])
     return "%s: synthetic 3-level nested-box AMR, domain %d^3, single scalar, DVR %dx%d, default camera/XF" % (name, domain, image[0], image[1])
 
 
@@ -298,7 +312,7 @@ def run_product(args):
     log("rank %d: renderer created in %.1fs (%d regions, L=%d, kd %s)" % (rank, time.time() - t, len(regions), len(leaf), r.kd_info()))
     stream = torch.cuda.current_stream()
     r.set_stream(stream.cuda_stream)
-    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())))
+    fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())), iso=has_iso(name))
     fd.apply(r)
     npix = W * H
     mode = "none" if world == 1 else args.partition

@@ -331,6 +331,73 @@ def test_image_tile_partition_union_is_the_frame(R, orc, built_lib, world):
     built_lib.check(built_lib.lib.exa_renderer_set_color_buffer(r.h, None))
 
 
+# ------------------------------------------------------------------------------------------
+# full size (BASELINE.json configs[1], ~95 M cells): size-independent properties, no oracle
+# ------------------------------------------------------------------------------------------
+_C2 = {}
+
+
+def _c2_scene(R):
+    """bricks + three fields of config C2, built once per session: f (SURVEY 8d analytic field),
+    the constant 1, and 2 f + 3"""
+    if not _C2:
+        cells = synth.nested_boxes(1024, [(320, 704), (192, 832)])
+        assert len(cells) == 94994432
+        f = np.empty(len(cells), np.float32)
+        for b in range(0, len(cells), 1 << 23):
+            f[b:b + (1 << 23)] = synth.analytic_field_chunked(cells[b:b + (1 << 23)], 1024, 0, first=b)
+        _C2["bricks"] = R.ExaBricks.build(cells)
+        _C2["fields"] = [f, np.ones_like(f), (2.0 * f.astype(np.float64) + 3.0).astype(np.float32)]
+    return _C2["bricks"], _C2["fields"]
+
+
+def test_full_size_c2_properties(R, orc, scalar_layout):
+    """at full size: partition of unity (constant field reconstructs to itself at every one of
+    1 M points), linearity across channels, every point of the domain is covered, the frame
+    is reproducible launch to launch (tile schedule changes between frames), multi-channel DVR
+    of identical channels is well defined"""
+    bricks, fields = _c2_scene(R)
+    r = R.Renderer(bricks, fields)
+    assert r.scalar_layout()[0] == (1 if scalar_layout == "flat" else 2)
+    regions, leaf = r.get_abr()
+    assert leaf.min() >= 0 and leaf.max() < bricks.num_bricks and len(set(leaf.tolist())) == bricks.num_bricks
+    pts = synth.random_points(1 << 20, [0.0] * 3, [1024.0] * 3, seed=7)
+    v0, ok0 = r.sample_points(pts, 0)
+    v1, ok1 = r.sample_points(pts, 1)
+    v2, ok2 = r.sample_points(pts, 2)
+    assert ok0.all() and ok1.all() and ok2.all()                       # the cells tile the whole domain
+    assert np.abs(v1 - 1.0).max() <= 2e-6                              # sum w * 1 / sum w
+    lin = 2.0 * v0.astype(np.float64) + 3.0
+    assert (np.abs(v2 - lin) <= REL_TOL * np.abs(lin)).all()
+    fmin, fmax = float(fields[0].min()), float(fields[0].max())
+    assert v0.min() >= fmin - 1e-5 and v0.max() <= fmax + 1e-5        # convex combination of cell values
+    # the frame: same bits from consecutive launches although the tile order changes
+    cam = R.default_camera([0] * 3, [1024.0] * 3, 1024, 1024)
+    fd = scenes.FrameDesc(1024, 1024, cam, 3)                           # multi-field DVR over the three channels
+    fd.xf_domain = [(fmin, fmax), (0.0, 2.0), (2 * fmin + 3, 2 * fmax + 3)]
+    fd.apply(r)
+    frames = []
+    for _ in range(3):
+        r.render()
+        frames.append(r.read_rgba8().copy())
+    assert (frames[0] == frames[1]).all() and (frames[1] == frames[2]).all()
+    st = r.render_stats()
+    assert st["samples"] > 10 ** 6 and st["segments"] > 10 ** 5
+    # transparent transfer function => every pixel is the background, whatever the data
+    alpha, rgb = fd.xf[0]
+    for c in range(3):
+        r.updateXF(c, np.zeros_like(alpha), rgb, fd.xf_domain[c], 1.0)
+    r.render()
+    acc = r.read_accum()
+    r2 = R.Renderer(bricks, [fields[1]])                                # constant field, same camera: no structure at all
+    fd1 = scenes.FrameDesc(1024, 1024, cam, 1)
+    fd1.xf_domain = [(0.0, 2.0)]
+    fd1.apply(r2)
+    r2.updateXF(0, np.zeros_like(alpha), rgb, (0.0, 2.0), 1.0)
+    r2.render()
+    assert np.abs(acc - r2.read_accum()).max() == 0.0
+
+
 def test_render_errors(R, orc):
     g = load_golden("ex4")
     b = R.ExaBricks.from_bytes(g["bricks"].tobytes())
