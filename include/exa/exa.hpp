@@ -207,11 +207,10 @@ struct OptixRenderer {
   { detail::check(exa_renderer_resize_framebuffer(handle, fbPointer, size.x, size.y)); fbSize = size; }
   void updateIsoValues(const float *isoValues, const int *channels, const int *enabled)
   { detail::check(exa_renderer_update_iso_values(handle, isoValues, channels, enabled)); }
-  void updateContourPlanes(const vec3f *, const float *, const int *, const int *enabled)
-  {
-    for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++)
-      if (enabled && enabled[i]) throw std::runtime_error("contour planes are outside the exabrick-b200 hot path (SURVEY 8f rank 3)");
-  }
+  void updateContourPlanes(const vec3f *normals, const float *offsets, const int *channels, const int *enabled)
+  { detail::check(exa_renderer_update_contour_planes(handle, &normals[0].x, offsets, channels, enabled)); }
+  // the viewer pokes frameState.ao directly (viewer.cpp:953-954); here it is a call
+  void setAO(bool enable, float length) { detail::check(exa_renderer_set_ao(handle, enable, length)); }
   void updateCamera(const vec3f &pos, const vec3f &dir00, const vec3f &dirDu, const vec3f &dirDv)
   { detail::check(exa_renderer_update_camera(handle, &pos.x, &dir00.x, &dirDu.x, &dirDv.x)); }
   void updateXF(int chan, const float *opacities, const std::vector<vec3f> &colorMap, const interval<float> &xfDomain,

@@ -238,6 +238,14 @@ int exa_renderer_set_space_skipping(exa_renderer_t *r, int enable);             
 int exa_renderer_set_gradient_shading_dvr(exa_renderer_t *r, int enable);            /* :434-437 */
 int exa_renderer_set_gradient_shading_iso(exa_renderer_t *r, int enable);            /* :439-442 */
 int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], const float hi[3]);
+/* updateContourPlanes(normals, offsets, channels, enabled) (OptixRenderer.cpp:504-531): arrays of
+ * EXA_MAX_CONTOUR_PLANES; normals are normalised; offset is in the unit cube that is scaled to
+ * the world-space bounds (exabrick.cu:1346-1364).  Forces space skipping off while a plane is on. */
+int exa_renderer_update_contour_planes(exa_renderer_t *r, const float *normals3, const float *offsets,
+                                       const int *channels, const int *enabled);
+/* frameState.ao.{enabled,length} (programs/FrameState.h:60-63, poked by viewer.cpp:953-954): two
+ * cosine-distributed occlusion rays of that length per shaded surface hit (exabrick.cu:1611-1646) */
+int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length);
 /* early-ray-termination threshold (reference constant 0.98, exabrick.cu:49); >1 disables */
 int exa_renderer_set_ert_threshold(exa_renderer_t *r, float threshold);
 /* tracer (OptixRenderer.h:155-165, .cpp:444-487) */

@@ -25,6 +25,7 @@ static inline V3 operator*(V3 a, float s) { return v3(a.x * s, a.y * s, a.z * s)
 static inline V3 operator*(float s, V3 a) { return v3(a.x * s, a.y * s, a.z * s); }
 static inline V3 operator-(V3 a) { return v3(-a.x, -a.y, -a.z); }
 static inline float dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+static inline V3 cross(V3 a, V3 b) { return v3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x); }
 static inline float length(V3 a) { return sqrtf(dot(a, a)); }
 // owl: normalize(v) = v * rsqrt(dot(v,v))  (owl/common/math/vec/functors.h)
 static inline V3 normalize(V3 a) { return a * (1.f / sqrtf(dot(a, a))); }
@@ -745,7 +746,7 @@ static inline V3 xfmPoint(const OrcFrame &f, V3 v)
 { V3 r = xfmVector(f, v); return v3(r.x + f.xf_p[0], r.y + f.xf_p[1], r.z + f.xf_p[2]); }
 
 struct Surface { int primID = -1; float t_hit = 0.f; V3 Ng = {0, 0, 0}; float ambient = 0.f; V3 base = {0, 0, 0}; };
-enum { PRIMID_STREAMLINE = -25, PRIMID_ISOSURFACE = -23 };
+enum { PRIMID_STREAMLINE = -25, PRIMID_PLANE = -24, PRIMID_ISOSURFACE = -23 };
 
 // traceIsoRay, exabrick.cu:1408-1460
 static Surface traceIsoRay(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &isoActive, Ray ray, OrcStats *st)
@@ -791,11 +792,12 @@ static bool roundedCone(V3 pa, V3 pb, float ra, float rb, const Ray &ray, float 
   return false;
 }
 
-// Streamline closest hit (exabrick.cu:503-530 intersect, 532-570 bounds/visibility), brute force
+// Streamline closest hit (exabrick.cu:503-530 intersect, 532-570 bounds/visibility), brute force.
+// prd comes in with primID -1 / t_hit 2e10 (:1505-1507); hits are accepted inside (ray.tmin, ray.tmax).
 static void traceStreamlines(const OrcFrame &f, const Ray &ray, Surface &prd)
 {
   if (!f.traces) return;
-  float tmax = prd.t_hit;
+  float tmax = ray.tmax;
   for (int i = 0; i < f.numTraces; i++)
     for (int k = 0; k + 1 < f.numTimesteps; k++) {
       if (k >= f.currentTimestep - 1) break;
@@ -806,6 +808,169 @@ static void traceStreamlines(const OrcFrame &f, const Ray &ray, Surface &prd)
         tmax = t; prd.primID = PRIMID_STREAMLINE; prd.t_hit = t; prd.Ng = normalize(n); prd.base = v3(.8f, .8f, .8f); prd.ambient = 0.f;
       }
     }
+}
+
+// intersectLinePlane, exabrick.cu:1267-1284
+static float intersectLinePlane(V3 p1, V3 p2, V3 normal, float offset)
+{
+  const float sdn = dot(normal, normalize(p2 - p1));
+  if (sdn == 0.f) return -1.f;
+  const float t = (offset - dot(normal, p1)) / sdn;
+  if (t < 0.f || t > length(p2 - p1)) return -1.f;
+  return t;
+}
+
+// intersectBoxPlane, exabrick.cu:1287-1314: the 12 edges of the box as 4 key corners x 3 axes
+static void intersectBoxPlane(const V3 corners[2], V3 normal, float offset, V3 *pts, int &cnt)
+{
+  static const int key[4][3] = {{0, 0, 0}, {1, 0, 1}, {1, 1, 0}, {0, 1, 1}};
+  cnt = 0;
+  for (int i = 0; i < 4 && cnt < 6; ++i)
+    for (int j = 0; j < 3 && cnt < 6; ++j) {
+      const V3 p1 = v3(j == 0 ? corners[1 - key[i][0]].x : corners[key[i][0]].x,
+                       j == 1 ? corners[1 - key[i][1]].y : corners[key[i][1]].y,
+                       j == 2 ? corners[1 - key[i][2]].z : corners[key[i][2]].z);
+      const V3 p2 = v3(corners[key[i][0]].x, corners[key[i][1]].y, corners[key[i][2]].z);
+      const float t = intersectLinePlane(p1, p2, normal, offset);
+      if (t >= 0.f) pts[cnt++] = p1 + normalize(p2 - p1) * t;
+    }
+}
+
+// intersectRayTriangle, exabrick.cu:1316-1344
+static float intersectRayTriangle(const Ray &ray, V3 v1, V3 e1, V3 e2)
+{
+  const V3 s1 = cross(ray.d, e2);
+  const float div = dot(s1, e1);
+  if (div == 0.f) return -1.f;
+  const float invDiv = 1.f / div;
+  const V3 d = ray.o - v1;
+  const float b1 = dot(d, s1) * invDiv;
+  if (b1 < 0.f || b1 > 1.f) return -1.f;
+  const V3 s2 = cross(d, e1);
+  const float b2 = dot(ray.d, s2) * invDiv;
+  if (b2 < 0.f || b1 + b2 > 1.f) return -1.f;
+  return dot(e2, s2) * invDiv;
+}
+
+// traceContourRay, exabrick.cu:1346-1406.  The plane is given in the unit cube and scaled to the
+// world-space bounds; the polygon is fanned from pts[0].  Quirks kept: the sample position is NOT
+// taken through voxelSpaceTransform and always reads channel 0 (samplePointWithInfRay(pos, 0),
+// :818-830, :1396), the XF is the plane's channel.  The reference leaves `value` uninitialised
+// when the sample is invalid; here it is 0 (decision recorded in DESIGN.md).
+static Surface traceContourRay(const OrcScene &s, const OrcFrame &f, const Ray &ray, V3 normal, float offset, int channel, OrcStats *st)
+{
+  Surface prd; prd.primID = -1; prd.t_hit = ray.tmax;
+  V3 pts[6]; int cnt;
+  const V3 unit[2] = {v3(0, 0, 0), v3(1, 1, 1)};
+  intersectBoxPlane(unit, normal, offset, pts, cnt);
+  for (int i = 0; i < cnt; ++i) {
+    pts[i] = v3(pts[i].x * (f.worldHi[0] - f.worldLo[0]), pts[i].y * (f.worldHi[1] - f.worldLo[1]), pts[i].z * (f.worldHi[2] - f.worldLo[2]));
+    pts[i] = pts[i] + v3(f.worldLo[0], f.worldLo[1], f.worldLo[2]);
+  }
+  float t = -1.f;
+  for (int i = 0; i < cnt - 1; ++i) {                      // "cyclical selection-sort" :1367-1383
+    int minIdx = i;
+    for (int j = i + 1; j < cnt; ++j) {
+      const V3 v = cross(pts[j] - pts[0], pts[minIdx] - pts[0]);
+      if (dot(v, normal) < 0.f) minIdx = j;
+    }
+    std::swap(pts[i], pts[minIdx]);
+  }
+  for (int i = 2; i < cnt; ++i) {
+    const V3 v1 = pts[0], e1 = pts[i - 1] - v1, e2 = pts[i] - v1;
+    const float tt = intersectRayTriangle(ray, v1, e1, e2);
+    if (tt >= 0.f && (tt < t || t < 0.f)) t = tt;
+  }
+  if (t < 0.f) return prd;
+  const V3 pos = ray.o + ray.d * t;
+  float value = 0.f;
+  const int leaf = locateRegion(s, pos);                   // closest region of a ray of length 2e-10 from pos
+  if (leaf >= 0) { float v2; if (samplePoint(s, v2, leaf, pos, 0, st)) value = v2; }
+  const V4 smp = lookupXF(f, value, channel);
+  prd.primID = PRIMID_PLANE; prd.t_hit = t; prd.Ng = normal; prd.ambient = 0.f; prd.base = v3(smp.x, smp.y, smp.z);
+  return prd;
+}
+
+// make_orthonormal_basis / cosine_sample_hemisphere, exabrick.cu:78-94
+static void makeOrthonormalBasis(V3 &u, V3 &v, V3 w)
+{
+  v = fabsf(w.x) > fabsf(w.y) ? normalize(v3(-w.z, 0, w.x)) : normalize(v3(0, w.z, -w.y));
+  u = cross(v, w);
+}
+static V3 cosineSampleHemisphere(float u1, float u2)
+{
+  const float r = sqrtf(u1);
+  const float theta = (float)(2.f * M_PI * u2);
+  return v3(r * cosf(theta), r * sinf(theta), sqrtf(1.f - u1));
+}
+
+// traceSurfaces, exabrick.cu:1476-1529 (no triangle meshes: SURVEY 8f rank 3, not restated)
+static void traceSurfaces(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &isoActive, bool anyIso,
+                          const Ray &ray, Surface &prd, bool withContourPlanes, OrcStats *st)
+{
+  prd.primID = -1; prd.t_hit = ray.tmax;
+  if (withContourPlanes)
+    for (int i = 0; i < 3; i++)
+      if (f.cpEnabled[i]) {
+        const Surface c = traceContourRay(s, f, ray, v3(f.cpNormal[i][0], f.cpNormal[i][1], f.cpNormal[i][2]), f.cpOffset[i], f.cpChannel[i], st);
+        if (c.primID == PRIMID_PLANE && c.t_hit < prd.t_hit) prd = c;
+      }
+  {
+    Surface sl; sl.primID = -1; sl.t_hit = 2e10f;
+    traceStreamlines(f, ray, sl);
+    if (sl.primID == PRIMID_STREAMLINE && sl.t_hit < prd.t_hit) prd = sl;
+  }
+  if (anyIso) {
+    const Surface iso = traceIsoRay(s, f, isoActive, ray, st);
+    if (iso.primID == PRIMID_ISOSURFACE && iso.t_hit < prd.t_hit) prd = iso;
+  }
+}
+
+// test entry points for the surface geometry (tests/test_surfaces_host.py compares the product's
+// csrc/surfaces.cuh, compiled for the host, with these)
+extern "C" int orc_rounded_cone(const float pa[3], const float pb[3], float ra, float rb, const float ro[3], const float rd[3],
+                                float *t, float n[3])
+{
+  Ray r; r.o = v3(ro[0], ro[1], ro[2]); r.d = v3(rd[0], rd[1], rd[2]); r.tmin = 0.f; r.tmax = 1e30f;
+  V3 nn = v3(0, 0, 0); float tt = 0.f;
+  const bool hit = roundedCone(v3(pa[0], pa[1], pa[2]), v3(pb[0], pb[1], pb[2]), ra, rb, r, tt, nn);
+  *t = tt; n[0] = nn.x; n[1] = nn.y; n[2] = nn.z;
+  return hit ? 1 : 0;
+}
+extern "C" float orc_contour_plane_t(const float ro[3], const float rd[3], const float normal[3], float offset,
+                                     const float wlo[3], const float whi[3], float *pts18, int *cnt)
+{
+  // polygon part of traceContourRay (exabrick.cu:1355-1394), without the sample
+  const V3 nrm = v3(normal[0], normal[1], normal[2]);
+  V3 pts[6]; int c;
+  const V3 unit[2] = {v3(0, 0, 0), v3(1, 1, 1)};
+  intersectBoxPlane(unit, nrm, offset, pts, c);
+  for (int i = 0; i < c; ++i) {
+    pts[i] = v3(pts[i].x * (whi[0] - wlo[0]), pts[i].y * (whi[1] - wlo[1]), pts[i].z * (whi[2] - wlo[2]));
+    pts[i] = pts[i] + v3(wlo[0], wlo[1], wlo[2]);
+  }
+  for (int i = 0; i < c - 1; ++i) {
+    int minIdx = i;
+    for (int j = i + 1; j < c; ++j) if (dot(cross(pts[j] - pts[0], pts[minIdx] - pts[0]), nrm) < 0.f) minIdx = j;
+    std::swap(pts[i], pts[minIdx]);
+  }
+  Ray r; r.o = v3(ro[0], ro[1], ro[2]); r.d = v3(rd[0], rd[1], rd[2]); r.tmin = 0.f; r.tmax = 1e30f;
+  float t = -1.f;
+  for (int i = 2; i < c; ++i) {
+    const float tt = intersectRayTriangle(r, pts[0], pts[i - 1] - pts[0], pts[i] - pts[0]);
+    if (tt >= 0.f && (tt < t || t < 0.f)) t = tt;
+  }
+  if (cnt) *cnt = c;
+  if (pts18) for (int i = 0; i < c; i++) { pts18[3 * i] = pts[i].x; pts18[3 * i + 1] = pts[i].y; pts18[3 * i + 2] = pts[i].z; }
+  return t;
+}
+extern "C" void orc_ao_direction(const float normal[3], float u1, float u2, float out[3])
+{
+  V3 u, v; const V3 w = v3(normal[0], normal[1], normal[2]);
+  makeOrthonormalBasis(u, v, w);
+  const V3 sp = cosineSampleHemisphere(u1, u2);
+  const V3 d = normalize(sp.x * u + sp.y * v + sp.z * w);
+  out[0] = d.x; out[1] = d.y; out[2] = d.z;
 }
 
 // owl::LCG<16>, owl/common/math/random.h:56-96
@@ -827,8 +992,7 @@ struct LCG16 {
 static inline float linear_to_srgb(float x) { return x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.f / 2.4f) - 0.055f; }
 static inline int make_8bit(float f) { return std::min(255, std::max(0, (int)(f * 256.f))); }
 
-// __raygen__renderFrame, exabrick.cu:1576-1720 (meshes, contour planes and AO are not
-// restated: out of north_star scope)
+// __raygen__renderFrame, exabrick.cu:1576-1720 (triangle meshes are not restated: SURVEY §8f rank 3)
 extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0, int x1, int y1,
                           float *accum, uint32_t *rgba8, OrcStats *stats)
 {
@@ -865,17 +1029,28 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
                              f.cam_dir00[1] + sx * f.cam_du[1] + sy * f.cam_dv[1],
                              f.cam_dir00[2] + sx * f.cam_du[2] + sy * f.cam_dv[2]));
         ray.tmin = 1e-6f; ray.tmax = 1e8f;
-        Surface surf; surf.primID = -1; surf.t_hit = ray.tmax;
-        traceStreamlines(f, ray, surf);                    // traceSurfaces :1503-1512
-        if (anyIso) {                                      // :1514-1527
-          Surface iso = traceIsoRay(s, f, isoActive, ray, &st);
-          if (iso.primID == PRIMID_ISOSURFACE && iso.t_hit < surf.t_hit) surf = iso;
-        }
+        Surface surf;
+        traceSurfaces(s, f, isoActive, anyIso, ray, surf, true, &st);        // :1598 ST_ALL_SURFACES
         V3 bg = v3(0, 0, 0);
-        if (surf.primID == PRIMID_ISOSURFACE || surf.primID == PRIMID_STREAMLINE) {   // :1604-1652, AO off
-          const bool shade = surf.primID == PRIMID_STREAMLINE || (surf.primID == PRIMID_ISOSURFACE && f.gradientShadingISO);
+        if (surf.primID != -1) {                           // :1604-1652
+          const bool shade = surf.primID == PRIMID_STREAMLINE || surf.primID == PRIMID_PLANE ||
+                             (surf.primID == PRIMID_ISOSURFACE && f.gradientShadingISO);
           if (shade && length(surf.Ng) > 0.f) {
-            const float k = fabsf(dot(ray.d, surf.Ng)) * (1.f - 0.f);
+            const int aoSamples = f.aoEnabled ? 2 : 0;
+            const V3 isect = ray.o + ray.d * surf.t_hit;
+            V3 u, v; const V3 w = surf.Ng;
+            makeOrthonormalBasis(u, v, w);
+            int hitCnt = 0;
+            for (int i = 0; i < aoSamples; ++i) {
+              const float u1 = rnd(), u2 = rnd();            // oracle fixes the first argument first
+              const V3 sp = cosineSampleHemisphere(u1, u2);
+              Ray ao; ao.o = isect; ao.d = normalize(sp.x * u + sp.y * v + sp.z * w); ao.tmin = 1e-4f; ao.tmax = f.aoLength;
+              Surface hit;
+              traceSurfaces(s, f, isoActive, anyIso, ao, hit, false, &st);   // ST_ALL & ~ST_CONTOUR_PLANES
+              if (hit.primID != -1) hitCnt++;
+            }
+            const float shadow = f.aoEnabled ? (float)hitCnt / aoSamples : 0.f;
+            const float k = fabsf(dot(ray.d, surf.Ng)) * (1.f - shadow);
             bg = v3(surf.ambient + surf.base.x * k, surf.ambient + surf.base.y * k, surf.ambient + surf.base.z * k);
           } else bg = surf.base;
         }

@@ -8,7 +8,8 @@
  *   - tent-basis sampling programs/exabrick.cu:581-594, 620-777, 781-816, 883-942
  *   - DVR / iso frame     programs/exabrick.cu:135-150, 184-238, 250-331, 373-402,
  *                         988-1256, 1408-1460, 1576-1720; programs/Camera.h:27-44
- *   - streamlines (RK4)   programs/exabrick.cu:945-963, 1531-1574
+ *   - streamlines (RK4)   programs/exabrick.cu:945-963, 1531-1574; rounded cones :441-573
+ *   - contour planes, AO  programs/exabrick.cu:78-94, 1267-1406, 1476-1529, 1604-1652
  *
  * Parity status: builder + ABR are PINNED against the reference's own code compiled in
  * place (oracle/_ref, see oracle/Makefile and tests/golden/make_golden.py).  The
@@ -61,6 +62,11 @@ typedef struct OrcFrame {
   /* streamlines drawn as rounded cones (exabrick.cu:441-573) */
   int32_t numTraces, numTimesteps, currentTimestep;
   const float *traces;             /* numTraces*numTimesteps*3 or NULL */
+  /* contour planes (exabrick.cu:1267-1406), ambient occlusion (:1611-1651) and the world-space
+     bounds the plane polygon is scaled to (LaunchParams.h:37) */
+  int32_t cpEnabled[3]; float cpNormal[3][3]; float cpOffset[3]; int32_t cpChannel[3];
+  int32_t aoEnabled; float aoLength;
+  float   worldLo[3], worldHi[3];
 } OrcFrame;
 
 typedef struct OrcStats {          /* counters for the algorithmic-bytes model */
@@ -103,6 +109,13 @@ int orc_render(const OrcScene *, const OrcFrame *, int x0, int y0, int x1, int y
 int orc_trace_streamlines(const OrcScene *, float *traces, int numTraces, int numTimesteps,
                           const int32_t channels[3], float steplen,
                           const float worldLo[3], const float worldHi[3]);
+
+/* surface geometry, exposed for tests (exabrick.cu:441-501, 1267-1394, 78-94) */
+int   orc_rounded_cone(const float pa[3], const float pb[3], float ra, float rb, const float ro[3],
+                       const float rd[3], float *t, float n[3]);
+float orc_contour_plane_t(const float ro[3], const float rd[3], const float normal[3], float offset,
+                          const float wlo[3], const float whi[3], float *pts18, int *cnt);
+void  orc_ao_direction(const float normal[3], float u1, float u2, float out[3]);
 
 #ifdef __cplusplus
 }

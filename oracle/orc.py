@@ -42,6 +42,9 @@ class OrcFrame(C.Structure):
         ("ertThreshold", C.c_float), ("texFilter8bit", C.c_int32), ("partial", C.c_int32),
         ("numTraces", C.c_int32), ("numTimesteps", C.c_int32), ("currentTimestep", C.c_int32),
         ("traces", C.POINTER(C.c_float)),
+        ("cpEnabled", C.c_int32 * 3), ("cpNormal", (C.c_float * 3) * 3), ("cpOffset", C.c_float * 3), ("cpChannel", C.c_int32 * 3),
+        ("aoEnabled", C.c_int32), ("aoLength", C.c_float),
+        ("worldLo", C.c_float * 3), ("worldHi", C.c_float * 3),
     ]
 
 

@@ -23,7 +23,7 @@ if os.environ.get("EXA_VARIANT"):
     LIB = os.path.join(HERE, "libexabrick_b200.%s.so" % os.environ["EXA_VARIANT"])
     OBJ = os.path.join(HERE, "build", os.environ["EXA_VARIANT"])
 SOURCES = ["host.cpp", "builder.cpp", "abr.cu", "render.cu", "capi.cu"]
-HEADERS = ["exa_internal.h", "render.cuh", "capi_render.inl", os.path.join("..", "..", "include", "exabrick_b200.h")]
+HEADERS = ["exa_internal.h", "render.cuh", "surfaces.cuh", "capi_render.inl", os.path.join("..", "..", "include", "exabrick_b200.h")]
 
 
 def _stale(out, deps):

@@ -96,6 +96,8 @@ _SIG = {
     "exa_renderer_set_gradient_shading_dvr": (i32, [vp, i32]),
     "exa_renderer_set_gradient_shading_iso": (i32, [vp, i32]),
     "exa_renderer_set_clip_box": (i32, [vp, i32, vp, vp]),
+    "exa_renderer_update_contour_planes": (i32, [vp, vp, vp, vp, vp]),
+    "exa_renderer_set_ao": (i32, [vp, i32, f32]),
     "exa_renderer_set_ert_threshold": (i32, [vp, f32]),
     "exa_renderer_set_tracer_enabled": (i32, [vp, i32]),
     "exa_renderer_set_tracer_params": (i32, [vp, i32, i32, f32, vp, vp, vp]),

@@ -49,6 +49,7 @@ struct exa_renderer {
   float steplen = 1e-6f; int tracerChannels[3] = {0, 1, 2};
   float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
   float *d_traces = nullptr; size_t tracesCap = 0;
+  float *d_traceBounds = nullptr; int traceBoundsCap = 0; bool traceBoundsDirty = true;   // one box per trace (k_traceBounds)
   unsigned long long *d_stats = nullptr;
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
   LongRay *d_longQueue = nullptr; int *d_longCount = nullptr; int sampleBudget = 0;       // long-ray hand-over to k_renderLong; 0 = single pass (default: measured faster on C2)
@@ -95,7 +96,22 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.volActive = r->d_volActive; P.isoActive = r->d_isoActive;
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
-  P.traces = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
+  // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
+  // copy of the time step stops at numTimesteps (OptixRenderer.cpp:481-484)
+  P.traces = nullptr; P.traceBounds = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
+  if (r->d_traces && r->numTraces > 0 && std::min(r->timestep, r->numTimesteps) >= 2) {
+    P.traces = r->d_traces; P.traceBounds = r->d_traceBounds; P.numTraces = r->numTraces; P.numTimesteps = r->numTimesteps;
+    P.currentTimestep = std::min(r->timestep, r->numTimesteps);
+  }
+  bool anyContour = false;
+  for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) {
+    P.cpEnabled[i] = r->fs.contourPlane[i].enabled; memcpy(P.cpNormal[i], r->fs.contourPlane[i].normal, 12);
+    P.cpOffset[i] = r->fs.contourPlane[i].offset; P.cpChannel[i] = r->fs.contourPlane[i].channel;
+    anyContour |= P.cpEnabled[i] != 0;
+  }
+  P.aoEnabled = r->fs.ao.enabled; P.aoLength = r->fs.ao.length;
+  memcpy(P.worldLo, r->worldLo, 12); memcpy(P.worldHi, r->worldHi, 12);
+  P.anySurf = (P.anyIso || anyContour || P.traces) ? 1 : 0;
   P.stats = nullptr;
   P.longQueue = r->d_longQueue; P.longCount = r->d_longCount; P.sampleBudget = r->sampleBudget;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
@@ -301,7 +317,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
-  cudaFree(r->d_traces); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
+  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
   delete r;
 }
 
@@ -485,6 +501,26 @@ int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], 
   r->fs.clipBox.enabled = enable ? 1 : 0;
   if (lo) memcpy(r->fs.clipBox.lower, lo, 12);
   if (hi) memcpy(r->fs.clipBox.upper, hi, 12);
+  return EXA_OK;
+}
+int exa_renderer_update_contour_planes(exa_renderer_t *r, const float *normals3, const float *offsets, const int *channels, const int *enabled)
+{
+  if (!r || !normals3 || !offsets || !channels || !enabled) { setError("null argument"); return EXA_ERR_INVALID; }
+  for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) {
+    if (enabled[i] && (channels[i] < 0 || channels[i] >= r->numFields)) { setError("updateContourPlanes: channel out of range"); return EXA_ERR_INVALID; }
+    // normalize(normals[i]) (OptixRenderer.cpp:511): v * (1 / sqrt(dot(v,v)))
+    const float *n = normals3 + 3 * i;
+    const float s = 1.f / sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    for (int d = 0; d < 3; d++) r->fs.contourPlane[i].normal[d] = n[d] * s;
+    r->fs.contourPlane[i].offset = offsets[i]; r->fs.contourPlane[i].channel = channels[i]; r->fs.contourPlane[i].enabled = enabled[i] ? 1 : 0;
+  }
+  r->masksDirty = true;                                     // space skipping is off while a plane is enabled (:518-530)
+  return EXA_OK;
+}
+int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  r->fs.ao.enabled = enable ? 1 : 0; r->fs.ao.length = length;      // viewer.cpp:953-954 pokes frameState.ao
   return EXA_OK;
 }
 uint64_t exa_renderer_launch_count(const exa_renderer_t *r) { return r ? r->launches : 0; }

@@ -23,6 +23,18 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
   RenderParams P; fillParams(r, P);
   int rc = refreshMasks(r, P); if (rc) return rc;
   P.partialOut = partialOut;
+  if (P.traces) {                                            // boxes around the visible cones of every trace
+    if (r->numTraces > r->traceBoundsCap) {
+      CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_traceBounds); r->d_traceBounds = nullptr;
+      CKR(cudaMalloc(&r->d_traceBounds, (size_t)r->numTraces * 24)); r->traceBoundsCap = r->numTraces; r->traceBoundsDirty = true;
+    }
+    if (r->traceBoundsDirty) {
+      const int k = launchTraceBounds(P.traces, P.numTraces, P.numTimesteps, P.currentTimestep, r->d_traceBounds, r->stream);
+      if (k < 0) { setError(std::string("trace bounds kernel failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+      r->launches += k; r->traceBoundsDirty = false;
+    }
+    P.traceBounds = r->d_traceBounds;
+  }
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)
     if (!r->tileOrderValid)                                  // (re)start: both buffers' counters to zero, once
@@ -203,7 +215,7 @@ static int uploadSeeds(exa_renderer *r, const std::vector<float> &host)
   if (n > r->tracesCap) { CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_traces); r->d_traces = nullptr; CKR(cudaMalloc(&r->d_traces, std::max(n, (size_t)3) * 4)); r->tracesCap = n; }
   if (n) CKR(cudaMemcpyAsync(r->d_traces, host.data(), n * 4, cudaMemcpyHostToDevice, r->stream));
   CKR(cudaStreamSynchronize(r->stream));
-  r->timestep = 0;
+  r->timestep = 0; r->traceBoundsDirty = true;
   return EXA_OK;
 }
 
@@ -255,7 +267,7 @@ int exa_renderer_advance_tracer(exa_renderer_t *r, int *rebuilt)
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
   if (rebuilt) *rebuilt = 0;
   if (!r->tracerEnabled) return EXA_OK;                      // advanceTracer (:476-487)
-  r->timestep++;
+  r->timestep++; r->traceBoundsDirty = true;
   if (r->timestep <= r->numTimesteps) {
     if (rebuilt) *rebuilt = 1;
     if (r->timestep < r->numTimesteps) return traceSteps(r, r->timestep, r->timestep);   // device: t < numTimesteps (exabrick.cu:1539)
@@ -270,6 +282,7 @@ int exa_renderer_trace_all(exa_renderer_t *r)
   if (first >= r->numTimesteps) return EXA_OK;
   int rc = traceSteps(r, first, r->numTimesteps - 1);
   if (!rc) r->timestep = r->numTimesteps;
+  r->traceBoundsDirty = true;
   return rc;
 }
 

@@ -18,6 +18,7 @@
 //   k_gather        scalar[i] = field[cellID[i]] (exa/OptixRenderer.cpp:103-132).
 //   k_over / k_finish  sort-last compositing helpers.
 #include "render.cuh"
+#include "surfaces.cuh"
 #include <cstdio>
 
 namespace exa {
@@ -490,6 +491,125 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 { const float3 r = xfmVector(m, v); return f3(__fadd_rn(r.x, m[9]), __fadd_rn(r.y, m[10]), __fadd_rn(r.z, m[11])); }
 
 // -----------------------------------------------------------------------------------------
+// surface pass (traceSurfaces, exabrick.cu:1476-1529): contour planes, streamline cones and
+// implicit iso-surfaces; primary rays and the two ambient-occlusion rays of a hit share it.
+// Triangle meshes are not built.
+// -----------------------------------------------------------------------------------------
+enum { PRIM_NONE = -1, PRIM_ISOSURFACE = -23, PRIM_PLANE = -24, PRIM_STREAMLINE = -25 };
+struct SurfHit { int prim; float t; float3 Ng, base; float ambient; };
+static constexpr int SURF_THREADS = 128;                      // = FRAME_THREADS (stride of the per-thread smem columns)
+
+template <bool GRAD, bool STATS, bool DUAL>
+__device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
+                                                  float &value, float3 &g, unsigned &visits, unsigned &corners);
+
+// traceIsoRay (exabrick.cu:1408-1460): march the iso-active regions front to back with lattice
+// offset 0 until two consecutive valid samples bracket an enabled iso value.
+// (not __noinline__: ptxas 12.9 segfaults on an out-of-line copy of this function)
+template <bool STATS, bool DUAL>
+__device__ void traceIsoRay(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
+                                         float3 o, float3 d, float tmin, float tmax, SurfHit &out, RayStats &rs)
+{
+  out.prim = PRIM_NONE; out.t = tmax; out.Ng = f3(0, 0, 0); out.base = f3(0, 0, 0); out.ambient = 0.f;
+  const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
+  const float dtScale = len3nc(vd); vd = normalize3nc(vd);
+  float already = dtScale * tmin; float rtmax = tmax;
+  for (int c = 0; c < P.numChannels; c++) { isoV[c * SURF_THREADS] = -1e36f; isoT[c * SURF_THREADS] = 0.f; }
+  rtmax = rtmax * dtScale;
+  Trav T; travInit(T, stack, vo, vd, already, rtmax, P.scene);
+  for (;;) {
+    Segment seg;
+    if (!travNext(T, P.scene, P.isoActive, already, rtmax, seg)) break;
+    float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
+    isoSegment<STATS, DUAL>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
+    if (th >= 0.f) {
+      out.prim = PRIM_ISOSURFACE; out.t = th / dtScale; out.Ng = normalize3(hg); out.ambient = 0.f; out.base = f3(ipc.x, ipc.y, ipc.z);
+      return;
+    }
+    already = seg.t1 * 1.0000001f;
+    rtmax = rtmax * dtScale;                          // (sic) exabrick.cu:1434
+  }
+}
+
+// traceContourRay for every enabled plane (exabrick.cu:1346-1406, 1491-1501).  Quirks kept: the
+// sample position is world-space (no voxelSpaceTransform) and reads channel 0
+// (samplePointWithInfRay(pos, 0), :818-830, :1396); the XF is the plane's channel.  An invalid
+// sample classifies the value 0 (the reference reads an uninitialised float there).
+template <bool STATS, bool DUAL>
+__device__ void traceContourPlanes(const RenderParams &P, const float4 *xfTables, float3 o, float3 d, SurfHit &prd, RayStats &rs)
+{
+  for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) {
+    if (!P.cpEnabled[i]) continue;
+    const float3 n = f3(P.cpNormal[i][0], P.cpNormal[i][1], P.cpNormal[i][2]);
+    const float t = surf::contourPlaneT(o, d, n, P.cpOffset[i], P.worldLo, P.worldHi);
+    if (t < 0.f) continue;
+    const float3 pos = rayAt(o, d, t);
+    float value = 0.f, v2 = 0.f; float3 g; unsigned vis = 0, cor = 0;
+    if (samplePointGlobal<false, STATS, DUAL>(P.scene, pos.x, pos.y, pos.z, 0, v2, g, vis, cor)) value = v2;
+    if (STATS && vis) { rs.samples++; rs.visits += vis; rs.corners += cor; }
+    const int ch = P.cpChannel[i];
+    const float4 smp = lookupXF(xfTables + ch * 128, P.xfDomain[ch][0], P.xfDomain[ch][1], P.xfOpacityScale, value);
+    if (t < prd.t) { prd.prim = PRIM_PLANE; prd.t = t; prd.Ng = n; prd.ambient = 0.f; prd.base = f3(smp.x, smp.y, smp.z); }
+  }
+}
+
+// Streamline closest hit (bounds :532-570, intersect :503-530): segment k of a trace is visible
+// while k < currentTimestep-1 and both ends are alive; radius 2 at both ends.  The reference
+// rebuilds an OptiX BVH over all segments after every tracer step; here k_traceBounds keeps one
+// box per trace (1000 boxes for the default tracer) and a ray tests the segments of the traces
+// whose box it hits.
+__device__ __noinline__ void traceCones(const RenderParams &P, float3 o, float3 d, float tmin, float tmax, SurfHit &sl)
+{
+  sl.prim = PRIM_NONE; sl.t = 2e10f; sl.Ng = f3(0, 0, 0); sl.base = f3(.8f, .8f, .8f); sl.ambient = 0.f;
+  if (!P.traces || !P.traceBounds) return;
+  const int nSeg = min(P.numTimesteps - 1, P.currentTimestep - 1);
+  if (nSeg <= 0) return;
+  float best = tmax;
+  const float3 invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+  for (int i = 0; i < P.numTraces; i++) {
+    const float *b = P.traceBounds + 6 * (size_t)i;
+    const float lx = __ldg(b), ly = __ldg(b + 1), lz = __ldg(b + 2), hx = __ldg(b + 3), hy = __ldg(b + 4), hz = __ldg(b + 5);
+    if (!(lx <= hx)) continue;                                 // no visible cone on this trace
+    // slab test against the box grown by a little (culling only; NaNs from 0*inf drop out of fmin/fmax)
+    const float px = 1e-3f * (hx - lx + 1.f), py = 1e-3f * (hy - ly + 1.f), pz = 1e-3f * (hz - lz + 1.f);
+    const float ax = (lx - px - o.x) * invd.x, bx = (hx + px - o.x) * invd.x;
+    const float ay = (ly - py - o.y) * invd.y, by = (hy + py - o.y) * invd.y;
+    const float az = (lz - pz - o.z) * invd.z, bz = (hz + pz - o.z) * invd.z;
+    const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
+    const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best));
+    if (t0 > t1) continue;
+    const float *tr = P.traces + 3 * (size_t)i * P.numTimesteps;
+    float3 pa = f3(__ldg(tr), __ldg(tr + 1), __ldg(tr + 2));
+    for (int k = 0; k < nSeg; k++) {
+      const float3 pb = f3(__ldg(tr + 3 * (k + 1)), __ldg(tr + 3 * (k + 1) + 1), __ldg(tr + 3 * (k + 1) + 2));
+      if (pa.x < 2e10f && pb.x < 2e10f) {
+        float t; float3 n;
+        if (surf::roundedCone(pa, pb, 2.f, 2.f, o, d, t, n) && t > tmin && t < best) {
+          best = t; sl.prim = PRIM_STREAMLINE; sl.t = t; sl.Ng = normalize3(n);
+        }
+      }
+      pa = pb;
+    }
+  }
+}
+
+template <bool STATS, bool DUAL>
+__device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
+                                              float3 o, float3 d, float tmin, float tmax, bool withContourPlanes, SurfHit &prd, RayStats &rs)
+{
+  prd.prim = PRIM_NONE; prd.t = tmax; prd.Ng = f3(0, 0, 0); prd.base = f3(0, 0, 0); prd.ambient = 0.f;
+  if (withContourPlanes) traceContourPlanes<STATS, DUAL>(P, xfTables, o, d, prd, rs);
+  if (P.traces) {
+    SurfHit sl; traceCones(P, o, d, tmin, tmax, sl);
+    if (sl.prim == PRIM_STREAMLINE && sl.t < prd.t) prd = sl;
+  }
+  if (P.anyIso) {
+    SurfHit iso; traceIsoRay<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, iso, rs);
+    if (iso.prim == PRIM_ISOSURFACE && iso.t < prd.t) prd = iso;
+  }
+}
+
+// -----------------------------------------------------------------------------------------
 // __raygen__renderFrame (exabrick.cu:1576-1720): one thread per pixel, 8x4 pixel tile per warp
 // -----------------------------------------------------------------------------------------
 // final colour of a pixel (exabrick.cu:1701-1719): background blend (sic: premultiplied colour
@@ -518,7 +638,8 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
 static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
-// ISO: the implicit iso-surface pass is compiled in only when an iso-surface is enabled; the plain
+// SURF: the surface pass (iso-surfaces, contour planes, streamline cones, AO) is compiled in only
+// when one of them is enabled (RenderParams::anySurf); the plain
 // DVR instantiation is less than half the code, which matters because every CTA runs through
 // the kernel once, front to back (instruction fetch, not data, is what a lone CTA waits for).
 // Image-tile mode: tiles are dealt in blocks of numRanks consecutive tiles and the deal rotates by
@@ -531,7 +652,7 @@ __host__ __device__ inline int numOwnedTiles(int numTiles, int rank, int numRank
   return full + ((rank + full) % numRanks < rem ? 1 : 0);
 }
 
-template <bool GRAD, bool STATS, bool DUAL, bool ISO>
+template <bool GRAD, bool STATS, bool DUAL, bool SURF>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
@@ -600,34 +721,30 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
                                __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
                                __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
     float tmin = 1e-6f, tmax = 1e8f;
-    // ---- surfaces: implicit iso-surfaces (traceSurfaces :1514-1527, traceIsoRay :1408-1460)
-    int surfPrim = -1; float surfT = tmax; float3 surfNg = f3(0, 0, 0), surfBase = f3(0, 0, 0); float surfAmbient = 0.f;
-    if (ISO && P.anyIso) {
-      const float3 vo = xfmPoint(P.xfm, o); float3 vd = xfmVector(P.xfm, d);
-      const float dtScale = len3nc(vd); vd = normalize3nc(vd);
-      float already = dtScale * tmin; float rtmax = tmax;
-      for (int c = 0; c < P.numChannels; c++) { isoV[c * FRAME_THREADS] = -1e36f; isoT[c * FRAME_THREADS] = 0.f; }
-      rtmax = rtmax * dtScale;
-      Trav T; travInit(T, stack, vo, vd, already, rtmax, P.scene);
-      for (;;) {
-        Segment seg;
-        if (!travNext(T, P.scene, P.isoActive, already, rtmax, seg)) break;
-        float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
-        isoSegment<STATS, DUAL>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
-        if (th >= 0.f) {
-          surfPrim = -23; surfT = th / dtScale; surfNg = normalize3(hg); surfAmbient = 0.f; surfBase = f3(ipc.x, ipc.y, ipc.z);
-          break;
-        }
-        already = seg.t1 * 1.0000001f;
-        rtmax = rtmax * dtScale;                          // (sic) exabrick.cu:1434
+    // ---- surfaces (traceSurfaces :1476-1529) and their shading with ambient occlusion (:1604-1652)
+    float surfT = tmax;
+    if (SURF && P.anySurf) {
+      SurfHit sh;
+      traceSurfaces<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, true, sh, rs);
+      surfT = sh.t;
+      if (sh.prim != PRIM_NONE) {
+        const bool shade = sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
+        if (shade && len3(sh.Ng) > 0.f) {
+          const int aoSamples = P.aoEnabled ? 2 : 0;
+          const float3 isect = rayAt(o, d, sh.t);
+          int hitCnt = 0;
+          for (int i = 0; i < aoSamples; i++) {
+            const float u1 = rnd.next(), u2 = rnd.next();
+            const float3 adir = surf::aoDirection(sh.Ng, u1, u2);
+            SurfHit ah;                                       // ST_ALL_SURFACES & ~ST_CONTOUR_PLANES (:1638-1640)
+            traceSurfaces<STATS, DUAL>(P, xfTables, stack, isoT, isoV, isect, adir, 1e-4f, P.aoLength, false, ah, rs);
+            if (ah.prim != PRIM_NONE) hitCnt++;
+          }
+          const float shadow = P.aoEnabled ? (float)hitCnt / (float)aoSamples : 0.f;
+          const float k = fabsf(dot3(d, sh.Ng)) * (1.f - shadow);
+          bg = f3(sh.ambient + sh.base.x * k, sh.ambient + sh.base.y * k, sh.ambient + sh.base.z * k);
+        } else bg = sh.base;
       }
-    }
-    if (surfPrim == -23) {                                // :1604-1652 with AO disabled
-      const bool shade = P.gradISO != 0;
-      if (shade && len3(surfNg) > 0.f) {
-        const float k = fabsf(dot3(d, surfNg));
-        bg = f3(surfAmbient + surfBase.x * k, surfAmbient + surfBase.y * k, surfAmbient + surfBase.z * k);
-      } else bg = surfBase;
     }
     // ---- DVR set-up (:1654-1674)
     offs = rnd.next();
@@ -877,7 +994,7 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   { static size_t capF = 0, capL = 0;                                                                       \
     if (smemBytes > capF) { cudaFuncSetAttribute(k_renderFrame<G, S_, D_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
                             cudaFuncSetAttribute(k_renderFrame<G, S_, D_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capF = smemBytes; } \
-    if (P.anyIso) k_renderFrame<G, S_, D_, true><<<grid, block, smemBytes, s>>>(P);                       \
+    if (P.anySurf) k_renderFrame<G, S_, D_, true><<<grid, block, smemBytes, s>>>(P);                       \
     else k_renderFrame<G, S_, D_, false><<<grid, block, smemBytes, s>>>(P);                               \
     if (twoPass) { if (smemLong > capL) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); capL = smemLong; } \
                    k_renderLong<G, S_, D_><<<gridLong, block, smemLong, s>>>(P); } }
@@ -1005,6 +1122,35 @@ int launchTrace(const TraceParams &P, cudaStream_t s)
 {
   if (P.numTraces <= 0) return 0;
   if (P.scene.dual) k_trace<true><<<(P.numTraces + 63) / 64, 64, 0, s>>>(P); else k_trace<false><<<(P.numTraces + 63) / 64, 64, 0, s>>>(P);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// One box per trace around its visible cones (OPTIX_BOUNDS_PROGRAM(Streamline), exabrick.cu:532-570:
+// segment k counts while k < currentTimestep-1 and both end points are alive; radius 2).  One
+// thread per trace; lo > hi marks a trace without a visible cone.  Re-run after every tracer step
+// (the reference rebuilds its streamline BVH there, OptixRenderer.cpp:539-543).
+__global__ void k_traceBounds(const float *__restrict__ traces, int numTraces, int numTimesteps, int currentTimestep, float *__restrict__ bounds)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= numTraces) return;
+  const int nSeg = min(numTimesteps - 1, currentTimestep - 1);
+  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f};
+  const float *tr = traces + 3 * (size_t)i * numTimesteps;
+  for (int k = 0; k < nSeg; k++) {
+    const float *a = tr + 3 * k, *b = a + 3;
+    if (!(a[0] < 2e10f && b[0] < 2e10f)) continue;
+    for (int d = 0; d < 3; d++) {
+      lo[d] = fminf(lo[d], fminf(a[d], b[d]) - 2.f);
+      hi[d] = fmaxf(hi[d], fmaxf(a[d], b[d]) + 2.f);
+    }
+  }
+  for (int d = 0; d < 3; d++) { bounds[6 * (size_t)i + d] = lo[d]; bounds[6 * (size_t)i + 3 + d] = hi[d]; }
+}
+
+int launchTraceBounds(const float *traces, int numTraces, int numTimesteps, int currentTimestep, float *bounds, cudaStream_t s)
+{
+  if (numTraces <= 0) return 0;
+  k_traceBounds<<<(numTraces + 127) / 128, 128, 0, s>>>(traces, numTraces, numTimesteps, currentTimestep, bounds);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -39,7 +39,13 @@ struct RenderParams {
   float4 *accum; uint32_t *rgba8;
   float4 *partialOut;                  // != null: write premultiplied partial, skip bg/accum/pack
   int tileMode, rank, numRanks;        // image-tile partition
-  const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones
+  const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones (null / 0: none visible)
+  const float *traceBounds;            // per trace {lo[3], hi[3]} around its visible cones (k_traceBounds); lo > hi: none
+  // contour planes (FrameState.h:45-52), ambient occlusion (:60-63), world bounds (LaunchParams.h:37)
+  int cpEnabled[EXA_MAX_CONTOUR_PLANES]; float cpNormal[EXA_MAX_CONTOUR_PLANES][3]; float cpOffset[EXA_MAX_CONTOUR_PLANES]; int cpChannel[EXA_MAX_CONTOUR_PLANES];
+  int aoEnabled; float aoLength;
+  float worldLo[3], worldHi[3];
+  int anySurf;                         // an iso-surface, contour plane or visible streamline: run the surface pass
   unsigned long long *stats;           // 4 counters (ExaStats) or null
   LongRay *longQueue; int *longCount;  // long-ray queue (capacity width*height) and {count, head}; null: off
   int sampleBudget;                    // samples a ray may take in k_renderFrame before it is handed over
@@ -69,6 +75,7 @@ struct TraceParams {
 int launchRenderFrame(const RenderParams &P, cudaStream_t s);
 int launchSamplePoints(const SampleParams &P, cudaStream_t s);
 int launchTrace(const TraceParams &P, cudaStream_t s);
+int launchTraceBounds(const float *traces, int numTraces, int numTimesteps, int currentTimestep, float *bounds, cudaStream_t s);
 int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping,
                          const uint8_t *nodeInPartition, uint8_t *volActive, uint8_t *isoActive /* = volActive + numNodes */, cudaStream_t s);
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);

@@ -277,6 +277,18 @@ class Renderer:
     def setClipBox(self, enable, lo=None, hi=None):
         check(lib.exa_renderer_set_clip_box(self.h, int(bool(enable)), _p(_f3(lo)) if lo is not None else None, _p(_f3(hi)) if hi is not None else None))
 
+    def updateContourPlanes(self, normals, offsets, channels, enabled):
+        """OptixRenderer::updateContourPlanes (exa/OptixRenderer.cpp:504-531); arrays of MAX_CONTOUR_PLANES = 3"""
+        n = np.ascontiguousarray(normals, dtype=np.float32).reshape(3, 3)
+        o = np.ascontiguousarray(offsets, dtype=np.float32)
+        c = np.ascontiguousarray(channels, dtype=np.int32)
+        e = np.ascontiguousarray(enabled, dtype=np.int32)
+        check(lib.exa_renderer_update_contour_planes(self.h, _p(n), _p(o), _p(c), _p(e)))
+
+    def setAO(self, enable, length=0.0):
+        """frameState.ao (programs/FrameState.h:60-63; exa/viewer.cpp:953-954)"""
+        check(lib.exa_renderer_set_ao(self.h, int(bool(enable)), float(length)))
+
     def setErtThreshold(self, t):
         check(lib.exa_renderer_set_ert_threshold(self.h, float(t)))
 

@@ -36,6 +36,13 @@ class FrameDesc:
         self.iso = [(0, 0.0, 0), (0, 0.0, 0)]           # (enabled, value, channel)
         self.clip = None
         self.ert = 0.98
+        # surfaces: contour planes (enabled, normal, offset, channel) x 3, AO (enabled, length),
+        # streamline cones (traces[numTraces, numTimesteps, 3], currentTimestep), world bounds
+        self.contour = [(0, (1.0, 0.0, 0.0), 0.5, 0)] * 3
+        self.ao = (0, 0.0)
+        self.traces = None
+        self.current_timestep = 0
+        self.world = ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
 
     def to_orc(self, orc):
         f = orc.OrcFrame()
@@ -65,6 +72,19 @@ class FrameDesc:
         f.texFilter8bit = 0
         f.partial = 0
         f.traces = None
+        if self.traces is not None:
+            tr = np.ascontiguousarray(self.traces, dtype=np.float32)
+            f._keep = tr                                  # keep the buffer alive with the frame
+            f.numTraces, f.numTimesteps, f.currentTimestep = tr.shape[0], tr.shape[1], int(self.current_timestep)
+            f.traces = tr.ctypes.data_as(C.POINTER(C.c_float))
+        for i, (en, nrm, off, ch) in enumerate(self.contour):
+            n = np.asarray(nrm, np.float32)
+            n = n * (np.float32(1) / np.sqrt(np.float32(n[0] * n[0] + n[1] * n[1] + n[2] * n[2])))   # OptixRenderer.cpp:511
+            f.cpEnabled[i], f.cpOffset[i], f.cpChannel[i] = int(en), float(off), int(ch)
+            f.cpNormal[i][:] = [float(x) for x in n]
+        f.aoEnabled, f.aoLength = int(self.ao[0]), float(self.ao[1])
+        f.worldLo[:] = [float(x) for x in self.world[0]]
+        f.worldHi[:] = [float(x) for x in self.world[1]]
         return f
 
     def apply(self, r):
@@ -86,6 +106,9 @@ class FrameDesc:
         else:
             r.setClipBox(False)
         r.setErtThreshold(self.ert)
+        r.updateContourPlanes([c[1] for c in self.contour], [c[2] for c in self.contour], [c[3] for c in self.contour],
+                              [c[0] for c in self.contour])
+        r.setAO(self.ao[0], self.ao[1])
 
 
 def unpack_rgba8(img):
