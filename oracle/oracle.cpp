@@ -1003,11 +1003,13 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
   std::vector<uint8_t> volActive(s.regions.size()), isoActive(s.regions.size());
   bool anyIso = false;
   for (int i = 0; i < 2; i++) anyIso |= f.isoEnabled[i] != 0;
+  bool anyContour = false;
+  for (int i = 0; i < 3; i++) anyContour |= f.cpEnabled[i] != 0;
   for (size_t i = 0; i < s.regions.size(); i++) {
     const OrcRegion &r = s.regions[i];
     bool act = false;
     for (int c = 0; c < f.numPrimaryChannels && !act; c++) act |= activeForVolume(f, r.vlo, r.vhi, c);
-    volActive[i] = f.spaceSkipping ? act : 1;
+    volActive[i] = (f.spaceSkipping && !anyContour) ? act : 1;   // no space skipping while a contour plane is on (OptixRenderer.cpp:518-530)
     bool ia = false;
     for (int k = 0; k < 2; k++) if (f.isoEnabled[k] && f.isoValue[k] >= r.vlo && f.isoValue[k] <= r.vhi) ia = true;
     isoActive[i] = ia;
