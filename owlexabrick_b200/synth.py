@@ -190,3 +190,98 @@ def linear_field(cells, coef=(0.01, 0.02, 0.03), offset=0.1):
     cw = (1 << cells[:, 3]).astype(np.float64)
     c = cells[:, :3].astype(np.float64) + 0.5 * cw[:, None]
     return (offset + c @ np.asarray(coef, np.float64)).astype(np.float32)
+
+
+# molecular-cloud-shaped — clumpy octree-like refinement from a seeded
+# multi-octave noise threshold, 4 levels, 3 channels.  The coarsest cells (level 3, width 8) tile the
+# domain; a cell of level l > 0 whose centre density exceeds CLOUD_THRESHOLD[l] is replaced by its 8
+# children (level l-1), which are tested in turn.  Density = 4 octaves (3, 6, 12, 24 cycles per
+# domain) of 3 plane waves each, directions/phases from splitmix64(CLOUD_SEED).
+CLOUD_DOMAIN = 2048
+CLOUD_SEED = 0xC10D5EED
+CLOUD_THRESHOLD = {3: 0.50, 2: 0.55, 1: 0.60}
+
+
+def _cloud_waves():
+    u = uniform01(4 * 3 * 4, CLOUD_SEED).astype(np.float64).reshape(4, 3, 4)
+    waves = []
+    for o in range(4):
+        f = 3.0 * (1 << o)
+        for k in range(3):
+            z = 2.0 * u[o, k, 0] - 1.0
+            phi = 2.0 * np.pi * u[o, k, 1]
+            r = np.sqrt(max(0.0, 1.0 - z * z))
+            d = np.array([r * np.cos(phi), r * np.sin(phi), z])
+            waves.append((2.0 * np.pi * f * d, 2.0 * np.pi * u[o, k, 2], 0.5 ** o / 3.0))
+    return waves
+
+
+def cloud_density(centres, domain):
+    """density in [0,1] at points given in finest units of a cubic domain of that width"""
+    p = np.asarray(centres, np.float64) / float(domain)
+    s = np.zeros(len(p))
+    norm = 0.0
+    waves = _cloud_waves()
+    for kvec, phase, amp in waves:
+        s += amp * np.sin(p @ kvec + phase)
+    for o in range(4):
+        norm += 0.5 ** o
+    return 0.5 + 0.5 * s / norm
+
+
+def _cloud_refine(scale, emit):
+    """top-down refinement; emit(level, xyz int32[n,3]) receives the final cells of every level,
+    in chunks; returns the per-level counts"""
+    dom = CLOUD_DOMAIN // scale
+    counts = [0, 0, 0, 0]
+    g = dom // 8
+    child = np.array([[i & 1, (i >> 1) & 1, (i >> 2) & 1] for i in range(8)], np.int32)
+    for z0 in range(0, g, 8):                                       # slabs of 8 coarse layers bound the memory
+        zz, yy, xx = np.meshgrid(np.arange(z0, min(g, z0 + 8), dtype=np.int32), np.arange(g, dtype=np.int32),
+                                 np.arange(g, dtype=np.int32), indexing="ij")
+        cur = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1) * 8
+        for l in (3, 2, 1):
+            w = 1 << l
+            refine = cloud_density(cur + 0.5 * w, dom) > CLOUD_THRESHOLD[l]
+            keep = cur[~refine]
+            counts[l] += len(keep)
+            emit(l, keep)
+            par = cur[refine]
+            cur = (par[:, None, :] + child[None, :, :] * (w // 2)).reshape(-1, 3)
+        counts[0] += len(cur)
+        emit(0, cur)
+    return counts
+
+
+def cloud_shaped_counts(scale=1):
+    """cells per level without materialising them"""
+    return _cloud_refine(scale, lambda l, xyz: None)
+
+
+def cloud_shaped(scale=8):
+    """-> (cells int32[N,4], domain).  scale=1: 2048^3 finest units (~2 B cells: 32 GB of
+    cells — generate only where that fits); scale=k: domain 2048/k, ~2 B / k^3 cells."""
+    parts = []
+
+    def emit(l, xyz):
+        if len(xyz):
+            c = np.empty((len(xyz), 4), np.int32)
+            c[:, :3] = xyz
+            c[:, 3] = l
+            parts.append(c)
+    _cloud_refine(scale, emit)
+    return np.concatenate(parts), CLOUD_DOMAIN // scale
+
+
+def cloud_velocity(cells, domain):
+    """3 smooth channels (vx, vy, vz) for the multichannel DVR + streamline config: a swirl around
+    the z axis through the domain centre plus an upward drift, modulated by the §8(d) analytic
+    field; values in about [-1, 1]"""
+    cells = np.asarray(cells)
+    cw = (1 << cells[:, 3]).astype(np.float64)
+    c = (cells[:, :3].astype(np.float64) + 0.5 * cw[:, None]) / float(domain) - 0.5
+    m = 0.75 + 0.5 * (analytic_field(cells, domain, 0, noise=0.0).astype(np.float64) - 0.5)
+    vx = (-2.0 * c[:, 1] + 0.1) * m
+    vy = (2.0 * c[:, 0]) * m
+    vz = (0.3 + 0.4 * c[:, 2]) * m
+    return [vx.astype(np.float32), vy.astype(np.float32), vz.astype(np.float32)]

@@ -169,3 +169,26 @@ def test_camera_matches_reference_math(R):
     # fovy 90, focal 5 -> screen height 10, width 20; lower-left = (-10,-5,-5)
     assert np.allclose(d00, [-10, -5, -5], atol=1e-5)
     assert np.allclose(du * 200, [20, 0, 0], atol=1e-5) and np.allclose(dv * 100, [0, 10, 0], atol=1e-5)
+
+
+def test_cloud_shaped_c5_generator(R, orc):
+    """config C5's shape at 1/16 scale: octree-like refinement, 4 levels, the cells tile the domain
+    exactly, and the host builder agrees bit-exactly with the oracle's exaBuilder restatement; with
+    the reference's own exaBuilder too when oracle/_ref is present"""
+    cells, dom = synth.cloud_shaped(16)
+    assert dom == 128 and set(np.unique(cells[:, 3])) == {0, 1, 2, 3}
+    w = (1 << cells[:, 3]).astype(np.int64)
+    assert int((w ** 3).sum()) == dom ** 3                       # no holes, no overlap (volumes add up ...
+    key = np.unique(cells[:, 0].astype(np.int64) + dom * (cells[:, 1].astype(np.int64) + dom * cells[:, 2].astype(np.int64)))
+    assert len(key) == len(cells)                                # ... and no two cells share a corner)
+    assert (cells[:, :3] % w[:, None] == 0).all()
+    counts = synth.cloud_shaped_counts(16)
+    assert [int((cells[:, 3] == l).sum()) for l in range(4)] == counts
+    mine = R.ExaBricks.build(cells).to_bytes()
+    assert mine == orc.build_bricks(cells)
+    if orc.have_ref():
+        import tempfile
+        with tempfile.TemporaryDirectory() as d:
+            assert mine == orc.ref_build_bricks(cells, d)
+    v = synth.cloud_velocity(cells, dom)
+    assert len(v) == 3 and all(abs(f).max() <= 1.5 for f in v)
