@@ -193,11 +193,14 @@ def linear_field(cells, coef=(0.01, 0.02, 0.03), offset=0.1):
 
 
 # molecular-cloud-shaped — clumpy octree-like refinement from a seeded
-# multi-octave noise threshold, 4 levels, 3 channels.  The coarsest cells (level 3, width 8) tile the
-# domain; a cell of level l > 0 whose centre density exceeds CLOUD_THRESHOLD[l] is replaced by its 8
-# children (level l-1), which are tested in turn.  Density = 4 octaves (3, 6, 12, 24 cycles per
-# domain) of 3 plane waves each, directions/phases from splitmix64(CLOUD_SEED).
+# multi-octave noise threshold, 4 levels, 3 channels.  Block-structured like the FLASH data the
+# reference shows (tools/fromFlash): an octree whose nodes each hold CLOUD_BLOCK^3 cells.  The
+# coarsest nodes (level 3, 8*8 = 64 finest units wide) tile the domain; a node of level l > 0 whose
+# centre density exceeds CLOUD_THRESHOLD[l] is replaced by its 8 children (level l-1), which are
+# tested in turn.  Density = 4 octaves (3, 6, 12, 24 cycles per domain) of 3 plane waves each,
+# directions/phases from splitmix64(CLOUD_SEED).
 CLOUD_DOMAIN = 2048
+CLOUD_BLOCK = 8
 CLOUD_SEED = 0xC10D5EED
 CLOUD_THRESHOLD = {3: 0.50, 2: 0.55, 1: 0.60}
 
@@ -220,57 +223,60 @@ def cloud_density(centres, domain):
     """density in [0,1] at points given in finest units of a cubic domain of that width"""
     p = np.asarray(centres, np.float64) / float(domain)
     s = np.zeros(len(p))
-    norm = 0.0
-    waves = _cloud_waves()
-    for kvec, phase, amp in waves:
+    for kvec, phase, amp in _cloud_waves():
         s += amp * np.sin(p @ kvec + phase)
-    for o in range(4):
-        norm += 0.5 ** o
-    return 0.5 + 0.5 * s / norm
+    return 0.5 + 0.5 * s / sum(0.5 ** o for o in range(4))
 
 
-def _cloud_refine(scale, emit):
-    """top-down refinement; emit(level, xyz int32[n,3]) receives the final cells of every level,
-    in chunks; returns the per-level counts"""
+def cloud_nodes(scale=1):
+    """-> per level l an int32[n,3] array of the lower corners of the octree nodes that stay at
+    that level (each is CLOUD_BLOCK^3 cells of width 1<<l)"""
     dom = CLOUD_DOMAIN // scale
-    counts = [0, 0, 0, 0]
-    g = dom // 8
+    top = CLOUD_BLOCK * 8                                           # width of a level-3 node
+    g = dom // top
+    assert g >= 1 and g * top == dom, "scale must divide %d" % (CLOUD_DOMAIN // top)
     child = np.array([[i & 1, (i >> 1) & 1, (i >> 2) & 1] for i in range(8)], np.int32)
-    for z0 in range(0, g, 8):                                       # slabs of 8 coarse layers bound the memory
-        zz, yy, xx = np.meshgrid(np.arange(z0, min(g, z0 + 8), dtype=np.int32), np.arange(g, dtype=np.int32),
-                                 np.arange(g, dtype=np.int32), indexing="ij")
-        cur = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1) * 8
-        for l in (3, 2, 1):
-            w = 1 << l
-            refine = cloud_density(cur + 0.5 * w, dom) > CLOUD_THRESHOLD[l]
-            keep = cur[~refine]
-            counts[l] += len(keep)
-            emit(l, keep)
-            par = cur[refine]
-            cur = (par[:, None, :] + child[None, :, :] * (w // 2)).reshape(-1, 3)
-        counts[0] += len(cur)
-        emit(0, cur)
-    return counts
+    zz, yy, xx = np.meshgrid(np.arange(g, dtype=np.int32), np.arange(g, dtype=np.int32), np.arange(g, dtype=np.int32), indexing="ij")
+    cur = np.stack([xx.ravel(), yy.ravel(), zz.ravel()], axis=1) * top
+    nodes = {}
+    for l in (3, 2, 1):
+        w = CLOUD_BLOCK << l
+        refine = cloud_density(cur + 0.5 * w, dom) > CLOUD_THRESHOLD[l]
+        nodes[l] = cur[~refine]
+        cur = (cur[refine][:, None, :] + child[None, :, :] * (w // 2)).reshape(-1, 3)
+    nodes[0] = cur
+    return nodes
 
 
 def cloud_shaped_counts(scale=1):
     """cells per level without materialising them"""
-    return _cloud_refine(scale, lambda l, xyz: None)
+    n = cloud_nodes(scale)
+    return [len(n[l]) * CLOUD_BLOCK ** 3 for l in range(4)]
 
 
 def cloud_shaped(scale=8):
     """-> (cells int32[N,4], domain).  scale=1: 2048^3 finest units (~2 B cells: 32 GB of
-    cells — generate only where that fits); scale=k: domain 2048/k, ~2 B / k^3 cells."""
-    parts = []
-
-    def emit(l, xyz):
-        if len(xyz):
-            c = np.empty((len(xyz), 4), np.int32)
-            c[:, :3] = xyz
-            c[:, 3] = l
-            parts.append(c)
-    _cloud_refine(scale, emit)
-    return np.concatenate(parts), CLOUD_DOMAIN // scale
+    cells — generate only where that fits); scale=k (a power of two <= 32): domain 2048/k, ~2 B / k^3 cells."""
+    nodes = cloud_nodes(scale)
+    B = CLOUD_BLOCK
+    total = sum(len(nodes[l]) for l in range(4)) * B ** 3
+    out = np.empty((total, 4), np.int32)
+    o = np.arange(B, dtype=np.int32)
+    oz, oy, ox = (a.ravel() for a in np.meshgrid(o, o, o, indexing="ij"))
+    pos = 0
+    for l in range(4):
+        lo = nodes[l]
+        for b in range(0, len(lo), 1 << 13):
+            blk_lo = lo[b:b + (1 << 13)]
+            n = len(blk_lo) * B ** 3
+            blk = out[pos:pos + n].reshape(-1, B ** 3, 4)
+            blk[:, :, 0] = blk_lo[:, None, 0] + (ox << l)[None, :]
+            blk[:, :, 1] = blk_lo[:, None, 1] + (oy << l)[None, :]
+            blk[:, :, 2] = blk_lo[:, None, 2] + (oz << l)[None, :]
+            blk[:, :, 3] = l
+            pos += n
+    assert pos == total
+    return out, CLOUD_DOMAIN // scale
 
 
 def cloud_velocity(cells, domain):

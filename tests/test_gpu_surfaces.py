@@ -120,3 +120,43 @@ def test_surface_setters_errors(R, orc):
     with pytest.raises(Exception):
         r.updateContourPlanes([(1, 0, 0)] * 3, [0.5] * 3, [3, 0, 0], [1, 0, 0])     # channel out of range
     r.updateContourPlanes([(1, 0, 0)] * 3, [0.5] * 3, [3, 0, 0], [0, 0, 0])         # ... ignored while disabled
+
+
+def test_c5_shaped_multichannel_dvr_and_streamlines(R, orc):
+    """BASELINE.json configs[4] at 1/16 scale (synth.cloud_shaped: block-structured octree from a
+    noise threshold, 4 levels, 3 velocity channels): ABR bit-exact, 3-channel DVR within 1e-3,
+    RK4 streamlines within 1e-5 of the domain, and the frame with the cones drawn"""
+    from owlexabrick_b200 import synth
+    cells, dom = synth.cloud_shaped(16)
+    fields = synth.cloud_velocity(cells, dom)
+    r, sc, _ = make_pair(R, orc, cells, fields)
+    regions, leaf = r.get_abr()
+    assert leaf.tobytes() == sc.leaf.tobytes() and regions.tobytes() == sc.regions.tobytes()
+    cam = R.default_camera([0] * 3, [dom] * 3, 128, 96)
+    fd = scenes.FrameDesc(128, 96, cam, 3)
+    _world(r, fd)
+    fd.xf_domain = [(-1.2, 1.2)] * 3
+    fd.opacity_scale = 0.1
+    g_acc, g_rgba, o_acc, o_rgba, o_st = _render_both(r, sc, fd, orc)
+    assert np.abs(g_acc[..., :3] - o_acc[..., :3]).max() <= RGBA_TOL
+    assert o_acc[..., :3].max() > 0.3
+    st = r.render_stats()
+    for k in ("samples", "brickVisits", "cornerLoads", "segments"):      # the counters behind the algorithmic-bytes model
+        assert abs(st[k] - o_st[k]) <= 1e-3 * o_st[k], (k, st[k], o_st[k])
+    seeds = synth.random_points(100, [0.25 * dom] * 3, [0.75 * dom, 0.75 * dom, 0.5 * dom], seed=5)
+    T = 50
+    r.setTracerParams(len(seeds), T, dom / 64.0, (0, 1, 2))
+    r.setTracerSeeds(seeds)
+    r.setTracerEnabled(True)
+    r.traceAll()
+    g = r.readTraces()
+    o = sc.trace(seeds, T, (0, 1, 2), dom / 64.0, [0, 0, 0], [dom] * 3)
+    dead_g, dead_o = g[..., 0] >= 2e10, o[..., 0] >= 2e10
+    assert (dead_g != dead_o).sum() <= 3
+    m = ~dead_g & ~dead_o
+    assert m.sum() > 0.5 * m.size and np.abs(g[m] - o[m]).max() <= 1e-5 * dom * 4
+    fd.traces = g
+    fd.current_timestep = T
+    g_acc, _, o_acc2, _, _ = _render_both(r, sc, fd, orc)
+    _close(g_acc, o_acc2)
+    assert (np.abs(o_acc2[..., :3] - o_acc[..., :3]).max(axis=-1) > 0.05).sum() > 50, "no cones in the test frame"
