@@ -11,6 +11,7 @@
 // standing in for owl::vec3f / box3f / affine3f (same member names; no OWL dependency).
 #pragma once
 #include "../exabrick_b200.h"
+#include <cstring>
 #include <algorithm>
 #include <memory>
 #include <stdexcept>
@@ -133,6 +134,27 @@ struct ColorMapper {
 };
 
 // ---------------------------------------------------------------------------------------
+// exa::TriangleMesh (exa/TriangleMesh.h:24-34): vertex / index arrays; load() reads every mesh of a file
+struct TriangleMesh {
+  typedef std::shared_ptr<TriangleMesh> SP;
+  std::vector<vec3f> vertex;
+  std::vector<vec3i> index;
+  // the C ABI returns the meshes of a file concatenated; the mirror hands them back as one mesh
+  static std::vector<SP> load(const std::string &fileName)
+  {
+    float *v = nullptr; int32_t *ix = nullptr; size_t nv = 0, nt = 0;
+    detail::check(exa_triangle_mesh_load(fileName.c_str(), &v, &nv, &ix, &nt));
+    SP m = std::make_shared<TriangleMesh>();
+    m->vertex.resize(nv); m->index.resize(nt);
+    if (nv) std::memcpy(m->vertex.data(), v, nv * 12);
+    if (nt) std::memcpy(m->index.data(), ix, nt * 12);
+    exa_free(v); exa_free(ix);
+    std::vector<SP> out; if (nt) out.push_back(m);
+    return out;
+  }
+};
+
+// ---------------------------------------------------------------------------------------
 struct Config {
   typedef std::shared_ptr<Config> SP;
 
@@ -151,6 +173,16 @@ struct Config {
       sf->name = name ? name : ""; sf->value.assign(v, v + count); sf->valueRange = {range[0], range[1]};
       cfg->scalarFields.push_back(sf);
     }
+    {                                                      // config->surfaces (Config.cpp:165-171)
+      const float *v = nullptr; const int32_t *ix = nullptr; size_t nv = 0, nt = 0;
+      detail::check(exa_config_triangles(c, &v, &nv, &ix, &nt));
+      if (nt) {
+        TriangleMesh::SP mesh = std::make_shared<TriangleMesh>();
+        mesh->vertex.resize(nv); mesh->index.resize(nt);
+        std::memcpy(mesh->vertex.data(), v, nv * 12); std::memcpy(mesh->index.data(), ix, nt * 12);
+        cfg->surfaces.push_back(mesh);
+      }
+    }
     float m[12];
     detail::check(exa_config_voxel_space_transform(c, m));
     affine3f &x = cfg->bricks.voxelSpaceTransform;
@@ -166,6 +198,7 @@ struct Config {
   }
   struct { ExaBricks::SP sp; affine3f voxelSpaceTransform; } bricks;
   std::vector<ScalarField::SP> scalarFields;
+  std::vector<TriangleMesh::SP> surfaces;
   exa_config_t *handle = nullptr;
   ~Config() { bricks.sp.reset(); exa_config_destroy(handle); }
   Config(const Config &) = delete;
@@ -175,21 +208,27 @@ private:
 
 // ---------------------------------------------------------------------------------------
 // exa::OptixRenderer (exa/OptixRenderer.h:32-188).  The name is kept so that exa/viewer.cpp
-// compiles unchanged; nothing here uses OptiX.  `surfaces` (triangle meshes) are outside the
-// hot path and must be empty.
+// compiles unchanged; nothing here uses OptiX.  `surfaces` are world-space triangle meshes.
 struct OptixRenderer {
   typedef std::shared_ptr<OptixRenderer> SP;
 
-  template <typename SurfaceVector = std::vector<int>>
-  OptixRenderer(ExaBricks::SP input_, const SurfaceVector &surfaces_, std::vector<ScalarField::SP> scalarField, int cudaDevice = 0)
+  OptixRenderer(ExaBricks::SP input_, const std::vector<TriangleMesh::SP> &surfaces_, std::vector<ScalarField::SP> scalarField, int cudaDevice = 0)
       : scalarFields(std::move(scalarField)), input(std::move(input_))
   {
-    if (!surfaces_.empty()) throw std::runtime_error("triangle-mesh surfaces are outside the exabrick-b200 hot path");
     if (!input) throw std::runtime_error("no bricks");
     std::vector<const float *> ptrs; std::vector<size_t> counts;
     for (auto &sf : scalarFields) { ptrs.push_back(sf->value.data()); counts.push_back(sf->value.size()); }
     detail::check(exa_renderer_create(input->handle, ptrs.data(), counts.data(), (int)ptrs.size(), cudaDevice, &handle));
     voxelSpaceBounds = input->getBounds(); worldSpaceBounds = voxelSpaceBounds;
+    // one instance group over all meshes (OptixRenderer.cpp:556-608) = one concatenated mesh here
+    std::vector<float> v; std::vector<int32_t> ix;
+    for (auto &m : surfaces_) {
+      if (!m) continue;
+      const int32_t base = (int32_t)(v.size() / 3);
+      for (auto &p : m->vertex) { v.push_back(p.x); v.push_back(p.y); v.push_back(p.z); }
+      for (auto &t : m->index) { ix.push_back(t.x + base); ix.push_back(t.y + base); ix.push_back(t.z + base); }
+    }
+    if (!ix.empty()) detail::check(exa_renderer_set_triangle_meshes(handle, v.data(), v.size() / 3, ix.data(), ix.size() / 3));
   }
   ~OptixRenderer() { exa_renderer_destroy(handle); }
   OptixRenderer(const OptixRenderer &) = delete;

@@ -152,6 +152,13 @@ int exa_bricks_get_bounds(const exa_bricks_t *b, float lower[3], float upper[3])
 size_t exa_bricks_kd_count(const exa_bricks_t *b);           /* 0 unless built here */
 const ExaKdTreeNode *exa_bricks_kd_nodes(const exa_bricks_t *b);
 
+/* TriangleMesh::load (exa/TriangleMesh.cpp:21-68): file = repeated {int32 numVerts; vec3f[];
+ * int32 numTris; vec3i[]}.  All meshes of the file come back concatenated (indices rebased);
+ * both arrays are malloc'd (exa_free).  Errors as the reference: "cannot open file",
+ * "broken triangle model". */
+int exa_triangle_mesh_load(const char *fileName, float **vertices, size_t *numVerts,
+                           int32_t **indices, size_t *numTris);
+
 /* ---------------------------------------------------------------------------------------
  * Loaders — replace exa::ScalarField (exa/ScalarField.cpp:22-96), exa::ColorMapper
  * (exa/ColorMapper.h:64-80) and exa::Config (exa/Config.cpp:23-180)
@@ -180,6 +187,9 @@ const float *exa_config_field(const exa_config_t *c, int i, size_t *count, float
 int exa_config_voxel_space_transform(const exa_config_t *c, float xfm12[12]);
 /* Config::getBounds — world-space bounds (Config.cpp:48-55) */
 int exa_config_get_bounds(const exa_config_t *c, float lower[3], float upper[3]);
+/* Config::surfaces (`triangles <file>`, Config.cpp:165-171), concatenated; owned by the config */
+int exa_config_triangles(const exa_config_t *c, const float **vertices, size_t *numVerts,
+                         const int32_t **indices, size_t *numTris);
 
 /* ---------------------------------------------------------------------------------------
  * Renderer — replaces exa::OptixRenderer (exa/OptixRenderer.h:32-188)
@@ -246,6 +256,12 @@ int exa_renderer_update_contour_planes(exa_renderer_t *r, const float *normals3,
 /* frameState.ao.{enabled,length} (programs/FrameState.h:60-63, poked by viewer.cpp:953-954): two
  * cosine-distributed occlusion rays of that length per shaded surface hit (exabrick.cu:1611-1646) */
 int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length);
+/* the `surfaces` argument of the OptixRenderer constructor (OptixRenderer.cpp:556-608): world-space
+ * triangle meshes, concatenated.  Builds a BVH on the host (set-up, like the reference's
+ * owlGroupBuildAccel) and uploads it; numTris = 0 removes the meshes.  Hits shade as
+ * ambient .2 + .8 |d.N| (closest hit SurfaceBVH, exabrick.cu:420-433). */
+int exa_renderer_set_triangle_meshes(exa_renderer_t *r, const float *vertices, size_t numVerts,
+                                     const int32_t *indices, size_t numTris);
 /* early-ray-termination threshold (reference constant 0.98, exabrick.cu:49); >1 disables */
 int exa_renderer_set_ert_threshold(exa_renderer_t *r, float threshold);
 /* tracer (OptixRenderer.h:155-165, .cpp:444-487) */

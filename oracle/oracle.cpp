@@ -904,11 +904,32 @@ static V3 cosineSampleHemisphere(float u1, float u2)
   return v3(r * cosf(theta), r * sinf(theta), sqrtf(1.f - u1));
 }
 
-// traceSurfaces, exabrick.cu:1476-1529 (no triangle meshes: SURVEY 8f rank 3, not restated)
+// traceSurfaces, exabrick.cu:1476-1529
 static void traceSurfaces(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &isoActive, bool anyIso,
                           const Ray &ray, Surface &prd, bool withContourPlanes, OrcStats *st)
 {
   prd.primID = -1; prd.t_hit = ray.tmax;
+  // triangle geometry first (:1488-1490); closest hit program SurfaceBVH (:420-433).  OptiX's
+  // built-in triangle test is replaced by a brute-force closest hit over all triangles (no
+  // culling: the ray flags only disable any-hit programs)
+  if (f.meshVerts && f.meshIndex) {
+    float best = ray.tmax; int bestTri = -1;
+    for (int t = 0; t < f.numMeshTris; t++) {
+      const int32_t *ix = f.meshIndex + 3 * (size_t)t;
+      const V3 A = v3(f.meshVerts[3 * ix[0]], f.meshVerts[3 * ix[0] + 1], f.meshVerts[3 * ix[0] + 2]);
+      const V3 B = v3(f.meshVerts[3 * ix[1]], f.meshVerts[3 * ix[1] + 1], f.meshVerts[3 * ix[1] + 2]);
+      const V3 Cc = v3(f.meshVerts[3 * ix[2]], f.meshVerts[3 * ix[2] + 1], f.meshVerts[3 * ix[2] + 2]);
+      const float tt = intersectRayTriangle(ray, A, B - A, Cc - A);
+      if (tt > ray.tmin && tt < best) { best = tt; bestTri = t; }
+    }
+    if (bestTri >= 0) {
+      const int32_t *ix = f.meshIndex + 3 * (size_t)bestTri;
+      const V3 A = v3(f.meshVerts[3 * ix[0]], f.meshVerts[3 * ix[0] + 1], f.meshVerts[3 * ix[0] + 2]);
+      const V3 B = v3(f.meshVerts[3 * ix[1]], f.meshVerts[3 * ix[1] + 1], f.meshVerts[3 * ix[1] + 2]);
+      const V3 Cc = v3(f.meshVerts[3 * ix[2]], f.meshVerts[3 * ix[2] + 1], f.meshVerts[3 * ix[2] + 2]);
+      prd.primID = bestTri; prd.t_hit = best; prd.Ng = normalize(cross(B - A, Cc - A)); prd.ambient = .2f; prd.base = v3(.8f, .8f, .8f);
+    }
+  }
   if (withContourPlanes)
     for (int i = 0; i < 3; i++)
       if (f.cpEnabled[i]) {
@@ -992,7 +1013,7 @@ struct LCG16 {
 static inline float linear_to_srgb(float x) { return x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.f / 2.4f) - 0.055f; }
 static inline int make_8bit(float f) { return std::min(255, std::max(0, (int)(f * 256.f))); }
 
-// __raygen__renderFrame, exabrick.cu:1576-1720 (triangle meshes are not restated: SURVEY §8f rank 3)
+// __raygen__renderFrame, exabrick.cu:1576-1720
 extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0, int x1, int y1,
                           float *accum, uint32_t *rgba8, OrcStats *stats)
 {
@@ -1035,7 +1056,7 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
         traceSurfaces(s, f, isoActive, anyIso, ray, surf, true, &st);        // :1598 ST_ALL_SURFACES
         V3 bg = v3(0, 0, 0);
         if (surf.primID != -1) {                           // :1604-1652
-          const bool shade = surf.primID == PRIMID_STREAMLINE || surf.primID == PRIMID_PLANE ||
+          const bool shade = surf.primID >= 0 || surf.primID == PRIMID_STREAMLINE || surf.primID == PRIMID_PLANE ||
                              (surf.primID == PRIMID_ISOSURFACE && f.gradientShadingISO);
           if (shade && length(surf.Ng) > 0.f) {
             const int aoSamples = f.aoEnabled ? 2 : 0;

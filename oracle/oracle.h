@@ -67,6 +67,10 @@ typedef struct OrcFrame {
   int32_t cpEnabled[3]; float cpNormal[3][3]; float cpOffset[3]; int32_t cpChannel[3];
   int32_t aoEnabled; float aoLength;
   float   worldLo[3], worldHi[3];
+  /* triangle meshes (world space; exabrick.cu:420-433, OptixRenderer.cpp:556-608), all meshes
+     concatenated: vertices 3*numVerts floats, indices 3*numTris ints */
+  int32_t numMeshVerts, numMeshTris;
+  const float *meshVerts; const int32_t *meshIndex;
 } OrcFrame;
 
 typedef struct OrcStats {          /* counters for the algorithmic-bytes model */

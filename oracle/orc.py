@@ -45,6 +45,8 @@ class OrcFrame(C.Structure):
         ("cpEnabled", C.c_int32 * 3), ("cpNormal", (C.c_float * 3) * 3), ("cpOffset", C.c_float * 3), ("cpChannel", C.c_int32 * 3),
         ("aoEnabled", C.c_int32), ("aoLength", C.c_float),
         ("worldLo", C.c_float * 3), ("worldHi", C.c_float * 3),
+        ("numMeshVerts", C.c_int32), ("numMeshTris", C.c_int32),
+        ("meshVerts", C.POINTER(C.c_float)), ("meshIndex", C.POINTER(C.c_int32)),
     ]
 
 

@@ -2,6 +2,8 @@
 // exa/OptixRenderer.{h,cpp}).  No CPU fallback anywhere: every entry point that needs the
 // device fails with EXA_ERR_CUDA when CUDA is unusable.
 #include "render.cuh"
+#include <algorithm>
+#include <vector>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -49,6 +51,7 @@ struct exa_renderer {
   float steplen = 1e-6f; int tracerChannels[3] = {0, 1, 2};
   float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
   float *d_traces = nullptr; size_t tracesCap = 0;
+  float4 *d_meshNodes = nullptr; float *d_meshTris = nullptr; int numMeshTris = 0;          // triangle-mesh BVH (set_triangle_meshes)
   float *d_traceBounds = nullptr; int traceBoundsCap = 0; bool traceBoundsDirty = true;   // one box per trace (k_traceBounds)
   unsigned long long *d_stats = nullptr;
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
@@ -111,7 +114,8 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   }
   P.aoEnabled = r->fs.ao.enabled; P.aoLength = r->fs.ao.length;
   memcpy(P.worldLo, r->worldLo, 12); memcpy(P.worldHi, r->worldHi, 12);
-  P.anySurf = (P.anyIso || anyContour || P.traces) ? 1 : 0;
+  P.meshNodes = r->d_meshNodes; P.meshTris = r->d_meshTris; P.numMeshTris = r->numMeshTris;
+  P.anySurf = (P.anyIso || anyContour || P.traces || P.numMeshTris > 0) ? 1 : 0;
   P.stats = nullptr;
   P.longQueue = r->d_longQueue; P.longCount = r->d_longCount; P.sampleBudget = r->sampleBudget;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
@@ -317,7 +321,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
-  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
+  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
   delete r;
 }
 
@@ -515,6 +519,75 @@ int exa_renderer_update_contour_planes(exa_renderer_t *r, const float *normals3,
     r->fs.contourPlane[i].offset = offsets[i]; r->fs.contourPlane[i].channel = channels[i]; r->fs.contourPlane[i].enabled = enabled[i] ? 1 : 0;
   }
   r->masksDirty = true;                                     // space skipping is off while a plane is enabled (:518-530)
+  return EXA_OK;
+}
+// ---- triangle meshes (OptixRenderer ctor :556-608: one OWL triangle geom per mesh under an instance group) ----
+namespace {
+struct MeshBuild {
+  const float *v; const int32_t *ix;
+  std::vector<uint32_t> order;                                 // triangle ids in BVH order
+  std::vector<float> cx[3];                                    // centroids
+  std::vector<float4> nodes;
+  void bounds(uint32_t first, uint32_t count, float lo[3], float hi[3]) const
+  {
+    for (int d = 0; d < 3; d++) { lo[d] = 3e38f; hi[d] = -3e38f; }
+    for (uint32_t i = first; i < first + count; i++)
+      for (int c = 0; c < 3; c++) { const float *p = v + 3 * (size_t)ix[3 * (size_t)order[i] + c];
+        for (int d = 0; d < 3; d++) { lo[d] = std::min(lo[d], p[d]); hi[d] = std::max(hi[d], p[d]); } }
+  }
+  // node `ni` over order[first, first+count): median split on the centroid along the widest axis
+  void build(uint32_t ni, uint32_t first, uint32_t count)
+  {
+    float lo[3], hi[3]; bounds(first, count, lo, hi);
+    if (count <= 4) {
+      nodes[2 * (size_t)ni] = make_float4(lo[0], lo[1], lo[2], __uint_as_float_host(first));
+      nodes[2 * (size_t)ni + 1] = make_float4(hi[0], hi[1], hi[2], __uint_as_float_host(count));
+      return;
+    }
+    int axis = 0; for (int d = 1; d < 3; d++) if (hi[d] - lo[d] > hi[axis] - lo[axis]) axis = d;
+    const uint32_t half = count / 2;
+    const std::vector<float> &c = cx[axis];
+    std::nth_element(order.begin() + first, order.begin() + first + half, order.begin() + first + count,
+                     [&](uint32_t a, uint32_t b) { return c[a] < c[b] || (c[a] == c[b] && a < b); });
+    const uint32_t child = (uint32_t)(nodes.size() / 2);
+    nodes.resize(nodes.size() + 4);
+    nodes[2 * (size_t)ni] = make_float4(lo[0], lo[1], lo[2], __uint_as_float_host(child));
+    nodes[2 * (size_t)ni + 1] = make_float4(hi[0], hi[1], hi[2], __uint_as_float_host(0u));
+    build(child, first, half);
+    build(child + 1, first + half, count - half);
+  }
+  static float __uint_as_float_host(uint32_t u) { float f; memcpy(&f, &u, 4); return f; }
+};
+}
+
+int exa_renderer_set_triangle_meshes(exa_renderer_t *r, const float *vertices, size_t numVerts, const int32_t *indices, size_t numTris)
+{
+  if (!r || (numTris && (!vertices || !indices))) { setError("set_triangle_meshes: null argument"); return EXA_ERR_INVALID; }
+  if (numTris > (size_t)1 << 30) { setError("set_triangle_meshes: too many triangles"); return EXA_ERR_INVALID; }
+  for (size_t i = 0; i < 3 * numTris; i++)
+    if (indices[i] < 0 || (size_t)indices[i] >= numVerts) { setError("broken triangle model"); return EXA_ERR_INVALID; }   // TriangleMesh.cpp:39-47
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaStreamSynchronize(r->stream));
+  cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); r->d_meshNodes = nullptr; r->d_meshTris = nullptr; r->numMeshTris = 0;
+  if (!numTris) return EXA_OK;
+  MeshBuild mb; mb.v = vertices; mb.ix = indices;
+  mb.order.resize(numTris);
+  for (int d = 0; d < 3; d++) mb.cx[d].resize(numTris);
+  for (size_t t = 0; t < numTris; t++) {
+    mb.order[t] = (uint32_t)t;
+    for (int d = 0; d < 3; d++)
+      mb.cx[d][t] = (vertices[3 * (size_t)indices[3 * t] + d] + vertices[3 * (size_t)indices[3 * t + 1] + d] + vertices[3 * (size_t)indices[3 * t + 2] + d]) * (1.f / 3.f);
+  }
+  mb.nodes.resize(2);
+  mb.build(0, 0, (uint32_t)numTris);
+  std::vector<float> tris(9 * numTris);
+  for (size_t i = 0; i < numTris; i++)
+    for (int c = 0; c < 3; c++) memcpy(&tris[9 * i + 3 * c], vertices + 3 * (size_t)indices[3 * (size_t)mb.order[i] + c], 12);
+  CKR(cudaMalloc(&r->d_meshNodes, mb.nodes.size() * sizeof(float4)));
+  CKR(cudaMalloc(&r->d_meshTris, tris.size() * sizeof(float)));
+  CKR(cudaMemcpy(r->d_meshNodes, mb.nodes.data(), mb.nodes.size() * sizeof(float4), cudaMemcpyHostToDevice));
+  CKR(cudaMemcpy(r->d_meshTris, tris.data(), tris.size() * sizeof(float), cudaMemcpyHostToDevice));
+  r->numMeshTris = (int)numTris;
   return EXA_OK;
 }
 int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length)

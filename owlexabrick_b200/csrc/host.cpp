@@ -146,6 +146,42 @@ int exa_bricks_get_bounds(const exa_bricks_t *b, float lower[3], float upper[3])
 }
 
 // ---------------------------------------------------------------------------------------
+// TriangleMesh::load (exa/TriangleMesh.cpp:21-68): a file is a sequence of meshes, each
+// {int32 numVerts; vec3f[numVerts]; int32 numTris; vec3i[numTris]}; here all meshes of the file are
+// returned as ONE vertex / index array (indices rebased), which is what the renderer consumes.
+int exa_triangle_mesh_load(const char *fileName, float **vertices, size_t *numVerts, int32_t **indices, size_t *numTris)
+{
+  if (!vertices || !numVerts || !indices || !numTris) { setError("exa_triangle_mesh_load: null argument"); return EXA_ERR_INVALID; }
+  std::vector<uint8_t> buf;
+  int rc = readFile(fileName, buf);
+  if (rc) { setError("cannot open file"); return rc; }
+  std::vector<float> v; std::vector<int32_t> ix;
+  size_t off = 0;
+  while (off + 4 <= buf.size()) {
+    int32_t nv; memcpy(&nv, buf.data() + off, 4); off += 4;
+    if (nv < 0 || off + (size_t)nv * 12 + 4 > buf.size()) { setError("broken triangle model"); return EXA_ERR_INVALID; }
+    const size_t base = v.size() / 3;
+    v.resize(v.size() + 3 * (size_t)nv);
+    memcpy(v.data() + 3 * base, buf.data() + off, (size_t)nv * 12); off += (size_t)nv * 12;
+    int32_t nt; memcpy(&nt, buf.data() + off, 4); off += 4;
+    if (nt < 0 || off + (size_t)nt * 12 > buf.size()) { setError("broken triangle model"); return EXA_ERR_INVALID; }
+    const size_t tbase = ix.size();
+    ix.resize(ix.size() + 3 * (size_t)nt);
+    memcpy(ix.data() + tbase, buf.data() + off, (size_t)nt * 12); off += (size_t)nt * 12;
+    for (size_t i = tbase; i < ix.size(); i++) {
+      if (ix[i] < 0 || ix[i] >= nv) { setError("broken triangle model"); return EXA_ERR_INVALID; }   // :39-47
+      ix[i] += (int32_t)base;
+    }
+  }
+  float *ov = (float *)malloc(std::max<size_t>(1, v.size()) * 4);
+  int32_t *oi = (int32_t *)malloc(std::max<size_t>(1, ix.size()) * 4);
+  if (!ov || !oi) { free(ov); free(oi); setError("out of host memory"); return EXA_ERR_LIMIT; }
+  memcpy(ov, v.data(), v.size() * 4); memcpy(oi, ix.data(), ix.size() * 4);
+  *vertices = ov; *numVerts = v.size() / 3; *indices = oi; *numTris = ix.size() / 3;
+  return EXA_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 int exa_scalar_field_load(const char *fileName, int compat, float **values, size_t *count, float valueRange[2])
 {
   if (!values || !count) { setError("exa_scalar_field_load: null argument"); return EXA_ERR_INVALID; }
@@ -201,6 +237,7 @@ struct exa_config {
   std::vector<Field> fields;
   float remapFrom[6] = {0, 0, 0, 1, 1, 1}, remapTo[6] = {0, 0, 0, 1, 1, 1};
   float xfm[12];
+  float *meshVerts = nullptr; int32_t *meshIndex = nullptr; size_t numMeshVerts = 0, numMeshTris = 0;   // `triangles <file>`
 };
 
 // 3x3 (column vectors) + translation helpers restating owl AffineSpace3f rcp / operator*
@@ -296,7 +333,13 @@ int exa_config_parse(const char *fileName, int scalarCompat, exa_config_t **out)
         if (rc) return fail(rc, "");
         it += 2; continue;
       }
-      if (t == "triangles") { need(1); it += 2; continue; }   // meshes are out of scope
+      if (t == "triangles") {                                 // Config.cpp:165-171
+        need(1);
+        free(cfg->meshVerts); free(cfg->meshIndex); cfg->meshVerts = nullptr; cfg->meshIndex = nullptr;
+        int rc = exa_triangle_mesh_load((basePath + tokens[it + 1]).c_str(), &cfg->meshVerts, &cfg->numMeshVerts, &cfg->meshIndex, &cfg->numMeshTris);
+        if (rc) return fail(rc, "");
+        it += 2; continue;
+      }
       return fail(EXA_ERR_INVALID, "error in parsing config file: unknown token '" + t + "'");
     }
   } catch (std::exception &e) { return fail(EXA_ERR_INVALID, e.what()); }
@@ -313,7 +356,14 @@ void exa_config_destroy(exa_config_t *c)
   if (!c) return;
   exa_bricks_destroy(c->bricks);
   for (auto &f : c->fields) free(f.values);
+  free(c->meshVerts); free(c->meshIndex);
   delete c;
+}
+int exa_config_triangles(const exa_config_t *c, const float **vertices, size_t *numVerts, const int32_t **indices, size_t *numTris)
+{
+  if (!c || !vertices || !numVerts || !indices || !numTris) { setError("exa_config_triangles: null argument"); return EXA_ERR_INVALID; }
+  *vertices = c->meshVerts; *numVerts = c->numMeshVerts; *indices = c->meshIndex; *numTris = c->numMeshTris;
+  return EXA_OK;
 }
 const exa_bricks_t *exa_config_bricks(const exa_config_t *c) { return c ? c->bricks : nullptr; }
 int exa_config_num_fields(const exa_config_t *c) { return c ? (int)c->fields.size() : 0; }

@@ -493,7 +493,6 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 // -----------------------------------------------------------------------------------------
 // surface pass (traceSurfaces, exabrick.cu:1476-1529): contour planes, streamline cones and
 // implicit iso-surfaces; primary rays and the two ambient-occlusion rays of a hit share it.
-// Triangle meshes are not built.
 // -----------------------------------------------------------------------------------------
 enum { PRIM_NONE = -1, PRIM_ISOSURFACE = -23, PRIM_PLANE = -24, PRIM_STREAMLINE = -25 };
 struct SurfHit { int prim; float t; float3 Ng, base; float ambient; };
@@ -593,11 +592,55 @@ __device__ __noinline__ void traceCones(const RenderParams &P, float3 o, float3 
   }
 }
 
+// Triangle meshes (owl::traceRay(surfaceModel) + closest hit SurfaceBVH, exabrick.cu:420-433,
+// 1488-1490): stack traversal of the host-built BVH, closest hit inside (tmin, tmax); no culling.
+// The ray/triangle test is the one the reference itself uses for contour planes (:1316-1344);
+// OptiX's built-in triangle test differs from it only on shared edges.
+__device__ __noinline__ void traceMesh(const RenderParams &P, float3 o, float3 d, float tmin, float tmax, SurfHit &prd)
+{
+  if (!P.meshNodes || P.numMeshTris <= 0) return;
+  float best = tmax; int bestTri = -1;
+  const float3 invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
+  uint32_t stack[64]; int sp = 0;
+  stack[sp++] = 0;
+  while (sp) {
+    const uint32_t ni = stack[--sp];
+    const float4 n0 = __ldg(P.meshNodes + 2 * (size_t)ni), n1 = __ldg(P.meshNodes + 2 * (size_t)ni + 1);
+    const float px = 1e-4f * (n1.x - n0.x) + 1e-6f * (fabsf(n0.x) + fabsf(n1.x)), py = 1e-4f * (n1.y - n0.y) + 1e-6f * (fabsf(n0.y) + fabsf(n1.y)),
+                pz = 1e-4f * (n1.z - n0.z) + 1e-6f * (fabsf(n0.z) + fabsf(n1.z));
+    const float ax = (n0.x - px - o.x) * invd.x, bx = (n1.x + px - o.x) * invd.x;
+    const float ay = (n0.y - py - o.y) * invd.y, by = (n1.y + py - o.y) * invd.y;
+    const float az = (n0.z - pz - o.z) * invd.z, bz = (n1.z + pz - o.z) * invd.z;
+    const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
+    const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best));
+    if (t0 > t1) continue;
+    const uint32_t a = __float_as_uint(n0.w), b = __float_as_uint(n1.w);
+    if (b) {
+      for (uint32_t k = 0; k < b; k++) {
+        const float *t = P.meshTris + 9 * (size_t)(a + k);
+        const float3 A = f3(__ldg(t), __ldg(t + 1), __ldg(t + 2));
+        const float3 e1 = f3(__ldg(t + 3) - A.x, __ldg(t + 4) - A.y, __ldg(t + 5) - A.z);
+        const float3 e2 = f3(__ldg(t + 6) - A.x, __ldg(t + 7) - A.y, __ldg(t + 8) - A.z);
+        const float tt = surf::rayTriangle(o, d, A, e1, e2);
+        if (tt > tmin && tt < best) { best = tt; bestTri = (int)(a + k); }
+      }
+    } else if (sp < 62) { stack[sp++] = a; stack[sp++] = a + 1; }
+  }
+  if (bestTri >= 0) {
+    const float *t = P.meshTris + 9 * (size_t)bestTri;
+    const float3 A = f3(__ldg(t), __ldg(t + 1), __ldg(t + 2));
+    const float3 e1 = f3(__ldg(t + 3) - A.x, __ldg(t + 4) - A.y, __ldg(t + 5) - A.z);
+    const float3 e2 = f3(__ldg(t + 6) - A.x, __ldg(t + 7) - A.y, __ldg(t + 8) - A.z);
+    prd.prim = bestTri; prd.t = best; prd.Ng = normalize3(surf::crossp(e1, e2)); prd.ambient = .2f; prd.base = f3(.8f, .8f, .8f);
+  }
+}
+
 template <bool STATS, bool DUAL>
 __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
                                               float3 o, float3 d, float tmin, float tmax, bool withContourPlanes, SurfHit &prd, RayStats &rs)
 {
   prd.prim = PRIM_NONE; prd.t = tmax; prd.Ng = f3(0, 0, 0); prd.base = f3(0, 0, 0); prd.ambient = 0.f;
+  traceMesh(P, o, d, tmin, tmax, prd);
   if (withContourPlanes) traceContourPlanes<STATS, DUAL>(P, xfTables, o, d, prd, rs);
   if (P.traces) {
     SurfHit sl; traceCones(P, o, d, tmin, tmax, sl);
@@ -728,7 +771,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       traceSurfaces<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, true, sh, rs);
       surfT = sh.t;
       if (sh.prim != PRIM_NONE) {
-        const bool shade = sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
+        const bool shade = sh.prim >= 0 || sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
         if (shade && len3(sh.Ng) > 0.f) {
           const int aoSamples = P.aoEnabled ? 2 : 0;
           const float3 isect = rayAt(o, d, sh.t);

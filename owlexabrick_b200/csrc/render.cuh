@@ -45,7 +45,11 @@ struct RenderParams {
   int cpEnabled[EXA_MAX_CONTOUR_PLANES]; float cpNormal[EXA_MAX_CONTOUR_PLANES][3]; float cpOffset[EXA_MAX_CONTOUR_PLANES]; int cpChannel[EXA_MAX_CONTOUR_PLANES];
   int aoEnabled; float aoLength;
   float worldLo[3], worldHi[3];
-  int anySurf;                         // an iso-surface, contour plane or visible streamline: run the surface pass
+  // triangle meshes (surfaceModel, OptixRenderer.cpp:556-608): host-built BVH, 2 x float4 per node
+  // {lo.xyz, a}{hi.xyz, b}: b == 0 inner node with children a, a+1; b > 0 leaf of triangles [a, a+b);
+  // triangles in BVH order, 9 floats each (A, B, C), world space
+  const float4 *meshNodes; const float *meshTris; int numMeshTris;
+  int anySurf;                         // a mesh, iso-surface, contour plane or visible streamline: run the surface pass
   unsigned long long *stats;           // 4 counters (ExaStats) or null
   LongRay *longQueue; int *longCount;  // long-ray queue (capacity width*height) and {count, head}; null: off
   int sampleBudget;                    // samples a ray may take in k_renderFrame before it is handed over

@@ -188,6 +188,20 @@ def simple_camera(pos, at, up, fovy_deg, width, height):
     return pos, lower_left, (horizontal / f(width)).astype(f), (vertical / f(height)).astype(f)
 
 
+def load_triangle_meshes(file_name):
+    """TriangleMesh::load (exa/TriangleMesh.cpp:21-68) -> (vertices float32[n,3], indices int32[m,3]), all meshes
+    of the file concatenated"""
+    v, i, nv, nt = C.c_void_p(), C.c_void_p(), C.c_size_t(), C.c_size_t()
+    check(lib.exa_triangle_mesh_load(file_name.encode(), C.byref(v), C.byref(nv), C.byref(i), C.byref(nt)))
+    try:
+        verts = np.frombuffer(C.string_at(v, nv.value * 12), np.float32).reshape(-1, 3).copy()
+        idx = np.frombuffer(C.string_at(i, nt.value * 12), np.int32).reshape(-1, 3).copy()
+    finally:
+        lib.exa_free(v)
+        lib.exa_free(i)
+    return verts, idx
+
+
 def default_camera(world_lo, world_hi, width, height, fovy=70.0):
     """viewer default: from = center + (-.3,.7,1)*span, at = center, up = y (viewer.cpp:1283-1295)"""
     lo, hi = np.asarray(world_lo, np.float32), np.asarray(world_hi, np.float32)
@@ -284,6 +298,16 @@ class Renderer:
         c = np.ascontiguousarray(channels, dtype=np.int32)
         e = np.ascontiguousarray(enabled, dtype=np.int32)
         check(lib.exa_renderer_update_contour_planes(self.h, _p(n), _p(o), _p(c), _p(e)))
+
+    def setTriangleMeshes(self, vertices=None, indices=None):
+        """the `surfaces` of the OptixRenderer constructor (exa/OptixRenderer.cpp:556-608): world-space
+        triangle meshes, concatenated; None removes them"""
+        if vertices is None or indices is None or len(indices) == 0:
+            check(lib.exa_renderer_set_triangle_meshes(self.h, None, 0, None, 0))
+            return
+        v = np.ascontiguousarray(vertices, dtype=np.float32).reshape(-1, 3)
+        i = np.ascontiguousarray(indices, dtype=np.int32).reshape(-1, 3)
+        check(lib.exa_renderer_set_triangle_meshes(self.h, _p(v), len(v), _p(i), len(i)))
 
     def setAO(self, enable, length=0.0):
         """frameState.ao (programs/FrameState.h:60-63; exa/viewer.cpp:953-954)"""

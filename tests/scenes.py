@@ -43,6 +43,7 @@ class FrameDesc:
         self.traces = None
         self.current_timestep = 0
         self.world = ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
+        self.mesh = None                                 # (vertices float32[n,3], indices int32[m,3]), world space
 
     def to_orc(self, orc):
         f = orc.OrcFrame()
@@ -77,6 +78,13 @@ class FrameDesc:
             f._keep = tr                                  # keep the buffer alive with the frame
             f.numTraces, f.numTimesteps, f.currentTimestep = tr.shape[0], tr.shape[1], int(self.current_timestep)
             f.traces = tr.ctypes.data_as(C.POINTER(C.c_float))
+        if self.mesh is not None:
+            mv = np.ascontiguousarray(self.mesh[0], dtype=np.float32).reshape(-1, 3)
+            mi = np.ascontiguousarray(self.mesh[1], dtype=np.int32).reshape(-1, 3)
+            f._keep_mesh = (mv, mi)
+            f.numMeshVerts, f.numMeshTris = len(mv), len(mi)
+            f.meshVerts = mv.ctypes.data_as(C.POINTER(C.c_float))
+            f.meshIndex = mi.ctypes.data_as(C.POINTER(C.c_int32))
         for i, (en, nrm, off, ch) in enumerate(self.contour):
             n = np.asarray(nrm, np.float32)
             n = n * (np.float32(1) / np.sqrt(np.float32(n[0] * n[0] + n[1] * n[1] + n[2] * n[2])))   # OptixRenderer.cpp:511
@@ -109,6 +117,28 @@ class FrameDesc:
         r.updateContourPlanes([c[1] for c in self.contour], [c[2] for c in self.contour], [c[3] for c in self.contour],
                               [c[0] for c in self.contour])
         r.setAO(self.ao[0], self.ao[1])
+        if self.mesh is not None:
+            r.setTriangleMeshes(self.mesh[0], self.mesh[1])
+        else:
+            r.setTriangleMeshes(None, None)
+
+
+def uv_sphere(centre, radius, nu=24, nv=12):
+    """triangle mesh of a sphere: (vertices float32[n,3], indices int32[m,3])"""
+    th = np.linspace(0, np.pi, nv + 1)
+    ph = np.linspace(0, 2 * np.pi, nu, endpoint=False)
+    v = np.array([[np.sin(t) * np.cos(p), np.cos(t), np.sin(t) * np.sin(p)] for t in th for p in ph])
+    v = (np.asarray(centre)[None, :] + radius * v).astype(np.float32)
+    idx = []
+    for j in range(nv):
+        for i in range(nu):
+            a, b = j * nu + i, j * nu + (i + 1) % nu
+            c, d = a + nu, b + nu
+            if j > 0:
+                idx.append((a, b, c))
+            if j < nv - 1:
+                idx.append((b, d, c))
+    return v, np.array(idx, np.int32)
 
 
 def unpack_rgba8(img):

@@ -160,3 +160,25 @@ def test_c5_shaped_multichannel_dvr_and_streamlines(R, orc):
     g_acc, _, o_acc2, _, _ = _render_both(r, sc, fd, orc)
     _close(g_acc, o_acc2)
     assert (np.abs(o_acc2[..., :3] - o_acc[..., :3]).max(axis=-1) > 0.05).sum() > 50, "no cones in the test frame"
+
+
+@pytest.mark.parametrize("ao", [False, True])
+def test_triangle_mesh_vs_oracle(R, orc, ao):
+    """world-space triangle meshes (the `surfaces` of the OptixRenderer ctor): BVH traversal in the
+    frame kernel against the oracle's brute-force closest hit; with AO the mesh and an iso-surface
+    occlude each other"""
+    r, sc, fd, dom = _frame_pair(R, orc, "nb64_off", 1)
+    _world(r, fd)
+    fd.opacity_scale = 0.03
+    v1, i1 = scenes.uv_sphere([dom * 0.45, dom * 0.5, dom * 0.55], dom * 0.2, 40, 20)
+    v2, i2 = scenes.uv_sphere([dom * 0.8, dom * 0.7, dom * 0.3], dom * 0.12, 16, 8)
+    fd.mesh = (np.concatenate([v1, v2]), np.concatenate([i1, i2 + len(v1)]))
+    if ao:
+        fd.iso = [(1, 0.85, 0), (0, 0.0, 0)]
+        fd.ao = (1, 10.0)
+    g_acc, _, o_acc, _, _ = _render_both(r, sc, fd, orc)
+    _close(g_acc, o_acc, 0.01 if ao else 0.003)
+    fd.mesh = None                                       # removing the meshes gives the plain frame again
+    g2, _, o2, _, _ = _render_both(r, sc, fd, orc)
+    _close(g2, o2, 0.01 if ao else 0.003)
+    assert (np.abs(o2[..., :3] - o_acc[..., :3]).max(axis=-1) > 0.05).sum() > 100, "no mesh in the test frame"

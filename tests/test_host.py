@@ -192,3 +192,25 @@ def test_cloud_shaped_c5_generator(R, orc):
             assert mine == orc.ref_build_bricks(cells, d)
     v = synth.cloud_velocity(cells, dom)
     assert len(v) == 3 and all(abs(f).max() <= 1.5 for f in v)
+
+
+def test_triangle_mesh_file_and_config(R, built_lib, tmp_path):
+    """TriangleMesh::load (exa/TriangleMesh.cpp:21-68): a file is a sequence of meshes; the loader
+    returns them concatenated with rebased indices; `triangles <file>` in a config (Config.cpp:165-171)"""
+    import scenes
+    v1, i1 = scenes.uv_sphere([1, 2, 3], 2.0, 8, 4)
+    v2 = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32)
+    i2 = np.array([[0, 1, 2]], np.int32)
+    p = tmp_path / "m.tris"
+    with open(p, "wb") as f:
+        for v, i in ((v1, i1), (v2, i2)):
+            f.write(np.int32(len(v)).tobytes() + v.tobytes() + np.int32(len(i)).tobytes() + i.tobytes())
+    v, i = R.load_triangle_meshes(str(p))
+    assert np.array_equal(v, np.concatenate([v1, v2])) and np.array_equal(i, np.concatenate([i1, i2 + len(v1)]))
+    # broken index -> the reference's error text
+    with open(tmp_path / "bad.tris", "wb") as f:
+        f.write(np.int32(3).tobytes() + v2.tobytes() + np.int32(1).tobytes() + np.array([[0, 1, 3]], np.int32).tobytes())
+    with pytest.raises(Exception, match="broken triangle model"):
+        R.load_triangle_meshes(str(tmp_path / "bad.tris"))
+    with pytest.raises(Exception, match="cannot open file"):
+        R.load_triangle_meshes(str(tmp_path / "missing.tris"))

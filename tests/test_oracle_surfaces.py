@@ -129,3 +129,28 @@ def test_surface_cuts_the_volume(orc):
     _, _, st1 = sc.render(fd.to_orc(orc))
     # space skipping is off with a plane, so compare samples per segment budget: fewer DVR samples
     assert 0 < st1["samples"] < st0["samples"] * 0.9
+
+
+def test_triangle_mesh_shading(orc):
+    """closest hit SurfaceBVH (:420-433) + primary-ray shading (:1604-1651): a mesh pixel shows
+    ambient .2 + .8 |d.N| with the geometric normal; a sphere's silhouette is a disc"""
+    cells, fields, dom = scenes.small_scene("nb32")
+    sc, _ = _scene(orc, cells, fields)
+    fd = _frame(dom)
+    fd.mesh = scenes.uv_sphere([dom / 2] * 3, dom / 4, 48, 24)
+    acc, _, _ = sc.render(fd.to_orc(orc))
+    hit = acc[..., 0] > 0
+    assert 0.03 * hit.size < hit.sum() < 0.5 * hit.size
+    assert np.allclose(acc[..., 0][hit], acc[..., 1][hit]) and np.allclose(acc[..., 0][hit], acc[..., 2][hit])
+    assert acc[..., 0][hit].min() >= 0.2 - 1e-6 and acc[..., 0].max() <= 1.0 + 1e-6
+    ys, xs = np.nonzero(hit)
+    assert abs((xs.max() - xs.min()) - (ys.max() - ys.min())) <= 3      # round silhouette
+    cy, cx = int(round(ys.mean())), int(round(xs.mean()))
+    assert acc[cy, cx, 0] > 0.9                                        # facing the camera: |d.N| ~ 1
+    # the mesh hides the streamlines behind it and cuts the volume (ray.tmax = t_hit)
+    fd2 = _frame(dom, transparent=False)
+    fd2.opacity_scale = 0.05
+    _, _, st0 = sc.render(fd2.to_orc(orc))
+    fd2.mesh = fd.mesh
+    _, _, st1 = sc.render(fd2.to_orc(orc))
+    assert 0 < st1["samples"] < st0["samples"]
