@@ -115,7 +115,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.aoEnabled = r->fs.ao.enabled; P.aoLength = r->fs.ao.length;
   memcpy(P.worldLo, r->worldLo, 12); memcpy(P.worldHi, r->worldHi, 12);
   P.meshNodes = r->d_meshNodes; P.meshTris = r->d_meshTris; P.numMeshTris = r->numMeshTris;
-  P.anySurf = (P.anyIso || anyContour || P.traces || P.numMeshTris > 0) ? 1 : 0;
+  P.anySurf = (anyContour || P.traces || P.numMeshTris > 0 || (P.aoEnabled && P.anyIso)) ? 2 : P.anyIso ? 1 : 0;
   P.stats = nullptr;
   P.longQueue = r->d_longQueue; P.longCount = r->d_longCount; P.sampleBudget = r->sampleBudget;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;

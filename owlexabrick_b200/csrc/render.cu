@@ -635,16 +635,20 @@ __device__ __noinline__ void traceMesh(const RenderParams &P, float3 o, float3 d
   }
 }
 
-template <bool STATS, bool DUAL>
+// ALL = false: iso-surfaces only (the instantiation the iso + DVR workload C4 runs; meshes, planes,
+// cones and AO cost it registers and 10 % of its frame time when compiled in)
+template <bool STATS, bool DUAL, bool ALL>
 __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
                                               float3 o, float3 d, float tmin, float tmax, bool withContourPlanes, SurfHit &prd, RayStats &rs)
 {
   prd.prim = PRIM_NONE; prd.t = tmax; prd.Ng = f3(0, 0, 0); prd.base = f3(0, 0, 0); prd.ambient = 0.f;
-  traceMesh(P, o, d, tmin, tmax, prd);
-  if (withContourPlanes) traceContourPlanes<STATS, DUAL>(P, xfTables, o, d, prd, rs);
-  if (P.traces) {
-    SurfHit sl; traceCones(P, o, d, tmin, tmax, sl);
-    if (sl.prim == PRIM_STREAMLINE && sl.t < prd.t) prd = sl;
+  if (ALL) {
+    traceMesh(P, o, d, tmin, tmax, prd);
+    if (withContourPlanes) traceContourPlanes<STATS, DUAL>(P, xfTables, o, d, prd, rs);
+    if (P.traces) {
+      SurfHit sl; traceCones(P, o, d, tmin, tmax, sl);
+      if (sl.prim == PRIM_STREAMLINE && sl.t < prd.t) prd = sl;
+    }
   }
   if (P.anyIso) {
     SurfHit iso; traceIsoRay<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, iso, rs);
@@ -681,8 +685,8 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
 static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
-// SURF: the surface pass (iso-surfaces, contour planes, streamline cones, AO) is compiled in only
-// when one of them is enabled (RenderParams::anySurf); the plain
+// SURF: the surface pass is compiled in only when a surface is enabled (RenderParams::anySurf):
+// 1 = implicit iso-surfaces only, 2 = + triangle meshes, contour planes, streamline cones, AO; the plain
 // DVR instantiation is less than half the code, which matters because every CTA runs through
 // the kernel once, front to back (instruction fetch, not data, is what a lone CTA waits for).
 // Image-tile mode: tiles are dealt in blocks of numRanks consecutive tiles and the deal rotates by
@@ -695,7 +699,7 @@ __host__ __device__ inline int numOwnedTiles(int numTiles, int rank, int numRank
   return full + ((rank + full) % numRanks < rem ? 1 : 0);
 }
 
-template <bool GRAD, bool STATS, bool DUAL, bool SURF>
+template <bool GRAD, bool STATS, bool DUAL, int SURF>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
@@ -768,22 +772,22 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     float surfT = tmax;
     if (SURF && P.anySurf) {
       SurfHit sh;
-      traceSurfaces<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, true, sh, rs);
+      traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, true, sh, rs);
       surfT = sh.t;
       if (sh.prim != PRIM_NONE) {
         const bool shade = sh.prim >= 0 || sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
         if (shade && len3(sh.Ng) > 0.f) {
-          const int aoSamples = P.aoEnabled ? 2 : 0;
+          const int aoSamples = (SURF == 2 && P.aoEnabled) ? 2 : 0;
           const float3 isect = rayAt(o, d, sh.t);
           int hitCnt = 0;
           for (int i = 0; i < aoSamples; i++) {
             const float u1 = rnd.next(), u2 = rnd.next();
             const float3 adir = surf::aoDirection(sh.Ng, u1, u2);
             SurfHit ah;                                       // ST_ALL_SURFACES & ~ST_CONTOUR_PLANES (:1638-1640)
-            traceSurfaces<STATS, DUAL>(P, xfTables, stack, isoT, isoV, isect, adir, 1e-4f, P.aoLength, false, ah, rs);
+            traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, isect, adir, 1e-4f, P.aoLength, false, ah, rs);
             if (ah.prim != PRIM_NONE) hitCnt++;
           }
-          const float shadow = P.aoEnabled ? (float)hitCnt / (float)aoSamples : 0.f;
+          const float shadow = aoSamples ? (float)hitCnt / (float)aoSamples : 0.f;
           const float k = fabsf(dot3(d, sh.Ng)) * (1.f - shadow);
           bg = f3(sh.ambient + sh.base.x * k, sh.ambient + sh.base.y * k, sh.ambient + sh.base.z * k);
         } else bg = sh.base;
@@ -1035,10 +1039,12 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   // limit only when it has to grow
 #define LAUNCH(G, S_, D_)                                                                                   \
   { static size_t capF = 0, capL = 0;                                                                       \
-    if (smemBytes > capF) { cudaFuncSetAttribute(k_renderFrame<G, S_, D_, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
-                            cudaFuncSetAttribute(k_renderFrame<G, S_, D_, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capF = smemBytes; } \
-    if (P.anySurf) k_renderFrame<G, S_, D_, true><<<grid, block, smemBytes, s>>>(P);                       \
-    else k_renderFrame<G, S_, D_, false><<<grid, block, smemBytes, s>>>(P);                               \
+    if (smemBytes > capF) { cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
+                            cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
+                            cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capF = smemBytes; } \
+    if (P.anySurf == 2) k_renderFrame<G, S_, D_, 2><<<grid, block, smemBytes, s>>>(P);                      \
+    else if (P.anySurf) k_renderFrame<G, S_, D_, 1><<<grid, block, smemBytes, s>>>(P);                      \
+    else k_renderFrame<G, S_, D_, 0><<<grid, block, smemBytes, s>>>(P);                                     \
     if (twoPass) { if (smemLong > capL) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); capL = smemLong; } \
                    k_renderLong<G, S_, D_><<<gridLong, block, smemLong, s>>>(P); } }
 #define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }

@@ -49,7 +49,7 @@ struct RenderParams {
   // {lo.xyz, a}{hi.xyz, b}: b == 0 inner node with children a, a+1; b > 0 leaf of triangles [a, a+b);
   // triangles in BVH order, 9 floats each (A, B, C), world space
   const float4 *meshNodes; const float *meshTris; int numMeshTris;
-  int anySurf;                         // a mesh, iso-surface, contour plane or visible streamline: run the surface pass
+  int anySurf;                         // surface pass: 0 none, 1 iso-surfaces only, 2 + meshes / contour planes / visible streamlines / AO
   unsigned long long *stats;           // 4 counters (ExaStats) or null
   LongRay *longQueue; int *longCount;  // long-ray queue (capacity width*height) and {count, head}; null: off
   int sampleBudget;                    // samples a ray may take in k_renderFrame before it is handed over
