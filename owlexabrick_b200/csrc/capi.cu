@@ -52,7 +52,9 @@ struct exa_renderer {
   float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
   float *d_traces = nullptr; size_t tracesCap = 0;
   float4 *d_meshNodes = nullptr; float *d_meshTris = nullptr; int numMeshTris = 0;          // triangle-mesh BVH (set_triangle_meshes)
-  float *d_traceBounds = nullptr; int traceBoundsCap = 0; bool traceBoundsDirty = true;   // one box per trace (k_traceBounds)
+  float *d_traceBounds = nullptr; int traceBoundsCap = 0; bool traceBoundsDirty = true;   // one box per trace (k_traceBounds) -> grid bounds
+  int *d_coneStart = nullptr, *d_coneCursor = nullptr, *d_coneList = nullptr; size_t coneListCap = 0; bool coneGridValid = false;
+  float coneLo[3] = {0, 0, 0}, coneCell[3] = {1, 1, 1};                                  // uniform grid over the visible cones (buildConeGrid)
   unsigned long long *d_stats = nullptr;
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
   LongRay *d_longQueue = nullptr; int *d_longCount = nullptr; int sampleBudget = 0;       // long-ray hand-over to k_renderLong; 0 = single pass (default: measured faster on C2)
@@ -101,9 +103,9 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
   // copy of the time step stops at numTimesteps (OptixRenderer.cpp:481-484)
-  P.traces = nullptr; P.traceBounds = nullptr; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
+  P.traces = nullptr; P.coneStart = nullptr; P.coneList = nullptr; P.coneG = 0; P.numTraces = 0; P.numTimesteps = 0; P.currentTimestep = 0;
   if (r->d_traces && r->numTraces > 0 && std::min(r->timestep, r->numTimesteps) >= 2) {
-    P.traces = r->d_traces; P.traceBounds = r->d_traceBounds; P.numTraces = r->numTraces; P.numTimesteps = r->numTimesteps;
+    P.traces = r->d_traces; P.numTraces = r->numTraces; P.numTimesteps = r->numTimesteps;
     P.currentTimestep = std::min(r->timestep, r->numTimesteps);
   }
   bool anyContour = false;
@@ -321,7 +323,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
-  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
+  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
   delete r;
 }
 

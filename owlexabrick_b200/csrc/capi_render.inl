@@ -15,6 +15,63 @@ static int refreshMasks(exa_renderer *r, RenderParams &P)
   return EXA_OK;
 }
 
+// Streamline cones: (re)build the uniform grid the frame kernel's traceCones walks.  Runs when the
+// traces changed (reset / advance), i.e. where the reference rebuilds its streamline BVH
+// (OptixRenderer.cpp:539-543).  Per-trace boxes (k_traceBounds) give the grid bounds; k_coneGrid
+// counts, the host turns counts into cell starts (1 MB each way), k_coneGrid fills.
+static const int CONE_GRID = 64;
+static int buildConeGrid(exa_renderer *r, const RenderParams &P)
+{
+  const size_t nc = (size_t)CONE_GRID * CONE_GRID * CONE_GRID;
+  r->coneGridValid = false; r->traceBoundsDirty = false;
+  if (r->numTraces > r->traceBoundsCap) {
+    CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_traceBounds); r->d_traceBounds = nullptr;
+    CKR(cudaMalloc(&r->d_traceBounds, (size_t)r->numTraces * 24)); r->traceBoundsCap = r->numTraces;
+  }
+  int k = launchTraceBounds(P.traces, P.numTraces, P.numTimesteps, P.currentTimestep, r->d_traceBounds, r->stream);
+  if (k < 0) { setError(std::string("trace bounds kernel failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  std::vector<float> hb((size_t)r->numTraces * 6);
+  CKR(cudaMemcpyAsync(hb.data(), r->d_traceBounds, hb.size() * 4, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  float lo[3] = {3e38f, 3e38f, 3e38f}, hi[3] = {-3e38f, -3e38f, -3e38f}; bool any = false;
+  for (int i = 0; i < r->numTraces; i++) {
+    const float *b = hb.data() + 6 * (size_t)i;
+    if (!(b[0] <= b[3])) continue;
+    any = true;
+    for (int d = 0; d < 3; d++) { lo[d] = std::min(lo[d], b[d]); hi[d] = std::max(hi[d], b[3 + d]); }
+  }
+  if (!any) return EXA_OK;
+  float inv[3];
+  for (int d = 0; d < 3; d++) {
+    const float pad = 1e-3f * (hi[d] - lo[d]) + 1e-3f;
+    lo[d] -= pad; hi[d] += pad;
+    r->coneLo[d] = lo[d]; r->coneCell[d] = (hi[d] - lo[d]) / CONE_GRID; inv[d] = 1.f / r->coneCell[d];
+  }
+  if (!r->d_coneStart) { CKR(cudaMalloc(&r->d_coneStart, (nc + 1) * sizeof(int))); CKR(cudaMalloc(&r->d_coneCursor, nc * sizeof(int))); }
+  CKR(cudaMemsetAsync(r->d_coneCursor, 0, nc * sizeof(int), r->stream));
+  k = launchConeGrid(P.traces, P.numTraces, P.numTimesteps, P.currentTimestep, CONE_GRID, lo, inv, r->d_coneCursor, nullptr, 0, r->stream);
+  if (k < 0) { setError(std::string("cone grid kernel failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  std::vector<int> h(nc + 1);
+  CKR(cudaMemcpyAsync(h.data(), r->d_coneCursor, nc * sizeof(int), cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  size_t total = 0;
+  for (size_t c = 0; c < nc; c++) { const int n = h[c]; h[c] = (int)total; total += (size_t)n; }
+  h[nc] = (int)total;
+  if (total == 0) return EXA_OK;
+  if (total > (size_t)0x7fffffff) { setError("cone grid: too many entries"); return EXA_ERR_LIMIT; }
+  if (total > r->coneListCap) { cudaFree(r->d_coneList); r->d_coneList = nullptr; CKR(cudaMalloc(&r->d_coneList, total * sizeof(int))); r->coneListCap = total; }
+  CKR(cudaMemcpyAsync(r->d_coneStart, h.data(), (nc + 1) * sizeof(int), cudaMemcpyHostToDevice, r->stream));
+  CKR(cudaMemcpyAsync(r->d_coneCursor, h.data(), nc * sizeof(int), cudaMemcpyHostToDevice, r->stream));
+  k = launchConeGrid(P.traces, P.numTraces, P.numTimesteps, P.currentTimestep, CONE_GRID, lo, inv, r->d_coneCursor, r->d_coneList, 1, r->stream);
+  if (k < 0) { setError(std::string("cone grid kernel failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  CKR(cudaStreamSynchronize(r->stream));                     // h[] is pageable and goes out of scope
+  r->coneGridValid = true;
+  return EXA_OK;
+}
+
 static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool sync)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
@@ -23,17 +80,12 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
   RenderParams P; fillParams(r, P);
   int rc = refreshMasks(r, P); if (rc) return rc;
   P.partialOut = partialOut;
-  if (P.traces) {                                            // boxes around the visible cones of every trace
-    if (r->numTraces > r->traceBoundsCap) {
-      CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_traceBounds); r->d_traceBounds = nullptr;
-      CKR(cudaMalloc(&r->d_traceBounds, (size_t)r->numTraces * 24)); r->traceBoundsCap = r->numTraces; r->traceBoundsDirty = true;
-    }
-    if (r->traceBoundsDirty) {
-      const int k = launchTraceBounds(P.traces, P.numTraces, P.numTimesteps, P.currentTimestep, r->d_traceBounds, r->stream);
-      if (k < 0) { setError(std::string("trace bounds kernel failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
-      r->launches += k; r->traceBoundsDirty = false;
-    }
-    P.traceBounds = r->d_traceBounds;
+  if (P.traces) {                                            // uniform grid over the visible cones
+    if (r->traceBoundsDirty) { rc = buildConeGrid(r, P); if (rc) return rc; }
+    if (r->coneGridValid) {
+      P.coneStart = r->d_coneStart; P.coneList = r->d_coneList; P.coneG = CONE_GRID;
+      for (int d = 0; d < 3; d++) { P.coneLo[d] = r->coneLo[d]; P.coneCell[d] = r->coneCell[d]; P.coneInvCell[d] = 1.f / r->coneCell[d]; }
+    } else P.traces = nullptr;                               // every visible segment has a dead end
   }
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)

@@ -19,6 +19,7 @@
 //   k_over / k_finish  sort-last compositing helpers.
 #include "render.cuh"
 #include "surfaces.cuh"
+#include <algorithm>
 #include <cstdio>
 
 namespace exa {
@@ -554,41 +555,49 @@ __device__ void traceContourPlanes(const RenderParams &P, const float4 *xfTables
 
 // Streamline closest hit (bounds :532-570, intersect :503-530): segment k of a trace is visible
 // while k < currentTimestep-1 and both ends are alive; radius 2 at both ends.  The reference
-// rebuilds an OptiX BVH over all segments after every tracer step; here k_traceBounds keeps one
-// box per trace (1000 boxes for the default tracer) and a ray tests the segments of the traces
-// whose box it hits.
+// rebuilds an OptiX BVH over all segments after every tracer step; here the segments are binned
+// into a uniform grid (k_coneGrid, same moment) and a ray walks the grid cells it crosses front to
+// back (3D DDA), testing the segments listed in each cell, and stops at the first cell whose exit
+// lies behind the closest hit found.  Ties go to the lower segment id (the order of a serial loop).
 __device__ __noinline__ void traceCones(const RenderParams &P, float3 o, float3 d, float tmin, float tmax, SurfHit &sl)
 {
   sl.prim = PRIM_NONE; sl.t = 2e10f; sl.Ng = f3(0, 0, 0); sl.base = f3(.8f, .8f, .8f); sl.ambient = 0.f;
-  if (!P.traces || !P.traceBounds) return;
-  const int nSeg = min(P.numTimesteps - 1, P.currentTimestep - 1);
-  if (nSeg <= 0) return;
-  float best = tmax;
-  const float3 invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
-  for (int i = 0; i < P.numTraces; i++) {
-    const float *b = P.traceBounds + 6 * (size_t)i;
-    const float lx = __ldg(b), ly = __ldg(b + 1), lz = __ldg(b + 2), hx = __ldg(b + 3), hy = __ldg(b + 4), hz = __ldg(b + 5);
-    if (!(lx <= hx)) continue;                                 // no visible cone on this trace
-    // slab test against the box grown by a little (culling only; NaNs from 0*inf drop out of fmin/fmax)
-    const float px = 1e-3f * (hx - lx + 1.f), py = 1e-3f * (hy - ly + 1.f), pz = 1e-3f * (hz - lz + 1.f);
-    const float ax = (lx - px - o.x) * invd.x, bx = (hx + px - o.x) * invd.x;
-    const float ay = (ly - py - o.y) * invd.y, by = (hy + py - o.y) * invd.y;
-    const float az = (lz - pz - o.z) * invd.z, bz = (hz + pz - o.z) * invd.z;
-    const float t0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), tmin));
-    const float t1 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), best));
-    if (t0 > t1) continue;
-    const float *tr = P.traces + 3 * (size_t)i * P.numTimesteps;
-    float3 pa = f3(__ldg(tr), __ldg(tr + 1), __ldg(tr + 2));
-    for (int k = 0; k < nSeg; k++) {
-      const float3 pb = f3(__ldg(tr + 3 * (k + 1)), __ldg(tr + 3 * (k + 1) + 1), __ldg(tr + 3 * (k + 1) + 2));
-      if (pa.x < 2e10f && pb.x < 2e10f) {
-        float t; float3 n;
-        if (surf::roundedCone(pa, pb, 2.f, 2.f, o, d, t, n) && t > tmin && t < best) {
-          best = t; sl.prim = PRIM_STREAMLINE; sl.t = t; sl.Ng = normalize3(n);
-        }
+  if (!P.traces || !P.coneStart) return;
+  const int G = P.coneG;
+  const float glo[3] = {P.coneLo[0], P.coneLo[1], P.coneLo[2]};
+  const float ghi[3] = {glo[0] + P.coneCell[0] * G, glo[1] + P.coneCell[1] * G, glo[2] + P.coneCell[2] * G};
+  float t0, t1;
+  if (!boxTest(o, d, tmin, tmax, glo, ghi, t0, t1)) return;
+  const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+  int cell[3], step[3]; float tNext[3], tDelta[3];
+  const float tStart = t0 + 1e-5f * fabsf(t0);
+#pragma unroll
+  for (int a = 0; a < 3; a++) {
+    const float pa = oo[a] + tStart * dd[a];
+    cell[a] = min(G - 1, max(0, (int)floorf((pa - glo[a]) * P.coneInvCell[a])));
+    if (dd[a] > 0.f) { step[a] = 1; tNext[a] = (glo[a] + (cell[a] + 1) * P.coneCell[a] - oo[a]) / dd[a]; tDelta[a] = P.coneCell[a] / dd[a]; }
+    else if (dd[a] < 0.f) { step[a] = -1; tNext[a] = (glo[a] + cell[a] * P.coneCell[a] - oo[a]) / dd[a]; tDelta[a] = -P.coneCell[a] / dd[a]; }
+    else { step[a] = 0; tNext[a] = 3e38f; tDelta[a] = 3e38f; }
+  }
+  float best = tmax; int bestId = 0x7fffffff;
+  for (;;) {
+    const int c = cell[0] + G * (cell[1] + G * cell[2]);
+    const int e0 = __ldg(P.coneStart + c), e1 = __ldg(P.coneStart + c + 1);
+    for (int e = e0; e < e1; e++) {
+      const int id = __ldg(P.coneList + e);
+      const float *q = P.traces + 3 * (size_t)id;
+      const float3 pa = f3(__ldg(q), __ldg(q + 1), __ldg(q + 2)), pb = f3(__ldg(q + 3), __ldg(q + 4), __ldg(q + 5));
+      float t; float3 n;
+      if (surf::roundedCone(pa, pb, 2.f, 2.f, o, d, t, n) && t > tmin && (t < best || (t == best && id < bestId))) {
+        best = t; bestId = id; sl.prim = PRIM_STREAMLINE; sl.t = t; sl.Ng = normalize3(n);
       }
-      pa = pb;
     }
+    const int a = tNext[0] <= tNext[1] ? (tNext[0] <= tNext[2] ? 0 : 2) : (tNext[1] <= tNext[2] ? 1 : 2);
+    const float tExit = tNext[a];
+    if (best <= tExit || tExit > t1) break;                    // the hit lies in a cell already visited / ray leaves the grid or its range
+    cell[a] += step[a];
+    if (cell[a] < 0 || cell[a] >= G) break;
+    tNext[a] += tDelta[a];
   }
 }
 
@@ -1200,6 +1209,46 @@ int launchTraceBounds(const float *traces, int numTraces, int numTimesteps, int 
 {
   if (numTraces <= 0) return 0;
   k_traceBounds<<<(numTraces + 127) / 128, 128, 0, s>>>(traces, numTraces, numTimesteps, currentTimestep, bounds);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// Bin the visible cone segments into the uniform grid: one thread per (trace, segment).  fill = 0:
+// counts[cell] += 1 for every cell the segment's box (end points -+ radius 2, grown a little)
+// overlaps; fill = 1: list[cursor[cell]++] = segment id.  The host turns the counts into cell starts.
+__global__ void k_coneGrid(const float *__restrict__ traces, int numTraces, int numTimesteps, int currentTimestep, int G,
+                           float lox, float loy, float loz, float icx, float icy, float icz, int *countsOrCursor, int *list, int fill)
+{
+  const int nSeg = min(numTimesteps - 1, currentTimestep - 1);
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (nSeg <= 0 || g >= numTraces * nSeg) return;
+  const int i = g / nSeg, k = g % nSeg;
+  const int id = i * numTimesteps + k;
+  const float *a = traces + 3 * (size_t)id, *b = a + 3;
+  if (!(a[0] < 2e10f && b[0] < 2e10f)) return;
+  const float lo[3] = {lox, loy, loz}, ic[3] = {icx, icy, icz};
+  int c0[3], c1[3];
+  for (int d = 0; d < 3; d++) {
+    const float pad = 2.f + 1e-3f * (2.f + fabsf(a[d]) * 1e-3f) + 0.01f / ic[d];
+    c0[d] = min(G - 1, max(0, (int)floorf((fminf(a[d], b[d]) - pad - lo[d]) * ic[d])));
+    c1[d] = min(G - 1, max(0, (int)floorf((fmaxf(a[d], b[d]) + pad - lo[d]) * ic[d])));
+  }
+  for (int z = c0[2]; z <= c1[2]; z++)
+    for (int y = c0[1]; y <= c1[1]; y++)
+      for (int x = c0[0]; x <= c1[0]; x++) {
+        const int c = x + G * (y + G * z);
+        const int slot = atomicAdd(countsOrCursor + c, 1);
+        if (fill) list[slot] = id;
+      }
+}
+
+int launchConeGrid(const float *traces, int numTraces, int numTimesteps, int currentTimestep, int G, const float lo[3], const float invCell[3],
+                   int *countsOrCursor, int *list, int fill, cudaStream_t s)
+{
+  const int nSeg = std::min(numTimesteps - 1, currentTimestep - 1);
+  if (numTraces <= 0 || nSeg <= 0) return 0;
+  const long long n = (long long)numTraces * nSeg;
+  k_coneGrid<<<(unsigned)((n + 127) / 128), 128, 0, s>>>(traces, numTraces, numTimesteps, currentTimestep, G, lo[0], lo[1], lo[2],
+                                                        invCell[0], invCell[1], invCell[2], countsOrCursor, list, fill);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

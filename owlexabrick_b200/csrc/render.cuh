@@ -40,7 +40,9 @@ struct RenderParams {
   float4 *partialOut;                  // != null: write premultiplied partial, skip bg/accum/pack
   int tileMode, rank, numRanks;        // image-tile partition
   const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones (null / 0: none visible)
-  const float *traceBounds;            // per trace {lo[3], hi[3]} around its visible cones (k_traceBounds); lo > hi: none
+  // uniform grid over the visible cones (rebuilt after a tracer step, where the reference rebuilds an
+  // OptiX BVH): cell c lists segment ids coneList[coneStart[c] .. coneStart[c+1]); id = trace * numTimesteps + k
+  const int *coneStart; const int *coneList; int coneG; float coneLo[3], coneCell[3], coneInvCell[3];
   // contour planes (FrameState.h:45-52), ambient occlusion (:60-63), world bounds (LaunchParams.h:37)
   int cpEnabled[EXA_MAX_CONTOUR_PLANES]; float cpNormal[EXA_MAX_CONTOUR_PLANES][3]; float cpOffset[EXA_MAX_CONTOUR_PLANES]; int cpChannel[EXA_MAX_CONTOUR_PLANES];
   int aoEnabled; float aoLength;
@@ -80,6 +82,9 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s);
 int launchSamplePoints(const SampleParams &P, cudaStream_t s);
 int launchTrace(const TraceParams &P, cudaStream_t s);
 int launchTraceBounds(const float *traces, int numTraces, int numTimesteps, int currentTimestep, float *bounds, cudaStream_t s);
+// cone grid: fill = 0 counts the segments per cell (counts[] += 1), fill = 1 writes their ids at cursor[cell]++
+int launchConeGrid(const float *traces, int numTraces, int numTimesteps, int currentTimestep, int G, const float lo[3], const float invCell[3],
+                   int *countsOrCursor, int *list, int fill, cudaStream_t s);
 int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping,
                          const uint8_t *nodeInPartition, uint8_t *volActive, uint8_t *isoActive /* = volActive + numNodes */, cudaStream_t s);
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
