@@ -152,6 +152,12 @@ int exa_bricks_get_bounds(const exa_bricks_t *b, float lower[3], float upper[3])
 size_t exa_bricks_kd_count(const exa_bricks_t *b);           /* 0 unless built here */
 const ExaKdTreeNode *exa_bricks_kd_nodes(const exa_bricks_t *b);
 
+/* exaRawToCells (tools/fromVolume/raw2cells.cpp): structured volume (x fastest) -> AMR cells +
+ * scalars in the order the tool writes them; format = voxel type.  Both arrays malloc'd (exa_free). */
+enum { EXA_RAW_BYTE = 0, EXA_RAW_FLOAT = 1, EXA_RAW_DOUBLE = 2 };
+int exa_raw_to_cells(const void *voxels, int format, int nx, int ny, int nz, float threshold,
+                     int maxLevel, int refinement, int32_t **cells, float **scalars, size_t *numCells);
+
 /* TriangleMesh::load (exa/TriangleMesh.cpp:21-68): file = repeated {int32 numVerts; vec3f[];
  * int32 numTris; vec3i[]}.  All meshes of the file come back concatenated (indices rebased);
  * both arrays are malloc'd (exa_free).  Errors as the reference: "cannot open file",

@@ -146,6 +146,76 @@ int exa_bricks_get_bounds(const exa_bricks_t *b, float lower[3], float upper[3])
 }
 
 // ---------------------------------------------------------------------------------------
+// exaRawToCells (tools/fromVolume/raw2cells.cpp:140-283): structured volume -> AMR cells.  Root
+// cells of width refinement^maxLevel tile the volume (x fastest); a cell whose value range is
+// <= threshold becomes one coarse cell carrying the average, otherwise its refinement^3 children
+// are visited (x fastest), down to single voxels.  Arithmetic kept as written: the sum of
+// `average` accumulates in the voxel type (bytes wrap), is divided by the UNCLIPPED cell volume
+// as float and converted back to the voxel type; level = int(log2f(cellWidth)).
+extern "C++" {
+namespace {
+template <typename T> struct RawVolume {
+  const T *elt; int nx, ny, nz;
+  T at(int x, int y, int z) const { return elt[x + (size_t)nx * (y + (size_t)ny * (size_t)z)]; }
+};
+template <typename T>
+void rawBuildCell(const RawVolume<T> &v, int lx, int ly, int lz, int level, float threshold, int refinement,
+                  std::vector<int32_t> &cells, std::vector<float> &scalars)
+{
+  if (lx >= v.nx || ly >= v.ny || lz >= v.nz) return;
+  if (level == 0) {
+    cells.insert(cells.end(), {lx, ly, lz, 0}); scalars.push_back((float)v.at(lx, ly, lz));
+    return;
+  }
+  int childWidth = 1;
+  for (int i = 0; i < level - 1; i++) childWidth *= refinement;
+  const int cellWidth = childWidth * refinement;
+  const int ux = std::min(v.nx, lx + cellWidth), uy = std::min(v.ny, ly + cellWidth), uz = std::min(v.nz, lz + cellWidth);
+  T lo = v.at(lx, ly, lz), hi = lo;
+  for (int z = lz; z < uz; z++) for (int y = ly; y < uy; y++) for (int x = lx; x < ux; x++) { const T t = v.at(x, y, z); lo = std::min(lo, t); hi = std::max(hi, t); }
+  if ((hi - lo) <= threshold) {
+    T sum = 0.f;
+    for (int z = lz; z < uz; z++) for (int y = ly; y < uy; y++) for (int x = lx; x < ux; x++) sum += v.at(x, y, z);
+    const T avg = sum / (float)(cellWidth * cellWidth * cellWidth);
+    cells.insert(cells.end(), {lx, ly, lz, int(log2f((float)cellWidth))}); scalars.push_back((float)avg);
+    return;
+  }
+  for (int iz = 0; iz < refinement; iz++) for (int iy = 0; iy < refinement; iy++) for (int ix = 0; ix < refinement; ix++)
+    rawBuildCell(v, lx + ix * childWidth, ly + iy * childWidth, lz + iz * childWidth, level - 1, threshold, refinement, cells, scalars);
+}
+template <typename T>
+void rawMakeCells(const void *voxels, int nx, int ny, int nz, float threshold, int maxLevel, int refinement,
+                  std::vector<int32_t> &cells, std::vector<float> &scalars)
+{
+  RawVolume<T> v{(const T *)voxels, nx, ny, nz};
+  int root = 1;
+  for (int i = 0; i < maxLevel; i++) root *= refinement;
+  const int rx = (nx + root - 1) / root, ry = (ny + root - 1) / root, rz = (nz + root - 1) / root;
+  for (int z = 0; z < rz; z++) for (int y = 0; y < ry; y++) for (int x = 0; x < rx; x++)
+    rawBuildCell(v, x * root, y * root, z * root, maxLevel, threshold, refinement, cells, scalars);
+}
+}
+} // extern "C++"
+
+int exa_raw_to_cells(const void *voxels, int format, int nx, int ny, int nz, float threshold, int maxLevel, int refinement,
+                     int32_t **cells, float **scalars, size_t *numCells)
+{
+  if (!voxels || !cells || !scalars || !numCells || nx <= 0 || ny <= 0 || nz <= 0 || maxLevel < 0 || maxLevel > 20 || refinement < 2)
+  { setError("exa_raw_to_cells: bad argument"); return EXA_ERR_INVALID; }
+  std::vector<int32_t> c; std::vector<float> s;
+  if (format == EXA_RAW_BYTE) rawMakeCells<uint8_t>(voxels, nx, ny, nz, threshold, maxLevel, refinement, c, s);
+  else if (format == EXA_RAW_FLOAT) rawMakeCells<float>(voxels, nx, ny, nz, threshold, maxLevel, refinement, c, s);
+  else if (format == EXA_RAW_DOUBLE) rawMakeCells<double>(voxels, nx, ny, nz, threshold, maxLevel, refinement, c, s);
+  else { setError("unknown format!?"); return EXA_ERR_INVALID; }             // raw2cells.cpp:268
+  int32_t *oc = (int32_t *)malloc(std::max<size_t>(1, c.size()) * 4);
+  float *os = (float *)malloc(std::max<size_t>(1, s.size()) * 4);
+  if (!oc || !os) { free(oc); free(os); setError("out of host memory"); return EXA_ERR_LIMIT; }
+  memcpy(oc, c.data(), c.size() * 4); memcpy(os, s.data(), s.size() * 4);
+  *cells = oc; *scalars = os; *numCells = s.size();
+  return EXA_OK;
+}
+
+// ---------------------------------------------------------------------------------------
 // TriangleMesh::load (exa/TriangleMesh.cpp:21-68): a file is a sequence of meshes, each
 // {int32 numVerts; vec3f[numVerts]; int32 numTris; vec3i[numTris]}; here all meshes of the file are
 // returned as ONE vertex / index array (indices rebased), which is what the renderer consumes.

@@ -188,6 +188,25 @@ def simple_camera(pos, at, up, fovy_deg, width, height):
     return pos, lower_left, (horizontal / f(width)).astype(f), (vertical / f(height)).astype(f)
 
 
+def raw_to_cells(volume, threshold, max_level, refinement=2):
+    """exaRawToCells (tools/fromVolume/raw2cells.cpp): volume[z, y, x] of uint8 / float32 / float64 ->
+    (cells int32[n,4], scalars float32[n]) in the tool's output order"""
+    vol = np.ascontiguousarray(volume)
+    fmt = {np.dtype(np.uint8): 0, np.dtype(np.float32): 1, np.dtype(np.float64): 2}.get(vol.dtype)
+    if fmt is None or vol.ndim != 3:
+        raise RuntimeError("unknown format!?")
+    nz, ny, nx = vol.shape
+    c, s, n = C.c_void_p(), C.c_void_p(), C.c_size_t()
+    check(lib.exa_raw_to_cells(_p(vol), fmt, nx, ny, nz, float(threshold), int(max_level), int(refinement), C.byref(c), C.byref(s), C.byref(n)))
+    try:
+        cells = np.frombuffer(C.string_at(c, n.value * 16), np.int32).reshape(-1, 4).copy()
+        scal = np.frombuffer(C.string_at(s, n.value * 4), np.float32).copy()
+    finally:
+        lib.exa_free(c)
+        lib.exa_free(s)
+    return cells, scal
+
+
 def load_triangle_meshes(file_name):
     """TriangleMesh::load (exa/TriangleMesh.cpp:21-68) -> (vertices float32[n,3], indices int32[m,3]), all meshes
     of the file concatenated"""

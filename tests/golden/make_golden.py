@@ -60,6 +60,38 @@ def main():
                                 max_leaf_width=mlw)
         print(name, hashes[name])
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
+    raw2cells_golden()
+
+
+def raw2cells_cases():
+    """small structured volumes for exaRawToCells (tools/fromVolume/raw2cells.cpp): (format, volume[z,y,x], threshold, maxLevel, refinement)"""
+    def smooth(shape, bump):
+        z, y, x = np.meshgrid(*[np.arange(n) for n in shape], indexing="ij")
+        v = 100 + 40 * np.sin(x / 9.0) * np.cos(y / 11.0) + 20 * np.sin(z / 6.0)
+        if bump:
+            v[2:4, 3:6, 1:5] += 90
+        return np.clip(v, 0, 255)
+    yield "byte", smooth((13, 17, 20), True).astype(np.uint8), 8.0, 3, 2
+    yield "byte", smooth((16, 16, 32), False).astype(np.uint8), 200.0, 4, 2      # whole root cells collapse: byte sums wrap
+    yield "float", smooth((9, 16, 11), True).astype(np.float32), 5.5, 2, 2
+    yield "double", smooth((8, 12, 8), False).astype(np.float64), 3.0, 3, 2
+    yield "byte", smooth((10, 9, 27), True).astype(np.uint8), 20.0, 2, 3         # refinement 3: level = int(log2f(3^l))
+
+
+def raw2cells_golden():
+    import subprocess
+    out = {}
+    for i, (fmt, vol, thr, ml, ref) in enumerate(raw2cells_cases()):
+        with tempfile.TemporaryDirectory() as d:
+            vol.tofile(os.path.join(d, "v.raw"))
+            nz, ny, nx = vol.shape
+            cmd = [os.path.join(orc.REF_DIR, "exaRawToCells"), str(nx), str(ny), str(nz), fmt, os.path.join(d, "v.raw"),
+                   os.path.join(d, "out"), str(thr), str(ml)] + ([str(ref)] if ref != 2 else [])
+            subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+            out["cells%d" % i] = np.fromfile(os.path.join(d, "out.cells"), np.int32).reshape(-1, 4)
+            out["scalars%d" % i] = np.fromfile(os.path.join(d, "out.scalars"), np.float32)
+        print("raw2cells", i, fmt, vol.shape, len(out["scalars%d" % i]), "cells, levels", np.unique(out["cells%d" % i][:, 3]))
+    np.savez_compressed(os.path.join(HERE, "raw2cells.npz"), **out)
 
 
 if __name__ == "__main__":

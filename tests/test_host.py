@@ -214,3 +214,25 @@ def test_triangle_mesh_file_and_config(R, built_lib, tmp_path):
         R.load_triangle_meshes(str(tmp_path / "bad.tris"))
     with pytest.raises(Exception, match="cannot open file"):
         R.load_triangle_meshes(str(tmp_path / "missing.tris"))
+
+
+def test_raw_to_cells_matches_reference(R, orc):
+    """exaRawToCells (tools/fromVolume/raw2cells.cpp) as a call: same cells and scalars, in the same
+    order, as the reference tool wrote for these volumes (tests/golden/raw2cells.npz, made by
+    tests/golden/make_golden.py from oracle/_ref/exaRawToCells) — including its byte-sum wrap-around
+    and its level = int(log2f(width)) for refinement 3"""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import make_golden
+    g = np.load(os.path.join(GOLDEN, "raw2cells.npz"))
+    levels = set()
+    for i, (fmt, vol, thr, ml, ref) in enumerate(make_golden.raw2cells_cases()):
+        cells, scal = R.raw_to_cells(vol, thr, ml, ref)
+        assert np.array_equal(cells, g["cells%d" % i]) and np.array_equal(scal, g["scalars%d" % i]), (i, fmt)
+        if ref == 2:                                             # the cells tile the volume (clipped at the far faces)
+            lo, hi = cells[:, :3], np.minimum(cells[:, :3] + (1 << cells[:, 3:4]), np.array(vol.shape[::-1]))
+            assert int(np.prod(hi - lo, axis=1).sum()) == vol.size
+        levels |= set(np.unique(cells[:, 3]).tolist())
+    assert len(levels) >= 3
+    with pytest.raises(Exception, match="unknown format"):
+        R.raw_to_cells(np.zeros((4, 4, 4), np.int16), 1.0, 2)
