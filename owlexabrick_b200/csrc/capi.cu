@@ -35,7 +35,7 @@ struct exa_renderer {
   float dt = 0.5f; float ert = 0.98f;
   int spaceSkipping = 1, gradDVR = 1, gradISO = 1;
   bool masksDirty = true;
-  uint8_t *d_volActive = nullptr, *d_isoActive = nullptr /* = d_volActive + numKdNodes */, *d_inPart = nullptr; int *d_kdParent = nullptr;
+  uint8_t *d_volActive = nullptr, *d_isoActive = nullptr /* = d_volActive + numKdNodes */, *d_regionActive = nullptr /* = d_volActive + 2 numKdNodes */, *d_inPart = nullptr; int *d_kdParent = nullptr;
   // framebuffer
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
@@ -98,7 +98,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   }
   P.clipEnabled = r->fs.clipBox.enabled; memcpy(P.clipLo, r->fs.clipBox.lower, 12); memcpy(P.clipHi, r->fs.clipBox.upper, 12);
   P.ertThreshold = r->ert;
-  P.volActive = r->d_volActive; P.isoActive = r->d_isoActive;
+  P.volActive = r->d_volActive; P.isoActive = r->d_isoActive; P.regionActive = r->d_regionActive;
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
@@ -281,7 +281,7 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   r->h_kd.resize(r->abr.numKdNodes);
   CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);
-  CKC(cudaMalloc(&r->d_volActive, 2 * (size_t)nn)); r->d_isoActive = r->d_volActive + r->abr.numKdNodes; CKC(cudaMalloc(&r->d_inPart, nn));
+  CKC(cudaMalloc(&r->d_volActive, 2 * (size_t)nn + nr)); r->d_isoActive = r->d_volActive + r->abr.numKdNodes; r->d_regionActive = r->d_volActive + 2 * (size_t)r->abr.numKdNodes; CKC(cudaMalloc(&r->d_inPart, nn));
   {
     // parent links for the activity pass (k_leafActiveUp climbs from the leaves)
     std::vector<int> parent(nn, -1);

@@ -8,7 +8,7 @@ static int refreshMasks(exa_renderer *r, RenderParams &P)
   for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) contour |= r->fs.contourPlane[i].enabled != 0;
   const uint8_t *inPart = r->partMode == EXA_PARTITION_SORT_LAST ? r->d_inPart : nullptr;
   int n = launchRegionActivity(P, r->abr.numKdNodes, r->d_kdParent, !contour && r->spaceSkipping, inPart,
-                               r->d_volActive, r->d_isoActive, r->stream);
+                               r->d_volActive, r->d_isoActive, r->d_regionActive, r->stream);
   if (n < 0) { setError(std::string("activity kernels failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
   r->launches += n;
   r->masksDirty = false;

@@ -502,6 +502,7 @@ static constexpr int SURF_THREADS = 128;                      // = FRAME_THREADS
 template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
                                                   float &value, float3 &g, unsigned &visits, unsigned &corners);
+__device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K);
 
 // traceIsoRay (exabrick.cu:1408-1460): march the iso-active regions front to back with lattice
 // offset 0 until two consecutive valid samples bracket an enabled iso value.
@@ -685,6 +686,9 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
 #ifndef EXA_LOOKAHEAD
 #define EXA_LOOKAHEAD 0     // kd traversal one node per trip ahead of the sampling: parity-green; C2 opaque 0.135 -> 0.152 ms, translucent 2.33 -> 2.30 ms: off
 #endif
+#ifndef EXA_ENTRY_FASTPATH
+#define EXA_ENTRY_FASTPATH 0   // first region of a ray by point location (location grid) instead of a kd descent: parity-green, but slower on C2 (opaque 0.134 -> 0.158 ms, translucent 2.31 -> 2.54 ms): off
+#endif
 #ifndef EXA_PREFETCH
 #define EXA_PREFETCH 0      // next-record L1 prefetch: measured slower on C2 (extra address math on an issue-bound kernel)
 #endif
@@ -765,6 +769,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   float4 pc = make_float4(0, 0, 0, 0);
   float offs = 0.f, already = 0.f, rayTmax = 0.f;
   Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.o = o; T.d = d; T.visits = 0; T.invd = f3(0, 0, 0);
+  bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;   // current region segment of this lane
+  float dtS = 0.f, t_i = 0.f, t_last = 0.f;
   if (inside) {
     uint2 *stack = stackBase + threadIdx.x;
     float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
@@ -813,6 +819,39 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     rayTmax = tHitWorld * dtScale;
     travInit(T, stack, o, d, already, rayTmax, P.scene);
     live = true;
+#if EXA_ENTRY_FASTPATH && !EXA_LOOKAHEAD
+    // First region by POINT LOCATION instead of a descent from the kd root (1 grid load + 0-2 nodes):
+    // the region that contains the ray just behind its entry into the volume.  It is THE answer of
+    // the ordered traversal iff it is active and its boxTest entry equals the entry into the scene
+    // bounds (no region starts earlier: every region box lies inside the bounds and fp subtraction /
+    // division are monotonic); otherwise the lane takes the normal traversal.  Most rays of an
+    // opaque frame end inside this region and never touch the tree; the others continue with the
+    // ordered traversal from the root at tmin = t1 * 1.0000001 as after any region.
+    if (T.cur == 0 && P.regionActive) {
+      float t0s, t1s;
+      if (boxTest(o, d, already, rayTmax, P.scene.boundsLo, P.scene.boundsHi, t0s, t1s)) {
+        const float3 pe = rayAt(o, d, t0s + 1e-3f);
+        uint32_t bo; int K;
+        if (locate(P.scene, pe.x, pe.y, pe.z, bo, K)) {
+          const U8 hb = ldg256(P.scene.blobs + bo);
+          const uint4 h0 = hb.lo, h1 = hb.hi;
+          const int rid = (int)__ldg(&P.scene.blobs[bo + 2].x);
+          if (P.regionActive[rid]) {
+            const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
+            const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
+            float a0, a1;
+            if (boxTest(o, d, already, rayTmax, lo, hi, a0, a1) && a0 == t0s) {
+              seg.blobOfs = bo; seg.K = K; seg.fcw = __uint_as_float(h1.z); seg.t0 = a0; seg.t1 = a1;
+              seg.hdr0 = ldg256(P.scene.blobs + bo + BLOB_HDR_UNITS);
+              haveSeg = true; T.tn = a1;                     // everything before t1 is done when the traversal starts
+              dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0;
+              if (STATS) rs.segments++;
+            }
+          }
+        }
+      }
+    }
+#endif
   }
 #ifdef EXA_PHASE_TIMING
   ph_setup = clock64() - t_start;
@@ -824,8 +863,6 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // longest lane's total.  __all_sync at the head keeps the warp converged.  Arithmetic and
   // per-ray order of operations are unchanged.
   {
-    bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;
-    float dtS = 0.f, t_i = 0.f, t_last = 0.f;
     int budget = P.sampleBudget;
 #if EXA_LOOKAHEAD
     bool haveNext = false, exhausted = false; Segment nseg = seg; float nextTmin = already;
@@ -1275,7 +1312,7 @@ __device__ bool activeForVolumeSampling(const RenderParams &P, float vlo, float 
 // marked it had found it unmarked (or raced with another marker) and keeps climbing, so the
 // chain always reaches the root.  Both masks were cleared by one memset (they are adjacent).
 __global__ void k_leafActiveUp(const __grid_constant__ RenderParams P, int numNodes, const int *kdParent, const uint8_t *inPart,
-                               int spaceSkipping, uint8_t *volActive, uint8_t *isoActive)
+                               int spaceSkipping, uint8_t *volActive, uint8_t *isoActive, uint8_t *regionActive)
 {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= numNodes) return;
@@ -1291,17 +1328,17 @@ __global__ void k_leafActiveUp(const __grid_constant__ RenderParams P, int numNo
   for (int k = 0; k < EXA_MAX_ISO_SURFACES; k++)
     if (P.isoEnabled[k] && P.isoValue[k] >= r.valueRange_lower && P.isoValue[k] <= r.valueRange_upper) ia = true;
   volatile uint8_t *va = volActive, *ia8 = isoActive;
-  if (act) for (int n = g; n >= 0 && !va[n]; n = kdParent[n]) va[n] = 1;
+  if (act) { regionActive[rid] = 1; for (int n = g; n >= 0 && !va[n]; n = kdParent[n]) va[n] = 1; }
   if (ia) for (int n = g; n >= 0 && !ia8[n]; n = kdParent[n]) ia8[n] = 1;
 }
 
 int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping, const uint8_t *inPart,
-                         uint8_t *volActive, uint8_t *isoActive, cudaStream_t s)
+                         uint8_t *volActive, uint8_t *isoActive, uint8_t *regionActive, cudaStream_t s)
 {
-  if (isoActive != volActive + numNodes) return -1;               // one allocation, one memset
-  cudaMemsetAsync(volActive, 0, 2 * (size_t)numNodes, s);
+  if (isoActive != volActive + numNodes || regionActive != volActive + 2 * (size_t)numNodes) return -1;   // one allocation, one memset
+  cudaMemsetAsync(volActive, 0, 2 * (size_t)numNodes + (size_t)std::max(P.scene.numRegions, 0), s);
   if (numNodes <= 0 || P.scene.numRegions <= 0) return 0;
-  k_leafActiveUp<<<(numNodes + 127) / 128, 128, 0, s>>>(P, numNodes, kdParent, inPart, spaceSkipping, volActive, isoActive);
+  k_leafActiveUp<<<(numNodes + 127) / 128, 128, 0, s>>>(P, numNodes, kdParent, inPart, spaceSkipping, volActive, isoActive, regionActive);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

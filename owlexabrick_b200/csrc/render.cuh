@@ -36,6 +36,7 @@ struct RenderParams {
   float ertThreshold;
   const uint8_t *volActive;            // per kd node: subtree has an active region (space skipping x partition)
   const uint8_t *isoActive;            // per kd node: subtree has a region whose range holds an iso value
+  const uint8_t *regionActive;         // per REGION: active for volume sampling (same classification as volActive's leaves); entry fast path
   float4 *accum; uint32_t *rgba8;
   float4 *partialOut;                  // != null: write premultiplied partial, skip bg/accum/pack
   int tileMode, rank, numRanks;        // image-tile partition
@@ -86,7 +87,8 @@ int launchTraceBounds(const float *traces, int numTraces, int numTimesteps, int 
 int launchConeGrid(const float *traces, int numTraces, int numTimesteps, int currentTimestep, int G, const float lo[3], const float invCell[3],
                    int *countsOrCursor, int *list, int fill, cudaStream_t s);
 int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParent, int spaceSkipping,
-                         const uint8_t *nodeInPartition, uint8_t *volActive, uint8_t *isoActive /* = volActive + numNodes */, cudaStream_t s);
+                         const uint8_t *nodeInPartition, uint8_t *volActive, uint8_t *isoActive /* = volActive + numNodes */,
+                         uint8_t *regionActive /* = volActive + 2 * numNodes, numRegions bytes */, cudaStream_t s);
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
 int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellIDs, size_t numCells, float *d_out,
                  int *d_errFlag, cudaStream_t s);
