@@ -1026,6 +1026,7 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
   for (int i = 0; i < 2; i++) anyIso |= f.isoEnabled[i] != 0;
   bool anyContour = false;
   for (int i = 0; i < 3; i++) anyContour |= f.cpEnabled[i] != 0;
+  const bool rtl = getenv("ORC_RND_ARGS_RTL") && atoi(getenv("ORC_RND_ARGS_RTL"));
   for (size_t i = 0; i < s.regions.size(); i++) {
     const OrcRegion &r = s.regions[i];
     bool act = false;
@@ -1044,7 +1045,11 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
         const int pixelIdx = px + W * py;
         { const char *e = getenv("ORC_DEBUG_PIXEL"); int dx = -1, dy = -1; g_dbg = e && sscanf(e, "%d,%d", &dx, &dy) == 2 && dx == px && dy == py; }
         LCG16 rnd((uint32_t)(f.frameID * W * H) + (uint32_t)px, (uint32_t)py);
-        const float jx = rnd(), jy = rnd();                // oracle fixes x first
+        // vec2f(rnd(), rnd()) (:1594): the order of the two calls is unspecified in C++.  nvcc evaluates
+        // left to right (x first), which is what the product and this oracle do; g++ evaluates right to
+        // left, so the reference shader compiled with g++ (oracle/_ref/ref_shader) needs rtl = true
+        float jx, jy;
+        if (rtl) { jy = rnd(); jx = rnd(); } else { jx = rnd(); jy = rnd(); }
         const float sx = (float)px + jx, sy = (float)py + jy;
         Ray ray;                                           // Camera::generateRay, Camera.h:27-44
         ray.o = v3(f.cam_pos[0], f.cam_pos[1], f.cam_pos[2]);
@@ -1065,7 +1070,8 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
             makeOrthonormalBasis(u, v, w);
             int hitCnt = 0;
             for (int i = 0; i < aoSamples; ++i) {
-              const float u1 = rnd(), u2 = rnd();            // oracle fixes the first argument first
+              float u1, u2;                                  // cosine_sample_hemisphere(rnd(), rnd()) (:1624): same remark
+              if (rtl) { u2 = rnd(); u1 = rnd(); } else { u1 = rnd(); u2 = rnd(); }
               const V3 sp = cosineSampleHemisphere(u1, u2);
               Ray ao; ao.o = isect; ao.d = normalize(sp.x * u + sp.y * v + sp.z * w); ao.tmin = 1e-4f; ao.tmax = f.aoLength;
               Surface hit;

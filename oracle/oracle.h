@@ -11,12 +11,19 @@
  *   - streamlines (RK4)   programs/exabrick.cu:945-963, 1531-1574; rounded cones :441-573
  *   - contour planes, AO  programs/exabrick.cu:78-94, 1267-1406, 1476-1529, 1604-1652
  *
- * Parity status: builder + ABR are PINNED against the reference's own code compiled in
- * place (oracle/_ref, see oracle/Makefile and tests/golden/make_golden.py).  The
- * reference ships no golden vectors for reconstruction / compositing / iso /
- * streamlines and its device code needs OptiX, so for those functions parity is
- * UNPINNED by reference outputs; they are pinned only by analytic known-answer tests
- * (tests/test_oracle.py).
+ * Parity status: PINNED by the reference's own code, compiled in place into oracle/_ref (see
+ * oracle/Makefile, tests/golden/make_golden.py):
+ *   - builder, ABR build, exaRawToCells: the reference's host sources (exaBuilder, ref_abr,
+ *     exaRawToCells) — bit-exact (tests/test_oracle.py, tests/test_host.py);
+ *   - reconstruction, transfer function, DVR / iso / contour-plane / streamline-cone / AO frames
+ *     and the RK4 tracer: the reference's DEVICE source programs/exabrick.cu compiled as plain
+ *     C++ (ref_shader_main.cpp + ref_shim/shader_shim.h supply the OptiX/OWL device API on the
+ *     host) — the oracle reproduces its accumulation buffers, RGBA8 frames and trace vertices
+ *     bit for bit on 15 frames + 1 tracer run (tests/test_oracle_pinned.py, golden vectors in
+ *     tests/golden/ref_shader_frames.npz).  Two things in that comparison are not reference code:
+ *     OptiX's closest-hit search (brute force in the shim) and the CUDA texture fetch of the
+ *     transfer function (a linear-filtered 128-texel table with a full-precision weight).
+ *     Triangle meshes use OptiX's built-in triangle test: unpinned (analytic tests only).
  */
 #pragma once
 #include <stdint.h>

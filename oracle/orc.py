@@ -199,6 +199,73 @@ def ref_build_bricks(cells, workdir, max_leaf_width=None):
     return open(bf, "rb").read()
 
 
+def have_ref_shader():
+    return os.path.exists(os.path.join(REF_DIR, "ref_shader"))
+
+
+def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None):
+    """one frame through the reference's OWN device source programs/exabrick.cu compiled as C++
+    (oracle/ref_shader_main.cpp + ref_shim/shader_shim.h) -> (accum float32[H,W,4], rgba8 uint32[H,W])"""
+    bf = os.path.join(workdir, "s.bricks")
+    open(bf, "wb").write(bricks_raw)
+    sfs = []
+    for i, f in enumerate(fields):
+        p = os.path.join(workdir, "s%d.scalars" % i)
+        np.ascontiguousarray(f, dtype=np.float32).tofile(p)
+        sfs.append(p)
+    ff, of = os.path.join(workdir, "frame.bin"), os.path.join(workdir, "out.bin")
+    with open(ff, "wb") as fh:
+        fh.write(bytes(frame))
+        if frame.numTraces > 0 and frame.traces:
+            n = frame.numTraces * frame.numTimesteps * 3
+            fh.write(np.ctypeslib.as_array(frame.traces, shape=(n,)).astype(np.float32).tobytes())
+    W, H = frame.width, frame.height
+    if accum is not None:                       # progressive: the previous sum is read from out.bin
+        with open(of, "wb") as fh:
+            fh.write(np.ascontiguousarray(accum, np.float32).tobytes())
+    elif os.path.exists(of):
+        os.remove(of)
+    env = dict(os.environ)
+    if window:
+        env["ORC_WINDOW"] = ",".join(str(int(x)) for x in window)
+    subprocess.check_call([os.path.join(REF_DIR, "ref_shader"), bf, ff, of] + sfs, stdout=subprocess.DEVNULL, env=env)
+    raw = open(of, "rb").read()
+    acc = np.frombuffer(raw[:W * H * 16], np.float32).reshape(H, W, 4).copy()
+    rgba = np.frombuffer(raw[W * H * 16:W * H * 20], np.uint32).reshape(H, W).copy()
+    return acc, rgba
+
+
+def ref_trace(bricks_raw, fields, seeds, num_timesteps, channels, steplen, wlo, whi, workdir):
+    """RK4 advection by the reference's own computeTraces (programs/exabrick.cu:1531-1574, compiled as C++)"""
+    seeds = np.asarray(seeds, np.float32).reshape(-1, 3)
+    tr = np.zeros((len(seeds), num_timesteps, 3), np.float32)
+    tr[:, 0] = seeds
+    f = OrcFrame()
+    f.width, f.height, f.numPrimaryChannels, f.dt = 1, 1, len(fields), 0.5
+    f.xf_vx[0] = f.xf_vy[1] = f.xf_vz[2] = 1.0
+    f.numTraces, f.numTimesteps, f.currentTimestep = len(seeds), num_timesteps, 0
+    f.traces = tr.ctypes.data_as(C.POINTER(C.c_float))
+    f.worldLo[:] = [float(x) for x in wlo]
+    f.worldHi[:] = [float(x) for x in whi]
+    os.environ["ORC_TRACE"] = "%r,%d,%d,%d" % (float(steplen), channels[0], channels[1], channels[2])
+    try:
+        bf = os.path.join(workdir, "s.bricks")
+        open(bf, "wb").write(bricks_raw)
+        sfs = []
+        for i, fl in enumerate(fields):
+            p = os.path.join(workdir, "s%d.scalars" % i)
+            np.ascontiguousarray(fl, dtype=np.float32).tofile(p)
+            sfs.append(p)
+        ff, of = os.path.join(workdir, "frame.bin"), os.path.join(workdir, "traces.bin")
+        with open(ff, "wb") as fh:
+            fh.write(bytes(f))
+            fh.write(tr.tobytes())
+        subprocess.check_call([os.path.join(REF_DIR, "ref_shader"), bf, ff, of] + sfs, stdout=subprocess.DEVNULL)
+        return np.fromfile(of, np.float32).reshape(tr.shape)
+    finally:
+        del os.environ["ORC_TRACE"]
+
+
 def ref_build_abr(bricks_raw, fields, workdir):
     """run the reference's ExaBrickRegions::buildFrom (exa/Regions.cpp) via oracle/ref_abr_main.cpp"""
     bf = os.path.join(workdir, "x.bricks")

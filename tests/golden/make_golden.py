@@ -61,6 +61,7 @@ def main():
         print(name, hashes[name])
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     raw2cells_golden()
+    ref_shader_golden()
 
 
 def raw2cells_cases():
@@ -96,3 +97,24 @@ def raw2cells_golden():
 
 if __name__ == "__main__":
     main()
+
+
+def ref_shader_golden():
+    """frames rendered by the reference's own device source compiled as C++ (oracle/_ref/ref_shader)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_shader_cases as RC
+    assert orc.have_ref_shader(), "run `make -C oracle ref` first"
+    out = {}
+    for name, kind, channels, mlw, configure in RC.cases():
+        raw, fields, dom, _ = RC.build(orc, kind, channels, mlw)
+        fd = RC.frame(dom, channels, configure)
+        acc0 = RC.start_accum(name) if fd.frame_id > 0 else None
+        with tempfile.TemporaryDirectory() as d:
+            acc, rgba = orc.ref_render(raw, fields, fd.to_orc(orc), d, accum=acc0)
+        out[name + "_accum"], out[name + "_rgba"] = acc, rgba
+        print("ref_shader", name, "max colour %.3f" % acc[..., :3].max(), "lit pixels", int((acc[..., :3].max(axis=-1) > 0).sum()))
+    cells, fields, dom, seeds, T, steplen = RC.tracer_case()
+    with tempfile.TemporaryDirectory() as d:
+        out["tracer"] = orc.ref_trace(orc.build_bricks(cells), fields, seeds, T, (0, 1, 2), steplen, [0, 0, 0], [dom] * 3, d)
+    print("ref_shader tracer: dead vertices", int((out["tracer"][..., 0] >= 2e10).sum()), "of", out["tracer"].shape[0] * T)
+    np.savez_compressed(os.path.join(HERE, "ref_shader_frames.npz"), **out)
