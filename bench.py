@@ -247,7 +247,7 @@ def run_reference(args):
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * tot_t / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload_name(name), "image": list(image), "dt": DT},
-            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": orc.num_threads(), "kind": "port", "sample": sample},
+            "cpu_baseline": {"value": value, "unit": "samples/s", "cores": orc.num_threads(), "kind": "port", "sample": sample, "pinned": "the port is bit-identical to the reference's own device source programs/exabrick.cu compiled as C++ (oracle/_ref/ref_shader, tests/test_oracle_pinned.py); that build is not timed here: its stand-in for the OptiX BVH is a brute-force loop over all regions"},
             "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
@@ -644,7 +644,7 @@ def run_product(args):
         for _ in range(reps):
             cst, cdt = cpu_frame_sample(orc, oscene, fd, (0, 0, W, H))
             tot_s += cst["samples"]; tot_t += cdt
-        cpu = {"value": tot_s / tot_t, "unit": "samples/s", "frames_per_s": reps / tot_t, "cores": orc.num_threads(), "kind": "port",
+        cpu = {"value": tot_s / tot_t, "unit": "samples/s", "frames_per_s": reps / tot_t, "cores": orc.num_threads(), "kind": "port", "pinned": "the port is bit-identical to the reference's own device source programs/exabrick.cu compiled as C++ (oracle/_ref/ref_shader, tests/test_oracle_pinned.py); that build is not timed here: its stand-in for the OptiX BVH is a brute-force loop over all regions",
                "sample": "the same whole frame, %d times, %.1f s (oracle port, OpenMP over pixel rows, BVH region query)" % (reps, tot_t)}
 
     if rank == 0:

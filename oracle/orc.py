@@ -235,6 +235,31 @@ def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None):
     return acc, rgba
 
 
+def ref_sample_points(bricks_raw, fields, pts, channel, workdir):
+    """tent-basis reconstruction (+ analytic gradient) at points by the reference's own samplePoint /
+    samplePointWithDerivative behind its point query (programs/exabrick.cu:781-830, 883-942, compiled as C++)
+    -> (value, valid uint8, grad[n,3])"""
+    pts = np.ascontiguousarray(pts, dtype=np.float32).reshape(-1, 3)
+    f = OrcFrame()
+    f.width, f.height, f.numPrimaryChannels, f.dt = 1, 1, len(fields), 0.5
+    f.xf_vx[0] = f.xf_vy[1] = f.xf_vz[2] = 1.0
+    bf = os.path.join(workdir, "s.bricks")
+    open(bf, "wb").write(bricks_raw)
+    sfs = []
+    for i, fl in enumerate(fields):
+        p = os.path.join(workdir, "s%d.scalars" % i)
+        np.ascontiguousarray(fl, dtype=np.float32).tofile(p)
+        sfs.append(p)
+    ff, of, pf = os.path.join(workdir, "frame.bin"), os.path.join(workdir, "pts.out"), os.path.join(workdir, "pts.in")
+    open(ff, "wb").write(bytes(f))
+    pts.tofile(pf)
+    env = dict(os.environ, ORC_POINTS=pf, ORC_CHANNEL=str(int(channel)))
+    subprocess.check_call([os.path.join(REF_DIR, "ref_shader"), bf, ff, of] + sfs, stdout=subprocess.DEVNULL, env=env)
+    out = np.fromfile(of, np.float32).reshape(-1, 5)
+    assert not (out[:, 1] == 2).any(), "samplePoint and samplePointWithDerivative disagree on the value"
+    return out[:, 0].copy(), (out[:, 1] == 1).astype(np.uint8), out[:, 2:5].copy()
+
+
 def ref_trace(bricks_raw, fields, seeds, num_timesteps, channels, steplen, wlo, whi, workdir):
     """RK4 advection by the reference's own computeTraces (programs/exabrick.cu:1531-1574, compiled as C++)"""
     seeds = np.asarray(seeds, np.float32).reshape(-1, 3)

@@ -153,6 +153,31 @@ int main(int ac, char **av)
   }
   // shim::geoms[4] (surfaceModel: triangle meshes) stays empty
 
+  // ---- point mode (ORC_POINTS=file of n x {x,y,z} floats, ORC_CHANNEL=c): the reference's reconstruction at
+  // arbitrary points exactly as samplePointWithInfRay does it (exabrick.cu:818-830: region query with a ray of
+  // length 2e-10, then samplePoint) plus samplePointWithDerivative (:883-942); out.bin = n x {value, valid, gx, gy, gz}
+  if (const char *pf = getenv("ORC_POINTS")) {
+    const int channel = getenv("ORC_CHANNEL") ? atoi(getenv("ORC_CHANNEL")) : 0;
+    std::vector<float> pts = readFloats(pf);
+    const size_t n = pts.size() / 3;
+    std::vector<float> out(n * 5, 0.f);
+#pragma omp parallel for schedule(dynamic, 256)
+    for (size_t i = 0; i < n; i++) {
+      const vec3f pos(pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+      owl::Ray ray; ray.origin = pos; ray.direction = vec3f(1.f); ray.tmin = 0.f; ray.tmax = 2e-10f;
+      VolumePRD prd = traceVolumeRay(ray);
+      if (prd.leafID < 0) continue;                              // the reference would index region -1 here
+      float v = 0.f, v2 = 0.f; vec3f g(0.f);
+      const bool ok = samplePoint(v, prd.leafID, pos, channel);
+      const bool ok2 = samplePointWithDerivative<false>(v2, g, prd.leafID, pos, channel);
+      if (ok) { out[5 * i] = v; out[5 * i + 1] = (ok2 && v2 == v) ? 1.f : 2.f; out[5 * i + 2] = g.x; out[5 * i + 3] = g.y; out[5 * i + 4] = g.z; }
+    }
+    FILE *o = fopen(av[3], "wb");
+    fwrite(out.data(), 4, out.size(), o);
+    fclose(o);
+    return 0;
+  }
+
   // ---- tracer mode (ORC_TRACE="steplen,c0,c1,c2"): the reference's computeTraces (exabrick.cu:1531-1574),
   // one call per seed and time step as advanceTracer + render would do; out.bin = the trace vertices
   if (const char *e = getenv("ORC_TRACE")) {

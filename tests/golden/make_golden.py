@@ -62,6 +62,8 @@ def main():
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     raw2cells_golden()
     ref_shader_golden()
+    points_golden(hashes)
+    json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
 
 def raw2cells_cases():
@@ -118,3 +120,18 @@ def ref_shader_golden():
         out["tracer"] = orc.ref_trace(orc.build_bricks(cells), fields, seeds, T, (0, 1, 2), steplen, [0, 0, 0], [dom] * 3, d)
     print("ref_shader tracer: dead vertices", int((out["tracer"][..., 0] >= 2e10).sum()), "of", out["tracer"].shape[0] * T)
     np.savez_compressed(os.path.join(HERE, "ref_shader_frames.npz"), **out)
+
+
+def points_golden(hashes):
+    """north_star check 2: the reference's reconstruction at 1 M random points of config C1, by its own
+    samplePoint behind its own point query (programs/exabrick.cu compiled as C++) — SHA-256 of the values
+    + validity, and the first 4096 values in the clear"""
+    c = synth.nested_boxes(256, [(72, 184), (32, 224)])
+    f = synth.analytic_field(c, 256, 0)
+    pts = synth.random_points(1000000, [0.0] * 3, [256.0] * 3, seed=1)
+    with tempfile.TemporaryDirectory() as d:
+        v, ok, g = orc.ref_sample_points(orc.build_bricks(c), [f], pts, 0, d)
+    hashes["C1_points_1M"] = {"values_sha256": hashlib.sha256(v.tobytes()).hexdigest(), "valid_sha256": hashlib.sha256(ok.tobytes()).hexdigest(),
+                              "grad_sha256": hashlib.sha256(g.tobytes()).hexdigest(), "valid": int(ok.sum())}
+    np.savez_compressed(os.path.join(HERE, "c1_points_head.npz"), values=v[:4096], valid=ok[:4096], grad=g[:4096])
+    print("C1 1M points", hashes["C1_points_1M"])

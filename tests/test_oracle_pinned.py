@@ -92,3 +92,28 @@ def test_tracer_equals_reference_compute_traces(orc, golden):
         with tempfile.TemporaryDirectory() as d:
             r = orc.ref_trace(raw, fields, seeds, T, (0, 1, 2), steplen, [0, 0, 0], [dom] * 3, d)
         assert np.array_equal(r, golden["tracer"])
+
+
+def test_reconstruction_1m_points_c1_equals_reference(orc):
+    """north_star correctness check 2, on the CPU side: the oracle's reconstruction (value, validity and
+    analytic gradient) at 1 M random points of config C1 is bit-identical to the reference's own
+    samplePoint / samplePointWithDerivative behind its own point query (SHA-256 made by
+    tests/golden/make_golden.py from oracle/_ref/ref_shader).  tests/test_gpu_parity.py::
+    test_reconstruction_1m_points_c1 holds the CUDA path to within 1e-5 relative of these same values."""
+    import hashlib
+    import json
+    from owlexabrick_b200 import synth
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["C1_points_1M"]
+    c = synth.nested_boxes(256, [(72, 184), (32, 224)])
+    f = synth.analytic_field(c, 256, 0)
+    bricks, ids = orc.parse_bricks(orc.build_bricks(c))
+    sc = orc.flatten_scalars(ids, [f])
+    regions, leaf = orc.build_abr(bricks, sc)
+    pts = synth.random_points(1000000, [0.0] * 3, [256.0] * 3, seed=1)
+    v, ok, g, _ = orc.Scene(bricks, sc, regions, leaf).sample(pts, 0, grad=True)
+    head = np.load(os.path.join(GOLDEN, "c1_points_head.npz"))
+    assert np.array_equal(v[:4096], head["values"]) and np.array_equal(ok[:4096], head["valid"]) and np.array_equal(g[:4096], head["grad"])
+    assert int(ok.sum()) == h["valid"]
+    assert hashlib.sha256(ok.tobytes()).hexdigest() == h["valid_sha256"]
+    assert hashlib.sha256(v.tobytes()).hexdigest() == h["values_sha256"]
+    assert hashlib.sha256(g.tobytes()).hexdigest() == h["grad_sha256"]
