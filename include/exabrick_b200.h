@@ -284,6 +284,9 @@ int exa_renderer_advance_tracer(exa_renderer_t *r, int *rebuilt);
  * animation artefact) */
 int exa_renderer_trace_all(exa_renderer_t *r);
 int exa_renderer_read_traces(exa_renderer_t *r, float *xyz /* numTraces*numTimesteps*3 */);
+/* load trace vertices computed elsewhere (a saved tracer state): traces.buffer + timestepHost of
+ * OptixRenderer.h:155-165; segments k < currentTimestep-1 are drawn */
+int exa_renderer_set_traces(exa_renderer_t *r, const float *xyz, int numTraces, int numTimesteps, int currentTimestep);
 
 /* render() (:531-552): refresh activity masks if dirty, launch the fused frame kernel,
  * synchronise */
@@ -304,6 +307,8 @@ int exa_renderer_read_rgba8(exa_renderer_t *r, uint32_t *hostOut);
  * the copy; exa_renderer_sync() waits for both.  Renderer-owned frame buffers only. */
 int exa_renderer_read_rgba8_async(exa_renderer_t *r, uint32_t *pinnedHostOut);
 int exa_renderer_read_accum(exa_renderer_t *r, float *hostOutRGBA);
+/* restore the accumulation buffer of a progressive sequence (the next frame with frameID > 0 adds to it) */
+int exa_renderer_write_accum(exa_renderer_t *r, const float *hostInRGBA);
 /* device pointers of the current frame buffers (float4 accum, uint32 rgba8) */
 int exa_renderer_device_buffers(exa_renderer_t *r, void **accum, void **rgba8);
 

@@ -115,6 +115,8 @@ _SIG = {
     "exa_renderer_sync": (i32, [vp]),
     "exa_renderer_read_rgba8": (i32, [vp, vp]),
     "exa_renderer_read_accum": (i32, [vp, vp]),
+    "exa_renderer_write_accum": (i32, [vp, vp]),
+    "exa_renderer_set_traces": (i32, [vp, vp, i32, i32, i32]),
     "exa_renderer_device_buffers": (i32, [vp, C.POINTER(vp), C.POINTER(vp)]),
     "exa_sample_points_host": (i32, [vp, vp, sz, i32, vp, vp, vp]),
     "exa_sample_points_device": (i32, [vp, vp, sz, i32, vp, vp, vp]),

@@ -176,6 +176,13 @@ int exa_renderer_read_rgba8_async(exa_renderer_t *r, uint32_t *pinnedHostOut)
   CKR(cudaStreamWaitEvent(r->stream, r->evCopied[r->rbCur], 0));
   return EXA_OK;
 }
+int exa_renderer_write_accum(exa_renderer_t *r, const float *hostIn)
+{
+  if (!r || !hostIn || !r->d_accum) { setError("write_accum: no framebuffer"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(r->d_accum, hostIn, (size_t)r->width * r->height * 16, cudaMemcpyHostToDevice, r->stream));
+  CKR(cudaStreamSynchronize(r->stream)); return EXA_OK;
+}
 int exa_renderer_read_accum(exa_renderer_t *r, float *hostOut)
 {
   if (!r || !hostOut || !r->d_accum) { setError("read_accum: no framebuffer"); return EXA_ERR_INVALID; }
@@ -336,6 +343,17 @@ int exa_renderer_trace_all(exa_renderer_t *r)
   if (!rc) r->timestep = r->numTimesteps;
   r->traceBoundsDirty = true;
   return rc;
+}
+
+int exa_renderer_set_traces(exa_renderer_t *r, const float *xyz, int numTraces, int numTimesteps, int currentTimestep)
+{
+  if (!r || !xyz || numTraces < 0 || numTimesteps < 1 || currentTimestep < 0) { setError("set_traces: bad argument"); return EXA_ERR_INVALID; }
+  r->numTraces = numTraces; r->numTimesteps = numTimesteps;
+  std::vector<float> host(xyz, xyz + (size_t)numTraces * numTimesteps * 3);
+  int rc = uploadSeeds(r, host);
+  if (rc) return rc;
+  r->timestep = currentTimestep; r->traceBoundsDirty = true;
+  return EXA_OK;
 }
 
 int exa_renderer_read_traces(exa_renderer_t *r, float *xyz)

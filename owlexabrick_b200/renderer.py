@@ -359,6 +359,16 @@ class Renderer:
     def traceAll(self):
         check(lib.exa_renderer_trace_all(self.h))
 
+    def load_traces(self, traces, current_timestep):
+        """trace vertices computed elsewhere: float32[numTraces, numTimesteps, 3] + the time step reached"""
+        t = np.ascontiguousarray(traces, dtype=np.float32)
+        check(lib.exa_renderer_set_traces(self.h, _p(t), t.shape[0], t.shape[1], int(current_timestep)))
+        self._trace_shape = (t.shape[0], t.shape[1])
+
+    def write_accum(self, accum):
+        a = np.ascontiguousarray(accum, dtype=np.float32)
+        check(lib.exa_renderer_write_accum(self.h, _p(a)))
+
     def readTraces(self):
         out = np.zeros(self._trace_shape + (3,), np.float32)
         check(lib.exa_renderer_read_traces(self.h, _p(out)))
