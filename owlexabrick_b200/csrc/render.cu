@@ -1145,8 +1145,17 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
   return accFinish<GRAD>(a, value, g);
 }
 
+// 128 threads x 16 CTAs per SM = 2048 resident threads at 32 registers (12 bytes of spills): the kernel is a
+// chain of dependent random loads, so resident threads are what hides the latency.  1 M points on C2
+// (tools/perf_quick.py): 256 x default registers (40 -> 1536 threads) 53.5 us, 256 x 8 53.3 us, 128 x 16 50.7 us
+#ifndef EXA_POINTS_THREADS
+#define EXA_POINTS_THREADS 128
+#endif
+#ifndef EXA_POINTS_MINBLOCKS
+#define EXA_POINTS_MINBLOCKS 16
+#endif
 template <bool GRAD, bool STATS, bool DUAL>
-__global__ void __launch_bounds__(256) k_samplePoints(const __grid_constant__ SampleParams P)
+__global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_samplePoints(const __grid_constant__ SampleParams P)
 {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   unsigned visits = 0, corners = 0; bool counted = false;
@@ -1169,9 +1178,9 @@ __global__ void __launch_bounds__(256) k_samplePoints(const __grid_constant__ Sa
 int launchSamplePoints(const SampleParams &P, cudaStream_t s)
 {
   if (P.n == 0) return 0;
-  const unsigned grid = (unsigned)((P.n + 255) / 256);
+  const unsigned grid = (unsigned)((P.n + EXA_POINTS_THREADS - 1) / EXA_POINTS_THREADS);
   const bool stats = P.stats != nullptr;
-#define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, 256, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, 256, 0, s>>>(P); }
+#define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); }
   if (P.grad) { if (stats) LAUNCH_P(true, true) else LAUNCH_P(true, false) }
   else { if (stats) LAUNCH_P(false, true) else LAUNCH_P(false, false) }
 #undef LAUNCH_P
