@@ -175,6 +175,10 @@ int exa_triangle_mesh_load(const char *fileName, float **vertices, size_t *numVe
 int exa_scalar_field_load(const char *fileName, int compat, float **values, size_t *count,
                           float valueRange[2]);
 /* ScalarField::loadAndComputeMagnitude on three arrays already in memory */
+/* ScalarField::createFromExpression (exa/ScalarField.cpp:96-230; `scalar <name> expr "<postfix>"` in a config):
+ * postfix expression over `fields` per cell; tokens %k, numbers, + - * / ** == != < > <= >=, log abs sqrt, select */
+int exa_scalar_field_expression(const float *const *fields, int numFields, size_t count,
+                                const char *const *tokens, int numTokens, float *out, float valueRange[2]);
 int exa_scalar_field_magnitude(const float *x, const float *y, const float *z, size_t count,
                                float *out, float valueRange[2]);
 /* ColorMapper::operator()(t) over control points {t,r,g,b} sorted by t */

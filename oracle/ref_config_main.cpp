@@ -1,0 +1,26 @@
+// oracle/ref_config_main.cpp — TEST INFRASTRUCTURE, not product code.
+//
+// Driver around the reference's own config loader (exa/Config.cpp:57-180 parseConfigFile, with
+// exa/ScalarField.cpp load / loadAndComputeMagnitude / createFromExpression), compiled from
+// /root/reference in place by oracle/Makefile into oracle/_ref/ref_config.  Dumps every scalar field:
+//   int32 numFields; per field: int32 nameLen; char name[]; int64 count; float range[2]; float values[count]
+// usage: ref_config in.exa out.bin
+#include "exa/Config.h"
+#include <cstdio>
+using namespace exa;
+int main(int ac, char **av)
+{
+  if (ac != 3) { fprintf(stderr, "usage: ref_config in.exa out.bin\n"); return 1; }
+  Config::SP cfg = Config::parseConfigFile(av[1]);
+  FILE *o = fopen(av[2], "wb");
+  int32_t n = (int32_t)cfg->scalarFields.size();
+  fwrite(&n, 4, 1, o);
+  for (auto &sf : cfg->scalarFields) {
+    int32_t nl = (int32_t)sf->name.size(); int64_t cnt = (int64_t)sf->value.size();
+    float r[2] = {sf->valueRange.lower, sf->valueRange.upper};
+    fwrite(&nl, 4, 1, o); fwrite(sf->name.data(), 1, nl, o); fwrite(&cnt, 8, 1, o); fwrite(r, 4, 2, o);
+    fwrite(sf->value.data(), 4, sf->value.size(), o);
+  }
+  fclose(o);
+  return 0;
+}

@@ -99,6 +99,7 @@ _SIG = {
     "exa_renderer_update_contour_planes": (i32, [vp, vp, vp, vp, vp]),
     "exa_renderer_set_ao": (i32, [vp, i32, f32]),
     "exa_renderer_set_triangle_meshes": (i32, [vp, vp, sz, vp, sz]),
+    "exa_scalar_field_expression": (i32, [vp, i32, sz, vp, i32, vp, vp]),
     "exa_raw_to_cells": (i32, [vp, i32, i32, i32, i32, f32, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(sz)]),
     "exa_triangle_mesh_load": (i32, [C.c_char_p, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),
     "exa_config_triangles": (i32, [vp, C.POINTER(vp), C.POINTER(sz), C.POINTER(vp), C.POINTER(sz)]),

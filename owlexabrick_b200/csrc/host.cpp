@@ -271,6 +271,74 @@ int exa_scalar_field_load(const char *fileName, int compat, float **values, size
   return EXA_OK;
 }
 
+// ScalarField::createFromExpression (exa/ScalarField.cpp:96-230): a postfix expression over the fields loaded
+// so far, evaluated per cell on a float stack.  Tokens: %k (field k), numbers, + - * / ** == != < > <= >=,
+// log abs sqrt, select (mask op1 op2 -> mask ? op1 : op2, mask truncated to int).  Tokens are trimmed of
+// double quotes and blanks as the reference does.  Where the reference prints a complaint and carries on
+// with an undefined value (bad token, stack underflow, more than one value left), this returns an error.
+int exa_scalar_field_expression(const float *const *fields, int numFields, size_t count, const char *const *tokens, int numTokens,
+                                float *out, float valueRange[2])
+{
+  if (!fields || numFields <= 0 || !tokens || numTokens <= 0 || !out) { setError("exa_scalar_field_expression: bad argument"); return EXA_ERR_INVALID; }
+  enum Op { FIELD, CONST, ADD, SUB, MUL, DIV, POW, EQ, NE, LT, GT, LE, GE, LOG, ABS, SQRT, SELECT };
+  struct Tok { Op op; int field; float value; };
+  std::vector<Tok> prog;
+  for (int i = 0; i < numTokens; i++) {
+    std::string t = tokens[i] ? tokens[i] : "";
+    auto strip = [&](char c) { while (!t.empty() && t.front() == c) t.erase(t.begin()); while (!t.empty() && t.back() == c) t.pop_back(); };
+    strip('"'); strip(' ');
+    if (t.empty()) { setError("expression: empty token"); return EXA_ERR_INVALID; }
+    static const struct { const char *name; Op op; } table[] = {{"+", ADD}, {"-", SUB}, {"*", MUL}, {"/", DIV}, {"**", POW}, {"==", EQ}, {"!=", NE},
+      {"<", LT}, {">", GT}, {"<=", LE}, {">=", GE}, {"log", LOG}, {"abs", ABS}, {"sqrt", SQRT}, {"select", SELECT}};
+    Tok k; k.field = 0; k.value = 0.f; bool found = false;
+    for (auto &e : table) if (t == e.name) { k.op = e.op; found = true; }
+    if (!found) {
+      try {
+        if (t[0] == '%') { k.op = FIELD; k.field = std::stoi(t.substr(t.find_first_not_of('%'))); if (k.field < 0 || k.field >= numFields) { setError("expression: invalid placeholder token " + t); return EXA_ERR_INVALID; } }
+        else { k.op = CONST; k.value = (float)std::stod(t); }
+      } catch (...) { setError("expression: not a floating point token: " + t); return EXA_ERR_INVALID; }
+    }
+    prog.push_back(k);
+  }
+  int depth = 0;                                             // validate the stack discipline once
+  for (auto &k : prog) {
+    const int need = k.op <= CONST ? 0 : k.op == SELECT ? 3 : k.op >= LOG ? 1 : 2;
+    if (depth < need) { setError("expression: insufficient operands"); return EXA_ERR_INVALID; }
+    depth += 1 - need;
+  }
+  if (depth != 1) { setError("Invalid expression"); return EXA_ERR_INVALID; }
+  float lo = INFINITY, hi = -INFINITY;
+#pragma omp parallel for reduction(min : lo) reduction(max : hi)
+  for (long long i = 0; i < (long long)count; i++) {
+    float st[64]; int sp = 0;
+    for (auto &k : prog) {
+      if (sp >= 62) break;
+      switch (k.op) {
+        case FIELD: st[sp++] = fields[k.field][i]; break;
+        case CONST: st[sp++] = k.value; break;
+        case SELECT: { const float op2 = st[--sp], op1 = st[--sp]; const int mask = (int)st[--sp]; st[sp++] = mask ? op1 : op2; break; }
+        case LOG: st[sp - 1] = logf(st[sp - 1]); break;
+        case ABS: st[sp - 1] = fabsf(st[sp - 1]); break;
+        case SQRT: st[sp - 1] = sqrtf(st[sp - 1]); break;
+        default: {
+          const float op2 = st[--sp], op1 = st[--sp]; float r = 0.f;
+          switch (k.op) {
+            case ADD: r = op1 + op2; break; case SUB: r = op1 - op2; break; case MUL: r = op1 * op2; break; case DIV: r = op1 / op2; break;
+            case POW: r = powf(op1, op2); break; case EQ: r = op1 == op2; break; case NE: r = op1 != op2; break;
+            case LT: r = op1 < op2; break; case GT: r = op1 > op2; break; case LE: r = op1 <= op2; break; case GE: r = op1 >= op2; break;
+            default: break;
+          }
+          st[sp++] = r;
+        }
+      }
+    }
+    const float f = st[0];
+    out[i] = f; lo = std::min(lo, f); hi = std::max(hi, f);
+  }
+  if (valueRange) { valueRange[0] = lo; valueRange[1] = hi; }
+  return EXA_OK;
+}
+
 int exa_scalar_field_magnitude(const float *x, const float *y, const float *z, size_t count, float *out, float valueRange[2])
 {
   if (!x || !y || !z || !out) { setError("exa_scalar_field_magnitude: null argument"); return EXA_ERR_INVALID; }
@@ -373,7 +441,16 @@ int exa_config_parse(const char *fileName, int scalarCompat, exa_config_t **out)
       }
       if (t == "scalar") {
         need(2);
-        if (tokens[it + 2] == "expr") return fail(EXA_ERR_INVALID, "config: 'scalar <name> expr ...' derived fields are not supported");
+        if (tokens[it + 2] == "expr") {                      // Config.cpp:113-123: tokens up to the one that ends with a quote
+          if (cfg->fields.empty()) return fail(EXA_ERR_INVALID, "config: expression before any scalar field");
+          std::vector<const char *> ex; size_t j = it + 3;
+          for (;; j++) { if (j >= tokens.size()) return fail(EXA_ERR_INVALID, "config: unterminated expression"); ex.push_back(tokens[j].c_str()); if (tokens[j].back() == '"') break; }
+          std::vector<const float *> in; for (auto &f : cfg->fields) in.push_back(f.values);
+          exa_config::Field f; f.name = tokens[it + 1]; f.count = cfg->fields[0].count; f.values = (float *)malloc(4 * (f.count ? f.count : 1));
+          int rc = exa_scalar_field_expression(in.data(), (int)in.size(), f.count, ex.data(), (int)ex.size(), f.values, f.range);
+          if (rc) { free(f.values); return fail(rc, ""); }
+          cfg->fields.push_back(f); it = j + 1; continue;
+        }
         exa_config::Field f; f.name = tokens[it + 1];
         int rc = exa_scalar_field_load((basePath + tokens[it + 2]).c_str(), scalarCompat, &f.values, &f.count, f.range);
         if (rc) return fail(rc, "");

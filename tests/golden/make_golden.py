@@ -63,6 +63,7 @@ def main():
     raw2cells_golden()
     ref_shader_golden()
     points_golden(hashes)
+    config_golden()
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
 
@@ -135,3 +136,54 @@ def points_golden(hashes):
                               "grad_sha256": hashlib.sha256(g.tobytes()).hexdigest(), "valid": int(ok.sum())}
     np.savez_compressed(os.path.join(HERE, "c1_points_head.npz"), values=v[:4096], valid=ok[:4096], grad=g[:4096])
     print("C1 1M points", hashes["C1_points_1M"])
+
+
+CONFIG_TEXT = """# expression fields (Config.cpp:113-123, ScalarField.cpp:96-230)
+scalar a a.scalars
+scalar b b.scalars
+vector v a.scalars b.scalars a.scalars
+scalar e0 expr "%0 2 ** %1 +"
+scalar e1 expr "%0 %1 < %0 %1 select"
+scalar e2 expr "%0 1 + log %1 abs sqrt * 0.25 -"
+scalar e3 expr "%2 %3 / %4 >= 3 *"
+bricks ex4.bricks
+"""
+
+
+def config_inputs(workdir):
+    g = np.load(os.path.join(HERE, "ex4.npz"))
+    open(os.path.join(workdir, "ex4.bricks"), "wb").write(g["bricks"].tobytes())
+    n = len(g["fields"][0])
+    a = (np.sin(np.arange(n) * 0.37) * 2 + 0.5).astype(np.float32)
+    b = (np.cos(np.arange(n) * 0.11) * 3 - 0.25).astype(np.float32)
+    a.tofile(os.path.join(workdir, "a.scalars"))
+    b.tofile(os.path.join(workdir, "b.scalars"))
+    p = os.path.join(workdir, "c.exa")
+    open(p, "w").write(CONFIG_TEXT)
+    return p
+
+
+def parse_ref_config(raw):
+    off, out = 4, []
+    n = int(np.frombuffer(raw[:4], "<i4")[0])
+    for _ in range(n):
+        nl = int(np.frombuffer(raw[off:off + 4], "<i4")[0]); off += 4
+        name = raw[off:off + nl].decode(); off += nl
+        cnt = int(np.frombuffer(raw[off:off + 8], "<i8")[0]); off += 8
+        rng = np.frombuffer(raw[off:off + 8], "<f4").copy(); off += 8
+        vals = np.frombuffer(raw[off:off + 4 * cnt], "<f4").copy(); off += 4 * cnt
+        out.append((name, rng, vals))
+    return out
+
+
+def config_golden():
+    import subprocess
+    with tempfile.TemporaryDirectory() as d:
+        p = config_inputs(d)
+        subprocess.check_call([os.path.join(orc.REF_DIR, "ref_config"), p, os.path.join(d, "out.bin")], stdout=subprocess.DEVNULL)
+        fields = parse_ref_config(open(os.path.join(d, "out.bin"), "rb").read())
+    out = {}
+    for i, (name, rng, vals) in enumerate(fields):
+        out["name%d" % i], out["range%d" % i], out["values%d" % i] = np.array(name), rng, vals
+        print("ref_config", name, rng, len(vals))
+    np.savez_compressed(os.path.join(HERE, "config_expr.npz"), **out)

@@ -236,3 +236,23 @@ def test_raw_to_cells_matches_reference(R, orc):
     assert len(levels) >= 3
     with pytest.raises(Exception, match="unknown format"):
         R.raw_to_cells(np.zeros((4, 4, 4), np.int16), 1.0, 2)
+
+
+def test_config_expression_fields_match_reference(R, tmp_path):
+    """`scalar <name> expr "<postfix>"` (Config.cpp:113-123, ScalarField::createFromExpression): every field
+    of the config — loaded, vector magnitude and four expressions (**, comparison + select, log/abs/sqrt,
+    division) — equals what the reference's own Config::parseConfigFile produced (tests/golden/
+    config_expr.npz, made from oracle/_ref/ref_config), values and value ranges"""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import make_golden
+    g = np.load(os.path.join(GOLDEN, "config_expr.npz"))
+    cfg = R.Config(make_golden.config_inputs(str(tmp_path)))
+    assert len(cfg.fields) == 7
+    for i, f in enumerate(cfg.fields):
+        assert f["name"] == str(g["name%d" % i])
+        assert np.array_equal(f["values"], g["values%d" % i], equal_nan=True), f["name"]
+        assert np.array_equal(np.asarray(f["valueRange"], np.float32), g["range%d" % i], equal_nan=True), f["name"]
+    open(tmp_path / "bad.exa", "w").write('scalar a a.scalars\nscalar e expr "%0 +"\n')
+    with pytest.raises(Exception, match="insufficient operands"):
+        R.Config(str(tmp_path / "bad.exa"))
