@@ -109,6 +109,19 @@ struct ScalarField {
     sf->valueRange = {range[0], range[1]};
     return sf;
   }
+  // ScalarField::createFromExpression (exa/ScalarField.cpp:96-230): postfix expression over `fields`
+  static SP createFromExpression(const std::string &fieldName, const std::vector<SP> &fields, const std::vector<std::string> &tokens)
+  {
+    if (fields.empty()) throw std::runtime_error("createFromExpression: no input fields");
+    std::vector<const float *> in; for (auto &f : fields) in.push_back(f->value.data());
+    std::vector<const char *> tk; for (auto &t : tokens) tk.push_back(t.c_str());
+    SP sf = std::make_shared<ScalarField>();
+    sf->name = fieldName; sf->value.resize(fields[0]->value.size());
+    float range[2];
+    detail::check(exa_scalar_field_expression(in.data(), (int)in.size(), sf->value.size(), tk.data(), (int)tk.size(), sf->value.data(), range));
+    sf->valueRange = {range[0], range[1]};
+    return sf;
+  }
   std::string name;
   interval<float> valueRange{0.f, 0.f};
   std::vector<float> value;
