@@ -35,6 +35,8 @@ def cases():
     yield "nb64_dups", c2, [synth.analytic_field(c2, 64, 0)], 127, True
     c = synth.nested_boxes(256, [(72, 184), (32, 224)])          # SURVEY config C1
     yield "C1", c, [synth.analytic_field(c, 256, 0)], 127, False
+    c, dom = synth.cloud_shaped(16)                               # SURVEY config C5's shape at 1/16 scale, 3 channels
+    yield "C5_scale16", c, synth.cloud_velocity(c, dom), 127, False
 
 
 def main():
@@ -97,9 +99,6 @@ def raw2cells_golden():
         print("raw2cells", i, fmt, vol.shape, len(out["scalars%d" % i]), "cells, levels", np.unique(out["cells%d" % i][:, 3]))
     np.savez_compressed(os.path.join(HERE, "raw2cells.npz"), **out)
 
-
-if __name__ == "__main__":
-    main()
 
 
 def ref_shader_golden():
@@ -187,3 +186,7 @@ def config_golden():
         out["name%d" % i], out["range%d" % i], out["values%d" % i] = np.array(name), rng, vals
         print("ref_config", name, rng, len(vals))
     np.savez_compressed(os.path.join(HERE, "config_expr.npz"), **out)
+
+
+if __name__ == "__main__":
+    main()

@@ -182,3 +182,19 @@ def test_bvh_region_query_equals_brute_force(orc, monkeypatch):
         out.append((acc.copy(), rgba.copy(), dict(st)))
     assert out[0][0].tobytes() == out[1][0].tobytes() and out[0][1].tobytes() == out[1][1].tobytes()
     assert out[0][2] == out[1][2]
+
+
+def test_c5_shaped_builder_and_abr_hash_vs_reference(orc):
+    """config C5's shape at 1/16 scale (block-structured octree, 4 levels, 3 channels): the oracle's bricks and
+    ABRs (domains, value ranges over all channels, leaf lists) hash to what the reference's own exaBuilder and
+    ExaBrickRegions::buildFrom produced (golden_hashes.json: C5_scale16)"""
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["C5_scale16"]
+    cells, dom = synth.cloud_shaped(16)
+    assert len(cells) == h["cells"]
+    fields = synth.cloud_velocity(cells, dom)
+    raw = orc.build_bricks(cells)
+    assert hashlib.sha256(raw).hexdigest() == h["bricks_sha256"]
+    bricks, ids = orc.parse_bricks(raw)
+    regions, leaf = orc.build_abr(bricks, orc.flatten_scalars(ids, fields))
+    blob = np.array([len(regions), len(leaf)], "<i4").tobytes() + regions.tobytes() + leaf.tobytes()
+    assert hashlib.sha256(blob).hexdigest() == h["abr_sha256"]
