@@ -66,6 +66,7 @@ def main():
     ref_shader_golden()
     points_golden(hashes)
     config_golden()
+    colormap_golden()
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
 
@@ -186,6 +187,30 @@ def config_golden():
         out["name%d" % i], out["range%d" % i], out["values%d" % i] = np.array(name), rng, vals
         print("ref_config", name, rng, len(vals))
     np.savez_compressed(os.path.join(HERE, "config_expr.npz"), **out)
+
+
+def colormap_cases():
+    rng = np.random.RandomState(9)
+    t = np.concatenate([np.linspace(-0.2, 1.2, 57), rng.uniform(0, 1, 200)]).astype(np.float32)
+    yield np.array([[0, 0, 0, 0], [0.5, 1, 0, 0], [1, 1, 1, 1]], np.float32), t
+    cp = np.concatenate([np.sort(rng.uniform(0, 1, 9))[:, None], rng.uniform(0, 1, (9, 3))], axis=1).astype(np.float32)
+    yield cp, t
+    yield np.array([[0.3, 0.2, 0.4, 0.6], [0.3, 0.9, 0.1, 0.5], [0.8, 0.0, 1.0, 0.25]], np.float32), t     # duplicate position
+    yield np.array([[0.5, 0.1, 0.2, 0.3]], np.float32), t                                                   # single point
+
+
+def colormap_golden():
+    """the reference's own ColorMapper::operator() (exa/ColorMapper.h:64-80) on a few control-point sets"""
+    import subprocess
+    out = {}
+    for i, (cp, t) in enumerate(colormap_cases()):
+        with tempfile.TemporaryDirectory() as d:
+            with open(os.path.join(d, "in.bin"), "wb") as f:
+                f.write(np.int32(len(cp)).tobytes() + cp.tobytes() + np.int32(len(t)).tobytes() + t.tobytes())
+            subprocess.check_call([os.path.join(orc.REF_DIR, "ref_colormap"), os.path.join(d, "in.bin"), os.path.join(d, "out.bin")])
+            out["rgb%d" % i] = np.fromfile(os.path.join(d, "out.bin"), np.float32).reshape(-1, 3)
+    np.savez_compressed(os.path.join(HERE, "colormap.npz"), **out)
+    print("ref_colormap:", len(out), "cases")
 
 
 if __name__ == "__main__":

@@ -256,3 +256,17 @@ def test_config_expression_fields_match_reference(R, tmp_path):
     open(tmp_path / "bad.exa", "w").write('scalar a a.scalars\nscalar e expr "%0 +"\n')
     with pytest.raises(Exception, match="insufficient operands"):
         R.Config(str(tmp_path / "bad.exa"))
+
+
+def test_colormapper_matches_reference(R):
+    """exa_colormap_eval == the reference's own ColorMapper::operator() (exa/ColorMapper.h:64-80, compiled in
+    place: oracle/_ref/ref_colormap -> tests/golden/colormap.npz), bit for bit: below / above the range, between
+    unevenly spaced points, at a duplicated position, with a single control point"""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import make_golden
+    g = np.load(os.path.join(GOLDEN, "colormap.npz"))
+    for i, (cp, t) in enumerate(make_golden.colormap_cases()):
+        cm = R.ColorMapper(control_points=cp)
+        mine = np.stack([cm(float(x)) for x in t])
+        assert np.array_equal(mine, g["rgb%d" % i]), "case %d: max diff %g" % (i, np.abs(mine - g["rgb%d" % i]).max())
