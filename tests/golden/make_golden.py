@@ -67,6 +67,8 @@ def main():
     points_golden(hashes)
     config_golden()
     colormap_golden()
+    builder_variants_golden(hashes)
+    json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
 
@@ -211,6 +213,30 @@ def colormap_golden():
             out["rgb%d" % i] = np.fromfile(os.path.join(d, "out.bin"), np.float32).reshape(-1, 3)
     np.savez_compressed(os.path.join(HERE, "colormap.npz"), **out)
     print("ref_colormap:", len(out), "cases")
+
+
+def builder_variant_cases():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    for kind in ("nb64_off", "nb32"):
+        cells = scenes.small_scene(kind)[0]
+        yield kind + "_sah", cells, []
+        yield kind + "_median", cells, ["--spatial-median"]
+
+
+def builder_variants_golden(hashes):
+    """exaBuilder with its kd-tree output (-kd, builder.cpp:904-907) for both builder types (builder.cpp:31-33,858-860)"""
+    import subprocess
+    out = {}
+    for name, cells, flags in builder_variant_cases():
+        with tempfile.TemporaryDirectory() as d:
+            np.ascontiguousarray(cells, np.int32).tofile(os.path.join(d, "in.cells"))
+            subprocess.check_call([os.path.join(orc.REF_DIR, "exaBuilder"), os.path.join(d, "in.cells"), "-o", os.path.join(d, "o.bricks"),
+                                   "-kd", os.path.join(d, "o.kd")] + flags, stdout=subprocess.DEVNULL)
+            b, k = open(os.path.join(d, "o.bricks"), "rb").read(), open(os.path.join(d, "o.kd"), "rb").read()
+        out[name] = {"bricks_sha256": hashlib.sha256(b).hexdigest(), "kd_sha256": hashlib.sha256(k).hexdigest(), "kd_nodes": len(k) // 12}
+        print("builder variant", name, out[name])
+    hashes["builder_variants"] = out
 
 
 if __name__ == "__main__":

@@ -270,3 +270,27 @@ def test_colormapper_matches_reference(R):
         cm = R.ColorMapper(control_points=cp)
         mine = np.stack([cm(float(x)) for x in t])
         assert np.array_equal(mine, g["rgb%d" % i]), "case %d: max diff %g" % (i, np.abs(mine - g["rgb%d" % i]).max())
+
+
+def test_builder_types_and_kd_file_match_reference(R, built_lib, orc, tmp_path):
+    """both builder types (SAH-alike default, --spatial-median) and the kd-tree file (`exaBuilder -kd`,
+    builder.cpp:904-907; 12-byte KdTreeNode, exa/KdTree.h) are byte-identical to the reference exaBuilder's
+    output (SHA-256 in golden_hashes.json; run live too when oracle/_ref is present)"""
+    import subprocess
+    import sys
+    sys.path.insert(0, GOLDEN)
+    import make_golden
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["builder_variants"]
+    for name, cells, flags in make_golden.builder_variant_cases():
+        bt = built_lib.BUILDER_SPATIAL_MEDIAN if flags else built_lib.BUILDER_SAH_ALIKE
+        b = R.ExaBricks.build(cells, builder=bt)
+        kd = b.kd_nodes.tobytes()
+        assert hashlib.sha256(b.to_bytes()).hexdigest() == h[name]["bricks_sha256"], name
+        assert hashlib.sha256(kd).hexdigest() == h[name]["kd_sha256"] and len(kd) // 12 == h[name]["kd_nodes"], name
+        b.save(str(tmp_path / "o.bricks"), str(tmp_path / "o.kd"))                    # the files the tool writes
+        assert open(tmp_path / "o.kd", "rb").read() == kd and open(tmp_path / "o.bricks", "rb").read() == b.to_bytes()
+        if orc.have_ref():
+            np.ascontiguousarray(cells, np.int32).tofile(tmp_path / "in.cells")
+            subprocess.check_call([os.path.join(orc.REF_DIR, "exaBuilder"), str(tmp_path / "in.cells"), "-o", str(tmp_path / "r.bricks"),
+                                   "-kd", str(tmp_path / "r.kd")] + flags, stdout=subprocess.DEVNULL)
+            assert open(tmp_path / "r.kd", "rb").read() == kd and open(tmp_path / "r.bricks", "rb").read() == b.to_bytes()
