@@ -3,7 +3,8 @@
 // Driver around the reference's own config loader (exa/Config.cpp:57-180 parseConfigFile, with
 // exa/ScalarField.cpp load / loadAndComputeMagnitude / createFromExpression), compiled from
 // /root/reference in place by oracle/Makefile into oracle/_ref/ref_config.  Dumps every scalar field:
-//   int32 numFields; per field: int32 nameLen; char name[]; int64 count; float range[2]; float values[count]
+//   int32 numFields; per field: int32 nameLen; char name[]; int64 count; float range[2]; float values[count];
+//   then float voxelSpaceTransform[12] (vx, vy, vz, p — Config::finalize) and float bounds[6] (Config::getBounds)
 // usage: ref_config in.exa out.bin
 #include "exa/Config.h"
 #include <cstdio>
@@ -21,6 +22,13 @@ int main(int ac, char **av)
     fwrite(&nl, 4, 1, o); fwrite(sf->name.data(), 1, nl, o); fwrite(&cnt, 8, 1, o); fwrite(r, 4, 2, o);
     fwrite(sf->value.data(), 4, sf->value.size(), o);
   }
+  cfg->finalize();
+  const affine3f &x = cfg->bricks.voxelSpaceTransform;
+  const float m[12] = {x.l.vx.x, x.l.vx.y, x.l.vx.z, x.l.vy.x, x.l.vy.y, x.l.vy.z, x.l.vz.x, x.l.vz.y, x.l.vz.z, x.p.x, x.p.y, x.p.z};
+  fwrite(m, 4, 12, o);
+  const box3f b = cfg->getBounds();
+  const float bb[6] = {b.lower.x, b.lower.y, b.lower.z, b.upper.x, b.upper.y, b.upper.z};
+  fwrite(bb, 4, 6, o);
   fclose(o);
   return 0;
 }

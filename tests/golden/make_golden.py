@@ -141,6 +141,8 @@ def points_golden(hashes):
 
 
 CONFIG_TEXT = """# expression fields (Config.cpp:113-123, ScalarField.cpp:96-230)
+remap_from 0.5 -1 2 8.5 7 6.25
+remap_to   -1.25 -1 -3  1 1.5 0.75
 scalar a a.scalars
 scalar b b.scalars
 vector v a.scalars b.scalars a.scalars
@@ -175,6 +177,7 @@ def parse_ref_config(raw):
         rng = np.frombuffer(raw[off:off + 8], "<f4").copy(); off += 8
         vals = np.frombuffer(raw[off:off + 4 * cnt], "<f4").copy(); off += 4 * cnt
         out.append((name, rng, vals))
+    out.append(("__xfm_bounds__", None, np.frombuffer(raw[off:off + 72], "<f4").copy()))
     return out
 
 
@@ -185,7 +188,9 @@ def config_golden():
         subprocess.check_call([os.path.join(orc.REF_DIR, "ref_config"), p, os.path.join(d, "out.bin")], stdout=subprocess.DEVNULL)
         fields = parse_ref_config(open(os.path.join(d, "out.bin"), "rb").read())
     out = {}
-    for i, (name, rng, vals) in enumerate(fields):
+    out["xfm"], out["bounds"] = fields[-1][2][:12], fields[-1][2][12:]
+    print("ref_config voxelSpaceTransform", out["xfm"], "bounds", out["bounds"])
+    for i, (name, rng, vals) in enumerate(fields[:-1]):
         out["name%d" % i], out["range%d" % i], out["values%d" % i] = np.array(name), rng, vals
         print("ref_config", name, rng, len(vals))
     np.savez_compressed(os.path.join(HERE, "config_expr.npz"), **out)

@@ -253,6 +253,10 @@ def test_config_expression_fields_match_reference(R, tmp_path):
         assert f["name"] == str(g["name%d" % i])
         assert np.array_equal(f["values"], g["values%d" % i], equal_nan=True), f["name"]
         assert np.array_equal(np.asarray(f["valueRange"], np.float32), g["range%d" % i], equal_nan=True), f["name"]
+    # Config::finalize / getBounds (Config.cpp:23-55) with a non-trivial remap_from / remap_to
+    assert np.array_equal(np.asarray(cfg.voxelSpaceTransform, np.float32), g["xfm"])
+    lo, hi = cfg.get_bounds()
+    assert np.array_equal(np.concatenate([lo, hi]).astype(np.float32), g["bounds"])
     open(tmp_path / "bad.exa", "w").write('scalar a a.scalars\nscalar e expr "%0 +"\n')
     with pytest.raises(Exception, match="insufficient operands"):
         R.Config(str(tmp_path / "bad.exa"))
