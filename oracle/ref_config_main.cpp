@@ -4,7 +4,8 @@
 // exa/ScalarField.cpp load / loadAndComputeMagnitude / createFromExpression), compiled from
 // /root/reference in place by oracle/Makefile into oracle/_ref/ref_config.  Dumps every scalar field:
 //   int32 numFields; per field: int32 nameLen; char name[]; int64 count; float range[2]; float values[count];
-//   then float voxelSpaceTransform[12] (vx, vy, vz, p — Config::finalize) and float bounds[6] (Config::getBounds)
+//   then float voxelSpaceTransform[12] (vx, vy, vz, p — Config::finalize) and float bounds[6] (Config::getBounds);
+//   then the `triangles` meshes (TriangleMesh::load) concatenated: int32 numVerts; float xyz[]; int32 numTris; int32 idx[] (rebased)
 // usage: ref_config in.exa out.bin
 #include "exa/Config.h"
 #include <cstdio>
@@ -29,6 +30,14 @@ int main(int ac, char **av)
   const box3f b = cfg->getBounds();
   const float bb[6] = {b.lower.x, b.lower.y, b.lower.z, b.upper.x, b.upper.y, b.upper.z};
   fwrite(bb, 4, 6, o);
+  std::vector<float> v; std::vector<int32_t> ix;
+  for (auto &m : cfg->surfaces) {
+    const int32_t base = (int32_t)(v.size() / 3);
+    for (auto &p : m->vertex) { v.push_back(p.x); v.push_back(p.y); v.push_back(p.z); }
+    for (auto &t : m->index) { ix.push_back(t.x + base); ix.push_back(t.y + base); ix.push_back(t.z + base); }
+  }
+  int32_t nv = (int32_t)(v.size() / 3), nt = (int32_t)(ix.size() / 3);
+  fwrite(&nv, 4, 1, o); fwrite(v.data(), 4, v.size(), o); fwrite(&nt, 4, 1, o); fwrite(ix.data(), 4, ix.size(), o);
   fclose(o);
   return 0;
 }

@@ -166,6 +166,15 @@ class Config:
         check(lib.exa_config_get_bounds(self.h, _p(lo), _p(hi)))
         return lo, hi
 
+    def triangles(self):
+        """Config::surfaces (`triangles <file>`, Config.cpp:165-171) -> (vertices float32[n,3], indices int32[m,3]),
+        concatenated"""
+        v, i, nv, nt = C.c_void_p(), C.c_void_p(), C.c_size_t(), C.c_size_t()
+        check(lib.exa_config_triangles(self.h, C.byref(v), C.byref(nv), C.byref(i), C.byref(nt)))
+        verts = np.frombuffer(C.string_at(v, nv.value * 12), np.float32).reshape(-1, 3).copy() if nv.value else np.zeros((0, 3), np.float32)
+        idx = np.frombuffer(C.string_at(i, nt.value * 12), np.int32).reshape(-1, 3).copy() if nt.value else np.zeros((0, 3), np.int32)
+        return verts, idx
+
 
 def simple_camera(pos, at, up, fovy_deg, width, height):
     """pos, dir00, dirDu, dirDv exactly as the viewer derives them in fp32

@@ -151,6 +151,7 @@ scalar e1 expr "%0 %1 < %0 %1 select"
 scalar e2 expr "%0 1 + log %1 abs sqrt * 0.25 -"
 scalar e3 expr "%2 %3 / %4 >= 3 *"
 bricks ex4.bricks
+triangles m.tris
 """
 
 
@@ -162,6 +163,11 @@ def config_inputs(workdir):
     b = (np.cos(np.arange(n) * 0.11) * 3 - 0.25).astype(np.float32)
     a.tofile(os.path.join(workdir, "a.scalars"))
     b.tofile(os.path.join(workdir, "b.scalars"))
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    with open(os.path.join(workdir, "m.tris"), "wb") as f:                 # two meshes in one file (TriangleMesh.cpp:21-68)
+        for v, i in (scenes.uv_sphere([1, 2, 3], 2.0, 8, 4), (np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0]], np.float32), np.array([[0, 1, 2]], np.int32))):
+            f.write(np.int32(len(v)).tobytes() + v.tobytes() + np.int32(len(i)).tobytes() + i.tobytes())
     p = os.path.join(workdir, "c.exa")
     open(p, "w").write(CONFIG_TEXT)
     return p
@@ -177,7 +183,12 @@ def parse_ref_config(raw):
         rng = np.frombuffer(raw[off:off + 8], "<f4").copy(); off += 8
         vals = np.frombuffer(raw[off:off + 4 * cnt], "<f4").copy(); off += 4 * cnt
         out.append((name, rng, vals))
-    out.append(("__xfm_bounds__", None, np.frombuffer(raw[off:off + 72], "<f4").copy()))
+    out.append(("__xfm_bounds__", None, np.frombuffer(raw[off:off + 72], "<f4").copy())); off += 72
+    nv = int(np.frombuffer(raw[off:off + 4], "<i4")[0]); off += 4
+    verts = np.frombuffer(raw[off:off + 12 * nv], "<f4").reshape(-1, 3).copy(); off += 12 * nv
+    nt = int(np.frombuffer(raw[off:off + 4], "<i4")[0]); off += 4
+    idx = np.frombuffer(raw[off:off + 12 * nt], "<i4").reshape(-1, 3).copy()
+    out.append(("__mesh__", verts, idx))
     return out
 
 
@@ -188,9 +199,10 @@ def config_golden():
         subprocess.check_call([os.path.join(orc.REF_DIR, "ref_config"), p, os.path.join(d, "out.bin")], stdout=subprocess.DEVNULL)
         fields = parse_ref_config(open(os.path.join(d, "out.bin"), "rb").read())
     out = {}
-    out["xfm"], out["bounds"] = fields[-1][2][:12], fields[-1][2][12:]
-    print("ref_config voxelSpaceTransform", out["xfm"], "bounds", out["bounds"])
-    for i, (name, rng, vals) in enumerate(fields[:-1]):
+    out["xfm"], out["bounds"] = fields[-2][2][:12], fields[-2][2][12:]
+    out["mesh_vertices"], out["mesh_indices"] = fields[-1][1], fields[-1][2]
+    print("ref_config voxelSpaceTransform", out["xfm"], "bounds", out["bounds"], "mesh", out["mesh_vertices"].shape, out["mesh_indices"].shape)
+    for i, (name, rng, vals) in enumerate(fields[:-2]):
         out["name%d" % i], out["range%d" % i], out["values%d" % i] = np.array(name), rng, vals
         print("ref_config", name, rng, len(vals))
     np.savez_compressed(os.path.join(HERE, "config_expr.npz"), **out)

@@ -257,6 +257,8 @@ def test_config_expression_fields_match_reference(R, tmp_path):
     assert np.array_equal(np.asarray(cfg.voxelSpaceTransform, np.float32), g["xfm"])
     lo, hi = cfg.get_bounds()
     assert np.array_equal(np.concatenate([lo, hi]).astype(np.float32), g["bounds"])
+    v, i = cfg.triangles()                                   # `triangles <file>` (Config.cpp:165-171, TriangleMesh::load)
+    assert np.array_equal(v, g["mesh_vertices"]) and np.array_equal(i, g["mesh_indices"]) and len(i) > 40
     open(tmp_path / "bad.exa", "w").write('scalar a a.scalars\nscalar e expr "%0 +"\n')
     with pytest.raises(Exception, match="insufficient operands"):
         R.Config(str(tmp_path / "bad.exa"))
