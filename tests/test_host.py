@@ -164,6 +164,30 @@ def test_no_cpu_fallback(R, built_lib):
     assert e.value.code == built_lib.EXA_ERR_CUDA
 
 
+def test_product_never_touches_the_oracle():
+    """the oracle is test infrastructure: nothing in the package, its CUDA/C++ sources, the public headers or
+    tools/ imports, includes, links or executes anything under oracle/; bench.py does so only in its two
+    CPU-baseline legs"""
+    root = ROOT
+    pat = re.compile(r"(from\s+oracle|import\s+oracle|import\s+orc\b|oracle/|oracle\.h|liboracle|\borc\.)")
+    files = []
+    for d in ("owlexabrick_b200", "include", "tools"):
+        for base, _, names in os.walk(os.path.join(root, d)):
+            files += [os.path.join(base, n) for n in names if n.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp", ".inl"))]
+    assert len(files) > 15
+    for f in files:
+        hits = [ln for ln in open(f, errors="replace") if pat.search(ln) and "#" not in ln.split("oracle")[0] and "//" not in ln.split("oracle")[0] and "*" not in ln.split("oracle")[0][:4]]
+        assert not hits, (f, hits[:3])
+    # bench.py: the oracle is imported in exactly two places — the reference arm and, in the product arm, the
+    # cpu_baseline block that runs AFTER the timed region and is skipped under torchrun / --no-cpu-baseline
+    src = open(os.path.join(root, "bench.py")).read().split("\n")
+    imports = [i for i, ln in enumerate(src) if re.search(r"from oracle import|import orc\b", ln)]
+    assert len(imports) == 2, imports
+    owner = lambda i: next(re.match(r"def (\w+)", src[j]).group(1) for j in range(i, -1, -1) if src[j].startswith("def "))
+    assert [owner(i) for i in imports] == ["run_reference", "run_product"]
+    assert "not args.no_cpu_baseline" in src[imports[1] - 1] and "world == 1" in src[imports[1] - 1]
+
+
 def test_camera_matches_reference_math(R):
     pos, d00, du, dv = R.simple_camera([0, 0, 5], [0, 0, 0], [0, 1, 0], 90.0, 200, 100)
     # fovy 90, focal 5 -> screen height 10, width 20; lower-left = (-10,-5,-5)
