@@ -110,7 +110,7 @@ def ref_shader_golden():
     import ref_shader_cases as RC
     assert orc.have_ref_shader(), "run `make -C oracle ref` first"
     out = {}
-    for name, kind, channels, mlw, configure in RC.cases():
+    for name, kind, channels, mlw, configure in RC.cases(extra=True):
         raw, fields, dom, _ = RC.build(orc, kind, channels, mlw)
         fd = RC.frame(dom, channels, configure)
         acc0 = RC.start_accum(name) if fd.frame_id > 0 else None

@@ -24,8 +24,9 @@ def _traces(dom):
     return tr
 
 
-def cases():
-    """-> name, scene kind, channels, max leaf width, configure(fd, dom)"""
+def cases(extra=False):
+    """-> name, scene kind, channels, max leaf width, configure(fd, dom).  extra=True adds the frames that pin the
+    oracle only (tests/test_oracle_pinned.py); tests/test_gpu_pinned_cases.py renders the first 15."""
     def base(fd, dom):
         pass
 
@@ -104,6 +105,55 @@ def cases():
     yield "cones", "nb32", 1, 127, cones
     yield "cones_ao_iso", "nb32", 1, 127, cones_ao_iso
     yield "progressive", "nb32", 1, 127, progressive
+    if not extra:
+        return
+
+    def xfm_world(fd, dom):
+        fd.xfm = np.array([2, 0, 0, 0, 2, 0, 0, 0, 2, 1.5, -2.0, 0.5], np.float32)
+        fd.cam = default_camera([-0.75, 1.0, -0.25], [dom / 2 - 0.75, dom / 2 + 1.0, dom / 2 - 0.25], W, H)
+        fd.world = ((-0.75, 1.0, -0.25), (dom / 2 - 0.75, dom / 2 + 1.0, dom / 2 - 0.25))
+
+    def contour_ch1_xfm(fd, dom):                        # plane classified by channel 1, world != voxel space
+        xfm_world(fd, dom)
+        fd.contour = [(1, (0.2, 1.0, 0.1), 0.55, 1), OFF, (1, (0.0, 0.0, 1.0), 0.35, 1)]
+        fd.opacity_scale = 0.03
+
+    def iso_ch1_ao(fd, dom):                             # AO with the iso-surface as the only occluder
+        fd.iso = [(0, 0.0, 0), (1, 0.55, 1)]
+        fd.ao = (1, 7.0)
+        fd.opacity_scale = 0.02
+
+    def contour_ao_clip(fd, dom):
+        fd.contour = [(1, (1.0, 0.2, 0.0), 0.5, 0), OFF, OFF]
+        fd.ao = (1, 5.0)
+        fd.iso = [(1, 0.7, 0), (0, 0.0, 0)]
+        fd.clip = ((dom * 0.1, dom * 0.15, dom * 0.05), (dom * 0.9, dom * 0.8, dom * 0.95))
+        fd.opacity_scale = 0.02
+
+    def cones_xfm_2ch(fd, dom):                          # cones live in world space
+        xfm_world(fd, dom)
+        fd.traces = ((_traces(dom) - np.array([1.5, -2.0, 0.5], np.float32)) / 2).astype(np.float32)
+        fd.traces[3, 9:] = 2e10
+        fd.current_timestep = 9
+        fd.opacity_scale = 0.01
+
+    def iso_inside(fd, dom):
+        inside(fd, dom)
+        fd.iso = [(1, 0.45, 0), (0, 0.0, 0)]
+        fd.opacity_scale = 0.01
+
+    def progressive7_dt(fd, dom):
+        fd.frame_id = 7
+        fd.dt = 0.8
+        fd.grad_dvr = False
+        fd.opacity_scale = 0.1
+
+    yield "x_contour_ch1_xfm", "nb32", 2, 127, contour_ch1_xfm
+    yield "x_iso_ch1_ao", "nb64_off", 2, 127, iso_ch1_ao
+    yield "x_contour_ao_clip", "nb32", 1, 127, contour_ao_clip
+    yield "x_cones_xfm_2ch", "nb32", 2, 127, cones_xfm_2ch
+    yield "x_iso_camera_inside", "nb64_off", 1, 127, iso_inside
+    yield "x_progressive7_dt", "nb64_off", 1, 9, progressive7_dt
 
 
 def build(orc, kind, channels, mlw):

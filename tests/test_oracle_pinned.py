@@ -20,7 +20,7 @@ import pytest
 from conftest import GOLDEN
 import ref_shader_cases as RC
 
-CASES = list(RC.cases())
+CASES = list(RC.cases(extra=True))
 
 
 @pytest.fixture(scope="module")
