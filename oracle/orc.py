@@ -219,6 +219,9 @@ def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None):
         if frame.numTraces > 0 and frame.traces:
             n = frame.numTraces * frame.numTimesteps * 3
             fh.write(np.ctypeslib.as_array(frame.traces, shape=(n,)).astype(np.float32).tobytes())
+        if frame.numMeshVerts > 0 and frame.numMeshTris > 0:
+            fh.write(np.ctypeslib.as_array(frame.meshVerts, shape=(frame.numMeshVerts * 3,)).astype(np.float32).tobytes())
+            fh.write(np.ctypeslib.as_array(frame.meshIndex, shape=(frame.numMeshTris * 3,)).astype(np.int32).tobytes())
     W, H = frame.width, frame.height
     if accum is not None:                       # progressive: the previous sum is read from out.bin
         with open(of, "wb") as fh:

@@ -26,6 +26,18 @@ namespace exa { extern "C" { LaunchParams optixLaunchParams; } }
 
 using namespace exa;
 
+// stand-in for OptiX's built-in triangle intersection (not in the reference's source): the reference's own
+// intersectRayTriangle (exabrick.cu:1316-1343) on triangle primID; hits strictly after tmin
+static void intersect_Triangles()
+{
+  const SurfaceGeomData &self = owl::getProgramData<SurfaceGeomData>();
+  const vec3i idx = self.indexBuffer[optixGetPrimitiveIndex()];
+  const vec3f A = self.vertexBuffer[idx.x], B = self.vertexBuffer[idx.y], C = self.vertexBuffer[idx.z];
+  owl::Ray ray(vec3f(optixGetWorldRayOrigin()), vec3f(optixGetWorldRayDirection()), optixGetRayTmin(), optixGetRayTmax());
+  const float t = intersectRayTriangle(ray, A, B - A, C - A);
+  if (t > optixGetRayTmin()) optixReportIntersection(t, 0);
+}
+
 static std::vector<float> readFloats(const char *fn)
 {
   FILE *f = fopen(fn, "rb");
@@ -67,12 +79,17 @@ int main(int ac, char **av)
   // ---- frame description ------------------------------------------------------------------
   OrcFrame of;
   std::vector<float> traces;
+  std::vector<vec3f> meshVerts; std::vector<vec3i> meshIndex;
   {
     FILE *f = fopen(av[2], "rb");
     if (!f || fread(&of, sizeof(of), 1, f) != 1) { fprintf(stderr, "cannot read %s\n", av[2]); return 1; }
     if (of.numTraces > 0) {
       traces.resize((size_t)of.numTraces * of.numTimesteps * 3);
       if (fread(traces.data(), 4, traces.size(), f) != traces.size()) { fprintf(stderr, "short traces\n"); return 1; }
+    }
+    if (of.numMeshVerts > 0 && of.numMeshTris > 0) {         // then the triangle meshes: vec3f verts[], vec3i index[]
+      meshVerts.resize(of.numMeshVerts); meshIndex.resize(of.numMeshTris);
+      if (fread(meshVerts.data(), 12, meshVerts.size(), f) != meshVerts.size() || fread(meshIndex.data(), 12, meshIndex.size(), f) != meshIndex.size()) { fprintf(stderr, "short mesh\n"); return 1; }
     }
     fclose(f);
   }
@@ -151,7 +168,12 @@ int main(int ac, char **av)
     for (size_t i = 0; i + 1 < gs.bounds.size(); i++) bounds_Streamline(&sd, gs.bounds[i], (int)i);
     gs.bounds.back() = box3f();
   }
-  // shim::geoms[4] (surfaceModel: triangle meshes) stays empty
+  // surfaceModel: the `surfaces` meshes (OptixRenderer.cpp:554-612).  OptiX's built-in triangle test has no source;
+  // intersect_Triangles (above) stands in for it with the reference's own intersectRayTriangle, and the
+  // reference's closest-hit program SurfaceBVH (:420-433) runs on the winner
+  static SurfaceGeomData md; md.vertexBuffer = meshVerts.data(); md.indexBuffer = meshIndex.data();
+  shim::Geom &gm = shim::geoms[4]; gm.programData = &md; gm.intersect = intersect_Triangles; gm.closestHit = closesthit_SurfaceBVH;
+  gm.bounds.assign(meshIndex.size(), box3f(vec3f(0.f), vec3f(1.f)));      // non-empty: every triangle is tested
 
   // ---- point mode (ORC_POINTS=file of n x {x,y,z} floats, ORC_CHANNEL=c): the reference's reconstruction at
   // arbitrary points exactly as samplePointWithInfRay does it (exabrick.cu:818-830: region query with a ray of

@@ -44,7 +44,7 @@ using std::max;
 namespace shim {
   struct Ctx {
     owl::common::vec3f org, dir; float tmin = 0.f, tmax = 0.f;
-    int primID = 0; void *prd = nullptr; const void *programData = nullptr;
+    int primID = 0, hitPrim = -1; void *prd = nullptr; const void *programData = nullptr;
     owl::common::vec2i launchIndex, launchDims;
   };
   extern thread_local Ctx ctx;
@@ -81,6 +81,7 @@ inline bool optixReportIntersection(float t, unsigned)
 {
   if (!(t >= shim::ctx.tmin && t < shim::ctx.tmax)) return false;
   shim::ctx.tmax = t;
+  shim::ctx.hitPrim = shim::ctx.primID;
   return true;
 }
 
@@ -104,12 +105,16 @@ namespace owl {
     const shim::Geom &g = shim::geoms[handle];
     const shim::Ctx saved = shim::ctx;
     shim::ctx.org = ray.origin; shim::ctx.dir = ray.direction; shim::ctx.tmin = ray.tmin; shim::ctx.tmax = ray.tmax;
-    shim::ctx.prd = &prd; shim::ctx.programData = g.programData;
+    shim::ctx.prd = &prd; shim::ctx.programData = g.programData; shim::ctx.hitPrim = -1;
     for (size_t i = 0; i < g.bounds.size(); i++) {
       const common::box3f &b = g.bounds[i];
       if (b.lower.x > b.upper.x || b.lower.y > b.upper.y || b.lower.z > b.upper.z) continue;   /* empty: never reported by a BVH */
       shim::ctx.primID = (int)i;
       g.intersect();
+    }
+    if (g.closestHit && shim::ctx.hitPrim >= 0) {            /* closest-hit program on the winner: tmax is its t */
+      shim::ctx.primID = shim::ctx.hitPrim;
+      g.closestHit();
     }
     shim::ctx = saved;
   }

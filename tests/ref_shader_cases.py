@@ -148,6 +148,22 @@ def cases(extra=False):
         fd.grad_dvr = False
         fd.opacity_scale = 0.1
 
+    def mesh(fd, dom):                                   # `surfaces` triangle meshes, closest-hit program SurfaceBVH
+        v1, i1 = scenes.uv_sphere([dom * 0.45, dom * 0.5, dom * 0.55], dom * 0.2, 24, 12)
+        v2, i2 = scenes.uv_sphere([dom * 0.8, dom * 0.7, dom * 0.3], dom * 0.12, 12, 6)
+        fd.mesh = (np.concatenate([v1, v2]), np.concatenate([i1, i2 + len(v1)]))
+        fd.opacity_scale = 0.03
+
+    def mesh_ao_iso_cones(fd, dom):                      # every surface type at once, occluding each other
+        mesh(fd, dom)
+        cones(fd, dom)
+        fd.iso = [(1, 0.8, 0), (0, 0.0, 0)]
+        fd.contour = [OFF, (1, (0.0, 1.0, 0.3), 0.3, 0), OFF]
+        fd.ao = (1, 8.0)
+        fd.opacity_scale = 0.02
+
+    yield "x_mesh", "nb64_off", 1, 127, mesh
+    yield "x_mesh_ao_iso_cones_contour", "nb32", 1, 127, mesh_ao_iso_cones
     yield "x_contour_ch1_xfm", "nb32", 2, 127, contour_ch1_xfm
     yield "x_iso_ch1_ao", "nb64_off", 2, 127, iso_ch1_ao
     yield "x_contour_ao_clip", "nb32", 1, 127, contour_ao_clip

@@ -1,7 +1,7 @@
 """CPU known-answer tests of the oracle's surface pass (contour planes, streamline cones, ambient
 occlusion; programs/exabrick.cu:441-573, 1267-1406, 1476-1529, 1604-1652).  The reference holds
-no vectors for these (parity unpinned by reference outputs): the oracle is pinned by what the
-maths implies."""
+no vectors for these; what the maths implies is checked here, and tests/test_oracle_pinned.py pins the
+same pass bit for bit against the reference's own device source compiled as C++."""
 import numpy as np
 
 import scenes
