@@ -121,6 +121,8 @@ def ref_shader_golden():
     cells, fields, dom, seeds, T, steplen = RC.tracer_case()
     with tempfile.TemporaryDirectory() as d:
         out["tracer"] = orc.ref_trace(orc.build_bricks(cells), fields, seeds, T, (0, 1, 2), steplen, [0, 0, 0], [dom] * 3, d)
+        ch, sl, lo, hi = RC.tracer_case_b()
+        out["tracer_b"] = orc.ref_trace(orc.build_bricks(cells), fields, seeds, T, ch, sl, lo, hi, d)
     print("ref_shader tracer: dead vertices", int((out["tracer"][..., 0] >= 2e10).sum()), "of", out["tracer"].shape[0] * T)
     np.savez_compressed(os.path.join(HERE, "ref_shader_frames.npz"), **out)
 

@@ -206,3 +206,9 @@ def tracer_case():
     vz = (0.3 + 0.002 * c[:, 2]).astype(np.float32)
     seeds = synth.random_points(64, [10, 10, 4], [54, 54, 20], seed=11)
     return cells, [vx, vy, vz], dom, seeds, 60, 1.3
+
+
+def tracer_case_b():
+    """same flow: permuted tracer channels, backward integration (negative step), world bounds inside the volume
+    -> channels, steplen, lo, hi"""
+    return (2, 0, 1), -0.7, [4, 6, 2], [60, 58, 40]

@@ -92,6 +92,10 @@ def test_tracer_equals_reference_compute_traces(orc, golden):
         with tempfile.TemporaryDirectory() as d:
             r = orc.ref_trace(raw, fields, seeds, T, (0, 1, 2), steplen, [0, 0, 0], [dom] * 3, d)
         assert np.array_equal(r, golden["tracer"])
+    ch, sl, lo, hi = RC.tracer_case_b()                  # permuted channels, backward, bounds inside the volume
+    o = orc.Scene(bricks, sc, regions, leaf).trace(seeds, T, ch, sl, lo, hi)
+    assert np.array_equal(o, golden["tracer_b"])
+    assert 0.2 * o.shape[0] * T < (o[..., 0] < 2e10).sum() < o.shape[0] * T
 
 
 def test_reconstruction_1m_points_c1_equals_reference(orc):
