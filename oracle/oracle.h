@@ -19,7 +19,7 @@
  *     and the RK4 tracer: the reference's DEVICE source programs/exabrick.cu compiled as plain
  *     C++ (ref_shader_main.cpp + ref_shim/shader_shim.h supply the OptiX/OWL device API on the
  *     host) — the oracle reproduces its accumulation buffers, RGBA8 frames and trace vertices
- *     bit for bit on 23 frames + 1 tracer run (tests/test_oracle_pinned.py, golden vectors in
+ *     bit for bit on 24 frames + 1 tracer run (tests/test_oracle_pinned.py, golden vectors in
  *     tests/golden/ref_shader_frames.npz).  Two things in that comparison are not reference code:
  *     OptiX's closest-hit search (brute force in the shim) and the CUDA texture fetch of the
  *     transfer function (a linear-filtered 128-texel table with a full-precision weight).

@@ -162,6 +162,11 @@ def cases(extra=False):
         fd.ao = (1, 8.0)
         fd.opacity_scale = 0.02
 
+    def colormap_second(fd, dom):                        # !multiFieldDvr: iso on channel 0 coloured by channel 1 through XF 0
+        fd.colormap_second = True
+        fd.iso = [(1, 0.5, 0), (1, 0.75, 0)]
+        fd.opacity_scale = 0.02
+
     yield "x_mesh", "nb64_off", 1, 127, mesh
     yield "x_mesh_ao_iso_cones_contour", "nb32", 1, 127, mesh_ao_iso_cones
     yield "x_contour_ch1_xfm", "nb32", 2, 127, contour_ch1_xfm
@@ -170,6 +175,7 @@ def cases(extra=False):
     yield "x_cones_xfm_2ch", "nb32", 2, 127, cones_xfm_2ch
     yield "x_iso_camera_inside", "nb64_off", 1, 127, iso_inside
     yield "x_progressive7_dt", "nb64_off", 1, 9, progressive7_dt
+    yield "x_iso_colormap_second_channel", "nb32", 2, 127, colormap_second
 
 
 def build(orc, kind, channels, mlw):

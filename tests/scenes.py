@@ -44,6 +44,7 @@ class FrameDesc:
         self.current_timestep = 0
         self.world = ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
         self.mesh = None                                 # (vertices float32[n,3], indices int32[m,3]), world space
+        self.colormap_second = False                     # oracle only: the reference's !multiFieldDvr mode (OptixRenderer.cpp:277-283)
 
     def to_orc(self, orc):
         f = orc.OrcFrame()
@@ -54,7 +55,7 @@ class FrameDesc:
         f.xf_vz[:] = [float(x) for x in self.xfm[6:9]]
         f.xf_p[:] = [float(x) for x in self.xfm[9:12]]
         f.width, f.height, f.frameID, f.dt = self.width, self.height, self.frame_id, self.dt
-        f.numPrimaryChannels, f.colormapChannel = self.num_channels, 0
+        f.numPrimaryChannels, f.colormapChannel = (1, 1) if self.colormap_second else (self.num_channels, 0)
         f.gradientShadingDVR, f.gradientShadingISO = int(self.grad_dvr), int(self.grad_iso)
         f.spaceSkipping = int(self.space_skipping)
         f.xfOpacityScale = self.opacity_scale
