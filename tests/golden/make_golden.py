@@ -68,6 +68,7 @@ def main():
     config_golden()
     colormap_golden()
     builder_variants_golden(hashes)
+    fuzz_golden(hashes)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
@@ -256,6 +257,22 @@ def builder_variants_golden(hashes):
         out[name] = {"bricks_sha256": hashlib.sha256(b).hexdigest(), "kd_sha256": hashlib.sha256(k).hexdigest(), "kd_nodes": len(k) // 12}
         print("builder variant", name, out[name])
     hashes["builder_variants"] = out
+
+
+def fuzz_golden(hashes):
+    """reference exaBuilder + ExaBrickRegions::buildFrom on the random octree AMR of tests/scenes.py:random_amr"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    hashes["fuzz"] = {}
+    for seed in range(12):
+        cells, mlw, fields = scenes.random_amr(seed)
+        with tempfile.TemporaryDirectory() as d:
+            rb = orc.ref_build_bricks(cells, d, None if mlw == 127 else mlw)
+            rr, rl = orc.parse_abr(orc.ref_build_abr(rb, fields, d))
+        hashes["fuzz"][str(seed)] = {"cells": len(cells), "max_leaf_width": mlw, "channels": len(fields), "regions": len(rr),
+                                     "bricks_sha256": hashlib.sha256(rb).hexdigest(),
+                                     "abr_sha256": hashlib.sha256(rr.tobytes() + rl.tobytes()).hexdigest()}
+        print("fuzz", seed, hashes["fuzz"][str(seed)])
 
 
 if __name__ == "__main__":

@@ -162,3 +162,40 @@ def small_scene(kind="nb32", channels=1):
         raise ValueError(kind)
     fields = [synth.analytic_field(cells, dom, c) for c in range(channels)]
     return cells, fields, dom
+
+
+def random_amr(seed):
+    """random octree AMR for the builder / ABR fuzz (tests/test_fuzz_vs_reference.py): domain 16^3 or 32^3 of
+    level-1..3 root cells, each refined recursively with a random probability; optionally ragged (missing root
+    cells), shifted to negative coordinates, shuffled, with duplicated cells -> cells int32[n,4], max leaf width,
+    fields"""
+    rng = np.random.RandomState(seed)
+    dom_log, max_level = int(rng.choice([4, 5])), int(rng.choice([1, 2, 3]))
+    cells = []
+
+    def rec(x, y, z, l, p):
+        if l > 0 and rng.rand() < p:
+            h = 1 << (l - 1)
+            for dz in (0, h):
+                for dy in (0, h):
+                    for dx in (0, h):
+                        rec(x + dx, y + dy, z + dz, l - 1, p * 0.8)
+        else:
+            cells.append((x, y, z, l))
+    top = 1 << max_level
+    n = (1 << dom_log) // top
+    holes = rng.rand() < 0.5
+    for z in range(n):
+        for y in range(n):
+            for x in range(n):
+                if holes and rng.rand() < 0.15:
+                    continue
+                rec(x * top, y * top, z * top, max_level, rng.uniform(0.2, 0.8))
+    c = np.array(cells, np.int32)
+    c[:, :3] += (rng.randint(-3, 4, 3) * top).astype(np.int32)
+    c = c[rng.permutation(len(c))]
+    if rng.rand() < 0.5:
+        c = np.concatenate([c, c[rng.randint(0, len(c), 50)]])
+    mlw = [127, 3, 8, 17][rng.randint(4)]
+    fields = [rng.uniform(-1, 1, len(c)).astype(np.float32) for _ in range(rng.randint(1, 3))]
+    return c, mlw, fields
