@@ -69,6 +69,7 @@ def main():
     colormap_golden()
     builder_variants_golden(hashes)
     fuzz_golden(hashes)
+    fuzz_frames_golden(hashes)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
@@ -273,6 +274,20 @@ def fuzz_golden(hashes):
                                      "bricks_sha256": hashlib.sha256(rb).hexdigest(),
                                      "abr_sha256": hashlib.sha256(rr.tobytes() + rl.tobytes()).hexdigest()}
         print("fuzz", seed, hashes["fuzz"][str(seed)])
+
+
+def fuzz_frames_golden(hashes):
+    """the reference shader's frames on tests/scenes.py:random_amr_frame"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    hashes["fuzz_frames"] = {}
+    for seed in range(8):
+        cells, mlw, fields, fd = scenes.random_amr_frame(seed)
+        with tempfile.TemporaryDirectory() as d:
+            acc, rgba = orc.ref_render(orc.ref_build_bricks(cells, d, None if mlw == 127 else mlw), fields, fd.to_orc(orc), d)
+        hashes["fuzz_frames"][str(seed)] = {"lit_pixels": int((acc[..., :3].max(axis=-1) > 0.02).sum()),
+                                            "frame_sha256": hashlib.sha256(acc.tobytes() + rgba.tobytes()).hexdigest()}
+        print("fuzz frame", seed, hashes["fuzz_frames"][str(seed)])
 
 
 if __name__ == "__main__":

@@ -199,3 +199,24 @@ def random_amr(seed):
     mlw = [127, 3, 8, 17][rng.randint(4)]
     fields = [rng.uniform(-1, 1, len(c)).astype(np.float32) for _ in range(rng.randint(1, 3))]
     return c, mlw, fields
+
+
+def random_amr_frame(seed, W=48, H=32):
+    """a frame over random_amr(seed) with smooth fields: DVR, + iso-surface (odd seeds), + contour plane (seed % 3 == 0),
+    + AO (seed % 4 == 1) -> cells, max leaf width, fields, FrameDesc"""
+    from owlexabrick_b200.renderer import default_camera
+    cells, mlw, fields = random_amr(seed)
+    c = cells[:, :3] + 0.5 * (1 << cells[:, 3:4])
+    lo, hi = cells[:, :3].min(0).astype(np.float32), (cells[:, :3] + (1 << cells[:, 3:4])).max(0).astype(np.float32)
+    u = (c - lo) / (hi - lo)
+    fields = [(0.5 + 0.5 * np.sin(3 * u[:, 0] + seed) * np.cos(2.5 * u[:, 1]) * np.cos(2 * u[:, 2])).astype(np.float32) for _ in fields]
+    fd = FrameDesc(W, H, default_camera(lo, hi, W, H), len(fields))
+    fd.world = (tuple(float(x) for x in lo), tuple(float(x) for x in hi))
+    fd.opacity_scale = 0.05
+    if seed % 2:
+        fd.iso = [(1, 0.5, 0), (0, 0.0, 0)]
+    if seed % 3 == 0:
+        fd.contour = [(1, (1.0, 0.3, 0.1), 0.5, 0), (0, (1.0, 0.0, 0.0), 0.5, 0), (0, (1.0, 0.0, 0.0), 0.5, 0)]
+    if seed % 4 == 1:
+        fd.ao = (1, 4.0)
+    return cells, mlw, fields, fd

@@ -3,7 +3,11 @@ widths 3 / 8 / 17 / 127, 1-2 channels) against the reference's own exaBuilder an
 (builder/builder.cpp, exa/Regions.cpp compiled in place): the product's host builder, the oracle's builder and
 the oracle's ABR build must be bit-identical.  SHA-256 of the reference outputs for the seeds below are in
 tests/golden/golden_hashes.json["fuzz"] (tests/golden/make_golden.py:fuzz_golden); with oracle/_ref present the
-reference binaries are also run live on further seeds."""
+reference binaries are also run live on further seeds.
+
+The same for frames: on those random scenes (ragged domains with holes: rays leave and re-enter the volume) the
+oracle's DVR / iso / contour-plane / AO frame is bit-identical to the reference's device source compiled as C++
+(oracle/_ref/ref_shader) — SHA-256 of the reference's accumulation buffer + RGBA8 frame under ["fuzz_frames"]."""
 import hashlib
 import json
 import os
@@ -55,3 +59,33 @@ def test_random_amr_equals_reference_live(R, orc, seed):
     ob, pb, regions, leaf = _ours(R, orc, cells, mlw, fields)
     assert ob == rb and pb == rb
     assert regions.tobytes() == rr.tobytes() and leaf.tobytes() == rl.tobytes()
+
+
+def _oracle_frame(orc, seed, monkeypatch):
+    cells, mlw, fields, fd = scenes.random_amr_frame(seed)
+    raw = orc.build_bricks(cells, mlw)
+    bricks, ids = orc.parse_bricks(raw)
+    sc = orc.flatten_scalars(ids, fields)
+    regions, leaf = orc.build_abr(bricks, sc)
+    monkeypatch.setenv("ORC_RND_ARGS_RTL", "1")          # g++'s argument order, as in tests/test_oracle_pinned.py
+    acc, rgba, _ = orc.Scene(bricks, sc, regions, leaf).render(fd.to_orc(orc))
+    return raw, fields, fd, acc, rgba
+
+
+@pytest.mark.parametrize("seed", SEEDS[:8])
+def test_random_amr_frame_equals_reference_shader_golden(orc, seed, monkeypatch):
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["fuzz_frames"][str(seed)]
+    _, _, _, acc, rgba = _oracle_frame(orc, seed, monkeypatch)
+    assert int((acc[..., :3].max(axis=-1) > 0.02).sum()) == h["lit_pixels"]
+    assert hashlib.sha256(acc.tobytes() + rgba.tobytes()).hexdigest() == h["frame_sha256"]
+
+
+@pytest.mark.parametrize("seed", [101, 103, 105, 108])
+def test_random_amr_frame_equals_reference_shader_live(orc, seed, monkeypatch):
+    if not orc.have_ref_shader():
+        pytest.skip("oracle/_ref/ref_shader not built (needs /root/reference)")
+    raw, fields, fd, acc, rgba = _oracle_frame(orc, seed, monkeypatch)
+    with tempfile.TemporaryDirectory() as d:
+        racc, rrgba = orc.ref_render(raw, fields, fd.to_orc(orc), d)
+    assert (acc != racc).sum() == 0 and (rgba != rrgba).sum() == 0
+    assert (racc[..., :3].max(axis=-1) > 0.02).sum() > 100
