@@ -92,11 +92,9 @@ def test_random_amr_frame_equals_reference_shader_live(orc, seed, monkeypatch):
 
 
 # ---- CUDA path on the same random scenes ------------------------------------------------------------
-# Written after round 1's GPU budget was spent: not yet run on a B200, so it is opt-in (EXA_GPU_FUZZ=1) until
-# it has been; round 2 runs it first.  What it adds over tests/test_gpu_*.py: domains with
-# holes (rays leave and re-enter the volume), negative coordinates, leaf widths 3 / 8 / 17.
+# What it adds over tests/test_gpu_*.py: domains with holes (rays leave and re-enter the volume), negative
+# coordinates, leaf widths 3 / 8 / 17.  First B200 run: profiles/pytest_gpu_r01_fuzz.log (12 passed).
 @pytest.mark.gpu
-@pytest.mark.skipif(os.environ.get("EXA_GPU_FUZZ") != "1", reason="opt-in until first run on a GPU: EXA_GPU_FUZZ=1")
 @pytest.mark.parametrize("seed", SEEDS)
 def test_cuda_path_on_random_amr(R, orc, seed):
     import numpy as np
