@@ -70,6 +70,7 @@ def main():
     builder_variants_golden(hashes)
     fuzz_golden(hashes)
     fuzz_frames_golden(hashes)
+    fuzz_points_golden(hashes)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
 
@@ -288,6 +289,19 @@ def fuzz_frames_golden(hashes):
         hashes["fuzz_frames"][str(seed)] = {"lit_pixels": int((acc[..., :3].max(axis=-1) > 0.02).sum()),
                                             "frame_sha256": hashlib.sha256(acc.tobytes() + rgba.tobytes()).hexdigest()}
         print("fuzz frame", seed, hashes["fuzz_frames"][str(seed)])
+
+
+def fuzz_points_golden(hashes):
+    """the reference's reconstruction at the points of tests/scenes.py:random_amr_points"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import scenes
+    hashes["fuzz_points"] = {}
+    for seed in range(8):
+        cells, mlw, fields, pts, ch = scenes.random_amr_points(seed)
+        with tempfile.TemporaryDirectory() as d:
+            v, ok, g = orc.ref_sample_points(orc.ref_build_bricks(cells, d, None if mlw == 127 else mlw), fields, pts, ch, d)
+        hashes["fuzz_points"][str(seed)] = {"valid": int(ok.sum()), "points_sha256": hashlib.sha256(v.tobytes() + ok.tobytes() + g.tobytes()).hexdigest()}
+        print("fuzz points", seed, hashes["fuzz_points"][str(seed)])
 
 
 if __name__ == "__main__":

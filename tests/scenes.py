@@ -220,3 +220,12 @@ def random_amr_frame(seed, W=48, H=32):
     if seed % 4 == 1:
         fd.ao = (1, 4.0)
     return cells, mlw, fields, fd
+
+
+def random_amr_points(seed, n=20000):
+    """points for the reconstruction fuzz: uniform over the bounds of random_amr(seed) grown by one unit (holes and
+    the outside included), sampled on the last channel -> cells, max leaf width, fields, points, channel"""
+    from owlexabrick_b200 import synth
+    cells, mlw, fields, fd = random_amr_frame(seed)
+    lo, hi = fd.world
+    return cells, mlw, fields, synth.random_points(n, [x - 1 for x in lo], [x + 1 for x in hi], seed=seed), len(fields) - 1

@@ -91,6 +91,38 @@ def test_random_amr_frame_equals_reference_shader_live(orc, seed, monkeypatch):
     assert (racc[..., :3].max(axis=-1) > 0.02).sum() > 100
 
 
+
+def _oracle_points(orc, seed):
+    cells, mlw, fields, pts, ch = scenes.random_amr_points(seed)
+    raw = orc.build_bricks(cells, mlw)
+    bricks, ids = orc.parse_bricks(raw)
+    sc = orc.flatten_scalars(ids, fields)
+    regions, leaf = orc.build_abr(bricks, sc)
+    v, ok, g, _ = orc.Scene(bricks, sc, regions, leaf).sample(pts, ch, grad=True)
+    return raw, fields, pts, ch, v, ok, g
+
+
+@pytest.mark.parametrize("seed", SEEDS[:8])
+def test_random_amr_reconstruction_equals_reference_golden(orc, seed):
+    """tent-basis reconstruction + analytic gradient at 20 000 points (holes and outside included): value, validity
+    and gradient hash to what the reference's samplePoint / samplePointWithDerivative returned"""
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["fuzz_points"][str(seed)]
+    _, _, _, _, v, ok, g = _oracle_points(orc, seed)
+    assert int(ok.sum()) == h["valid"]
+    assert hashlib.sha256(v.tobytes() + ok.tobytes() + g.tobytes()).hexdigest() == h["points_sha256"]
+
+
+@pytest.mark.parametrize("seed", [102, 107])
+def test_random_amr_reconstruction_equals_reference_live(orc, seed):
+    if not orc.have_ref_shader():
+        pytest.skip("oracle/_ref/ref_shader not built (needs /root/reference)")
+    raw, fields, pts, ch, v, ok, g = _oracle_points(orc, seed)
+    with tempfile.TemporaryDirectory() as d:
+        rv, rok, rg = orc.ref_sample_points(raw, fields, pts, ch, d)
+    assert (ok != rok).sum() == 0 and (v != rv).sum() == 0 and (g != rg).sum() == 0
+    assert 0 < ok.sum()
+
+
 # ---- CUDA path on the same random scenes ------------------------------------------------------------
 # What it adds over tests/test_gpu_*.py: domains with holes (rays leave and re-enter the volume), negative
 # coordinates, leaf widths 3 / 8 / 17.  First B200 run: profiles/pytest_gpu_r01_fuzz.log (12 passed).
