@@ -159,8 +159,8 @@ struct TriangleMesh {
     detail::check(exa_triangle_mesh_load(fileName.c_str(), &v, &nv, &ix, &nt));
     SP m = std::make_shared<TriangleMesh>();
     m->vertex.resize(nv); m->index.resize(nt);
-    if (nv) std::memcpy(m->vertex.data(), v, nv * 12);
-    if (nt) std::memcpy(m->index.data(), ix, nt * 12);
+    if (nv) std::memcpy((void *)m->vertex.data(), v, nv * 12);
+    if (nt) std::memcpy((void *)m->index.data(), ix, nt * 12);
     exa_free(v); exa_free(ix);
     std::vector<SP> out; if (nt) out.push_back(m);
     return out;
@@ -192,7 +192,7 @@ struct Config {
       if (nt) {
         TriangleMesh::SP mesh = std::make_shared<TriangleMesh>();
         mesh->vertex.resize(nv); mesh->index.resize(nt);
-        std::memcpy(mesh->vertex.data(), v, nv * 12); std::memcpy(mesh->index.data(), ix, nt * 12);
+        std::memcpy((void *)mesh->vertex.data(), v, nv * 12); std::memcpy((void *)mesh->index.data(), ix, nt * 12);
         cfg->surfaces.push_back(mesh);
       }
     }

@@ -324,3 +324,42 @@ def test_builder_types_and_kd_file_match_reference(R, built_lib, orc, tmp_path):
             subprocess.check_call([os.path.join(orc.REF_DIR, "exaBuilder"), str(tmp_path / "in.cells"), "-o", str(tmp_path / "r.bricks"),
                                    "-kd", str(tmp_path / "r.kd")] + flags, stdout=subprocess.DEVNULL)
             assert open(tmp_path / "r.kd", "rb").read() == kd and open(tmp_path / "r.bricks", "rb").read() == b.to_bytes()
+
+
+def test_cpp_class_wrapper_over_the_c_abi(R, built_lib, tmp_path):
+    """include/exa/exa.hpp — the reference's C++ class names (Config, ExaBricks, ScalarField, ColorMapper,
+    TriangleMesh, OptixRenderer) over the C ABI — compiles with g++ -Wall -Wextra as a reference-side caller would
+    use it (tests/harness/exa_hpp_host.cpp), links against the library alone, and sees exactly what the Python
+    mirror sees on the config fixture; without a CUDA device its renderer constructor throws (no CPU fallback)"""
+    import subprocess
+    import sys
+    import torch
+    sys.path.insert(0, GOLDEN)
+    import make_golden
+    libdir = os.path.join(ROOT, "owlexabrick_b200")
+    exe = str(tmp_path / "exa_hpp_host")
+    cc = subprocess.run(["g++", "-std=c++14", "-O1", "-Wall", "-Wextra", "-Wno-comment", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                         os.path.join(ROOT, "tests", "harness", "exa_hpp_host.cpp"), "-o", exe,
+                         "-L" + libdir, "-lexabrick_b200", "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert cc.returncode == 0, cc.stderr[-2000:]
+    cfg_path = make_golden.config_inputs(str(tmp_path))
+    run = subprocess.run([exe, cfg_path], capture_output=True, text=True, timeout=120)
+    assert run.returncode == 0, run.stdout + run.stderr
+    out = {ln.split(" ", 1)[0]: ln.split(" ", 1)[1] for ln in run.stdout.splitlines() if " " in ln and not ln.startswith("field ")}
+    cfg = R.Config(cfg_path)
+    fields = [ln.split() for ln in run.stdout.splitlines() if ln.startswith("field ")]
+    assert int(out["fields"]) == len(cfg.fields) == len(fields)
+    for f, (_, name, n, lo, hi) in zip(cfg.fields, fields):
+        assert f["name"] == name and len(f["values"]) == int(n)
+        assert np.float32(lo) == np.float32(f["valueRange"][0]) and np.float32(hi) == np.float32(f["valueRange"][1])
+    lo, hi = cfg.get_bounds()
+    assert np.array_equal(np.array(out["bounds"].split(), np.float32), np.concatenate([lo, hi]).astype(np.float32))
+    v, i = cfg.triangles()
+    assert out["surfaces"].split() == [str(len(v)), str(len(i))]
+    assert np.array_equal(np.array(out["colormap"].split(), np.float32), np.array([0.5, 0, 0], np.float32))
+    a = cfg.fields[0]["valueRange"]
+    assert np.array_equal(np.array(out["expr"].split()[1:], np.float32), np.array([2 * a[0], 2 * a[1]], np.float32))
+    if torch.cuda.is_available():
+        assert out["renderer"] == "ok"
+    else:
+        assert out["renderer"].startswith("error: no usable CUDA device")
