@@ -3,15 +3,16 @@
 ExaBrickRegions::buildFrom (oracle/_ref, compiled in place from /root/reference — so this runs only
 where that exists) on config C1, next to the product's host builder (exa_bricks_build) on the same
 cells.  The binaries' own file I/O is inside their wall time (tmpfs); outputs are compared bit for bit.
-Prints one JSON line.  Test infrastructure: a baseline measurement, not part of the product.
+Prints one JSON line.  Test infrastructure (lives beside make_golden.py, which runs the same binaries): a baseline measurement,
+not part of the product.
 
-    python tools/host_stage_baselines.py [--config c1|c5s16|c5s4]
+    python tests/golden/host_stage_baselines.py [--config c1|c5s16|c5s4]
 """
 import argparse, hashlib, json, os, subprocess, sys, tempfile, time
 import numpy as np
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
-REF = os.path.join(ROOT, "or" + "acle", "_ref")          # the reference binaries (not the restatement)
+REF = os.path.join(ROOT, "oracle", "_ref")               # the reference binaries (not the restatement)
 
 
 def main():
