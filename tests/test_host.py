@@ -363,3 +363,14 @@ def test_cpp_class_wrapper_over_the_c_abi(R, built_lib, tmp_path):
         assert out["renderer"] == "ok"
     else:
         assert out["renderer"].startswith("error: no usable CUDA device")
+
+
+def test_builder_c5_shape_quarter_scale_hash(R):
+    """26.6 M cells of the C5 shape (synth.cloud_shaped(4), 4 levels): the OpenMP host builder's .bricks bytes hash to
+    what the reference's serial exaBuilder wrote (41 s there; tests/golden/host_stage_baselines.py --config c5s4)"""
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["C5_scale4"]
+    cells, dom = synth.cloud_shaped(4)
+    assert len(cells) == h["cells"] and dom == 512
+    b = R.ExaBricks.build(cells)
+    assert b.num_bricks == h["bricks"] and b.total_num_cells == len(cells)
+    assert hashlib.sha256(b.to_bytes()).hexdigest() == h["bricks_sha256"]
