@@ -365,12 +365,20 @@ def test_cpp_class_wrapper_over_the_c_abi(R, built_lib, tmp_path):
         assert out["renderer"].startswith("error: no usable CUDA device")
 
 
-def test_builder_c5_shape_quarter_scale_hash(R):
+def test_builder_c5_shape_quarter_scale_hash(R, orc):
     """26.6 M cells of the C5 shape (synth.cloud_shaped(4), 4 levels): the OpenMP host builder's .bricks bytes hash to
-    what the reference's serial exaBuilder wrote (41 s there; tests/golden/host_stage_baselines.py --config c5s4)"""
+    what the reference's serial exaBuilder wrote (41 s there; tests/golden/host_stage_baselines.py --config c5s4), and
+    the oracle's ABR build over them with 3 channels (251 744 regions) to the reference's ExaBrickRegions::buildFrom"""
     h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["C5_scale4"]
     cells, dom = synth.cloud_shaped(4)
     assert len(cells) == h["cells"] and dom == 512
     b = R.ExaBricks.build(cells)
     assert b.num_bricks == h["bricks"] and b.total_num_cells == len(cells)
     assert hashlib.sha256(b.to_bytes()).hexdigest() == h["bricks_sha256"]
+    fields = [np.empty(len(cells), np.float32) for _ in range(3)]
+    for s0 in range(0, len(cells), 1 << 22):                 # chunked: the generator's temporaries stay small
+        for c, v in enumerate(synth.cloud_velocity(cells[s0:s0 + (1 << 22)], dom)):
+            fields[c][s0:s0 + (1 << 22)] = v
+    regions, leaf = orc.build_abr(b.headers.view(orc.BRICK_DT), orc.flatten_scalars(b.cell_ids, fields))
+    assert len(regions) == h["regions"]
+    assert hashlib.sha256(regions.tobytes() + leaf.tobytes()).hexdigest() == h["abr_sha256"]
