@@ -87,6 +87,24 @@ def test_abr_c1_hash_vs_reference(R, orc):
     assert hashlib.sha256(raw).hexdigest() == hashes["C1"]["abr_sha256"]
 
 
+@pytest.mark.skipif(os.environ.get("EXA_GPU_LARGE") != "1", reason="written after round 1's GPU minutes were spent: opt-in (EXA_GPU_LARGE=1) until first run on a B200")
+def test_abr_c5_quarter_scale_hash_vs_reference(R, orc):
+    """C5 shape at 1/4 scale (26.6 M cells, 3 channels, 4 021 bricks): GPU ABR output (251 744 regions) ==
+    reference buildFrom output (SHA-256; the oracle's equals it: tests/test_host.py)"""
+    h = json.load(open(os.path.join(GOLDEN, "golden_hashes.json")))["C5_scale4"]
+    cells, dom = synth.cloud_shaped(4)
+    fields = [np.empty(len(cells), np.float32) for _ in range(3)]
+    for s0 in range(0, len(cells), 1 << 22):
+        for c, v in enumerate(synth.cloud_velocity(cells[s0:s0 + (1 << 22)], dom)):
+            fields[c][s0:s0 + (1 << 22)] = v
+    b = R.ExaBricks.build(cells)
+    assert hashlib.sha256(b.to_bytes()).hexdigest() == h["bricks_sha256"]
+    r = R.Renderer(b, fields)
+    regions, leaf = r.get_abr()
+    assert len(regions) == h["regions"]
+    assert hashlib.sha256(regions.tobytes() + leaf.tobytes()).hexdigest() == h["abr_sha256"]
+
+
 # ------------------------------------------------------------------------------------------
 # tent-basis reconstruction (exabrick.cu:620-816, 883-942) — 1e-5 relative
 # ------------------------------------------------------------------------------------------
