@@ -28,7 +28,11 @@ import time
 if os.environ.get("OMP_NUM_THREADS") == "1" and "TORCHELASTIC_RUN_ID" in os.environ:
     _w = int(os.environ.get("LOCAL_WORLD_SIZE", os.environ.get("WORLD_SIZE", "1")))
     _n = os.cpu_count() or 1
-    os.environ["OMP_NUM_THREADS"] = str(max(1, _n - 2 * (_w - 1)) if os.environ.get("RANK", "0") == "0" else 2)
+    if "--impl" in sys.argv and "reference" in sys.argv:
+        # the CPU arm: ranks > 0 exit at once, so rank 0 has the whole host at EVERY N (same thread count for N = 1, 2, 4, 8)
+        os.environ["OMP_NUM_THREADS"] = str(_n)
+    else:
+        os.environ["OMP_NUM_THREADS"] = str(max(1, _n - 2 * (_w - 1)) if os.environ.get("RANK", "0") == "0" else 2)
 
 import numpy as np
 
@@ -252,6 +256,43 @@ def run_reference(args):
     print(json.dumps(line), flush=True)
 
 
+def reference_host_stages(name, bricks, field):
+    """BASELINE.md rows B1/B2 beside the GPU numbers: wall time of the reference's OWN host stages (oracle/_ref, the
+    reference's sources compiled in place) on this box: exaBuilder on config C1 (serial, as shipped) and
+    ExaBrickRegions::buildFrom on the benchmarked bricks.  File I/O on tmpfs is inside their wall time."""
+    import tempfile
+    from owlexabrick_b200 import synth
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    out = {}
+    if not os.path.exists(os.path.join(ref, "exaBuilder")):
+        return {"reference_host_stages": "oracle/_ref not built on this box"}
+    with tempfile.TemporaryDirectory(dir="/dev/shm" if os.path.isdir("/dev/shm") else None) as d:
+        try:
+            cells = synth.nested_boxes(256, [(72, 184), (32, 224)])
+            cf, bf = os.path.join(d, "c1.cells"), os.path.join(d, "c1.bricks")
+            np.ascontiguousarray(cells, np.int32).tofile(cf)
+            t = time.time()
+            subprocess.check_call([os.path.join(ref, "exaBuilder"), cf, "-o", bf], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=300)
+            dt = time.time() - t
+            out["reference_exaBuilder_c1"] = {"wall_s": round(dt, 3), "cells": int(len(cells)), "cells_per_s": round(len(cells) / dt), "threads": 1,
+                                              "note": "the reference's builder/builder.cpp compiled in place, serial as shipped, incl. .cells/.bricks I/O on tmpfs"}
+        except Exception as e:
+            out["reference_exaBuilder_c1"] = {"error": str(e)[:200]}
+        base = os.path.join(os.environ.get("EXA_SCENE_CACHE", "/dev/shm"), "exa_scene_%s_v%d" % (name, SCENE_CACHE_VERSION))
+        if os.path.exists(base + ".bricks") and os.path.exists(base + ".scalars") and os.path.exists(os.path.join(ref, "ref_abr")):
+            try:
+                of = os.path.join(d, "w.abr")
+                t = time.time()
+                subprocess.check_call([os.path.join(ref, "ref_abr"), base + ".bricks", of, base + ".scalars"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL, timeout=600)
+                dt = time.time() - t
+                nr = int(np.frombuffer(open(of, "rb").read(8), "<i4")[0])
+                out["reference_buildFrom"] = {"wall_s": round(dt, 2), "regions": nr, "regions_per_s": round(nr / dt),
+                                              "note": "ExaBrickRegions::buildFrom (exa/Regions.cpp) on the benchmarked bricks incl. ExaBricks::load and the scalar gather; serial build (-DOWL_DISABLE_TBB)"}
+            except Exception as e:
+                out["reference_buildFrom"] = {"error": str(e)[:200]}
+    return out
+
+
 def workload_name(name):
     domain, shape, image = WORKLOADS[name]
     if isinstance(shape, tuple):
@@ -263,18 +304,74 @@ def workload_name(name):
     return "%s: synthetic 3-level nested-box AMR, domain %d^3, single scalar, DVR %dx%d, default camera/XF" % (name, domain, image[0], image[1])
 
 
-def binary_swap(r, dist, torch, partial, npix, rank, world, rgba8_full):
-    """sort-last compositing (owlexabrick_b200/multigpu.py) with the CUDA kernels of the library"""
-    from owlexabrick_b200 import multigpu
-
-    def composite(mine, other, front):
-        r.composite_over(mine.data_ptr(), other.data_ptr(), mine.shape[0], front)
-
-    def finish(pixels, first):
-        strip = torch.empty(pixels.shape[0], dtype=torch.int32, device=pixels.device)
-        r.finish_pixels(pixels.data_ptr(), first, pixels.shape[0], strip.data_ptr())
-        return strip
-    return multigpu.binary_swap(dist, torch, partial, rank, world, composite, r.swap_order, finish)
+def measure_sortlast(args, torch, dist, capi, R, multigpu, r, sl_r, sl_pipe, bricks, field, fd, name, rank, world, local, W, H, stream,
+                     compare_with_single, frame_via_pipeline):
+    """sort-last sub-object of the N>1 line: data-partitioned renderer per rank, direct-send composite through peer memory"""
+    if args.no_sortlast:
+        return None
+    own = sl_pipe is None
+    try:
+        if own:
+            t = time.time()
+            sl_r = R.Renderer(bricks, [field], device=local, part=(rank, world))
+            sl_r.set_stream(stream.cuda_stream)
+            fd.apply(sl_r)
+            sl_pipe = multigpu.SortLastPipeline(dist, torch, capi, np, sl_r, rank, world, local, W, H, stream, nccl_barrier=args.nccl_barrier,
+                                                surf=has_iso(name), tag="%s_sl" % os.environ.get("MASTER_PORT", "0"))
+            log("rank %d: sort-last renderer in %.1fs, resident %s of %d bricks" % (rank, time.time() - t, sl_r.residency(), bricks.num_bricks))
+        nb, ncell = sl_r.residency()
+        res = torch.tensor([nb, ncell, sl_r.scalar_layout()[1]], dtype=torch.int64, device="cuda")
+        allres = [torch.zeros(3, dtype=torch.int64, device="cuda") for _ in range(world)]
+        dist.all_gather(allres, res)
+        out = {"mode": "data partitioned along the ABR kd-tree (balanced by estimated lattice samples), float4 partials in peer-mapped buffers, "
+                       "one barrier, fused composite+finish kernel reading all ranks' partials over NVLink (direct send), triple-buffered",
+               "resident_bricks_per_rank": [int(x[0]) for x in allres], "resident_cells_per_rank": [int(x[1]) for x in allres],
+               "scalar_bytes_per_rank": [int(x[2]) for x in allres], "bricks_total": bricks.num_bricks, "cells_total": int(bricks.total_num_cells),
+               "peer_bytes_read_per_rank_per_frame": sl_pipe.peer_read_bytes, "barrier": "NCCL all-reduce" if sl_pipe.bar.nccl else "peer memory"}
+        alpha, rgb = fd.xf[0]
+        for label, scale in (("opaque", fd.opacity_scale), ("translucent", 0.02)):
+            sl_r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
+            st = sl_r.render_stats()
+            stt = torch.tensor([st["samples"]], dtype=torch.int64, device="cuda"); dist.all_reduce(stt)
+            for _ in range(3):
+                sl_pipe.step()
+            sl_pipe.drain(); torch.cuda.synchronize(); dist.barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            for _ in range(args.steps):
+                sl_pipe.step()
+            sl_pipe.drain(); b.record(stream); torch.cuda.synchronize()
+            ms = torch.tensor([a.elapsed_time(b) / args.steps], dtype=torch.float64, device="cuda"); dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            # end to end: every rank's span to the shared host frame
+            dist.barrier(); t = time.perf_counter()
+            for _ in range(args.steps):
+                sl_r.updateCamera(*fd.cam)
+                sl_pipe.step(readback=True)
+            sl_pipe.drain(); sl_pipe.finish(); torch.cuda.synchronize()
+            te = torch.tensor([time.perf_counter() - t], dtype=torch.float64, device="cuda"); dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            ent = {"ms_per_frame": float(ms.item()), "frames_per_s": 1e3 / float(ms.item()), "samples_per_frame": int(stt.item()),
+                   "samples_per_s": int(stt.item()) / (float(ms.item()) * 1e-3), "e2e_frames_per_s": args.steps / float(te.item())}
+            # deviation from the single-GPU frame: with the reference's termination threshold, and with it off
+            for ert_label, ert in (("ert_0.98", 0.98), ("ert_off", 2.0)):
+                sl_r.setErtThreshold(ert)
+                img_n = frame_via_pipeline(sl_pipe)
+                if rank == 0:
+                    r.updateXF(0, alpha, rgb, fd.xf_domain[0], scale)
+                    ent["vs_1gpu_" + ert_label] = compare_with_single(img_n, ert=ert)
+                dist.barrier()
+            sl_r.setErtThreshold(0.98)
+            out[label] = ent
+        if rank == 0:
+            r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)
+            out["barrier_timed_out"] = sl_pipe.bar.timed_out()
+            log("sort-last:", json.dumps(out))
+        if own:
+            sl_pipe.close()
+            sl_r.close()
+        return out
+    except Exception as e:                                            # the secondary measurement must not take the headline line down
+        log("rank %d: sort-last measurement failed: %r" % (rank, e))
+        return {"error": repr(e)[:300]}
 
 
 def run_product(args):
@@ -309,111 +406,55 @@ def run_product(args):
     r = R.Renderer(bricks, [field], device=local)
     torch.cuda.synchronize()
     regions, leaf = r.get_abr()
-    log("rank %d: renderer created in %.1fs (%d regions, L=%d, kd %s)" % (rank, time.time() - t, len(regions), len(leaf), r.kd_info()))
+    create_s = time.time() - t
+    bt = r.build_times()
+    build_info = {"renderer_create_wall_s": round(create_s, 3), **{k: round(v, 3) for k, v in bt.items()},
+                  "abr_build_ms": round(bt["abr_geometry_ms"] + bt["value_ranges_ms"], 3), "abr_regions": int(len(regions)),
+                  "abr_regions_per_s": round(len(regions) / max(1e-9, 1e-3 * (bt["abr_geometry_ms"] + bt["value_ranges_ms"]))),
+                  "note": "device time (CUDA events): ABR geometry = kd build + regions + leaf lists (ExaBrickRegions::buildFrom, exa/Regions.cpp:242-287), value ranges = Regions.cpp:182-240; the reference's buildFrom on the same bricks is timed in cpu_baseline.reference_buildFrom"}
+    log("rank %d: renderer created in %.1fs (%d regions, L=%d, kd %s) %s" % (rank, create_s, len(regions), len(leaf), r.kd_info(), build_info))
     stream = torch.cuda.current_stream()
     r.set_stream(stream.cuda_stream)
     fd = frame_desc(R, domain, image, (float(field.min()), float(field.max())), iso=has_iso(name))
     fd.apply(r)
     npix = W * H
     mode = "none" if world == 1 else args.partition
-    peer_fb = None
-    if mode == "sortlast":
-        r.set_partition(capi.PARTITION_SORT_LAST, rank, world)
-        partial = torch.zeros((npix, 4), dtype=torch.float32, device="cuda")
-    elif mode == "tiles":
-        # data replicated, rank r renders tiles r, r+N, ...; every rank's frame kernel stores its
-        # RGBA8 tiles straight into rank 0's frame buffer over NVLink (CUDA IPC peer pointer), so
-        # the only per-frame exchange is a 4-byte all-reduce that orders the frame's completion
-        r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
-        import ctypes as C
-        # swap chain of two RGBA8 frame buffers on rank 0, mapped into every rank (CUDA IPC): frame i
-        # goes to buffer i&1, so the completion exchange (and the consumer's read-back) of frame i
-        # overlaps the rendering of frame i+1
-        hbuf = torch.zeros(2 * 64, dtype=torch.uint8)
-        fb_ptrs = [None, None]
-        if rank == 0:
-            for k in range(2):
-                pp = C.c_void_p()
-                capi.check(capi.lib.exa_device_malloc(npix * 4, local, C.byref(pp)))
-                fb_ptrs[k] = pp.value
-                capi.check(capi.lib.exa_ipc_export(C.c_void_p(pp.value), C.c_void_p(hbuf.data_ptr() + 64 * k)))
-        hdev = hbuf.cuda()
-        dist.broadcast(hdev, 0)
-        hbuf = hdev.cpu()
-        if rank != 0:
-            try:
-                if args.no_peer_fb:
-                    raise RuntimeError("--no-peer-fb")
-                for k in range(2):
-                    pp = C.c_void_p()
-                    capi.check(capi.lib.exa_ipc_import(C.c_void_p(hbuf.data_ptr() + 64 * k), local, C.byref(pp)))
-                    fb_ptrs[k] = pp.value
-            except Exception as e:                                    # no peer mapping: fall back to an NCCL reduce of the frame
-                log("rank %d: CUDA IPC import failed (%s); using NCCL reduce" % (rank, e))
-                fb_ptrs = [None, None]
-        ok = torch.tensor([1 if (fb_ptrs[1] and not args.no_peer_fb) else 0], device="cuda")
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        use_peer = bool(ok.item())
-        fb_t, fb_views = None, None
-        if use_peer:
-            r.resizeFrameBuffer(fb_ptrs[0], (W, H))
-            if rank == 0:                                             # torch views of the two raw allocations (read-back source)
-                class _Raw:
-                    def __init__(self, ptr):
-                        self.__cuda_array_interface__ = {"shape": (H, W), "typestr": "<i4", "data": (ptr, False), "version": 2}
-                fb_views = [torch.as_tensor(_Raw(p_), device="cuda") for p_ in fb_ptrs]
-        else:                                                         # caller-owned torch frame buffers, summed onto rank 0
-            fb_t = torch.zeros(npix, dtype=torch.int32, device="cuda")
-            r.resizeFrameBuffer(fb_t.data_ptr(), (W, H))
-        done_flag = torch.zeros(1, dtype=torch.int32, device="cuda")
-        side = torch.cuda.Stream()                                    # completion exchange + read-back of the previous frame
-        ev_render = [torch.cuda.Event(), torch.cuda.Event()]
-        ev_done = [torch.cuda.Event(), torch.cuda.Event()]
-        frame_no = [0]
-        log("rank %d: image-tile mode, %s" % (rank, "double-buffered peer frame buffer over NVLink" if use_peer else "NCCL reduce"))
+    pipe, sl_r = None, None
+    if world > 1:
+        from owlexabrick_b200 import multigpu
+        tag = "%s_%s" % (os.environ.get("MASTER_PORT", "0"), mode)
+        if mode == "tiles":
+            # data replicated; the frame is N row strips, strip k on GPU k: every rank's frame kernel stores its tiles into
+            # the strips over NVLink (peer pointers), a peer-memory barrier orders "frame complete", and rank k reads strip k
+            # back over its own PCIe link into a pinned host frame shared by the ranks (owlexabrick_b200/multigpu.py)
+            pipe = multigpu.TilePipeline(dist, torch, capi, np, r, rank, world, local, W, H, stream, nccl_barrier=args.nccl_barrier, tag=tag)
+        else:
+            # sort-last with the DATA partitioned: a second renderer that holds only this rank's kd subtree
+            sl_r = R.Renderer(bricks, [field], device=local, part=(rank, world))
+            sl_r.set_stream(stream.cuda_stream)
+            fd.apply(sl_r)
+            pipe = multigpu.SortLastPipeline(dist, torch, capi, np, sl_r, rank, world, local, W, H, stream, nccl_barrier=args.nccl_barrier, surf=has_iso(name), tag=tag)
+        log("rank %d: %s pipeline, barrier: %s" % (rank, mode, "NCCL all-reduce" if pipe.bar.nccl else "peer memory"))
 
     def drain():
-        """main stream waits for the completion exchanges still in flight on the side stream"""
-        if mode == "tiles" and use_peer:
-            stream.wait_event(ev_done[0]); stream.wait_event(ev_done[1])
+        """main stream waits for the completion barriers still in flight on the side stream"""
+        if pipe is not None:
+            pipe.drain()
 
-    def step(readback=None):
-        if mode == "none":
+    def step(readback=False):
+        if pipe is None:
             r.render(sync=False)
             return 1
-        if mode == "tiles" and use_peer:
-            b = frame_no[0] & 1
-            frame_no[0] += 1
-            stream.wait_event(ev_done[b])                             # buffer b: frame i-2 complete everywhere (and read back)
-            capi.check(capi.lib.exa_renderer_set_color_buffer(r.h, C.c_void_p(fb_ptrs[b])))
-            r.render(sync=False)                                      # own tiles -> rank 0's buffer b over NVLink
-            ev_render[b].record(stream)
-            with torch.cuda.stream(side):
-                side.wait_event(ev_render[b])
-                dist.all_reduce(done_flag)                            # frame i complete on every rank
-                if readback is not None:
-                    if rank == 0:
-                        readback[b].copy_(fb_views[b], non_blocking=True)
-                    dist.all_reduce(done_flag)                        # buffer b released by the consumer
-                ev_done[b].record(side)
-            return 1
-        if mode == "tiles":
-            r.render(sync=False)
-            dist.reduce(fb_t, 0)                                      # tiles are disjoint and the rest is 0: sum = union (rank 0's copy is final)
-            return 1
-        r.render_partial(partial.data_ptr())
-        _, _, k = binary_swap(r, dist, torch, partial, npix, rank, world, None)
-        return 1 + k
+        pipe.step(readback)
+        return 2 + (1 if mode == "sortlast" else 0)              # frame kernel + barrier kernel (+ composite kernel)
 
+    rr = sl_r if sl_r is not None else r                          # the renderer the timed frames run on
     # instrumented, untimed: counters of the algorithmic-bytes model
-    st = r.render_stats()
+    st = rr.render_stats() if sl_r is None else sl_r.render_stats()
     stats_t = torch.tensor([st["samples"], st["brickVisits"], st["cornerLoads"], st["segments"]], dtype=torch.int64, device="cuda")
     if world > 1:
         dist.all_reduce(stats_t)
     tot = dict(zip(["samples", "brickVisits", "cornerLoads", "segments"], [int(x) for x in stats_t.tolist()]))
-    if mode == "tiles" and not use_peer:
-        fb_t.zero_()
-
     sampler = ClockSampler(local)          # samples clocks from the warm-up to the end of the e2e loop
     if rank == 0:
         sampler.start()
@@ -424,7 +465,7 @@ def run_product(args):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    l0 = r.launch_count()
+    l0 = rr.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     ev0.record(stream)
@@ -443,7 +484,7 @@ def run_product(args):
     if world > 1:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
     ms = float(tms.item())
-    lib_launches = r.launch_count() - l0
+    lib_launches = rr.launch_count() - l0
     ms_step = ms / args.steps
     value = tot["samples"] / (ms_step * 1e-3)
 
@@ -453,25 +494,16 @@ def run_product(args):
     alpha, rgb = fd.xf[0]
     e2e_count = [0]
     def e2e_step():
-        r.updateCamera(*fd.cam)
-        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)       # host -> device: 128 float4 (stream-ordered, pinned ring)
+        rr.updateCamera(*fd.cam)
+        rr.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)      # host -> device: 128 float4 (stream-ordered, pinned ring)
         if world == 1:
             # every frame is rendered from this step's inputs and read back to (pinned) host memory;
             # the copy of frame i runs on the copy stream while frame i+1 renders into the second buffer
             r.render(sync=False)
             capi.check(capi.lib.exa_renderer_read_rgba8_async(r.h, host_ring[e2e_count[0] & 1].data_ptr()))   # device -> host: W*H*4
             e2e_count[0] += 1
-        elif mode == "tiles" and use_peer:
-            step(readback=host_ring)                                  # rank 0 copies frame i to pinned host memory while frame i+1 renders
-        elif mode == "tiles":
-            step()
-            if rank == 0:
-                host_img.view(-1).copy_(fb_t, non_blocking=False)
         else:
-            r.render_partial(partial.data_ptr())
-            strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
-            if rank == 0:
-                torch.cat(strips).cpu()
+            step(readback=True)                                       # every rank copies ITS strip / span of frame i to the shared pinned host frame while frame i+1 renders
     for _ in range(2):
         e2e_step()
     torch.cuda.synchronize()
@@ -482,6 +514,8 @@ def run_product(args):
         e2e_step()
     drain()
     r.sync()                                                         # render stream + copy stream: the last frame is in host memory
+    if pipe is not None:
+        pipe.finish()                                                # this rank's strips / spans have landed in the shared host frames
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
@@ -518,62 +552,84 @@ def run_product(args):
 
     # ---- secondary measurement: the same frame with a translucent XF (opacity scale 0.02), which
     # makes rays traverse the whole volume instead of terminating after a few samples ----
-    # ---- N>1 diagnostic: this rank's frame kernel alone (no completion exchange), max over ranks ----
-    render_only_ms = None
-    if world > 1 and mode == "tiles":
+    # ---- N>1 diagnostics: this rank's frame kernel alone (no exchange), max over ranks; the barrier alone ----
+    render_only_ms, barrier_ms = None, None
+    if world > 1:
+        def alone():
+            if mode == "tiles":
+                r.render(sync=False)
+            else:
+                sl_r.render_partial(pipe.partials.ptr[rank][0], pipe.surfs.ptr[rank][0] if pipe.surfs else None)
         for _ in range(3):
-            r.render(sync=False)
+            alone()
         torch.cuda.synchronize(); dist.barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
         for _ in range(args.steps):
-            r.render(sync=False)
+            alone()
         b.record(stream); torch.cuda.synchronize()
-        log("rank %d: own frame kernel %.4f ms/step" % (rank, a.elapsed_time(b) / args.steps))
-        ro = torch.tensor([a.elapsed_time(b) / args.steps], dtype=torch.float64, device="cuda")
-        dist.all_reduce(ro, op=dist.ReduceOp.MAX)
-        render_only_ms = float(ro.item())
+        mine_ms = a.elapsed_time(b) / args.steps
+        ro = torch.tensor([mine_ms], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(allr, ro)
+        per_rank = [float(x.item()) for x in allr]
+        render_only_ms = max(per_rank)
+        dist.barrier()
         a.record(stream)
         for _ in range(args.steps):
-            dist.all_reduce(done_flag)
+            pipe.bar.wait(stream)
         b.record(stream); torch.cuda.synchronize()
-        log("rank %d: frame kernel alone %.4f ms/step, 4-byte all-reduce alone %.4f ms" % (rank, render_only_ms, a.elapsed_time(b) / args.steps))
+        barrier_ms = a.elapsed_time(b) / args.steps
+        log("rank %d: own frame kernel %.4f ms/step; per rank %s; barrier alone %.4f ms (%s)" % (
+            rank, mine_ms, ["%.4f" % x for x in per_rank], barrier_ms, "NCCL all-reduce" if pipe.bar.nccl else "peer memory"))
         dist.barrier()
 
-    # ---- multi-GPU check (untimed): the N-GPU frame against the same frame rendered by rank 0 alone ----
+    # ---- multi-GPU check (untimed): the N-GPU frame as it arrives in the shared host frame (every rank's strip / span
+    # copied over its own PCIe link) against the same frame rendered by rank 0 alone ----
     mg_check = None
-    if world > 1:
-        from owlexabrick_b200 import multigpu
-        if mode == "tiles":
-            last = frame_no[0] & 1 if use_peer else 0
-            drain(); torch.cuda.synchronize()
-            if rank == 0:                                             # stale pixels must not be able to hide a missing tile
-                (fb_views[last] if use_peer else fb_t).zero_(); torch.cuda.synchronize()
-            dist.barrier()
-            step(); drain(); torch.cuda.synchronize(); dist.barrier()
-            if rank == 0:
-                img_n = (fb_views[last] if use_peer else fb_t).cpu().numpy().view(np.uint32).reshape(-1)
-        else:
-            r.render_partial(partial.data_ptr())
-            strips, _, _ = binary_swap(r, dist, torch, partial, npix, rank, world, None)
-            if rank == 0:
-                img_n = np.zeros(npix, np.uint32)
-                for k in range(world):
-                    lo, hi = multigpu.final_span(k, world, npix)
-                    img_n[lo:hi] = strips[k].cpu().numpy().view(np.uint32)
-        dist.barrier()
+
+    def frame_via_pipeline(p):
+        """one frame through pipeline p with read-back -> the host frame (valid on every rank after the barrier)"""
+        p.drain(); torch.cuda.synchronize(); dist.barrier()
+        bsel = p.j % 3
         if rank == 0:
-            r.set_partition(capi.PARTITION_NONE, 0, 1)
-            r.resizeFrameBuffer(None, (W, H))
-            r.render()
-            img_1 = r.read_rgba8().reshape(-1)
-            sys.path.insert(0, os.path.join(ROOT, "tests"))
-            import scenes
-            dif = np.abs(scenes.unpack_rgba8(img_n) - scenes.unpack_rgba8(img_1))
-            mg_check = {"max_abs_rgba8_diff_vs_1gpu": int(dif.max()), "pixels_differing": int((dif.max(axis=-1) > 0).sum()),
-                        "note": "image tiles: bit-identical expected; sort-last: per-rank early termination (H1) bounds the deviation"}
-            log("multi-GPU check:", mg_check)
+            p.host_frame(bsel)[:] = 0                                 # stale pixels must not be able to hide a missing tile
         dist.barrier()
+        p.step(readback=True); p.drain(); p.finish(); torch.cuda.synchronize(); dist.barrier()
+        return p.host_frame(bsel).reshape(-1).copy()
+
+    def compare_with_single(img_n, ert=None):
+        """rank 0: the same frame on the replicated renderer alone"""
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import scenes
+        r.set_partition(capi.PARTITION_NONE, 0, 1)
+        capi.check(capi.lib.exa_renderer_set_color_strips(r.h, None, 0))
+        if ert is not None:
+            r.setErtThreshold(ert)
+        r.render()
+        img_1 = r.read_rgba8().reshape(-1)
+        if ert is not None:
+            r.setErtThreshold(0.98)
+        dif = np.abs(scenes.unpack_rgba8(img_n) - scenes.unpack_rgba8(img_1))
+        return {"max_abs_rgba8_diff_vs_1gpu": int(dif.max()), "pixels_differing": int((dif.max(axis=-1) > 0).sum())}
+
+    if world > 1:
+        img_n = frame_via_pipeline(pipe)
+        if rank == 0:
+            mg_check = compare_with_single(img_n)
+            mg_check["note"] = "image tiles: bit-identical expected; sort-last: per-rank early termination (H1) bounds the deviation"
+            mg_check["barrier_timed_out"] = pipe.bar.timed_out()
+            log("multi-GPU check:", mg_check)
+            if mode == "tiles":
+                r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
+        dist.barrier()
+
+    # ---- sort-last (north_star's primary multi-GPU mode), measured inside the default --gpus N run: data partitioned
+    # along the ABR kd-tree, partials composited through peer memory; opaque and translucent frame, deviation vs 1 GPU ----
+    sortlast = None
+    if world > 1:
+        sortlast = measure_sortlast(args, torch, dist, capi, R, multigpu, r, sl_r, pipe if mode == "sortlast" else None, bricks, field, fd, name,
+                                    rank, world, local, W, H, stream, compare_with_single, frame_via_pipeline)
 
     translucent = None
     if world == 1:
@@ -628,24 +684,72 @@ def run_product(args):
                  "achieved_gbs": pbytes / (pms * 1e-3) / 1e9, "frac": pbytes / (pms * 1e-3) / 1e9 / peak,
                  "traffic": ncu_traffic("k_samplePoints", name), "e2e_samples_per_s": npts / h_s, "l2_flush": "256 MiB write + 256 MiB read between iterations"}
 
-    # ---- CPU baseline beside it (rank 0, N=1 only): the oracle on a bounded sample ----
-    cpu = None
+    # ---- CPU baseline + parity (rank 0, N=1 only): the oracle builds ITS OWN scene from the same bricks
+    # (flatten, ABR build), renders the benchmarked frames and samples the benchmarked points; the GPU results
+    # are compared with it here, on the full-size workload ----
+    cpu, parity = None, None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import orc
         orc.build()
         t = time.time()
         hdr = bricks.headers.view(orc.BRICK_DT)
         sc = orc.flatten_scalars(bricks.cell_ids, [field])
-        oscene = orc.Scene(hdr, sc, regions.view(orc.REGION_DT), leaf)      # same bricks/ABRs (bit-exact with the oracle's, tests/)
-        log("cpu baseline scene in %.1fs" % (time.time() - t))
-        cst, cdt = cpu_frame_sample(orc, oscene, fd, (0, 0, W, H))  # calibration: the whole frame once
+        t_fl = time.time() - t
+        t = time.time()
+        o_regions, o_leaf = orc.build_abr(hdr, sc)                   # the oracle's own ABRs (not the product's)
+        t_oabr = time.time() - t
+        oscene = orc.Scene(hdr, sc, o_regions, o_leaf)
+        log("cpu baseline scene: flatten %.1fs, oracle ABR build %.1fs (%d regions)" % (t_fl, t_oabr, len(o_regions)))
+        parity = {"abr_bit_exact": bool(regions.tobytes() == o_regions.tobytes() and leaf.tobytes() == o_leaf.tobytes()),
+                  "abr_regions": int(len(o_regions)), "abr_leaf_list": int(len(o_leaf)),
+                  "against": "oracle port with its own flatten + ABR build over the same bricks (bit-identical to the reference's device source on the pinned set, tests/test_oracle_pinned.py)"}
+        # the timed frame (opaque XF): GPU accumulation buffer vs the oracle's
+        r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)
+        r.render()
+        g_acc = r.read_accum()
+        t = time.time()
+        o_acc, _, cst = oscene.render(fd.to_orc(orc), window=(0, 0, W, H))
+        cdt = time.time() - t
+        def frame_parity(g, o):
+            e = np.abs(g[..., :3] - o[..., :3]).max(axis=-1)
+            return {"rgba_max_abs": float(e.max()), "pixels_over_1e-3": int((e > 1e-3).sum()), "pixels": int(e.size)}
+        parity["frame"] = frame_parity(g_acc, o_acc)
+        parity["frame"]["samples_gpu_vs_oracle"] = [tot["samples"], int(cst["samples"])]
         reps = int(min(200, max(1, round(12.0 / max(cdt, 1e-3)))))  # aim at ~12 s of CPU work
-        tot_s, tot_t = 0, 0.0
-        for _ in range(reps):
+        tot_s, tot_t = int(cst["samples"]), cdt
+        for _ in range(reps - 1):
             cst, cdt = cpu_frame_sample(orc, oscene, fd, (0, 0, W, H))
             tot_s += cst["samples"]; tot_t += cdt
+        # the translucent frame (rays cross the whole volume)
+        if translucent is not None and not args.quick_parity:
+            import copy
+            fd2 = copy.copy(fd); fd2.opacity_scale = 0.02
+            r.updateXF(0, alpha, rgb, fd.xf_domain[0], 0.02)
+            r.render()
+            g2 = r.read_accum()
+            t = time.time()
+            o2, _, cst2 = oscene.render(fd2.to_orc(orc), window=(0, 0, W, H))
+            parity["frame_translucent"] = frame_parity(g2, o2)
+            parity["frame_translucent"]["cpu_s"] = round(time.time() - t, 1)
+            translucent["cpu_samples_per_s"] = cst2["samples"] / (time.time() - t)
+            r.updateXF(0, alpha, rgb, fd.xf_domain[0], fd.opacity_scale)
+        # reconstruction at the benchmarked 1 M points
+        if recon is not None:
+            t = time.time()
+            ov, ook, _ = oscene.sample(pts, 0)
+            t_pts = time.time() - t
+            gv, gok = d_val.cpu().numpy(), d_ok.cpu().numpy()
+            m = ook == 1
+            fmax = float(np.abs(field).max())
+            rel = np.abs(gv[m].astype(np.float64) - ov[m]) / np.maximum(np.abs(ov[m]), 1e-3 * fmax)
+            parity["recon"] = {"points": int(len(pts)), "valid": int(m.sum()), "validity_mismatches": int((gok != ook).sum()),
+                               "max_rel_err": float(rel.max()) if m.any() else 0.0, "gate": 1e-5}
+            recon["cpu_samples_per_s"] = len(pts) / t_pts
         cpu = {"value": tot_s / tot_t, "unit": "samples/s", "frames_per_s": reps / tot_t, "cores": orc.num_threads(), "kind": "port", "pinned": "the port is bit-identical to the reference's own device source programs/exabrick.cu compiled as C++ (oracle/_ref/ref_shader, tests/test_oracle_pinned.py); that build is not timed here: its stand-in for the OptiX BVH is a brute-force loop over all regions",
-               "sample": "the same whole frame, %d times, %.1f s (oracle port, OpenMP over pixel rows, BVH region query)" % (reps, tot_t)}
+               "sample": "the same whole frame, %d times, %.1f s (oracle port, OpenMP over pixel rows, BVH region query)" % (reps, tot_t),
+               "abr_build": {"oracle_port_s": round(t_oabr, 2), "regions": int(len(o_regions))}}
+        cpu.update(reference_host_stages(name, bricks, field))
+        log("parity:", json.dumps(parity))
 
     if rank == 0:
         peak, peak_src = peaks()
@@ -656,33 +760,30 @@ def run_product(args):
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload_name(name), "cells": int(ncells), "bricks": bricks.num_bricks, "regions": int(len(regions)),
                            "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
-                           "parallelism": "1 GPU" if world == 1 else ("sort-last kd partition x%d, NCCL binary swap" % world if mode == "sortlast" else
-                                           "image tiles x%d (data replicated), %s" % (world, "RGBA8 stored into rank 0's double-buffered frame buffer over NVLink peer memory + 4-B all-reduce per frame" if use_peer else "NCCL reduce of the RGBA8 frame")),
+                           "parallelism": "1 GPU" if world == 1 else ("sort-last x%d: data partitioned along the ABR kd-tree, float4 partials composited through NVLink peer memory inside the composite kernel (direct send), %s barrier per frame" % (world, "NCCL" if pipe.bar.nccl else "peer-memory") if mode == "sortlast" else
+                                           "image tiles x%d (data replicated): RGBA8 tiles stored into N peer-mapped row strips (strip k on GPU k) over NVLink, %s barrier per frame, triple-buffered" % (world, "NCCL" if pipe.bar.nccl else "peer-memory")),
                            "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
                            "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"],
-                           "step": "eager launches" + (", frames double-buffered: the completion all-reduce of frame i runs on a side stream while frame i+1 renders" if (world > 1 and mode == "tiles" and use_peer) else "")},
+                           "step": "eager launches" + (", frames triple-buffered: the completion barrier (and the composite) of frame i runs on a side stream while frame i+1 renders" if world > 1 else "")},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
-                        "h2d_bytes_per_step": 128 * 16 + 48, "d2h_bytes_per_step": W * H * 4,
-                        "d2h_copy_alone_ms": d2h_ms, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory" + (" (exa_renderer_read_rgba8_async)" if world == 1 else " on rank 0 (swap chain of two peer-mapped buffers)") if (world == 1 or (mode == "tiles" and use_peer)) else "blocking read-back on rank 0"},
+                        "h2d_bytes_per_step": (128 * 16 + 48) * world, "d2h_bytes_per_step": W * H * 4,
+                        "d2h_bytes_per_step_per_rank": (W * H * 4) if world == 1 else pipe.d2h_bytes,
+                        "d2h_copy_alone_ms": d2h_ms, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory" + (" (exa_renderer_read_rgba8_async)" if world == 1 else
+                                     ": every rank copies its own strip / span over its own PCIe link into one pinned host frame shared by the ranks (POSIX shared memory, scan-line layout)")},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": ncu_traffic("k_renderFrame", name) if world == 1 else None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; almost all are served by L1/L2 (traffic = measured DRAM bytes of one launch, ncu): the frame kernel is issue-bound, not HBM-bound"},
-                "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms, "cpu_baseline": cpu}
+                "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms,
+                "barrier_alone_ms": barrier_ms, "sortlast": sortlast, "cpu_baseline": cpu,
+                "parity": parity, "build": build_info}
         print(json.dumps(line), flush=True)
     if world > 1:
         torch.cuda.synchronize()
         dist.barrier()
-        if mode == "tiles" and use_peer:                             # unmap / free the swap chain
-            r.resizeFrameBuffer(None, (W, H))
-            for p_ in fb_ptrs:
-                capi.check(capi.lib.exa_ipc_close(C.c_void_p(p_)) if rank != 0 else 0)
-            dist.barrier()
-            if rank == 0:
-                fb_views = None
-                for p_ in fb_ptrs:
-                    capi.check(capi.lib.exa_device_free(C.c_void_p(p_)))
+        if pipe is not None:
+            pipe.close()
         dist.destroy_process_group()
 
 
@@ -694,8 +795,10 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around warm-up + timed steps (for ncu --profile-from-start off)")
-    ap.add_argument("--no-peer-fb", action="store_true", help="N>1 image tiles: NCCL reduce of the frame instead of peer-memory stores")
+    ap.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce per frame instead of the peer-memory barrier kernel")
+    ap.add_argument("--no-sortlast", action="store_true", help="N>1: skip the secondary sort-last measurement")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "product" else args.warmup

@@ -186,7 +186,7 @@ int exa_colormap_eval(const float *controlPoints4, int numPoints, float t, float
 
 typedef struct exa_config exa_config_t;
 /* Config::parseConfigFile + finalize (tokens remap_from remap_to scalar vector value_range
- * bricks; 'triangles' is accepted and ignored, 'scalar .. expr' is not supported) */
+ * bricks triangles; 'scalar <name> expr "<postfix>"' evaluates ScalarField::createFromExpression) */
 int exa_config_parse(const char *fileName, int scalarCompat, exa_config_t **out);
 void exa_config_destroy(exa_config_t *c);
 const exa_bricks_t *exa_config_bricks(const exa_config_t *c);
@@ -215,6 +215,10 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields,
                         const size_t *fieldCounts, int numFields, int cudaDevice,
                         exa_renderer_t **out);
 void exa_renderer_destroy(exa_renderer_t *r);
+/* device time of the construction stages in ms: [0] ABR geometry (kd build, regions, leaf lists:
+ * ExaBrickRegions::buildFrom, exa/Regions.cpp:242-287), [1] scalar gather incl. the upload of cell IDs and
+ * fields (OptixRenderer.cpp:103-141), [2] dual-cell records, [3] value ranges (Regions.cpp:182-240, 290-300) */
+int exa_renderer_get_build_times(const exa_renderer_t *r, double ms[4]);
 /* Device layout of the scalars the sampling kernels read (new; the reference has only FLAT,
  * exa/OptixRenderer.cpp:103-132).  DUAL = one 32-byte record of the 8 corner scalars per dual
  * cell: 8x the memory, one DRAM sector per brick visit.  AUTO (default) = DUAL when the records
@@ -244,6 +248,13 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
  * frame i+1 renders into one caller-owned buffer while frame i's is copied to the host).
  * NULL: back to a renderer-owned buffer. */
 int exa_renderer_set_color_buffer(exa_renderer_t *r, void *fbPointer);
+/* Multi-GPU image tiles: the RGBA8 frame as `numStrips` row strips, strip k = rows [y0, y1) of
+ * exa_strip_rows (whole 8-row tile rows), stripPtrs[k] = device pointer of the strip's first pixel (local
+ * or peer memory).  Every rank's frame kernel stores its tiles into the strip they fall in, so strip k
+ * is complete on GPU k when all ranks have rendered and GPU k reads it back over its own PCIe link: the host
+ * frame is filled by N concurrent copies.  numStrips = 0: back to the single colour buffer. */
+int exa_renderer_set_color_strips(exa_renderer_t *r, void *const *stripPtrs, int numStrips);
+int exa_strip_rows(int k, int numStrips, int height, int *y0, int *y1);
 int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3],
                                const float dirDu[3], const float dirDv[3]);          /* :357-368 */
 /* updateXF(chan, opacities[128], colorMap[128] rgb, domain, opacityScale) (:370-404) */
@@ -335,21 +346,40 @@ uint64_t exa_renderer_launch_count(const exa_renderer_t *r);
  * Multi-GPU (new; the reference only replicates)
  * ------------------------------------------------------------------------------------- */
 enum { EXA_PARTITION_NONE = 0, EXA_PARTITION_SORT_LAST = 1, EXA_PARTITION_IMAGE_TILES = 2 };
-/* restrict this renderer to part `rank` of `numRanks` (power of two for sort-last) */
+/* Restrict this renderer to part `rank` of `numRanks`.
+ * IMAGE_TILES: the scene is replicated, the rank renders its share of the 16x8-pixel tiles.
+ * SORT_LAST on a renderer that holds the whole scene: the rank's kd subtree as a visibility mask
+ * (same partition tree as exa_renderer_create_partitioned; used by tests and as the replicated variant). */
 int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRanks);
-/* sort-last: render this rank's sub-volume to a premultiplied float4 partial image
- * (device memory, W*H*4 floats) */
-int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA);
-/* for round `round` of binary swap: 1 if this rank's sub-volume is in FRONT of its
- * partner's (rank ^ (1<<round)) as seen from the current camera */
-int exa_renderer_swap_order(exa_renderer_t *r, int round, int *iAmFront);
-/* d_mine = over(front, back) on `count` float4 pixels; mineIsFront selects the order */
-int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, size_t count,
-                       int mineIsFront);
-/* final shading of composited pixels [first, first+count): background, accumulation,
- * sRGB, RGBA8 pack (exabrick.cu:1701-1719) */
-int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_compositedRGBA, size_t first,
-                               size_t count, uint32_t *d_rgba8Out);
+/* Sort-last with the DATA partitioned (north_star's primary multi-GPU mode; the reference has none:
+ * programs/LaunchParams.h:31-32 deviceIndex/deviceCount are never read).  The ABR kd-tree is built from
+ * the brick headers (all ranks build the same one), cut into numRanks subtrees balanced by estimated
+ * lattice samples (volume / finest cell width; EXA_PARTITION_BALANCE=cells: by cells), and only the
+ * bricks listed by the regions of subtree `rank` are gathered, expanded and kept in device memory; the
+ * rest of this rank's kd-tree is pruned to empty leaves.  Regions inside the part see every brick that
+ * overlaps them (bricks straddling a cut are resident on both sides), so samples equal the single-GPU
+ * renderer's.  exa_renderer_get_abr still returns all regions; value ranges exist for the owned ones. */
+int exa_renderer_create_partitioned(const exa_bricks_t *bricks, const float *const *fields,
+                                    const size_t *fieldCounts, int numFields, int cudaDevice,
+                                    int rank, int numRanks, exa_renderer_t **out);
+/* bricks / cells resident on this renderer's device (all of them unless created partitioned) */
+int exa_renderer_get_residency(const exa_renderer_t *r, int *residentBricks, uint64_t *residentCells);
+/* visibility order of the sort-last parts for the current camera: order[0] is the front-most rank.
+ * All primary rays start at the camera position, so the order holds for every pixel. */
+int exa_renderer_partition_order(exa_renderer_t *r, int *order /* numRanks */, int *numParts);
+/* sort-last: render this rank's sub-volume to a premultiplied float4 partial image (device memory,
+ * W*H*4 floats; a ray that met the early-termination threshold carries alpha + 2) and, when a surface
+ * is enabled (iso / plane / mesh / cones), its nearest surface hit {shaded rgb, distance} per pixel
+ * into d_partialSurf (W*H*4 floats; may be NULL when no surface is enabled). */
+int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA, float *d_partialSurf);
+/* Fused composite + frame tail for the pixel span [first, first+count): reads the partials of ALL parts
+ * front-most first (pointers may be peer memory of other GPUs - the exchange then happens inside this
+ * kernel over NVLink - or local copies after an all-to-all), composites, picks the nearest surface,
+ * then background blend, accumulation, sRGB, RGBA8 pack (exabrick.cu:1701-1719) into d_rgba8Out
+ * (a whole-frame buffer; only the span is written). */
+int exa_renderer_composite_partials(exa_renderer_t *r, const float *const *d_partials,
+                                    const float *const *d_surfs /* or NULL */, int numParts,
+                                    size_t first, size_t count, uint32_t *d_rgba8Out);
 
 /* A device allocation of its own (cudaMalloc, zero-filled): unlike a sub-allocation of a caching
  * allocator it can be exported with exa_ipc_export.  Multi-GPU image-tile callers allocate the
@@ -363,6 +393,21 @@ int exa_device_free(void *d_ptr);
 int exa_ipc_export(const void *d_ptr, uint8_t handle[64]);
 int exa_ipc_import(const uint8_t handle[64], int cudaDevice, void **d_ptr);
 int exa_ipc_close(void *d_ptr);
+
+/* Stream-ordered barrier between the ranks of one NVSwitch box over peer memory (one process per GPU).
+ * flagPtrs[k] = rank k's flag array (exa_device_malloc of >= 17 uint32, zero-filled, IPC-mapped into every
+ * rank).  Enqueues a one-warp kernel on `cudaStream` that publishes `seq` (increasing, first call 1) to every
+ * rank and waits until every rank has published it: work enqueued after it on this stream sees what every
+ * rank's stream did before its own call (frame strips, partial images).  Replaces a 4-byte NCCL all-reduce
+ * (~64 us at 8 ranks) with ~2 us.  A rank that never arrives makes the wait time out after ~2 s and sets
+ * word 16 of the local array to 1 (check it after synchronising). */
+int exa_peer_barrier(void *const *flagPtrs, int rank, int numRanks, unsigned seq, void *cudaStream);
+/* cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault) on a caller's stream: strip / span read-back into a
+ * host frame shared by the ranks (each rank copies its part over its own PCIe link) */
+int exa_copy_async(void *dst, const void *src, size_t bytes, void *cudaStream);
+/* page-lock host memory the caller owns (e.g. a POSIX shared-memory frame mapped by all ranks) */
+int exa_host_register(void *ptr, size_t bytes);
+int exa_host_unregister(void *ptr);
 
 #ifdef __cplusplus
 }

@@ -125,10 +125,18 @@ _SIG = {
     "exa_sample_points_stats": (i32, [vp, vp, sz, i32, C.POINTER(ExaStats)]),
     "exa_renderer_launch_count": (C.c_uint64, [vp]),
     "exa_renderer_set_partition": (i32, [vp, i32, i32, i32]),
-    "exa_renderer_render_partial": (i32, [vp, vp]),
-    "exa_renderer_swap_order": (i32, [vp, i32, C.POINTER(i32)]),
-    "exa_composite_over": (i32, [vp, vp, vp, sz, i32]),
-    "exa_renderer_finish_pixels": (i32, [vp, vp, sz, sz, vp]),
+    "exa_renderer_render_partial": (i32, [vp, vp, vp]),
+    "exa_renderer_partition_order": (i32, [vp, vp, C.POINTER(i32)]),
+    "exa_renderer_composite_partials": (i32, [vp, vp, vp, i32, sz, sz, vp]),
+    "exa_renderer_create_partitioned": (i32, [vp, vp, vp, i32, i32, i32, i32, C.POINTER(vp)]),
+    "exa_renderer_get_residency": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
+    "exa_renderer_get_build_times": (i32, [vp, vp]),
+    "exa_renderer_set_color_strips": (i32, [vp, vp, i32]),
+    "exa_peer_barrier": (i32, [vp, i32, i32, C.c_uint32, vp]),
+    "exa_copy_async": (i32, [vp, vp, sz, vp]),
+    "exa_host_register": (i32, [vp, sz]),
+    "exa_host_unregister": (i32, [vp]),
+    "exa_strip_rows": (i32, [i32, i32, i32, C.POINTER(i32), C.POINTER(i32)]),
 }
 EXPORTS = sorted(_SIG)
 for _name, (_res, _args) in _SIG.items():

@@ -240,8 +240,7 @@ __device__ __forceinline__ float decF(unsigned a) { a ^= (a >> 31) ? 0x80000000u
 // per kd node that is a leaf: write region record, leaf list, blob; renumber the node
 __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, const int *offLeaf, const int *offList,
                            const Box3 *leafDom, const int *leafPoolBegin, const int *leafCount, const int *pool,
-                           const ExaBrick *bricks, const uint32_t *dualBegin, ExaBrickRegion *regions, int *leafList, int *entryRegion,
-                           unsigned *rangeEnc, uint4 *blobs)
+                           const ExaBrick *bricks, ExaBrickRegion *regions, int *leafList, int *entryRegion, uint4 *blobs)
 {
   int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= numNodes) return;
@@ -258,7 +257,7 @@ __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, cons
     const ExaBrick b = bricks[bid];
     finest = min(finest, b.level);
     BrickHdr h; h.lx = (float)b.lower[0]; h.ly = (float)b.lower[1]; h.lz = (float)b.lower[2];
-    h.invCw = 1.f / (float)(1 << b.level); h.sx = b.size[0]; h.sy = b.size[1]; h.sz = b.size[2]; h.begin = dualBegin ? dualBegin[bid] : b.begin;
+    h.invCw = 1.f / (float)(1 << b.level); h.sx = b.size[0]; h.sy = b.size[1]; h.sz = b.size[2]; h.begin = 0;   // first record: k_blobBegins
     const uint4 *hp = reinterpret_cast<const uint4 *>(&h);
     blobs[blobOfs + BLOB_HDR_UNITS + 2 * k] = hp[0]; blobs[blobOfs + BLOB_HDR_UNITS + 2 * k + 1] = hp[1];
   }
@@ -267,18 +266,20 @@ __global__ void k_finalize(int numNodes, KdNode *kd, const int *leafOfNode, cons
   r.valueRange_lower = 0.f; r.valueRange_upper = 0.f;            // filled by k_rangeDecode
   r.leafListBegin = lb; r.leafListSize = cnt; r.finestLevelCellWidth = (float)(1 << finest);
   regions[rid] = r;
-  rangeEnc[2 * rid] = 0xffffffffu; rangeEnc[2 * rid + 1] = 0u;   // empty: [+inf, -inf] after decode of untouched
   kd[g].k = (uint32_t)cnt; kd[g].info = (3u << 30) | blobOfs;
 }
 
-// computeValueRange, Regions.cpp:182-240: one CTA per (region, brick) leaf-list entry
+// computeValueRange, Regions.cpp:182-240: one CTA per (region, brick) leaf-list entry.
+// regionOwned != null (sort-last data partition): only the regions of this rank are ranged, the
+// bricks of the others are not resident
 __global__ void k_valueRange(int L, const int *leafList, const int *entryRegion, const ExaBrick *bricks,
                              const ExaBrickRegion *regions, const float *scalars, unsigned long long numCells,
-                             int numFields, unsigned *rangeEnc)
+                             int numFields, const uint8_t *regionOwned, unsigned *rangeEnc)
 {
   const int j = blockIdx.x;
   if (j >= L) return;
   const int rid = entryRegion[j];
+  if (regionOwned && !regionOwned[rid]) return;
   const ExaBrick b = bricks[leafList[j]];
   const ExaBrickRegion r = regions[rid];
   const float cw = (float)(1 << b.level);
@@ -304,6 +305,24 @@ __global__ void k_valueRange(int L, const int *leafList, const int *entryRegion,
   }
   for (int o = 16; o > 0; o >>= 1) { vmin = fminf(vmin, __shfl_xor_sync(0xffffffffu, vmin, o)); vmax = fmaxf(vmax, __shfl_xor_sync(0xffffffffu, vmax, o)); }
   if ((threadIdx.x & 31) == 0 && total > 0) { atomicMin(&rangeEnc[2 * rid], encF(vmin)); atomicMax(&rangeEnc[2 * rid + 1], encF(vmax)); }
+}
+
+// first record of every brick header inside the region blobs: the brick's first dual-cell record
+// or its first flat cell (both depend on which bricks are resident, so they are attached after
+// the structure is built); one thread per leaf-list entry
+__global__ void k_blobBegins(int L, const int *leafList, const int *entryRegion, const ExaBrick *bricks, const uint32_t *dualBegin, uint4 *blobs)
+{
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= L) return;
+  const int bid = leafList[j];
+  const size_t ofs = (size_t)BLOB_HDR_UNITS * (entryRegion[j] + 1) + (size_t)2 * j + 1;     // second 16-B unit of the header
+  blobs[ofs].w = dualBegin ? dualBegin[bid] : bricks[bid].begin;
+}
+
+__global__ void k_rangeInit(int nr, unsigned *rangeEnc)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < nr) { rangeEnc[2 * i] = 0xffffffffu; rangeEnc[2 * i + 1] = 0u; }
 }
 
 __global__ void k_rangeDecode(int nr, const unsigned *rangeEnc, ExaBrickRegion *regions, uint4 *blobs)
@@ -345,8 +364,7 @@ void abrFree(AbrResult &r)
   r = AbrResult();
 }
 
-int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t numCells,
-             int numFields, const uint32_t *d_dualBegin, void *streamV, AbrResult &out)
+int abrBuild(const ExaBrick *d_bricks, int nb, void *streamV, AbrResult &out)
 {
   cudaStream_t s = (cudaStream_t)streamV;
   out = AbrResult();
@@ -354,12 +372,12 @@ int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t 
   uint64_t launches = 0;
 
   // ---- root bounds (Regions.cpp:264-278) ----
-  unsigned *d_enc; CK(cudaMalloc(&d_enc, 6 * sizeof(unsigned)));
+  DevBuf<unsigned> d_enc; CK(d_enc.reserve(6, s));
   unsigned encInit[6] = {0xffffffffu, 0xffffffffu, 0xffffffffu, 0, 0, 0};
-  CK(cudaMemcpyAsync(d_enc, encInit, sizeof(encInit), cudaMemcpyHostToDevice, s));
-  k_rootBounds<<<blocks(nb), 256, 0, s>>>(d_bricks, nb, d_enc); launches++;
-  unsigned encOut[6]; CK(cudaMemcpyAsync(encOut, d_enc, sizeof(encOut), cudaMemcpyDeviceToHost, s));
-  CK(cudaStreamSynchronize(s)); cudaFree(d_enc);
+  CK(cudaMemcpyAsync(d_enc.p, encInit, sizeof(encInit), cudaMemcpyHostToDevice, s));
+  k_rootBounds<<<blocks(nb), 256, 0, s>>>(d_bricks, nb, d_enc.p); launches++;
+  unsigned encOut[6]; CK(cudaMemcpyAsync(encOut, d_enc.p, sizeof(encOut), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
   Box3 rootDom;
   for (int d = 0; d < 3; d++) {
     unsigned a = encOut[d], b = encOut[3 + d];
@@ -437,36 +455,55 @@ int abrBuild(const ExaBrick *d_bricks, int nb, const float *d_scalars, uint64_t 
   CK(cudaStreamSynchronize(s));
 
   // ---- right-first DFS numbering ----
-  int *cntLeaf, *cntList, *offLeaf, *offList;
-  CK(cudaMalloc(&cntLeaf, 4 * (size_t)numNodes)); CK(cudaMalloc(&cntList, 4 * (size_t)numNodes));
-  CK(cudaMalloc(&offLeaf, 4 * (size_t)numNodes)); CK(cudaMalloc(&offList, 4 * (size_t)numNodes));
+  DevBuf<int> cntLeaf, cntList, offLeaf, offList;
+  CK(cntLeaf.reserve((size_t)numNodes, s)); CK(cntList.reserve((size_t)numNodes, s));
+  CK(offLeaf.reserve((size_t)numNodes, s)); CK(offList.reserve((size_t)numNodes, s));
   for (int lv = depth - 1; lv >= 0; lv--) {
     const int first = levelOffset[lv], cnt = levelOffset[lv + 1] - first;
-    k_countUp<<<blocks(cnt), 256, 0, s>>>(first, cnt, kd.p, leafOfNode.p, leafCount.p, cntLeaf, cntList); launches++;
+    k_countUp<<<blocks(cnt), 256, 0, s>>>(first, cnt, kd.p, leafOfNode.p, leafCount.p, cntLeaf.p, cntList.p); launches++;
   }
-  CK(cudaMemsetAsync(offLeaf, 0, 4, s)); CK(cudaMemsetAsync(offList, 0, 4, s));
+  CK(cudaMemsetAsync(offLeaf.p, 0, 4, s)); CK(cudaMemsetAsync(offList.p, 0, 4, s));
   for (int lv = 0; lv < depth; lv++) {
     const int first = levelOffset[lv], cnt = levelOffset[lv + 1] - first;
-    k_offsetDown<<<blocks(cnt), 256, 0, s>>>(first, cnt, kd.p, cntLeaf, cntList, offLeaf, offList); launches++;
+    k_offsetDown<<<blocks(cnt), 256, 0, s>>>(first, cnt, kd.p, cntLeaf.p, cntList.p, offLeaf.p, offList.p); launches++;
   }
   const int nr = numLeaves, L = poolUsed;
-  ExaBrickRegion *regions; int *leafList, *entryRegion; unsigned *rangeEnc; uint4 *blobs;
   const size_t blobUnits = (size_t)BLOB_HDR_UNITS * nr + (size_t)2 * L;
   if (blobUnits >= KD_EMPTY) { setError("abrBuild: region blob exceeds 30-bit offset"); return EXA_ERR_LIMIT; }
-  CK(cudaMalloc(&regions, sizeof(ExaBrickRegion) * (size_t)std::max(nr, 1))); CK(cudaMalloc(&leafList, 4 * (size_t)std::max(L, 1)));
-  CK(cudaMalloc(&entryRegion, 4 * (size_t)std::max(L, 1))); CK(cudaMalloc(&rangeEnc, 8 * (size_t)std::max(nr, 1)));
-  CK(cudaMalloc(&blobs, 16 * std::max(blobUnits, (size_t)1)));
-  k_finalize<<<blocks(numNodes), 256, 0, s>>>(numNodes, kd.p, leafOfNode.p, offLeaf, offList, leafDom.p, leafPoolBegin.p, leafCount.p, pool.p,
-                                               d_bricks, d_dualBegin, regions, leafList, entryRegion, rangeEnc, blobs); launches++;
-  if (L > 0) { k_valueRange<<<L, 256, 0, s>>>(L, leafList, entryRegion, d_bricks, regions, d_scalars, (unsigned long long)numCells, numFields, rangeEnc); launches++; }
-  if (nr > 0) { k_rangeDecode<<<blocks(nr), 256, 0, s>>>(nr, rangeEnc, regions, blobs); launches++; }
+  // the results go into `out` as soon as they exist: on an error below the caller's abrFree(out) releases them
+  CK(cudaMalloc(&out.regions, sizeof(ExaBrickRegion) * (size_t)std::max(nr, 1))); CK(cudaMalloc(&out.leafList, 4 * (size_t)std::max(L, 1)));
+  CK(cudaMalloc(&out.entryRegion, 4 * (size_t)std::max(L, 1)));
+  CK(cudaMalloc(&out.blobs, 16 * std::max(blobUnits, (size_t)1)));
+  k_finalize<<<blocks(numNodes), 256, 0, s>>>(numNodes, kd.p, leafOfNode.p, offLeaf.p, offList.p, leafDom.p, leafPoolBegin.p, leafCount.p, pool.p,
+                                               d_bricks, out.regions, out.leafList, out.entryRegion, out.blobs); launches++;
   CK(cudaStreamSynchronize(s));
   CK(cudaGetLastError());
-  cudaFree(cntLeaf); cudaFree(cntList); cudaFree(offLeaf); cudaFree(offList); cudaFree(rangeEnc);
-
-  out.regions = regions; out.numRegions = nr; out.leafList = leafList; out.leafListLen = L; out.entryRegion = entryRegion;
+  out.numRegions = nr; out.leafListLen = L;
   out.kd = kd.release(); out.numKdNodes = numNodes; out.depth = depth; out.levelOffset = levelOffset;
-  out.blobs = blobs; out.blobUnits = blobUnits; out.launches = launches;
+  out.blobUnits = blobUnits; out.launches = launches;
+  return EXA_OK;
+}
+
+// Second phase: attach the resident scalars.  Writes the first-record field of the brick headers in the
+// region blobs, computes the value ranges (Regions.cpp:182-240) of the regions in d_regionOwned (null: all)
+// and completes the region records / blob headers.
+int abrAttachScalars(AbrResult &abr, const ExaBrick *d_bricks, const float *d_scalars, uint64_t numCells, int numFields,
+                     const uint32_t *d_dualBegin, const uint8_t *d_regionOwned, void *streamV)
+{
+  cudaStream_t s = (cudaStream_t)streamV;
+  const int nr = abr.numRegions, L = abr.leafListLen;
+  DevBuf<unsigned> rangeEnc;
+  CK(rangeEnc.reserve(2 * (size_t)std::max(nr, 1), s));
+  // empty range: [+inf, -inf] after decode
+  if (nr > 0) { k_rangeInit<<<blocks(nr), 256, 0, s>>>(nr, rangeEnc.p); abr.launches++; }
+  if (L > 0) {
+    k_blobBegins<<<blocks(L), 256, 0, s>>>(L, abr.leafList, abr.entryRegion, d_bricks, d_dualBegin, abr.blobs); abr.launches++;
+    k_valueRange<<<L, 256, 0, s>>>(L, abr.leafList, abr.entryRegion, d_bricks, abr.regions, d_scalars, (unsigned long long)numCells, numFields,
+                                   d_regionOwned, rangeEnc.p); abr.launches++;
+  }
+  if (nr > 0) { k_rangeDecode<<<blocks(nr), 256, 0, s>>>(nr, rangeEnc.p, abr.regions, abr.blobs); abr.launches++; }
+  CK(cudaStreamSynchronize(s));
+  CK(cudaGetLastError());
   return EXA_OK;
 }
 

@@ -251,7 +251,7 @@ struct Builder {
     } else {
       const int T = omp_get_max_threads();
       std::vector<size_t> cl(T + 1, 0);
-      bool straddle = false;
+      std::atomic<bool> straddle{false};
 #pragma omp parallel num_threads(T)
       {
         const int t = omp_get_thread_num();
@@ -260,17 +260,17 @@ struct Builder {
         for (size_t i = b; i < e; i++) {
           const int lo = coord(v[i]);
           if (lo >= bestPos) continue;
-          if (lo + (1 << v[i].level) <= bestPos) k++; else straddle = true;
+          if (lo + (1 << v[i].level) <= bestPos) k++; else straddle.store(true, std::memory_order_relaxed);
         }
         cl[t + 1] = k;
 #pragma omp barrier
 #pragma omp single
         for (int q = 0; q < T; q++) cl[q + 1] += cl[q];
         size_t pl = cl[t], pr = cl[T] + (b - cl[t]);
-        if (!straddle)
+        if (!straddle.load())
           for (size_t i = b; i < e; i++) { if (coord(v[i]) >= bestPos) o[pr++] = v[i]; else o[pl++] = v[i]; }
       }
-      if (straddle) throw std::runtime_error("cell straddles split plane!?");
+      if (straddle.load()) throw std::runtime_error("cell straddles split plane!?");
       nl = cl[T];
     }
     if (nl == 0 || nl == n) throw std::runtime_error("invalid split...");

@@ -25,6 +25,7 @@ struct exa_renderer {
   float *d_scalars = nullptr; uint64_t numCells = 0; int numFields = 0;
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
   uint2 *d_locGrid = nullptr; int locG = 0; float locScale[3] = {0, 0, 0};              // point-location grid
+  int indexPrefetch = 1;                 // EXA_INDEX_PREFETCH=0 switches the L2 index prefetch of large point queries off
   float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
@@ -39,15 +40,22 @@ struct exa_renderer {
   // framebuffer
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
+  uint32_t *strips[EXA_MAX_PARTS] = {}; int numStrips = 0;   // exa_renderer_set_color_strips
   // pipelined read-back (exa_renderer_read_rgba8_async): second renderer-owned RGBA8 buffer, copy stream
   uint32_t *d_rgba8Alt = nullptr; cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr, evCopied[2] = {nullptr, nullptr}; int rbCur = 0;
   // pinned staging ring for updateXF (no stream synchronise per update)
   float4 *h_xfRing = nullptr; cudaEvent_t evXf[8] = {}; unsigned xfRingPos = 0;
   // partition
   int partMode = EXA_PARTITION_NONE, rank = 0, numRanks = 1; int partRoot = 0;
-  std::vector<int> partPath;             // kd node visited at each partition level
+  // sort-last: partition tree over the top of the ABR kd-tree (buildPartitionTree); leaf: left < 0, owner = rank
+  struct PartNode { int kd; int left, right; int rank; };
+  std::vector<PartNode> partTree;
+  bool dataPartitioned = false;          // exa_renderer_create_partitioned: only this rank's bricks are resident, the rest of the kd-tree is pruned
+  int residentBricks = 0;
+  double buildMs[4] = {0, 0, 0, 0};      // ABR geometry, scalar gather, dual records, value ranges (device time)
   // tracer
-  int tracerEnabled = 0, numTraces = 1000, numTimesteps = 100, timestep = 0;
+  int tracerEnabled = 0, numTraces = 1000, numTimesteps = 100, timestep = 0;   // numTraces x numTimesteps = the shape of d_traces
+  int pendNumTraces = 1000, pendNumTimesteps = 100;                           // set_tracer_params; committed when d_traces is rebuilt
   float steplen = 1e-6f; int tracerChannels[3] = {0, 1, 2};
   float seedLo[3] = {.3f, .3f, .5f}, seedHi[3] = {.8f, .8f, .5f};
   float *d_traces = nullptr; size_t tracesCap = 0;
@@ -57,7 +65,6 @@ struct exa_renderer {
   float coneLo[3] = {0, 0, 0}, coneCell[3] = {1, 1, 1};                                  // uniform grid over the visible cones (buildConeGrid)
   unsigned long long *d_stats = nullptr;
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
-  LongRay *d_longQueue = nullptr; int *d_longCount = nullptr; int sampleBudget = 0;       // long-ray hand-over to k_renderLong; 0 = single pass (default: measured faster on C2)
   TileOrder *d_tileOrder[2] = {nullptr, nullptr}; int tileOrderCap = 0, tileOrderCur = 0; bool tileOrderValid = false;
 };
 
@@ -86,6 +93,16 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   memcpy(P.camPos, r->fs.camera.pos, 12); memcpy(P.dir00, r->fs.camera.dir00, 12);
   memcpy(P.dirDu, r->fs.camera.dirDu, 12); memcpy(P.dirDv, r->fs.camera.dirDv, 12);
   memcpy(P.xfm, &r->fs.voxelSpaceTransform, 48);
+  {
+    // xfmPoint(xfm, camPos) exactly as the device evaluates it (render.cu: products and sums rounded separately, no FMA)
+    const float *m = P.xfm, *v = P.camPos;
+    for (int k = 0; k < 3; k++) {
+      volatile float p0 = v[0] * m[k], p1 = v[1] * m[3 + k], p2 = v[2] * m[6 + k];
+      volatile float s01 = p0 + p1; volatile float s012 = s01 + p2;
+      volatile float q = s012 + m[9 + k];
+      P.camVoxel[k] = q;
+    }
+  }
   P.width = r->width; P.height = r->height; P.frameID = r->fs.frameID; P.dt = r->dt;
   P.numChannels = r->numFields; P.colormapChannel = 0;     // multiFieldDvr (OptixRenderer.h:110, .cpp:276-283)
   P.gradDVR = r->gradDVR; P.gradISO = r->gradISO;
@@ -100,6 +117,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.ertThreshold = r->ert;
   P.volActive = r->d_volActive; P.isoActive = r->d_isoActive; P.regionActive = r->d_regionActive;
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
+  P.numStrips = r->numStrips; for (int k = 0; k < r->numStrips; k++) P.strip[k] = r->strips[k];
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
   // copy of the time step stops at numTimesteps (OptixRenderer.cpp:481-484)
@@ -119,7 +137,6 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.meshNodes = r->d_meshNodes; P.meshTris = r->d_meshTris; P.numMeshTris = r->numMeshTris;
   P.anySurf = (anyContour || P.traces || P.numMeshTris > 0 || (P.aoEnabled && P.anyIso)) ? 2 : P.anyIso ? 1 : 0;
   P.stats = nullptr;
-  P.longQueue = r->d_longQueue; P.longCount = r->d_longCount; P.sampleBudget = r->sampleBudget;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
   P.kdStack = r->abr.depth + 2;
   P.dbg = 0;
@@ -177,13 +194,77 @@ int exa_cuda_available(void)
   return 1;
 }
 
-int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
-                        int numFields, int cudaDevice, exa_renderer_t **out)
+// ---- sort-last partition tree --------------------------------------------------------------------
+// The partition is a prefix of the ABR kd-tree: starting from {root}, the subtree with the largest
+// cost is replaced by its two children until there are numRanks subtrees (or only leaves are left).
+// Rank k owns the k-th subtree in left-to-right order.  Every subtree is a convex box of disjoint
+// regions, so for a pinhole camera the visibility order of the parts is the same for every pixel:
+// at each inner node of the partition tree the side that holds the camera comes first.
+static void nodeCosts(const std::vector<KdNode> &kd, const std::vector<ExaBrickRegion> &regions, const std::vector<int32_t> &leafList,
+                      const ExaBrick *hb, bool byCells, std::vector<double> &cost)
+{
+  // region of a kd leaf: blob offset = BLOB_HDR_UNITS * rid + 2 * leafListBegin(rid), increasing in rid
+  std::vector<uint32_t> blobOfs(regions.size());
+  for (size_t i = 0; i < regions.size(); i++) blobOfs[i] = (uint32_t)(BLOB_HDR_UNITS * i + 2 * (size_t)regions[i].leafListBegin);
+  cost.assign(kd.size(), 0.0);
+  for (size_t g = kd.size(); g-- > 0;) {                       // children have larger indices than their parent (level order)
+    const KdNode nd = kd[g];
+    const uint32_t pl = nd.info & 0x3fffffffu;
+    if ((nd.info >> 30) != 3) { cost[g] = cost[pl] + cost[pl + 1]; continue; }
+    if (pl == KD_EMPTY) continue;
+    const size_t rid = std::lower_bound(blobOfs.begin(), blobOfs.end(), pl) - blobOfs.begin();
+    const ExaBrickRegion &r = regions[rid];
+    const double vol = (double)(r.domain_upper[0] - r.domain_lower[0]) * (double)(r.domain_upper[1] - r.domain_lower[1]) * (double)(r.domain_upper[2] - r.domain_lower[2]);
+    if (!byCells) cost[g] = vol / (double)r.finestLevelCellWidth;          // ~ lattice samples of a uniform ray bundle
+    else for (int k = 0; k < r.leafListSize; k++) { const double cw = (double)(1 << hb[leafList[r.leafListBegin + k]].level); cost[g] += vol / (cw * cw * cw); }
+  }
+}
+
+static void buildPartitionTree(exa_renderer *r, int numRanks, const std::vector<double> &cost)
+{
+  typedef exa_renderer::PartNode PN;
+  r->partTree.clear();
+  r->partTree.push_back(PN{0, -1, -1, 0});
+  int parts = 1;
+  while (parts < numRanks) {
+    int best = -1; double bc = -1.0;
+    for (size_t i = 0; i < r->partTree.size(); i++) {
+      const PN &n = r->partTree[i];
+      if (n.left >= 0 || (r->h_kd[n.kd].info >> 30) == 3) continue;     // already split / a kd leaf cannot be split
+      if (cost[n.kd] > bc) { bc = cost[n.kd]; best = (int)i; }
+    }
+    if (best < 0) break;
+    const int c = (int)(r->h_kd[r->partTree[best].kd].info & 0x3fffffffu);
+    const int li = (int)r->partTree.size();
+    r->partTree.push_back(PN{c, -1, -1, 0}); r->partTree.push_back(PN{c + 1, -1, -1, 0});
+    r->partTree[best].left = li; r->partTree[best].right = li + 1;
+    parts++;
+  }
+  // ranks in left-to-right order of the partition leaves
+  int next = 0;
+  std::vector<int> st; st.push_back(0);
+  while (!st.empty()) {
+    const int i = st.back(); st.pop_back();
+    PN &n = r->partTree[i];
+    if (n.left < 0) { n.rank = next++; continue; }
+    st.push_back(n.right); st.push_back(n.left);
+  }
+}
+
+static int partitionRootOf(const exa_renderer *r, int rank)
+{
+  for (const exa_renderer::PartNode &n : r->partTree) if (n.left < 0 && n.rank == rank) return n.kd;
+  return -1;                                                   // fewer parts than ranks: this rank owns nothing
+}
+
+static int createImpl(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
+                      int numFields, int cudaDevice, int partRank, int partRanks, exa_renderer_t **out)
 {
   if (!bricks || !out || !fields || !fieldCounts) { setError("exa_renderer_create: null argument"); return EXA_ERR_INVALID; }
   if (numFields < 1 || numFields > EXA_MAX_CHANNELS) { setError("exa_renderer_create: numFields must be 1.." + std::to_string(EXA_MAX_CHANNELS)); return EXA_ERR_INVALID; }
-  const size_t nb = exa_bricks_count(bricks), nc = exa_bricks_num_cells(bricks);
-  if (nb == 0 || nc == 0) { setError("exa_renderer_create: empty brick set"); return EXA_ERR_INVALID; }
+  if (partRanks < 1 || partRank < 0 || partRank >= partRanks) { setError("exa_renderer_create_partitioned: bad rank"); return EXA_ERR_INVALID; }
+  const size_t nb = exa_bricks_count(bricks), ncAll = exa_bricks_num_cells(bricks);
+  if (nb == 0 || ncAll == 0) { setError("exa_renderer_create: empty brick set"); return EXA_ERR_INVALID; }
   if (nb > 0x3fffffffull) { setError("too many bricks"); return EXA_ERR_LIMIT; }
   const int ndev = cudaUsable(); if (!ndev) return EXA_ERR_CUDA;
   if (cudaDevice < 0 || cudaDevice >= ndev) { setError("exa_renderer_create: bad device index"); return EXA_ERR_INVALID; }
@@ -191,40 +272,105 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   if (const char *e = getenv("EXA_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob: 32/64/128
   exa_renderer *r = new exa_renderer;
   r->device = cudaDevice;
+  if (const char *e = getenv("EXA_INDEX_PREFETCH")) r->indexPrefetch = atoi(e);
   memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
   identityXfm((float *)&r->fs.voxelSpaceTransform);
   r->fs.xfOpacityScale = 1.f; r->fs.ao.length = 1e20f; r->fs.ao.enabled = 0;
   for (int i = 0; i < EXA_MAX_CONTOUR_PLANES; i++) { r->fs.contourPlane[i].normal[0] = 1.f; r->fs.contourPlane[i].offset = .5f; }
   for (int c = 0; c < EXA_MAX_CHANNELS; c++) { r->fs.xfDomain[c][0] = 0.f; r->fs.xfDomain[c][1] = 1.f; }
-  r->numBricks = (int)nb; r->numCells = nc; r->numFields = numFields;
+  r->numBricks = (int)nb; r->numFields = numFields;
   exa_bricks_get_bounds(bricks, r->voxelLo, r->voxelHi);
   memcpy(r->worldLo, r->voxelLo, 12); memcpy(r->worldHi, r->voxelHi, 12);
   cudaStream_t s = r->stream;
   int rc = EXA_OK;
+  // temporaries of the set-up live in RAII holders: every error path below releases them
+  struct Dev { void *p = nullptr; ~Dev() { if (p) cudaFree(p); } } d_ids, d_field, d_err, d_owned;
+  struct Ev { cudaEvent_t e = nullptr; ~Ev() { if (e) cudaEventDestroy(e); } } ev[6];
 #define CKC(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { \
     setError(std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call); exa_renderer_destroy(r); return EXA_ERR_CUDA; } } while (0)
-  // ---- flatten: Brick[] + scalar gather through the cell IDs (OptixRenderer.cpp:71-141) ----
+  for (int i = 0; i < 6; i++) CKC(cudaEventCreate(&ev[i].e));
+  const ExaBrick *hb = exa_bricks_headers(bricks);
+  const int32_t *hids = exa_bricks_cell_ids(bricks);
+  // ---- Brick[] (OptixRenderer.cpp:71-93) and the ABR geometry on the GPU (exa/Regions.cpp:242-287) ----
   CKC(cudaMalloc(&r->d_bricks, nb * sizeof(ExaBrick)));
-  CKC(cudaMemcpyAsync(r->d_bricks, exa_bricks_headers(bricks), nb * sizeof(ExaBrick), cudaMemcpyHostToDevice, s));
+  CKC(cudaMemcpyAsync(r->d_bricks, hb, nb * sizeof(ExaBrick), cudaMemcpyHostToDevice, s));
+  CKC(cudaEventRecord(ev[0].e, s));
+  rc = abrBuild(r->d_bricks, r->numBricks, s, r->abr);
+  if (rc) { exa_renderer_destroy(r); return rc; }
+  CKC(cudaEventRecord(ev[1].e, s));
+  if (r->abr.depth + 2 > 160) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
+  r->h_kd.resize(r->abr.numKdNodes);
+  CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
+  // ---- which bricks are resident: all of them, or (sort-last data partition) those of this rank's kd subtree ----
+  std::vector<uint32_t> newBegin;                            // first flat cell of every resident brick in the compacted arrays
+  std::vector<uint8_t> resident(nb, 1);
+  size_t nc = ncAll;
+  if (partRanks > 1) {
+    std::vector<ExaBrickRegion> regions(r->abr.numRegions); std::vector<int32_t> leafList(r->abr.leafListLen);
+    CKC(cudaMemcpy(regions.data(), r->abr.regions, sizeof(ExaBrickRegion) * regions.size(), cudaMemcpyDeviceToHost));
+    CKC(cudaMemcpy(leafList.data(), r->abr.leafList, 4 * leafList.size(), cudaMemcpyDeviceToHost));
+    std::vector<double> cost;
+    const char *bal = getenv("EXA_PARTITION_BALANCE");
+    nodeCosts(r->h_kd, regions, leafList, hb, bal && !strcmp(bal, "cells"), cost);
+    buildPartitionTree(r, partRanks, cost);
+    r->partMode = EXA_PARTITION_SORT_LAST; r->rank = partRank; r->numRanks = partRanks; r->dataPartitioned = true;
+    r->partRoot = partitionRootOf(r, partRank);
+    // owned leaves: DFS below the partition root; everything else becomes an empty leaf of THIS rank's kd-tree
+    std::vector<uint8_t> ownedNode(r->h_kd.size(), 0), ownedRegion(std::max<size_t>(regions.size(), 1), 0);
+    std::fill(resident.begin(), resident.end(), 0);
+    std::vector<uint32_t> blobOfs(regions.size());
+    for (size_t i = 0; i < regions.size(); i++) blobOfs[i] = (uint32_t)(BLOB_HDR_UNITS * i + 2 * (size_t)regions[i].leafListBegin);
+    std::vector<int> st; if (r->partRoot >= 0) st.push_back(r->partRoot);
+    while (!st.empty()) {
+      const int g = st.back(); st.pop_back(); ownedNode[g] = 1;
+      const KdNode nd = r->h_kd[g]; const uint32_t pl = nd.info & 0x3fffffffu;
+      if ((nd.info >> 30) != 3) { st.push_back((int)pl); st.push_back((int)pl + 1); continue; }
+      if (pl == KD_EMPTY) continue;
+      const size_t rid = std::lower_bound(blobOfs.begin(), blobOfs.end(), pl) - blobOfs.begin();
+      ownedRegion[rid] = 1;
+      for (int k = 0; k < regions[rid].leafListSize; k++) resident[leafList[regions[rid].leafListBegin + k]] = 1;
+    }
+    for (size_t g = 0; g < r->h_kd.size(); g++)
+      if (!ownedNode[g] && (r->h_kd[g].info >> 30) == 3) { r->h_kd[g].k = 0; r->h_kd[g].info = (3u << 30) | KD_EMPTY; }
+    CKC(cudaMemcpy(r->abr.kd, r->h_kd.data(), sizeof(KdNode) * r->h_kd.size(), cudaMemcpyHostToDevice));
+    CKC(cudaMalloc(&d_owned.p, ownedRegion.size()));
+    CKC(cudaMemcpy(d_owned.p, ownedRegion.data(), ownedRegion.size(), cudaMemcpyHostToDevice));
+    // compacted flat layout: resident bricks keep their order; the others get begin = 0 and are unreachable
+    newBegin.assign(nb, 0); size_t tot = 0; int nres = 0;
+    for (size_t i = 0; i < nb; i++) if (resident[i]) { newBegin[i] = (uint32_t)tot; tot += (size_t)hb[i].size[0] * hb[i].size[1] * hb[i].size[2]; nres++; }
+    nc = std::max<size_t>(tot, 1); r->residentBricks = nres;
+    std::vector<ExaBrick> hdr(hb, hb + nb);
+    for (size_t i = 0; i < nb; i++) hdr[i].begin = newBegin[i];
+    CKC(cudaMemcpy(r->d_bricks, hdr.data(), nb * sizeof(ExaBrick), cudaMemcpyHostToDevice));
+  } else r->residentBricks = (int)nb;
+  r->numCells = nc;
+  // ---- flatten: scalar gather through the cell IDs (OptixRenderer.cpp:103-141) ----
+  CKC(cudaEventRecord(ev[2].e, s));
   CKC(cudaMalloc(&r->d_scalars, sizeof(float) * nc * (size_t)numFields));
   {
-    int32_t *d_ids = nullptr; float *d_field = nullptr; int *d_err = nullptr; size_t fieldCap = 0;
-    CKC(cudaMalloc(&d_ids, nc * 4)); CKC(cudaMalloc(&d_err, 4)); CKC(cudaMemsetAsync(d_err, 0, 4, s));
-    CKC(cudaMemcpyAsync(d_ids, exa_bricks_cell_ids(bricks), nc * 4, cudaMemcpyHostToDevice, s));
+    size_t fieldCap = 0;
+    CKC(cudaMalloc(&d_ids.p, nc * 4)); CKC(cudaMalloc(&d_err.p, 4)); CKC(cudaMemsetAsync(d_err.p, 0, 4, s));
+    if (partRanks > 1) {
+      for (size_t i = 0; i < nb; i++) if (resident[i]) {
+        const size_t n = (size_t)hb[i].size[0] * hb[i].size[1] * hb[i].size[2];
+        CKC(cudaMemcpyAsync((int32_t *)d_ids.p + newBegin[i], hids + hb[i].begin, n * 4, cudaMemcpyHostToDevice, s));
+      }
+    } else CKC(cudaMemcpyAsync(d_ids.p, hids, nc * 4, cudaMemcpyHostToDevice, s));
     for (int f = 0; f < numFields; f++) {
       if (!fields[f] || fieldCounts[f] == 0) { setError("exa_renderer_create: empty scalar field"); rc = EXA_ERR_INVALID; break; }
-      if (fieldCounts[f] > fieldCap) { if (d_field) { cudaStreamSynchronize(s); cudaFree(d_field); } CKC(cudaMalloc(&d_field, fieldCounts[f] * 4)); fieldCap = fieldCounts[f]; }
-      CKC(cudaMemcpyAsync(d_field, fields[f], fieldCounts[f] * 4, cudaMemcpyHostToDevice, s));
-      if (launchGather(d_field, fieldCounts[f], d_ids, nc, r->d_scalars + (size_t)f * nc, d_err, s) < 0) { setError("gather launch failed"); rc = EXA_ERR_CUDA; break; }
+      if (fieldCounts[f] > fieldCap) { if (d_field.p) { cudaStreamSynchronize(s); cudaFree(d_field.p); d_field.p = nullptr; } CKC(cudaMalloc(&d_field.p, fieldCounts[f] * 4)); fieldCap = fieldCounts[f]; }
+      CKC(cudaMemcpyAsync(d_field.p, fields[f], fieldCounts[f] * 4, cudaMemcpyHostToDevice, s));
+      if (launchGather((const float *)d_field.p, fieldCounts[f], (const int32_t *)d_ids.p, nc, r->d_scalars + (size_t)f * nc, (int *)d_err.p, s) < 0) { setError("gather launch failed"); rc = EXA_ERR_CUDA; break; }
       r->launches++;
       CKC(cudaStreamSynchronize(s));
     }
     int herr = 0;
-    if (!rc) { CKC(cudaMemcpy(&herr, d_err, 4, cudaMemcpyDeviceToHost)); }
-    cudaFree(d_ids); cudaFree(d_field); cudaFree(d_err);
+    if (!rc) { CKC(cudaMemcpy(&herr, d_err.p, 4, cudaMemcpyDeviceToHost)); }
+    cudaFree(d_ids.p); d_ids.p = nullptr; cudaFree(d_field.p); d_field.p = nullptr;
     if (!rc && herr) { setError(herr == 1 ? "negative cell ID" : "invalid cell ID"); rc = EXA_ERR_INVALID; }   // OptixRenderer.cpp:122-127
     if (rc) { exa_renderer_destroy(r); return rc; }
   }
+  CKC(cudaEventRecord(ev[3].e, s));
   {
     std::vector<unsigned> offs(numFields); std::vector<int> prim(numFields);
     for (int f = 0; f < numFields; f++) { offs[f] = (unsigned)((size_t)f * nc); prim[f] = f; }   // 32-bit view valid while C*Nc < 2^32
@@ -236,18 +382,18 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   {
     int mode = g_scalarLayout;
     if (const char *e = getenv("EXA_SCALAR_LAYOUT")) mode = atoi(e);
-    const ExaBrick *hb = exa_bricks_headers(bricks);
-    std::vector<uint32_t> begin(nb); uint64_t total = 0; bool fits32 = true;
+    std::vector<uint32_t> begin(nb, 0); uint64_t total = 0; bool fits32 = true;
     for (size_t i = 0; i < nb; i++) {
       if (total > 0xffffffffull) { fits32 = false; break; }
-      begin[i] = (uint32_t)total;
+      begin[i] = (uint32_t)total;                              // non-resident bricks: empty span (keeps begin[] sorted for k_expandDual's search)
+      if (!resident[i]) continue;
       total += (uint64_t)(hb[i].size[0] + 1) * (uint64_t)(hb[i].size[1] + 1) * (uint64_t)(hb[i].size[2] + 1);
     }
     size_t freeB = 0, totalB = 0; CKC(cudaMemGetInfo(&freeB, &totalB));
     const uint64_t need = total * 32ull * (uint64_t)numFields;
     // auto: build the records when they fit in 40% of the free HBM and 32-bit record offsets
     const bool want = mode == EXA_LAYOUT_DUAL || (mode == EXA_LAYOUT_AUTO && need <= (uint64_t)(0.4 * (double)freeB));
-    if (want && fits32 && total <= 0xffffffffull && need + (64ull << 20) < freeB) {
+    if (want && total > 0 && fits32 && total <= 0xffffffffull && need + (64ull << 20) < freeB) {
       CKC(cudaMalloc(&r->d_dualBegin, nb * 4));
       CKC(cudaMemcpyAsync(r->d_dualBegin, begin.data(), nb * 4, cudaMemcpyHostToDevice, s));
       CKC(cudaMalloc(&r->d_dual, need));
@@ -257,17 +403,26 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
           setError("dual-record expansion failed"); exa_renderer_destroy(r); return EXA_ERR_CUDA; }
         r->launches++;
       }
-      CKC(cudaStreamSynchronize(s));
-    } else if (mode == EXA_LAYOUT_DUAL) {
+      CKC(cudaStreamSynchronize(s));                           // begin[] goes out of scope
+    } else if (mode == EXA_LAYOUT_DUAL && total > 0) {
       setError("EXA_LAYOUT_DUAL requested but the dual-cell records do not fit (memory or 32-bit record offsets)");
       exa_renderer_destroy(r); return EXA_ERR_LIMIT;
     }
   }
-  // ---- ABR build on the GPU (exa/Regions.cpp:242-320) ----
-  rc = abrBuild(r->d_bricks, r->numBricks, r->d_scalars, r->numCells, numFields, r->d_dualBegin, s, r->abr);
+  CKC(cudaEventRecord(ev[4].e, s));
+  // ---- value ranges + scalar offsets of the region blobs (exa/Regions.cpp:182-240, 290-300) ----
+  rc = abrAttachScalars(r->abr, r->d_bricks, r->d_scalars, r->numCells, numFields, r->d_dualBegin, (const uint8_t *)d_owned.p, s);
   if (rc) { exa_renderer_destroy(r); return rc; }
+  CKC(cudaEventRecord(ev[5].e, s));
+  CKC(cudaEventSynchronize(ev[5].e));
+  {
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[0].e, ev[1].e); r->buildMs[0] = ms;      // ABR geometry (kd build, regions, leaf lists)
+    cudaEventElapsedTime(&ms, ev[2].e, ev[3].e); r->buildMs[1] = ms;      // scalar gather incl. H2D of ids and fields
+    cudaEventElapsedTime(&ms, ev[3].e, ev[4].e); r->buildMs[2] = ms;      // dual-cell records
+    cudaEventElapsedTime(&ms, ev[4].e, ev[5].e); r->buildMs[3] = ms;      // value ranges
+  }
   r->launches += r->abr.launches;
-  if (r->abr.depth + 2 > 160) { setError("ABR kd-tree deeper than the traversal stack limit"); exa_renderer_destroy(r); return EXA_ERR_LIMIT; }
   {
     // point-location grid: ~32+ cells per region, 16^3 .. 128^3 (8 B per cell)
     int G = 16; while (G < 128 && (double)G * G * G < 32.0 * r->abr.numRegions) G *= 2;
@@ -278,8 +433,6 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
       r->locG = G; r->launches++;
     }
   }
-  r->h_kd.resize(r->abr.numKdNodes);
-  CKC(cudaMemcpy(r->h_kd.data(), r->abr.kd, sizeof(KdNode) * r->abr.numKdNodes, cudaMemcpyDeviceToHost));
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);
   CKC(cudaMalloc(&r->d_volActive, 2 * (size_t)nn + nr)); r->d_isoActive = r->d_volActive + r->abr.numKdNodes; r->d_regionActive = r->d_volActive + 2 * (size_t)r->abr.numKdNodes; CKC(cudaMalloc(&r->d_inPart, nn));
   {
@@ -309,6 +462,29 @@ int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, 
   return EXA_OK;
 }
 
+int exa_renderer_create(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
+                        int numFields, int cudaDevice, exa_renderer_t **out)
+{ return createImpl(bricks, fields, fieldCounts, numFields, cudaDevice, 0, 1, out); }
+
+int exa_renderer_create_partitioned(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
+                                    int numFields, int cudaDevice, int rank, int numRanks, exa_renderer_t **out)
+{ return createImpl(bricks, fields, fieldCounts, numFields, cudaDevice, rank, numRanks, out); }
+
+int exa_renderer_get_build_times(const exa_renderer_t *r, double ms[4])
+{
+  if (!r || !ms) { setError("null argument"); return EXA_ERR_INVALID; }
+  for (int i = 0; i < 4; i++) ms[i] = r->buildMs[i];
+  return EXA_OK;
+}
+
+int exa_renderer_get_residency(const exa_renderer_t *r, int *residentBricks, uint64_t *residentCells)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (residentBricks) *residentBricks = r->residentBricks;
+  if (residentCells) *residentCells = r->numCells;
+  return EXA_OK;
+}
+
 void exa_renderer_destroy(exa_renderer_t *r)
 {
   if (!r) return;
@@ -323,7 +499,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
-  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_longQueue); cudaFree(r->d_longCount);
+  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]);
   delete r;
 }
 
@@ -428,12 +604,6 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   if (fbPointer) r->d_rgba8 = (uint32_t *)fbPointer;
   else { CKR(cudaMalloc(&r->d_rgba8, n * 4)); CKR(cudaMemset(r->d_rgba8, 0, n * 4)); r->ownRgba8 = true; }
   r->width = width; r->height = height;
-  cudaFree(r->d_longQueue); r->d_longQueue = nullptr;
-  if (const char *e = getenv("EXA_SAMPLE_BUDGET")) r->sampleBudget = atoi(e);         // 0: single pass
-  if (r->sampleBudget > 0) {
-    CKR(cudaMalloc(&r->d_longQueue, sizeof(LongRay) * n));
-    if (!r->d_longCount) CKR(cudaMalloc(&r->d_longCount, 2 * sizeof(int)));
-  }
   for (int i = 0; i < 2; i++) { cudaFree(r->d_tileOrder[i]); r->d_tileOrder[i] = nullptr; }
   r->tileOrderCap = ((width + 15) / 16) * ((height + 7) / 8); r->tileOrderValid = false;
   if (!getenv("EXA_NO_TILE_ORDER"))
@@ -449,6 +619,27 @@ int exa_renderer_set_color_buffer(exa_renderer_t *r, void *fbPointer)
     CKR(cudaSetDevice(r->device));
     CKR(cudaMalloc(&r->d_rgba8, (size_t)r->width * r->height * 4)); r->ownRgba8 = true;
   }
+  return EXA_OK;
+}
+
+int exa_strip_rows(int k, int numStrips, int height, int *y0, int *y1)
+{
+  if (numStrips < 1 || k < 0 || k >= numStrips || height < 1 || !y0 || !y1) { setError("exa_strip_rows: bad argument"); return EXA_ERR_INVALID; }
+  const int tileRows = (height + 7) / 8;
+  *y0 = std::min(height, 8 * ((tileRows * k) / numStrips)); *y1 = std::min(height, 8 * ((tileRows * (k + 1)) / numStrips));
+  return EXA_OK;
+}
+
+int exa_renderer_set_color_strips(exa_renderer_t *r, void *const *stripPtrs, int numStrips)
+{
+  if (!r || !r->d_accum) { setError("set_color_strips: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
+  if (numStrips < 0 || numStrips > EXA_MAX_PARTS || (numStrips && !stripPtrs)) { setError("set_color_strips: 0..16 strips"); return EXA_ERR_INVALID; }
+  for (int k = 0; k < numStrips; k++) {
+    int y0, y1; exa_strip_rows(k, numStrips, r->height, &y0, &y1);
+    if (!stripPtrs[k] && y1 > y0) { setError("set_color_strips: null strip"); return EXA_ERR_INVALID; }
+    r->strips[k] = (uint32_t *)stripPtrs[k];
+  }
+  r->numStrips = numStrips;
   return EXA_OK;
 }
 

@@ -72,14 +72,15 @@ static int buildConeGrid(exa_renderer *r, const RenderParams &P)
   return EXA_OK;
 }
 
-static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool sync)
+static int doRender(exa_renderer *r, float4 *partialOut, float4 *partialSurf, ExaStats *stats, bool sync)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
   if (!r->d_accum || r->width <= 0) { setError("render: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
   CKR(cudaSetDevice(r->device));
   RenderParams P; fillParams(r, P);
   int rc = refreshMasks(r, P); if (rc) return rc;
-  P.partialOut = partialOut;
+  P.partialOut = partialOut; P.partialSurf = P.anySurf ? partialSurf : nullptr;
+  if (partialOut && P.anySurf && !partialSurf) { setError("render_partial: a surface is enabled (iso / plane / mesh / cones): pass a surface buffer too"); return EXA_ERR_INVALID; }
   if (P.traces) {                                            // uniform grid over the visible cones
     if (r->traceBoundsDirty) { rc = buildConeGrid(r, P); if (rc) return rc; }
     if (r->coneGridValid) {
@@ -109,17 +110,12 @@ static int doRender(exa_renderer *r, float4 *partialOut, ExaStats *stats, bool s
 
 extern "C" {
 
-int exa_renderer_render(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, true); }
-int exa_renderer_render_async(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, false); }
+int exa_renderer_render(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, nullptr, true); }
+int exa_renderer_render_async(exa_renderer_t *r) { return doRender(r, nullptr, nullptr, nullptr, false); }
 int exa_renderer_render_stats(exa_renderer_t *r, ExaStats *stats)
 {
   if (!stats) { setError("null stats"); return EXA_ERR_INVALID; }
-  return doRender(r, nullptr, stats, true);
-}
-int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA)
-{
-  if (!d_partialRGBA) { setError("null partial buffer"); return EXA_ERR_INVALID; }
-  return doRender(r, (float4 *)d_partialRGBA, nullptr, false);
+  return doRender(r, nullptr, nullptr, stats, true);
 }
 int exa_renderer_get_tile_cost_histogram(exa_renderer_t *r, int counts[16])
 {
@@ -207,6 +203,8 @@ static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int ch
   CKR(cudaSetDevice(r->device));
   RenderParams RP; fillParams(r, RP);
   SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
+  // index prefetch pays when the query touches a good part of the grid / blobs anyway (one 32-B sector per point and hop)
+  P.blobUnits = r->abr.blobUnits; P.prefetchIndex = r->indexPrefetch && n * 32 >= (size_t)r->locG * r->locG * r->locG * 8 / 4;
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   const int k = launchSamplePoints(P, r->stream);
   if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
@@ -260,7 +258,9 @@ int exa_renderer_set_tracer_params(exa_renderer_t *r, int numTraces, int numTime
 {
   if (!r || numTraces < 0 || numTimesteps < 1) { setError("set_tracer_params: bad argument"); return EXA_ERR_INVALID; }
   if (channels) for (int i = 0; i < 3; i++) if (channels[i] < 0 || channels[i] >= r->numFields) { setError("tracer channel out of range"); return EXA_ERR_INVALID; }
-  r->numTraces = numTraces; r->numTimesteps = numTimesteps; r->steplen = steplen;
+  // the shape of d_traces changes only where the buffer is rebuilt (reset_tracer / set_tracer_seeds / set_traces), as in
+  // the reference, which pushes these values to the device inside resetTracer (OptixRenderer.cpp:450-474)
+  r->pendNumTraces = numTraces; r->pendNumTimesteps = numTimesteps; r->steplen = steplen;
   if (channels) memcpy(r->tracerChannels, channels, 12);
   if (seedLo) memcpy(r->seedLo, seedLo, 12);
   if (seedHi) memcpy(r->seedHi, seedHi, 12);
@@ -284,6 +284,7 @@ int exa_renderer_reset_tracer(exa_renderer_t *r)
   for (int i = 0; i < 3; i++) if (r->tracerChannels[i] >= r->numFields) { setError("tracer needs 3 scalar channels (vx,vy,vz)"); return EXA_ERR_INVALID; }
   // OptixRenderer::resetTracer (:450-460): seeds from std::default_random_engine(0), x,y,z in
   // that order, uniform in seedRegion * voxel-bounds EXTENT (not offset by bounds.lower)
+  r->numTraces = r->pendNumTraces; r->numTimesteps = r->pendNumTimesteps;
   std::vector<float> host((size_t)r->numTraces * r->numTimesteps * 3, 0.f);
   const float size[3] = {r->voxelHi[0] - r->voxelLo[0], r->voxelHi[1] - r->voxelLo[1], r->voxelHi[2] - r->voxelLo[2]};
   std::default_random_engine engine(0);
@@ -301,7 +302,7 @@ int exa_renderer_set_tracer_seeds(exa_renderer_t *r, const float *xyz, int numTr
 {
   if (!r || !xyz || numTraces < 0) { setError("set_tracer_seeds: bad argument"); return EXA_ERR_INVALID; }
   for (int i = 0; i < 3; i++) if (r->tracerChannels[i] >= r->numFields) { setError("tracer needs 3 scalar channels (vx,vy,vz)"); return EXA_ERR_INVALID; }
-  r->numTraces = numTraces;
+  r->numTraces = r->pendNumTraces = numTraces; r->numTimesteps = r->pendNumTimesteps;
   std::vector<float> host((size_t)numTraces * r->numTimesteps * 3, 0.f);
   for (int i = 0; i < numTraces; i++) memcpy(host.data() + (size_t)i * r->numTimesteps * 3, xyz + 3 * i, 12);
   return uploadSeeds(r, host);
@@ -348,7 +349,7 @@ int exa_renderer_trace_all(exa_renderer_t *r)
 int exa_renderer_set_traces(exa_renderer_t *r, const float *xyz, int numTraces, int numTimesteps, int currentTimestep)
 {
   if (!r || !xyz || numTraces < 0 || numTimesteps < 1 || currentTimestep < 0) { setError("set_traces: bad argument"); return EXA_ERR_INVALID; }
-  r->numTraces = numTraces; r->numTimesteps = numTimesteps;
+  r->numTraces = r->pendNumTraces = numTraces; r->numTimesteps = r->pendNumTimesteps = numTimesteps;
   std::vector<float> host(xyz, xyz + (size_t)numTraces * numTimesteps * 3);
   int rc = uploadSeeds(r, host);
   if (rc) return rc;
@@ -370,74 +371,109 @@ int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRan
 {
   if (!r || numRanks < 1 || rank < 0 || rank >= numRanks) { setError("set_partition: bad rank"); return EXA_ERR_INVALID; }
   if (mode != EXA_PARTITION_NONE && mode != EXA_PARTITION_SORT_LAST && mode != EXA_PARTITION_IMAGE_TILES) { setError("set_partition: bad mode"); return EXA_ERR_INVALID; }
+  if (numRanks > EXA_MAX_PARTS && mode == EXA_PARTITION_SORT_LAST) { setError("set_partition: at most 16 sort-last parts"); return EXA_ERR_LIMIT; }
+  if (r->dataPartitioned) {
+    // the scene of this renderer IS one part (exa_renderer_create_partitioned): nothing else is resident
+    if (mode == EXA_PARTITION_SORT_LAST && rank == r->rank && numRanks == r->numRanks) return EXA_OK;
+    setError("set_partition: this renderer holds only the bricks of its own sort-last part"); return EXA_ERR_INVALID;
+  }
   r->partMode = mode; r->rank = rank; r->numRanks = numRanks; r->masksDirty = true;
   r->tileOrderValid = false;                                 // the set of owned tiles may have changed
-  r->partPath.clear(); r->partRoot = 0;
+  r->partTree.clear(); r->partRoot = 0;
   if (mode != EXA_PARTITION_SORT_LAST) return EXA_OK;
-  int levels = 0; while ((1 << levels) < numRanks) levels++;
-  if ((1 << levels) != numRanks) { setError("sort-last needs a power-of-two rank count"); return EXA_ERR_INVALID; }
-  // Walk the top `levels` levels of the ABR kd-tree, most significant rank bit first:
-  // bit 0 -> left (below the plane), 1 -> right.  If a leaf is reached early, the rank whose
-  // remaining bits are all 0 keeps it and the others own nothing.
-  int node = 0;
-  for (int l = 0; l < levels; l++) {
-    const int bit = (rank >> (levels - 1 - l)) & 1;
-    const KdNode nd = r->h_kd[node];
-    r->partPath.push_back(node);
-    if ((nd.info >> 30) == 3) {
-      const int rest = rank & ((1 << (levels - l)) - 1);
-      if (rest != 0) node = -1;
-      for (int k = l + 1; k < levels; k++) r->partPath.push_back(-1);
-      break;
-    }
-    node = (int)(nd.info & 0x3fffffffu) + bit;
-  }
-  r->partRoot = node;
+  // replicated scene: the same partition tree as the data-partitioned mode, applied as a visibility mask
   CKR(cudaSetDevice(r->device));
-  const int k = launchPartitionMask(r->abr.kd, r->abr.levelOffset, node, r->d_inPart, r->stream);
+  std::vector<ExaBrickRegion> regions(r->abr.numRegions); std::vector<int32_t> leafList(r->abr.leafListLen);
+  std::vector<ExaBrick> hb(r->numBricks);
+  CKR(cudaStreamSynchronize(r->stream));
+  if (!regions.empty()) CKR(cudaMemcpy(regions.data(), r->abr.regions, sizeof(ExaBrickRegion) * regions.size(), cudaMemcpyDeviceToHost));
+  if (!leafList.empty()) CKR(cudaMemcpy(leafList.data(), r->abr.leafList, 4 * leafList.size(), cudaMemcpyDeviceToHost));
+  CKR(cudaMemcpy(hb.data(), r->d_bricks, sizeof(ExaBrick) * hb.size(), cudaMemcpyDeviceToHost));
+  std::vector<double> cost;
+  const char *bal = getenv("EXA_PARTITION_BALANCE");
+  nodeCosts(r->h_kd, regions, leafList, hb.data(), bal && !strcmp(bal, "cells"), cost);
+  buildPartitionTree(r, numRanks, cost);
+  r->partRoot = partitionRootOf(r, rank);
+  const int k = launchPartitionMask(r->abr.kd, r->abr.levelOffset, r->partRoot, r->d_inPart, r->stream);
   if (k < 0) { setError("partition mask kernels failed"); return EXA_ERR_CUDA; }
   r->launches += k;
   return EXA_OK;
 }
 
-int exa_renderer_swap_order(exa_renderer_t *r, int round, int *iAmFront)
+int exa_renderer_partition_order(exa_renderer_t *r, int *order, int *numParts)
 {
-  if (!r || !iAmFront || r->partMode != EXA_PARTITION_SORT_LAST) { setError("swap_order: renderer is not in sort-last mode"); return EXA_ERR_INVALID; }
-  int levels = 0; while ((1 << levels) < r->numRanks) levels++;
-  if (round < 0 || round >= levels) { setError("swap_order: bad round"); return EXA_ERR_INVALID; }
-  // partner = rank ^ (1<<round): both share the path down to tree level (levels-1-round)
-  const int lvl = levels - 1 - round;
-  const int node = lvl < (int)r->partPath.size() ? r->partPath[lvl] : -1;
-  const int myBit = (r->rank >> round) & 1;
-  if (node < 0 || (r->h_kd[node].info >> 30) == 3) { *iAmFront = myBit == 0; return EXA_OK; }   // one side is empty: order is irrelevant
-  const KdNode nd = r->h_kd[node];
-  const int axis = (int)(nd.info >> 30);
-  // camera position in voxel space decides which half-space is in front for every pixel
+  if (!r || !order || r->partMode != EXA_PARTITION_SORT_LAST || r->partTree.empty()) { setError("partition_order: renderer is not in sort-last mode"); return EXA_ERR_INVALID; }
+  // camera position in voxel space decides, at every plane of the partition tree, which side comes first
+  // for EVERY pixel (all primary rays start there); ranks beyond the number of parts own nothing and go last
   const float *m = (const float *)&r->fs.voxelSpaceTransform; const float *p = r->fs.camera.pos;
-  const float camV = p[0] * m[axis] + p[1] * m[3 + axis] + p[2] * m[6 + axis] + m[9 + axis];
-  const bool camBelow = camV < nd.split;
-  *iAmFront = (myBit == 0) == camBelow;
+  float cam[3];
+  for (int a = 0; a < 3; a++) cam[a] = p[0] * m[a] + p[1] * m[3 + a] + p[2] * m[6 + a] + m[9 + a];
+  int n = 0;
+  std::vector<int> st; st.push_back(0);
+  while (!st.empty()) {
+    const int i = st.back(); st.pop_back();
+    const exa_renderer::PartNode &pn = r->partTree[i];
+    if (pn.left < 0) { order[n++] = pn.rank; continue; }
+    const KdNode nd = r->h_kd[pn.kd];
+    const int axis = (int)(nd.info >> 30);
+    const bool camBelow = cam[axis] < nd.split;              // left child = below the plane
+    const int first = camBelow ? pn.left : pn.right, second = camBelow ? pn.right : pn.left;
+    st.push_back(second); st.push_back(first);
+  }
+  if (numParts) *numParts = n;
+  for (int k = n; k < r->numRanks; k++) order[k] = k;        // empty parts
   return EXA_OK;
 }
 
-int exa_composite_over(exa_renderer_t *r, float *d_mine, const float *d_other, size_t count, int mineIsFront)
+int exa_renderer_render_partial(exa_renderer_t *r, float *d_partialRGBA, float *d_partialSurf)
 {
-  if (!r || !d_mine || !d_other) { setError("composite_over: null argument"); return EXA_ERR_INVALID; }
+  if (!d_partialRGBA) { setError("null partial buffer"); return EXA_ERR_INVALID; }
+  return doRender(r, (float4 *)d_partialRGBA, (float4 *)d_partialSurf, nullptr, false);
+}
+
+int exa_renderer_composite_partials(exa_renderer_t *r, const float *const *d_partials, const float *const *d_surfs, int numParts,
+                                    size_t first, size_t count, uint32_t *d_rgba8Out)
+{
+  if (!r || !d_partials || !d_rgba8Out || !r->d_accum) { setError("composite_partials: bad argument"); return EXA_ERR_INVALID; }
+  if (numParts < 1 || numParts > EXA_MAX_PARTS) { setError("composite_partials: 1..16 parts"); return EXA_ERR_INVALID; }
+  if (first + count > (size_t)r->width * r->height) { setError("composite_partials: span outside the frame"); return EXA_ERR_INVALID; }
   CKR(cudaSetDevice(r->device));
-  const int k = launchCompositeOver((float4 *)d_mine, (const float4 *)d_other, count, mineIsFront, r->ert, r->stream);
+  RenderParams P; fillParams(r, P);
+  CompositeParams C; memset(&C, 0, sizeof(C));
+  for (int j = 0; j < numParts; j++) {
+    if (!d_partials[j] || (d_surfs && !d_surfs[j])) { setError("composite_partials: null partial"); return EXA_ERR_INVALID; }
+    C.part[j] = (const float4 *)d_partials[j]; C.surf[j] = d_surfs ? (const float4 *)d_surfs[j] : nullptr;
+  }
+  C.n = numParts; C.hasSurf = d_surfs != nullptr; C.first = first; C.count = count; C.out = d_rgba8Out;
+  const int k = launchCompositeFinish(P, C, r->stream);
   if (k < 0) { setError("composite kernel launch failed"); return EXA_ERR_CUDA; }
   r->launches += k; return EXA_OK;
 }
 
-int exa_renderer_finish_pixels(exa_renderer_t *r, const float *d_comp, size_t first, size_t count, uint32_t *d_rgba8Out)
+int exa_peer_barrier(void *const *flagPtrs, int rank, int numRanks, unsigned seq, void *cudaStream)
 {
-  if (!r || !d_comp || !d_rgba8Out || !r->d_accum) { setError("finish_pixels: bad argument"); return EXA_ERR_INVALID; }
-  if (first + count > (size_t)r->width * r->height) { setError("finish_pixels: range outside the frame"); return EXA_ERR_INVALID; }
-  CKR(cudaSetDevice(r->device));
-  RenderParams P; fillParams(r, P);
-  const int k = launchFinishPixels(P, (const float4 *)d_comp, first, count, d_rgba8Out, r->stream);
-  if (k < 0) { setError("finish kernel launch failed"); return EXA_ERR_CUDA; }
-  r->launches += k; return EXA_OK;
+  if (!flagPtrs || numRanks < 1 || numRanks > EXA_MAX_PARTS || rank < 0 || rank >= numRanks) { setError("peer_barrier: bad argument"); return EXA_ERR_INVALID; }
+  PeerBarrierParams B; memset(&B, 0, sizeof(B));
+  for (int k = 0; k < numRanks; k++) { if (!flagPtrs[k]) { setError("peer_barrier: null flag array"); return EXA_ERR_INVALID; } B.flags[k] = (unsigned *)flagPtrs[k]; }
+  B.rank = rank; B.n = numRanks; B.seq = seq; B.timeoutCycles = 4000000000ll;      // ~2 s at 1.9 GHz
+  B.err = (unsigned *)flagPtrs[rank] + EXA_MAX_PARTS;                              // word 16 of the local array: sticky time-out flag
+  if (launchPeerBarrier(B, (cudaStream_t)cudaStream) < 0) { setError(std::string("peer barrier launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  return EXA_OK;
 }
+
+int exa_copy_async(void *dst, const void *src, size_t bytes, void *cudaStream)
+{
+  if (!dst || !src) { setError("copy_async: null pointer"); return EXA_ERR_INVALID; }
+  CKR(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)cudaStream));
+  return EXA_OK;
+}
+
+int exa_host_register(void *ptr, size_t bytes)
+{
+  if (!ptr || !bytes) { setError("host_register: bad argument"); return EXA_ERR_INVALID; }
+  CKR(cudaHostRegister(ptr, bytes, cudaHostRegisterPortable));
+  return EXA_OK;
+}
+int exa_host_unregister(void *ptr) { if (ptr) CKR(cudaHostUnregister(ptr)); return EXA_OK; }
 
 } // extern "C"

@@ -90,10 +90,13 @@ struct AbrResult {
 };
 
 // abr.cu
-// d_dualBegin != null: brick headers inside the region blobs carry the brick's first dual-cell
-// record instead of its first flat cell
-int abrBuild(const ExaBrick *d_bricks, int numBricks, const float *d_scalars, uint64_t numCells,
-             int numFields, const uint32_t *d_dualBegin, void *stream, AbrResult &out);
+// Phase 1, geometry only: kd-tree, regions (domain, leaf list, finest level), blobs without scalar offsets.
+int abrBuild(const ExaBrick *d_bricks, int numBricks, void *stream, AbrResult &out);
+// Phase 2: attach the (resident) scalars: first-record field of the brick headers in the blobs
+// (d_dualBegin != null: the brick's first dual-cell record, else its first flat cell = d_bricks[].begin),
+// value ranges of the regions in d_regionOwned (null: all), blob headers.
+int abrAttachScalars(AbrResult &abr, const ExaBrick *d_bricks, const float *d_scalars, uint64_t numCells, int numFields,
+                     const uint32_t *d_dualBegin, const uint8_t *d_regionOwned, void *stream);
 void abrFree(AbrResult &r);
 
 } // namespace exa

@@ -305,6 +305,7 @@ int exa_scalar_field_expression(const float *const *fields, int numFields, size_
     const int need = k.op <= CONST ? 0 : k.op == SELECT ? 3 : k.op >= LOG ? 1 : 2;
     if (depth < need) { setError("expression: insufficient operands"); return EXA_ERR_INVALID; }
     depth += 1 - need;
+    if (depth > 62) { setError("expression: deeper than the 62-entry evaluation stack"); return EXA_ERR_LIMIT; }
   }
   if (depth != 1) { setError("Invalid expression"); return EXA_ERR_INVALID; }
   float lo = INFINITY, hi = -INFINITY;
@@ -312,7 +313,6 @@ int exa_scalar_field_expression(const float *const *fields, int numFields, size_
   for (long long i = 0; i < (long long)count; i++) {
     float st[64]; int sp = 0;
     for (auto &k : prog) {
-      if (sp >= 62) break;
       switch (k.op) {
         case FIELD: st[sp++] = fields[k.field][i]; break;
         case CONST: st[sp++] = k.value; break;

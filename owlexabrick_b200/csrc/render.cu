@@ -149,25 +149,6 @@ __device__ __forceinline__ void accumBricks(Acc &a, const U8 &hdr0, const uint4 
   }
 }
 
-// L1 prefetch of the dual-cell record the NEXT lattice sample of this segment will read from the
-// segment's first brick (its address depends only on the ray parameter): takes the L2/DRAM
-// latency of the one dependent load off the per-sample critical path.
-template <bool DUAL>
-__device__ __forceinline__ void prefetchRecord(const U8 &hdr, const void *chanV, float px, float py, float pz)
-{
-  if (!DUAL) return;
-  const float invCw = __uint_as_float(hdr.lo.w);
-  const int sx = (int)hdr.hi.x, sy = (int)hdr.hi.y, sz = (int)hdr.hi.z;
-  const int ix0 = max(-1, (int)floorf((px - __uint_as_float(hdr.lo.x)) * invCw - 0.5f));
-  const int iy0 = max(-1, (int)floorf((py - __uint_as_float(hdr.lo.y)) * invCw - 0.5f));
-  const int iz0 = max(-1, (int)floorf((pz - __uint_as_float(hdr.lo.z)) * invCw - 0.5f));
-  if (ix0 < sx && iy0 < sy && iz0 < sz) {
-    const int rx = sx + 1, ry = sy + 1;
-    const float4 *rec = reinterpret_cast<const float4 *>(chanV) + 2 * ((size_t)hdr.hi.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry)));
-    asm volatile("prefetch.global.L1 [%0];" :: "l"(rec));
-  }
-}
-
 // samplePoint / samplePointWithDerivative tail (exabrick.cu:800-806, 910-927)
 template <bool GRAD>
 __device__ __forceinline__ bool accFinish(const Acc &a, float &value, float3 &g)
@@ -235,7 +216,9 @@ struct LCG16 {
   __device__ float next() { state = 1664525u * state + 1013904223u; return ldexpf((float)state, -32); }
 };
 
-__device__ __forceinline__ float linear_to_srgb(float x) { return x <= 0.0031308f ? 12.92f * x : 1.055f * powf(x, 1.f / 2.4f) - 0.055f; }
+// powf as exp2(y * log2(x)): what the reference's --use_fast_math device build evaluates (exabrick.cu:53-60); the full-precision
+// powf was 10 % of the opaque frame's instructions
+__device__ __forceinline__ float linear_to_srgb(float x) { return x <= 0.0031308f ? 12.92f * x : 1.055f * __powf(x, 1.f / 2.4f) - 0.055f; }
 __device__ __forceinline__ int make_8bit(float f) { return min(255, max(0, (int)(f * 256.f))); }
 __device__ __forceinline__ uint32_t make_rgba8(float3 c)
 { return (uint32_t)(make_8bit(c.x) << 0) + (uint32_t)(make_8bit(c.y) << 8) + (uint32_t)(make_8bit(c.z) << 16) + (0xffu << 24); }
@@ -243,18 +226,20 @@ __device__ __forceinline__ uint32_t make_rgba8(float3 c)
 // -----------------------------------------------------------------------------------------
 // ordered kd traversal, one thread per ray; per-thread stack in shared memory
 // -----------------------------------------------------------------------------------------
+static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA; also the stride of the per-thread shared-memory columns
 struct Trav {
-  uint2 *stack;          // this thread's column: entry e at stack[e * blockDim.x]  {node, tf bits}
+  uint2 *stack;          // this thread's column: entry e at stack[e * FRAME_THREADS]  {node, tf bits}
   int sp;
   int cur; float tn, tf; // node being descended (-1: pop)
-  unsigned visits;       // kd nodes touched so far (instrumentation)
-  float3 o, d;
+  unsigned visits;       // kd nodes touched so far (instrumentation; only counted in the STATS instantiations)
   float3 invd;           // 1/d (IEEE): plane distances at inner nodes are (split - o) * invd; they only order and cull
 };
+// The ray (o, d) is passed to every call instead of living in Trav: for primary rays the voxel-space origin is the
+// same for the whole grid (a kernel parameter, no registers), and d is the lane's own copy.
 
-__device__ __forceinline__ void travInit(Trav &T, uint2 *stack, float3 o, float3 d, float tmin, float tmax, const DeviceScene &S)
+__device__ __forceinline__ void travInit(Trav &T, uint2 *stack, const float3 &o, const float3 &d, float tmin, float tmax, const DeviceScene &S)
 {
-  T.stack = stack; T.sp = 0; T.o = o; T.d = d; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.visits = 0;
+  T.stack = stack; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.visits = 0;
   T.invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
   float t0, t1;
   if (boxTest(o, d, tmin, tmax, S.boundsLo, S.boundsHi, t0, t1)) {
@@ -269,11 +254,13 @@ struct Segment { uint32_t blobOfs; int K; float t0, t1, fcw; U8 hdr0; };   // hd
 // going, 1 = `seg` holds the next region (front-to-back) with t0 = max(tmin, entry) < t1 =
 // min(tmax, exit) (exabrick.cu:213-238), 2 = traversal exhausted.  Inner nodes only order and
 // cull (plane distance by reciprocal, intervals widened by eps); leaves run the reference's
-// boxTest verbatim, which alone decides t0/t1.
-__device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
+// boxTest verbatim, which alone decides t0/t1.  The node and its activity byte are fetched
+// together, before the cull test needs either.
+template <bool COUNT>
+__device__ __forceinline__ int travStep(Trav &T, const float3 &o, const float3 &d, const DeviceScene &S, const uint8_t *__restrict__ active,
                                         float tmin, float tmax, Segment &seg)
 {
-  const int stride = blockDim.x;
+  constexpr int stride = FRAME_THREADS;
   if (T.cur < 0) {
     if (T.sp == 0) return 2;
     T.sp--;
@@ -281,9 +268,10 @@ __device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uin
     T.cur = (int)e.x; T.tf = __uint_as_float(e.y);
     T.tn = tmin;                                     // conservative: everything before tmin is done
   }
-  T.visits++;
-  if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || !active[T.cur]) { T.cur = -1; return 0; }
+  if (COUNT) T.visits++;
   const uint2 raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + T.cur);
+  const unsigned act = __ldg(active + T.cur);
+  if (T.tf < tmin - 1e-5f * fabsf(tmin) || T.tn > tmax || !act) { T.cur = -1; return 0; }
   const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
   if (axis == 3) {
     T.cur = -1;
@@ -292,7 +280,7 @@ __device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uin
     const uint4 h0 = hb.lo, h1 = hb.hi;
     const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
     const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
-    if (boxTest(T.o, T.d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
+    if (boxTest(o, d, tmin, tmax, lo, hi, seg.t0, seg.t1)) {
       seg.blobOfs = payload; seg.K = (int)raw.x; seg.fcw = __uint_as_float(h1.z);
       seg.hdr0 = ldg256(S.blobs + payload + BLOB_HDR_UNITS);
       return 1;
@@ -300,7 +288,7 @@ __device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uin
     return 0;
   }
   const float split = __uint_as_float(raw.x);
-  const float oa = comp(T.o, (int)axis), da = comp(T.d, (int)axis);
+  const float oa = comp(o, (int)axis), da = comp(d, (int)axis);
   const float tp = (split - oa) * comp(T.invd, (int)axis);
   const bool belowFirst = (oa < split) || (oa == split && da <= 0.f);
   const int first = (int)payload + (belowFirst ? 0 : 1), second = (int)payload + (belowFirst ? 1 : 0);
@@ -321,22 +309,24 @@ __device__ __forceinline__ int travStep(Trav &T, const DeviceScene &S, const uin
 }
 
 // next region of ONE ray; callable from divergent code (iso pass)
-__device__ __forceinline__ bool travNext(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
+template <bool COUNT>
+__device__ __forceinline__ bool travNext(Trav &T, const float3 &o, const float3 &d, const DeviceScene &S, const uint8_t *__restrict__ active,
                                          float tmin, float tmax, Segment &seg)
 {
-  for (;;) { const int r = travStep(T, S, active, tmin, tmax, seg); if (r) return r == 1; }
+  for (;;) { const int r = travStep<COUNT>(T, o, d, S, active, tmin, tmax, seg); if (r) return r == 1; }
 }
 
 // next region for every lane with `need` set; must be called by ALL 32 lanes of the warp.  The
 // lanes advance in lock step, one node visit per trip, until the last one has its answer: the
 // cost is the LONGEST lane's node count.  (With per-lane loops and early returns the lanes of a
 // warp ran their traversals one after the other: measured ~5000 cycles per call on C1/C2.)
-__device__ __forceinline__ bool travNextWarp(Trav &T, const DeviceScene &S, const uint8_t *__restrict__ active,
+template <bool COUNT>
+__device__ __forceinline__ bool travNextWarp(Trav &T, const float3 &o, const float3 &d, const DeviceScene &S, const uint8_t *__restrict__ active,
                                              float tmin, float tmax, Segment &seg, bool need)
 {
   bool found = false;
   while (__any_sync(FULL, need)) {
-    if (need) { const int r = travStep(T, S, active, tmin, tmax, seg); if (r) { need = false; found = r == 1; } }
+    if (need) { const int r = travStep<COUNT>(T, o, d, S, active, tmin, tmax, seg); if (r) { need = false; found = r == 1; } }
   }
   return found;
 }
@@ -497,7 +487,7 @@ __device__ __forceinline__ float3 xfmPoint(const float *m, float3 v)
 // -----------------------------------------------------------------------------------------
 enum { PRIM_NONE = -1, PRIM_ISOSURFACE = -23, PRIM_PLANE = -24, PRIM_STREAMLINE = -25 };
 struct SurfHit { int prim; float t; float3 Ng, base; float ambient; };
-static constexpr int SURF_THREADS = 128;                      // = FRAME_THREADS (stride of the per-thread smem columns)
+static constexpr int SURF_THREADS = FRAME_THREADS;            // stride of the per-thread smem columns
 
 template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
@@ -520,7 +510,7 @@ __device__ void traceIsoRay(const RenderParams &P, const float4 *xfTables, uint2
   Trav T; travInit(T, stack, vo, vd, already, rtmax, P.scene);
   for (;;) {
     Segment seg;
-    if (!travNext(T, P.scene, P.isoActive, already, rtmax, seg)) break;
+    if (!travNext<STATS>(T, vo, vd, P.scene, P.isoActive, already, rtmax, seg)) break;
     float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
     isoSegment<STATS, DUAL>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
     if (th >= 0.f) {
@@ -634,7 +624,7 @@ __device__ __noinline__ void traceMesh(const RenderParams &P, float3 o, float3 d
         const float tt = surf::rayTriangle(o, d, A, e1, e2);
         if (tt > tmin && tt < best) { best = tt; bestTri = (int)(a + k); }
       }
-    } else if (sp < 62) { stack[sp++] = a; stack[sp++] = a + 1; }
+    } else if (sp < 62) { stack[sp++] = a; stack[sp++] = a + 1; }   // median-split BVH over < 2^30 triangles: depth <= 30, at most depth + 1 entries pending
   }
   if (bestTri >= 0) {
     const float *t = P.meshTris + 9 * (size_t)bestTri;
@@ -672,30 +662,33 @@ __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float
 // final colour of a pixel (exabrick.cu:1701-1719): background blend (sic: premultiplied colour
 // times alpha again), progressive accumulation, sRGB, RGBA8 pack; or the raw premultiplied
 // partial in sort-last mode
-__device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, float4 pc, float3 bg)
+// Sort-last: the premultiplied partial of this rank's sub-volume, NOT yet scaled by the early-termination
+// rule (a terminated ray is marked by alpha + 2), and - when a surface pass ran - the shaded colour and
+// world-space distance of this rank's nearest surface hit (w = 1e30: none); k_compositeFinish puts them together.
+__device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, float4 pc, float3 bg, float surfT = 1e30f)
 {
-  if (P.partialOut) { P.partialOut[pixelIdx] = pc; return; }
+  if (P.partialOut) {
+    P.partialOut[pixelIdx] = pc;
+    if (P.partialSurf) P.partialSurf[pixelIdx] = make_float4(bg.x, bg.y, bg.z, surfT);
+    return;
+  }
   float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
   if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
   P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
   const float inv = (float)P.frameID + 1.f;
   color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
-  P.rgba8[pixelIdx] = make_rgba8(color);
+  if (P.numStrips > 0) {
+    // frame distributed as row strips over the GPUs: store into the strip that holds this pixel's tile row
+    const int tileRows = (P.height + 7) >> 3, tr = (pixelIdx / P.width) >> 3;
+    const int k = ((tr + 1) * P.numStrips - 1) / tileRows;
+    const int y0 = ((tileRows * k) / P.numStrips) << 3;
+    P.strip[k][pixelIdx - y0 * P.width] = make_rgba8(color);
+  } else P.rgba8[pixelIdx] = make_rgba8(color);
 }
 
-#ifndef EXA_LOOKAHEAD
-#define EXA_LOOKAHEAD 0     // kd traversal one node per trip ahead of the sampling: parity-green; C2 opaque 0.135 -> 0.152 ms, translucent 2.33 -> 2.30 ms: off
-#endif
-#ifndef EXA_ENTRY_FASTPATH
-#define EXA_ENTRY_FASTPATH 0   // first region of a ray by point location (location grid) instead of a kd descent: parity-green, but slower on C2 (opaque 0.134 -> 0.158 ms, translucent 2.31 -> 2.54 ms): off
-#endif
-#ifndef EXA_PREFETCH
-#define EXA_PREFETCH 0      // next-record L1 prefetch: measured slower on C2 (extra address math on an issue-bound kernel)
-#endif
 #ifndef EXA_FRAME_MINBLOCKS
 #define EXA_FRAME_MINBLOCKS 5
 #endif
-static constexpr int FRAME_THREADS = 128;   // 16x8 pixel tile per CTA
 static constexpr int TILE_W = 16, TILE_H = 8;
 
 // SURF: the surface pass is compiled in only when a surface is enabled (RenderParams::anySurf):
@@ -712,6 +705,9 @@ __host__ __device__ inline int numOwnedTiles(int numTiles, int rank, int numRank
   return full + ((rank + full) % numRanks < rem ? 1 : 0);
 }
 
+// Measured and dropped in round 1 (profiles/perf_quick_r01_*; the code is in the history before round 2): a
+// one-node traversal look-ahead, the first region by point location, next-record L1 prefetch, and a second
+// kernel that finishes long rays one warp per ray.  All parity-green, all slower on an issue-bound kernel.
 template <bool GRAD, bool STATS, bool DUAL, int SURF>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
@@ -729,7 +725,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #pragma unroll
     for (int i = 0; i < TILE_BUCKETS / 4; i++) tc[i] = cp[i];
   }
-  for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
+  for (int i = threadIdx.x; i < P.numChannels * 128; i += FRAME_THREADS) xfTables[i] = P.xf[i];
   if (threadIdx.x < P.numChannels) xfK[threadIdx.x] = 127.f / ((P.xfDomain[threadIdx.x][1] - P.xfDomain[threadIdx.x][0]) + 1e-20f);
   __syncthreads();
 
@@ -740,9 +736,6 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // frame writes the lists the next one reads.  Image-tile mode (multi-GPU, data replicated):
   // the grid holds only the owned tiles (ownedTile()).
   const long long t_start = clock64();
-#ifdef EXA_PHASE_TIMING
-  long long ph_setup = 0, ph_trav = 0, ph_sample = 0, ph_iters = 0, ph_t;
-#endif
   int tileId;
   if (P.tileOrderIn) {
     int q = (int)blockIdx.x, b = 0; bool found = false;
@@ -762,38 +755,44 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 #ifdef EXA_DEBUG
   if (P.dbg && (px + P.width * py) != P.dbg - 1) inside = false;
 #endif
-  // per-lane DVR state; the integration loop below is shared by all 32 lanes of the warp
+  // per-lane DVR state; the integration loop below is shared by all 32 lanes of the warp.  The voxel-space
+  // ray origin is the transformed camera position for EVERY ray of the frame: it comes from the kernel
+  // parameters (computed once on the host with the same separately rounded products and sums as xfmPoint),
+  // costs no registers and makes the plane-side tests of the traversal warp-uniform.
   const int pixelIdx = px + P.width * py;
-  bool live = false, parked = false;                         // lane still has volume to integrate / ray handed to k_renderLong
-  float3 o = f3(0, 0, 0), d = f3(0, 0, 1), bg = f3(0, 0, 0);
+  bool live = false;                                         // lane still has volume to integrate
+  const float3 o = f3(P.camVoxel[0], P.camVoxel[1], P.camVoxel[2]);
+  float3 d = f3(0, 0, 1), bg = f3(0, 0, 0);
   float4 pc = make_float4(0, 0, 0, 0);
   float offs = 0.f, already = 0.f, rayTmax = 0.f;
-  Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.o = o; T.d = d; T.visits = 0; T.invd = f3(0, 0, 0);
+  Trav T; T.stack = stackBase + threadIdx.x; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.visits = 0; T.invd = f3(0, 0, 0);
   bool haveSeg = false; Segment seg; seg.blobOfs = 0; seg.K = 0; seg.t0 = seg.t1 = 0.f; seg.fcw = 1.f;   // current region segment of this lane
   float dtS = 0.f, t_i = 0.f, t_last = 0.f;
+  float surfHitT = 1e30f;                                    // sort-last: distance of this rank's nearest surface hit
   if (inside) {
     uint2 *stack = stackBase + threadIdx.x;
-    float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
     LCG16 rnd((uint32_t)(P.frameID * P.width * P.height) + (uint32_t)px, (uint32_t)py);
     const float jx = rnd.next(), jy = rnd.next();
     const float sx = (float)px + jx, sy = (float)py + jy;
     // Camera::generateRay (programs/Camera.h:27-44)
-    o = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
     d = normalize3nc(f3(__fadd_rn(__fadd_rn(P.dir00[0], __fmul_rn(sx, P.dirDu[0])), __fmul_rn(sy, P.dirDv[0])),
-                               __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
-                               __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
+                        __fadd_rn(__fadd_rn(P.dir00[1], __fmul_rn(sx, P.dirDu[1])), __fmul_rn(sy, P.dirDv[1])),
+                        __fadd_rn(__fadd_rn(P.dir00[2], __fmul_rn(sx, P.dirDu[2])), __fmul_rn(sy, P.dirDv[2]))));
     float tmin = 1e-6f, tmax = 1e8f;
     // ---- surfaces (traceSurfaces :1476-1529) and their shading with ambient occlusion (:1604-1652)
     float surfT = tmax;
     if (SURF && P.anySurf) {
+      float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
+      const float3 ow = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
       SurfHit sh;
-      traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, true, sh, rs);
+      traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, ow, d, tmin, tmax, true, sh, rs);
       surfT = sh.t;
       if (sh.prim != PRIM_NONE) {
+        surfHitT = sh.t;
         const bool shade = sh.prim >= 0 || sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
         if (shade && len3(sh.Ng) > 0.f) {
           const int aoSamples = (SURF == 2 && P.aoEnabled) ? 2 : 0;
-          const float3 isect = rayAt(o, d, sh.t);
+          const float3 isect = rayAt(ow, d, sh.t);
           int hitCnt = 0;
           for (int i = 0; i < aoSamples; i++) {
             const float u1 = rnd.next(), u2 = rnd.next();
@@ -811,152 +810,53 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     // ---- DVR set-up (:1654-1674)
     offs = rnd.next();
     tmax = surfT;
-    if (P.clipEnabled) { float a, b; boxTest(o, d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
+    if (P.clipEnabled) { float a, b; boxTest(f3(P.camPos[0], P.camPos[1], P.camPos[2]), d, tmin, tmax, P.clipLo, P.clipHi, a, b); tmin = a; tmax = b; }
     const float tHitWorld = tmax;
-    o = xfmPoint(P.xfm, o); d = xfmVector(P.xfm, d);
+    d = xfmVector(P.xfm, d);
     const float dtScale = len3nc(d); d = normalize3nc(d);
     already = dtScale * tmin;
     rayTmax = tHitWorld * dtScale;
     travInit(T, stack, o, d, already, rayTmax, P.scene);
     live = true;
-#if EXA_ENTRY_FASTPATH && !EXA_LOOKAHEAD
-    // First region by POINT LOCATION instead of a descent from the kd root (1 grid load + 0-2 nodes):
-    // the region that contains the ray just behind its entry into the volume.  It is THE answer of
-    // the ordered traversal iff it is active and its boxTest entry equals the entry into the scene
-    // bounds (no region starts earlier: every region box lies inside the bounds and fp subtraction /
-    // division are monotonic); otherwise the lane takes the normal traversal.  Most rays of an
-    // opaque frame end inside this region and never touch the tree; the others continue with the
-    // ordered traversal from the root at tmin = t1 * 1.0000001 as after any region.
-    if (T.cur == 0 && P.regionActive) {
-      float t0s, t1s;
-      if (boxTest(o, d, already, rayTmax, P.scene.boundsLo, P.scene.boundsHi, t0s, t1s)) {
-        const float3 pe = rayAt(o, d, t0s + 1e-3f);
-        uint32_t bo; int K;
-        if (locate(P.scene, pe.x, pe.y, pe.z, bo, K)) {
-          const U8 hb = ldg256(P.scene.blobs + bo);
-          const uint4 h0 = hb.lo, h1 = hb.hi;
-          const int rid = (int)__ldg(&P.scene.blobs[bo + 2].x);
-          if (P.regionActive[rid]) {
-            const float lo[3] = {__uint_as_float(h0.x), __uint_as_float(h0.y), __uint_as_float(h0.z)};
-            const float hi[3] = {__uint_as_float(h0.w), __uint_as_float(h1.x), __uint_as_float(h1.y)};
-            float a0, a1;
-            if (boxTest(o, d, already, rayTmax, lo, hi, a0, a1) && a0 == t0s) {
-              seg.blobOfs = bo; seg.K = K; seg.fcw = __uint_as_float(h1.z); seg.t0 = a0; seg.t1 = a1;
-              seg.hdr0 = ldg256(P.scene.blobs + bo + BLOB_HDR_UNITS);
-              haveSeg = true; T.tn = a1;                     // everything before t1 is done when the traversal starts
-              dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0;
-              if (STATS) rs.segments++;
-            }
-          }
-        }
-      }
-    }
-#endif
   }
-#ifdef EXA_PHASE_TIMING
-  ph_setup = clock64() - t_start;
-#endif
   // ---- DVR region loop (:1675-1699) + integrateBrick's sample loop (:1141-1184), flattened into
   // one per-lane state machine: each trip, lanes without a current region segment advance the kd
   // traversal to their next one, then every live lane takes exactly ONE lattice sample.  With the
   // nested loops as written, a warp pays sum-over-segments of the longest lane; flat, it pays the
   // longest lane's total.  __all_sync at the head keeps the warp converged.  Arithmetic and
   // per-ray order of operations are unchanged.
-  {
-    int budget = P.sampleBudget;
-#if EXA_LOOKAHEAD
-    bool haveNext = false, exhausted = false; Segment nseg = seg; float nextTmin = already;
-#endif
-    for (;;) {
-      if (__all_sync(FULL, !live)) break;
-#ifdef EXA_PHASE_TIMING
-      ph_t = clock64(); ph_iters++;
-#endif
-#if EXA_LOOKAHEAD
-      // (1) one kd-traversal step towards the NEXT region segment.  Its query depends only on the
-      // current segment (tmin = t1 * 1.0000001, :1698), so it runs ahead while the current segment
-      // is being sampled: one node visit per trip, interleaved with the samples, instead of a
-      // whole descent that every lane of the warp waits for.
-      if (live && !haveNext && !exhausted) {
-        const int tr = travStep(T, P.scene, P.volActive, nextTmin, rayTmax, nseg);
-        if (tr == 1) haveNext = true; else if (tr == 2) exhausted = true;
-      }
-      // (2) a lane without a current segment takes the prefetched one (or waits for it)
-      const bool need = live && !haveSeg && (haveNext || exhausted);
-      const bool got = haveNext;
-      if (need && got) { seg = nseg; haveNext = false; already = nextTmin; nextTmin = seg.t1 * 1.0000001f; }
-#else
-      const bool need = live && !haveSeg;
-      const bool got = travNextWarp(T, P.scene, P.volActive, already, rayTmax, seg, need);
-#endif
-      if (need) {
-        if (!got) live = false;
-        else {
-          dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0; haveSeg = true;
-          if (STATS) rs.segments++;
+  for (;;) {
+    if (__all_sync(FULL, !live)) break;
+    const bool need = live && !haveSeg;
+    const bool got = travNextWarp<STATS>(T, o, d, P.scene, P.volActive, already, rayTmax, seg, need);
+    if (need) {
+      if (!got) live = false;
+      else {
+        dtS = P.dt * seg.fcw; t_i = firstLatticeT(seg.t0, dtS, offs); t_last = seg.t0; haveSeg = true;
+        if (STATS) rs.segments++;
 #ifdef EXA_DEBUG
-          if (P.dbg) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)P.scene.blobs[seg.blobOfs + 2].x, seg.K, seg.t0, seg.t1, dtS, t_i);
+        if (P.dbg) printf("G seg rid=%d K=%d t0=%.9g t1=%.9g dt=%.9g tFirst=%.9g\n", (int)P.scene.blobs[seg.blobOfs + 2].x, seg.K, seg.t0, seg.t1, dtS, t_i);
 #endif
-        }
-      }
-#ifdef EXA_PHASE_TIMING
-      __syncwarp(); ph_trav += clock64() - ph_t; ph_t = clock64();
-#endif
-      if (live && haveSeg) {
-        const float t_next = fminf(t_i, seg.t1);
-        const float t_sample = 0.5f * (t_next + t_last);
-        const float actual_dt = t_next - t_last;
-        t_last = t_next;
-        integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
-        if (pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); live = false; }   // :1180, :1694-1697
-        else if (t_next >= seg.t1) {                                                                               // :1698
-          haveSeg = false;
-#if !EXA_LOOKAHEAD
-          already = seg.t1 * 1.0000001f;
-#endif
-        }
-        else {
-          t_i += dtS;
-#if EXA_PREFETCH
-          const float tn2 = fminf(t_i, seg.t1);
-          const float3 pn = rayAt(o, d, 0.5f * (tn2 + t_last));
-          prefetchRecord<DUAL>(seg.hdr0, chanBase<DUAL>(P.scene, 0), pn.x, pn.y, pn.z);
-#endif
-        }
-        // A ray that is still alive after `sampleBudget` samples is a LONG ray: one lane stepping
-        // it sample by sample would be the critical path of the whole frame.  It is handed,
-        // with its state, to k_renderLong, where a full warp finishes it 32 samples at a time.
-        if (live && --budget <= 0 && P.longQueue) {
-          LongRay q;
-          q.ox = o.x; q.oy = o.y; q.oz = o.z; q.dx = d.x; q.dy = d.y; q.dz = d.z;
-          q.pcx = pc.x; q.pcy = pc.y; q.pcz = pc.z; q.pcw = pc.w;
-          q.offs = offs; q.rayTmax = rayTmax;
-#if EXA_LOOKAHEAD
-          q.already = haveSeg ? already : nextTmin;                // tmin of the query that finds the ray's current / next segment
-#else
-          q.already = already;
-#endif
-          q.t_i = t_i; q.t_last = t_last; q.haveSeg = haveSeg ? 1 : 0;
-          q.bgx = bg.x; q.bgy = bg.y; q.bgz = bg.z; q.pixelIdx = pixelIdx;
-          P.longQueue[atomicAdd(P.longCount, 1)] = q;              // capacity = width * height: cannot overflow
-          live = false; parked = true;
-        }
       }
     }
+    if (live && haveSeg) {
+      const float t_next = fminf(t_i, seg.t1);
+      const float t_sample = 0.5f * (t_next + t_last);
+      const float actual_dt = t_next - t_last;
+      t_last = t_next;
+      integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
+      if (pc.w >= P.ertThreshold) {                                                                               // :1180, :1694-1697
+        if (P.partialOut) pc.w += 2.f; else pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f);
+        live = false;
+      }
+      else if (t_next >= seg.t1) { haveSeg = false; already = seg.t1 * 1.0000001f; }                              // :1698
+      else t_i += dtS;
+    }
   }
-#ifdef EXA_PHASE_TIMING
-  ph_sample = clock64() - t_start - ph_setup - ph_trav;
-  const long long ph_before_write = clock64() - t_start;
-#endif
-  if (inside && !parked) writePixel(P, pixelIdx, pc, bg);
-#ifdef EXA_PHASE_TIMING
-  if (lane == 0 && (blockIdx.x % 997) == 0 && P.frameID == 77)
-    printf("CTA %d warp %d tile %d: setup %lld, loop trips %lld, traversal %lld, sampling+rest %lld, total-before-write %lld, total %lld cycles\n",
-           (int)blockIdx.x, warp, tileId, ph_setup, ph_iters, ph_trav, ph_sample, ph_before_write, (long long)(clock64() - t_start));
-#endif
+  if (inside) writePixel(P, pixelIdx, pc, bg, surfHitT);
   if (STATS && P.stats && inside) {                          // instrumentation: per-ray maxima
     atomicMax(&P.stats[4], (unsigned long long)T.visits); atomicAdd(&P.stats[6], (unsigned long long)T.visits);
-    atomicMax(&P.stats[5], (unsigned long long)(P.sampleBudget > 0 ? 0 : rs.samples));
+    atomicMax(&P.stats[5], (unsigned long long)rs.samples);
   }
   if (STATS) {
     unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
@@ -983,88 +883,6 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   }
 }
 
-// -----------------------------------------------------------------------------------------
-// k_renderLong: warp-cooperative continuation of the long rays parked by k_renderFrame.
-// One warp per ray (persistent warps pull rays from the queue).  The traversal state is
-// uniform across the warp (every lane walks the same kd stack); the 32 lanes take 32
-// consecutive lattice samples of the current region segment (t_i by repeated addition:
-// exactly the values of the sequential loop), each forms its sample's premultiplied
-// contribution, and an inclusive shuffle scan of the associative "over" operator yields
-// every prefix, hence the first sample at which alpha >= threshold (early termination,
-// exabrick.cu:1180) or the segment ends (:1184).  Same result as the sequential loop up to
-// fp32 re-association of the compositing sum.
-// -----------------------------------------------------------------------------------------
-template <bool GRAD, bool STATS, bool DUAL>
-__global__ void __launch_bounds__(FRAME_THREADS) k_renderLong(const __grid_constant__ RenderParams P)
-{
-  extern __shared__ uint4 smem[];
-  float4 *xfTables = reinterpret_cast<float4 *>(smem);
-  uint2 *stackBase = reinterpret_cast<uint2 *>(smem + P.numChannels * 128);
-  __shared__ float xfK[EXA_MAX_CHANNELS];
-  const int count = *P.longCount;                           // written by k_renderFrame, earlier on this stream
-  if (count == 0) return;
-  for (int i = threadIdx.x; i < P.numChannels * 128; i += blockDim.x) xfTables[i] = P.xf[i];
-  if (threadIdx.x < P.numChannels) xfK[threadIdx.x] = 127.f / ((P.xfDomain[threadIdx.x][1] - P.xfDomain[threadIdx.x][0]) + 1e-20f);
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  RayStats rs = {0, 0, 0, 0};
-  for (;;) {
-    int qi = 0;
-    if (lane == 0) qi = atomicAdd(P.longCount + 1, 1);
-    qi = __shfl_sync(FULL, qi, 0);
-    if (qi >= count) break;
-    const LongRay q = P.longQueue[qi];                       // same address in every lane: broadcast
-    const float3 ro = f3(q.ox, q.oy, q.oz), rd = f3(q.dx, q.dy, q.dz);
-    float4 rp = make_float4(q.pcx, q.pcy, q.pcz, q.pcw);
-    // restart the ordered traversal at the ray's current tmin: it returns the segment the ray
-    // was parked in (same boxTest, same tmin), so no kd stack has to travel with the ray
-    Trav RT; travInit(RT, stackBase + warp, ro, rd, q.already, q.rayTmax, P.scene);
-    Segment rseg; rseg.blobOfs = 0; rseg.K = 0; rseg.t0 = rseg.t1 = 0.f; rseg.fcw = 1.f;
-    float rdt = 0.f, rti = q.t_i, rtl = q.t_last, ralready = q.already;
-    bool rHave = false, alive = true;
-    if (q.haveSeg) {
-      if (travNextWarp(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg, true)) { rdt = P.dt * rseg.fcw; rHave = true; }
-      else alive = false;
-    }
-    while (alive) {
-      if (!rHave) {
-        if (!travNextWarp(RT, P.scene, P.volActive, ralready, q.rayTmax, rseg, true)) break;
-        rdt = P.dt * rseg.fcw; rti = firstLatticeT(rseg.t0, rdt, q.offs); rtl = rseg.t0; rHave = true;
-        if (STATS && lane == 0) rs.segments++;
-      }
-      float ti = rti; for (int j = 0; j < lane; j++) ti += rdt;   // t_i of lattice sample `lane`
-      const float tnext = fminf(ti, rseg.t1);
-      float tprev = __shfl_up_sync(FULL, tnext, 1); if (lane == 0) tprev = rtl;
-      const bool exists = lane == 0 || tprev < rseg.t1;
-      float4 c = make_float4(0, 0, 0, 0); RayStats bs = {0, 0, 0, 0};
-      if (exists) integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, rseg, ro, rd, 0.5f * (tnext + tprev), tnext - tprev, c, bs);
-#pragma unroll
-      for (int s2 = 1; s2 < 32; s2 <<= 1) {
-        const float4 f = make_float4(__shfl_up_sync(FULL, c.x, s2), __shfl_up_sync(FULL, c.y, s2), __shfl_up_sync(FULL, c.z, s2), __shfl_up_sync(FULL, c.w, s2));
-        if (lane >= s2) c = over(f, c);
-      }
-      const float4 tot = over(rp, c);
-      const bool ert = exists && tot.w >= P.ertThreshold, last = exists && tnext >= rseg.t1;
-      const unsigned stopMask = __ballot_sync(FULL, ert || last);
-      const int stop = stopMask ? __ffs(stopMask) - 1 : 31;
-      if (STATS && lane <= stop) { rs.samples += bs.samples; rs.visits += bs.visits; rs.corners += bs.corners; }
-      rp = make_float4(__shfl_sync(FULL, tot.x, stop), __shfl_sync(FULL, tot.y, stop), __shfl_sync(FULL, tot.z, stop), __shfl_sync(FULL, tot.w, stop));
-      if (stopMask) {
-        if (__shfl_sync(FULL, ert ? 1 : 0, stop)) { rp = make_float4(rp.x * rp.w, rp.y * rp.w, rp.z * rp.w, 1.f); break; }   // :1180, :1694-1697
-        rHave = false; ralready = rseg.t1 * 1.0000001f;                                                          // :1698
-      } else { rti = __shfl_sync(FULL, ti + rdt, 31); rtl = __shfl_sync(FULL, tnext, 31); }
-    }
-    if (lane == 0) writePixel(P, q.pixelIdx, rp, f3(q.bgx, q.bgy, q.bgz));
-  }
-  if (STATS) {
-    unsigned long long a = rs.samples, b = rs.visits, c = rs.corners, e = rs.segments;
-    for (int o2 = 16; o2 > 0; o2 >>= 1) {
-      a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); e += __shfl_xor_sync(FULL, e, o2);
-    }
-    if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], e); }
-  }
-}
-
 int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 {
   const int tilesX = (P.width + TILE_W - 1) / TILE_W, tilesY = (P.height + TILE_H - 1) / TILE_H;
@@ -1075,30 +893,23 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   if (numMine <= 0) return 0;
   const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
-  static int numSMs = 0;
-  if (!numSMs) { int dev = 0; cudaGetDevice(&dev); cudaDeviceGetAttribute(&numSMs, cudaDevAttrMultiProcessorCount, dev); if (numSMs <= 0) numSMs = 148; }
-  const bool twoPass = P.longQueue != nullptr;
-  if (twoPass) cudaMemsetAsync(P.longCount, 0, 2 * sizeof(int), s);
-  const size_t smemLong = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS;
-  const dim3 gridLong(numSMs * 8);
-  // cudaFuncSetAttribute is a slow driver call: raise each instantiation's dynamic shared memory
-  // limit only when it has to grow
+  // the shared-memory attribute is per device (a process may hold renderers on several devices); cudaFuncSetAttribute
+  // is a slow driver call: raise each instantiation's dynamic shared memory limit only when it has to grow
+  int dev = 0; cudaGetDevice(&dev); dev &= 63;
 #define LAUNCH(G, S_, D_)                                                                                   \
-  { static size_t capF = 0, capL = 0;                                                                       \
+  { static size_t capFd[64] = {}; size_t &capF = capFd[dev];                                                \
     if (smemBytes > capF) { cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
                             cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);            \
                             cudaFuncSetAttribute(k_renderFrame<G, S_, D_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capF = smemBytes; } \
     if (P.anySurf == 2) k_renderFrame<G, S_, D_, 2><<<grid, block, smemBytes, s>>>(P);                      \
     else if (P.anySurf) k_renderFrame<G, S_, D_, 1><<<grid, block, smemBytes, s>>>(P);                      \
-    else k_renderFrame<G, S_, D_, 0><<<grid, block, smemBytes, s>>>(P);                                     \
-    if (twoPass) { if (smemLong > capL) { cudaFuncSetAttribute(k_renderLong<G, S_, D_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemLong); capL = smemLong; } \
-                   k_renderLong<G, S_, D_><<<gridLong, block, smemLong, s>>>(P); } }
+    else k_renderFrame<G, S_, D_, 0><<<grid, block, smemBytes, s>>>(P); }
 #define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }
   if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
   else { if (stats) LAUNCH_D(false, true) else LAUNCH_D(false, false) }
 #undef LAUNCH_D
 #undef LAUNCH
-  return cudaGetLastError() == cudaSuccess ? (twoPass ? 2 : 1) : -1;
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
 // -----------------------------------------------------------------------------------------
@@ -1154,22 +965,77 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
 #ifndef EXA_POINTS_MINBLOCKS
 #define EXA_POINTS_MINBLOCKS 16
 #endif
+#ifndef EXA_POINTS_PER_THREAD
+#define EXA_POINTS_PER_THREAD 1     // > 1: each thread runs that many independent locate -> header -> record chains, stage by stage
+#endif
+
+// Index structures of a point query (location grid, kd nodes, region blobs: 26 MB on C3) are read at random, one 32-B
+// sector per point and hop, and after a cold start every one of those sectors is a DRAM access of its own.  For a large
+// query the grid's first threads instead ask for them line by line (prefetch.global.L2, 128 B each, sequential
+// addresses: full-rate DRAM bursts); the dependent loads of the points then mostly hit L2.
+__device__ __forceinline__ void prefetchIndexToL2(const DeviceScene &S, size_t blobUnits, size_t t, size_t nThreads)
+{
+  const size_t gridLines = S.locGrid ? ((size_t)S.locG * S.locG * S.locG * sizeof(uint2) + 127) / 128 : 0;
+  const size_t kdLines = ((size_t)S.numKdNodes * sizeof(KdNode) + 127) / 128;
+  const size_t blobLines = (blobUnits * 16 + 127) / 128;
+  for (size_t l = t; l < gridLines + kdLines + blobLines; l += nThreads) {
+    const char *p = l < gridLines ? reinterpret_cast<const char *>(S.locGrid) + 128 * l
+                  : l < gridLines + kdLines ? reinterpret_cast<const char *>(S.kd) + 128 * (l - gridLines)
+                  : reinterpret_cast<const char *>(S.blobs) + 128 * (l - gridLines - kdLines);
+    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
+  }
+}
+
 template <bool GRAD, bool STATS, bool DUAL>
 __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_samplePoints(const __grid_constant__ SampleParams P)
 {
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  unsigned visits = 0, corners = 0; bool counted = false;
-  if (i < P.n) {
-    const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
-    float v = 0.f; float3 g = f3(0, 0, 0);
-    const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners);
-    counted = visits > 0;
-    if (P.values) P.values[i] = ok ? v : 0.f;
-    if (P.valid) P.valid[i] = ok ? 1 : 0;
-    if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
+  constexpr int PPT = EXA_POINTS_PER_THREAD;
+  if (P.prefetchIndex) prefetchIndexToL2(P.scene, P.blobUnits, (size_t)blockIdx.x * blockDim.x + threadIdx.x, (size_t)gridDim.x * blockDim.x);
+  unsigned visits = 0, corners = 0, counted = 0;
+  if (PPT == 1) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < P.n) {
+      const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
+      float v = 0.f; float3 g = f3(0, 0, 0);
+      const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners);
+      counted = visits > 0;
+      if (P.values) P.values[i] = ok ? v : 0.f;
+      if (P.valid) P.valid[i] = ok ? 1 : 0;
+      if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
+    }
+  } else {
+    // PPT independent chains per thread, advanced stage by stage so that the loads of one stage are all in flight
+    // together: coordinates, location (grid cell + the rare kd steps), first brick header, bricks
+    const size_t base = (size_t)blockIdx.x * blockDim.x * PPT + threadIdx.x;
+    float px[PPT], py[PPT], pz[PPT]; bool in[PPT], located[PPT]; uint32_t bo[PPT]; int K[PPT]; U8 hdr[PPT];
+#pragma unroll
+    for (int j = 0; j < PPT; j++) {
+      const size_t i = base + (size_t)j * blockDim.x;
+      in[j] = i < P.n; px[j] = py[j] = pz[j] = 0.f;
+      if (in[j]) { px[j] = P.xyz[3 * i]; py[j] = P.xyz[3 * i + 1]; pz[j] = P.xyz[3 * i + 2]; }
+    }
+#pragma unroll
+    for (int j = 0; j < PPT; j++) { bo[j] = 0; K[j] = 0; located[j] = in[j] && locate(P.scene, px[j], py[j], pz[j], bo[j], K[j]); }
+#pragma unroll
+    for (int j = 0; j < PPT; j++) if (located[j]) hdr[j] = ldg256(P.scene.blobs + bo[j] + BLOB_HDR_UNITS);
+#pragma unroll
+    for (int j = 0; j < PPT; j++) {
+      const size_t i = base + (size_t)j * blockDim.x;
+      if (!in[j]) continue;
+      float v = 0.f; float3 g = f3(0, 0, 0); bool ok = false;
+      if (located[j]) {
+        Acc a; accZero(a); unsigned nc = 0;
+        accumBricks<GRAD, STATS, DUAL>(a, hdr[j], P.scene.blobs + bo[j] + BLOB_HDR_UNITS, K[j], chanBase<DUAL>(P.scene, P.channel), px[j], py[j], pz[j], nc);
+        if (STATS) { visits += K[j]; corners += nc; counted++; }
+        ok = accFinish<GRAD>(a, v, g);
+      }
+      if (P.values) P.values[i] = ok ? v : 0.f;
+      if (P.valid) P.valid[i] = ok ? 1 : 0;
+      if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
+    }
   }
   if (STATS && P.stats) {
-    unsigned long long a = counted ? 1 : 0, b = visits, c = corners;
+    unsigned long long a = counted, b = visits, c = corners;
     for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); }
     if ((threadIdx.x & 31) == 0) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], a); }
   }
@@ -1178,7 +1044,8 @@ __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_sa
 int launchSamplePoints(const SampleParams &P, cudaStream_t s)
 {
   if (P.n == 0) return 0;
-  const unsigned grid = (unsigned)((P.n + EXA_POINTS_THREADS - 1) / EXA_POINTS_THREADS);
+  const size_t perBlock = (size_t)EXA_POINTS_THREADS * EXA_POINTS_PER_THREAD;
+  const unsigned grid = (unsigned)((P.n + perBlock - 1) / perBlock);
   const bool stats = P.stats != nullptr;
 #define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); }
   if (P.grad) { if (stats) LAUNCH_P(true, true) else LAUNCH_P(true, false) }
@@ -1470,40 +1337,82 @@ int launchExpandDual(const ExaBrick *d_bricks, int numBricks, const uint32_t *d_
 }
 
 // -----------------------------------------------------------------------------------------
-// sort-last helpers
+// sort-last compositing, fused with the frame's tail: for every pixel of this rank's span, read the
+// partials of ALL ranks in visibility order (part[0] is the front-most; the pointers are peer
+// memory of the other GPUs, read over NVLink - or local copies after an all-to-all), composite
+// front to back, apply the early-termination rule (exabrick.cu:1180, 1694-1697) where the
+// single-GPU ray would have met it at the latest, pick the nearest surface hit of all ranks as
+// background, then background blend, accumulation, sRGB, RGBA8 pack (:1701-1719).
 // -----------------------------------------------------------------------------------------
-__global__ void k_over(float4 *mine, const float4 *other, size_t n, int mineIsFront, float thr)
+__global__ void k_compositeFinish(const __grid_constant__ RenderParams P, const __grid_constant__ CompositeParams C)
 {
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float4 a = mineIsFront ? mine[i] : other[i], b = mineIsFront ? other[i] : mine[i];
-  // a partial that already hit the termination threshold is opaque (alpha was forced to 1)
-  mine[i] = over(a, b);
-  (void)thr;
-}
-int launchCompositeOver(float4 *mine, const float4 *other, size_t count, int mineIsFront, float thr, cudaStream_t s)
-{
-  if (!count) return 0;
-  k_over<<<(unsigned)((count + 255) / 256), 256, 0, s>>>(mine, other, count, mineIsFront, thr);
-  return cudaGetLastError() == cudaSuccess ? 1 : -1;
-}
-
-__global__ void k_finish(const __grid_constant__ RenderParams P, const float4 *comp, size_t first, size_t n, uint32_t *out)
-{
-  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  const float4 pc = comp[i];
-  const size_t pixelIdx = first + i;
-  float3 color = f3(pc.w * pc.x, pc.w * pc.y, pc.w * pc.z);   // :1701 with bg = 0
+  if (i >= C.count) return;
+  const size_t pixelIdx = C.first + i;
+  float4 q[EXA_MAX_PARTS];
+#pragma unroll
+  for (int j = 0; j < EXA_MAX_PARTS; j++)                     // all loads in flight before the dependent chain
+    if (j < C.n) q[j] = __ldcs(C.part[j] + pixelIdx);
+  float4 pc = make_float4(0, 0, 0, 0);
+#pragma unroll
+  for (int j = 0; j < EXA_MAX_PARTS; j++) {
+    if (j >= C.n) break;
+    float4 a = q[j];
+    const bool term = a.w >= 2.f;
+    if (term) a.w -= 2.f;
+    const float k = 1.f - pc.w;
+    pc = make_float4(pc.x + k * a.x, pc.y + k * a.y, pc.z + k * a.z, pc.w + k * a.w);
+    if (term || pc.w >= P.ertThreshold) { pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f); break; }
+  }
+  float3 bg = f3(0, 0, 0);
+  if (C.hasSurf) {
+    float tBest = 1e30f;
+    for (int j = 0; j < C.n; j++) {
+      const float4 sv = __ldcs(C.surf[j] + pixelIdx);
+      if (sv.w < tBest) { tBest = sv.w; bg = f3(sv.x, sv.y, sv.z); }
+    }
+  }
+  float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
   if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
   P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
   const float inv = (float)P.frameID + 1.f;
-  out[i] = make_rgba8(f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv)));
+  C.out[pixelIdx] = make_rgba8(f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv)));
 }
-int launchFinishPixels(const RenderParams &P, const float4 *composited, size_t first, size_t count, uint32_t *rgba8Out, cudaStream_t s)
+
+int launchCompositeFinish(const RenderParams &P, const CompositeParams &C, cudaStream_t s)
 {
-  if (!count) return 0;
-  k_finish<<<(unsigned)((count + 255) / 256), 256, 0, s>>>(P, composited, first, count, rgba8Out);
+  if (!C.count) return 0;
+  k_compositeFinish<<<(unsigned)((C.count + 255) / 256), 256, 0, s>>>(P, C);
+  return cudaGetLastError() == cudaSuccess ? 1 : -1;
+}
+
+// -----------------------------------------------------------------------------------------
+// Barrier between the ranks of one NVSwitch box over peer memory, stream-ordered: lane k stores this rank's
+// sequence number into slot `rank` of rank k's flag array (a peer pointer), then spins until slot k of the
+// local array has reached it.  Everything the stream did before (pixels stored into other GPUs' frame
+// strips, a partial image) completed with its kernel, so a rank that sees the flag sees that data.  ~2 us
+// instead of a 4-byte NCCL all-reduce (64 us at 8 ranks); the spin is bounded, a missing rank sets *err.
+// -----------------------------------------------------------------------------------------
+__global__ void k_peerBarrier(PeerBarrierParams B)
+{
+  const int k = threadIdx.x;
+  if (k >= B.n) return;
+  __threadfence_system();
+  volatile unsigned *remote = B.flags[k] + B.rank;
+  *remote = B.seq;
+  __threadfence_system();
+  volatile unsigned *mine = B.flags[B.rank] + k;
+  const long long t0 = clock64();
+  while ((int)(*mine - B.seq) < 0) {
+    if (clock64() - t0 > B.timeoutCycles) { atomicExch(B.err, 1u); break; }
+    __nanosleep(100);
+  }
+  __threadfence_system();
+}
+
+int launchPeerBarrier(const PeerBarrierParams &B, cudaStream_t s)
+{
+  k_peerBarrier<<<1, 32, 0, s>>>(B);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -12,17 +12,13 @@ static const int TILE_BUCKETS = 16;
 // last CTA of a frame clears the buffer it read (the next frame's output), so no per-frame memset
 struct TileOrder { int count[TILE_BUCKETS]; int done; int pad[3]; uint32_t list[4]; };   // list: TILE_BUCKETS * cap entries
 
-// a long ray handed from k_renderFrame to k_renderLong (voxel-space ray + integration state)
-struct LongRay {
-  float ox, oy, oz, dx, dy, dz, pcx, pcy, pcz, pcw, offs, already, rayTmax, t_i, t_last;
-  int haveSeg; float bgx, bgy, bgz; int pixelIdx;
-};
-static_assert(sizeof(LongRay) == 80, "LongRay");
+static const int EXA_MAX_PARTS = 16;     // ranks of one node (sort-last parts / frame strips)
 
 struct RenderParams {
   DeviceScene scene;
   // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
   float camPos[3], dir00[3], dirDu[3], dirDv[3];
+  float camVoxel[3];                   // voxelSpaceTransform applied to camPos (host, same rounding as the device's xfmPoint): origin of every primary ray in voxel space
   float xfm[12];                       // voxelSpaceTransform: vx, vy, vz, p
   int width, height, frameID;
   float dt;
@@ -38,7 +34,11 @@ struct RenderParams {
   const uint8_t *isoActive;            // per kd node: subtree has a region whose range holds an iso value
   const uint8_t *regionActive;         // per REGION: active for volume sampling (same classification as volActive's leaves); entry fast path
   float4 *accum; uint32_t *rgba8;
-  float4 *partialOut;                  // != null: write premultiplied partial, skip bg/accum/pack
+  // image-tile mode across GPUs: the RGBA8 frame as numStrips row strips (whole 8-row tile rows), strip k in the
+  // memory of GPU k (peer-mapped); 0 = one buffer (rgba8).  Strip k starts at tile row (tileRows * k) / numStrips.
+  uint32_t *strip[EXA_MAX_PARTS]; int numStrips;
+  float4 *partialOut;                  // != null (sort-last): write the premultiplied partial, skip bg/accum/pack
+  float4 *partialSurf;                 // with partialOut: nearest surface hit of this rank {shaded rgb, distance} (null: no surface pass)
   int tileMode, rank, numRanks;        // image-tile partition
   const float *traces; int numTraces, numTimesteps, currentTimestep;   // streamline cones (null / 0: none visible)
   // uniform grid over the visible cones (rebuilt after a tracer step, where the reference rebuilds an
@@ -54,8 +54,6 @@ struct RenderParams {
   const float4 *meshNodes; const float *meshTris; int numMeshTris;
   int anySurf;                         // surface pass: 0 none, 1 iso-surfaces only, 2 + meshes / contour planes / visible streamlines / AO
   unsigned long long *stats;           // 4 counters (ExaStats) or null
-  LongRay *longQueue; int *longCount;  // long-ray queue (capacity width*height) and {count, head}; null: off
-  int sampleBudget;                    // samples a ray may take in k_renderFrame before it is handed over
   const TileOrder *tileOrderIn;        // previous frame's tile cost order (null: scan order)
   TileOrder *tileOrderOut; int tileOrderCap;   // where this frame records its own (null: off)
   int kdStack;                         // stack entries per warp
@@ -63,11 +61,25 @@ struct RenderParams {
   int dbg;                             // EXA_DEBUG builds only: print segments/samples
 };
 
+// sort-last composite of one pixel span (render.cu:k_compositeFinish)
+struct CompositeParams {
+  const float4 *part[EXA_MAX_PARTS];   // partial images of all ranks, front-most first (whole-frame buffers, indexed by pixel)
+  const float4 *surf[EXA_MAX_PARTS];   // their surface records (hasSurf)
+  int n, hasSurf;
+  size_t first, count;                 // pixel span [first, first + count) this rank composites
+  uint32_t *out;                       // RGBA8 frame buffer (whole frame; only the span is written)
+};
+
+// stream-ordered barrier over peer memory (render.cu:k_peerBarrier); flags[k] = rank k's array of n counters
+struct PeerBarrierParams { unsigned *flags[EXA_MAX_PARTS]; int rank, n; unsigned seq; long long timeoutCycles; unsigned *err; };
+int launchPeerBarrier(const PeerBarrierParams &B, cudaStream_t s);
+
 struct SampleParams {
   DeviceScene scene;
   const float *xyz; size_t n; int channel;
   float *values; uint8_t *valid; float *grad;
   unsigned long long *stats;
+  size_t blobUnits; int prefetchIndex;   // large query: stream the index structures into L2 first (render.cu:prefetchIndexToL2)
 };
 
 struct TraceParams {
@@ -95,7 +107,6 @@ int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellI
 int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s);
 int launchExpandDual(const ExaBrick *d_bricks, int numBricks, const uint32_t *d_dualBegin, uint64_t numRecords,
                      const float *d_scalars, float4 *d_dual, cudaStream_t s);
-int launchCompositeOver(float4 *mine, const float4 *other, size_t count, int mineIsFront, float ertThreshold, cudaStream_t s);
-int launchFinishPixels(const RenderParams &P, const float4 *composited, size_t first, size_t count, uint32_t *rgba8Out, cudaStream_t s);
+int launchCompositeFinish(const RenderParams &P, const CompositeParams &C, cudaStream_t s);
 
 } // namespace exa

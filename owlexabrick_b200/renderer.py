@@ -242,7 +242,9 @@ def default_camera(world_lo, world_hi, width, height, fovy=70.0):
 class Renderer:
     """exa::OptixRenderer, headless.  fields: list of float32 arrays indexed by cell ID."""
 
-    def __init__(self, bricks, fields, device=0, layout=None):
+    def __init__(self, bricks, fields, device=0, layout=None, part=None):
+        """part = (rank, num_ranks): sort-last with the data partitioned (exa_renderer_create_partitioned): only the
+        bricks of this rank's kd subtree are uploaded"""
         self.bricks = bricks
         if layout is not None:
             check(lib.exa_set_scalar_layout(int(layout)))
@@ -251,12 +253,27 @@ class Renderer:
         counts = (C.c_size_t * len(fields))(*[len(f) for f in fields])
         handle = bricks.h if isinstance(bricks, ExaBricks) else C.c_void_p(bricks)
         out = C.c_void_p()
-        check(lib.exa_renderer_create(handle, ptrs, counts, len(fields), device, C.byref(out)))
+        if part is not None:
+            check(lib.exa_renderer_create_partitioned(handle, ptrs, counts, len(fields), device, int(part[0]), int(part[1]), C.byref(out)))
+        else:
+            check(lib.exa_renderer_create(handle, ptrs, counts, len(fields), device, C.byref(out)))
         if layout is not None:
             lib.exa_set_scalar_layout(capi.LAYOUT_AUTO)
         self.h = out
         self.num_fields = len(fields)
         self.fb_size = (0, 0)
+        self._trace_shape = self._pending_shape = (1000, 100)      # OptixRenderer.h:155-165 defaults
+
+    def build_times(self):
+        """device ms of the construction stages: ABR geometry, scalar gather, dual-cell records, value ranges"""
+        ms = (C.c_double * 4)()
+        check(lib.exa_renderer_get_build_times(self.h, ms))
+        return {"abr_geometry_ms": ms[0], "gather_ms": ms[1], "dual_records_ms": ms[2], "value_ranges_ms": ms[3]}
+
+    def residency(self):
+        nb, nc = C.c_int(), C.c_uint64()
+        check(lib.exa_renderer_get_residency(self.h, C.byref(nb), C.byref(nc)))
+        return nb.value, int(nc.value)
 
     def __del__(self):
         self.close()
@@ -350,15 +367,16 @@ class Renderer:
     def setTracerParams(self, num_traces, num_timesteps, steplen, channels=(0, 1, 2), seed_lo=(.3, .3, .5), seed_hi=(.8, .8, .5)):
         ch = np.ascontiguousarray(channels, dtype=np.int32)
         check(lib.exa_renderer_set_tracer_params(self.h, num_traces, num_timesteps, float(steplen), _p(ch), _p(_f3(seed_lo)), _p(_f3(seed_hi))))
-        self._trace_shape = (num_traces, num_timesteps)
+        self._pending_shape = (num_traces, num_timesteps)             # takes effect where the trace buffer is rebuilt
 
     def resetTracer(self):
         check(lib.exa_renderer_reset_tracer(self.h))
+        self._trace_shape = self._pending_shape
 
     def setTracerSeeds(self, seeds):
         s = np.ascontiguousarray(seeds, dtype=np.float32).reshape(-1, 3)
         check(lib.exa_renderer_set_tracer_seeds(self.h, _p(s), len(s)))
-        self._trace_shape = (len(s), self._trace_shape[1])
+        self._trace_shape = self._pending_shape = (len(s), self._pending_shape[1])
 
     def advanceTracer(self):
         rebuilt = C.c_int()
@@ -372,7 +390,7 @@ class Renderer:
         """trace vertices computed elsewhere: float32[numTraces, numTimesteps, 3] + the time step reached"""
         t = np.ascontiguousarray(traces, dtype=np.float32)
         check(lib.exa_renderer_set_traces(self.h, _p(t), t.shape[0], t.shape[1], int(current_timestep)))
-        self._trace_shape = (t.shape[0], t.shape[1])
+        self._trace_shape = self._pending_shape = (t.shape[0], t.shape[1])
 
     def write_accum(self, accum):
         a = np.ascontiguousarray(accum, dtype=np.float32)
@@ -457,16 +475,18 @@ class Renderer:
     def set_partition(self, mode, rank, num_ranks):
         check(lib.exa_renderer_set_partition(self.h, mode, rank, num_ranks))
 
-    def render_partial(self, d_partial):
-        check(lib.exa_renderer_render_partial(self.h, C.c_void_p(d_partial)))
+    def render_partial(self, d_partial, d_surf=None):
+        check(lib.exa_renderer_render_partial(self.h, C.c_void_p(d_partial), C.c_void_p(d_surf) if d_surf else None))
 
-    def swap_order(self, rnd):
-        out = C.c_int()
-        check(lib.exa_renderer_swap_order(self.h, rnd, C.byref(out)))
-        return bool(out.value)
+    def partition_order(self):
+        """front-to-back order of the sort-last parts for the current camera"""
+        order, n = (C.c_int * 16)(), C.c_int()
+        check(lib.exa_renderer_partition_order(self.h, order, C.byref(n)))
+        return list(order)[:max(n.value, 0)], n.value
 
-    def composite_over(self, d_mine, d_other, count, mine_is_front):
-        check(lib.exa_composite_over(self.h, C.c_void_p(d_mine), C.c_void_p(d_other), count, int(mine_is_front)))
-
-    def finish_pixels(self, d_comp, first, count, d_rgba8):
-        check(lib.exa_renderer_finish_pixels(self.h, C.c_void_p(d_comp), first, count, C.c_void_p(d_rgba8)))
+    def composite_partials(self, d_partials, d_surfs, first, count, d_rgba8):
+        """d_partials / d_surfs: device pointers of all parts' buffers, front-most first"""
+        n = len(d_partials)
+        pa = (C.c_void_p * n)(*d_partials)
+        su = (C.c_void_p * n)(*d_surfs) if d_surfs else None
+        check(lib.exa_renderer_composite_partials(self.h, pa, su, n, first, count, C.c_void_p(d_rgba8)))

@@ -87,7 +87,6 @@ def test_abr_c1_hash_vs_reference(R, orc):
     assert hashlib.sha256(raw).hexdigest() == hashes["C1"]["abr_sha256"]
 
 
-@pytest.mark.skipif(os.environ.get("EXA_GPU_LARGE") != "1", reason="written after round 1's GPU minutes were spent: opt-in (EXA_GPU_LARGE=1) until first run on a B200")
 def test_abr_c5_quarter_scale_hash_vs_reference(R, orc):
     """C5 shape at 1/4 scale (26.6 M cells, 3 channels, 4 021 bricks): GPU ABR output (251 744 regions) ==
     reference buildFrom output (SHA-256; the oracle's equals it: tests/test_host.py)"""

@@ -1,7 +1,8 @@
-"""World-size-2 (and 4) gloo tests of the multi-GPU host logic on CPU: the binary-swap schedule of
-owlexabrick_b200/multigpu.py with numpy "over"/finish callbacks must reproduce the sequential
-front-to-back composite of all ranks' partial images; image-tile ownership must partition the
-frame.  (The CUDA composite/finish kernels are covered by the -m gpu tests.)"""
+"""World-size-2 / 3 / 4 gloo tests of the multi-GPU host logic on CPU: the direct-send exchange of
+owlexabrick_b200/multigpu.py (every rank receives all ranks' partials of ITS pixel span) followed by the
+ordered composite must reproduce the sequential front-to-back composite of all ranks' partial images,
+including the early-termination marker; pixel spans, frame strips and image-tile ownership must partition
+the frame.  (The CUDA composite kernel is checked against multigpu.composite_reference by the -m gpu tests.)"""
 import os
 import sys
 
@@ -23,77 +24,76 @@ def _partials(world, npix, seed=3):
         a = rng.uniform(0, 0.9, (npix, 1)).astype(np.float32)
         a[rng.uniform(size=(npix, 1)) < 0.3] = 0.0                  # empty pixels
         rgb = rng.uniform(0, 1, (npix, 3)).astype(np.float32) * a   # premultiplied
-        out.append(np.concatenate([rgb, a], axis=1))
+        term = (rng.uniform(size=(npix, 1)) < 0.1) & (a > 0.5)      # rays that met the termination threshold in this rank
+        out.append(np.concatenate([rgb, a + 2.0 * term], axis=1).astype(np.float32))
     return out
 
 
-def _over(front, back):
-    return front + (1.0 - front[:, 3:4]) * back
+def _sequential(parts, order):
+    """the single-GPU ray: accumulate rank after rank, stop (and scale by alpha, exabrick.cu:1694-1697) at a marked one"""
+    n = parts[0].shape[0]
+    out = np.zeros((n, 4), np.float32)
+    for i in range(n):
+        pc = np.zeros(4, np.float32)
+        for k in order:
+            a = parts[k][i].copy()
+            term = a[3] >= 2.0
+            if term:
+                a[3] -= 2.0
+            pc = pc + (np.float32(1.0) - pc[3]) * a
+            if term:
+                pc = np.array([pc[0] * pc[3], pc[1] * pc[3], pc[2] * pc[3], 1.0], np.float32)
+                break
+        out[i] = pc
+    return out
 
 
-def _front_order(world, front_bits):
-    """depth order of the ranks (front first) when at tree level l the child with bit b == front_bits[l] is in front"""
-    levels = world.bit_length() - 1
-
-    def key(rank):
-        # most significant rank bit = first kd level; round r pairs ranks differing in bit r
-        return [0 if ((rank >> (levels - 1 - l)) & 1) == front_bits[l] else 1 for l in range(levels)]
-    return sorted(range(world), key=key)
-
-
-def _worker(rank, world, port, npix, front_bits, ret):
+def _worker(rank, world, port, npix, order, ret):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    levels = world.bit_length() - 1
     mine = torch.from_numpy(_partials(world, npix)[rank].copy())
-
-    def composite(a, b, front):
-        res = _over(a.numpy(), b.numpy()) if front else _over(b.numpy(), a.numpy())
-        a.copy_(torch.from_numpy(res))
-
-    def i_am_front(rnd):
-        lvl = levels - 1 - rnd                                       # partner differs in bit `rnd` = tree level lvl
-        return ((rank >> rnd) & 1) == front_bits[lvl]
-
-    def finish(pixels, first):
-        return (pixels[:, 3] * 1000).to(torch.int32) + first * 0     # any per-pixel function; keep alpha*1000
-
-    strips, span, calls = multigpu.binary_swap(dist, torch, mine, rank, world, composite, i_am_front, finish)
-    lo, hi = span
-    ret[rank] = (mine[lo:hi].numpy().copy(), span, torch.cat(strips).numpy().copy(), calls)
+    got = multigpu.exchange_spans(dist, torch, mine, rank, world)
+    comp = multigpu.composite_reference(np, [g.numpy() for g in got], order)
+    ret[rank] = (comp, multigpu.span_of(rank, world, npix))
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,front_bits", [(2, [0]), (2, [1]), (4, [1, 0])])
-def test_binary_swap_matches_sequential_composite(world, front_bits):
-    npix = 1000
+@pytest.mark.parametrize("world,order", [(2, [0, 1]), (2, [1, 0]), (3, [2, 0, 1]), (4, [1, 0, 3, 2])])
+def test_direct_send_matches_sequential_composite(world, order):
+    npix = 1001                                                      # not a multiple of the rank count
     mgr = mp.Manager()
     ret = mgr.dict()
-    port = 29500 + (os.getpid() % 2000) + world
-    mp.spawn(_worker, args=(world, port, npix, front_bits, ret), nprocs=world, join=True)
-    parts = _partials(world, npix)
-    ref = np.zeros((npix, 4), np.float32)
-    for rk in _front_order(world, front_bits):                       # front to back
-        ref = _over(ref, parts[rk])
+    port = 29500 + (os.getpid() % 2000) + 7 * world + order[0]
+    mp.spawn(_worker, args=(world, port, npix, order, ret), nprocs=world, join=True)
+    ref = _sequential(_partials(world, npix), order)
     covered = np.zeros(npix, bool)
     for rank in range(world):
-        strip, (lo, hi), gathered, calls = ret[rank]
-        assert np.allclose(strip, ref[lo:hi], atol=1e-6)
-        assert calls == world.bit_length()                           # log2(N) composites + 1 finish
+        comp, (lo, hi) = ret[rank]
+        assert comp.shape[0] == hi - lo
+        assert np.allclose(comp, ref[lo:hi], atol=1e-6)
+        assert not covered[lo:hi].any()
         covered[lo:hi] = True
-        assert len(gathered) == npix
     assert covered.all()
-    # the gathered image is ordered by each rank's final span
-    spans = sorted((ret[r][1], r) for r in range(world))
-    assert [s for s, _ in spans][0][0] == 0 and [s for s, _ in spans][-1][1] == npix
 
 
-def test_swap_schedule_and_tiles():
-    for world in (1, 2, 4, 8):
-        spans = [multigpu.final_span(r, world, 3840 * 2160) for r in range(world)]
-        assert sorted(spans)[0][0] == 0 and sum(h - l for l, h in spans) == 3840 * 2160
+def test_composite_reference_applies_threshold_between_parts():
+    a = np.array([[0.5, 0.0, 0.0, 0.99]], np.float32)               # first part alone crosses 0.98 without a marker
+    b = np.array([[0.0, 0.5, 0.0, 0.5]], np.float32)
+    out = multigpu.composite_reference(np, [a, b], [0, 1], ert=0.98)
+    assert np.allclose(out, [[0.5 * 0.99, 0, 0, 1.0]])
+    out = multigpu.composite_reference(np, [a, b], [0, 1], ert=2.0)  # threshold off: plain over
+    assert np.allclose(out, a + (1 - 0.99) * b)
+
+
+def test_spans_strips_and_tiles_partition_the_frame():
+    for world in (1, 2, 3, 4, 8):
+        npix = 3840 * 2160
+        spans = [multigpu.span_of(r, world, npix) for r in range(world)]
+        assert spans[0][0] == 0 and spans[-1][1] == npix and all(spans[i][1] == spans[i + 1][0] for i in range(world - 1))
+        for height in (2160, 1024, 116, 5):
+            strips = [multigpu.strip_rows(r, world, height) for r in range(world)]
+            assert strips[0][0] == 0 and strips[-1][1] == height and all(strips[i][1] == strips[i + 1][0] for i in range(world - 1))
+            assert all(y0 % 8 == 0 for y0, _ in strips)
         tiles = [set(multigpu.owned_tiles(r, world, 1024, 1024)) for r in range(world)]
         assert sum(len(t) for t in tiles) == 64 * 128 and len(set.union(*tiles)) == 64 * 128
-    with pytest.raises(ValueError):
-        multigpu.swap_schedule(0, 3, 100)
