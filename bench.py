@@ -176,6 +176,9 @@ def frame_desc(R, domain, image, field_range, iso=False):
     fd.opacity_scale = OPACITY_SCALE
     fd.dt = DT
     fd.xf_domain = [(float(field_range[0]), float(field_range[1]))]
+    # the viewer's default transfer function: alpha ramp i/127 over colour map 0, "Paraview Cool Warm"
+    # (exa/viewer.cpp:526-568: xfColorMap[c] = 0, xfColor[j][i] = colormaps[j](i/127))
+    fd.xf = [scenes.xf_ramp(colors=R.ColorMapper.embedded(0).table())]
     if iso:                                  # C4: one implicit iso-surface at the XF-domain midpoint, channel 0, + DVR
         fd.iso = [(1, 0.5 * (float(field_range[0]) + float(field_range[1])), 0), (0, 0.0, 0)]
     return fd
@@ -759,7 +762,7 @@ def run_product(args):
                 "warmup": args.warmup, "ms_per_step": ms_step, "frames_per_s": 1e3 / ms_step, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": workload_name(name), "cells": int(ncells), "bricks": bricks.num_bricks, "regions": int(len(regions)),
-                           "image": [W, H], "dt": DT, "xf": "alpha ramp i/127, opacity scale %.2f" % OPACITY_SCALE,
+                           "image": [W, H], "dt": DT, "xf": "alpha ramp i/127 over colour map 0 (Paraview Cool Warm), opacity scale %.2f" % OPACITY_SCALE,
                            "parallelism": "1 GPU" if world == 1 else ("sort-last x%d: data partitioned along the ABR kd-tree, float4 partials composited through NVLink peer memory inside the composite kernel (direct send), %s barrier per frame" % (world, "NCCL" if pipe.bar.nccl else "peer-memory") if mode == "sortlast" else
                                            "image tiles x%d (data replicated): RGBA8 tiles stored into N peer-mapped row strips (strip k on GPU k) over NVLink, %s barrier per frame, triple-buffered" % (world, "NCCL" if pipe.bar.nccl else "peer-memory")),
                            "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],

@@ -134,6 +134,21 @@ struct ColorMapper {
   { for (std::size_t i = 0; i < num; i++) values_.push_back({num > 1 ? i / float(num - 1) : 0.f, colors[i]}); }
   ColorMapper(std::initializer_list<vec3f> colors) : ColorMapper(colors.begin(), colors.size()) {}
   ColorMapper(std::initializer_list<ControlPoint> colors) : values_(colors) {}
+  // ColorMapper(std::string): "0.0,(0.0,0.1,0.2)\n1.0,(1.0,0.9,0.8)" (exa/ColorMapper.cpp:92-131)
+  ColorMapper(std::string colorMapString)
+  {
+    float *cp = nullptr; int n = 0;
+    detail::check(exa_colormap_parse_string(colorMapString.c_str(), &cp, &n));
+    take(cp, n);
+  }
+  // ColorMapper(buf, size): first pixel row of a PNG (exa/ColorMapper.h:44-61); the viewer's embedded maps are in
+  // include/exa/embedded_colormaps.h under the reference's names: ColorMapper(paraview_cool_warm, sizeof(paraview_cool_warm))
+  ColorMapper(const uint8_t *buf, std::size_t buf_size)
+  {
+    float *cp = nullptr; int n = 0;
+    detail::check(exa_colormap_from_png(buf, buf_size, &cp, &n));
+    take(cp, n);
+  }
   // ColorMapper::operator() (exa/ColorMapper.h:64-80): piecewise-linear over sorted control points
   vec3f operator()(float t) const
   {
@@ -144,6 +159,12 @@ struct ColorMapper {
     return vec3f(rgb[0], rgb[1], rgb[2]);
   }
   std::vector<ControlPoint> values_;
+private:
+  void take(float *cp, int n)
+  {
+    for (int i = 0; i < n; i++) values_.push_back({cp[4 * i], vec3f(cp[4 * i + 1], cp[4 * i + 2], cp[4 * i + 3])});
+    exa_free(cp);
+  }
 };
 
 // ---------------------------------------------------------------------------------------

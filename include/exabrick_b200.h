@@ -183,6 +183,17 @@ int exa_scalar_field_magnitude(const float *x, const float *y, const float *z, s
                                float *out, float valueRange[2]);
 /* ColorMapper::operator()(t) over control points {t,r,g,b} sorted by t */
 int exa_colormap_eval(const float *controlPoints4, int numPoints, float t, float rgb[3]);
+/* ColorMapper(std::string) (exa/ColorMapper.cpp:92-131): lines "t,(r,g,b)" -> control points {t,r,g,b}, sorted by t when
+ * they are not; malformed lines are skipped as in the reference.  controlPoints4 is malloc'd (exa_free). */
+int exa_colormap_parse_string(const char *colorMapString, float **controlPoints4, int *numPoints);
+/* ColorMapper(const uint8_t *buf, size_t size) (exa/ColorMapper.h:44-61): the first pixel row of a PNG image (8-bit grey,
+ * RGB, palette, with or without alpha; non-interlaced) -> control points {i/(w-1), rgb/255}.  malloc'd (exa_free). */
+int exa_colormap_from_png(const uint8_t *pngBytes, size_t numBytes, float **controlPoints4, int *numPoints);
+/* the colour maps the viewer offers (exa/viewer.cpp:506-542): 0 "Paraview Cool Warm" (the default, :568) .. 14 "HSV",
+ * 15 "Custom" (grey ramp); control points malloc'd (exa_free), name static.  include/exa/embedded_colormaps.h holds the
+ * same maps as PNG arrays under the reference's symbol names for the PNG constructor. */
+int exa_colormap_embedded_count(void);
+int exa_colormap_embedded(int index, const char **name, float **controlPoints4, int *numPoints);
 
 typedef struct exa_config exa_config_t;
 /* Config::parseConfigFile + finalize (tokens remap_from remap_to scalar vector value_range

@@ -72,6 +72,10 @@ _SIG = {
     "exa_scalar_field_load": (i32, [C.c_char_p, i32, C.POINTER(vp), C.POINTER(sz), vp]),
     "exa_scalar_field_magnitude": (i32, [vp, vp, vp, sz, vp, vp]),
     "exa_colormap_eval": (i32, [vp, i32, f32, vp]),
+    "exa_colormap_parse_string": (i32, [C.c_char_p, C.POINTER(vp), C.POINTER(i32)]),
+    "exa_colormap_from_png": (i32, [vp, sz, C.POINTER(vp), C.POINTER(i32)]),
+    "exa_colormap_embedded_count": (i32, []),
+    "exa_colormap_embedded": (i32, [i32, C.POINTER(C.c_char_p), C.POINTER(vp), C.POINTER(i32)]),
     "exa_config_parse": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
     "exa_config_destroy": (None, [vp]),
     "exa_config_bricks": (vp, [vp]),

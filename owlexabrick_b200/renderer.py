@@ -115,10 +115,17 @@ def load_scalar_field(file_name, compat=True):
 
 
 class ColorMapper:
-    """exa::ColorMapper: piece-wise linear colour map over control points (t, r, g, b)."""
+    """exa::ColorMapper (exa/ColorMapper.h:29-83): piece-wise linear colour map over control points (t, r, g, b).
+    Constructors as in the reference: colours (equally spaced), control points, a "t,(r,g,b)" string, PNG bytes;
+    ColorMapper.embedded(i) / ColorMapper.names() are the maps of the viewer (exa/viewer.cpp:506-542)."""
 
-    def __init__(self, colors=None, control_points=None):
-        if control_points is not None:
+    def __init__(self, colors=None, control_points=None, string=None, png=None):
+        if string is not None:
+            cp = self._from_c(lambda p, n: lib.exa_colormap_parse_string(string.encode(), p, n))
+        elif png is not None:
+            buf = np.frombuffer(bytes(png), np.uint8)
+            cp = self._from_c(lambda p, n: lib.exa_colormap_from_png(_p(buf), len(buf), p, n))
+        elif control_points is not None:
             cp = np.asarray(control_points, np.float32).reshape(-1, 4)
             cp = cp[np.argsort(cp[:, 0], kind="stable")]
         else:
@@ -126,6 +133,32 @@ class ColorMapper:
             t = np.arange(len(colors), dtype=np.float32) / np.float32(max(len(colors) - 1, 1))
             cp = np.concatenate([t[:, None], colors], axis=1)
         self.values_ = np.ascontiguousarray(cp, dtype=np.float32)
+
+    @staticmethod
+    def _from_c(call):
+        ptr, n = C.c_void_p(), C.c_int()
+        check(call(C.byref(ptr), C.byref(n)))
+        try:
+            return np.frombuffer(C.string_at(ptr, 16 * n.value), np.float32).reshape(-1, 4).copy()
+        finally:
+            lib.exa_free(ptr)
+
+    @staticmethod
+    def names():
+        out = []
+        for i in range(lib.exa_colormap_embedded_count()):
+            name, ptr, n = C.c_char_p(), C.c_void_p(), C.c_int()
+            check(lib.exa_colormap_embedded(i, C.byref(name), C.byref(ptr), C.byref(n)))
+            lib.exa_free(ptr)
+            out.append(name.value.decode())
+        return out
+
+    @staticmethod
+    def embedded(index):
+        name = C.c_char_p()
+        cm = ColorMapper(control_points=ColorMapper._from_c(lambda p, n: lib.exa_colormap_embedded(int(index), C.byref(name), p, n)))
+        cm.name = name.value.decode()
+        return cm
 
     def __call__(self, t):
         out = np.zeros(3, np.float32)
@@ -135,6 +168,21 @@ class ColorMapper:
     def table(self, n=NUM_XF_VALUES):
         """the 128-entry colour table the viewer feeds to updateXF (viewer.cpp:552-566)"""
         return np.stack([self(i / float(n - 1)) for i in range(n)])
+
+
+def load_xf(file_name):
+    """.xf file of the viewer (`--xf`, exa/viewer.cpp:139-145 writes it): 128 float32 opacities"""
+    a = np.fromfile(file_name, np.float32)
+    if len(a) != NUM_XF_VALUES:
+        raise RuntimeError("mismatching xf size!?")
+    return a
+
+
+def save_xf(file_name, opacities):
+    a = np.ascontiguousarray(opacities, np.float32)
+    if a.shape != (NUM_XF_VALUES,):
+        raise RuntimeError("mismatching xf size!?")
+    a.tofile(file_name)
 
 
 class Config:

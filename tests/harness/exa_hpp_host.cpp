@@ -6,6 +6,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include "exa/exa.hpp"
+#include "exa/embedded_colormaps.h"
 
 int main(int ac, char **av)
 {
@@ -27,6 +28,13 @@ int main(int ac, char **av)
     exa::ColorMapper cm({exa::vec3f(0.f, 0.f, 0.f), exa::vec3f(1.f, 0.f, 0.f), exa::vec3f(1.f, 1.f, 1.f)});
     const exa::vec3f c = cm(0.25f);
     printf("colormap %.9g %.9g %.9g\n", c.x, c.y, c.z);
+    // the constructors the viewer uses (exa/viewer.cpp:526-541) and the string form (exa/ColorMapper.cpp:92-131)
+    exa::ColorMapper emb(paraview_cool_warm, sizeof(paraview_cool_warm));
+    const exa::vec3f e0 = emb(0.3f);
+    printf("colormap_png %zu %.9g %.9g %.9g\n", emb.values_.size(), e0.x, e0.y, e0.z);
+    exa::ColorMapper str(std::string("1.0,(1.0,0.9,0.8)\n0.0,(0.0,0.1,0.2)\nnot a point\n"));
+    const exa::vec3f s0 = str(0.5f);
+    printf("colormap_string %zu %.9g %.9g %.9g\n", str.values_.size(), s0.x, s0.y, s0.z);
     exa::ScalarField::SP e = exa::ScalarField::createFromExpression("twice", {cfg->scalarFields[0]}, {"%0", "2", "*"});
     printf("expr %s %.9g %.9g\n", e->name.c_str(), e->valueRange.lower, e->valueRange.upper);
     try {

@@ -6,6 +6,7 @@ import hashlib
 import json
 import os
 import re
+import sys
 
 import numpy as np
 import pytest
@@ -326,6 +327,147 @@ def test_builder_types_and_kd_file_match_reference(R, built_lib, orc, tmp_path):
             assert open(tmp_path / "r.kd", "rb").read() == kd and open(tmp_path / "r.bricks", "rb").read() == b.to_bytes()
 
 
+def test_colormapper_embedded_maps_equal_the_reference_decode(R):
+    """exa_colormap_embedded == what the reference's PNG constructor (stb_image) decodes from exa/embedded_colormaps.h,
+    control point for control point (tests/golden/colormaps_embedded.npz, written by make_colormaps.py from
+    oracle/_ref/ref_colormap --embedded; compared live too when the reference binaries are here)"""
+    import subprocess
+    sys_maps = np.load(os.path.join(GOLDEN, "colormaps_embedded.npz"))
+    names = R.ColorMapper.names()
+    assert len(names) == 16 and names[0] == "Paraview Cool Warm" and names[14] == "HSV" and names[15] == "Custom"
+    sys.path.insert(0, GOLDEN)
+    import make_colormaps
+    for i, (name, sym) in enumerate(make_colormaps.MAPS):
+        cm = R.ColorMapper.embedded(i)
+        assert cm.name == name
+        assert cm.values_.tobytes() == sys_maps[sym].tobytes()
+    custom = R.ColorMapper.embedded(15)
+    assert np.array_equal(custom.values_, np.array([[0, 0, 0, 0], [1, 1, 1, 1]], np.float32))
+    if os.path.exists(make_colormaps.REF):
+        import tempfile
+        with tempfile.TemporaryDirectory() as d:
+            subprocess.check_call([make_colormaps.REF, "--embedded", os.path.join(d, "e.bin")])
+            for (name, sym), cp in zip(make_colormaps.MAPS, make_colormaps.read_maps(os.path.join(d, "e.bin"))):
+                assert cp.tobytes() == sys_maps[sym].tobytes()
+
+
+def test_colormapper_png_constructor(R):
+    """the PNG constructor: our decoder on PNGs with stored, fixed-Huffman and dynamic-Huffman streams, every row filter,
+    grey / RGB / RGBA / palette; on the re-encoded embedded maps of include/exa/embedded_colormaps.h; and - where the
+    reference tree is present - on the reference's own PNG arrays, against its stb_image decode"""
+    import re
+    import struct
+    import zlib
+    sys.path.insert(0, GOLDEN)
+    import make_colormaps
+
+    def png(rows, ctype, level, filt=0, palette=None):
+        h, w = rows.shape[0], rows.shape[1]
+        ch = rows.shape[2] if rows.ndim == 3 else 1
+        raw = b""
+        prev = np.zeros(w * ch, np.int32)
+        for y in range(h):
+            cur = rows[y].reshape(-1).astype(np.int32)
+            a = np.concatenate([np.zeros(ch, np.int32), cur[:-ch]])
+            cc = np.concatenate([np.zeros(ch, np.int32), prev[:-ch]])
+            if filt == 0: enc = cur
+            elif filt == 1: enc = cur - a
+            elif filt == 2: enc = cur - prev
+            elif filt == 3: enc = cur - ((a + prev) >> 1)
+            else:
+                p = a + prev - cc
+                pa, pb, pc = np.abs(p - a), np.abs(p - prev), np.abs(p - cc)
+                pred = np.where((pa <= pb) & (pa <= pc), a, np.where(pb <= pc, prev, cc))
+                enc = cur - pred
+            raw += bytes([filt]) + (enc & 0xff).astype(np.uint8).tobytes()
+            prev = cur
+
+        def chunk(tag, data):
+            return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xffffffff)
+        if level == "fixed":
+            co = zlib.compressobj(9, zlib.DEFLATED, 15, 9, zlib.Z_FIXED)
+            z = co.compress(raw) + co.flush()
+        else:
+            z = zlib.compress(raw, level)
+        out = b"\x89PNG\r\n\x1a\n" + chunk(b"IHDR", struct.pack(">IIBBBBB", w, h, 8, ctype, 0, 0, 0))
+        if palette is not None:
+            out += chunk(b"PLTE", palette.astype(np.uint8).tobytes())
+        half = len(z) // 2                                        # two IDAT chunks: the stream spans chunk boundaries
+        return out + chunk(b"IDAT", z[:half]) + chunk(b"IDAT", z[half:]) + chunk(b"IEND", b"")
+
+    rng = np.random.RandomState(5)
+    smooth = (np.linspace(0, 255, 300)[None, :, None] * np.array([1.0, 0.5, 0.25])[None, None, :]).astype(np.uint8)
+    smooth = np.repeat(smooth, 3, axis=0)
+    noise = rng.randint(0, 256, (2, 257, 3)).astype(np.uint8)
+    for rows in (smooth, noise):
+        w = rows.shape[1]
+        want = np.concatenate([(np.arange(w, dtype=np.float32) / np.float32(w - 1))[:, None], rows[0] / np.float32(255.0)], axis=1).astype(np.float32)
+        for level in (0, 6, 9, "fixed"):
+            for filt in range(5):
+                cm = R.ColorMapper(png=png(rows, 2, level, filt))
+                assert cm.values_.tobytes() == want.tobytes(), (level, filt)
+        rgba = np.concatenate([rows, np.full(rows.shape[:2] + (1,), 200, np.uint8)], axis=2)
+        assert R.ColorMapper(png=png(rgba, 6, 6, 4)).values_.tobytes() == want.tobytes()
+    grey = rng.randint(0, 256, (1, 100)).astype(np.uint8)
+    g = R.ColorMapper(png=png(grey, 0, 6, 1)).values_
+    assert np.array_equal(g[:, 1], grey[0] / np.float32(255.0)) and np.array_equal(g[:, 1], g[:, 3])
+    pal = rng.randint(0, 256, (256, 3))
+    idx = rng.randint(0, 256, (1, 64)).astype(np.uint8)
+    pcm = R.ColorMapper(png=png(idx, 3, 6, 0, palette=pal)).values_
+    assert np.array_equal(pcm[:, 1:], (pal[idx[0]] / np.float32(255.0)).astype(np.float32))
+    with pytest.raises(Exception):
+        R.ColorMapper(png=b"not a png at all")
+    with pytest.raises(Exception):
+        R.ColorMapper(png=png(smooth, 2, 6)[:-40])                 # truncated
+    # the generated header (what a C++ caller includes): each array decodes to the embedded map
+    hdr = open(os.path.join(ROOT, "include", "exa", "embedded_colormaps.h")).read()
+
+    def arrays(text):
+        return {m.group(1): bytes(int(x, 16) for x in re.findall(r"0x[0-9a-fA-F]+", m.group(2)))
+                for m in re.finditer(r"uint8_t\s+(\w+)\[\]\s*=\s*\{([^}]*)\}", text)}
+    ours = arrays(hdr)
+    assert len(ours) == 15
+    for i, (name, sym) in enumerate(make_colormaps.MAPS):
+        assert R.ColorMapper(png=ours[sym]).values_.tobytes() == R.ColorMapper.embedded(i).values_.tobytes()
+    ref_hdr = "/root/reference/exa/embedded_colormaps.h"
+    if os.path.exists(ref_hdr):                                     # the reference's own (deflate-compressed) PNG bytes, read where they lie
+        theirs = arrays(open(ref_hdr).read())
+        for i, (name, sym) in enumerate(make_colormaps.MAPS):
+            assert theirs[sym] != ours[sym]                         # not a copy
+            assert R.ColorMapper(png=theirs[sym]).values_.tobytes() == R.ColorMapper.embedded(i).values_.tobytes()
+
+
+def test_colormapper_string_constructor_matches_reference(R, tmp_path):
+    """ColorMapper(std::string) (exa/ColorMapper.cpp:92-131) vs the reference's own constructor where it is built"""
+    import subprocess
+    sys.path.insert(0, GOLDEN)
+    import make_colormaps
+    cases = ["0.0,(0.0,0.1,0.2)\n1.0,(1.0,0.9,0.8)",
+             "1.0,(1.0,0.9,0.8)\n0.25,(0.5,0.5,0.5)\n\n0.0,(0.0,0.1,0.2)\n",
+             "  0.5,(0.1, 0.2 ,0.3)  \n\tgarbage line\n0.1,(1,2,3)\n0.7,1,2\n",
+             ""]
+    want = [np.array([[0, 0, .1, .2], [1, 1, .9, .8]], np.float32),
+            np.array([[0, 0, .1, .2], [.25, .5, .5, .5], [1, 1, .9, .8]], np.float32),
+            np.array([[.1, 1, 2, 3], [.5, .1, .2, .3]], np.float32), np.zeros((0, 4), np.float32)]
+    for sidx, (text, w) in enumerate(zip(cases, want)):
+        cm = R.ColorMapper(string=text)
+        assert np.array_equal(cm.values_, w), sidx
+        if os.path.exists(make_colormaps.REF):
+            open(tmp_path / "s.txt", "w").write(text)
+            subprocess.check_call([make_colormaps.REF, "--string", str(tmp_path / "s.txt"), str(tmp_path / "o.bin")], stdout=subprocess.DEVNULL)
+            ref = make_colormaps.read_maps(str(tmp_path / "o.bin"))[0]
+            assert ref.tobytes() == cm.values_.tobytes(), sidx
+
+
+def test_xf_file_roundtrip(R, tmp_path):
+    """.xf files (exa/viewer.cpp:139-145): 128 float32 opacities"""
+    a = (np.arange(128) / 127.0).astype(np.float32) ** 2
+    R.save_xf(str(tmp_path / "t.xf"), a)
+    assert os.path.getsize(tmp_path / "t.xf") == 512 and np.array_equal(R.load_xf(str(tmp_path / "t.xf")), a)
+    with pytest.raises(RuntimeError):
+        R.save_xf(str(tmp_path / "bad.xf"), a[:100])
+
+
 def test_cpp_class_wrapper_over_the_c_abi(R, built_lib, tmp_path):
     """include/exa/exa.hpp — the reference's C++ class names (Config, ExaBricks, ScalarField, ColorMapper,
     TriangleMesh, OptixRenderer) over the C ABI — compiles with g++ -Wall -Wextra as a reference-side caller would
@@ -357,6 +499,11 @@ def test_cpp_class_wrapper_over_the_c_abi(R, built_lib, tmp_path):
     v, i = cfg.triangles()
     assert out["surfaces"].split() == [str(len(v)), str(len(i))]
     assert np.array_equal(np.array(out["colormap"].split(), np.float32), np.array([0.5, 0, 0], np.float32))
+    emb = R.ColorMapper.embedded(0)
+    assert out["colormap_png"].split()[0] == str(len(emb.values_))
+    assert np.array_equal(np.array(out["colormap_png"].split()[1:], np.float32), emb(0.3))
+    st = R.ColorMapper(string="1.0,(1.0,0.9,0.8)\n0.0,(0.0,0.1,0.2)\nnot a point\n")
+    assert out["colormap_string"].split()[0] == "2" and np.array_equal(np.array(out["colormap_string"].split()[1:], np.float32), st(0.5))
     a = cfg.fields[0]["valueRange"]
     assert np.array_equal(np.array(out["expr"].split()[1:], np.float32), np.array([2 * a[0], 2 * a[1]], np.float32))
     if torch.cuda.is_available():
