@@ -81,7 +81,7 @@ def field_threaded(cells, domain, channel=0, chunk=1 << 20):
     return out
 
 
-def make_workload(name):
+def make_workload(name, with_field=True):
     from owlexabrick_b200 import synth
     domain, shape, image = WORKLOADS[name]
     t = time.time()
@@ -89,18 +89,43 @@ def make_workload(name):
         cells, _ = synth.exajet_shaped(shape[1])
     else:
         cells = synth.nested_boxes(domain, shape)
-    field = field_threaded(cells, domain, 0)
+    field = field_threaded(cells, domain, 0) if with_field else None
     log("workload %s: %d cells generated in %.1fs" % (name, len(cells), time.time() - t))
     return cells, field, domain, image
 
 
-def load_or_build_scene(name, R, cache_dir=None):
-    """-> (ExaBricks, field).  Cells -> bricks with the library's host builder (exa_bricks_build,
-    bit-exact with the reference's exaBuilder: tests/test_host.py, tests/test_oracle.py); the
-    result is cached in /dev/shm so that the two bench arms and the ranks of one box build once."""
+BUILDER_INFO = {}
+
+
+def load_or_build_scene(name, R, cache_dir=None, gpu_builder=False, time_builder=False):
+    """-> (ExaBricks, field).  Cells -> bricks with the library's builder: the GPU builder (exa_bricks_build_gpu) on the
+    product arm, the OpenMP host builder (exa_bricks_build) on the CPU arm; both bit-exact with the reference's exaBuilder
+    (tests/test_host.py, tests/test_gpu_builder.py).  The result is cached in /dev/shm so that the two bench arms and the
+    ranks of one box build once; time_builder: when the cache exists already, the cells are generated again and the GPU
+    build is run and timed anyway (and compared with the cached bricks)."""
     cache_dir = cache_dir or os.environ.get("EXA_SCENE_CACHE", "/dev/shm")
     base = os.path.join(cache_dir, "exa_scene_%s_v%d" % (name, SCENE_CACHE_VERSION))
+
+    def gpu_build(cells):
+        t = time.time()
+        b = R.ExaBricks.build_gpu(cells, device=int(os.environ.get("LOCAL_RANK", "0")))
+        BUILDER_INFO.update({"exa_builder_gpu": {**{k: (round(v, 3) if isinstance(v, float) else v) for k, v in b.timings.items()},
+                                                  "wall_s": round(time.time() - t, 3), "cells": int(len(cells)), "bricks": b.num_bricks,
+                                                  "cells_per_s": round(len(cells) / max(b.timings["total_s"], 1e-9))}})
+        log("exa_bricks_build_gpu: %d cells -> %d bricks, %s" % (len(cells), b.num_bricks, b.timings))
+        return b
     if os.path.exists(base + ".ok"):
+        if gpu_builder and time_builder:
+            try:
+                cells, _, _, _ = make_workload(name, with_field=False)
+                b = gpu_build(cells)
+                del cells
+                cached = R.ExaBricks.load(base + ".bricks")
+                BUILDER_INFO["exa_builder_gpu"]["identical_to_cached_bricks"] = bool(b.headers.tobytes() == cached.headers.tobytes() and np.array_equal(b.cell_ids, cached.cell_ids))
+                del b, cached
+            except Exception as e:
+                BUILDER_INFO["exa_builder_gpu"] = {"error": repr(e)[:300]}
+                log("GPU builder timing failed: %r" % e)
         t = time.time()
         bricks = R.ExaBricks.load(base + ".bricks")
         field = np.fromfile(base + ".scalars", np.float32)
@@ -108,8 +133,11 @@ def load_or_build_scene(name, R, cache_dir=None):
         return bricks, field
     cells, field, _, _ = make_workload(name)
     t = time.time()
-    bricks = R.ExaBricks.build(cells)
-    log("exa_bricks_build: %d cells -> %d bricks in %.1fs" % (len(cells), bricks.num_bricks, time.time() - t))
+    if gpu_builder:
+        bricks = gpu_build(cells)
+    else:
+        bricks = R.ExaBricks.build(cells)
+        log("exa_bricks_build: %d cells -> %d bricks in %.1fs" % (len(cells), bricks.num_bricks, time.time() - t))
     del cells
     try:
         bricks.save(base + ".bricks")
@@ -399,7 +427,7 @@ def run_product(args):
     # ---- setup (untimed): rank 0 generates + builds, the others load from /dev/shm ----
     t0 = time.time()
     if rank == 0:
-        bricks, field = load_or_build_scene(name, R)
+        bricks, field = load_or_build_scene(name, R, gpu_builder=True, time_builder=not args.no_builder_timing)
     if world > 1:
         dist.barrier()
         if rank != 0:
@@ -411,7 +439,7 @@ def run_product(args):
     regions, leaf = r.get_abr()
     create_s = time.time() - t
     bt = r.build_times()
-    build_info = {"renderer_create_wall_s": round(create_s, 3), **{k: round(v, 3) for k, v in bt.items()},
+    build_info = {**BUILDER_INFO, "renderer_create_wall_s": round(create_s, 3), **{k: round(v, 3) for k, v in bt.items()},
                   "abr_build_ms": round(bt["abr_geometry_ms"] + bt["value_ranges_ms"], 3), "abr_regions": int(len(regions)),
                   "abr_regions_per_s": round(len(regions) / max(1e-9, 1e-3 * (bt["abr_geometry_ms"] + bt["value_ranges_ms"]))),
                   "note": "device time (CUDA events): ABR geometry = kd build + regions + leaf lists (ExaBrickRegions::buildFrom, exa/Regions.cpp:242-287), value ranges = Regions.cpp:182-240; the reference's buildFrom on the same bricks is timed in cpu_baseline.reference_buildFrom"}
@@ -798,6 +826,7 @@ def main():
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-builder-timing", action="store_true", help="do not re-run the GPU exaBuilder for its timing when the scene cache exists")
     ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around warm-up + timed steps (for ncu --profile-from-start off)")
     ap.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce per frame instead of the peer-memory barrier kernel")

@@ -136,6 +136,14 @@ enum { EXA_BUILDER_SPATIAL_MEDIAN = 0, EXA_BUILDER_SAH_ALIKE = 1 };   /* builder
  * (builder.cpp:50). */
 int exa_bricks_build(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth,
                      exa_bricks_t **out);
+/* The same builder on the GPU: duplicate removal, per-node bounds, per-slice statistics, the partition
+ * and the brick writer run as CUDA kernels level by level over all nodes of the frontier; the split decisions are taken
+ * by the same host code as exa_bricks_build from those statistics, so the output (brick order, cell IDs, kd file) is
+ * bit-exact with it and with the reference.  timings (may be NULL): seconds of [0] cell upload, [1] duplicate removal,
+ * [2] level loop, [3] brick writer + download, [4] total; [5] tree levels, [6] nodes visited.  Fails with
+ * EXA_ERR_CUDA without a usable device (exa_bricks_build is the host builder; there is no silent fallback). */
+int exa_bricks_build_gpu(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth,
+                         int cudaDevice, exa_bricks_t **out, double timings[8]);
 /* ExaBricks::load (exa/ExaBricks.cpp:21-55) */
 int exa_bricks_load(const char *fileName, exa_bricks_t **out);
 int exa_bricks_from_memory(const void *bytes, size_t numBytes, exa_bricks_t **out);

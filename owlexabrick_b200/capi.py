@@ -58,6 +58,7 @@ _SIG = {
     "exa_set_scalar_layout": (i32, [i32]),
     "exa_renderer_get_scalar_layout": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
     "exa_bricks_build": (i32, [vp, sz, i32, i32, C.POINTER(vp)]),
+    "exa_bricks_build_gpu": (i32, [vp, sz, i32, i32, i32, C.POINTER(vp), vp]),
     "exa_bricks_load": (i32, [C.c_char_p, C.POINTER(vp)]),
     "exa_bricks_from_memory": (i32, [vp, sz, C.POINTER(vp)]),
     "exa_bricks_save": (i32, [vp, C.c_char_p, C.c_char_p]),

@@ -14,6 +14,7 @@
 // and the children recurse with the roles swapped, so nothing is allocated, zero-filled or
 // page-faulted serially on the way down (that, not the passes, dominated at 650 M cells).
 #include "exa_internal.h"
+#include "builder_common.h"
 #include <algorithm>
 #include <atomic>
 #include <climits>
@@ -32,24 +33,8 @@ namespace {
 
 struct Rec { int x, y, z, level, id; };
 
-struct Box4 {
-  int lo[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
-  int hi[4] = {INT_MIN, INT_MIN, INT_MIN, INT_MIN};
-  inline void extendCell(const Rec &c)
-  {
-    const int cw = 1 << c.level;                      // SingleCell::getBounds, builder.cpp:121-130
-    lo[0] = std::min(lo[0], c.x); lo[1] = std::min(lo[1], c.y); lo[2] = std::min(lo[2], c.z); lo[3] = std::min(lo[3], c.level);
-    hi[0] = std::max(hi[0], c.x + cw); hi[1] = std::max(hi[1], c.y + cw); hi[2] = std::max(hi[2], c.z + cw); hi[3] = std::max(hi[3], c.level + 1);
-  }
-  inline void extend(const Box4 &o) { for (int i = 0; i < 4; i++) { lo[i] = std::min(lo[i], o.lo[i]); hi[i] = std::max(hi[i], o.hi[i]); } }
-  inline int size(int i) const { return hi[i] - lo[i]; }
-  inline bool empty() const { return lo[0] > hi[0]; }
-};
-inline size_t unitCellVolume(const Box4 &b) { return (size_t)b.size(0) * (size_t)b.size(1) * (size_t)b.size(2); }   // :164-168
-inline size_t areaOf(const Box4 &b)                                                                                    // :170-177
-{ return (size_t)b.size(0) * (size_t)b.size(1) + (size_t)b.size(1) * (size_t)b.size(2) + (size_t)b.size(2) * (size_t)b.size(0); }
-inline int divDown(int a, int b) { return a >= 0 ? a / b : (a - (b - 1)) / b; }   // :53-59
-inline int divUp(int a, int b) { return a >= 0 ? (a + b - 1) / b : a / b; }       // :61-67
+using bld::Box4; using bld::unitCellVolume; using bld::areaOf; using bld::divDown; using bld::divUp;
+inline void extendCell(Box4 &b, const Rec &c) { b.extendCell(c.x, c.y, c.z, c.level); }
 
 static const size_t PAR_THRESHOLD = 1u << 16;
 
@@ -128,12 +113,12 @@ struct Builder {
   Box4 boundsOf(const Rec *v, size_t n)
   {
     Box4 b;
-    if (n < PAR_THRESHOLD) { for (size_t i = 0; i < n; i++) b.extendCell(v[i]); return b; }
+    if (n < PAR_THRESHOLD) { for (size_t i = 0; i < n; i++) extendCell(b, v[i]); return b; }
 #pragma omp parallel
     {
       Box4 lb;
 #pragma omp for schedule(static) nowait
-      for (size_t i = 0; i < n; i++) lb.extendCell(v[i]);
+      for (size_t i = 0; i < n; i++) extendCell(lb, v[i]);
 #pragma omp critical
       b.extend(lb);
     }
@@ -144,11 +129,8 @@ struct Builder {
   bool tryMakeLeaf(const Box4 &b, const Rec *v, size_t n, unsigned nodeID)
   {
     if (n == 0) throw std::runtime_error("empty ID vector in tryMakeLeaf!?");
-    if (b.size(3) > 1) return false;
+    if (!bld::isLeaf(b, n, maxLeafWidth)) return false;
     const size_t cw = 1ULL << (b.hi[3] - 1);
-    for (int d = 0; d < 3; d++) if ((size_t)b.size(d) / cw > (size_t)maxLeafWidth) return false;
-    const long long vol = (long long)b.size(0) * b.size(1) * b.size(2) * b.size(3);
-    if ((size_t)vol != n * (cw * cw * cw)) return false;
     ExaBrick h;
     for (int d = 0; d < 3; d++) { h.lower[d] = b.lo[d]; h.size[d] = b.size(d) / (int)cw; }
     h.level = b.lo[3];
@@ -177,8 +159,7 @@ struct Builder {
   void buildRec(Rec *v, Rec *o, size_t n, unsigned nodeID)
   {
     Box4 cb = boundsOf(v, n);                              // computeCoarsestLevelBounds :201-225
-    const int ccw = 1 << (cb.hi[3] - 1);
-    for (int d = 0; d < 3; d++) { cb.lo[d] = ccw * divDown(cb.lo[d], ccw); cb.hi[d] = ccw * divUp(cb.hi[d], ccw); }
+    const int ccw = bld::snapToCoarsest(cb);
     if (tryMakeLeaf(cb, v, n, nodeID)) return;
     const int dims[3] = {cb.size(0) / ccw, cb.size(1) / ccw, cb.size(2) / ccw};
     if (dims[0] == 1 && dims[1] == 1 && dims[2] == 1) throw std::runtime_error("coarse size 1 that's not a leaf!?");
@@ -192,7 +173,7 @@ struct Builder {
       auto splat = [&](Slices *s, const Rec &c) {
         const int cw = 1 << c.level; const size_t cv = (size_t)cw * cw * cw;
         const int bin[3] = {(c.x - cb.lo[0]) / ccw, (c.y - cb.lo[1]) / ccw, (c.z - cb.lo[2]) / ccw};
-        for (int d = 0; d < 3; d++) { s[d].vol[bin[d]] += cv; s[d].box[bin[d]].extendCell(c); }
+        for (int d = 0; d < 3; d++) { s[d].vol[bin[d]] += cv; extendCell(s[d].box[bin[d]], c); }
       };
       if (n < PAR_THRESHOLD) { for (size_t i = 0; i < n; i++) splat(sl, v[i]); }
       else {
@@ -206,34 +187,13 @@ struct Builder {
           for (int d = 0; d < 3; d++) for (int i = 0; i < dims[d]; i++) { sl[d].vol[i] += loc[d].vol[i]; sl[d].box[i].extend(loc[d].box[i]); }
         }
       }
-      // ---- boundary planes and SAH-alike cost (:603-722) ----
-      double bestCost = std::numeric_limits<float>::infinity();
-      for (int d = 0; d < 3; d++) {
-        if (dims[d] == 0) continue;
-        const size_t expected = unitCellVolume(cb) / dims[d];
-        std::vector<Box4> suffix(dims[d] + 1);           // suffix[i] = union of slices [i, dims)
-        for (int i = dims[d] - 1; i >= 0; i--) { suffix[i] = suffix[i + 1]; suffix[i].extend(sl[d].box[i]); }
-        Box4 prefix;                                     // union of slices [0, plane)
-        for (int plane = 1; plane < dims[d]; plane++) {
-          prefix.extend(sl[d].box[plane - 1]);
-          const int L = plane - 1, R = plane;
-          const bool lFull = sl[d].vol[L] == expected, rFull = sl[d].vol[R] == expected;
-          // :636-643 — an empty slice is never full, so its w-extent never decides anything
-          bool isBoundary = true;
-          if (lFull && rFull)
-            isBoundary = !(sl[d].box[L].lo[3] == sl[d].box[R].lo[3] && sl[d].box[L].size(3) == sl[d].box[R].size(3));
-          if (!isBoundary) continue;
-          const Box4 &lb = prefix, &rb = suffix[plane];
-          const double cost = areaOf(lb) * (double)unitCellVolume(lb) * lb.size(3)
-                            + areaOf(rb) * (double)unitCellVolume(rb) * rb.size(3);
-          if (cost < bestCost) { bestCost = cost; bestDim = d; bestPos = cb.lo[d] + plane * ccw; }
-        }
-      }
-    }
-    if (bestDim == -1) {                                 // spatial median fallback, :728-734
-      bestDim = 0;
-      for (int i = 1; i < 3; i++) if (dims[i] > dims[bestDim]) bestDim = i;
-      bestPos = cb.lo[bestDim] + (dims[bestDim] / 2) * ccw;
+      // ---- boundary planes and SAH-alike cost (:603-722): builder_common.h ----
+      const size_t *const vol[3] = {sl[0].vol.data(), sl[1].vol.data(), sl[2].vol.data()};
+      const Box4 *const box[3] = {sl[0].box.data(), sl[1].box.data(), sl[2].box.data()};
+      bld::chooseSplit(cb, dims, ccw, true, vol, box, bestDim, bestPos);
+    } else {
+      const size_t *const vol[3] = {nullptr, nullptr, nullptr}; const Box4 *const box[3] = {nullptr, nullptr, nullptr};
+      bld::chooseSplit(cb, dims, ccw, false, vol, box, bestDim, bestPos);   // spatial median, :728-734
     }
 
     // ---- partition (:753-770): v -> o, left part first, order kept ----

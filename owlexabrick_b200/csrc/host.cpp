@@ -27,6 +27,7 @@ BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, std::vector<int32_t> &&
   BricksImpl *b = new BricksImpl; b->hdr = std::move(hdr); b->ids = std::move(ids); b->kd = std::move(kd); return b;
 }
 BricksImpl *buildBricks(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth);   // builder.cpp
+BricksImpl *buildBricksGpu(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth, int cudaDevice, double timings[8]);   // gpu_builder.cu
 
 // .bricks stream: repeated {int32 size[3]; int32 lower[3]; int32 level; int32 cellID[sx*sy*sz]}
 static BricksImpl *parseBricks(const uint8_t *p, size_t n)
@@ -73,6 +74,19 @@ int exa_bricks_build(const int32_t *cells, size_t numCells, int builderType, int
   if (maxLeafWidth <= 0) maxLeafWidth = 127;
   EXA_TRY
   *out = new exa_bricks{buildBricks(cells, numCells, builderType, maxLeafWidth)};
+  return EXA_OK;
+  EXA_CATCH
+}
+
+int exa_bricks_build_gpu(const int32_t *cells, size_t numCells, int builderType, int maxLeafWidth, int cudaDevice,
+                         exa_bricks_t **out, double timings[8])
+{
+  if (!out || (!cells && numCells)) { setError("exa_bricks_build_gpu: null argument"); return EXA_ERR_INVALID; }
+  if (builderType != EXA_BUILDER_SAH_ALIKE && builderType != EXA_BUILDER_SPATIAL_MEDIAN) { setError("exa_bricks_build_gpu: unknown builder type"); return EXA_ERR_INVALID; }
+  if (maxLeafWidth <= 0) maxLeafWidth = 127;
+  if (!exa_cuda_available()) return EXA_ERR_CUDA;            // no CPU fallback: exa_bricks_build is the host builder
+  EXA_TRY
+  *out = new exa_bricks{buildBricksGpu(cells, numCells, builderType, maxLeafWidth, cudaDevice, timings)};
   return EXA_OK;
   EXA_CATCH
 }

@@ -44,6 +44,16 @@ class ExaBricks:
         return ExaBricks(out.value)
 
     @staticmethod
+    def build_gpu(cells, builder=capi.BUILDER_SAH_ALIKE, max_leaf_width=127, device=0):
+        """exaBuilder on the GPU (exa_bricks_build_gpu); .timings = seconds per stage"""
+        cells = np.ascontiguousarray(cells, dtype=np.int32).reshape(-1, 4)
+        out, tm = C.c_void_p(), (C.c_double * 8)()
+        check(lib.exa_bricks_build_gpu(_p(cells), len(cells), builder, max_leaf_width, device, C.byref(out), tm))
+        b = ExaBricks(out.value)
+        b.timings = {"upload_s": tm[0], "dedup_s": tm[1], "levels_s": tm[2], "write_s": tm[3], "total_s": tm[4], "levels": int(tm[5]), "nodes": int(tm[6])}
+        return b
+
+    @staticmethod
     def load(file_name):
         out = C.c_void_p()
         check(lib.exa_bricks_load(file_name.encode(), C.byref(out)))

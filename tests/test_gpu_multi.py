@@ -85,7 +85,7 @@ def test_sort_last_equals_single_gpu_without_ert(R, orc, world, data_partitioned
     assert np.abs(col.reshape(H, W, 3) - acc[..., :3]).max() <= 1e-5
     if data_partitioned:
         total_cells = b.total_num_cells
-        assert sum(c for _, c in res) < 2.5 * total_cells           # straddling bricks are duplicated, nothing more
+        assert sum(c for _, c in res) < (2.5 if world <= 4 else 4.0) * total_cells   # straddling bricks are duplicated (this scene has 9 192 cells in a few bricks), nothing more
         assert max(c for _, c in res) < total_cells                  # no rank holds everything
         assert all(nb <= b.num_bricks for nb, _ in res)
 
