@@ -493,6 +493,12 @@ def run_product(args):
         torch.cuda.profiler.start()
     for _ in range(args.warmup):
         step()
+    balance = None
+    if world > 1 and mode == "tiles" and not args.static_tiles:
+        # tiles dealt by measured cost (part of the warm-up, as a viewer would do every few dozen frames)
+        balance = {"max_over_mean_rank_load_after_lpt": pipe.rebalance()}
+        for _ in range(3):
+            step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -651,8 +657,8 @@ def run_product(args):
             mg_check["note"] = "image tiles: bit-identical expected; sort-last: per-rank early termination (H1) bounds the deviation"
             mg_check["barrier_timed_out"] = pipe.bar.timed_out()
             log("multi-GPU check:", mg_check)
-            if mode == "tiles":
-                r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
+        if mode == "tiles":                                           # rank 0 left tile mode for the comparison: back to the static deal on EVERY rank (consistent)
+            r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
         dist.barrier()
 
     # ---- sort-last (north_star's primary multi-GPU mode), measured inside the default --gpus N run: data partitioned
@@ -807,7 +813,7 @@ def run_product(args):
                              "traffic": ncu_traffic("k_renderFrame", name) if world == 1 else None, "algorithmic_bytes_per_launch": bframe // world, "peak_source": peak_src,
                              "note": "algorithmic bytes (SURVEY 8d) count every brick-header/scalar load of addBasisFunctions; almost all are served by L1/L2 (traffic = measured DRAM bytes of one launch, ncu): the frame kernel is issue-bound, not HBM-bound"},
                 "dvr_translucent": translucent, "recon": recon, "multi_gpu_check": mg_check, "frame_kernel_only_ms_per_step": render_only_ms,
-                "barrier_alone_ms": barrier_ms, "sortlast": sortlast, "cpu_baseline": cpu,
+                "barrier_alone_ms": barrier_ms, "tile_balance": balance, "sortlast": sortlast, "cpu_baseline": cpu,
                 "parity": parity, "build": build_info}
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -830,6 +836,7 @@ def main():
     ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around warm-up + timed steps (for ncu --profile-from-start off)")
     ap.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce per frame instead of the peer-memory barrier kernel")
+    ap.add_argument("--static-tiles", action="store_true", help="N>1 image tiles: keep the static round-robin deal (no cost-balanced tile lists)")
     ap.add_argument("--no-sortlast", action="store_true", help="N>1: skip the secondary sort-last measurement")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")
     args = ap.parse_args()

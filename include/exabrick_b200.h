@@ -413,6 +413,16 @@ int exa_ipc_export(const void *d_ptr, uint8_t handle[64]);
 int exa_ipc_import(const uint8_t handle[64], int cudaDevice, void **d_ptr);
 int exa_ipc_close(void *d_ptr);
 
+/* Image tiles balanced by measured cost (multi-GPU, data replicated).  With tile costs enabled the frame kernel
+ * records, per 16x8-pixel tile it rendered, the SM cycles its CTA took.  The ranks combine their arrays (each tile
+ * is rendered by one rank; max or sum), exa_balance_tiles deals the tiles longest-processing-time-first
+ * (deterministic: every rank computes the same deal) and exa_renderer_set_tile_list installs this rank's tiles,
+ * most expensive first, in place of the static round-robin deal.  numTiles = ceil(W/16) * ceil(H/8); a list of
+ * length 0 restores the static deal.  The union of the ranks' tiles is the frame either way. */
+int exa_renderer_enable_tile_costs(exa_renderer_t *r, int enable);
+int exa_renderer_get_tile_costs(exa_renderer_t *r, uint32_t *costs, int numTiles);
+int exa_renderer_set_tile_list(exa_renderer_t *r, const uint32_t *tiles, int numTiles);
+int exa_balance_tiles(const uint32_t *costs, int numTiles, int numRanks, int rank, uint32_t *outTiles /* numTiles */, int *outCount);
 /* Stream-ordered barrier between the ranks of one NVSwitch box over peer memory (one process per GPU).
  * flagPtrs[k] = rank k's flag array (exa_device_malloc of >= 17 uint32, zero-filled, IPC-mapped into every
  * rank).  Enqueues a one-warp kernel on `cudaStream` that publishes `seq` (increasing, first call 1) to every

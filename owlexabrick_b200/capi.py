@@ -137,6 +137,10 @@ _SIG = {
     "exa_renderer_get_residency": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
     "exa_renderer_get_build_times": (i32, [vp, vp]),
     "exa_renderer_set_color_strips": (i32, [vp, vp, i32]),
+    "exa_renderer_enable_tile_costs": (i32, [vp, i32]),
+    "exa_renderer_get_tile_costs": (i32, [vp, vp, i32]),
+    "exa_renderer_set_tile_list": (i32, [vp, vp, i32]),
+    "exa_balance_tiles": (i32, [vp, i32, i32, i32, vp, C.POINTER(i32)]),
     "exa_peer_barrier": (i32, [vp, i32, i32, C.c_uint32, vp]),
     "exa_copy_async": (i32, [vp, vp, sz, vp]),
     "exa_host_register": (i32, [vp, sz]),

@@ -41,6 +41,8 @@ struct exa_renderer {
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
   uint32_t *strips[EXA_MAX_PARTS] = {}; int numStrips = 0;   // exa_renderer_set_color_strips
+  uint32_t *d_tileList = nullptr; int tileListLen = 0; size_t tileListCap = 0;   // exa_renderer_set_tile_list (balanced image tiles)
+  uint32_t *d_tileCost = nullptr; int tileCostLen = 0;
   // pipelined read-back (exa_renderer_read_rgba8_async): second renderer-owned RGBA8 buffer, copy stream
   uint32_t *d_rgba8Alt = nullptr; cudaStream_t copyStream = nullptr; cudaEvent_t evRendered = nullptr, evCopied[2] = {nullptr, nullptr}; int rbCur = 0;
   // pinned staging ring for updateXF (no stream synchronise per update)
@@ -138,6 +140,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.anySurf = (anyContour || P.traces || P.numMeshTris > 0 || (P.aoEnabled && P.anyIso)) ? 2 : P.anyIso ? 1 : 0;
   P.stats = nullptr;
   P.tileOrderIn = nullptr; P.tileOrderOut = nullptr; P.tileOrderCap = r->tileOrderCap;
+  P.tileList = r->tileListLen > 0 ? r->d_tileList : nullptr; P.tileListLen = r->tileListLen; P.tileCost = r->d_tileCost;
   P.kdStack = r->abr.depth + 2;
   P.dbg = 0;
 #ifdef EXA_DEBUG
@@ -499,7 +502,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
-  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]);
+  cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_tileList); cudaFree(r->d_tileCost);
   delete r;
 }
 
@@ -605,6 +608,7 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   else { CKR(cudaMalloc(&r->d_rgba8, n * 4)); CKR(cudaMemset(r->d_rgba8, 0, n * 4)); r->ownRgba8 = true; }
   r->width = width; r->height = height;
   for (int i = 0; i < 2; i++) { cudaFree(r->d_tileOrder[i]); r->d_tileOrder[i] = nullptr; }
+  cudaFree(r->d_tileCost); r->d_tileCost = nullptr; r->tileCostLen = 0; r->tileListLen = 0;    // tile ids of the old size are meaningless
   r->tileOrderCap = ((width + 15) / 16) * ((height + 7) / 8); r->tileOrderValid = false;
   if (!getenv("EXA_NO_TILE_ORDER"))
     for (int i = 0; i < 2; i++) CKR(cudaMalloc(&r->d_tileOrder[i], sizeof(TileOrder) + sizeof(uint32_t) * (size_t)TILE_BUCKETS * r->tileOrderCap));

@@ -89,7 +89,7 @@ static int doRender(exa_renderer *r, float4 *partialOut, float4 *partialSurf, Ex
     } else P.traces = nullptr;                               // every visible segment has a dead end
   }
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
-  if (r->d_tileOrder[0]) {                                   // cost-ordered tile schedule (render.cu)
+  if (r->d_tileOrder[0] && !P.tileList) {                    // cost-ordered tile schedule (render.cu); an explicit tile list is already ordered
     if (!r->tileOrderValid)                                  // (re)start: both buffers' counters to zero, once
       for (int i = 0; i < 2; i++) CKR(cudaMemsetAsync(r->d_tileOrder[i], 0, offsetof(TileOrder, list), r->stream));
     if (r->tileOrderValid) P.tileOrderIn = r->d_tileOrder[r->tileOrderCur];
@@ -378,7 +378,7 @@ int exa_renderer_set_partition(exa_renderer_t *r, int mode, int rank, int numRan
     setError("set_partition: this renderer holds only the bricks of its own sort-last part"); return EXA_ERR_INVALID;
   }
   r->partMode = mode; r->rank = rank; r->numRanks = numRanks; r->masksDirty = true;
-  r->tileOrderValid = false;                                 // the set of owned tiles may have changed
+  r->tileOrderValid = false; r->tileListLen = 0;             // the set of owned tiles may have changed
   r->partTree.clear(); r->partRoot = 0;
   if (mode != EXA_PARTITION_SORT_LAST) return EXA_OK;
   // replicated scene: the same partition tree as the data-partitioned mode, applied as a visibility mask
@@ -448,6 +448,63 @@ int exa_renderer_composite_partials(exa_renderer_t *r, const float *const *d_par
   const int k = launchCompositeFinish(P, C, r->stream);
   if (k < 0) { setError("composite kernel launch failed"); return EXA_ERR_CUDA; }
   r->launches += k; return EXA_OK;
+}
+
+// ---- image tiles balanced by measured cost --------------------------------------------------------------
+int exa_renderer_enable_tile_costs(exa_renderer_t *r, int enable)
+{
+  if (!r || !r->d_accum) { setError("enable_tile_costs: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  const int numTiles = ((r->width + 15) / 16) * ((r->height + 7) / 8);
+  if (!enable) { CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_tileCost); r->d_tileCost = nullptr; r->tileCostLen = 0; return EXA_OK; }
+  if (!r->d_tileCost) { CKR(cudaMalloc(&r->d_tileCost, 4 * (size_t)numTiles)); r->tileCostLen = numTiles; }
+  CKR(cudaMemsetAsync(r->d_tileCost, 0, 4 * (size_t)numTiles, r->stream));
+  return EXA_OK;
+}
+
+int exa_renderer_get_tile_costs(exa_renderer_t *r, uint32_t *costs, int numTiles)
+{
+  if (!r || !costs || !r->d_tileCost || numTiles != r->tileCostLen) { setError("get_tile_costs: tile costs are not enabled / wrong tile count"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  CKR(cudaMemcpyAsync(costs, r->d_tileCost, 4 * (size_t)numTiles, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  return EXA_OK;
+}
+
+int exa_renderer_set_tile_list(exa_renderer_t *r, const uint32_t *tiles, int numTiles)
+{
+  if (!r || !r->d_accum || numTiles < 0 || (numTiles && !tiles)) { setError("set_tile_list: bad argument"); return EXA_ERR_INVALID; }
+  const int total = ((r->width + 15) / 16) * ((r->height + 7) / 8);
+  for (int i = 0; i < numTiles; i++) if (tiles[i] >= (uint32_t)total) { setError("set_tile_list: tile id outside the frame"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  if ((size_t)numTiles > r->tileListCap) {
+    CKR(cudaStreamSynchronize(r->stream)); cudaFree(r->d_tileList); r->d_tileList = nullptr;
+    CKR(cudaMalloc(&r->d_tileList, 4 * (size_t)numTiles)); r->tileListCap = numTiles;
+  }
+  if (numTiles) { CKR(cudaMemcpyAsync(r->d_tileList, tiles, 4 * (size_t)numTiles, cudaMemcpyHostToDevice, r->stream)); CKR(cudaStreamSynchronize(r->stream)); }
+  r->tileListLen = numTiles;
+  return EXA_OK;
+}
+
+int exa_balance_tiles(const uint32_t *costs, int numTiles, int numRanks, int rank, uint32_t *outTiles, int *outCount)
+{
+  if (!costs || !outTiles || !outCount || numTiles < 0 || numRanks < 1 || rank < 0 || rank >= numRanks) { setError("balance_tiles: bad argument"); return EXA_ERR_INVALID; }
+  // longest-processing-time-first: tiles by descending cost (ties: ascending id), each to the rank with the smallest load
+  // (ties: the lowest rank).  Deterministic, so every rank computes the same deal from the same costs.
+  std::vector<uint32_t> order(numTiles);
+  for (int i = 0; i < numTiles; i++) order[i] = (uint32_t)i;
+  std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return costs[a] > costs[b]; });
+  std::vector<unsigned long long> load(numRanks, 0); std::vector<int> cnt(numRanks, 0);
+  int n = 0;
+  const int cap = (numTiles + numRanks - 1) / numRanks + numTiles / (4 * numRanks) + 1;   // no rank gets more than ~1.25x its share of tiles (zero-cost tails)
+  for (int i = 0; i < numTiles; i++) {
+    int best = -1;
+    for (int k = 0; k < numRanks; k++) if (cnt[k] < cap && (best < 0 || load[k] < load[best])) best = k;
+    load[best] += (unsigned long long)costs[order[i]] + 1ull; cnt[best]++;
+    if (best == rank) outTiles[n++] = order[i];
+  }
+  *outCount = n;
+  return EXA_OK;
 }
 
 int exa_peer_barrier(void *const *flagPtrs, int rank, int numRanks, unsigned seq, void *cudaStream)

@@ -737,7 +737,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // the grid holds only the owned tiles (ownedTile()).
   const long long t_start = clock64();
   int tileId;
-  if (P.tileOrderIn) {
+  if (P.tileList) tileId = (int)P.tileList[blockIdx.x];
+  else if (P.tileOrderIn) {
     int q = (int)blockIdx.x, b = 0; bool found = false;
 #pragma unroll
     for (int i = TILE_BUCKETS - 1; i > 0; i--) {            // most expensive bucket first
@@ -865,6 +866,10 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     }
     if (lane == 0 && P.stats) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], e); }
   }
+  if (P.tileCost) {                                          // cross-rank balancing: this tile's cycles, for the next deal
+    __syncthreads();
+    if (threadIdx.x == 0) P.tileCost[tileId] = (uint32_t)min((unsigned long long)(clock64() - t_start), 0xffffffffull);
+  }
   if (P.tileOrderOut) {                                      // record this tile's cost for the next frame's schedule
     __syncthreads();
     if (threadIdx.x == 0) {
@@ -889,7 +894,7 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
   const int numTiles = tilesX * tilesY;
-  const int numMine = P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
+  const int numMine = P.tileList ? P.tileListLen : P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
   if (numMine <= 0) return 0;
   const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;

@@ -56,6 +56,9 @@ struct RenderParams {
   unsigned long long *stats;           // 4 counters (ExaStats) or null
   const TileOrder *tileOrderIn;        // previous frame's tile cost order (null: scan order)
   TileOrder *tileOrderOut; int tileOrderCap;   // where this frame records its own (null: off)
+  // image tiles across GPUs with measured load balance: an explicit list of this rank's tiles (most expensive first;
+  // replaces ownedTile() and the bucket order) and, per tile of the frame, the CTA cycles it took (input of the next deal)
+  const uint32_t *tileList; int tileListLen; uint32_t *tileCost;
   int kdStack;                         // stack entries per warp
   int warpUnits;                       // set by launchRenderFrame: 16-B units of shared memory per warp
   int dbg;                             // EXA_DEBUG builds only: print segments/samples

@@ -276,7 +276,35 @@ class TilePipeline(_Pipeline):
                                                          self.d2h_bytes, C.c_void_p(self.side.cuda_stream)))
         return b
 
+    def rebalance(self, rounds=2):
+        """Deal the tiles by measured cost: render a frame with per-tile cycle counters on, combine the ranks' counters
+        (each tile is rendered by exactly one rank), run the deterministic LPT deal on every rank and install this rank's
+        list.  The second round measures under the balanced deal.  A viewer calls this every few dozen frames (the cost
+        is one frame plus a 130 KB all-reduce); bench.py calls it during warm-up.  Returns max / mean rank load."""
+        np, torch, capi = self.np, self.torch, self.capi
+        nt = ((self.W + 15) // 16) * ((self.H + 7) // 8)
+        ratio = None
+        for _ in range(rounds):
+            capi.check(capi.lib.exa_renderer_enable_tile_costs(self.r.h, 1))
+            self.step(); self.drain(); torch.cuda.synchronize()
+            costs = np.zeros(nt, np.uint32)
+            capi.check(capi.lib.exa_renderer_get_tile_costs(self.r.h, costs.ctypes.data_as(C.c_void_p), nt))
+            capi.check(capi.lib.exa_renderer_enable_tile_costs(self.r.h, 0))
+            t = torch.from_numpy(np.minimum(costs, 0x7fffffff).astype(np.int32)).cuda()
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+            costs = t.cpu().numpy().astype(np.uint32)
+            mine, n = np.zeros(nt, np.uint32), C.c_int()
+            capi.check(capi.lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, self.world, self.rank, mine.ctypes.data_as(C.c_void_p), C.byref(n)))
+            capi.check(capi.lib.exa_renderer_set_tile_list(self.r.h, mine.ctypes.data_as(C.c_void_p), n.value))
+            load = torch.tensor([float(costs[mine[:n.value]].astype(np.float64).sum())], dtype=torch.float64, device="cuda")
+            loads = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(self.world)]
+            self.dist.all_gather(loads, load)
+            v = [float(x.item()) for x in loads]
+            ratio = max(v) / max(sum(v) / len(v), 1e-9)
+        return ratio
+
     def _close_buffers(self):
+        self.capi.lib.exa_renderer_set_tile_list(self.r.h, None, 0)
         self.capi.lib.exa_renderer_set_color_strips(self.r.h, None, 0)
         self.strips.close(self.dist)
 

@@ -207,3 +207,49 @@ def test_tracer_params_take_effect_at_reset(R, orc):
     assert np.array_equal(r.readTraces(), before)
     r.resetTracer()                                                  # now the new shape
     assert r.readTraces().shape == (4000, 500, 3)
+
+
+@pytest.mark.parametrize("world", [2, 5])
+def test_cost_balanced_tile_lists_partition_the_frame(R, orc, built_lib, world):
+    """image tiles dealt by measured cost (exa_balance_tiles + exa_renderer_set_tile_list): the lists of the ranks are a
+    partition of the tiles, balanced in cost, and the union of what they render is the single-renderer frame bit for bit"""
+    import torch
+    lib, check = built_lib.lib, built_lib.check
+    b, fields, dom = _scene(R, mlw=127)
+    W, H = 200, 116
+    nt = ((W + 15) // 16) * ((H + 7) // 8)
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [dom] * 3, W, H))
+    fd.opacity_scale = 0.1
+    r = R.Renderer(b, fields)
+    fd.apply(r)
+    r.render()
+    ref = r.read_rgba8().copy()
+    check(lib.exa_renderer_enable_tile_costs(r.h, 1))
+    r.render()
+    costs = np.zeros(nt, np.uint32)
+    check(lib.exa_renderer_get_tile_costs(r.h, costs.ctypes.data_as(C.c_void_p), nt))
+    check(lib.exa_renderer_enable_tile_costs(r.h, 0))
+    assert (costs > 0).all()                                        # every tile was rendered and timed
+    fb = torch.zeros((H, W), dtype=torch.int32, device="cuda")
+    check(lib.exa_renderer_set_color_buffer(r.h, fb.data_ptr()))
+    seen, loads = np.zeros(nt, int), []
+    for k in range(world):
+        mine, n = np.zeros(nt, np.uint32), C.c_int()
+        check(lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, world, k, mine.ctypes.data_as(C.c_void_p), C.byref(n)))
+        mine = mine[:n.value]
+        assert (np.diff(costs[mine].astype(np.int64)) <= 0).all()   # most expensive first
+        seen[mine] += 1
+        loads.append(int(costs[mine].astype(np.int64).sum()))
+        r.set_partition(built_lib.PARTITION_IMAGE_TILES, k, world)
+        check(lib.exa_renderer_set_tile_list(r.h, mine.ctypes.data_as(C.c_void_p), len(mine)))
+        r.render()
+    assert (seen == 1).all()
+    assert max(loads) <= 1.05 * (sum(loads) / world) + int(costs.max())
+    assert (fb.cpu().numpy().view(np.uint32) == ref).all()
+    with pytest.raises(Exception):
+        bad = np.array([nt], np.uint32)
+        check(lib.exa_renderer_set_tile_list(r.h, bad.ctypes.data_as(C.c_void_p), 1))
+    r.set_partition(built_lib.PARTITION_NONE, 0, 1)
+    check(lib.exa_renderer_set_color_buffer(r.h, None))
+    r.render()
+    assert (r.read_rgba8() == ref).all()
