@@ -413,6 +413,30 @@ int exa_ipc_export(const void *d_ptr, uint8_t handle[64]);
 int exa_ipc_import(const uint8_t handle[64], int cudaDevice, void **d_ptr);
 int exa_ipc_close(void *d_ptr);
 
+/* ---------------------------------------------------------------------------------------
+ * Renderer group: N GPUs of one node driven by one host thread (the reference only replicates
+ * its launch on every device, programs/LaunchParams.h:31-32 are never read).  One renderer per device;
+ * mode EXA_PARTITION_IMAGE_TILES replicates the scene and splits the image, EXA_PARTITION_SORT_LAST partitions
+ * the DATA along the ABR kd-tree (exa_renderer_create_partitioned) and composites the partial images through
+ * NVLink peer memory.  exa_group_render renders one frame on all devices and returns when the whole RGBA8 frame
+ * (scan-line layout) is in hostRgba8; every device copies its own strip / span over its own PCIe link.
+ * Per-frame setters are forwarded to all devices; the others are called per device on exa_group_renderer(g, i).
+ * A device may be listed more than once (several parts on one GPU: tests).
+ * ------------------------------------------------------------------------------------- */
+typedef struct exa_group exa_group_t;
+int exa_group_create(const exa_bricks_t *bricks, const float *const *fields, const size_t *fieldCounts,
+                     int numFields, const int *cudaDevices, int numDevices, int mode, exa_group_t **out);
+void exa_group_destroy(exa_group_t *g);
+int exa_group_size(const exa_group_t *g);
+exa_renderer_t *exa_group_renderer(exa_group_t *g, int i);
+int exa_group_resize_framebuffer(exa_group_t *g, int width, int height);
+int exa_group_update_camera(exa_group_t *g, const float pos[3], const float dir00[3], const float dirDu[3], const float dirDv[3]);
+int exa_group_update_xf(exa_group_t *g, int channel, const float *opacities128, const float *rgb128x3,
+                        float domainLower, float domainUpper, float opacityScale);
+int exa_group_update_frame_id(exa_group_t *g, int frameID);
+int exa_group_set_voxel_space_transform(exa_group_t *g, const float xfm12[12]);
+int exa_group_render(exa_group_t *g, uint32_t *hostRgba8);
+
 /* Image tiles balanced by measured cost (multi-GPU, data replicated).  With tile costs enabled the frame kernel
  * records, per 16x8-pixel tile it rendered, the SM cycles its CTA took.  The ranks combine their arrays (each tile
  * is rendered by one rank; max or sum), exa_balance_tiles deals the tiles longest-processing-time-first

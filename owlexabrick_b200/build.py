@@ -23,7 +23,7 @@ if os.environ.get("EXA_VARIANT"):
     LIB = os.path.join(HERE, "libexabrick_b200.%s.so" % os.environ["EXA_VARIANT"])
     OBJ = os.path.join(HERE, "build", os.environ["EXA_VARIANT"])
 SOURCES = ["host.cpp", "colormap.cpp", "builder.cpp", "gpu_builder.cu", "abr.cu", "render.cu", "capi.cu"]
-HEADERS = ["exa_internal.h", "builder_common.h", "render.cuh", "surfaces.cuh", "capi_render.inl", "colormaps_data.inc", os.path.join("..", "..", "include", "exabrick_b200.h")]
+HEADERS = ["exa_internal.h", "builder_common.h", "render.cuh", "surfaces.cuh", "capi_render.inl", "capi_group.inl", "colormaps_data.inc", os.path.join("..", "..", "include", "exabrick_b200.h")]
 
 
 def _stale(out, deps):

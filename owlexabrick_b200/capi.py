@@ -141,6 +141,16 @@ _SIG = {
     "exa_renderer_get_tile_costs": (i32, [vp, vp, i32]),
     "exa_renderer_set_tile_list": (i32, [vp, vp, i32]),
     "exa_balance_tiles": (i32, [vp, i32, i32, i32, vp, C.POINTER(i32)]),
+    "exa_group_create": (i32, [vp, vp, vp, i32, vp, i32, i32, C.POINTER(vp)]),
+    "exa_group_destroy": (None, [vp]),
+    "exa_group_size": (i32, [vp]),
+    "exa_group_renderer": (vp, [vp, i32]),
+    "exa_group_resize_framebuffer": (i32, [vp, i32, i32]),
+    "exa_group_update_camera": (i32, [vp, vp, vp, vp, vp]),
+    "exa_group_update_xf": (i32, [vp, i32, vp, vp, f32, f32, f32]),
+    "exa_group_update_frame_id": (i32, [vp, i32]),
+    "exa_group_set_voxel_space_transform": (i32, [vp, vp]),
+    "exa_group_render": (i32, [vp, vp]),
     "exa_peer_barrier": (i32, [vp, i32, i32, C.c_uint32, vp]),
     "exa_copy_async": (i32, [vp, vp, sz, vp]),
     "exa_host_register": (i32, [vp, sz]),

@@ -798,3 +798,4 @@ uint64_t exa_renderer_launch_count(const exa_renderer_t *r) { return r ? r->laun
 } // extern "C"
 
 #include "capi_render.inl"
+#include "capi_group.inl"

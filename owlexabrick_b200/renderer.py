@@ -548,3 +548,51 @@ class Renderer:
         pa = (C.c_void_p * n)(*d_partials)
         su = (C.c_void_p * n)(*d_surfs) if d_surfs else None
         check(lib.exa_renderer_composite_partials(self.h, pa, su, n, first, count, C.c_void_p(d_rgba8)))
+
+
+class RendererGroup:
+    """exa_group_*: N GPUs of one node driven by this one host thread (image tiles over a replicated scene, or sort-last
+    over a partitioned one).  .renderers[i] are ordinary Renderer objects (not owning) for the per-device setters."""
+
+    def __init__(self, bricks, fields, devices, mode=capi.PARTITION_IMAGE_TILES):
+        fields = [np.ascontiguousarray(f, dtype=np.float32) for f in fields]
+        ptrs = (C.c_void_p * len(fields))(*[f.ctypes.data for f in fields])
+        counts = (C.c_size_t * len(fields))(*[len(f) for f in fields])
+        dev = (C.c_int * len(devices))(*devices)
+        out = C.c_void_p()
+        check(lib.exa_group_create(bricks.h, ptrs, counts, len(fields), dev, len(devices), mode, C.byref(out)))
+        self.h, self.bricks, self.size = out, bricks, (0, 0)
+        self.renderers = []
+        for i in range(lib.exa_group_size(self.h)):
+            r = Renderer.__new__(Renderer)
+            r.h, r.bricks, r.num_fields, r.fb_size = None, bricks, len(fields), (0, 0)
+            r._trace_shape = r._pending_shape = (1000, 100)
+            r.h = C.c_void_p(lib.exa_group_renderer(self.h, i))
+            r.close = lambda: None                                    # owned by the group
+            self.renderers.append(r)
+
+    def close(self):
+        if getattr(self, "h", None):
+            for r in self.renderers:
+                r.h = None
+            lib.exa_group_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def apply(self, fd):
+        """a tests/scenes.FrameDesc on every device (the frame buffers belong to the group)"""
+        if self.size != (fd.width, fd.height):
+            check(lib.exa_group_resize_framebuffer(self.h, fd.width, fd.height))
+            self.size = (fd.width, fd.height)
+        for r in self.renderers:
+            r.fb_size = self.size
+            fd.apply(r)
+
+    def render(self, out=None):
+        """one frame -> uint32[H, W] host array"""
+        if out is None:
+            out = np.zeros((self.size[1], self.size[0]), np.uint32)
+        check(lib.exa_group_render(self.h, _p(out)))
+        return out

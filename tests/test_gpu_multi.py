@@ -253,3 +253,40 @@ def test_cost_balanced_tile_lists_partition_the_frame(R, orc, built_lib, world):
     check(lib.exa_renderer_set_color_buffer(r.h, None))
     r.render()
     assert (r.read_rgba8() == ref).all()
+
+
+@pytest.mark.parametrize("mode_name,parts", [("tiles", 1), ("tiles", 3), ("sortlast", 1), ("sortlast", 4)])
+def test_renderer_group_behind_the_c_abi(R, orc, built_lib, mode_name, parts):
+    """exa_group_*: one host thread, N devices (here one GPU listed `parts` times; with real peers the same code path
+    uses cudaDeviceEnablePeerAccess): image tiles reproduce the single-renderer frame bit for bit, sort-last within
+    1 RGBA8 level with the termination threshold off"""
+    b, fields, dom = _scene(R)
+    W, H = 200, 116
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [dom] * 3, W, H))
+    fd.opacity_scale = 0.05
+    fd.ert = 2.0
+    r1 = R.Renderer(b, fields)
+    fd.apply(r1)
+    r1.render()
+    ref = r1.read_rgba8()
+    mode = built_lib.PARTITION_IMAGE_TILES if mode_name == "tiles" else built_lib.PARTITION_SORT_LAST
+    g = R.RendererGroup(b, fields, [0] * parts, mode)
+    g.apply(fd)
+    for _ in range(2):                                               # second frame: cost-ordered tile schedule
+        img = g.render()
+    if mode_name == "tiles":
+        assert (img == ref).all()
+    else:
+        assert np.abs(scenes.unpack_rgba8(img) - scenes.unpack_rgba8(ref)).max() <= 1
+    # a per-device setter through the group's renderer handles, then a per-frame setter through the group
+    for r in g.renderers:
+        r.setGradientShadingDVR(False)
+    alpha, rgb = fd.xf[0]
+    built_lib.check(built_lib.lib.exa_group_update_xf(g.h, 0, alpha.ctypes.data_as(C.c_void_p), np.ascontiguousarray(rgb).ctypes.data_as(C.c_void_p), 0.0, 1.0, 0.2))
+    r1.setGradientShadingDVR(False)
+    r1.updateXF(0, alpha, rgb, (0.0, 1.0), 0.2)
+    r1.render()
+    img2 = g.render()
+    assert np.abs(scenes.unpack_rgba8(img2) - scenes.unpack_rgba8(r1.read_rgba8())).max() <= (0 if mode_name == "tiles" else 1)
+    assert (img2 != img).any()
+    g.close()
