@@ -749,7 +749,11 @@ def run_product(args):
         cdt = time.time() - t
         def frame_parity(g, o):
             e = np.abs(g[..., :3] - o[..., :3]).max(axis=-1)
-            return {"rgba_max_abs": float(e.max()), "pixels_over_1e-3": int((e > 1e-3).sum()), "pixels": int(e.size)}
+            worst = np.argsort(e.reshape(-1))[-3:][::-1]
+            return {"rgba_max_abs": float(e.max()), "pixels_over_1e-3": int((e > 1e-3).sum()), "pixels_over_1e-2": int((e > 1e-2).sum()), "pixels": int(e.size),
+                    "p99.99_abs": float(np.quantile(e, 0.9999)),
+                    "worst": [{"xy": [int(i % W), int(i // W)], "gpu": [round(float(v), 5) for v in g.reshape(-1, 4)[i, :3]],
+                               "oracle": [round(float(v), 5) for v in o.reshape(-1, 4)[i, :3]]} for i in worst]}
         parity["frame"] = frame_parity(g_acc, o_acc)
         parity["frame"]["samples_gpu_vs_oracle"] = [tot["samples"], int(cst["samples"])]
         reps = int(min(200, max(1, round(12.0 / max(cdt, 1e-3)))))  # aim at ~12 s of CPU work
