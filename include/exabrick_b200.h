@@ -330,6 +330,8 @@ int exa_renderer_sync(exa_renderer_t *r);
 /* instrumentation of the last exa_renderer_render_stats frame: out[0] = most kd nodes touched by
  * one ray, out[1] = most samples taken by one ray (frame kernel), out[2] = kd nodes touched in total */
 int exa_renderer_debug_counters(exa_renderer_t *r, uint64_t out[4]);
+/* after exa_sample_points_stats: out[0] = kd steps below the location grid summed over the slowest lane of every warp (what
+ * the warps pay), out[1] = most steps by one point, out[2] = steps summed over all points */
 /* histogram of the last frame's per-tile (16x8 pixels) cost: counts[b] = tiles whose CTA ran for
  * [2^(b+10), 2^(b+11)) SM cycles (b = 15: or more).  The frame kernel schedules the next frame's
  * tiles in descending order of these buckets. */

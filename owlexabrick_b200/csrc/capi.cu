@@ -24,8 +24,7 @@ struct exa_renderer {
   ExaBrick *d_bricks = nullptr; int numBricks = 0;
   float *d_scalars = nullptr; uint64_t numCells = 0; int numFields = 0;
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
-  uint2 *d_locGrid = nullptr; int locG = 0; float locScale[3] = {0, 0, 0};              // point-location grid
-  int indexPrefetch = 1;                 // EXA_INDEX_PREFETCH=0 switches the L2 index prefetch of large point queries off
+  uint2 *d_locGrid = nullptr; int locG[3] = {0, 0, 0}; float locScale[3] = {0, 0, 0};   // point-location grid
   float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
@@ -89,7 +88,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   S.bricks = r->d_bricks; S.numBricks = r->numBricks; S.scalars = r->d_scalars; S.numCells = r->numCells; S.numFields = r->numFields;
   S.regions = r->abr.regions; S.numRegions = r->abr.numRegions; S.leafList = r->abr.leafList; S.leafListLen = r->abr.leafListLen;
   S.dual = r->d_dual; S.dualRecords = r->dualRecords;
-  S.locGrid = r->d_locGrid; S.locG = r->locG; for (int d = 0; d < 3; d++) S.locScale[d] = r->locScale[d];
+  S.locGrid = r->d_locGrid; for (int d = 0; d < 3; d++) { S.locG[d] = r->locG[d]; S.locScale[d] = r->locScale[d]; }
   S.kd = r->abr.kd; S.numKdNodes = r->abr.numKdNodes; S.kdDepth = r->abr.depth; S.blobs = r->abr.blobs;
   for (int d = 0; d < 3; d++) { S.boundsLo[d] = r->abr.boundsLo[d]; S.boundsHi[d] = r->abr.boundsHi[d]; }
   memcpy(P.camPos, r->fs.camera.pos, 12); memcpy(P.dir00, r->fs.camera.dir00, 12);
@@ -275,7 +274,6 @@ static int createImpl(const exa_bricks_t *bricks, const float *const *fields, co
   if (const char *e = getenv("EXA_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob: 32/64/128
   exa_renderer *r = new exa_renderer;
   r->device = cudaDevice;
-  if (const char *e = getenv("EXA_INDEX_PREFETCH")) r->indexPrefetch = atoi(e);
   memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
   identityXfm((float *)&r->fs.voxelSpaceTransform);
   r->fs.xfOpacityScale = 1.f; r->fs.ao.length = 1e20f; r->fs.ao.enabled = 0;
@@ -427,13 +425,21 @@ static int createImpl(const exa_bricks_t *bricks, const float *const *fields, co
   }
   r->launches += r->abr.launches;
   {
-    // point-location grid: ~32+ cells per region, 16^3 .. 128^3 (8 B per cell)
-    int G = 16; while (G < 128 && (double)G * G * G < 32.0 * r->abr.numRegions) G *= 2;
+    // point-location grid: roughly cubic cells (the domain need not be), ~32 per region, 4 K .. EXA_LOCGRID_CELLS (8 B each)
+    double maxCells = 2097152.0;
+    if (const char *e = getenv("EXA_LOCGRID_CELLS")) maxCells = std::max(4096.0, atof(e));
+    const double target = std::min(maxCells, std::max(4096.0, 32.0 * r->abr.numRegions));
+    double ext[3], vol = 1.0;
+    for (int d = 0; d < 3; d++) { ext[d] = std::max(1e-20, (double)r->abr.boundsHi[d] - (double)r->abr.boundsLo[d]); vol *= ext[d]; }
+    const double w = std::cbrt(vol / target);
+    int G[3];
+    for (int d = 0; d < 3; d++) G[d] = (int)std::min(2048.0, std::max(1.0, std::ceil(ext[d] / w)));
     if (!getenv("EXA_NO_LOCGRID")) {
-      CKC(cudaMalloc(&r->d_locGrid, sizeof(uint2) * (size_t)G * G * G));
+      CKC(cudaMalloc(&r->d_locGrid, sizeof(uint2) * (size_t)G[0] * G[1] * G[2]));
       if (launchBuildLocGrid(r->abr.kd, G, r->abr.boundsLo, r->abr.boundsHi, r->d_locGrid, r->locScale, s) < 0) {
         setError("point-location grid kernel failed"); exa_renderer_destroy(r); return EXA_ERR_CUDA; }
-      r->locG = G; r->launches++;
+      for (int d = 0; d < 3; d++) r->locG[d] = G[d];
+      r->launches++;
     }
   }
   const int nn = std::max(r->abr.numKdNodes, 1), nr = std::max(r->abr.numRegions, 1);

@@ -203,8 +203,6 @@ static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int ch
   CKR(cudaSetDevice(r->device));
   RenderParams RP; fillParams(r, RP);
   SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
-  // index prefetch pays when the query touches a good part of the grid / blobs anyway (one 32-B sector per point and hop)
-  P.blobUnits = r->abr.blobUnits; P.prefetchIndex = r->indexPrefetch && n * 32 >= (size_t)r->locG * r->locG * r->locG * 8 / 4;
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   const int k = launchSamplePoints(P, r->stream);
   if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }

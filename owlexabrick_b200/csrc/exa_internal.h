@@ -74,7 +74,7 @@ struct DeviceScene {
   float boundsLo[3], boundsHi[3];                           // root domain of the ABR tree
   // point-location grid: per cell the deepest kd node whose box contains the whole (slightly
   // grown) cell; a point query starts its descent there instead of at the root
-  const uint2 *locGrid; int locG; float locScale[3];
+  const uint2 *locGrid; int locG[3]; float locScale[3];       // locG[d] cells along axis d (cells are roughly cubic)
 };
 
 // result of the GPU ABR build (all device pointers owned by the caller afterwards)

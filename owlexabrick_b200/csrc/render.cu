@@ -491,8 +491,8 @@ static constexpr int SURF_THREADS = FRAME_THREADS;            // stride of the p
 
 template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
-                                                  float &value, float3 &g, unsigned &visits, unsigned &corners);
-__device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K);
+                                                  float &value, float3 &g, unsigned &visits, unsigned &corners, unsigned *kdSteps = nullptr);
+__device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K, unsigned *steps);
 
 // traceIsoRay (exabrick.cu:1408-1460): march the iso-active regions front to back with lattice
 // offset 0 until two consecutive valid samples bracket an enabled iso value.
@@ -789,7 +789,9 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, ow, d, tmin, tmax, true, sh, rs);
       surfT = sh.t;
       if (sh.prim != PRIM_NONE) {
-        surfHitT = sh.t;
+        // sort-last: an iso-surface hit lies inside THIS rank's part (everything behind the part is hidden); meshes, planes
+        // and cones are replicated, every rank finds the same hit and has clipped its own samples at it: marked by -t
+        surfHitT = sh.prim == PRIM_ISOSURFACE ? sh.t : -sh.t;
         const bool shade = sh.prim >= 0 || sh.prim == PRIM_STREAMLINE || sh.prim == PRIM_PLANE || (sh.prim == PRIM_ISOSURFACE && P.gradISO != 0);
         if (shade && len3(sh.Ng) > 0.f) {
           const int aoSamples = (SURF == 2 && P.aoEnabled) ? 2 : 0;
@@ -920,7 +922,7 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 // -----------------------------------------------------------------------------------------
 // point location + reconstruction at arbitrary points (one thread per point)
 // -----------------------------------------------------------------------------------------
-__device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K)
+__device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py, float pz, uint32_t &blobOfs, int &K, unsigned *steps)
 {
   // Regions are the half-open leaf boxes [lo,hi) of the kd-tree and tile its root box, so
   // "lo <= p < hi of the root" + a descent with (p < split -> left) finds the region with
@@ -931,11 +933,10 @@ __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py,
   if (S.locGrid) {
     // the grid cell holds a COPY of the deepest kd node that contains the whole cell: for most
     // cells that is already the leaf, and the query is one 8-byte load
-    const int G = S.locG;
-    const int cx = min(G - 1, (int)((px - S.boundsLo[0]) * S.locScale[0]));
-    const int cy = min(G - 1, (int)((py - S.boundsLo[1]) * S.locScale[1]));
-    const int cz = min(G - 1, (int)((pz - S.boundsLo[2]) * S.locScale[2]));
-    raw = __ldg(S.locGrid + cx + G * (cy + G * cz));
+    const int cx = min(S.locG[0] - 1, (int)((px - S.boundsLo[0]) * S.locScale[0]));
+    const int cy = min(S.locG[1] - 1, (int)((py - S.boundsLo[1]) * S.locScale[1]));
+    const int cz = min(S.locG[2] - 1, (int)((pz - S.boundsLo[2]) * S.locScale[2]));
+    raw = __ldg(S.locGrid + cx + (size_t)S.locG[0] * (cy + (size_t)S.locG[1] * cz));
   } else raw = __ldg(reinterpret_cast<const uint2 *>(S.kd));
   for (;;) {
     const uint32_t axis = raw.y >> 30, payload = raw.y & 0x3fffffffu;
@@ -945,16 +946,17 @@ __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py,
       return true;
     }
     const float p = axis == 0 ? px : axis == 1 ? py : pz;
+    if (steps) ++*steps;
     raw = __ldg(reinterpret_cast<const uint2 *>(S.kd) + payload + (p < __uint_as_float(raw.x) ? 0 : 1));
   }
 }
 
 template <bool GRAD, bool STATS, bool DUAL>
 __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px, float py, float pz, int channel,
-                                                  float &value, float3 &g, unsigned &visits, unsigned &corners)
+                                                  float &value, float3 &g, unsigned &visits, unsigned &corners, unsigned *kdSteps)
 {
   uint32_t bo; int K;
-  if (!locate(S, px, py, pz, bo, K)) return false;
+  if (!locate(S, px, py, pz, bo, K, STATS ? kdSteps : nullptr)) return false;
   Acc a; accZero(a);
   accumBricks<GRAD, STATS, DUAL>(a, ldg256(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
@@ -974,35 +976,17 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
 #define EXA_POINTS_PER_THREAD 1     // > 1: each thread runs that many independent locate -> header -> record chains, stage by stage
 #endif
 
-// Index structures of a point query (location grid, kd nodes, region blobs: 26 MB on C3) are read at random, one 32-B
-// sector per point and hop, and after a cold start every one of those sectors is a DRAM access of its own.  For a large
-// query the grid's first threads instead ask for them line by line (prefetch.global.L2, 128 B each, sequential
-// addresses: full-rate DRAM bursts); the dependent loads of the points then mostly hit L2.
-__device__ __forceinline__ void prefetchIndexToL2(const DeviceScene &S, size_t blobUnits, size_t t, size_t nThreads)
-{
-  const size_t gridLines = S.locGrid ? ((size_t)S.locG * S.locG * S.locG * sizeof(uint2) + 127) / 128 : 0;
-  const size_t kdLines = ((size_t)S.numKdNodes * sizeof(KdNode) + 127) / 128;
-  const size_t blobLines = (blobUnits * 16 + 127) / 128;
-  for (size_t l = t; l < gridLines + kdLines + blobLines; l += nThreads) {
-    const char *p = l < gridLines ? reinterpret_cast<const char *>(S.locGrid) + 128 * l
-                  : l < gridLines + kdLines ? reinterpret_cast<const char *>(S.kd) + 128 * (l - gridLines)
-                  : reinterpret_cast<const char *>(S.blobs) + 128 * (l - gridLines - kdLines);
-    asm volatile("prefetch.global.L2 [%0];" :: "l"(p));
-  }
-}
-
 template <bool GRAD, bool STATS, bool DUAL>
 __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_samplePoints(const __grid_constant__ SampleParams P)
 {
   constexpr int PPT = EXA_POINTS_PER_THREAD;
-  if (P.prefetchIndex) prefetchIndexToL2(P.scene, P.blobUnits, (size_t)blockIdx.x * blockDim.x + threadIdx.x, (size_t)gridDim.x * blockDim.x);
-  unsigned visits = 0, corners = 0, counted = 0;
+  unsigned visits = 0, corners = 0, counted = 0, kdSteps = 0;
   if (PPT == 1) {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < P.n) {
       const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
       float v = 0.f; float3 g = f3(0, 0, 0);
-      const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners);
+      const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners, &kdSteps);
       counted = visits > 0;
       if (P.values) P.values[i] = ok ? v : 0.f;
       if (P.valid) P.valid[i] = ok ? 1 : 0;
@@ -1020,7 +1004,7 @@ __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_sa
       if (in[j]) { px[j] = P.xyz[3 * i]; py[j] = P.xyz[3 * i + 1]; pz[j] = P.xyz[3 * i + 2]; }
     }
 #pragma unroll
-    for (int j = 0; j < PPT; j++) { bo[j] = 0; K[j] = 0; located[j] = in[j] && locate(P.scene, px[j], py[j], pz[j], bo[j], K[j]); }
+    for (int j = 0; j < PPT; j++) { bo[j] = 0; K[j] = 0; located[j] = in[j] && locate(P.scene, px[j], py[j], pz[j], bo[j], K[j], STATS ? &kdSteps : nullptr); }
 #pragma unroll
     for (int j = 0; j < PPT; j++) if (located[j]) hdr[j] = ldg256(P.scene.blobs + bo[j] + BLOB_HDR_UNITS);
 #pragma unroll
@@ -1043,6 +1027,11 @@ __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_sa
     unsigned long long a = counted, b = visits, c = corners;
     for (int o2 = 16; o2 > 0; o2 >>= 1) { a += __shfl_xor_sync(FULL, a, o2); b += __shfl_xor_sync(FULL, b, o2); c += __shfl_xor_sync(FULL, c, o2); }
     if ((threadIdx.x & 31) == 0) { atomicAdd(&P.stats[0], a); atomicAdd(&P.stats[1], b); atomicAdd(&P.stats[2], c); atomicAdd(&P.stats[3], a); }
+    // point location: kd steps below the location grid - total, most by one point, and the total a warp PAYS (its slowest lane)
+    unsigned wmax = kdSteps;
+    for (int o2 = 16; o2 > 0; o2 >>= 1) wmax = max(wmax, __shfl_xor_sync(FULL, wmax, o2));
+    atomicAdd(&P.stats[6], (unsigned long long)kdSteps); atomicMax(&P.stats[5], (unsigned long long)kdSteps);
+    if ((threadIdx.x & 31) == 0) atomicAdd(&P.stats[4], (unsigned long long)wmax);
   }
 }
 
@@ -1275,11 +1264,11 @@ int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellI
 // cell lies inside the grown box, so starting at the stored node gives exactly the leaf the
 // root descent would reach.
 // -----------------------------------------------------------------------------------------
-__global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, float loz, float wx, float wy, float wz, uint2 *grid)
+__global__ void k_buildLocGrid(const KdNode *kd, int gx, int gy, int gz, float lox, float loy, float loz, float wx, float wy, float wz, uint2 *grid)
 {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= G * G * G) return;
-  const int cx = c % G, cy = (c / G) % G, cz = c / (G * G);
+  const size_t c = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= (size_t)gx * gy * gz) return;
+  const int cx = (int)(c % gx), cy = (int)((c / gx) % gy), cz = (int)(c / ((size_t)gx * gy));
   const float lo[3] = {lox + ((float)cx - 0.01f) * wx, loy + ((float)cy - 0.01f) * wy, loz + ((float)cz - 0.01f) * wz};
   const float hi[3] = {lox + ((float)cx + 1.01f) * wx, loy + ((float)cy + 1.01f) * wy, loz + ((float)cz + 1.01f) * wz};
   int node = 0;
@@ -1295,11 +1284,12 @@ __global__ void k_buildLocGrid(const KdNode *kd, int G, float lox, float loy, fl
   grid[c] = reinterpret_cast<const uint2 *>(kd)[node];
 }
 
-int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s)
+int launchBuildLocGrid(const KdNode *kd, const int G[3], const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s)
 {
   float w[3];
-  for (int d = 0; d < 3; d++) { w[d] = (hi[d] - lo[d]) / (float)G; scaleOut[d] = (float)G / (hi[d] - lo[d]); }
-  k_buildLocGrid<<<(G * G * G + 255) / 256, 256, 0, s>>>(kd, G, lo[0], lo[1], lo[2], w[0], w[1], w[2], d_grid);
+  for (int d = 0; d < 3; d++) { w[d] = (hi[d] - lo[d]) / (float)G[d]; scaleOut[d] = (float)G[d] / (hi[d] - lo[d]); }
+  const size_t n = (size_t)G[0] * G[1] * G[2];
+  k_buildLocGrid<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(kd, G[0], G[1], G[2], lo[0], lo[1], lo[2], w[0], w[1], w[2], d_grid);
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
 }
 
@@ -1359,9 +1349,12 @@ __global__ void k_compositeFinish(const __grid_constant__ RenderParams P, const 
   for (int j = 0; j < EXA_MAX_PARTS; j++)                     // all loads in flight before the dependent chain
     if (j < C.n) q[j] = __ldcs(C.part[j] + pixelIdx);
   float4 pc = make_float4(0, 0, 0, 0);
+  int jStop = C.n - 1;                                        // last part that contributes: the first one with a surface hit of its own
+  if (C.hasSurf)
+    for (int j = 0; j < C.n; j++) { const float w = __ldcs(&C.surf[j][pixelIdx].w); if (w > 0.f && w < 1e30f) { jStop = j; break; } }
 #pragma unroll
   for (int j = 0; j < EXA_MAX_PARTS; j++) {
-    if (j >= C.n) break;
+    if (j >= C.n || j > jStop) break;
     float4 a = q[j];
     const bool term = a.w >= 2.f;
     if (term) a.w -= 2.f;
@@ -1371,10 +1364,15 @@ __global__ void k_compositeFinish(const __grid_constant__ RenderParams P, const 
   }
   float3 bg = f3(0, 0, 0);
   if (C.hasSurf) {
-    float tBest = 1e30f;
-    for (int j = 0; j < C.n; j++) {
+    // background = the nearest surface.  Parts are convex and ordered along the ray, so the first part (front to back) with
+    // a hit of its OWN (iso-surface, w = t > 0) holds the nearest one and hides every part behind it; a replicated surface
+    // (w = -t) is reported identically by all parts, which have clipped their samples at it themselves.
+    bool have = false;
+    for (int j = 0; j < C.n && j <= jStop; j++) {
       const float4 sv = __ldcs(C.surf[j] + pixelIdx);
-      if (sv.w < tBest) { tBest = sv.w; bg = f3(sv.x, sv.y, sv.z); }
+      if (sv.w >= 1e30f) continue;
+      if (sv.w > 0.f) { bg = f3(sv.x, sv.y, sv.z); break; }
+      if (!have) { bg = f3(sv.x, sv.y, sv.z); have = true; }
     }
   }
   float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)

@@ -82,7 +82,6 @@ struct SampleParams {
   const float *xyz; size_t n; int channel;
   float *values; uint8_t *valid; float *grad;
   unsigned long long *stats;
-  size_t blobUnits; int prefetchIndex;   // large query: stream the index structures into L2 first (render.cu:prefetchIndexToL2)
 };
 
 struct TraceParams {
@@ -107,7 +106,7 @@ int launchRegionActivity(const RenderParams &P, int numNodes, const int *kdParen
 int launchPartitionMask(const KdNode *kd, const std::vector<int> &levelOffset, int partRoot, uint8_t *inPart, cudaStream_t s);
 int launchGather(const float *d_field, size_t fieldCount, const int32_t *d_cellIDs, size_t numCells, float *d_out,
                  int *d_errFlag, cudaStream_t s);
-int launchBuildLocGrid(const KdNode *kd, int G, const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s);
+int launchBuildLocGrid(const KdNode *kd, const int G[3], const float lo[3], const float hi[3], uint2 *d_grid, float scaleOut[3], cudaStream_t s);
 int launchExpandDual(const ExaBrick *d_bricks, int numBricks, const uint32_t *d_dualBegin, uint64_t numRecords,
                      const float *d_scalars, float4 *d_dual, cudaStream_t s);
 int launchCompositeFinish(const RenderParams &P, const CompositeParams &C, cudaStream_t s);

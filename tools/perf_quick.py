@@ -57,6 +57,10 @@ def main():
     d_pts = torch.from_numpy(pts).cuda(); d_val = torch.empty(npts, dtype=torch.float32, device="cuda"); d_ok = torch.empty(npts, dtype=torch.uint8, device="cuda")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     pst = r.sample_points_stats(d_pts.data_ptr(), npts, 0)
+    import ctypes as C
+    dbg = (C.c_uint64 * 4)(); capi.check(capi.lib.exa_renderer_debug_counters(r.h, dbg))
+    out["points_locate"] = {"kd_steps_per_point": round(int(dbg[2]) / npts, 3), "max_kd_steps": int(dbg[1]), "kd_steps_paid_per_warp": round(int(dbg[0]) / (npts / 32), 2),
+                            "locgrid_cells": os.environ.get("EXA_LOCGRID_CELLS", "default 2M")}
     ts = []
     flush2 = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     for i in range(8):
