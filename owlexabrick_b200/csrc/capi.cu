@@ -81,6 +81,45 @@ static int g_scalarLayout = EXA_LAYOUT_AUTO;
 
 static void identityXfm(float m[12]) { memset(m, 0, 48); m[0] = m[4] = m[8] = 1.f; }
 
+// Pixel rectangle that contains every pixel whose primary ray can hit the scene bounds (the ABR root domain): the
+// projections of its 8 corners, grown by 2 pixels (sub-pixel jitter, rounding).  Conservative: the whole frame when the
+// camera is inside the box, a corner is not in front of it, or the camera basis is degenerate.  Tiles outside the
+// rectangle skip ray set-up and traversal and write the background directly (render.cu).
+static void sceneScreenRect(const exa_renderer *r, int rect[4])
+{
+  rect[0] = 0; rect[1] = 0; rect[2] = r->width - 1; rect[3] = r->height - 1;
+  const float *m = (const float *)&r->fs.voxelSpaceTransform;      // voxel = L * world + p  (columns vx, vy, vz)
+  const double L[9] = {m[0], m[3], m[6], m[1], m[4], m[7], m[2], m[5], m[8]};   // row-major
+  auto inv3 = [](const double A[9], double B[9]) {
+    const double c0 = A[4] * A[8] - A[5] * A[7], c1 = A[5] * A[6] - A[3] * A[8], c2 = A[3] * A[7] - A[4] * A[6];
+    const double det = A[0] * c0 + A[1] * c1 + A[2] * c2;
+    if (!(std::fabs(det) > 1e-300)) return false;
+    B[0] = c0 / det; B[1] = (A[2] * A[7] - A[1] * A[8]) / det; B[2] = (A[1] * A[5] - A[2] * A[4]) / det;
+    B[3] = c1 / det; B[4] = (A[0] * A[8] - A[2] * A[6]) / det; B[5] = (A[2] * A[3] - A[0] * A[5]) / det;
+    B[6] = c2 / det; B[7] = (A[1] * A[6] - A[0] * A[7]) / det; B[8] = (A[0] * A[4] - A[1] * A[3]) / det;
+    return true;
+  };
+  double Li[9], Mi[9];
+  const ExaFrameState &fs = r->fs;
+  const double M[9] = {fs.camera.dir00[0], fs.camera.dirDu[0], fs.camera.dirDv[0], fs.camera.dir00[1], fs.camera.dirDu[1], fs.camera.dirDv[1],
+                       fs.camera.dir00[2], fs.camera.dirDu[2], fs.camera.dirDv[2]};
+  if (!inv3(L, Li) || !inv3(M, Mi)) return;
+  double lo[2] = {1e300, 1e300}, hi[2] = {-1e300, -1e300};
+  for (int c = 0; c < 8; c++) {
+    const double v[3] = {(c & 1 ? r->abr.boundsHi[0] : r->abr.boundsLo[0]) - (double)m[9], (c & 2 ? r->abr.boundsHi[1] : r->abr.boundsLo[1]) - (double)m[10],
+                         (c & 4 ? r->abr.boundsHi[2] : r->abr.boundsLo[2]) - (double)m[11]};
+    double q[3];
+    for (int k = 0; k < 3; k++) q[k] = Li[3 * k] * v[0] + Li[3 * k + 1] * v[1] + Li[3 * k + 2] * v[2] - fs.camera.pos[k];
+    const double a = Mi[0] * q[0] + Mi[1] * q[1] + Mi[2] * q[2], b = Mi[3] * q[0] + Mi[4] * q[1] + Mi[5] * q[2], d = Mi[6] * q[0] + Mi[7] * q[1] + Mi[8] * q[2];
+    if (!(a > 1e-6 * (std::fabs(b) + std::fabs(d)) && a > 0.0)) return;       // corner beside / behind the camera: no bound
+    lo[0] = std::min(lo[0], b / a); hi[0] = std::max(hi[0], b / a); lo[1] = std::min(lo[1], d / a); hi[1] = std::max(hi[1], d / a);
+  }
+  if (!(lo[0] <= hi[0]) || !std::isfinite(lo[0]) || !std::isfinite(hi[0]) || !std::isfinite(lo[1]) || !std::isfinite(hi[1])) return;
+  auto clampi = [](double x, int a, int b) { return (int)std::min((double)b, std::max((double)a, x)); };
+  rect[0] = clampi(std::floor(lo[0]) - 3.0, 0, r->width); rect[1] = clampi(std::floor(lo[1]) - 3.0, 0, r->height);
+  rect[2] = clampi(std::ceil(hi[0]) + 2.0, -1, r->width - 1); rect[3] = clampi(std::ceil(hi[1]) + 2.0, -1, r->height - 1);
+}
+
 static void fillParams(exa_renderer *r, RenderParams &P)
 {
   memset(&P, 0, sizeof(P));
@@ -118,6 +157,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.ertThreshold = r->ert;
   P.volActive = r->d_volActive; P.isoActive = r->d_isoActive; P.regionActive = r->d_regionActive;
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
+  sceneScreenRect(r, P.sceneRect);
   P.numStrips = r->numStrips; for (int k = 0; k < r->numStrips; k++) P.strip[k] = r->strips[k];
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
@@ -426,9 +466,8 @@ static int createImpl(const exa_bricks_t *bricks, const float *const *fields, co
   r->launches += r->abr.launches;
   {
     // point-location grid: roughly cubic cells (the domain need not be), ~32 per region, 4 K .. EXA_LOCGRID_CELLS (8 B each)
-    double maxCells = 2097152.0;
-    if (const char *e = getenv("EXA_LOCGRID_CELLS")) maxCells = std::max(4096.0, atof(e));
-    const double target = std::min(maxCells, std::max(4096.0, 32.0 * r->abr.numRegions));
+    double target = std::min(2097152.0, std::max(4096.0, 32.0 * r->abr.numRegions));
+    if (const char *e = getenv("EXA_LOCGRID_CELLS")) target = std::max(4096.0, atof(e));        // experiment knob: exact cell budget
     double ext[3], vol = 1.0;
     for (int d = 0; d < 3; d++) { ext[d] = std::max(1e-20, (double)r->abr.boundsHi[d] - (double)r->abr.boundsLo[d]); vol *= ext[d]; }
     const double w = std::cbrt(vol / target);

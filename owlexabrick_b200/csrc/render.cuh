@@ -18,6 +18,7 @@ struct RenderParams {
   DeviceScene scene;
   // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
   float camPos[3], dir00[3], dirDu[3], dirDv[3];
+  int sceneRect[4];                    // pixel rectangle (x0, y0, x1, y1 inclusive) outside which no primary ray can hit the scene bounds (host: projected corners, grown)
   float camVoxel[3];                   // voxelSpaceTransform applied to camPos (host, same rounding as the device's xfmPoint): origin of every primary ray in voxel space
   float xfm[12];                       // voxelSpaceTransform: vx, vy, vz, p
   int width, height, frameID;

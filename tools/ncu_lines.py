@@ -18,14 +18,18 @@ def launches(rep):
     h = None
     line = None
     fname = ""
+    pending_file = ""
     for r in csv.reader(out.splitlines()):
         if len(r) == 2 and r[0] in ("File Path", "File Name"):
             fname = r[1].split("/")[-1]
+            pending_file = r[1]
             continue
         if len(r) == 2 and r[0] == "Function Name":
-            if cur is None or cur["name"] != r[1] or cur.get("closed"):
-                cur = {"name": r[1], "lines": {}}
+            # a launch lists each of its source files once: a repeated file (or another function) starts the next launch
+            if cur is None or cur["name"] != r[1] or pending_file in cur["files"]:
+                cur = {"name": r[1], "lines": {}, "files": set()}
                 res.append(cur)
+            cur["files"].add(pending_file)
             continue
         if len(r) > 8 and r[0] == "Line No":
             h = r
