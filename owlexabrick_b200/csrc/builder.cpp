@@ -27,7 +27,7 @@
 namespace exa {
 
 struct BricksImpl;
-BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, std::vector<int32_t> &&ids, std::vector<ExaKdTreeNode> &&kd);
+BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, IdVector &&ids, std::vector<ExaKdTreeNode> &&kd);
 
 namespace {
 
@@ -40,7 +40,7 @@ static const size_t PAR_THRESHOLD = 1u << 16;
 
 struct Builder {
   int builderType, maxLeafWidth;
-  std::vector<ExaBrick> hdr; std::vector<int32_t> ids; std::vector<ExaKdTreeNode> tree;
+  std::vector<ExaBrick> hdr; IdVector ids; std::vector<ExaKdTreeNode> tree;
 
   // ---- duplicate removal (builder.cpp:301-350) ----
   static inline uint64_t hashCell(const int32_t *c)

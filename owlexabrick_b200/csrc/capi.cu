@@ -10,6 +10,7 @@
 #include <cstring>
 #include <random>
 #include <string>
+#include <omp.h>
 
 using namespace exa;
 
@@ -26,6 +27,7 @@ struct exa_renderer {
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
   uint2 *d_locGrid = nullptr; int locG[3] = {0, 0, 0}; float locScale[3] = {0, 0, 0};   // point-location grid
   float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
+  int pointsQueue = -1;                  // point queries: -1 auto (persistent-lane kernel from 1024 points on), 0 / 1 force (EXA_POINTS_QUEUE)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
   float voxelLo[3], voxelHi[3], worldLo[3], worldHi[3];
@@ -65,6 +67,9 @@ struct exa_renderer {
   int *d_coneStart = nullptr, *d_coneCursor = nullptr, *d_coneList = nullptr; size_t coneListCap = 0; bool coneGridValid = false;
   float coneLo[3] = {0, 0, 0}, coneCell[3] = {1, 1, 1};                                  // uniform grid over the visible cones (buildConeGrid)
   unsigned long long *d_stats = nullptr;
+  // exa_sample_points_host: two sets of pinned / device staging buffers for STAGE_POINTS points each
+  static constexpr size_t STAGE_POINTS = 262144;
+  char *h_stage[2] = {nullptr, nullptr}, *d_stage[2] = {nullptr, nullptr}; cudaEvent_t evStage[2] = {nullptr, nullptr};
   // tile cost order, double buffered (render.cuh:TileOrder); valid once a frame has written it
   TileOrder *d_tileOrder[2] = {nullptr, nullptr}; int tileOrderCap = 0, tileOrderCur = 0; bool tileOrderValid = false;
 };
@@ -314,6 +319,7 @@ static int createImpl(const exa_bricks_t *bricks, const float *const *fields, co
   if (const char *e = getenv("EXA_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob: 32/64/128
   exa_renderer *r = new exa_renderer;
   r->device = cudaDevice;
+  if (const char *e = getenv("EXA_POINTS_QUEUE")) r->pointsQueue = atoi(e);
   memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
   identityXfm((float *)&r->fs.voxelSpaceTransform);
   r->fs.xfOpacityScale = 1.f; r->fs.ao.length = 1e20f; r->fs.ao.enabled = 0;
@@ -547,6 +553,7 @@ void exa_renderer_destroy(exa_renderer_t *r)
   for (int i = 0; i < 2; i++) if (r->evCopied[i]) cudaEventDestroy(r->evCopied[i]);
   for (int i = 0; i < 8; i++) if (r->evXf[i]) cudaEventDestroy(r->evXf[i]);
   if (r->h_xfRing) cudaFreeHost(r->h_xfRing);
+  for (int i = 0; i < 2; i++) { if (r->h_stage[i]) cudaFreeHost(r->h_stage[i]); cudaFree(r->d_stage[i]); if (r->evStage[i]) cudaEventDestroy(r->evStage[i]); }
   cudaFree(r->d_traces); cudaFree(r->d_traceBounds); cudaFree(r->d_coneStart); cudaFree(r->d_coneCursor); cudaFree(r->d_coneList); cudaFree(r->d_meshNodes); cudaFree(r->d_meshTris); cudaFree(r->d_stats); cudaFree(r->d_tileOrder[0]); cudaFree(r->d_tileOrder[1]); cudaFree(r->d_tileList); cudaFree(r->d_tileCost);
   delete r;
 }

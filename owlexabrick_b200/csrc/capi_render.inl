@@ -203,6 +203,7 @@ static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int ch
   CKR(cudaSetDevice(r->device));
   RenderParams RP; fillParams(r, RP);
   SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
+  P.queue = r->pointsQueue == 1 || (r->pointsQueue < 0 && n >= 1024);
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   const int k = launchSamplePoints(P, r->stream);
   if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
@@ -225,26 +226,59 @@ int exa_sample_points_stats(exa_renderer_t *r, const float *d_xyz, size_t n, int
   return samplePointsDev(r, d_xyz, n, channel, nullptr, nullptr, nullptr, stats);
 }
 
+// Host buffers in, host buffers out.  The caller's arrays are pageable, so the query is cut into chunks that travel
+// through two sets of pinned staging buffers owned by the renderer: while chunk c is copied up, sampled and copied
+// down by the GPU, the host copies chunk c+1 into the other staging set and chunk c-1 out of it (all cores).
+static void hostCopyParallel(void *dst, const void *src, size_t n)
+{
+  if (n < (1u << 20)) { memcpy(dst, src, n); return; }
+  const int T = std::max(1, std::min(omp_get_max_threads(), 16));
+#pragma omp parallel for num_threads(T) schedule(static)
+  for (int t = 0; t < T; t++) { const size_t b0 = n * t / T, e0 = n * (t + 1) / T; memcpy((char *)dst + b0, (const char *)src + b0, e0 - b0); }
+}
+
 int exa_sample_points_host(exa_renderer_t *r, const float *xyz, size_t n, int channel, float *values, uint8_t *valid, float *grad)
 {
   if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
   if (n == 0) return EXA_OK;
   if (!xyz || !values || !valid) { setError("sample_points: null argument"); return EXA_ERR_INVALID; }
+  if (channel < 0 || channel >= r->numFields) { setError("sample_points: channel out of range"); return EXA_ERR_INVALID; }
   CKR(cudaSetDevice(r->device));
-  float *d_xyz = nullptr, *d_val = nullptr, *d_grad = nullptr; uint8_t *d_ok = nullptr;
-  int rc = EXA_OK;
-  cudaError_t e;
-  if ((e = cudaMalloc(&d_xyz, n * 12)) != cudaSuccess || (e = cudaMalloc(&d_val, n * 4)) != cudaSuccess || (e = cudaMalloc(&d_ok, n)) != cudaSuccess ||
-      (grad && (e = cudaMalloc(&d_grad, n * 12)) != cudaSuccess)) { setError(std::string("CUDA error: ") + cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
-  if (!rc && (e = cudaMemcpyAsync(d_xyz, xyz, n * 12, cudaMemcpyHostToDevice, r->stream)) != cudaSuccess) { setError(cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
-  if (!rc) rc = samplePointsDev(r, d_xyz, n, channel, d_val, d_ok, d_grad, nullptr);
-  if (!rc) {
-    cudaMemcpyAsync(values, d_val, n * 4, cudaMemcpyDeviceToHost, r->stream);
-    cudaMemcpyAsync(valid, d_ok, n, cudaMemcpyDeviceToHost, r->stream);
-    if (grad) cudaMemcpyAsync(grad, d_grad, n * 12, cudaMemcpyDeviceToHost, r->stream);
-    if ((e = cudaStreamSynchronize(r->stream)) != cudaSuccess) { setError(std::string("CUDA error: ") + cudaGetErrorString(e)); rc = EXA_ERR_CUDA; }
+  const size_t CH = exa_renderer::STAGE_POINTS;
+  if (!r->h_stage[0]) {
+    // per set: xyz (12 B) + value (4) + gradient (12) + valid (1) per point, device and pinned host
+    for (int b = 0; b < 2; b++) {
+      CKR(cudaMallocHost(&r->h_stage[b], CH * 29)); CKR(cudaMalloc(&r->d_stage[b], CH * 29));
+      CKR(cudaEventCreateWithFlags(&r->evStage[b], cudaEventDisableTiming));
+    }
   }
-  cudaFree(d_xyz); cudaFree(d_val); cudaFree(d_ok); cudaFree(d_grad);
+  auto hx = [&](int b) { return (float *)r->h_stage[b]; };        auto dx = [&](int b) { return (float *)r->d_stage[b]; };
+  auto hv = [&](int b) { return (float *)(r->h_stage[b] + CH * 12); }; auto dv = [&](int b) { return (float *)(r->d_stage[b] + CH * 12); };
+  auto hg = [&](int b) { return (float *)(r->h_stage[b] + CH * 16); }; auto dg = [&](int b) { return (float *)(r->d_stage[b] + CH * 16); };
+  auto ho = [&](int b) { return (uint8_t *)(r->h_stage[b] + CH * 28); }; auto dok = [&](int b) { return (uint8_t *)(r->d_stage[b] + CH * 28); };
+  auto drain = [&](size_t off, size_t cnt, int b) -> int {          // chunk finished on the device: pinned -> caller's arrays
+    CKR(cudaEventSynchronize(r->evStage[b]));
+    hostCopyParallel(values + off, hv(b), cnt * 4); hostCopyParallel(valid + off, ho(b), cnt);
+    if (grad) hostCopyParallel(grad + 3 * off, hg(b), cnt * 12);
+    return EXA_OK;
+  };
+  size_t prevOff = 0, prevCnt = 0; int c = 0, rc = EXA_OK;
+  for (size_t off = 0; off < n && !rc; off += CH, c++) {
+    const size_t cnt = std::min(CH, n - off); const int b = c & 1;
+    if (c >= 2) { /* set b was drained when chunk c-1 was enqueued */ }
+    hostCopyParallel(hx(b), xyz + 3 * off, cnt * 12);
+    CKR(cudaMemcpyAsync(dx(b), hx(b), cnt * 12, cudaMemcpyHostToDevice, r->stream));
+    rc = samplePointsDev(r, dx(b), cnt, channel, dv(b), dok(b), grad ? dg(b) : nullptr, nullptr);
+    if (rc) break;
+    CKR(cudaMemcpyAsync(hv(b), dv(b), cnt * 4, cudaMemcpyDeviceToHost, r->stream));
+    CKR(cudaMemcpyAsync(ho(b), dok(b), cnt, cudaMemcpyDeviceToHost, r->stream));
+    if (grad) CKR(cudaMemcpyAsync(hg(b), dg(b), cnt * 12, cudaMemcpyDeviceToHost, r->stream));
+    CKR(cudaEventRecord(r->evStage[b], r->stream));
+    if (c >= 1) rc = drain(prevOff, prevCnt, b ^ 1);                // overlaps the GPU's work on chunk c
+    prevOff = off; prevCnt = cnt;
+  }
+  if (!rc && c >= 1) rc = drain(prevOff, prevCnt, (c - 1) & 1);
+  if (rc) cudaStreamSynchronize(r->stream);
   return rc;
 }
 

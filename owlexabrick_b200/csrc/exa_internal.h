@@ -4,6 +4,8 @@
 #include <cstddef>
 #include <string>
 #include <vector>
+#include <memory>
+#include <utility>
 #include "../../include/exabrick_b200.h"
 
 static_assert(sizeof(ExaBrick) == 32, "programs/Brick.h layout");
@@ -32,6 +34,17 @@ static_assert(offsetof(ExaLaunchParams, volumeBVH) == 8 && offsetof(ExaLaunchPar
 namespace exa {
 
 void setError(const std::string &msg);
+
+// std::vector whose resize(n) leaves new elements uninitialised (cell-ID arrays of billions of entries are written
+// right afterwards, in parallel; value-initialising them first is a serial page-fault pass over gigabytes)
+template <typename T> struct DefaultInitAllocator : std::allocator<T> {
+  template <typename U> struct rebind { typedef DefaultInitAllocator<U> other; };
+  DefaultInitAllocator() = default;
+  template <typename U> DefaultInitAllocator(const DefaultInitAllocator<U> &) {}
+  template <typename U> void construct(U *p) { ::new (static_cast<void *>(p)) U; }
+  template <typename U, typename... A> void construct(U *p, A &&...a) { ::new (static_cast<void *>(p)) U(std::forward<A>(a)...); }
+};
+typedef std::vector<int32_t, DefaultInitAllocator<int32_t>> IdVector;
 
 // ---- traversal kd-tree over the ABRs (the tree Regions.cpp builds and throws away) -----
 // inner: split plane + axis + index of the left child (right = left+1)

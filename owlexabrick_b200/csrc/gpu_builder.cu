@@ -27,7 +27,7 @@
 namespace exa {
 
 struct BricksImpl;
-BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, std::vector<int32_t> &&ids, std::vector<ExaKdTreeNode> &&kd);
+BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, IdVector &&ids, std::vector<ExaKdTreeNode> &&kd);
 
 namespace {
 
@@ -69,9 +69,9 @@ __device__ __forceinline__ bool sameCell(int4 a, int4 b) { return a.x == b.x && 
 
 // ---- duplicate removal (builder.cpp:301-350): every cell enters the hash set; a slot is owned by one (lower, level) key and
 // holds the smallest index that carries it
-__global__ void k_dedupInsert(const int4 *__restrict__ cells, unsigned long long n, int *table, unsigned long long mask, int *badLevel)
+__global__ void k_dedupInsert(const int4 *__restrict__ cells, unsigned long long first, unsigned long long n, int *table, unsigned long long mask, int *badLevel)
 {
-  const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long i = first + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   const int4 c = cells[i];
   if (c.w < 0 || c.w > 30) { *badLevel = 1; return; }
@@ -286,6 +286,46 @@ __global__ void __launch_bounds__(BT) k_leafScatter(const Work *__restrict__ wor
   }
 }
 
+// Host <-> device transfers of pageable arrays of gigabytes through two pinned staging buffers: the host-side memcpy of
+// chunk c+1 (all cores, which is also the parallel first touch of a fresh destination) overlaps the DMA of chunk c.
+struct Staging {
+  static constexpr size_t CHUNK_BYTES = 64u << 20;
+  char *buf[2] = {nullptr, nullptr}; cudaEvent_t ev[2] = {nullptr, nullptr};
+  Staging() { for (int i = 0; i < 2; i++) { GCK(cudaMallocHost(&buf[i], CHUNK_BYTES)); GCK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming)); } }
+  ~Staging() { for (int i = 0; i < 2; i++) { if (buf[i]) cudaFreeHost(buf[i]); if (ev[i]) cudaEventDestroy(ev[i]); } }
+  static void parallelCopy(char *dst, const char *src, size_t n)
+  {
+    const int T = std::max(1, std::min(omp_get_max_threads(), 16));
+#pragma omp parallel for num_threads(T) schedule(static)
+    for (int t = 0; t < T; t++) { const size_t b = n * t / T, e = n * (t + 1) / T; memcpy(dst + b, src + b, e - b); }
+  }
+  // afterChunk(firstByte, bytes) is called once the chunk's copy is enqueued (stream-ordered work on that range)
+  template <typename F> void upload(char *dDst, const char *hSrc, size_t bytes, cudaStream_t s, F afterChunk)
+  {
+    size_t c = 0;
+    for (size_t off = 0; off < bytes; off += CHUNK_BYTES, c++) {
+      const size_t n = std::min(CHUNK_BYTES, bytes - off); const int b = (int)(c & 1);
+      GCK(cudaEventSynchronize(ev[b]));                              // the DMA that last read this buffer is done
+      parallelCopy(buf[b], hSrc + off, n);
+      GCK(cudaMemcpyAsync(dDst + off, buf[b], n, cudaMemcpyHostToDevice, s));
+      GCK(cudaEventRecord(ev[b], s));
+      afterChunk(off, n);
+    }
+  }
+  void download(char *hDst, const char *dSrc, size_t bytes, cudaStream_t s)
+  {
+    size_t c = 0, prevOff = 0, prevN = 0;
+    for (size_t off = 0; off < bytes; off += CHUNK_BYTES, c++) {
+      const size_t n = std::min(CHUNK_BYTES, bytes - off); const int b = (int)(c & 1);
+      GCK(cudaMemcpyAsync(buf[b], dSrc + off, n, cudaMemcpyDeviceToHost, s));
+      GCK(cudaEventRecord(ev[b], s));
+      if (c) { GCK(cudaEventSynchronize(ev[b ^ 1])); parallelCopy(hDst + prevOff, buf[b ^ 1], prevN); }
+      prevOff = off; prevN = n;
+    }
+    if (c) { GCK(cudaEventSynchronize(ev[(c - 1) & 1])); parallelCopy(hDst + prevOff, buf[(c - 1) & 1], prevN); }
+  }
+};
+
 inline unsigned blocksFor(unsigned long long n, int t = 256) { return (unsigned)((n + t - 1) / t); }
 inline double nowS() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
@@ -303,22 +343,27 @@ BricksImpl *buildBricksGpu(const int32_t *cells, size_t numCells, int builderTyp
   cudaStream_t s = nullptr;
   const double tStart = nowS();
   double tm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  std::vector<ExaBrick> hdr; std::vector<int32_t> ids; std::vector<ExaKdTreeNode> kd;
+  std::vector<ExaBrick> hdr; IdVector ids; std::vector<ExaKdTreeNode> kd;
   kd.push_back(ExaKdTreeNode{0, 0, 0});
   if (numCells == 0) { if (timings) memcpy(timings, tm, sizeof(tm)); return bricksFromParts(std::move(hdr), std::move(ids), std::move(kd)); }
 
   // ---- upload + duplicate removal ----
+  Staging staging;
   Dev<int4> recCell[2]; Dev<int> recId[2];
   unsigned long long n = 0;
   {
     Dev<int4> dCells; Dev<int> table, bad; Dev<unsigned long long> counter;
     dCells.reserve(numCells);
-    GCK(cudaMemcpy(dCells.p, cells, numCells * 16, cudaMemcpyHostToDevice));
-    tm[0] = nowS() - tStart;
     unsigned long long cap = 1; while (cap < 2 * (unsigned long long)numCells + 16) cap <<= 1;
     table.reserve(cap); bad.reserve(1); counter.reserve(1);
     GCK(cudaMemsetAsync(table.p, 0xff, cap * 4, s)); GCK(cudaMemsetAsync(bad.p, 0, 4, s)); GCK(cudaMemsetAsync(counter.p, 0, 8, s));
-    k_dedupInsert<<<blocksFor(numCells), 256, 0, s>>>(dCells.p, numCells, table.p, cap - 1, bad.p);
+    // the cells go up in chunks through pinned staging; every chunk enters the hash set as soon as it has arrived
+    staging.upload(reinterpret_cast<char *>(dCells.p), reinterpret_cast<const char *>(cells), numCells * 16, s, [&](size_t off, size_t bytes) {
+      const unsigned long long i0 = off / 16, i1 = i0 + bytes / 16;
+      k_dedupInsert<<<blocksFor(i1 - i0), 256, 0, s>>>(dCells.p, i0, i1, table.p, cap - 1, bad.p);
+    });
+    GCK(cudaStreamSynchronize(s));
+    tm[0] = nowS() - tStart;
     recCell[0].reserve(numCells); recId[0].reserve(numCells);
     k_dedupCompact<<<blocksFor(numCells), 256, 0, s>>>(dCells.p, numCells, table.p, cap - 1, recCell[0].p, recId[0].p, counter.p);
     int hBad = 0;
@@ -492,8 +537,7 @@ BricksImpl *buildBricksGpu(const int32_t *cells, size_t numCells, int builderTyp
     GCK(cudaMemcpyAsync(dWork.p, work.data(), work.size() * sizeof(Work), cudaMemcpyHostToDevice, s));
     k_leafScatter<<<(unsigned)work.size(), BT, 0, s>>>(dWork.p, dLeaves.p, recCell[0].p, recId[0].p, recCell[1].p, recId[1].p, dIds.p);
     GCK(cudaGetLastError());
-    GCK(cudaMemcpyAsync(ids.data(), dIds.p, total * 4, cudaMemcpyDeviceToHost, s));
-    GCK(cudaStreamSynchronize(s));
+    staging.download(reinterpret_cast<char *>(ids.data()), reinterpret_cast<const char *>(dIds.p), total * 4, s);
   }
   tm[3] = nowS() - tOut; tm[4] = nowS() - tStart;
   if (timings) memcpy(timings, tm, sizeof(tm));

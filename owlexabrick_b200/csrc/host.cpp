@@ -19,10 +19,10 @@ void setError(const std::string &msg) { g_lastError = msg; }
 
 struct BricksImpl {
   std::vector<ExaBrick> hdr;          // flattened headers, begin = running cell offset
-  std::vector<int32_t> ids;           // indexVector
+  IdVector ids;                       // indexVector
   std::vector<ExaKdTreeNode> kd;      // builder kd-tree (empty when loaded from file)
 };
-BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, std::vector<int32_t> &&ids, std::vector<ExaKdTreeNode> &&kd)
+BricksImpl *bricksFromParts(std::vector<ExaBrick> &&hdr, IdVector &&ids, std::vector<ExaKdTreeNode> &&kd)
 {
   BricksImpl *b = new BricksImpl; b->hdr = std::move(hdr); b->ids = std::move(ids); b->kd = std::move(kd); return b;
 }

@@ -19,6 +19,7 @@ def main():
     ap.add_argument("--tag", default="base")
     ap.add_argument("--steps", type=int, default=10)
     a = ap.parse_args()
+    a.workload = os.environ.get("PQ_WORKLOAD", a.workload)
     import torch
     import bench
     from owlexabrick_b200 import capi, renderer as R, synth
@@ -73,6 +74,11 @@ def main():
     pb = 16 * npts + 44 * pst["segments"] + 36 * pst["brickVisits"] + 4 * pst["cornerLoads"]
     out["points"] = {"us": round(1e3 * float(np.mean(ts)), 2), "alg_GBs": round(pb / np.mean(ts) / 1e6, 1), "visits_per_pt": round(pst["brickVisits"] / npts, 3), "corners_per_pt": round(pst["cornerLoads"] / npts, 3)}
     out["checksum"] = float(d_val.double().sum().item())
+    r.sample_points(pts, 0)                                          # host buffers in and out (first call allocates the staging)
+    t = time.perf_counter()
+    for _ in range(5): hv, hok = r.sample_points(pts, 0)
+    hs = (time.perf_counter() - t) / 5
+    out["points_host"] = {"ms": round(hs * 1e3, 3), "Gsamples_s": round(npts / hs / 1e9, 3), "equals_device": bool(np.array_equal(hv, d_val.cpu().numpy()))}
     if os.environ.get("PQ_DIAG"):
         # diagnostics: (a) points confined to a 128^3 box (data L2-resident), (b) the same random points sorted along x-major cells
         def run(p_np):
