@@ -27,7 +27,6 @@ struct exa_renderer {
   unsigned *d_scalarOffsets = nullptr; int *d_primaryChannels = nullptr;
   uint2 *d_locGrid = nullptr; int locG[3] = {0, 0, 0}; float locScale[3] = {0, 0, 0};   // point-location grid
   float4 *d_dual = nullptr; uint64_t dualRecords = 0; uint32_t *d_dualBegin = nullptr;   // dual-cell records (render.cu:k_expandDual)
-  int pointsQueue = -1;                  // point queries: -1 auto (persistent-lane kernel from 1024 points on), 0 / 1 force (EXA_POINTS_QUEUE)
   AbrResult abr;
   std::vector<KdNode> h_kd;              // host copy (partitioning decisions)
   float voxelLo[3], voxelHi[3], worldLo[3], worldHi[3];
@@ -319,7 +318,6 @@ static int createImpl(const exa_bricks_t *bricks, const float *const *fields, co
   if (const char *e = getenv("EXA_L2_FETCH")) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));   // experiment knob: 32/64/128
   exa_renderer *r = new exa_renderer;
   r->device = cudaDevice;
-  if (const char *e = getenv("EXA_POINTS_QUEUE")) r->pointsQueue = atoi(e);
   memset(&r->fs, 0, sizeof(r->fs)); memset(&r->lp, 0, sizeof(r->lp));
   identityXfm((float *)&r->fs.voxelSpaceTransform);
   r->fs.xfOpacityScale = 1.f; r->fs.ao.length = 1e20f; r->fs.ao.enabled = 0;

@@ -203,7 +203,6 @@ static int samplePointsDev(exa_renderer *r, const float *d_xyz, size_t n, int ch
   CKR(cudaSetDevice(r->device));
   RenderParams RP; fillParams(r, RP);
   SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_values; P.valid = d_valid; P.grad = d_grad; P.stats = nullptr;
-  P.queue = r->pointsQueue == 1 || (r->pointsQueue < 0 && n >= 1024);
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   const int k = launchSamplePoints(P, r->stream);
   if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }

@@ -1044,176 +1044,16 @@ __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_sa
   }
 }
 
-// -----------------------------------------------------------------------------------------
-// k_samplePointsQ: the same point query with PERSISTENT LANES.  One thread per point (k_samplePoints) makes a warp pay for
-// its slowest lane: on C3 a point needs 1.8 kd steps below the location grid on average, but the slowest of 32 random
-// points needs 12, so every warp sits through ~15 dependent loads while most lanes idle (ncu: 45 % of the warp
-// instructions at 4-7 active lanes, 46 % of the stall samples inside the descent loop).  Here a warp owns a chunk of
-// points staged in shared memory with coalesced loads, and each LANE walks its own chain
-//     grid cell -> kd node(s) -> brick header -> dual-cell record [-> next header -> record ...]
-// one dependent load per trip of the warp's loop: every trip each busy lane consumes the load it issued in the previous
-// trip and issues the next one, a lane whose point is finished takes the next point of the chunk (ballot-ranked, no
-// atomics).  The warp now pays the AVERAGE chain length of its points, and 32 independent loads are in flight per trip.
-// Same arithmetic as k_samplePoints (accumBricks): results are bit-identical on the dual-cell layout.
-// -----------------------------------------------------------------------------------------
-#ifndef EXA_PQ_PER_LANE
-#define EXA_PQ_PER_LANE 8
-#endif
-static constexpr int PQ_THREADS = 128, PQ_CHUNK = 32 * EXA_PQ_PER_LANE;
-
-// one brick visit of addBasisFunctions on a dual-cell record that is already in registers (same expressions as accumBricks)
-template <bool GRAD, bool STATS>
-__device__ __forceinline__ void accumRecord(Acc &a, const U8 &hdr, const U8 &q, float px, float py, float pz, unsigned &nCorners)
-{
-  const uint4 u0 = hdr.lo, u1 = hdr.hi;
-  const float invCw = __uint_as_float(u0.w);
-  const int sx = (int)u1.x, sy = (int)u1.y, sz = (int)u1.z;
-  const float lx = (px - __uint_as_float(u0.x)) * invCw - 0.5f;
-  const float ly = (py - __uint_as_float(u0.y)) * invCw - 0.5f;
-  const float lz = (pz - __uint_as_float(u0.z)) * invCw - 0.5f;
-  const int ix0 = max(-1, (int)floorf(lx)), iy0 = max(-1, (int)floorf(ly)), iz0 = max(-1, (int)floorf(lz));
-  const float fx = lx - (float)ix0, fy = ly - (float)iy0, fz = lz - (float)iz0;
-  const bool x0 = ix0 >= 0 && ix0 < sx, x1 = ix0 + 1 < sx;
-  const bool y0 = iy0 >= 0 && iy0 < sy, y1 = iy0 + 1 < sy;
-  const bool z0 = iz0 >= 0 && iz0 < sz, z1 = iz0 + 1 < sz;
-  const float s000 = __uint_as_float(q.lo.x), s001 = __uint_as_float(q.lo.y), s010 = __uint_as_float(q.lo.z), s011 = __uint_as_float(q.lo.w);
-  const float s100 = __uint_as_float(q.hi.x), s101 = __uint_as_float(q.hi.y), s110 = __uint_as_float(q.hi.z), s111 = __uint_as_float(q.hi.w);
-  if (STATS) nCorners += ((int)z0 + (int)z1) * ((int)y0 + (int)y1) * ((int)x0 + (int)x1);
-  const float wx0 = x0 ? 1.f - fx : 0.f, wx1 = x1 ? fx : 0.f;
-  const float wy0 = y0 ? 1.f - fy : 0.f, wy1 = y1 ? fy : 0.f;
-  const float wz0 = z0 ? 1.f - fz : 0.f, wz1 = z1 ? fz : 0.f;
-  const float X00 = wx0 * s000 + wx1 * s001, X01 = wx0 * s010 + wx1 * s011;
-  const float X10 = wx0 * s100 + wx1 * s101, X11 = wx0 * s110 + wx1 * s111;
-  const float Y0 = wy0 * X00 + wy1 * X01, Y1 = wy0 * X10 + wy1 * X11;
-  const float wsx = wx0 + wx1, wsy = wy0 + wy1, wsz = wz0 + wz1;
-  a.swv += wz0 * Y0 + wz1 * Y1;
-  a.sw += (wsz * wsy) * wsx;
-  if (GRAD) {
-    const float D00 = s001 - s000, D01 = s011 - s010, D10 = s101 - s100, D11 = s111 - s110;
-    a.sd.x += wz0 * (wy0 * D00 + wy1 * D01) + wz1 * (wy0 * D10 + wy1 * D11);
-    a.sd.y += wz0 * (X01 - X00) + wz1 * (X11 - X10);
-    a.sd.z += Y1 - Y0;
-    a.sdc.x += (wsz * wsy) * ((x1 ? 1.f : 0.f) - (x0 ? 1.f : 0.f));
-    a.sdc.y += (wsz * wsx) * ((y1 ? 1.f : 0.f) - (y0 ? 1.f : 0.f));
-    a.sdc.z += (wsy * wsx) * ((z1 ? 1.f : 0.f) - (z0 ? 1.f : 0.f));
-  }
-}
-
-template <bool GRAD, bool STATS>
-__global__ void __launch_bounds__(PQ_THREADS, GRAD ? 8 : 10) k_samplePointsQ(const __grid_constant__ SampleParams P)
-{
-  __shared__ float sxyz[PQ_THREADS / 32][PQ_CHUNK * 3];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const size_t base = ((size_t)blockIdx.x * (PQ_THREADS / 32) + warp) * PQ_CHUNK;
-  if (base >= P.n) return;                                   // whole warps leave; nothing below synchronises the block
-  const int nw = (int)min((size_t)PQ_CHUNK, P.n - base);
-  float *xyz = sxyz[warp];
-  for (int i = lane; i < 3 * nw; i += 32) xyz[i] = P.xyz[3 * base + i];
-  __syncwarp();
-  const DeviceScene &S = P.scene;
-  const float4 *chan = reinterpret_cast<const float4 *>(chanBase<true>(S, P.channel));
-  enum { IDLE = 0, LOC = 1, HDR = 2, REC = 3, DONE = 4 };
-  int state = IDLE, idx = 0, K = 0, brick = 0, next = 0;
-  uint32_t bo = 0;
-  float px = 0.f, py = 0.f, pz = 0.f;
-  Acc a; accZero(a);
-  U8 hdr, pend;                                              // pend: the load in flight (kd node in lo.x/lo.y, header, or record)
-  hdr.lo = hdr.hi = pend.lo = pend.hi = make_uint4(0, 0, 0, 0);
-  bool haveRec = false;
-  unsigned visits = 0, corners = 0, counted = 0, kdSteps = 0;
-  auto finish = [&](bool located) {
-    float v = 0.f; float3 g = f3(0, 0, 0);
-    const bool ok = located && accFinish<GRAD>(a, v, g);
-    const size_t i = base + idx;
-    if (P.values) P.values[i] = ok ? v : 0.f;
-    if (P.valid) P.valid[i] = ok ? 1 : 0;
-    if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
-    state = IDLE;
-  };
-  for (;;) {
-    // ---- 1. consume the load issued in the previous trip, issue the next one of this lane's chain
-    if (state == LOC) {
-      const uint32_t axis = pend.lo.y >> 30, payload = pend.lo.y & 0x3fffffffu;
-      if (axis == 3) {
-        if (payload == KD_EMPTY) finish(false);             // a hole of the domain
-        else {
-          bo = payload; K = (int)pend.lo.x; brick = 0;
-          if (STATS) { visits += K; counted++; }
-          pend = ldg256(S.blobs + bo + BLOB_HDR_UNITS); state = HDR;
-        }
-      } else {
-        const float p = axis == 0 ? px : axis == 1 ? py : pz;
-        if (STATS) kdSteps++;
-        const uint2 r2 = __ldg(reinterpret_cast<const uint2 *>(S.kd) + payload + (p < __uint_as_float(pend.lo.x) ? 0 : 1));
-        pend.lo.x = r2.x; pend.lo.y = r2.y;
-      }
-    } else if (state == HDR) {
-      hdr = pend;
-      const float invCw = __uint_as_float(hdr.lo.w);
-      const int sx = (int)hdr.hi.x, sy = (int)hdr.hi.y, sz = (int)hdr.hi.z;
-      const int ix0 = max(-1, (int)floorf((px - __uint_as_float(hdr.lo.x)) * invCw - 0.5f));
-      const int iy0 = max(-1, (int)floorf((py - __uint_as_float(hdr.lo.y)) * invCw - 0.5f));
-      const int iz0 = max(-1, (int)floorf((pz - __uint_as_float(hdr.lo.z)) * invCw - 0.5f));
-      haveRec = ix0 < sx && iy0 < sy && iz0 < sz;
-      if (haveRec) {
-        const int rx = sx + 1, ry = sy + 1;
-        pend = ldg256(chan + 2 * ((size_t)hdr.hi.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry))));
-      } else pend.lo = pend.hi = make_uint4(0, 0, 0, 0);
-      state = REC;
-    } else if (state == REC) {
-      accumRecord<GRAD, STATS>(a, hdr, pend, px, py, pz, corners);
-      if (++brick < K) { pend = ldg256(S.blobs + bo + BLOB_HDR_UNITS + 2 * brick); state = HDR; }
-      else finish(true);
-    }
-    // ---- 2. lanes without a point take the next ones of the chunk
-    const bool want = state == IDLE;
-    const unsigned m = __ballot_sync(FULL, want);
-    if (m) {
-      const int my = next + __popc(m & ((1u << lane) - 1u));
-      next += __popc(m);
-      if (want) {
-        if (my < nw) {
-          idx = my; px = xyz[3 * my]; py = xyz[3 * my + 1]; pz = xyz[3 * my + 2];
-          accZero(a);
-          if (!(px >= S.boundsLo[0] && px < S.boundsHi[0] && py >= S.boundsLo[1] && py < S.boundsHi[1] && pz >= S.boundsLo[2] && pz < S.boundsHi[2]))
-            finish(false);                                   // outside (or NaN): invalid, the lane asks again next trip
-          else {
-            uint2 raw;
-            if (S.locGrid) {
-              const int cx = min(S.locG[0] - 1, (int)((px - S.boundsLo[0]) * S.locScale[0]));
-              const int cy = min(S.locG[1] - 1, (int)((py - S.boundsLo[1]) * S.locScale[1]));
-              const int cz = min(S.locG[2] - 1, (int)((pz - S.boundsLo[2]) * S.locScale[2]));
-              raw = __ldg(S.locGrid + cx + (size_t)S.locG[0] * (cy + (size_t)S.locG[1] * cz));
-            } else raw = __ldg(reinterpret_cast<const uint2 *>(S.kd));
-            pend.lo.x = raw.x; pend.lo.y = raw.y; state = LOC;
-          }
-        } else state = DONE;
-      }
-    }
-    if (__all_sync(FULL, state == DONE)) break;
-  }
-  if (STATS && P.stats) {
-    unsigned long long sa = counted, sb = visits, sc = corners;
-    unsigned wmax = kdSteps;
-    for (int o2 = 16; o2 > 0; o2 >>= 1) {
-      sa += __shfl_xor_sync(FULL, sa, o2); sb += __shfl_xor_sync(FULL, sb, o2); sc += __shfl_xor_sync(FULL, sc, o2);
-      wmax = max(wmax, __shfl_xor_sync(FULL, wmax, o2));
-    }
-    atomicAdd(&P.stats[6], (unsigned long long)kdSteps);
-    if (lane == 0) { atomicAdd(&P.stats[0], sa); atomicAdd(&P.stats[1], sb); atomicAdd(&P.stats[2], sc); atomicAdd(&P.stats[3], sa); atomicAdd(&P.stats[4], (unsigned long long)wmax); }
-  }
-}
+// Tried and removed (round 2, profiles/perf_quick_r02_{f,g}_points_*.json): a persistent-lane variant (a warp owns a chunk of
+// points in shared memory, every lane walks its own grid -> kd -> header -> record chain one dependent load per trip and takes
+// the next point when done).  It cut the kd steps a warp pays from 11.9 to 3.5 per point but ran 1 M random points on C3 in
+// 93-109 us (1 / 2 / 4 / 8 points per lane) against 50 us here: the query is bound by random 32-B DRAM sectors, not by the
+// descent's divergence.
 
 int launchSamplePoints(const SampleParams &P, cudaStream_t s)
 {
   if (P.n == 0) return 0;
   const bool stats = P.stats != nullptr;
-  if (P.queue && P.scene.dual) {                             // persistent lanes (dual-cell records only)
-    const unsigned grid = (unsigned)((P.n + (size_t)(PQ_THREADS / 32) * PQ_CHUNK - 1) / ((size_t)(PQ_THREADS / 32) * PQ_CHUNK));
-    if (P.grad) { if (stats) k_samplePointsQ<true, true><<<grid, PQ_THREADS, 0, s>>>(P); else k_samplePointsQ<true, false><<<grid, PQ_THREADS, 0, s>>>(P); }
-    else { if (stats) k_samplePointsQ<false, true><<<grid, PQ_THREADS, 0, s>>>(P); else k_samplePointsQ<false, false><<<grid, PQ_THREADS, 0, s>>>(P); }
-    return cudaGetLastError() == cudaSuccess ? 1 : -1;
-  }
   const size_t perBlock = (size_t)EXA_POINTS_THREADS * EXA_POINTS_PER_THREAD;
   const unsigned grid = (unsigned)((P.n + perBlock - 1) / perBlock);
 #define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); }

@@ -83,7 +83,6 @@ struct SampleParams {
   const float *xyz; size_t n; int channel;
   float *values; uint8_t *valid; float *grad;
   unsigned long long *stats;
-  int queue;                           // persistent-lane kernel (render.cu:k_samplePointsQ) instead of one thread per point
 };
 
 struct TraceParams {
