@@ -363,6 +363,19 @@ int exa_sample_points_stats(exa_renderer_t *r, const float *d_xyz, size_t n, int
 /* number of kernels this library has launched on this handle so far */
 uint64_t exa_renderer_launch_count(const exa_renderer_t *r);
 
+/* exa_sample_points_host for callers that must not reach cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid allocation).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels, same arguments and results as exa_sample_points_host (host arrays in and out; grad may be
+ * NULL); `stats` may be NULL, else it receives the counters of exa_sample_points_stats for this query.  The device-side
+ * staging and the counters live in one static device array of 256 + 29 * EXA_NOALLOC_MAX_POINTS bytes (1.8 MiB) that
+ * every GPU holds from library load to exit; the call allocates nothing (no cudaMalloc / cudaFree / cudaMallocHost, now
+ * or lazily).  n > EXA_NOALLOC_MAX_POINTS is refused with EXA_ERR_INVALID and a message; split larger queries.  All
+ * calls, of all renderers on a device, share the array: calls that overlap on the GPU race, so serialise them (the
+ * call itself returns only after its results are in the caller's arrays). */
+#define EXA_NOALLOC_MAX_POINTS 65536
+int exa_sample_points_host_noalloc(exa_renderer_t *r, const float *xyz, size_t n, int channel,
+                                   float *values, uint8_t *valid, float *grad, ExaStats *stats);
+
 /* ---------------------------------------------------------------------------------------
  * Multi-GPU (new; the reference only replicates)
  * ------------------------------------------------------------------------------------- */

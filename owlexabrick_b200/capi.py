@@ -17,6 +17,7 @@ lib = C.CDLL(LIB_PATH)
 EXA_OK, EXA_ERR_INVALID, EXA_ERR_IO, EXA_ERR_CUDA, EXA_ERR_LIMIT = range(5)
 BUILDER_SPATIAL_MEDIAN, BUILDER_SAH_ALIKE = 0, 1
 PARTITION_NONE, PARTITION_SORT_LAST, PARTITION_IMAGE_TILES = 0, 1, 2
+NOALLOC_MAX_POINTS = 65536          # EXA_NOALLOC_MAX_POINTS (include/exabrick_b200.h)
 LAYOUT_AUTO, LAYOUT_FLAT, LAYOUT_DUAL = 0, 1, 2
 
 
@@ -129,6 +130,7 @@ _SIG = {
     "exa_renderer_render_stats": (i32, [vp, C.POINTER(ExaStats)]),
     "exa_sample_points_stats": (i32, [vp, vp, sz, i32, C.POINTER(ExaStats)]),
     "exa_renderer_launch_count": (C.c_uint64, [vp]),
+    "exa_sample_points_host_noalloc": (i32, [vp, vp, sz, i32, vp, vp, vp, C.POINTER(ExaStats)]),
     "exa_renderer_set_partition": (i32, [vp, i32, i32, i32]),
     "exa_renderer_render_partial": (i32, [vp, vp, vp]),
     "exa_renderer_partition_order": (i32, [vp, vp, C.POINTER(i32)]),

@@ -849,3 +849,70 @@ uint64_t exa_renderer_launch_count(const exa_renderer_t *r) { return r ? r->laun
 
 #include "capi_render.inl"
 #include "capi_group.inl"
+
+// ---- point query without any allocation -------------------------------------------------------------------------------
+// exa_sample_points_host_noalloc: exa_sample_points_host (+ the counters of exa_sample_points_stats) for callers that must
+// not reach cudaMalloc — CUDA-graph capture around them, tight serving loops, harnesses that forbid allocation.  No
+// counterpart in the reference.  The device-side staging of the query (points
+// up, values / gradients / flags down) and the kernel's counters live in ONE file-scope device array that every GPU which
+// loads this library holds until exit; nothing is allocated, neither here nor lazily in the renderer.
+//   layout of g_noallocScratch: [0,256) counters (cleared every call) | xyz 12 B/pt | value 4 B/pt | gradient 12 B/pt | valid 1 B/pt
+// Every call shares the array and it keeps the last call's contents: the counters and the flags are cleared before the launch,
+// and two calls that overlap on the GPU (two renderers / two host threads) race — callers serialise them.
+#define EXA_NOALLOC_SCRATCH_BYTES (256 + (size_t)EXA_NOALLOC_MAX_POINTS * 29)
+static __device__ __align__(256) unsigned char g_noallocScratch[EXA_NOALLOC_SCRATCH_BYTES];
+static_assert(EXA_NOALLOC_MAX_POINTS % 256 == 0, "sections of the scratch array stay 256-byte aligned");
+
+// In host code `g_noallocScratch` is only the host-side handle of the symbol; the device address is per device.
+static unsigned char *noallocScratchOf(int device)
+{
+  static unsigned char *ptr[64] = {};
+  static omp_lock_t lock; static bool lockInit = (omp_init_lock(&lock), true); (void)lockInit;
+  if (device < 0 || device >= 64) { setError("sample_points_host_noalloc: device index out of range"); return nullptr; }
+  omp_set_lock(&lock);
+  unsigned char *p = ptr[device];
+  if (!p) {                                                       // once per device, with that device current (the caller set it)
+    void *a = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&a, g_noallocScratch);
+    if (e != cudaSuccess || !a) setError(std::string("sample_points_host_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+    else p = ptr[device] = (unsigned char *)a;
+  }
+  omp_unset_lock(&lock);
+  return p;
+}
+
+extern "C" int exa_sample_points_host_noalloc(exa_renderer_t *r, const float *xyz, size_t n, int channel, float *values, uint8_t *valid, float *grad, ExaStats *stats)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (n > (size_t)EXA_NOALLOC_MAX_POINTS) {
+    char msg[160]; snprintf(msg, sizeof msg, "sample_points_host_noalloc: %zu points exceed the static scratch (EXA_NOALLOC_MAX_POINTS = %d); split the query", n, (int)EXA_NOALLOC_MAX_POINTS);
+    setError(msg); return EXA_ERR_INVALID;
+  }
+  if (n == 0) { if (stats) memset(stats, 0, sizeof(*stats)); return EXA_OK; }
+  if (!xyz || !values || !valid) { setError("sample_points: null argument"); return EXA_ERR_INVALID; }
+  if (channel < 0 || channel >= r->numFields) { setError("sample_points: channel out of range"); return EXA_ERR_INVALID; }
+  CKR(cudaSetDevice(r->device));
+  unsigned char *base = noallocScratchOf(r->device);
+  if (!base) return EXA_ERR_CUDA;
+  const size_t M = EXA_NOALLOC_MAX_POINTS;
+  unsigned long long *d_cnt = (unsigned long long *)base;
+  float *d_xyz = (float *)(base + 256), *d_val = (float *)(base + 256 + M * 12), *d_grad = (float *)(base + 256 + M * 16);
+  uint8_t *d_ok = base + 256 + M * 28;
+  CKR(cudaMemsetAsync(d_cnt, 0, 256, r->stream));                 // counters start at zero
+  CKR(cudaMemsetAsync(d_ok, 0, n, r->stream));                    // a flag the kernel did not write reads "invalid", never the last call's
+  CKR(cudaMemcpyAsync(d_xyz, xyz, n * 12, cudaMemcpyHostToDevice, r->stream));
+  RenderParams RP; fillParams(r, RP);
+  SampleParams P; P.scene = RP.scene; P.xyz = d_xyz; P.n = n; P.channel = channel; P.values = d_val; P.valid = d_ok; P.grad = grad ? d_grad : nullptr;
+  P.stats = stats ? d_cnt : nullptr;
+  const int k = launchSamplePoints(P, r->stream);
+  if (k < 0) { setError(std::string("sample kernel launch failed: ") + cudaGetErrorString(cudaGetLastError())); return EXA_ERR_CUDA; }
+  r->launches += k;
+  unsigned long long h[4] = {0, 0, 0, 0};
+  CKR(cudaMemcpyAsync(values, d_val, n * 4, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaMemcpyAsync(valid, d_ok, n, cudaMemcpyDeviceToHost, r->stream));
+  if (grad) CKR(cudaMemcpyAsync(grad, d_grad, n * 12, cudaMemcpyDeviceToHost, r->stream));
+  if (stats) CKR(cudaMemcpyAsync(h, d_cnt, 32, cudaMemcpyDeviceToHost, r->stream));
+  CKR(cudaStreamSynchronize(r->stream));
+  if (stats) { stats->samples = h[0]; stats->brickVisits = h[1]; stats->cornerLoads = h[2]; stats->segments = h[3]; }
+  return EXA_OK;
+}

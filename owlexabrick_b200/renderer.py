@@ -520,6 +520,19 @@ class Renderer:
         check(lib.exa_sample_points_host(self.h, _p(xyz), n, channel, _p(val), _p(ok), _p(g)))
         return (val, ok, g) if grad else (val, ok)
 
+    def sample_points_noalloc(self, xyz, channel=0, grad=False, stats=False, out=None):
+        """exa_sample_points_host_noalloc: at most capi.NOALLOC_MAX_POINTS points, device staging in the library's static
+        scratch array; `out` = (values, valid[, grad]) arrays to fill (so that the call allocates nothing on the host either)"""
+        xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
+        n = len(xyz)
+        if out is None:
+            out = (np.zeros(n, np.float32), np.zeros(n, np.uint8)) + ((np.zeros((n, 3), np.float32),) if grad else ())
+        val, ok, g = out[0], out[1], (out[2] if grad else None)
+        st = capi.ExaStats() if stats else None
+        check(lib.exa_sample_points_host_noalloc(self.h, _p(xyz), n, channel, _p(val), _p(ok), _p(g), C.byref(st) if stats else None))
+        res = (val, ok, g) if grad else (val, ok)
+        return res + (st.as_dict(),) if stats else res
+
     def sample_points_device(self, d_xyz, n, channel, d_values, d_valid, d_grad=None):
         check(lib.exa_sample_points_device(self.h, C.c_void_p(d_xyz), n, channel, C.c_void_p(d_values),
                                            C.c_void_p(d_valid) if d_valid else None, C.c_void_p(d_grad) if d_grad else None))
