@@ -34,8 +34,24 @@ def _stale(out, deps):
 
 
 def build_lib(force=False, verbose=False):
+    """Compile what is stale and link.  Safe to call from several processes at once (the ranks of a torchrun job all
+    import the package): an exclusive file lock serialises the builders, and every output is written under a temporary
+    name and renamed into place, so a process that loads the library meanwhile sees a complete file."""
+    import fcntl
     os.makedirs(OBJ, exist_ok=True)
     hdrs = [os.path.join(CSRC, h) for h in HEADERS]
+
+    def run(cmd, out):
+        tmp = "%s.tmp%d" % (out, os.getpid())
+        cmd = [tmp if a == out else a for a in cmd]
+        if verbose:
+            print(" ".join(cmd))
+        try:
+            subprocess.check_call(cmd)
+            os.replace(tmp, out)
+        finally:
+            if os.path.exists(tmp):
+                os.unlink(tmp)
 
     def compile_one(src):
         s = os.path.join(CSRC, src)
@@ -44,18 +60,18 @@ def build_lib(force=False, verbose=False):
             cmd = [NVCC] + ARCH + COMMON + ["-c", s, "-o", o]
             if src.endswith(".cpp"):
                 cmd = [NVCC] + COMMON + ["-x", "cu", "-c", s, "-o", o] + ARCH
-            if verbose:
-                print(" ".join(cmd))
-            subprocess.check_call(cmd)
+            run(cmd, o)
         return o
 
-    with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
-        objs = list(ex.map(compile_one, SOURCES))
-    if force or _stale(LIB, objs):
-        cmd = [NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-Xcompiler", "-fopenmp", "-lgomp"]
-        if verbose:
-            print(" ".join(cmd))
-        subprocess.check_call(cmd)
+    with open(os.path.join(OBJ, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
+                objs = list(ex.map(compile_one, SOURCES))
+            if force or _stale(LIB, objs):
+                run([NVCC] + ARCH + ["-shared", "-o", LIB] + objs + ["-Xcompiler", "-fopenmp", "-lgomp"], LIB)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
     return LIB
 
 
