@@ -465,7 +465,8 @@ def run_product(args):
             # data replicated; the frame is N row strips, strip k on GPU k: every rank's frame kernel stores its tiles into
             # the strips over NVLink (peer pointers), a peer-memory barrier orders "frame complete", and rank k reads strip k
             # back over its own PCIe link into a pinned host frame shared by the ranks (owlexabrick_b200/multigpu.py)
-            pipe = multigpu.TilePipeline(dist, torch, capi, np, r, rank, world, local, W, H, stream, nccl_barrier=args.nccl_barrier, tag=tag)
+            pipe = multigpu.TilePipeline(dist, torch, capi, np, r, rank, world, local, W, H, stream, nccl_barrier=args.nccl_barrier, tag=tag, weighted=not args.uniform_strips)
+            log("rank %d: strips %s rows, copy bandwidth per rank %s GB/s" % (rank, pipe.rows, [round(x, 1) for x in pipe.copy_gbs]))
         else:
             # sort-last with the DATA partitioned: a second renderer that holds only this rank's kd subtree
             sl_r = R.Renderer(bricks, [field], device=local, part=(rank, world))
@@ -859,7 +860,8 @@ def run_product(args):
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
                         "h2d_bytes_per_step": (128 * 16 + 48) * world, "d2h_bytes_per_step": W * H * 4,
                         "d2h_bytes_per_step_per_rank": (W * H * 4) if world == 1 else pipe.d2h_bytes,
-                        "d2h_copy_alone_ms": d2h_ms, "diagnostics": e2e_diag, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory" + (" (exa_renderer_read_rgba8_async)" if world == 1 else
+                        "d2h_copy_alone_ms": d2h_ms, "diagnostics": e2e_diag,
+                        "strip_rows": getattr(pipe, "rows", None), "d2h_gbs_per_rank_all_copying": [round(x, 1) for x in pipe.copy_gbs] if hasattr(pipe, "copy_gbs") else None, "pipeline": "frame i+1 renders while frame i is copied to pinned host memory" + (" (exa_renderer_read_rgba8_async)" if world == 1 else
                                      ": every rank copies its own strip / span over its own PCIe link into one pinned host frame shared by the ranks (POSIX shared memory, scan-line layout)")},
                 "gpu_launches": int(lib_launches), "clocks": clocks,
                 "roofline": {"bound": "hbm", "kernel": "k_renderFrame", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -891,6 +893,7 @@ def main():
     ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around warm-up + timed steps (for ncu --profile-from-start off)")
     ap.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce per frame instead of the peer-memory barrier kernel")
+    ap.add_argument("--uniform-strips", action="store_true", help="N>1 image tiles: equal frame strips instead of strips sized by each GPU's measured copy bandwidth")
     ap.add_argument("--static-tiles", action="store_true", help="N>1 image tiles: keep the static round-robin deal (no cost-balanced tile lists)")
     ap.add_argument("--no-sortlast", action="store_true", help="N>1: skip the secondary sort-last measurement")
     ap.add_argument("--partition", default="tiles", choices=["tiles", "sortlast"], help="multi-GPU mode (N>1)")

@@ -274,6 +274,10 @@ int exa_renderer_set_color_buffer(exa_renderer_t *r, void *fbPointer);
  * frame is filled by N concurrent copies.  numStrips = 0: back to the single colour buffer. */
 int exa_renderer_set_color_strips(exa_renderer_t *r, void *const *stripPtrs, int numStrips);
 int exa_strip_rows(int k, int numStrips, int height, int *y0, int *y1);
+/* the same with caller-chosen strips: strip k = pixel rows [firstRow[k], firstRow[k+1]) (numStrips + 1 entries: multiples
+ * of 8 ascending from 0, the last = the frame height; empty strips allowed).  For hosts whose GPUs do not reach host
+ * memory equally fast (shared PCIe uplinks): strips sized by each GPU's measured copy bandwidth finish together. */
+int exa_renderer_set_color_strips_rows(exa_renderer_t *r, void *const *stripPtrs, const int *firstRow, int numStrips);
 int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3],
                                const float dirDu[3], const float dirDv[3]);          /* :357-368 */
 /* updateXF(chan, opacities[128], colorMap[128] rgb, domain, opacityScale) (:370-404) */

@@ -139,6 +139,7 @@ _SIG = {
     "exa_renderer_get_residency": (i32, [vp, C.POINTER(i32), C.POINTER(C.c_uint64)]),
     "exa_renderer_get_build_times": (i32, [vp, vp]),
     "exa_renderer_set_color_strips": (i32, [vp, vp, i32]),
+    "exa_renderer_set_color_strips_rows": (i32, [vp, vp, vp, i32]),
     "exa_renderer_enable_tile_costs": (i32, [vp, i32]),
     "exa_renderer_get_tile_costs": (i32, [vp, vp, i32]),
     "exa_renderer_set_tile_list": (i32, [vp, vp, i32]),

@@ -40,7 +40,7 @@ struct exa_renderer {
   // framebuffer
   int width = 0, height = 0;
   float4 *d_accum = nullptr; uint32_t *d_rgba8 = nullptr; bool ownRgba8 = false;
-  uint32_t *strips[EXA_MAX_PARTS] = {}; int numStrips = 0;   // exa_renderer_set_color_strips
+  uint32_t *strips[EXA_MAX_PARTS] = {}; int numStrips = 0; int stripRow[EXA_MAX_PARTS + 1] = {};   // exa_renderer_set_color_strips[_rows]
   uint32_t *d_tileList = nullptr; int tileListLen = 0; size_t tileListCap = 0;   // exa_renderer_set_tile_list (balanced image tiles)
   uint32_t *d_tileCost = nullptr; int tileCostLen = 0;
   // pipelined read-back (exa_renderer_read_rgba8_async): second renderer-owned RGBA8 buffer, copy stream
@@ -163,6 +163,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
   sceneScreenRect(r, P.sceneRect);
   P.numStrips = r->numStrips; for (int k = 0; k < r->numStrips; k++) P.strip[k] = r->strips[k];
+  for (int k = 0; k <= r->numStrips; k++) P.stripRow[k] = r->stripRow[k];
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;
   // streamline cones: segment k is drawn while k < currentTimestep-1 (exabrick.cu:532-545); the device
   // copy of the time step stops at numTimesteps (OptixRenderer.cpp:481-484)
@@ -659,6 +660,7 @@ int exa_renderer_resize_framebuffer(exa_renderer_t *r, void *fbPointer, int widt
   r->width = width; r->height = height;
   for (int i = 0; i < 2; i++) { cudaFree(r->d_tileOrder[i]); r->d_tileOrder[i] = nullptr; }
   cudaFree(r->d_tileCost); r->d_tileCost = nullptr; r->tileCostLen = 0; r->tileListLen = 0;    // tile ids of the old size are meaningless
+  r->numStrips = 0;                                           // so are strips laid out for the old height
   r->tileOrderCap = ((width + 15) / 16) * ((height + 7) / 8); r->tileOrderValid = false;
   if (!getenv("EXA_NO_TILE_ORDER"))
     for (int i = 0; i < 2; i++) CKR(cudaMalloc(&r->d_tileOrder[i], sizeof(TileOrder) + sizeof(uint32_t) * (size_t)TILE_BUCKETS * r->tileOrderCap));
@@ -684,17 +686,31 @@ int exa_strip_rows(int k, int numStrips, int height, int *y0, int *y1)
   return EXA_OK;
 }
 
-int exa_renderer_set_color_strips(exa_renderer_t *r, void *const *stripPtrs, int numStrips)
+int exa_renderer_set_color_strips_rows(exa_renderer_t *r, void *const *stripPtrs, const int *firstRow, int numStrips)
 {
   if (!r || !r->d_accum) { setError("set_color_strips: resizeFrameBuffer was never called"); return EXA_ERR_INVALID; }
-  if (numStrips < 0 || numStrips > EXA_MAX_PARTS || (numStrips && !stripPtrs)) { setError("set_color_strips: 0..16 strips"); return EXA_ERR_INVALID; }
+  if (numStrips < 0 || numStrips > EXA_MAX_PARTS || (numStrips && (!stripPtrs || !firstRow))) { setError("set_color_strips: 0..16 strips"); return EXA_ERR_INVALID; }
+  // strip k = pixel rows [firstRow[k], firstRow[k+1]): whole 8-row tile rows, ascending, covering the frame
   for (int k = 0; k < numStrips; k++) {
-    int y0, y1; exa_strip_rows(k, numStrips, r->height, &y0, &y1);
-    if (!stripPtrs[k] && y1 > y0) { setError("set_color_strips: null strip"); return EXA_ERR_INVALID; }
-    r->strips[k] = (uint32_t *)stripPtrs[k];
+    const bool last = k == numStrips - 1;
+    if ((firstRow[k] % 8 != 0 && firstRow[k] != r->height) || firstRow[k] > firstRow[k + 1] || (k == 0 && firstRow[0] != 0) || (last && firstRow[k + 1] != r->height) || (!last && firstRow[k + 1] > r->height)) {
+      setError("set_color_strips: strip rows must start at multiples of 8, ascend from 0 and end at the frame height"); return EXA_ERR_INVALID;
+    }
+    if (!stripPtrs[k] && firstRow[k + 1] > firstRow[k]) { setError("set_color_strips: null strip"); return EXA_ERR_INVALID; }
   }
+  for (int k = 0; k < numStrips; k++) { r->strips[k] = (uint32_t *)stripPtrs[k]; r->stripRow[k] = (firstRow[k] + 7) / 8; }
+  r->stripRow[numStrips] = numStrips ? (r->height + 7) / 8 : 0;
   r->numStrips = numStrips;
   return EXA_OK;
+}
+
+int exa_renderer_set_color_strips(exa_renderer_t *r, void *const *stripPtrs, int numStrips)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  if (numStrips < 0 || numStrips > EXA_MAX_PARTS) { setError("set_color_strips: 0..16 strips"); return EXA_ERR_INVALID; }
+  int rows[EXA_MAX_PARTS + 1] = {0};
+  for (int k = 0; k < numStrips; k++) { int y0; exa_strip_rows(k, numStrips, std::max(r->height, 1), &y0, &rows[k + 1]); }
+  return exa_renderer_set_color_strips_rows(r, stripPtrs, rows, numStrips);
 }
 
 int exa_renderer_update_camera(exa_renderer_t *r, const float pos[3], const float dir00[3], const float dirDu[3], const float dirDv[3])

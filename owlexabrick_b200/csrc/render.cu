@@ -679,10 +679,10 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
   color = f3(linear_to_srgb(color.x / inv), linear_to_srgb(color.y / inv), linear_to_srgb(color.z / inv));
   if (P.numStrips > 0) {
     // frame distributed as row strips over the GPUs: store into the strip that holds this pixel's tile row
-    const int tileRows = (P.height + 7) >> 3, tr = (pixelIdx / P.width) >> 3;
-    const int k = ((tr + 1) * P.numStrips - 1) / tileRows;
-    const int y0 = ((tileRows * k) / P.numStrips) << 3;
-    P.strip[k][pixelIdx - y0 * P.width] = make_rgba8(color);
+    const int tr = (pixelIdx / P.width) >> 3;
+    int k = 0;
+    while (tr >= P.stripRow[k + 1]) k++;                         // warp-uniform: a warp's 4 pixel rows lie in one tile row
+    P.strip[k][pixelIdx - (P.stripRow[k] << 3) * P.width] = make_rgba8(color);
   } else P.rgba8[pixelIdx] = make_rgba8(color);
 }
 

@@ -36,8 +36,8 @@ struct RenderParams {
   const uint8_t *regionActive;         // per REGION: active for volume sampling (same classification as volActive's leaves); entry fast path
   float4 *accum; uint32_t *rgba8;
   // image-tile mode across GPUs: the RGBA8 frame as numStrips row strips (whole 8-row tile rows), strip k in the
-  // memory of GPU k (peer-mapped); 0 = one buffer (rgba8).  Strip k starts at tile row (tileRows * k) / numStrips.
-  uint32_t *strip[EXA_MAX_PARTS]; int numStrips;
+  // memory of GPU k (peer-mapped); 0 = one buffer (rgba8).  Strip k holds tile rows [stripRow[k], stripRow[k+1]).
+  uint32_t *strip[EXA_MAX_PARTS]; int numStrips; int stripRow[EXA_MAX_PARTS + 1];
   float4 *partialOut;                  // != null (sort-last): write the premultiplied partial, skip bg/accum/pack
   float4 *partialSurf;                 // with partialOut: nearest surface hit of this rank {shaded rgb, distance} (null: no surface pass)
   int tileMode, rank, numRanks;        // image-tile partition

@@ -27,6 +27,29 @@ def strip_rows(rank, world, height, tile_h=8):
     return min(height, tile_h * ((rows * rank) // world)), min(height, tile_h * ((rows * (rank + 1)) // world))
 
 
+def weighted_strip_rows(weights, height, tile_h=8):
+    """first pixel row of every strip (len(weights) + 1 entries) when strip k gets a share of the tile rows proportional
+    to weights[k] (a GPU's measured device-to-host bandwidth): largest-remainder rounding, deterministic, every rank
+    computes the same table.  Equal weights give strip_rows()."""
+    n = len(weights)
+    rows = (height + tile_h - 1) // tile_h
+    w = [max(float(x), 0.0) for x in weights]
+    tot = sum(w)
+    if tot <= 0 or max(w) - min(w) <= 1e-6 * tot:                 # equal: the kernel's default split, exactly
+        return [strip_rows(k, n, height, tile_h)[0] for k in range(n)] + [height]
+    exact = [rows * x / tot for x in w]
+    base = [int(e) for e in exact]
+    rest = rows - sum(base)
+    for k in sorted(range(n), key=lambda k: (-(exact[k] - base[k]), k))[:rest]:
+        base[k] += 1
+    out, acc = [0], 0
+    for k in range(n):
+        acc += base[k]
+        out.append(min(height, tile_h * acc))
+    out[-1] = height
+    return out
+
+
 def exchange_spans(dist, torch, partial, rank, world):
     """partial: (npix, C) tensor of this rank.  Returns a list of `world` tensors: every rank's partial
     restricted to THIS rank's span (index = source rank)."""
@@ -255,20 +278,46 @@ class TilePipeline(_Pipeline):
     NVLink), one peer-memory barrier says "frame complete", then every rank copies ITS strip to the shared pinned host
     frame over its own PCIe link."""
 
-    def __init__(self, dist, torch, capi, np, r, rank, world, device, W, H, stream, nccl_barrier=False, tag="t"):
+    def __init__(self, dist, torch, capi, np, r, rank, world, device, W, H, stream, nccl_barrier=False, tag="t", weighted=True):
         super().__init__(dist, torch, capi, np, r, rank, world, device, W, H, stream, nccl_barrier, tag)
         r.set_partition(capi.PARTITION_IMAGE_TILES, rank, world)
-        self.y0, self.y1 = strip_rows(rank, world, H)
-        rows = max(strip_rows(k, world, H)[1] - strip_rows(k, world, H)[0] for k in range(world))
+        # strips sized by what each GPU's link to host memory delivers while ALL ranks copy (GPUs behind a shared PCIe
+        # uplink get less): the N copies of a frame then finish together
+        self.copy_gbs = self._measure_copy_bandwidth() if (weighted and world > 1) else [1.0] * world
+        self.rows = weighted_strip_rows(self.copy_gbs, H)
+        self.y0, self.y1 = self.rows[rank], self.rows[rank + 1]
+        rows = max(self.rows[k + 1] - self.rows[k] for k in range(world))
         self.strips = PeerBuffers(dist, torch, capi, rank, world, device, max(rows, 1) * W * 4, 3)
         if not self.strips.ok:
             raise RuntimeError("CUDA IPC mapping of the frame strips failed")
         self.tables = [(C.c_void_p * world)(*[self.strips.ptr[k][b] for k in range(world)]) for b in range(3)]
+        self.row_table = (C.c_int * (world + 1))(*self.rows)
         self.d2h_bytes = (self.y1 - self.y0) * W * 4
+
+    def _measure_copy_bandwidth(self, reps=8):
+        """GB/s of this rank's device-to-host copy into the shared host frame while every rank copies its uniform strip"""
+        torch, dist = self.torch, self.dist
+        y0, y1 = strip_rows(self.rank, self.world, self.H)
+        nbytes = max((y1 - y0) * self.W * 4, 4096)
+        src = torch.zeros(nbytes, dtype=torch.uint8, device="cuda")
+        dst = self.host.ptr(0, min(y0 * self.W * 4, max(self.W * self.H * 4 - nbytes, 0)))
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        def burst(n):
+            for _ in range(n):
+                self.capi.check(self.capi.lib.exa_copy_async(C.c_void_p(dst), C.c_void_p(src.data_ptr()), nbytes, C.c_void_p(self.side.cuda_stream)))
+        burst(2); torch.cuda.synchronize(); dist.barrier()
+        c0.record(self.side); burst(reps); c1.record(self.side); torch.cuda.synchronize()
+        mine = torch.tensor([nbytes * reps / (c0.elapsed_time(c1) * 1e-3) / 1e9], dtype=torch.float64, device="cuda")
+        allbw = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(self.world)]
+        dist.all_gather(allbw, mine)
+        bw = [float(x.item()) for x in allbw]
+        # two classes of links, not eight noisy numbers: snap to 5 % of the fastest
+        top = max(bw)
+        return [round(x / top * 20) / 20 * top for x in bw]
 
     def step(self, readback=False):
         b = self._begin()
-        self.capi.check(self.capi.lib.exa_renderer_set_color_strips(self.r.h, self.tables[b], self.world))
+        self.capi.check(self.capi.lib.exa_renderer_set_color_strips_rows(self.r.h, self.tables[b], self.row_table, self.world))
         self.r.render(sync=False)                                  # own tiles -> the strips of all GPUs
         self._exchange(b)
         if readback and self.d2h_bytes:

@@ -183,6 +183,39 @@ def test_frame_strips_union_is_the_frame(R, orc, built_lib, world):
     assert (r.read_rgba8() == ref).all()
 
 
+def test_weighted_frame_strips(R, orc, built_lib):
+    """strips of caller-chosen heights (sized by copy bandwidth in the bench): same frame bit for bit; bad tables refused"""
+    import torch
+    b, fields, dom = _scene(R, mlw=127)
+    W, H = 200, 116
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [dom] * 3, W, H))
+    r = R.Renderer(b, fields)
+    fd.apply(r)
+    r.render()
+    ref = r.read_rgba8().copy()
+    for weights in ([1.0, 1.0, 2.0, 2.0], [12.0, 12.0, 21.0], [1.0, 0.0, 1.0], [3.0]):
+        world = len(weights)
+        rows = multigpu.weighted_strip_rows(weights, H)
+        assert rows[0] == 0 and rows[-1] == H and all(a <= c for a, c in zip(rows, rows[1:])) and all(y % 8 == 0 or y == H for y in rows)
+        strips = [torch.zeros((max(rows[k + 1] - rows[k], 1), W), dtype=torch.int32, device="cuda") for k in range(world)]
+        ptrs = (C.c_void_p * world)(*[s.data_ptr() for s in strips])
+        built_lib.check(built_lib.lib.exa_renderer_set_color_strips_rows(r.h, ptrs, (C.c_int * (world + 1))(*rows), world))
+        for k in range(world):
+            r.set_partition(built_lib.PARTITION_IMAGE_TILES, k, world)
+            r.render()
+        got = np.concatenate([strips[k].cpu().numpy().view(np.uint32)[:rows[k + 1] - rows[k]] for k in range(world)])
+        assert got.shape == ref.shape and (got == ref).all()
+    assert multigpu.weighted_strip_rows([1.0] * 3, H) == [multigpu.strip_rows(k, 3, H)[0] for k in range(3)] + [H]
+    assert multigpu.weighted_strip_rows([2.0, 1.0], 64) == [0, 40, 64]      # 8 tile rows: 5.33 / 2.67 -> 5 + 3
+    two = (C.c_void_p * 2)(strips[0].data_ptr(), strips[0].data_ptr())
+    for bad in ([0, 4, H], [0, 64, H - 1], [8, 64, H], [0, 64, 32]):
+        assert built_lib.lib.exa_renderer_set_color_strips_rows(r.h, two, (C.c_int * 3)(*bad), 2) == built_lib.EXA_ERR_INVALID
+    built_lib.check(built_lib.lib.exa_renderer_set_color_strips(r.h, None, 0))
+    r.set_partition(built_lib.PARTITION_NONE, 0, 1)
+    r.render()
+    assert (r.read_rgba8() == ref).all()
+
+
 def test_tracer_params_take_effect_at_reset(R, orc):
     """growing numTraces / numTimesteps without a reset must not change the shape the kernels index
     the trace buffer with (the reference pushes them inside resetTracer, OptixRenderer.cpp:450-474)"""

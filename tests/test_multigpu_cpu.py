@@ -95,5 +95,8 @@ def test_spans_strips_and_tiles_partition_the_frame():
             strips = [multigpu.strip_rows(r, world, height) for r in range(world)]
             assert strips[0][0] == 0 and strips[-1][1] == height and all(strips[i][1] == strips[i + 1][0] for i in range(world - 1))
             assert all(y0 % 8 == 0 for y0, _ in strips)
+            rows = multigpu.weighted_strip_rows([1.0 + (r % 2) for r in range(world)], height)
+            assert rows[0] == 0 and rows[-1] == height and all(a <= c for a, c in zip(rows, rows[1:])) and all(y % 8 == 0 or y == height for y in rows)
+            assert multigpu.weighted_strip_rows([3.0] * world, height) == [s[0] for s in strips] + [height]
         tiles = [set(multigpu.owned_tiles(r, world, 1024, 1024)) for r in range(world)]
         assert sum(len(t) for t in tiles) == 64 * 128 and len(set.union(*tiles)) == 64 * 128
