@@ -52,6 +52,7 @@ struct exa_renderer {
   // sort-last: partition tree over the top of the ABR kd-tree (buildPartitionTree); leaf: left < 0, owner = rank
   struct PartNode { int kd; int left, right; int rank; };
   std::vector<PartNode> partTree;
+  int lastGrid[4] = {0, 0, 0, 0};        // tile rectangle of the last sort-last partial (a change restarts the cost-ordered tile schedule)
   bool dataPartitioned = false;          // exa_renderer_create_partitioned: only this rank's bricks are resident, the rest of the kd-tree is pruned
   int residentBricks = 0;
   double buildMs[4] = {0, 0, 0, 0};      // ABR geometry, scalar gather, dual records, value ranges (device time)
@@ -89,7 +90,7 @@ static void identityXfm(float m[12]) { memset(m, 0, 48); m[0] = m[4] = m[8] = 1.
 // projections of its 8 corners, grown by 2 pixels (sub-pixel jitter, rounding).  Conservative: the whole frame when the
 // camera is inside the box, a corner is not in front of it, or the camera basis is degenerate.  Tiles outside the
 // rectangle skip ray set-up and traversal and write the background directly (render.cu).
-static void sceneScreenRect(const exa_renderer *r, int rect[4])
+static void boxScreenRect(const exa_renderer *r, const float boxLo[3], const float boxHi[3], int rect[4])
 {
   rect[0] = 0; rect[1] = 0; rect[2] = r->width - 1; rect[3] = r->height - 1;
   const float *m = (const float *)&r->fs.voxelSpaceTransform;      // voxel = L * world + p  (columns vx, vy, vz)
@@ -110,8 +111,7 @@ static void sceneScreenRect(const exa_renderer *r, int rect[4])
   if (!inv3(L, Li) || !inv3(M, Mi)) return;
   double lo[2] = {1e300, 1e300}, hi[2] = {-1e300, -1e300};
   for (int c = 0; c < 8; c++) {
-    const double v[3] = {(c & 1 ? r->abr.boundsHi[0] : r->abr.boundsLo[0]) - (double)m[9], (c & 2 ? r->abr.boundsHi[1] : r->abr.boundsLo[1]) - (double)m[10],
-                         (c & 4 ? r->abr.boundsHi[2] : r->abr.boundsLo[2]) - (double)m[11]};
+    const double v[3] = {(c & 1 ? boxHi[0] : boxLo[0]) - (double)m[9], (c & 2 ? boxHi[1] : boxLo[1]) - (double)m[10], (c & 4 ? boxHi[2] : boxLo[2]) - (double)m[11]};
     double q[3];
     for (int k = 0; k < 3; k++) q[k] = Li[3 * k] * v[0] + Li[3 * k + 1] * v[1] + Li[3 * k + 2] * v[2] - fs.camera.pos[k];
     const double a = Mi[0] * q[0] + Mi[1] * q[1] + Mi[2] * q[2], b = Mi[3] * q[0] + Mi[4] * q[1] + Mi[5] * q[2], d = Mi[6] * q[0] + Mi[7] * q[1] + Mi[8] * q[2];
@@ -123,6 +123,31 @@ static void sceneScreenRect(const exa_renderer *r, int rect[4])
   rect[0] = clampi(std::floor(lo[0]) - 3.0, 0, r->width); rect[1] = clampi(std::floor(lo[1]) - 3.0, 0, r->height);
   rect[2] = clampi(std::ceil(hi[0]) + 2.0, -1, r->width - 1); rect[3] = clampi(std::ceil(hi[1]) + 2.0, -1, r->height - 1);
 }
+
+// Box of sort-last part `rank`: the scene bounds cut by the split planes on the way down the partition tree (a prefix of the
+// ABR kd-tree, so every part is a box and all of the part's regions lie inside it).  false: that rank owns nothing.
+static bool partBoxOf(const exa_renderer *r, int rank, float lo[3], float hi[3])
+{
+  struct Item { int node; float lo[3], hi[3]; };
+  if (r->partTree.empty()) return false;
+  std::vector<Item> st(1);
+  st[0].node = 0; for (int d = 0; d < 3; d++) { st[0].lo[d] = r->abr.boundsLo[d]; st[0].hi[d] = r->abr.boundsHi[d]; }
+  while (!st.empty()) {
+    const Item it = st.back(); st.pop_back();
+    const exa_renderer::PartNode &pn = r->partTree[it.node];
+    if (pn.left < 0) {
+      if (pn.rank != rank) continue;
+      memcpy(lo, it.lo, 12); memcpy(hi, it.hi, 12); return true;
+    }
+    const KdNode nd = r->h_kd[pn.kd];
+    const int axis = (int)(nd.info >> 30);
+    Item l = it, rr = it;
+    l.node = pn.left; l.hi[axis] = nd.split; rr.node = pn.right; rr.lo[axis] = nd.split;
+    st.push_back(rr); st.push_back(l);
+  }
+  return false;
+}
+static inline bool sortLastParts(const exa_renderer *r) { return r->partMode == EXA_PARTITION_SORT_LAST && !r->partTree.empty(); }
 
 static void fillParams(exa_renderer *r, RenderParams &P)
 {
@@ -161,7 +186,12 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.ertThreshold = r->ert;
   P.volActive = r->d_volActive; P.isoActive = r->d_isoActive; P.regionActive = r->d_regionActive;
   P.accum = r->d_accum; P.rgba8 = r->d_rgba8; P.partialOut = nullptr;
-  sceneScreenRect(r, P.sceneRect);
+  // rays are clipped to the scene bounds - in sort-last mode to the box of this rank's part, outside of which it holds nothing
+  for (int d = 0; d < 3; d++) { P.rayLo[d] = r->abr.boundsLo[d]; P.rayHi[d] = r->abr.boundsHi[d]; }
+  bool ownsNothing = false;
+  if (sortLastParts(r) && !partBoxOf(r, r->rank, P.rayLo, P.rayHi)) ownsNothing = true;
+  boxScreenRect(r, P.rayLo, P.rayHi, P.sceneRect);
+  if (ownsNothing) { P.sceneRect[0] = P.sceneRect[1] = 0; P.sceneRect[2] = P.sceneRect[3] = -1; }
   P.numStrips = r->numStrips; for (int k = 0; k < r->numStrips; k++) P.strip[k] = r->strips[k];
   for (int k = 0; k <= r->numStrips; k++) P.stripRow[k] = r->stripRow[k];
   P.tileMode = r->partMode == EXA_PARTITION_IMAGE_TILES; P.rank = r->rank; P.numRanks = r->numRanks;

@@ -89,6 +89,16 @@ static int doRender(exa_renderer *r, float4 *partialOut, float4 *partialSurf, Ex
     } else P.traces = nullptr;                               // every visible segment has a dead end
   }
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
+  if (partialOut && sortLastParts(r) && P.anySurf != 2 && !P.tileList) {
+    // Sort-last partial: only the tiles that hold the projection of this part's box are launched; the rest of the partial
+    // is not written, and the composite does not read it (exa_renderer_composite_partials derives the same rectangles).
+    // Replicated surfaces (meshes, planes, cones: anySurf == 2) can lie anywhere on the screen: whole frame then.
+    if (P.sceneRect[2] < P.sceneRect[0] || P.sceneRect[3] < P.sceneRect[1]) return EXA_OK;          // nothing of this part is on the screen
+    P.gridX0 = P.sceneRect[0] / 16; P.gridY0 = P.sceneRect[1] / 8;
+    P.gridW = P.sceneRect[2] / 16 - P.gridX0 + 1; P.gridH = P.sceneRect[3] / 8 - P.gridY0 + 1;
+    const int g[4] = {P.gridX0, P.gridY0, P.gridW, P.gridH};
+    if (memcmp(g, r->lastGrid, sizeof g)) { r->tileOrderValid = false; memcpy(r->lastGrid, g, sizeof g); }   // other tiles than the recorded costs describe
+  } else if (r->lastGrid[2]) { r->tileOrderValid = false; memset(r->lastGrid, 0, sizeof r->lastGrid); }
   if (r->d_tileOrder[0] && !P.tileList) {                    // cost-ordered tile schedule (render.cu); an explicit tile list is already ordered
     if (!r->tileOrderValid)                                  // (re)start: both buffers' counters to zero, once
       for (int i = 0; i < 2; i++) CKR(cudaMemsetAsync(r->d_tileOrder[i], 0, offsetof(TileOrder, list), r->stream));
@@ -476,6 +486,18 @@ int exa_renderer_composite_partials(exa_renderer_t *r, const float *const *d_par
     C.part[j] = (const float4 *)d_partials[j]; C.surf[j] = d_surfs ? (const float4 *)d_surfs[j] : nullptr;
   }
   C.n = numParts; C.hasSurf = d_surfs != nullptr; C.first = first; C.count = count; C.out = d_rgba8Out;
+  // what every part wrote: the rectangle of its box (doRender), the whole frame when replicated surfaces are on or the
+  // renderer is not in sort-last mode (buffers filled by the caller)
+  for (int j = 0; j < numParts; j++) { C.rect[j][0] = 0; C.rect[j][1] = 0; C.rect[j][2] = r->width - 1; C.rect[j][3] = r->height - 1; }
+  if (sortLastParts(r) && P.anySurf != 2 && r->tileListLen == 0) {
+    int order[EXA_MAX_PARTS], np = 0;
+    const int rc = exa_renderer_partition_order(r, order, &np); if (rc) return rc;
+    for (int j = 0; j < numParts && j < r->numRanks; j++) {
+      float lo[3], hi[3];
+      if (partBoxOf(r, order[j], lo, hi)) boxScreenRect(r, lo, hi, C.rect[j]);
+      else { C.rect[j][0] = C.rect[j][1] = 0; C.rect[j][2] = C.rect[j][3] = -1; }
+    }
+  }
   const int k = launchCompositeFinish(P, C, r->stream);
   if (k < 0) { setError("composite kernel launch failed"); return EXA_ERR_CUDA; }
   r->launches += k; return EXA_OK;

@@ -237,12 +237,12 @@ struct Trav {
 // The ray (o, d) is passed to every call instead of living in Trav: for primary rays the voxel-space origin is the
 // same for the whole grid (a kernel parameter, no registers), and d is the lane's own copy.
 
-__device__ __forceinline__ void travInit(Trav &T, uint2 *stack, const float3 &o, const float3 &d, float tmin, float tmax, const DeviceScene &S)
+__device__ __forceinline__ void travInit(Trav &T, uint2 *stack, const float3 &o, const float3 &d, float tmin, float tmax, const float *boxLo, const float *boxHi)
 {
   T.stack = stack; T.sp = 0; T.cur = -1; T.tn = 0.f; T.tf = 0.f; T.visits = 0;
   T.invd = f3(1.f / d.x, 1.f / d.y, 1.f / d.z);
   float t0, t1;
-  if (boxTest(o, d, tmin, tmax, S.boundsLo, S.boundsHi, t0, t1)) {
+  if (boxTest(o, d, tmin, tmax, boxLo, boxHi, t0, t1)) {
     // widen a little: node intervals are only used for culling, leaves do the exact test
     T.cur = 0; T.tn = t0 - 1e-5f * fabsf(t0) - 1e-6f; T.tf = t1 + 1e-5f * fabsf(t1) + 1e-6f;
   }
@@ -507,7 +507,7 @@ __device__ void traceIsoRay(const RenderParams &P, const float4 *xfTables, uint2
   float already = dtScale * tmin; float rtmax = tmax;
   for (int c = 0; c < P.numChannels; c++) { isoV[c * SURF_THREADS] = -1e36f; isoT[c * SURF_THREADS] = 0.f; }
   rtmax = rtmax * dtScale;
-  Trav T; travInit(T, stack, vo, vd, already, rtmax, P.scene);
+  Trav T; travInit(T, stack, vo, vd, already, rtmax, P.rayLo, P.rayHi);
   for (;;) {
     Segment seg;
     if (!travNext<STATS>(T, vo, vd, P.scene, P.isoActive, already, rtmax, seg)) break;
@@ -746,7 +746,8 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       if (!found) { if (q < n) { b = i; found = true; } else q -= n; }
     }
     tileId = (int)P.tileOrderIn->list[(size_t)b * P.tileOrderCap + q];
-  } else tileId = P.tileMode ? ownedTile((int)blockIdx.x, P.rank, P.numRanks) : (int)blockIdx.x;
+  } else if (P.gridW > 0) tileId = (P.gridY0 + (int)blockIdx.x / P.gridW) * tilesX + P.gridX0 + (int)blockIdx.x % P.gridW;
+  else tileId = P.tileMode ? ownedTile((int)blockIdx.x, P.rank, P.numRanks) : (int)blockIdx.x;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // warp w covers the 8x4 sub-tile (w&1, w>>1) of the 16x8 CTA tile
   const int px = (tileId % tilesX) * TILE_W + (warp & 1) * 8 + (lane & 7);
@@ -828,7 +829,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
     const float dtScale = len3nc(d); d = normalize3nc(d);
     already = dtScale * tmin;
     rayTmax = tHitWorld * dtScale;
-    travInit(T, stack, o, d, already, rayTmax, P.scene);
+    travInit(T, stack, o, d, already, rayTmax, P.rayLo, P.rayHi);
     live = true;
   }
   // ---- DVR region loop (:1675-1699) + integrateBrick's sample loop (:1141-1184), flattened into
@@ -905,7 +906,7 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
   const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
   const int numTiles = tilesX * tilesY;
-  const int numMine = P.tileList ? P.tileListLen : P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
+  const int numMine = P.tileList ? P.tileListLen : P.gridW > 0 ? P.gridW * P.gridH : P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
   if (numMine <= 0) return 0;
   const dim3 grid(numMine), block(FRAME_THREADS);
   const bool stats = P.stats != nullptr;
@@ -1359,14 +1360,20 @@ __global__ void k_compositeFinish(const __grid_constant__ RenderParams P, const 
   const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= C.count) return;
   const size_t pixelIdx = C.first + i;
+  const int px = (int)(pixelIdx % (size_t)P.width), py = (int)(pixelIdx / (size_t)P.width);
   float4 q[EXA_MAX_PARTS];
+  unsigned covered = 0;                                       // parts whose rectangle holds this pixel: the others wrote nothing here and are not read
 #pragma unroll
   for (int j = 0; j < EXA_MAX_PARTS; j++)                     // all loads in flight before the dependent chain
-    if (j < C.n) q[j] = __ldcs(C.part[j] + pixelIdx);
+    if (j < C.n) {
+      const bool in = px >= C.rect[j][0] && px <= C.rect[j][2] && py >= C.rect[j][1] && py <= C.rect[j][3];
+      q[j] = in ? __ldcs(C.part[j] + pixelIdx) : make_float4(0.f, 0.f, 0.f, 0.f);
+      covered |= in ? 1u << j : 0u;
+    }
   float4 pc = make_float4(0, 0, 0, 0);
   int jStop = C.n - 1;                                        // last part that contributes: the first one with a surface hit of its own
   if (C.hasSurf)
-    for (int j = 0; j < C.n; j++) { const float w = __ldcs(&C.surf[j][pixelIdx].w); if (w > 0.f && w < 1e30f) { jStop = j; break; } }
+    for (int j = 0; j < C.n; j++) { if (!(covered >> j & 1u)) continue; const float w = __ldcs(&C.surf[j][pixelIdx].w); if (w > 0.f && w < 1e30f) { jStop = j; break; } }
 #pragma unroll
   for (int j = 0; j < EXA_MAX_PARTS; j++) {
     if (j >= C.n || j > jStop) break;
@@ -1384,6 +1391,7 @@ __global__ void k_compositeFinish(const __grid_constant__ RenderParams P, const 
     // (w = -t) is reported identically by all parts, which have clipped their samples at it themselves.
     bool have = false;
     for (int j = 0; j < C.n && j <= jStop; j++) {
+      if (!(covered >> j & 1u)) continue;
       const float4 sv = __ldcs(C.surf[j] + pixelIdx);
       if (sv.w >= 1e30f) continue;
       if (sv.w > 0.f) { bg = f3(sv.x, sv.y, sv.z); break; }

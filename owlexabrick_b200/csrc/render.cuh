@@ -19,6 +19,8 @@ struct RenderParams {
   // FrameState (programs/FrameState.h) / LaunchParams (programs/LaunchParams.h) subset
   float camPos[3], dir00[3], dirDu[3], dirDv[3];
   int sceneRect[4];                    // pixel rectangle (x0, y0, x1, y1 inclusive) outside which no primary ray can hit the scene bounds (host: projected corners, grown)
+  float rayLo[3], rayHi[3];            // box every primary / iso ray is clipped to before the traversal: the scene bounds, or in sort-last mode the box of this rank's part
+  int gridX0, gridY0, gridW, gridH;    // gridW > 0 (sort-last partial): the grid covers only the tile rectangle that holds this part's projection; pixels outside it are not written
   float camVoxel[3];                   // voxelSpaceTransform applied to camPos (host, same rounding as the device's xfmPoint): origin of every primary ray in voxel space
   float xfm[12];                       // voxelSpaceTransform: vx, vy, vz, p
   int width, height, frameID;
@@ -69,6 +71,7 @@ struct RenderParams {
 struct CompositeParams {
   const float4 *part[EXA_MAX_PARTS];   // partial images of all ranks, front-most first (whole-frame buffers, indexed by pixel)
   const float4 *surf[EXA_MAX_PARTS];   // their surface records (hasSurf)
+  int rect[EXA_MAX_PARTS][4];          // pixel rectangle (x0, y0, x1, y1 inclusive) each part has written; outside it the part contributes nothing and is not read
   int n, hasSurf;
   size_t first, count;                 // pixel span [first, first + count) this rank composites
   uint32_t *out;                       // RGBA8 frame buffer (whole frame; only the span is written)

@@ -41,8 +41,9 @@ def _sort_last_frame(R, torch, b, fields, fd, world, data_partitioned, surf=Fals
         if not data_partitioned:
             from owlexabrick_b200 import capi
             r.set_partition(capi.PARTITION_SORT_LAST, k, world)
-        p = torch.zeros((npix, 4), dtype=torch.float32, device="cuda")
-        sv = torch.zeros((npix, 4), dtype=torch.float32, device="cuda") if surf else None
+        # NaN-filled: a part renders only the tile rectangle of its box, and the composite must not read the rest
+        p = torch.full((npix, 4), float("nan"), dtype=torch.float32, device="cuda")
+        sv = torch.full((npix, 4), float("nan"), dtype=torch.float32, device="cuda") if surf else None
         r.render_partial(p.data_ptr(), sv.data_ptr() if surf else None)
         r.sync()
         parts.append(p); surfs.append(sv); rs.append(r)
@@ -59,7 +60,12 @@ def _sort_last_frame(R, torch, b, fields, fd, world, data_partitioned, surf=Fals
         a = rs[k].read_accum().reshape(-1, 4)
         acc.reshape(-1, 4)[lo:hi] = a[lo:hi]
     res = [r.residency() for r in rs]
-    return acc, out.cpu().numpy().view(np.uint32).reshape(H, W), res, [p.cpu().numpy() for p in parts], order
+    assert np.isfinite(acc).all()
+    host_parts = [p.cpu().numpy() for p in parts]
+    unwritten = [float(np.isnan(h[:, 3]).mean()) for h in host_parts]
+    if world >= 4:
+        assert max(unwritten) > 0.2, unwritten                      # the rectangles do restrict the work
+    return acc, out.cpu().numpy().view(np.uint32).reshape(H, W), res, [np.nan_to_num(h, nan=0.0) for h in host_parts], order
 
 
 @pytest.mark.parametrize("world", [2, 3, 4, 8])
