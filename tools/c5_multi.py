@@ -25,6 +25,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--image", default="7680x4320")
     ap.add_argument("--no-replica", action="store_true", help="skip the flat 1-GPU replica (parity reference + tracer)")
+    ap.add_argument("--modes", default="sortlast", help="comma list: sortlast (data partitioned, dual-cell records), tiles (flat layout replicated on every GPU, image tiles)")
     a = ap.parse_args()
     if os.environ.get("OMP_NUM_THREADS") == "1":
         os.environ.pop("OMP_NUM_THREADS")                          # torchrun's default; rank 0 builds with all cores
@@ -92,6 +93,11 @@ def main():
     if rank != 0:
         bricks = R.ExaBricks.load(base + ".bricks")
         fields = [np.load("%s_f%d.npy" % (base, c), mmap_mode="r") for c in range(3)]
+    modes = a.modes.split(",")
+    if "tiles" in modes:
+        run_tiles(a, dist, torch, capi, multigpu, R, scenes, bench, bricks, fields, n, dom, xfd, rank, world, local, W, H, log, info)
+    if "sortlast" not in modes:
+        cleanup(rank, base); dist.destroy_process_group(); return
     t = time.time()
     r = R.Renderer(bricks, fields, device=local, part=(rank, world))
     torch.cuda.synchronize()
@@ -115,7 +121,8 @@ def main():
         for c in range(3):
             rr.updateXF(c, fd.xf[c][0], fd.xf[c][1], fd.xf_domain[c], scale)
 
-    def timed(pipe, k, readback=False):
+    def timed(pipe, k, readback=False, rr=None):
+        rr = rr or r
         for _ in range(3):
             pipe.step(readback)
         pipe.drain(); torch.cuda.synchronize(); dist.barrier()
@@ -124,7 +131,7 @@ def main():
         e0.record(stream)
         for _ in range(k):
             if readback:
-                r.updateCamera(*fd.cam); set_opacity(r, cur_scale[0])
+                rr.updateCamera(*fd.cam); set_opacity(rr, cur_scale[0])
             pipe.step(readback)
         pipe.drain(); e1.record(stream)
         if readback:
@@ -227,14 +234,102 @@ def main():
     if rank == 0:
         print(json.dumps(out), flush=True)
     pipe.close()
-    for c in range(3):
-        if rank == 0:
-            try: os.unlink("%s_f%d.npy" % (base, c))
-            except OSError: pass
-    if rank == 0:
-        try: os.unlink(base + ".bricks")
-        except OSError: pass
+    cleanup(rank, base)
     dist.destroy_process_group()
+
+
+def cleanup(rank, base):
+    if rank == 0:
+        for f in ["%s_f%d.npy" % (base, c) for c in range(3)] + [base + ".bricks"]:
+            try: os.unlink(f)
+            except OSError: pass
+
+
+def run_tiles(a, dist, torch, capi, multigpu, R, scenes, bench, bricks, fields, n, dom, xfd, rank, world, local, W, H, log, info):
+    """C5 with the scene REPLICATED in the flat layout (3 x 4 B per cell: 24.8 GB per GPU) and the frame split into image
+    tiles: every GPU renders its cost-balanced share of the tiles into the peer-mapped frame strips"""
+    t = time.time()
+    full = R.Renderer(bricks, fields, device=local, layout=capi.LAYOUT_FLAT)
+    torch.cuda.synchronize()
+    create_s = time.time() - t
+    stream = torch.cuda.current_stream(); full.set_stream(stream.cuda_stream)
+    fd = scenes.FrameDesc(W, H, R.default_camera([0] * 3, [dom] * 3, W, H), 3)
+    fd.opacity_scale, fd.dt, fd.xf_domain = bench.OPACITY_SCALE, bench.DT, xfd
+    fd.apply(full)
+    lay, nbytes = full.scalar_layout()
+
+    def gmax(v):
+        t_ = torch.tensor([v], dtype=torch.float64, device="cuda"); dist.all_reduce(t_, op=dist.ReduceOp.MAX); return float(t_.item())
+
+    def set_opacity(scale):
+        for c in range(3):
+            full.updateXF(c, fd.xf[c][0], fd.xf[c][1], fd.xf_domain[c], scale)
+
+    def one_gpu(k):
+        for _ in range(2): full.render(sync=False)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(k): full.render(sync=False)
+        e1.record(stream); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / k, full.read_rgba8().copy(), full.render_stats()["samples"]
+    ref = {}
+    for key, scale in (("dvr_3ch", fd.opacity_scale), ("dvr_3ch_translucent", 0.02)):
+        set_opacity(scale)
+        ref[key] = one_gpu(3)                                        # every rank holds the whole scene: the same 1-GPU frame everywhere
+    set_opacity(fd.opacity_scale)
+    regions, leaf = full.get_abr()
+    pipe = multigpu.TilePipeline(dist, torch, capi, np, full, rank, world, local, W, H, stream, tag="c5t_%d" % os.getppid())
+
+    def timed(k, scale, readback=False):
+        for _ in range(3): pipe.step(readback)
+        pipe.drain(); torch.cuda.synchronize(); dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter(); e0.record(stream)
+        for _ in range(k):
+            if readback:
+                full.updateCamera(*fd.cam); set_opacity(scale)
+            pipe.step(readback)
+        pipe.drain(); e1.record(stream)
+        if readback: pipe.finish()
+        torch.cuda.synchronize()
+        return gmax(e0.elapsed_time(e1) / k), gmax((time.perf_counter() - t0) / k * 1e3)
+    out = {"workload": "c5 (synth.cloud_shaped(%d)): %d cells, domain %d^3, 3 channels, multichannel DVR %dx%d + streamlines" % (a.scale, n, dom, W, H),
+           "cells": n, "bricks": bricks.num_bricks, "regions": len(regions), "kd": full.kd_info(), "n_gpus": world,
+           "mode": "image tiles, scene replicated in the flat layout", "scalar_layout": "dual-cell records" if lay == capi.LAYOUT_DUAL else "flat",
+           "scalar_bytes_per_rank": nbytes, "renderer_create_s_max": round(gmax(create_s), 2), "build_times_rank0": full.build_times(), "scene": info}
+    for key, scale, k in (("dvr_3ch", fd.opacity_scale, a.steps), ("dvr_3ch_translucent", 0.02, max(3, a.steps // 2))):
+        set_opacity(scale)
+        bal = pipe.rebalance()
+        ms, _ = timed(k, scale)
+        _, wall = timed(k, scale, readback=True)
+        b = pipe.step(readback=True); pipe.drain(); pipe.finish(); torch.cuda.synchronize(); dist.barrier()
+        ms1, img1, s1 = ref[key]
+        o = {"ms_per_frame": round(ms, 4), "frames_per_s": round(1e3 / ms, 2), "samples_per_frame": int(s1), "samples_per_s": s1 / ms * 1e3,
+             "e2e_frames_per_s": round(1e3 / wall, 2), "e2e_d2h_bytes_per_rank": pipe.d2h_bytes, "tile_balance_max_over_mean": bal,
+             "one_gpu_flat_layout": {"ms_per_frame": round(ms1, 3)}, "speedup_vs_one_gpu_flat": round(ms1 / ms, 2)}
+        if rank == 0:
+            d = np.abs(scenes.unpack_rgba8(pipe.host_frame(b)) - scenes.unpack_rgba8(img1))
+            o["vs_one_gpu_frame"] = {"max_abs_rgba8_diff": int(d.max()), "pixels_differing": int((d.max(axis=-1) > 0).sum())}
+        out[key] = o
+    # streamlines: every GPU holds the whole field, so every GPU advects all seeds itself (7-8 ms) and draws the cones in its tiles
+    set_opacity(fd.opacity_scale)
+    NT, T = 1000, 100
+    full.setTracerParams(NT, T, dom / 100.0, (0, 1, 2)); full.setTracerEnabled(True)
+    ts = []
+    for i in range(3):
+        full.resetTracer()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream); full.traceAll(); e1.record(stream); torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    out["streamlines"] = {"traces": NT, "timesteps": T, "ms_trace_all": round(gmax(float(np.mean(ts[1:]))), 4), "where": "every rank, replicated"}
+    pipe.rebalance()
+    ms, _ = timed(max(3, a.steps // 2), fd.opacity_scale)
+    out["dvr_3ch_with_cones"] = {"ms_per_frame": round(ms, 4), "frames_per_s": round(1e3 / ms, 2)}
+    if rank == 0:
+        print(json.dumps(out), flush=True)
+    pipe.close()
+    full.close()
+    torch.cuda.empty_cache()
 
 
 if __name__ == "__main__":
