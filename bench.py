@@ -441,7 +441,7 @@ def run_product(args):
             bricks, field = load_or_build_scene(name, R)              # from rank 0's /dev/shm cache
     ncells = bricks.total_num_cells
     t = time.time()
-    r = R.Renderer(bricks, [field], device=local)
+    r = R.Renderer(bricks, [field], device=local, layout=capi.LAYOUT_FLAT if args.flat_layout else None)
     torch.cuda.synchronize()
     regions, leaf = r.get_abr()
     create_s = time.time() - t
@@ -888,6 +888,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="product", choices=["product", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
+    ap.add_argument("--flat-layout", action="store_true", help="keep the scalars in the reference's flat layout (4 B per cell) instead of the dual-cell records (32 B per cell): what a scene too large for the records runs on")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-builder-timing", action="store_true", help="do not re-run the GPU exaBuilder for its timing when the scene cache exists")
     ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
