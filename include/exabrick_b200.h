@@ -297,6 +297,10 @@ int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], 
  * the world-space bounds (exabrick.cu:1346-1364).  Forces space skipping off while a plane is on. */
 int exa_renderer_update_contour_planes(exa_renderer_t *r, const float *normals3, const float *offsets,
                                        const int *channels, const int *enabled);
+/* frameState.clockScale (programs/FrameState.h:57, set by the viewer at viewer.cpp:956): > 0 turns the red channel of
+ * every pixel into min(clockScale * cycles / 1e6, 1), the SM cycles the pixel's thread ran (exabrick.cu:1703-1707; here
+ * counted from the start of its 16x8-pixel CTA).  A profiling aid: values depend on the hardware, not on the reference. */
+int exa_renderer_set_clock_scale(exa_renderer_t *r, float clockScale);
 /* frameState.ao.{enabled,length} (programs/FrameState.h:60-63, poked by viewer.cpp:953-954): two
  * cosine-distributed occlusion rays of that length per shaded surface hit (exabrick.cu:1611-1646) */
 int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length);

@@ -104,6 +104,7 @@ _SIG = {
     "exa_renderer_set_clip_box": (i32, [vp, i32, vp, vp]),
     "exa_renderer_update_contour_planes": (i32, [vp, vp, vp, vp, vp]),
     "exa_renderer_set_ao": (i32, [vp, i32, f32]),
+    "exa_renderer_set_clock_scale": (i32, [vp, C.c_float]),
     "exa_renderer_set_triangle_meshes": (i32, [vp, vp, sz, vp, sz]),
     "exa_scalar_field_expression": (i32, [vp, i32, sz, vp, i32, vp, vp]),
     "exa_raw_to_cells": (i32, [vp, i32, i32, i32, i32, f32, i32, i32, C.POINTER(vp), C.POINTER(vp), C.POINTER(sz)]),

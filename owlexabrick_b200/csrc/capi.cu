@@ -175,7 +175,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   P.width = r->width; P.height = r->height; P.frameID = r->fs.frameID; P.dt = r->dt;
   P.numChannels = r->numFields; P.colormapChannel = 0;     // multiFieldDvr (OptixRenderer.h:110, .cpp:276-283)
   P.gradDVR = r->gradDVR; P.gradISO = r->gradISO;
-  P.xfOpacityScale = r->fs.xfOpacityScale;
+  P.xfOpacityScale = r->fs.xfOpacityScale; P.clockScale = r->fs.clockScale;
   memcpy(P.xfDomain, r->fs.xfDomain, sizeof(P.xfDomain));
   P.xf = r->d_xf;
   for (int i = 0; i < EXA_MAX_ISO_SURFACES; i++) {
@@ -881,6 +881,12 @@ int exa_renderer_set_triangle_meshes(exa_renderer_t *r, const float *vertices, s
   CKR(cudaMemcpy(r->d_meshNodes, mb.nodes.data(), mb.nodes.size() * sizeof(float4), cudaMemcpyHostToDevice));
   CKR(cudaMemcpy(r->d_meshTris, tris.data(), tris.size() * sizeof(float), cudaMemcpyHostToDevice));
   r->numMeshTris = (int)numTris;
+  return EXA_OK;
+}
+int exa_renderer_set_clock_scale(exa_renderer_t *r, float clockScale)
+{
+  if (!r) { setError("null renderer"); return EXA_ERR_INVALID; }
+  r->fs.clockScale = clockScale;                                     // viewer.cpp:956 pokes frameState.clockScale
   return EXA_OK;
 }
 int exa_renderer_set_ao(exa_renderer_t *r, int enable, float length)

@@ -665,7 +665,7 @@ __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float
 // Sort-last: the premultiplied partial of this rank's sub-volume, NOT yet scaled by the early-termination
 // rule (a terminated ray is marked by alpha + 2), and - when a surface pass ran - the shaded colour and
 // world-space distance of this rank's nearest surface hit (w = 1e30: none); k_compositeFinish puts them together.
-__device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, float4 pc, float3 bg, float surfT = 1e30f)
+__device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, float4 pc, float3 bg, long long tStart, float surfT = 1e30f)
 {
   if (P.partialOut) {
     P.partialOut[pixelIdx] = pc;
@@ -673,6 +673,8 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
     return;
   }
   float3 color = f3(pc.w * pc.x + (1.f - pc.w) * bg.x, pc.w * pc.y + (1.f - pc.w) * bg.y, pc.w * pc.z + (1.f - pc.w) * bg.z);   // :1701 (sic)
+  // clockScale heat-map (:1703-1707): the cycles this pixel took (here: since its CTA started), scaled, into the red channel
+  if (P.clockScale > 0.f) color.x = fminf(P.clockScale * (float)(clock64() - tStart) / 1000000.f, 1.f);
   if (P.frameID > 0) { const float4 acc = P.accum[pixelIdx]; color = color + f3(acc.x, acc.y, acc.z); }
   P.accum[pixelIdx] = make_float4(color.x, color.y, color.z, 1.f);
   const float inv = (float)P.frameID + 1.f;
@@ -759,7 +761,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   if (SURF == 0) {
     const int tx0 = (tileId % tilesX) * TILE_W, ty0 = (tileId / tilesX) * TILE_H;
     if (tx0 > P.sceneRect[2] || tx0 + TILE_W - 1 < P.sceneRect[0] || ty0 > P.sceneRect[3] || ty0 + TILE_H - 1 < P.sceneRect[1]) {
-      if (inside) writePixel(P, px + P.width * py, make_float4(0, 0, 0, 0), f3(0, 0, 0));
+      if (inside) writePixel(P, px + P.width * py, make_float4(0, 0, 0, 0), f3(0, 0, 0), t_start);
       inside = false;
     }
   }
@@ -866,7 +868,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       else t_i += dtS;
     }
   }
-  if (inside) writePixel(P, pixelIdx, pc, bg, surfHitT);
+  if (inside) writePixel(P, pixelIdx, pc, bg, t_start, surfHitT);
   if (STATS && P.stats && inside) {                          // instrumentation: per-ray maxima
     atomicMax(&P.stats[4], (unsigned long long)T.visits); atomicAdd(&P.stats[6], (unsigned long long)T.visits);
     atomicMax(&P.stats[5], (unsigned long long)rs.samples);

@@ -416,6 +416,10 @@ class Renderer:
         """frameState.ao (programs/FrameState.h:60-63; exa/viewer.cpp:953-954)"""
         check(lib.exa_renderer_set_ao(self.h, int(bool(enable)), float(length)))
 
+    def setClockScale(self, scale):
+        """frameState.clockScale (viewer.cpp:956): > 0 = per-pixel cycle heat-map in the red channel"""
+        check(lib.exa_renderer_set_clock_scale(self.h, float(scale)))
+
     def setErtThreshold(self, t):
         check(lib.exa_renderer_set_ert_threshold(self.h, float(t)))
 

@@ -258,6 +258,27 @@ def test_progressive_accumulation(R, orc):
         assert np.abs(scenes.unpack_rgba8(g_rgba) - scenes.unpack_rgba8(o_rgba)).max() <= 1
 
 
+def test_clock_scale_heat_map(R, orc):
+    """frameState.clockScale > 0 (exabrick.cu:1703-1707): the red channel becomes min(clockScale * cycles / 1e6, 1);
+    green and blue, and the frame with clockScale back at 0, are untouched"""
+    r, sc, fd, dom = _frame_pair(R, orc, "nb32", 1, size=(48, 32))
+    fd.opacity_scale = 0.3
+    fd.apply(r)
+    r.render()
+    ref = r.read_accum().copy()
+    r.setClockScale(10.0)
+    r.render()
+    hot = r.read_accum().copy()
+    assert np.array_equal(hot[..., 1:3], ref[..., 1:3])
+    assert (hot[..., 0] > 0).all() and (hot[..., 0] <= 1.0).all() and not np.array_equal(hot[..., 0], ref[..., 0])
+    r.setClockScale(1e9)
+    r.render()
+    assert (r.read_accum()[..., 0] == 1.0).all()                    # saturates
+    r.setClockScale(0.0)
+    r.render()
+    assert np.array_equal(r.read_accum(), ref)
+
+
 @pytest.mark.parametrize("grad_iso", [True, False])
 def test_iso_surface_plus_dvr(R, orc, grad_iso):
     r, sc, fd, dom = _frame_pair(R, orc, "nb64_off", 1)
