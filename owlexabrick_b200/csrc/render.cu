@@ -735,8 +735,10 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
   // Tile schedule: CTA q renders the q-th tile of the PREVIOUS frame's cost order (most expensive
   // first: longest-processing-time-first keeps the SMs busy to the end of the frame; without it
   // a few tiles of long rays finish alone).  Costs are CTA cycle counts, bucketed by log2; each
-  // frame writes the lists the next one reads.  Image-tile mode (multi-GPU, data replicated):
-  // the grid holds only the owned tiles (ownedTile()).
+  // frame writes the lists the next one reads.  Every thread runs the 15-bucket search itself: doing it in
+  // warp 0 only (prefix sum over the counts, tile id through shared memory) saves 3 % of the opaque frame's
+  // instructions and is 0.6 % SLOWER (the CTA then waits for one warp's dependent loads; profiles/perf_quick_r02_n_*).
+  // Image-tile mode (multi-GPU, data replicated): the grid holds only the owned tiles (ownedTile()) or an explicit list.
   const long long t_start = clock64();
   int tileId;
   if (P.tileList) tileId = (int)P.tileList[blockIdx.x];
