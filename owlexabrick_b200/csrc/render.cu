@@ -907,9 +907,12 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
 int launchRenderFrame(const RenderParams &P, cudaStream_t s)
 {
   const int tilesX = (P.width + TILE_W - 1) / TILE_W, tilesY = (P.height + TILE_H - 1) / TILE_H;
-  const size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
+  size_t smemBytes = 16 * (size_t)P.numChannels * 128 + 8 * (size_t)P.kdStack * FRAME_THREADS +
                            (P.anyIso ? 8 * (size_t)P.numChannels * FRAME_THREADS : 0);
   const int numTiles = tilesX * tilesY;
+  // experiment knob: at most EXA_FRAME_MAX_CTAS CTAs per SM (dynamic shared memory padded so that no more fit)
+  static const int maxCtas = getenv("EXA_FRAME_MAX_CTAS") ? atoi(getenv("EXA_FRAME_MAX_CTAS")) : 0;
+  if (maxCtas > 0 && maxCtas < EXA_FRAME_MINBLOCKS) smemBytes = std::max(smemBytes, (size_t)(227 * 1024) / maxCtas - 2048);
   const int numMine = P.tileList ? P.tileListLen : P.gridW > 0 ? P.gridW * P.gridH : P.tileMode ? numOwnedTiles(numTiles, P.rank, P.numRanks) : numTiles;
   if (numMine <= 0) return 0;
   const dim3 grid(numMine), block(FRAME_THREADS);
