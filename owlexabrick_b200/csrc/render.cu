@@ -989,56 +989,26 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
 #ifndef EXA_POINTS_MINBLOCKS
 #define EXA_POINTS_MINBLOCKS 16
 #endif
-#ifndef EXA_POINTS_PER_THREAD
-#define EXA_POINTS_PER_THREAD 1     // > 1: each thread runs that many independent locate -> header -> record chains, stage by stage
-#endif
+// One point per thread.  More chains in flight per SM make it SLOWER, not faster (round 2, profiles/perf_quick_r02_s_*): 2 / 3 / 4
+// points per thread with the descents advanced together: 63-69 / 88 / 94 us against 50.6 us; so do persistent lanes (93-109 us), a
+// two-level location grid (53.7 us although the kd steps a warp pays drop from 11.9 to 8.1), and halving the DRAM reads with
+// .L2::64B on the record loads (the default fetches 128 B per miss; 5.36 M -> 3.28 M sectors) changes nothing (48.8 us): the
+// query is bound neither by DRAM bandwidth nor by the chain length but by how many random sector requests the L1 / L2 / fabric
+// path turns around, and 2048 single-chain threads per SM sit at that optimum.
 
 template <bool GRAD, bool STATS, bool DUAL>
 __global__ void __launch_bounds__(EXA_POINTS_THREADS, EXA_POINTS_MINBLOCKS) k_samplePoints(const __grid_constant__ SampleParams P)
 {
-  constexpr int PPT = EXA_POINTS_PER_THREAD;
   unsigned visits = 0, corners = 0, counted = 0, kdSteps = 0;
-  if (PPT == 1) {
-    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < P.n) {
-      const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
-      float v = 0.f; float3 g = f3(0, 0, 0);
-      const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners, &kdSteps);
-      counted = visits > 0;
-      if (P.values) P.values[i] = ok ? v : 0.f;
-      if (P.valid) P.valid[i] = ok ? 1 : 0;
-      if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
-    }
-  } else {
-    // PPT independent chains per thread, advanced stage by stage so that the loads of one stage are all in flight
-    // together: coordinates, location (grid cell + the rare kd steps), first brick header, bricks
-    const size_t base = (size_t)blockIdx.x * blockDim.x * PPT + threadIdx.x;
-    float px[PPT], py[PPT], pz[PPT]; bool in[PPT], located[PPT]; uint32_t bo[PPT]; int K[PPT]; U8 hdr[PPT];
-#pragma unroll
-    for (int j = 0; j < PPT; j++) {
-      const size_t i = base + (size_t)j * blockDim.x;
-      in[j] = i < P.n; px[j] = py[j] = pz[j] = 0.f;
-      if (in[j]) { px[j] = P.xyz[3 * i]; py[j] = P.xyz[3 * i + 1]; pz[j] = P.xyz[3 * i + 2]; }
-    }
-#pragma unroll
-    for (int j = 0; j < PPT; j++) { bo[j] = 0; K[j] = 0; located[j] = in[j] && locate(P.scene, px[j], py[j], pz[j], bo[j], K[j], STATS ? &kdSteps : nullptr); }
-#pragma unroll
-    for (int j = 0; j < PPT; j++) if (located[j]) hdr[j] = ldg256(P.scene.blobs + bo[j] + BLOB_HDR_UNITS);
-#pragma unroll
-    for (int j = 0; j < PPT; j++) {
-      const size_t i = base + (size_t)j * blockDim.x;
-      if (!in[j]) continue;
-      float v = 0.f; float3 g = f3(0, 0, 0); bool ok = false;
-      if (located[j]) {
-        Acc a; accZero(a); unsigned nc = 0;
-        accumBricks<GRAD, STATS, DUAL>(a, hdr[j], P.scene.blobs + bo[j] + BLOB_HDR_UNITS, K[j], chanBase<DUAL>(P.scene, P.channel), px[j], py[j], pz[j], nc);
-        if (STATS) { visits += K[j]; corners += nc; counted++; }
-        ok = accFinish<GRAD>(a, v, g);
-      }
-      if (P.values) P.values[i] = ok ? v : 0.f;
-      if (P.valid) P.valid[i] = ok ? 1 : 0;
-      if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
-    }
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < P.n) {
+    const float px = P.xyz[3 * i], py = P.xyz[3 * i + 1], pz = P.xyz[3 * i + 2];
+    float v = 0.f; float3 g = f3(0, 0, 0);
+    const bool ok = samplePointGlobal<GRAD, STATS, DUAL>(P.scene, px, py, pz, P.channel, v, g, visits, corners, &kdSteps);
+    counted = visits > 0;
+    if (P.values) P.values[i] = ok ? v : 0.f;
+    if (P.valid) P.valid[i] = ok ? 1 : 0;
+    if (GRAD && P.grad) { P.grad[3 * i] = ok ? g.x : 0.f; P.grad[3 * i + 1] = ok ? g.y : 0.f; P.grad[3 * i + 2] = ok ? g.z : 0.f; }
   }
   if (STATS && P.stats) {
     unsigned long long a = counted, b = visits, c = corners;
@@ -1062,7 +1032,7 @@ int launchSamplePoints(const SampleParams &P, cudaStream_t s)
 {
   if (P.n == 0) return 0;
   const bool stats = P.stats != nullptr;
-  const size_t perBlock = (size_t)EXA_POINTS_THREADS * EXA_POINTS_PER_THREAD;
+  const size_t perBlock = (size_t)EXA_POINTS_THREADS;
   const unsigned grid = (unsigned)((P.n + perBlock - 1) / perBlock);
 #define LAUNCH_P(G, S_) { if (P.scene.dual) k_samplePoints<G, S_, true><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); else k_samplePoints<G, S_, false><<<grid, EXA_POINTS_THREADS, 0, s>>>(P); }
   if (P.grad) { if (stats) LAUNCH_P(true, true) else LAUNCH_P(true, false) }
