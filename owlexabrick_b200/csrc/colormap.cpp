@@ -57,7 +57,9 @@ struct Huffman {
   }
 };
 
-bool inflateZlib(const uint8_t *src, size_t n, std::vector<uint8_t> &out)
+// stops as soon as `want` bytes are out (the caller needs the first pixel row only: bounds the work and the memory a
+// hostile stream can cost)
+bool inflateZlib(const uint8_t *src, size_t n, std::vector<uint8_t> &out, size_t want)
 {
   if (n < 6 || (src[0] & 0x0f) != 8 || ((src[0] << 8) | src[1]) % 31 != 0 || (src[1] & 0x20)) return false;
   BitReader br{src + 2, n - 2};
@@ -75,6 +77,7 @@ bool inflateZlib(const uint8_t *src, size_t n, std::vector<uint8_t> &out)
       br.pos += 4;
       if ((len ^ 0xffffu) != nlen || br.pos + len > br.n) return false;
       out.insert(out.end(), br.p + br.pos, br.p + br.pos + len); br.pos += len;
+      if (out.size() >= want) return true;
     } else if (type == 1 || type == 2) {
       Huffman lit, dist;
       uint8_t lens[320];
@@ -112,7 +115,7 @@ bool inflateZlib(const uint8_t *src, size_t n, std::vector<uint8_t> &out)
       for (;;) {
         int sym = lit.decode(br);
         if (sym < 0) return false;
-        if (sym < 256) { out.push_back((uint8_t)sym); continue; }
+        if (sym < 256) { out.push_back((uint8_t)sym); if (out.size() >= want) return true; continue; }
         if (sym == 256) break;
         sym -= 257;
         if (sym >= 29) return false;
@@ -122,6 +125,7 @@ bool inflateZlib(const uint8_t *src, size_t n, std::vector<uint8_t> &out)
         const size_t d = distBase[ds] + (size_t)br.bits(distExtra[ds]);
         if (br.bad || d > out.size()) return false;
         for (int i = 0; i < len; i++) out.push_back(out[out.size() - d]);
+        if (out.size() >= want) return true;
       }
     } else return false;
     if (last) break;
@@ -150,9 +154,10 @@ bool pngFirstRowRGB(const uint8_t *buf, size_t n, std::vector<uint8_t> &rgb, int
   if (!w || !h || depth != 8 || interlace) { why = "unsupported PNG (need 8-bit, non-interlaced)"; return false; }
   const int chans = ctype == 0 ? 1 : ctype == 2 ? 3 : ctype == 3 ? 1 : ctype == 4 ? 2 : ctype == 6 ? 4 : 0;
   if (!chans) { why = "unsupported PNG colour type"; return false; }
-  std::vector<uint8_t> raw;
-  if (!inflateZlib(idat.data(), idat.size(), raw)) { why = "corrupt PNG data stream"; return false; }
+  if (w > (1u << 20)) { why = "PNG wider than 1 Mi pixels"; return false; }
   const size_t stride = (size_t)w * chans;
+  std::vector<uint8_t> raw;
+  if (!inflateZlib(idat.data(), idat.size(), raw, stride + 1)) { why = "corrupt PNG data stream"; return false; }
   if (raw.size() < stride + 1) { why = "short PNG data stream"; return false; }
   // un-filter row 0 (the row above it is all zeros)
   std::vector<uint8_t> row(raw.begin() + 1, raw.begin() + 1 + stride);

@@ -419,6 +419,23 @@ def test_colormapper_png_constructor(R):
         R.ColorMapper(png=b"not a png at all")
     with pytest.raises(Exception):
         R.ColorMapper(png=png(smooth, 2, 6)[:-40])                 # truncated
+    # hostile input: corrupted / truncated streams must be refused or decoded, never crash or balloon (the decoder stops
+    # after the first pixel row); a header that claims a huge image over a tiny stream is refused
+    base = bytearray(png(noise, 2, 6, 4))
+    frng = np.random.RandomState(11)
+    for _ in range(1500):
+        m = bytearray(base)
+        for _k in range(int(frng.randint(1, 6))):
+            m[int(frng.randint(8, len(m)))] = int(frng.randint(0, 256))
+        if frng.rand() < 0.2:
+            m = m[:int(frng.randint(8, len(m)))]
+        try:
+            R.ColorMapper(png=bytes(m))
+        except Exception:
+            pass
+    huge = bytearray(base); huge[16:24] = struct.pack(">II", 0x7fffffff, 0x7fffffff)
+    with pytest.raises(Exception):
+        R.ColorMapper(png=bytes(huge))
     # the generated header (what a C++ caller includes): each array decodes to the embedded map
     hdr = open(os.path.join(ROOT, "include", "exa", "embedded_colormaps.h")).read()
 
