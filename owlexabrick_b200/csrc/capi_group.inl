@@ -47,9 +47,10 @@ int exa_group_create(const exa_bricks_t *bricks, const float *const *fields, con
     if (rc) { exa_group_destroy(g); return rc; }
     g->r.push_back(r);
     cudaStream_t s = nullptr; cudaEvent_t e = nullptr;
-    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess || cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) {
-      setError("exa_group_create: stream / event creation failed"); exa_group_destroy(g); return EXA_ERR_CUDA; }
-    g->stream.push_back(s); g->evRendered.push_back(e);
+    if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) { setError("exa_group_create: stream creation failed"); exa_group_destroy(g); return EXA_ERR_CUDA; }
+    g->stream.push_back(s);                                  // owned by the group from here on (destroyed on every error path)
+    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { setError("exa_group_create: event creation failed"); exa_group_destroy(g); return EXA_ERR_CUDA; }
+    g->evRendered.push_back(e);
     r->stream = s;
     if (mode == EXA_PARTITION_IMAGE_TILES && numDevices > 1) exa_renderer_set_partition(r, EXA_PARTITION_IMAGE_TILES, k, numDevices);
   }
