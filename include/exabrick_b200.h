@@ -459,6 +459,10 @@ int exa_group_update_xf(exa_group_t *g, int channel, const float *opacities128, 
 int exa_group_update_frame_id(exa_group_t *g, int frameID);
 int exa_group_set_voxel_space_transform(exa_group_t *g, const float xfm12[12]);
 int exa_group_render(exa_group_t *g, uint32_t *hostRgba8);
+/* image-tile mode: deal the tiles by measured cost (per-tile cycle counters of `rounds` frames, longest-processing-time-
+ * first across the devices; exa_balance_tiles) instead of the static interleaved deal.  Call it after the camera or the
+ * transfer function changed a lot - a viewer every few dozen frames.  maxOverMeanLoad may be NULL.  No-op for sort-last. */
+int exa_group_rebalance(exa_group_t *g, int rounds, double *maxOverMeanLoad);
 
 /* Image tiles balanced by measured cost (multi-GPU, data replicated).  With tile costs enabled the frame kernel
  * records, per 16x8-pixel tile it rendered, the SM cycles its CTA took.  The ranks combine their arrays (each tile

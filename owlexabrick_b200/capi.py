@@ -155,6 +155,7 @@ _SIG = {
     "exa_group_update_frame_id": (i32, [vp, i32]),
     "exa_group_set_voxel_space_transform": (i32, [vp, vp]),
     "exa_group_render": (i32, [vp, vp]),
+    "exa_group_rebalance": (i32, [vp, i32, C.POINTER(C.c_double)]),
     "exa_peer_barrier": (i32, [vp, i32, i32, C.c_uint32, vp]),
     "exa_copy_async": (i32, [vp, vp, sz, vp]),
     "exa_host_register": (i32, [vp, sz]),

@@ -123,6 +123,39 @@ int exa_group_update_frame_id(exa_group_t *g, int frameID)
 int exa_group_set_voxel_space_transform(exa_group_t *g, const float xfm12[12])
 { if (!g) { setError("null group"); return EXA_ERR_INVALID; } for (exa_renderer *r : g->r) { const int rc = exa_renderer_set_voxel_space_transform(r, xfm12); if (rc) return rc; } return EXA_OK; }
 
+// Image tiles dealt by measured cost (what multigpu.TilePipeline.rebalance does across processes): `rounds` frames are
+// rendered with per-tile cycle counters on, every tile's cost comes from the device that rendered it, the deterministic
+// LPT deal (exa_balance_tiles) gives every device its list.  A viewer calls this every few dozen frames (cost: the frames
+// plus N small copies); maxOverMeanLoad (may be NULL) receives the balance of the new deal under the measured costs.
+int exa_group_rebalance(exa_group_t *g, int rounds, double *maxOverMeanLoad)
+{
+  if (!g || g->width <= 0) { setError("exa_group_rebalance: resize the frame buffer first"); return EXA_ERR_INVALID; }
+  if (maxOverMeanLoad) *maxOverMeanLoad = 1.0;
+  if (g->mode != EXA_PARTITION_IMAGE_TILES || g->n < 2) return EXA_OK;
+  const int N = g->n, nt = ((g->width + 15) / 16) * ((g->height + 7) / 8);
+  std::vector<uint32_t> costs(nt), one(nt), mine(nt);
+  for (int it = 0; it < std::max(rounds, 1); it++) {
+    for (int k = 0; k < N; k++) { const int rc = exa_renderer_enable_tile_costs(g->r[k], 1); if (rc) return rc; }
+    for (int k = 0; k < N; k++) { const int rc = doRender(g->r[k], nullptr, nullptr, nullptr, false); if (rc) return rc; }
+    std::fill(costs.begin(), costs.end(), 0u);
+    for (int k = 0; k < N; k++) {
+      int rc = exa_renderer_get_tile_costs(g->r[k], one.data(), nt); if (rc) return rc;      // synchronises device k
+      for (int i = 0; i < nt; i++) costs[i] = std::max(costs[i], one[i]);                       // each tile was rendered by exactly one device
+      rc = exa_renderer_enable_tile_costs(g->r[k], 0); if (rc) return rc;
+    }
+    double total = 0.0, worst = 0.0;
+    for (int k = 0; k < N; k++) {
+      int n = 0;
+      int rc = exa_balance_tiles(costs.data(), nt, N, k, mine.data(), &n); if (rc) return rc;
+      rc = exa_renderer_set_tile_list(g->r[k], mine.data(), n); if (rc) return rc;
+      double load = 0.0; for (int i = 0; i < n; i++) load += (double)costs[mine[i]];
+      total += load; worst = std::max(worst, load);
+    }
+    if (maxOverMeanLoad && total > 0.0) *maxOverMeanLoad = worst / (total / N);
+  }
+  return EXA_OK;
+}
+
 int exa_group_render(exa_group_t *g, uint32_t *hostRgba8)
 {
   if (!g || !hostRgba8 || g->width <= 0) { setError("exa_group_render: resize the frame buffer first"); return EXA_ERR_INVALID; }

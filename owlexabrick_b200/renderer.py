@@ -598,6 +598,12 @@ class RendererGroup:
     def __del__(self):
         self.close()
 
+    def rebalance(self, rounds=2):
+        """exa_group_rebalance: image tiles dealt by measured cost; returns max / mean device load of the new deal"""
+        ratio = C.c_double(1.0)
+        check(lib.exa_group_rebalance(self.h, int(rounds), C.byref(ratio)))
+        return ratio.value
+
     def apply(self, fd):
         """a tests/scenes.FrameDesc on every device (the frame buffers belong to the group)"""
         if self.size != (fd.width, fd.height):

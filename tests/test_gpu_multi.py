@@ -317,6 +317,12 @@ def test_renderer_group_behind_the_c_abi(R, orc, built_lib, mode_name, parts):
         assert (img == ref).all()
     else:
         assert np.abs(scenes.unpack_rgba8(img) - scenes.unpack_rgba8(ref)).max() <= 1
+    # tiles dealt by measured cost: the same frame, a balanced deal (no-op for sort-last)
+    ratio = g.rebalance()
+    assert 1.0 <= ratio < 1.2
+    img = g.render()
+    if mode_name == "tiles":
+        assert (img == ref).all()
     # a per-device setter through the group's renderer handles, then a per-frame setter through the group
     for r in g.renderers:
         r.setGradientShadingDVR(False)
