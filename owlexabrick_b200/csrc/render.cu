@@ -689,7 +689,7 @@ __device__ __forceinline__ void writePixel(const RenderParams &P, int pixelIdx, 
 }
 
 #ifndef EXA_FRAME_MINBLOCKS
-#define EXA_FRAME_MINBLOCKS 6     // 80 registers, 24 warps / SM: C3 opaque 0.718 -> 0.660 ms, translucent 7.29 -> 6.92 ms against 5 (96 registers); 8 (64 registers, spills) is slower (profiles/perf_quick_r02_c_*)
+#define EXA_FRAME_MINBLOCKS 6     // 80 registers, 24 warps / SM: C3 opaque 0.718 -> 0.660 ms, translucent 7.29 -> 6.92 ms against 5 (96 registers); 8 (64 registers, spills) is slower (round 2, GPU calls A-C)
 #endif
 static constexpr int TILE_W = 16, TILE_H = 8;
 
