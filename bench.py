@@ -480,11 +480,16 @@ def run_product(args):
         if pipe is not None:
             pipe.drain()
 
-    def step(readback=False):
+    overlap = world > 1 and mode == "tiles" and not args.static_tiles and not args.no_frame_overlap
+
+    def step(readback=False, overlapped=False):
         if pipe is None:
             r.render(sync=False)
             return 1
-        pipe.step(readback)
+        if overlapped and overlap:
+            pipe.step(readback, overlap=True)                     # frames on two alternating streams (no device-state update in between)
+        else:
+            pipe.step(readback)
         return 2 + (1 if mode == "sortlast" else 0)              # frame kernel + barrier kernel (+ composite kernel)
 
     rr = sl_r if sl_r is not None else r                          # the renderer the timed frames run on
@@ -506,7 +511,8 @@ def run_product(args):
         # tiles dealt by measured cost (part of the warm-up, as a viewer would do every few dozen frames)
         balance = {"max_over_mean_rank_load_after_lpt": pipe.rebalance()}
         for _ in range(3):
-            step()
+            step(overlapped=True)
+        drain()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
@@ -516,7 +522,7 @@ def run_product(args):
     ev0.record(stream)
     launches = 0
     for _ in range(args.steps):
-        launches += step()
+        launches += step(overlapped=True)
     drain()
     ev1.record(stream)
     torch.cuda.synchronize()
@@ -677,8 +683,16 @@ def run_product(args):
         p.drain(); torch.cuda.synchronize(); dist.barrier()
         bsel = p.j % 3
         if rank == 0:
-            p.host_frame(bsel)[:] = 0                                 # stale pixels must not be able to hide a missing tile
+            for k in range(3):
+                p.host_frame(k)[:] = 0                                # stale pixels must not be able to hide a missing tile
         dist.barrier()
+        if overlap and p is pipe:
+            # the checked frame is the LAST of three overlapped ones: it ran while its predecessor was still finishing
+            for _ in range(3):
+                bsel = p.j % 3
+                p.step(readback=True, overlap=True)
+            p.drain(); p.finish(); torch.cuda.synchronize(); dist.barrier()
+            return p.host_frame(bsel).reshape(-1).copy()
         p.step(readback=True); p.drain(); p.finish(); torch.cuda.synchronize(); dist.barrier()
         return p.host_frame(bsel).reshape(-1).copy()
 
@@ -856,7 +870,7 @@ def run_product(args):
                            "scalar_layout": {1: "flat", 2: "dual-cell records"}[r.scalar_layout()[0]], "scalar_bytes": r.scalar_layout()[1],
                            "l2": "inputs larger than L2 (%.0f MB of scalars vs 126 MB), no flush" % (4e-6 * ncells),
                            "samples_per_frame": tot["samples"], "segments_per_frame": tot["segments"],
-                           "step": "eager launches" + (", frames triple-buffered: the completion barrier (and the composite) of frame i runs on a side stream while frame i+1 renders" if world > 1 else "")},
+                           "step": "eager launches" + (", consecutive frames on two alternating streams: the tail of frame i (its last long-ray tiles) overlaps the head of frame i+1; no device state changes between the timed frames" if overlap else "") + (", frames triple-buffered: the completion barrier (and the composite) of frame i runs on a side stream while frame i+1 renders" if world > 1 else "")},
                 "e2e": {"value": e2e_value, "unit": "samples/s", "frames_per_s": args.steps / e2e_s,
                         "h2d_bytes_per_step": (128 * 16 + 48) * world, "d2h_bytes_per_step": W * H * 4,
                         "d2h_bytes_per_step_per_rank": (W * H * 4) if world == 1 else pipe.d2h_bytes,
@@ -894,6 +908,7 @@ def main():
     ap.add_argument("--quick-parity", action="store_true", help="skip the CPU render of the translucent frame (about 30 s on C3)")
     ap.add_argument("--profile-range", action="store_true", help="cudaProfilerStart/Stop around warm-up + timed steps (for ncu --profile-from-start off)")
     ap.add_argument("--nccl-barrier", action="store_true", help="N>1: 4-byte NCCL all-reduce per frame instead of the peer-memory barrier kernel")
+    ap.add_argument("--no-frame-overlap", action="store_true", help="N>1 image tiles: every frame on the one render stream (no overlap of a frame's tail with the next frame's head)")
     ap.add_argument("--uniform-strips", action="store_true", help="N>1 image tiles: equal frame strips instead of strips sized by each GPU's measured copy bandwidth")
     ap.add_argument("--static-tiles", action="store_true", help="N>1 image tiles: keep the static round-robin deal (no cost-balanced tile lists)")
     ap.add_argument("--no-sortlast", action="store_true", help="N>1: skip the secondary sort-last measurement")

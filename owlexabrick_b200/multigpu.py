@@ -239,15 +239,15 @@ class _Pipeline:
         self.ev_bar = [torch.cuda.Event() for _ in range(3)]
         self.j = 0
 
-    def _begin(self):
+    def _begin(self, s=None):
         j = self.j
         self.j += 1
         if j >= 2:
-            self.stream.wait_event(self.ev_bar[(j - 2) % 3])
+            (s or self.stream).wait_event(self.ev_bar[(j - 2) % 3])
         return j % 3
 
-    def _exchange(self, b):
-        self.ev_render[b].record(self.stream)
+    def _exchange(self, b, s=None):
+        self.ev_render[b].record(s or self.stream)
         self.side.wait_event(self.ev_render[b])
         self.bar.wait(self.side)
         self.ev_bar[b].record(self.side)
@@ -293,6 +293,7 @@ class TilePipeline(_Pipeline):
         self.tables = [(C.c_void_p * world)(*[self.strips.ptr[k][b] for k in range(world)]) for b in range(3)]
         self.row_table = (C.c_int * (world + 1))(*self.rows)
         self.d2h_bytes = (self.y1 - self.y0) * W * 4
+        self.balanced, self.alt = False, None
 
     def _measure_copy_bandwidth(self, reps=8):
         """GB/s of this rank's device-to-host copy into the shared host frame while every rank copies its uniform strip"""
@@ -315,11 +316,24 @@ class TilePipeline(_Pipeline):
         top = max(bw)
         return [round(x / top * 20) / 20 * top for x in bw]
 
-    def step(self, readback=False):
-        b = self._begin()
+    def step(self, readback=False, overlap=False):
+        """overlap: consecutive frames go to two alternating streams, so that the head of frame j+1 (its most expensive
+        tiles) fills the SMs that the tail of frame j (a few tiles of long rays) leaves idle; the frames write different
+        strip buffers.  Only with an installed tile list (the per-frame cost-order feedback of the single-GPU schedule is a
+        frame-to-frame dependency) and only while NO device state of the renderer changes between the frames (camera
+        changes are kernel parameters and fine; transfer-function / iso / trace updates are not): call drain() first."""
+        s = None
+        if overlap and self.balanced:
+            if self.alt is None:
+                self.alt = self.torch.cuda.Stream()
+            s = self.alt if (self.j & 1) else self.stream
+            self.r.set_stream(s.cuda_stream)
+        b = self._begin(s)
         self.capi.check(self.capi.lib.exa_renderer_set_color_strips_rows(self.r.h, self.tables[b], self.row_table, self.world))
         self.r.render(sync=False)                                  # own tiles -> the strips of all GPUs
-        self._exchange(b)
+        self._exchange(b, s)
+        if s is not None:
+            self.r.set_stream(self.stream.cuda_stream)
         if readback and self.d2h_bytes:
             self.capi.check(self.capi.lib.exa_copy_async(C.c_void_p(self.host.ptr(b, self.y0 * self.W * 4)), C.c_void_p(self.strips.ptr[self.rank][b]),
                                                          self.d2h_bytes, C.c_void_p(self.side.cuda_stream)))
@@ -345,6 +359,7 @@ class TilePipeline(_Pipeline):
             mine, n = np.zeros(nt, np.uint32), C.c_int()
             capi.check(capi.lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, self.world, self.rank, mine.ctypes.data_as(C.c_void_p), C.byref(n)))
             capi.check(capi.lib.exa_renderer_set_tile_list(self.r.h, mine.ctypes.data_as(C.c_void_p), n.value))
+            self.balanced = True
             load = torch.tensor([float(costs[mine[:n.value]].astype(np.float64).sum())], dtype=torch.float64, device="cuda")
             loads = [torch.zeros(1, dtype=torch.float64, device="cuda") for _ in range(self.world)]
             self.dist.all_gather(loads, load)
