@@ -13,4 +13,4 @@ print("e2e", {k: d["e2e"][k] for k in ("value", "frames_per_s", "d2h_bytes_per_s
 print("sortlast", {k: d["sortlast"][k] for k in ("resident_cells_per_rank", "opaque", "translucent")})
 print("translucent", d.get("dvr_translucent"))
 PY
-timeout 300 $TR bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/u_ref_n${N}.json 2> gpurun_out/u_ref_n${N}.err; echo "reference arm under torchrun rc=$?"; tail -c 300 gpurun_out/u_ref_n${N}.json
+[ -n "$SKIPREF" ] || timeout 300 $TR bench.py --impl reference --gpus $N --steps 2 --warmup 1 > gpurun_out/u_ref_n${N}.json 2> gpurun_out/u_ref_n${N}.err; echo "reference arm under torchrun rc=$?"; tail -c 300 gpurun_out/u_ref_n${N}.json
