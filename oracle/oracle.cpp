@@ -612,6 +612,35 @@ static int closestRegion(const OrcScene &s, const std::vector<uint8_t> &active, 
   t0 = bt0; t1 = bt1; return best;
 }
 
+// gradientCD<ISO> (exabrick.cu:833-880, FAST_CENTRAL_DIFFERENCES off) behind samplePointWithDerivative built with
+// ANALYTIC_GRADIENTS=0 (:928-931): six more point samples at pos -+ delta along the axes, each located by its own region
+// query over the BVH of the ACTIVE regions (volume BVH, or the iso-surface BVH for ISO) with a ray of length 2e-10
+// along (1,1,1); the result is f(pos - delta) - f(pos + delta) per axis (sic).  A position outside every active region
+// samples 0.  Decided: a located position whose sample is invalid (sum of weights <= 1e-20) samples 0 too - the
+// reference leaves that float uninitialised.
+static V3 gradientCD(const OrcScene &s, const std::vector<uint8_t> &active, V3 pos, float delta, int channel)
+{
+  float sv[2][3];
+  for (int i = 0; i < 3; i++)
+    for (int j = 0; j < 2; j++) {
+      const V3 dt = v3(i == 0 ? delta : 0.f, i == 1 ? delta : 0.f, i == 2 ? delta : 0.f);
+      Ray ray; ray.o = j == 0 ? pos + dt : pos - dt; ray.d = v3(1.f, 1.f, 1.f); ray.tmin = 0.f; ray.tmax = 2e-10f;
+      float t0, t1, v = 0.f;
+      const int leaf = closestRegion(s, active, ray, t0, t1);
+      sv[j][i] = (leaf >= 0 && samplePoint(s, v, leaf, ray.o, channel, nullptr)) ? v : 0.f;
+    }
+  return v3(sv[1][0] - sv[0][0], sv[1][1] - sv[0][1], sv[1][2] - sv[0][2]);
+}
+// samplePointWithDerivative<ISO> in either build: analytic (default) or central differences
+static inline bool sampleWithGradient(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &active, float &value, V3 &g,
+                                      int leafID, V3 pos, int channel, OrcStats *st)
+{
+  if (!f.centralDifferences) return samplePointD(s, value, g, leafID, pos, channel, st);
+  if (!samplePoint(s, value, leafID, pos, channel, st)) return false;
+  g = gradientCD(s, active, pos, (s.regions[leafID].finestLevelCellWidth + 1.f) * .5f, channel);
+  return true;
+}
+
 struct IntResult { V4 *pc; float t_hit = -1.f; V3 grad = {0, 0, 0}; };
 
 // integrateVolume, exabrick.cu:988-1016
@@ -634,7 +663,7 @@ static inline void integrateVolume(const OrcFrame &f, const Ray &ray, IntResult 
 // IsoSurfaceIntegrationFunction, exabrick.cu:1018-1114
 struct IsoFunc {
   float last_t = 0.f, lastCellValue = -1e36f;
-  void operator()(const OrcScene &s, const OrcFrame &f, const Ray &ray, IntResult &res, float t_sample,
+  void operator()(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &isoActive, const Ray &ray, IntResult &res, float t_sample,
                   float cellValue, int leafID, int channel, OrcStats *st)
   {
     if (lastCellValue >= -1e35f) {
@@ -648,7 +677,7 @@ struct IsoFunc {
           float cv = 0.f; V3 grad = v3(0, 0, 0); V4 smp = {1.f, 0.f, 0.f, 1.f};
           const V3 isopt = ray.o + tavg * ray.d;
           if (f.gradientShadingISO) {
-            if (samplePointD(s, cv, grad, leafID, isopt, f.isoChannel[i], st)) {
+            if (sampleWithGradient(s, f, isoActive, cv, grad, leafID, isopt, f.isoChannel[i], st)) {     // <ISO = true>
               smp = lookupXF(f, cv, f.isoChannel[i]);
               grad = normalize(grad);
               if (dot(grad, ray.d) > 0.f) grad = -grad;
@@ -689,7 +718,7 @@ static inline float firstLatticeT(float t0, float dt, float offs)
 
 // integrateBrick<GRADIENT_SHADING>, exabrick.cu:1116-1185
 static thread_local bool g_dbg = false;
-static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res, float offs, const Ray &ray,
+static void integrateBrick(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &volActive, IntResult &res, float offs, const Ray &ray,
                            int leafID, float t0, float t1, int numChannels, bool gradShading, OrcStats *st)
 {
   const OrcRegion &r = s.regions[leafID];
@@ -705,7 +734,7 @@ static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res,
     float cv = 0.f; V3 g = v3(0, 0, 0);
     for (int c = 0; c < numChannels; c++) {
       if (g_dbg) { float v2; V3 g2; if (samplePointD(s, v2, g2, leafID, pos, c, nullptr)) printf("O   smp t=%.9g adt=%.9g v=%.9g g=(%.6g %.6g %.6g)\n", t_sample, actual_dt, v2, g2.x, g2.y, g2.z); }
-      if (gradShading) { if (samplePointD(s, cv, g, leafID, pos, c, st)) integrateVolume(f, ray, res, actual_dt, cv, g, fcw, c); }
+      if (gradShading) { if (sampleWithGradient(s, f, volActive, cv, g, leafID, pos, c, st)) integrateVolume(f, ray, res, actual_dt, cv, g, fcw, c); }
       else             { if (samplePoint(s, cv, leafID, pos, c, st))     integrateVolume(f, ray, res, actual_dt, cv, g, fcw, c); }
     }
     if (res.pc->w >= f.ertThreshold) break;
@@ -714,7 +743,7 @@ static void integrateBrick(const OrcScene &s, const OrcFrame &f, IntResult &res,
 }
 
 // isoIntegrateBrick, exabrick.cu:1187-1256
-static void isoIntegrateBrick(const OrcScene &s, const OrcFrame &f, IsoFunc *funcs, IntResult &res, float offs,
+static void isoIntegrateBrick(const OrcScene &s, const OrcFrame &f, const std::vector<uint8_t> &isoActive, IsoFunc *funcs, IntResult &res, float offs,
                               const Ray &ray, int leafID, float t0, float t1, int numChannels, OrcStats *st)
 {
   const OrcRegion &r = s.regions[leafID];
@@ -728,10 +757,12 @@ static void isoIntegrateBrick(const OrcScene &s, const OrcFrame &f, IsoFunc *fun
     const V3 pos = ray.o + t_sample * ray.d;
     for (int c = 0; c < numChannels; c++) {
       float cv = 0.f; V3 g = v3(0, 0, 0); bool ok;
-      if (f.gradientShadingISO) ok = samplePointD(s, cv, g, leafID, pos, c, st);
+      // the gradient of this sample is never used by the iso functor: the central-difference build's six extra samples
+      // (samplePointWithDerivative<false>, :1237) have no effect and are not taken
+      if (f.gradientShadingISO && !f.centralDifferences) ok = samplePointD(s, cv, g, leafID, pos, c, st);
       else ok = samplePoint(s, cv, leafID, pos, c, st);
       if (ok) {
-        funcs[c](s, f, ray, res, t_sample, cv, leafID, c, st);
+        funcs[c](s, f, isoActive, ray, res, t_sample, cv, leafID, c, st);
         if (res.pc->w >= f.ertThreshold) break;
       }
     }
@@ -761,7 +792,7 @@ static Surface traceIsoRay(const OrcScene &s, const OrcFrame &f, const std::vect
     float t0, t1; int leaf = closestRegion(s, isoActive, ray, t0, t1);
     if (leaf < 0) break;
     V4 pc = {0, 0, 0, 0}; IntResult ir; ir.pc = &pc;
-    isoIntegrateBrick(s, f, funcs, ir, 0.f, ray, leaf, fmaxf(ray.tmin, t0), fminf(ray.tmax, t1), f.numPrimaryChannels, st);
+    isoIntegrateBrick(s, f, isoActive, funcs, ir, 0.f, ray, leaf, fmaxf(ray.tmin, t0), fminf(ray.tmax, t1), f.numPrimaryChannels, st);
     if (ir.t_hit >= 0.f) {
       result.primID = PRIMID_ISOSURFACE; result.t_hit = ir.t_hit / dt_scale;
       result.Ng = normalize(ir.grad); result.ambient = 0.f; result.base = v3(pc.x, pc.y, pc.z);
@@ -1096,7 +1127,7 @@ extern "C" int orc_render(const OrcScene *sp, const OrcFrame *fp, int x0, int y0
           float t0, t1; int leaf = closestRegion(s, volActive, ray, t0, t1);
           if (leaf < 0) break;
           IntResult ir; ir.pc = &pc;
-          integrateBrick(s, f, ir, offs, ray, leaf, t0, t1, f.numPrimaryChannels, f.gradientShadingDVR != 0, &st);
+          integrateBrick(s, f, volActive, ir, offs, ray, leaf, t0, t1, f.numPrimaryChannels, f.gradientShadingDVR != 0, &st);
           if (pc.w >= f.ertThreshold) { pc = V4{pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f}; break; }
           already = t1 * 1.0000001f;
         }

@@ -79,6 +79,8 @@ typedef struct OrcFrame {
      concatenated: vertices 3*numVerts floats, indices 3*numTris ints */
   int32_t numMeshVerts, numMeshTris;
   const float *meshVerts; const int32_t *meshIndex;
+  /* 1: gradients by central differences, the reference built with -DANALYTIC_GRADIENTS=0 (exabrick.cu:833-880, 928-931) */
+  int32_t centralDifferences;
 } OrcFrame;
 
 typedef struct OrcStats {          /* counters for the algorithmic-bytes model */

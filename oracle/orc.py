@@ -47,6 +47,7 @@ class OrcFrame(C.Structure):
         ("worldLo", C.c_float * 3), ("worldHi", C.c_float * 3),
         ("numMeshVerts", C.c_int32), ("numMeshTris", C.c_int32),
         ("meshVerts", C.POINTER(C.c_float)), ("meshIndex", C.POINTER(C.c_int32)),
+        ("centralDifferences", C.c_int32),
     ]
 
 
@@ -203,9 +204,14 @@ def have_ref_shader():
     return os.path.exists(os.path.join(REF_DIR, "ref_shader"))
 
 
-def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None):
+def have_ref_shader_cd():
+    return os.path.exists(os.path.join(REF_DIR, "ref_shader_cd"))
+
+
+def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None, binary="ref_shader"):
     """one frame through the reference's OWN device source programs/exabrick.cu compiled as C++
-    (oracle/ref_shader_main.cpp + ref_shim/shader_shim.h) -> (accum float32[H,W,4], rgba8 uint32[H,W])"""
+    (oracle/ref_shader_main.cpp + ref_shim/shader_shim.h) -> (accum float32[H,W,4], rgba8 uint32[H,W]);
+    binary = "ref_shader_cd": the build with -DANALYTIC_GRADIENTS=0"""
     bf = os.path.join(workdir, "s.bricks")
     open(bf, "wb").write(bricks_raw)
     sfs = []
@@ -231,7 +237,7 @@ def ref_render(bricks_raw, fields, frame, workdir, accum=None, window=None):
     env = dict(os.environ)
     if window:
         env["ORC_WINDOW"] = ",".join(str(int(x)) for x in window)
-    subprocess.check_call([os.path.join(REF_DIR, "ref_shader"), bf, ff, of] + sfs, stdout=subprocess.DEVNULL, env=env)
+    subprocess.check_call([os.path.join(REF_DIR, binary), bf, ff, of] + sfs, stdout=subprocess.DEVNULL, env=env)
     raw = open(of, "rb").read()
     acc = np.frombuffer(raw[:W * H * 16], np.float32).reshape(H, W, 4).copy()
     rgba = np.frombuffer(raw[W * H * 16:W * H * 20], np.uint32).reshape(H, W).copy()

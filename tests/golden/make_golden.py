@@ -64,6 +64,7 @@ def main():
     json.dump(hashes, open(os.path.join(HERE, "golden_hashes.json"), "w"), indent=1, sort_keys=True)
     raw2cells_golden()
     ref_shader_golden()
+    ref_shader_cd_golden()
     points_golden(hashes)
     config_golden()
     colormap_golden()
@@ -105,6 +106,22 @@ def raw2cells_golden():
         print("raw2cells", i, fmt, vol.shape, len(out["scalars%d" % i]), "cells, levels", np.unique(out["cells%d" % i][:, 3]))
     np.savez_compressed(os.path.join(HERE, "raw2cells.npz"), **out)
 
+
+
+def ref_shader_cd_golden():
+    """the gradient-shaded frames again through the reference built with -DANALYTIC_GRADIENTS=0 (oracle/_ref/ref_shader_cd)"""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_shader_cases as RC
+    assert orc.have_ref_shader_cd(), "run `make -C oracle ref` first"
+    out = {}
+    for name, kind, channels, mlw, configure in RC.cd_cases():
+        raw, fields, dom, _ = RC.build(orc, kind, channels, mlw)
+        fd = RC.frame(dom, channels, configure)
+        with tempfile.TemporaryDirectory() as d:
+            acc, rgba = orc.ref_render(raw, fields, fd.to_orc(orc), d, binary="ref_shader_cd")
+        out[name + "_accum"], out[name + "_rgba"] = acc, rgba
+        print("ref_shader_cd", name, "max colour %.3f" % acc[..., :3].max())
+    np.savez_compressed(os.path.join(HERE, "ref_shader_frames_cd.npz"), **out)
 
 
 def ref_shader_golden():

@@ -178,6 +178,23 @@ def cases(extra=False):
     yield "x_iso_colormap_second_channel", "nb32", 2, 127, colormap_second
 
 
+CD_CASES = ["dvr", "dvr_thin_dt", "dvr_2ch_small_bricks", "dvr_partial_xf", "dvr_clip_transform", "dvr_camera_inside",
+            "iso", "two_iso_2ch", "x_iso_ch1_ao", "x_iso_camera_inside"]
+
+
+def cd_cases():
+    """the frames with gradient shading among the cases above, with gradients by central differences (the reference
+    built with -DANALYTIC_GRADIENTS=0, oracle/_ref/ref_shader_cd): name "cd_<case>" """
+    for name, kind, channels, mlw, configure in cases(extra=True):
+        if name not in CD_CASES:
+            continue
+
+        def cfg(fd, dom, configure=configure):
+            configure(fd, dom)
+            fd.central_differences = True
+        yield "cd_" + name, kind, channels, mlw, cfg
+
+
 def build(orc, kind, channels, mlw):
     cells, fields, dom = scenes.small_scene(kind, channels)
     raw = orc.build_bricks(cells, mlw)

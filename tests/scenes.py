@@ -45,6 +45,7 @@ class FrameDesc:
         self.world = ((0.0, 0.0, 0.0), (1.0, 1.0, 1.0))
         self.mesh = None                                 # (vertices float32[n,3], indices int32[m,3]), world space
         self.colormap_second = False                     # oracle only: the reference's !multiFieldDvr mode (OptixRenderer.cpp:277-283)
+        self.central_differences = False                 # gradients as in the reference built with ANALYTIC_GRADIENTS=0
 
     def to_orc(self, orc):
         f = orc.OrcFrame()
@@ -58,6 +59,7 @@ class FrameDesc:
         f.numPrimaryChannels, f.colormapChannel = (1, 1) if self.colormap_second else (self.num_channels, 0)
         f.gradientShadingDVR, f.gradientShadingISO = int(self.grad_dvr), int(self.grad_iso)
         f.spaceSkipping = int(self.space_skipping)
+        f.centralDifferences = int(self.central_differences)
         f.xfOpacityScale = self.opacity_scale
         for c in range(self.num_channels):
             f.xfDomain[c][0], f.xfDomain[c][1] = self.xf_domain[c]

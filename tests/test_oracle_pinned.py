@@ -64,6 +64,27 @@ def test_oracle_equals_reference_shader_live(orc, case, monkeypatch):
     _compare(case[0], acc, rgba, racc, rrgba)
 
 
+CD_CASES = list(RC.cd_cases())
+
+
+@pytest.mark.parametrize("case", CD_CASES, ids=[c[0] for c in CD_CASES])
+def test_oracle_central_differences_equal_reference_build(orc, case, monkeypatch):
+    """the reference's off-default gradient option (-DANALYTIC_GRADIENTS=0: gradientCD, exabrick.cu:833-880): the oracle
+    with OrcFrame.centralDifferences against frames of oracle/_ref/ref_shader_cd (tests/golden/ref_shader_frames_cd.npz;
+    live too where the binary is present), and the frames do differ from the analytic-gradient ones"""
+    g = np.load(os.path.join(GOLDEN, "ref_shader_frames_cd.npz"))
+    raw, fields, fd, _, acc, rgba = _oracle_frame(orc, case, monkeypatch)
+    _compare(case[0], acc, rgba, g[case[0] + "_accum"], g[case[0] + "_rgba"])
+    fd.central_differences = False
+    acc_a, _, _ = RC.build(orc, case[1], case[2], case[3])[3].render(fd.to_orc(orc))
+    assert np.abs(acc_a[..., :3] - acc[..., :3]).max() > 0.02
+    if orc.have_ref_shader_cd() and case[0] in ("cd_dvr", "cd_iso", "cd_x_iso_ch1_ao"):
+        fd.central_differences = True
+        with tempfile.TemporaryDirectory() as d:
+            racc, rrgba = orc.ref_render(raw, fields, fd.to_orc(orc), d, binary="ref_shader_cd")
+        _compare(case[0], acc, rgba, racc, rrgba)
+
+
 def test_rnd_order_is_the_only_difference(orc, golden, monkeypatch):
     """with nvcc's left-to-right order (the product's and the oracle's default) the same frame differs
     from the g++-compiled reference only through the swapped pixel jitter"""
