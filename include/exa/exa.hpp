@@ -284,6 +284,7 @@ struct OptixRenderer {
   { detail::check(exa_renderer_update_contour_planes(handle, &normals[0].x, offsets, channels, enabled)); }
   // the viewer pokes frameState.ao directly (viewer.cpp:953-954); here it is a call
   void setAO(bool enable, float length) { detail::check(exa_renderer_set_ao(handle, enable, length)); }
+  void setCentralDifferenceGradients(bool on) { detail::check(exa_renderer_set_gradient_mode(handle, on ? EXA_GRADIENTS_CENTRAL_DIFFERENCES : EXA_GRADIENTS_ANALYTIC)); }   // the reference: -DANALYTIC_GRADIENTS=0 at build time
   void setClockScale(float s) { detail::check(exa_renderer_set_clock_scale(handle, s)); }   // the viewer writes frameState.clockScale (viewer.cpp:956)
   void updateCamera(const vec3f &pos, const vec3f &dir00, const vec3f &dirDu, const vec3f &dirDv)
   { detail::check(exa_renderer_update_camera(handle, &pos.x, &dir00.x, &dirDu.x, &dirDv.x)); }

@@ -291,6 +291,13 @@ int exa_renderer_update_dt(exa_renderer_t *r, float dt);                        
 int exa_renderer_set_space_skipping(exa_renderer_t *r, int enable);                  /* :418-432 */
 int exa_renderer_set_gradient_shading_dvr(exa_renderer_t *r, int enable);            /* :434-437 */
 int exa_renderer_set_gradient_shading_iso(exa_renderer_t *r, int enable);            /* :439-442 */
+/* How the gradients of the two shading options above are computed.  ANALYTIC (default) is the reference's default build
+ * (-DANALYTIC_GRADIENTS=1: quotient rule over the tent-basis sums, exabrick.cu:913-927); CENTRAL_DIFFERENCES is its
+ * off-default build (-DANALYTIC_GRADIENTS=0: gradientCD, :833-880, six more point samples at +-(finestLevelCellWidth+1)/2,
+ * each located among the ACTIVE regions).  A run-time switch here, a compile-time one in the reference.  Not available
+ * together with the instrumented (stats) frame. */
+enum { EXA_GRADIENTS_ANALYTIC = 0, EXA_GRADIENTS_CENTRAL_DIFFERENCES = 1 };
+int exa_renderer_set_gradient_mode(exa_renderer_t *r, int mode);
 int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], const float hi[3]);
 /* updateContourPlanes(normals, offsets, channels, enabled) (OptixRenderer.cpp:504-531): arrays of
  * EXA_MAX_CONTOUR_PLANES; normals are normalised; offset is in the unit cube that is scaled to

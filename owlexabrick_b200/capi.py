@@ -17,6 +17,7 @@ lib = C.CDLL(LIB_PATH)
 EXA_OK, EXA_ERR_INVALID, EXA_ERR_IO, EXA_ERR_CUDA, EXA_ERR_LIMIT = range(5)
 BUILDER_SPATIAL_MEDIAN, BUILDER_SAH_ALIKE = 0, 1
 PARTITION_NONE, PARTITION_SORT_LAST, PARTITION_IMAGE_TILES = 0, 1, 2
+GRADIENTS_ANALYTIC, GRADIENTS_CENTRAL_DIFFERENCES = 0, 1
 NOALLOC_MAX_POINTS = 65536          # EXA_NOALLOC_MAX_POINTS (include/exabrick_b200.h)
 LAYOUT_AUTO, LAYOUT_FLAT, LAYOUT_DUAL = 0, 1, 2
 
@@ -101,6 +102,7 @@ _SIG = {
     "exa_renderer_set_space_skipping": (i32, [vp, i32]),
     "exa_renderer_set_gradient_shading_dvr": (i32, [vp, i32]),
     "exa_renderer_set_gradient_shading_iso": (i32, [vp, i32]),
+    "exa_renderer_set_gradient_mode": (i32, [vp, i32]),
     "exa_renderer_set_clip_box": (i32, [vp, i32, vp, vp]),
     "exa_renderer_update_contour_planes": (i32, [vp, vp, vp, vp, vp]),
     "exa_renderer_set_ao": (i32, [vp, i32, f32]),

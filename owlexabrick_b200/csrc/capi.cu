@@ -34,7 +34,7 @@ struct exa_renderer {
   ExaFrameState fs; ExaLaunchParams lp;
   float4 *d_xf = nullptr;                // [numFields][128]
   float dt = 0.5f; float ert = 0.98f;
-  int spaceSkipping = 1, gradDVR = 1, gradISO = 1;
+  int spaceSkipping = 1, gradDVR = 1, gradISO = 1, gradCD = 0;
   bool masksDirty = true;
   uint8_t *d_volActive = nullptr, *d_isoActive = nullptr /* = d_volActive + numKdNodes */, *d_regionActive = nullptr /* = d_volActive + 2 numKdNodes */, *d_inPart = nullptr; int *d_kdParent = nullptr;
   // framebuffer
@@ -174,7 +174,7 @@ static void fillParams(exa_renderer *r, RenderParams &P)
   }
   P.width = r->width; P.height = r->height; P.frameID = r->fs.frameID; P.dt = r->dt;
   P.numChannels = r->numFields; P.colormapChannel = 0;     // multiFieldDvr (OptixRenderer.h:110, .cpp:276-283)
-  P.gradDVR = r->gradDVR; P.gradISO = r->gradISO;
+  P.gradDVR = r->gradDVR; P.gradISO = r->gradISO; P.gradCD = r->gradCD;
   P.xfOpacityScale = r->fs.xfOpacityScale; P.clockScale = r->fs.clockScale;
   memcpy(P.xfDomain, r->fs.xfDomain, sizeof(P.xfDomain));
   P.xf = r->d_xf;
@@ -791,6 +791,11 @@ int exa_renderer_update_dt(exa_renderer_t *r, float dt) { if (!r || !(dt > 0.f))
 int exa_renderer_set_space_skipping(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->spaceSkipping = enable != 0; r->masksDirty = true; return EXA_OK; }
 int exa_renderer_set_gradient_shading_dvr(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->gradDVR = enable != 0; return EXA_OK; }
 int exa_renderer_set_gradient_shading_iso(exa_renderer_t *r, int enable) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->gradISO = enable != 0; return EXA_OK; }
+int exa_renderer_set_gradient_mode(exa_renderer_t *r, int mode)
+{
+  if (!r || (mode != EXA_GRADIENTS_ANALYTIC && mode != EXA_GRADIENTS_CENTRAL_DIFFERENCES)) { setError("set_gradient_mode: bad argument"); return EXA_ERR_INVALID; }
+  r->gradCD = mode == EXA_GRADIENTS_CENTRAL_DIFFERENCES; return EXA_OK;
+}
 int exa_renderer_set_ert_threshold(exa_renderer_t *r, float t) { if (!r) { setError("null renderer"); return EXA_ERR_INVALID; } r->ert = t; return EXA_OK; }
 int exa_renderer_set_clip_box(exa_renderer_t *r, int enable, const float lo[3], const float hi[3])
 {

@@ -88,6 +88,7 @@ static int doRender(exa_renderer *r, float4 *partialOut, float4 *partialSurf, Ex
       for (int d = 0; d < 3; d++) { P.coneLo[d] = r->coneLo[d]; P.coneCell[d] = r->coneCell[d]; P.coneInvCell[d] = 1.f / r->coneCell[d]; }
     } else P.traces = nullptr;                               // every visible segment has a dead end
   }
+  if (stats && P.gradCD) { setError("render_stats: the instrumented frame is not available with central-difference gradients"); return EXA_ERR_INVALID; }
   if (stats) { CKR(cudaMemsetAsync(r->d_stats, 0, 64, r->stream)); P.stats = r->d_stats; }
   if (partialOut && sortLastParts(r) && P.anySurf != 2 && !P.tileList) {
     // Sort-last partial: only the tiles that hold the projection of this part's box are launched; the rest of the partial

@@ -366,14 +366,17 @@ __device__ __forceinline__ bool sampleRegion(const DeviceScene &S, const Segment
 // 988-1016), as written: t_next = min(t_i, t1), sample at the midpoint of [t_last, t_next] with the
 // actual segment length in the opacity correction.  The caller owns the loop (k_renderFrame runs
 // it as a flat per-lane state machine so that the lanes of a warp stay converged).
-template <bool GRAD, bool STATS, bool DUAL>
+template <bool DUAL> __device__ float3 gradientCD(const RenderParams &P, bool iso, float3 pos, float delta, int channel);
+
+template <bool GRAD, bool STATS, bool DUAL, bool CD = false>
 __device__ __forceinline__ void integrateSample(const RenderParams &P, const float4 *xfTables, const float *xfK, const Segment &seg,
                                                 float3 o, float3 d, float t_sample, float actual_dt, float4 &pc, RayStats &rs)
 {
   const float3 pos = rayAt(o, d, t_sample);
   for (int c = 0; c < P.numChannels; c++) {
     float v = 0.f; float3 g = f3(0, 0, 0);
-    if (sampleRegion<GRAD, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
+    if (sampleRegion<GRAD && !CD, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs) && actual_dt != 0.f) {
+      if (GRAD && CD) g = gradientCD<DUAL>(P, false, pos, (seg.fcw + 1.f) * .5f, c);      // samplePointWithDerivative<false>, central differences (:928-931)
       float4 s = lookupXFfast(xfTables + c * 128, P.xfDomain[c][0], xfK[c], P.xfOpacityScale, v);
       if (GRAD) {
         const float gg = dot3(g, g), thr = (float)(int)seg.fcw * 1e-6f;
@@ -396,7 +399,7 @@ __device__ __forceinline__ void integrateSample(const RenderParams &P, const flo
 }
 
 // IsoSurfaceIntegrationFunction::operator() (exabrick.cu:1024-1109) for channel `c`
-template <bool STATS, bool DUAL>
+template <bool STATS, bool DUAL, bool CD = false>
 __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
                                            int c, float t_sample, float cellValue, float &lastT, float &lastV,
                                            float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
@@ -414,7 +417,8 @@ __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *
         float4 smp = make_float4(1.f, 0.f, 0.f, 1.f);
         const int ich = P.isoChannel[i];
         if (P.gradISO) {
-          if (sampleRegion<true, STATS, DUAL>(P.scene, seg, ich, isopt, cv, grad, rs)) {
+          if (sampleRegion<!CD, STATS, DUAL>(P.scene, seg, ich, isopt, cv, grad, rs)) {
+            if (CD) grad = gradientCD<DUAL>(P, true, isopt, (seg.fcw + 1.f) * .5f, ich);     // samplePointWithDerivative<true>: the iso-surface BVH
             smp = lookupXF(xfTables + ich * 128, P.xfDomain[ich][0], P.xfDomain[ich][1], P.xfOpacityScale, cv);
             grad = normalize3(grad);
             if (dot3(grad, d) > 0.f) grad = f3(-grad.x, -grad.y, -grad.z);
@@ -446,7 +450,7 @@ __device__ __forceinline__ void isoFunctor(const RenderParams &P, const float4 *
 
 // isoIntegrateBrick (exabrick.cu:1187-1256), as written; per-channel functor state lives in
 // this thread's column of shared memory (isoT / isoV, entry c at [c * blockDim.x])
-template <bool STATS, bool DUAL>
+template <bool STATS, bool DUAL, bool CD = false>
 __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *xfTables, const Segment &seg, float3 o, float3 d,
                                            float t0, float t1, float *isoT, float *isoV,
                                            float4 &pc, float &tHit, float3 &hitGrad, RayStats &rs)
@@ -463,11 +467,12 @@ __device__ __forceinline__ void isoSegment(const RenderParams &P, const float4 *
     const float3 pos = rayAt(o, d, t_sample);
     for (int c = 0; c < P.numChannels; c++) {
       float v = 0.f; float3 g = f3(0, 0, 0); bool ok;
-      if (P.gradISO) ok = sampleRegion<true, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs);
+      // (the gradient of these samples is never used; the central-difference build's six extra samples are not taken)
+      if (P.gradISO && !CD) ok = sampleRegion<true, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs);
       else ok = sampleRegion<false, STATS, DUAL>(P.scene, seg, c, pos, v, g, rs);
       if (ok) {
         float lt = isoT[c * stride], lv = isoV[c * stride];
-        isoFunctor<STATS, DUAL>(P, xfTables, seg, o, d, c, t_sample, v, lt, lv, pc, tHit, hitGrad, rs);
+        isoFunctor<STATS, DUAL, CD>(P, xfTables, seg, o, d, c, t_sample, v, lt, lv, pc, tHit, hitGrad, rs);
         isoT[c * stride] = lt; isoV[c * stride] = lv;
         if (pc.w >= P.ertThreshold) break;
       }
@@ -497,7 +502,7 @@ __device__ __forceinline__ bool locate(const DeviceScene &S, float px, float py,
 // traceIsoRay (exabrick.cu:1408-1460): march the iso-active regions front to back with lattice
 // offset 0 until two consecutive valid samples bracket an enabled iso value.
 // (not __noinline__: ptxas 12.9 segfaults on an out-of-line copy of this function)
-template <bool STATS, bool DUAL>
+template <bool STATS, bool DUAL, bool CD = false>
 __device__ void traceIsoRay(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
                                          float3 o, float3 d, float tmin, float tmax, SurfHit &out, RayStats &rs)
 {
@@ -512,7 +517,7 @@ __device__ void traceIsoRay(const RenderParams &P, const float4 *xfTables, uint2
     Segment seg;
     if (!travNext<STATS>(T, vo, vd, P.scene, P.isoActive, already, rtmax, seg)) break;
     float4 ipc = make_float4(0, 0, 0, 0); float th = -1.f; float3 hg = f3(0, 0, 0);
-    isoSegment<STATS, DUAL>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
+    isoSegment<STATS, DUAL, CD>(P, xfTables, seg, vo, vd, fmaxf(already, seg.t0), fminf(rtmax, seg.t1), isoT, isoV, ipc, th, hg, rs);
     if (th >= 0.f) {
       out.prim = PRIM_ISOSURFACE; out.t = th / dtScale; out.Ng = normalize3(hg); out.ambient = 0.f; out.base = f3(ipc.x, ipc.y, ipc.z);
       return;
@@ -637,7 +642,7 @@ __device__ __noinline__ void traceMesh(const RenderParams &P, float3 o, float3 d
 
 // ALL = false: iso-surfaces only (the instantiation the iso + DVR workload C4 runs; meshes, planes,
 // cones and AO cost it registers and 10 % of its frame time when compiled in)
-template <bool STATS, bool DUAL, bool ALL>
+template <bool STATS, bool DUAL, bool ALL, bool CD = false>
 __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float4 *xfTables, uint2 *stack, float *isoT, float *isoV,
                                               float3 o, float3 d, float tmin, float tmax, bool withContourPlanes, SurfHit &prd, RayStats &rs)
 {
@@ -651,7 +656,7 @@ __device__ __forceinline__ void traceSurfaces(const RenderParams &P, const float
     }
   }
   if (P.anyIso) {
-    SurfHit iso; traceIsoRay<STATS, DUAL>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, iso, rs);
+    SurfHit iso; traceIsoRay<STATS, DUAL, CD>(P, xfTables, stack, isoT, isoV, o, d, tmin, tmax, iso, rs);
     if (iso.prim == PRIM_ISOSURFACE && iso.t < prd.t) prd = iso;
   }
 }
@@ -710,7 +715,7 @@ __host__ __device__ inline int numOwnedTiles(int numTiles, int rank, int numRank
 // Measured and dropped in round 1 (profiles/perf_quick_r01_*; the code is in the history before round 2): a
 // one-node traversal look-ahead, the first region by point location, next-record L1 prefetch, and a second
 // kernel that finishes long rays one warp per ray.  All parity-green, all slower on an issue-bound kernel.
-template <bool GRAD, bool STATS, bool DUAL, int SURF>
+template <bool GRAD, bool STATS, bool DUAL, int SURF, bool CD = false>
 __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFrame(const __grid_constant__ RenderParams P)
 {
   extern __shared__ uint4 smem[];
@@ -800,7 +805,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       float *isoT = isoBase + threadIdx.x, *isoV = isoBase + (size_t)P.numChannels * FRAME_THREADS + threadIdx.x;
       const float3 ow = f3(P.camPos[0], P.camPos[1], P.camPos[2]);
       SurfHit sh;
-      traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, ow, d, tmin, tmax, true, sh, rs);
+      traceSurfaces<STATS, DUAL, SURF == 2, CD>(P, xfTables, stack, isoT, isoV, ow, d, tmin, tmax, true, sh, rs);
       surfT = sh.t;
       if (sh.prim != PRIM_NONE) {
         // sort-last: an iso-surface hit lies inside THIS rank's part (everything behind the part is hidden); meshes, planes
@@ -815,7 +820,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
             const float u1 = rnd.next(), u2 = rnd.next();
             const float3 adir = surf::aoDirection(sh.Ng, u1, u2);
             SurfHit ah;                                       // ST_ALL_SURFACES & ~ST_CONTOUR_PLANES (:1638-1640)
-            traceSurfaces<STATS, DUAL, SURF == 2>(P, xfTables, stack, isoT, isoV, isect, adir, 1e-4f, P.aoLength, false, ah, rs);
+            traceSurfaces<STATS, DUAL, SURF == 2, CD>(P, xfTables, stack, isoT, isoV, isect, adir, 1e-4f, P.aoLength, false, ah, rs);
             if (ah.prim != PRIM_NONE) hitCnt++;
           }
           const float shadow = aoSamples ? (float)hitCnt / (float)aoSamples : 0.f;
@@ -861,7 +866,7 @@ __global__ void __launch_bounds__(FRAME_THREADS, EXA_FRAME_MINBLOCKS) k_renderFr
       const float t_sample = 0.5f * (t_next + t_last);
       const float actual_dt = t_next - t_last;
       t_last = t_next;
-      integrateSample<GRAD, STATS, DUAL>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
+      integrateSample<GRAD, STATS, DUAL, CD>(P, xfTables, xfK, seg, o, d, t_sample, actual_dt, pc, rs);
       if (pc.w >= P.ertThreshold) {                                                                               // :1180, :1694-1697
         if (P.partialOut) pc.w += 2.f; else pc = make_float4(pc.x * pc.w, pc.y * pc.w, pc.z * pc.w, 1.f);
         live = false;
@@ -929,8 +934,22 @@ int launchRenderFrame(const RenderParams &P, cudaStream_t s)
     else if (P.anySurf) k_renderFrame<G, S_, D_, 1><<<grid, block, smemBytes, s>>>(P);                      \
     else k_renderFrame<G, S_, D_, 0><<<grid, block, smemBytes, s>>>(P); }
 #define LAUNCH_D(G, S_) { if (P.scene.dual) LAUNCH(G, S_, true) else LAUNCH(G, S_, false) }
-  if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
+  // central-difference gradients (the reference's ANALYTIC_GRADIENTS=0 build): separate instantiations, so that the default
+  // kernels are the code they were; only where a gradient is used at all (DVR shading, or shaded iso-surfaces)
+  const bool cd = P.gradCD && !stats && (P.gradDVR || (P.anySurf && P.gradISO));
+#define LAUNCH_CD(G, D_, SF)                                                                                \
+  { static size_t capCd[64] = {}; size_t &capC = capCd[dev];                                                \
+    if (smemBytes > capC) { cudaFuncSetAttribute(k_renderFrame<G, false, D_, SF, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes); capC = smemBytes; } \
+    k_renderFrame<G, false, D_, SF, true><<<grid, block, smemBytes, s>>>(P); }
+#define LAUNCH_CD_D(G, SF) { if (P.scene.dual) LAUNCH_CD(G, true, SF) else LAUNCH_CD(G, false, SF) }
+  if (cd) {
+    if (P.gradDVR) { if (P.anySurf == 2) LAUNCH_CD_D(true, 2) else if (P.anySurf) LAUNCH_CD_D(true, 1) else LAUNCH_CD_D(true, 0) }
+    else { if (P.anySurf == 2) LAUNCH_CD_D(false, 2) else LAUNCH_CD_D(false, 1) }
+  }
+  else if (P.gradDVR) { if (stats) LAUNCH_D(true, true) else LAUNCH_D(true, false) }
   else { if (stats) LAUNCH_D(false, true) else LAUNCH_D(false, false) }
+#undef LAUNCH_CD_D
+#undef LAUNCH_CD
 #undef LAUNCH_D
 #undef LAUNCH
   return cudaGetLastError() == cudaSuccess ? 1 : -1;
@@ -978,6 +997,44 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
   accumBricks<GRAD, STATS, DUAL>(a, ldg256(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
   return accFinish<GRAD>(a, value, g);
+}
+
+// gradientCD<ISO> (exabrick.cu:833-880, FAST_CENTRAL_DIFFERENCES off) for samplePointWithDerivative of the reference built
+// with ANALYTIC_GRADIENTS=0 (:928-931): six more samples at pos -+ delta along the axes.  The reference locates each with a
+// ray of length 2e-10 through the BVH of the ACTIVE regions (volume BVH, iso-surface BVH for ISO): here the point location
+// (regions are half-open boxes, as that ray sees them) followed by the activity test of the region found - the per-region
+// volume mask, or the iso values against the region's value range.  Outside every active region, and (decided; the
+// reference reads an uninitialised float) where the sample is invalid, the sample is 0.  Result: f(pos - delta) -
+// f(pos + delta) per axis (sic).  Only the CD instantiations of the frame kernel call it (not __noinline__: ptxas 12.9
+// segfaults on an out-of-line copy, as for traceIsoRay).
+template <bool DUAL>
+__device__ float3 gradientCD(const RenderParams &P, bool iso, float3 pos, float delta, int channel)
+{
+  const DeviceScene &S = P.scene;
+  float sv[6];
+#pragma unroll 1
+  for (int k = 0; k < 6; k++) {
+    const float dd = (k & 1) ? -delta : delta;                 // j = 0: pos + dt[i], j = 1: pos - dt[i]
+    const int i = k >> 1;
+    const float qx = i == 0 ? __fadd_rn(pos.x, dd) : pos.x, qy = i == 1 ? __fadd_rn(pos.y, dd) : pos.y, qz = i == 2 ? __fadd_rn(pos.z, dd) : pos.z;
+    float v = 0.f;
+    uint32_t bo; int K;
+    if (locate(S, qx, qy, qz, bo, K, nullptr)) {
+      const uint4 h2 = __ldg(S.blobs + bo + 2);                // {regionID, value range lower, upper, -}
+      bool act = false;
+      if (iso) {
+        const float vlo = __uint_as_float(h2.y), vhi = __uint_as_float(h2.z);
+        for (int q = 0; q < EXA_MAX_ISO_SURFACES; q++) act |= P.isoEnabled[q] && P.isoValue[q] >= vlo && P.isoValue[q] <= vhi;
+      } else act = P.regionActive[(int)h2.x] != 0;
+      if (act) {
+        Acc a; accZero(a); unsigned nc = 0; float val; float3 g;
+        accumBricks<false, false, DUAL>(a, ldg256(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), qx, qy, qz, nc);
+        if (accFinish<false>(a, val, g)) v = val;
+      }
+    }
+    sv[k] = v;
+  }
+  return f3(sv[1] - sv[0], sv[3] - sv[2], sv[5] - sv[4]);
 }
 
 // 128 threads x 16 CTAs per SM = 2048 resident threads at 32 registers (12 bytes of spills): the kernel is a

@@ -21,6 +21,7 @@ struct RenderParams {
   int sceneRect[4];                    // pixel rectangle (x0, y0, x1, y1 inclusive) outside which no primary ray can hit the scene bounds (host: projected corners, grown)
   float rayLo[3], rayHi[3];            // box every primary / iso ray is clipped to before the traversal: the scene bounds, or in sort-last mode the box of this rank's part
   int gridX0, gridY0, gridW, gridH;    // gridW > 0 (sort-last partial): the grid covers only the tile rectangle that holds this part's projection; pixels outside it are not written
+  int gradCD;                          // gradients by central differences (the reference built with ANALYTIC_GRADIENTS=0) instead of the analytic ones
   float clockScale;                    // > 0: the pixel's red channel becomes min(clockScale * cycles / 1e6, 1) (exabrick.cu:1703-1707, a profiling aid)
   float camVoxel[3];                   // voxelSpaceTransform applied to camPos (host, same rounding as the device's xfmPoint): origin of every primary ray in voxel space
   float xfm[12];                       // voxelSpaceTransform: vx, vy, vz, p

@@ -416,6 +416,10 @@ class Renderer:
         """frameState.ao (programs/FrameState.h:60-63; exa/viewer.cpp:953-954)"""
         check(lib.exa_renderer_set_ao(self.h, int(bool(enable)), float(length)))
 
+    def setGradientMode(self, central_differences):
+        """gradients by central differences (the reference's ANALYTIC_GRADIENTS=0 build) instead of the analytic ones"""
+        check(lib.exa_renderer_set_gradient_mode(self.h, capi.GRADIENTS_CENTRAL_DIFFERENCES if central_differences else capi.GRADIENTS_ANALYTIC))
+
     def setClockScale(self, scale):
         """frameState.clockScale (viewer.cpp:956): > 0 = per-pixel cycle heat-map in the red channel"""
         check(lib.exa_renderer_set_clock_scale(self.h, float(scale)))

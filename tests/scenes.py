@@ -117,6 +117,7 @@ class FrameDesc:
         else:
             r.setClipBox(False)
         r.setErtThreshold(self.ert)
+        r.setGradientMode(self.central_differences)
         r.updateContourPlanes([c[1] for c in self.contour], [c[2] for c in self.contour], [c[3] for c in self.contour],
                               [c[0] for c in self.contour])
         r.setAO(self.ao[0], self.ao[1])

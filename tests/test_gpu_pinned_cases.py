@@ -36,3 +36,38 @@ def test_cuda_path_on_pinned_case(R, orc, case):
     allowed = 0.03 * err.size if name == "cones_ao_iso" else 0.01 * err.size if name in SURFACE else 0
     assert (err > RGBA_TOL).sum() <= allowed, "%s: %d pixels differ (max %.3g)" % (name, int((err > RGBA_TOL).sum()), err.max())
     assert o_acc[..., :3].max() > 0.05
+
+
+CD_CASES = list(RC.cd_cases())
+
+
+@pytest.mark.parametrize("case", CD_CASES, ids=[c[0] for c in CD_CASES])
+def test_cuda_path_central_difference_gradients(R, orc, case):
+    """exa_renderer_set_gradient_mode(CENTRAL_DIFFERENCES): the reference's off-default -DANALYTIC_GRADIENTS=0 build
+    (gradientCD, exabrick.cu:833-880).  The oracle with the same option is bit-identical to the reference's own shader
+    compiled that way (tests/test_oracle_pinned.py); here the CUDA path against that oracle, and the switch back"""
+    name, kind, channels, mlw, configure = case
+    raw, fields, dom, sc = RC.build(orc, kind, channels, mlw)
+    r = R.Renderer(R.ExaBricks.from_bytes(raw), fields)
+    fd = RC.frame(dom, channels, configure)
+    fd.apply(r)
+    r.render()
+    g_acc = r.read_accum().copy()
+    o_acc, _, _ = sc.render(fd.to_orc(orc))
+    err = np.abs(g_acc[..., :3] - o_acc[..., :3]).max(axis=-1)
+    surface = "iso" in name
+    # a shading sample that falls within rounding of a region face may be located on the other side (six more point
+    # locations per shaded sample): a few pixels on top of the surface-hit flips
+    allowed = 0.03 * err.size if "ao" in name else 0.01 * err.size if surface else 0.002 * err.size
+    assert (err > RGBA_TOL).sum() <= allowed, "%s: %d pixels differ (max %.3g)" % (name, int((err > RGBA_TOL).sum()), err.max())
+    with pytest.raises(RuntimeError, match="central-difference"):
+        r.render_stats()
+    # back to the analytic gradients: a different frame, equal to the analytic oracle frame
+    fd.central_differences = False
+    fd.apply(r)
+    r.render()
+    a_acc = r.read_accum()
+    oa_acc, _, _ = sc.render(fd.to_orc(orc))
+    assert np.abs(a_acc[..., :3] - g_acc[..., :3]).max() > 0.02
+    aerr = np.abs(a_acc[..., :3] - oa_acc[..., :3]).max(axis=-1)
+    assert (aerr > RGBA_TOL).sum() <= (0.03 * err.size if "ao" in name else 0.01 * err.size if surface else 0)
