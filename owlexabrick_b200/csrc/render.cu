@@ -55,11 +55,20 @@ __device__ __forceinline__ float comp(float3 a, int d) { return d == 0 ? a.x : d
 // One aligned 256-bit read-only load (PTX ld.global.nc.v8.f32 -> SASS LDG.E.ENL2.256, new on
 // sm_100): a 32-byte brick header or dual-cell record costs ONE L1 tag look-up per thread.
 struct __align__(32) U8 { uint4 lo, hi; };
+// L2N: with the .L2::64B qualifier (SASS LDG.E.ENL2.LTC64B.256).  A 256-bit load that misses makes the L2 fetch the whole
+// 128-byte line from DRAM; for the random records of a point query three quarters of that line are never used, and
+// .L2::64B halves the fetch (ncu: 5.36 M -> 3.28 M DRAM sectors per 1 M points, same 48.8 us).  The frame kernels keep
+// the default: their neighbouring samples do use the rest of the line (0.5-1 % slower with the qualifier).
+template <bool L2N = false>
 __device__ __forceinline__ U8 ldg256(const void *p)
 {
   U8 r;
-  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
-               : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
+  if (L2N)
+    asm volatile("ld.global.nc.L2::64B.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
+  else
+    asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w) : "l"(p));
   return r;
 }
 
@@ -81,14 +90,14 @@ __device__ __forceinline__ void accZero(Acc &a) { a.sw = 0.f; a.swv = 0.f; a.sd 
 //   sumDC.x = sum_valid (wz*wy)*sx      sumD.x = sum_valid (wz*wy)*sx*s      (sx = -1 low, +1 high)
 // into differences of the same partial sums.  Same real-number result as the reference's
 // corner loop, different fp32 rounding order (gate: 1e-5 relative).
-template <bool GRAD, bool STATS, bool DUAL>
+template <bool GRAD, bool STATS, bool DUAL, bool L2N = false>
 __device__ __forceinline__ void accumBricks(Acc &a, const U8 &hdr0, const uint4 *__restrict__ hdrs, int k, const void *__restrict__ chanV,
                                             float px, float py, float pz, unsigned &nCorners)
 {
   for (int i = 0; i < k; i++) {
     // the first brick's header travels with the region segment (registers): for the common
     // one-brick region a sample has ONE dependent load (the record), not header -> record
-    const U8 hdr = i == 0 ? hdr0 : ldg256(hdrs + 2 * i);
+    const U8 hdr = i == 0 ? hdr0 : ldg256<L2N>(hdrs + 2 * i);
     const uint4 u0 = hdr.lo, u1 = hdr.hi;
     const float invCw = __uint_as_float(u0.w);
     const int sx = (int)u1.x, sy = (int)u1.y, sz = (int)u1.z;
@@ -109,7 +118,7 @@ __device__ __forceinline__ void accumBricks(Acc &a, const U8 &hdr0, const uint4 
         const int rx = sx + 1, ry = sy + 1;
         const float4 *rec = reinterpret_cast<const float4 *>(chanV) +
                             2 * ((size_t)u1.w + (size_t)((ix0 + 1) + (iy0 + 1) * rx + (iz0 + 1) * (rx * ry)));
-        const U8 q = ldg256(rec);
+        const U8 q = ldg256<L2N>(rec);
         lo4 = make_float4(__uint_as_float(q.lo.x), __uint_as_float(q.lo.y), __uint_as_float(q.lo.z), __uint_as_float(q.lo.w));
         hi4 = make_float4(__uint_as_float(q.hi.x), __uint_as_float(q.hi.y), __uint_as_float(q.hi.z), __uint_as_float(q.hi.w));
       }
@@ -994,7 +1003,7 @@ __device__ __forceinline__ bool samplePointGlobal(const DeviceScene &S, float px
   uint32_t bo; int K;
   if (!locate(S, px, py, pz, bo, K, STATS ? kdSteps : nullptr)) return false;
   Acc a; accZero(a);
-  accumBricks<GRAD, STATS, DUAL>(a, ldg256(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
+  accumBricks<GRAD, STATS, DUAL, true>(a, ldg256<true>(S.blobs + bo + BLOB_HDR_UNITS), S.blobs + bo + BLOB_HDR_UNITS, K, chanBase<DUAL>(S, channel), px, py, pz, corners);
   if (STATS) visits += K;
   return accFinish<GRAD>(a, value, g);
 }
