@@ -520,11 +520,16 @@ class Renderer:
     def launch_count(self):
         return int(lib.exa_renderer_launch_count(self.h))
 
-    def sample_points(self, xyz, channel=0, grad=False):
+    def sample_points(self, xyz, channel=0, grad=False, out=None):
+        """out = (values, valid[, grad]): arrays to fill (a caller in a loop reuses them; fresh arrays cost a page fault per
+        4 KB on top of the query)"""
         xyz = np.ascontiguousarray(xyz, dtype=np.float32).reshape(-1, 3)
         n = len(xyz)
-        val, ok = np.zeros(n, np.float32), np.zeros(n, np.uint8)
-        g = np.zeros((n, 3), np.float32) if grad else None
+        if out is not None:
+            val, ok, g = out[0], out[1], (out[2] if grad else None)
+        else:
+            val, ok = np.zeros(n, np.float32), np.zeros(n, np.uint8)
+            g = np.zeros((n, 3), np.float32) if grad else None
         check(lib.exa_sample_points_host(self.h, _p(xyz), n, channel, _p(val), _p(ok), _p(g)))
         return (val, ok, g) if grad else (val, ok)
 
