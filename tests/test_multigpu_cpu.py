@@ -100,3 +100,43 @@ def test_spans_strips_and_tiles_partition_the_frame():
             assert multigpu.weighted_strip_rows([3.0] * world, height) == [s[0] for s in strips] + [height]
         tiles = [set(multigpu.owned_tiles(r, world, 1024, 1024)) for r in range(world)]
         assert sum(len(t) for t in tiles) == 64 * 128 and len(set.union(*tiles)) == 64 * 128
+
+
+def test_cost_balanced_tile_deal_and_strip_rows_in_the_library():
+    """exa_balance_tiles / exa_strip_rows are host-only entry points of the C ABI (no GPU needed): the LPT deal is a
+    partition of the tiles, deterministic, balanced to within the heaviest tile, capped at ~1.25x a rank's share of the
+    tile COUNT (zero-cost tails), and every rank's list is sorted by descending cost; the strips equal the Python mirror"""
+    import ctypes as C
+    from owlexabrick_b200 import build, capi
+    build.build_lib()
+    lib = capi.lib
+    rng = np.random.RandomState(7)
+    nt = 240 * 270                                                   # 4K frame
+    costs = (rng.pareto(1.5, nt) * 2000).astype(np.uint32)           # heavy tail, like the frame's tile costs
+    costs[rng.uniform(size=nt) < 0.4] = 0                            # tiles outside the scene
+    for world in (1, 2, 3, 8, 16):
+        lists = []
+        for k in range(world):
+            mine, n = np.zeros(nt, np.uint32), C.c_int()
+            capi.check(lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, world, k, mine.ctypes.data_as(C.c_void_p), C.byref(n)))
+            again, n2 = np.zeros(nt, np.uint32), C.c_int()
+            capi.check(lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, world, k, again.ctypes.data_as(C.c_void_p), C.byref(n2)))
+            assert n.value == n2.value and np.array_equal(mine[:n.value], again[:n.value])
+            lists.append(mine[:n.value].copy())
+        allt = np.concatenate(lists)
+        assert len(allt) == nt and len(np.unique(allt)) == nt       # a partition of the frame's tiles
+        loads = np.array([costs[l].astype(np.int64).sum() for l in lists], np.float64)
+        assert loads.max() - loads.min() <= costs.max() + len(lists[0])
+        share = (nt + world - 1) // world
+        assert max(len(l) for l in lists) <= share + nt // (4 * world) + 1
+        for l in lists:
+            c = costs[l].astype(np.int64)
+            assert (np.diff(c) <= 0).all()                           # most expensive first: the launch order of the rank
+    assert lib.exa_balance_tiles(costs.ctypes.data_as(C.c_void_p), nt, 4, 4, costs.ctypes.data_as(C.c_void_p), C.byref(C.c_int())) == capi.EXA_ERR_INVALID
+    for world in (1, 2, 3, 5, 8, 16):
+        for height in (2160, 1080, 116, 9, 5):
+            for k in range(world):
+                y0, y1 = C.c_int(), C.c_int()
+                capi.check(lib.exa_strip_rows(k, world, height, C.byref(y0), C.byref(y1)))
+                assert (y0.value, y1.value) == multigpu.strip_rows(k, world, height)
+    assert lib.exa_strip_rows(3, 3, 100, C.byref(C.c_int()), C.byref(C.c_int())) == capi.EXA_ERR_INVALID
